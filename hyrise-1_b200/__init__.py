@@ -1,0 +1,211 @@
+"""hyrise-1_b200 — B200-native JoinHash (Hyrise's radix-partitioned hash equi-join) behind a C ABI.
+
+The product is `csrc/libhj.so` (hand-written sm_100a CUDA kernels + the C ABI of include/hj.h) and the C++ host
+shim in `host/` that keeps the reference's `JoinHash : AbstractJoinOperator` interface. This Python module is only
+the thin ctypes binding the tests and bench.py drive the library through; it contains no join logic and no CPU
+fallback: loading fails loudly when the CUDA library has not been built.
+
+Import with `importlib.import_module("hyrise-1_b200")` (the directory name is not a Python identifier).
+"""
+import ctypes as C
+import importlib
+import os
+
+import numpy as np
+
+abi = importlib.import_module(__name__ + ".abi")
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libhj.so")
+_lib = None
+
+
+class HjError(RuntimeError):
+    def __init__(self, status, msg):
+        super().__init__(f"libhj status {status}: {msg}")
+        self.status = status
+
+
+def lib():
+    """The loaded libhj.so with typed entry points. Raises if the extension is missing — there is no fallback."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(f"{LIB_PATH} not built: run `python -c 'import __graft_entry__ as g; g.build()'`")
+        _lib = abi.bind(C.CDLL(LIB_PATH))
+        if _lib.hj_abi_version() != abi.HJ_ABI_VERSION:
+            raise ImportError("libhj.so ABI version does not match hyrise-1_b200/abi.py")
+    return _lib
+
+
+def _ptr_and_keep(x):
+    """(address, object to keep alive) for a numpy array or a torch tensor (host or device)."""
+    if x is None:
+        return None, None
+    if isinstance(x, np.ndarray):
+        assert x.flags["C_CONTIGUOUS"]
+        return x.ctypes.data, x
+    # torch tensor (duck-typed so that torch is not imported when only numpy is used)
+    assert x.is_contiguous()
+    return x.data_ptr(), x
+
+
+_KEY_DTYPES = {"int32": abi.KEY_INT32, "int64": abi.KEY_INT64}
+
+
+def _dtype_name(x):
+    return str(x.dtype).replace("torch.", "")
+
+
+class RelationBuilder:
+    """Collects the per-chunk segment descriptors of one key column (hj_relation)."""
+
+    def __init__(self, location=abi.LOC_HOST):
+        self.location = location
+        self._segs = []
+        self._keep = []
+
+    def _add(self, seg, *keep):
+        self._segs.append(seg)
+        self._keep.extend(keep)
+        return self
+
+    def add_value(self, chunk_id, values, nulls=None, kind=abi.SEG_VALUE, row_offsets=None):
+        """ValueColumn<T> (or a pre-gathered ReferenceColumn with kind=SEG_GATHERED)."""
+        s = abi.Segment()
+        s.chunk_id, s.n_rows, s.kind = chunk_id, len(values), kind
+        s.key_type = _KEY_DTYPES[_dtype_name(values)]
+        s.values, k1 = _ptr_and_keep(values)
+        s.nulls, k2 = _ptr_and_keep(nulls)
+        s.row_offsets, k3 = _ptr_and_keep(row_offsets)
+        if nulls is not None:
+            assert _dtype_name(nulls) in ("uint8", "bool") and len(nulls) == len(values)
+        if row_offsets is not None:
+            assert _dtype_name(row_offsets) in ("uint32", "int32") and len(row_offsets) == len(values)
+        return self._add(s, k1, k2, k3)
+
+    def add_dict(self, chunk_id, dictionary, attr, null_value_id=None):
+        """DictionaryColumn<T> with a FixedSizeByteAligned attribute vector (uint8/uint16/uint32 or torch int types)."""
+        s = abi.Segment()
+        s.chunk_id, s.n_rows, s.kind = chunk_id, len(attr), abi.SEG_DICT
+        s.key_type = _KEY_DTYPES[_dtype_name(dictionary)]
+        width = {"uint8": 1, "uint16": 2, "int16": 2, "uint32": 4, "int32": 4}[_dtype_name(attr)]
+        s.attr_width = width
+        s.dict_n = len(dictionary)
+        s.null_value_id = len(dictionary) if null_value_id is None else null_value_id
+        s.values, k1 = _ptr_and_keep(dictionary)
+        s.attr, k2 = _ptr_and_keep(attr)
+        return self._add(s, k1, k2)
+
+    def build(self):
+        n = len(self._segs)
+        arr = (abi.Segment * max(n, 1))(*self._segs)
+        rel = abi.Relation()
+        rel.segs = C.cast(arr, C.POINTER(abi.Segment))
+        rel.n_segs = n
+        rel.location = self.location
+        rel.n_rows = sum(s.n_rows for s in self._segs)
+        rel._keep = (arr, self._keep)  # keep the descriptor array and the data alive
+        return rel
+
+
+def rowids_to_numpy(buf, n):
+    """View n hj_row_id structs as an (n, 2) uint32 array [chunk_id, chunk_offset]."""
+    return np.frombuffer(buf, dtype=np.uint32, count=2 * n).reshape(n, 2)
+
+
+class HashJoin:
+    """One hj_ctx. Mirrors the call sequence of the C++ shim's JoinHash::_on_execute: join -> fetch."""
+
+    def __init__(self, device=0, flags=0, radix_bits=-1, output_capacity=0):
+        self._l = lib()
+        opts = abi.Options()
+        opts.abi_version = abi.HJ_ABI_VERSION
+        opts.flags = flags
+        opts.radix_bits = radix_bits
+        opts.output_capacity = output_capacity
+        self._ctx = C.c_void_p()
+        st = self._l.hj_create(device, C.byref(opts), C.byref(self._ctx))
+        if st != abi.OK:
+            raise HjError(st, (self._l.hj_last_error(None) or b"").decode())
+        self.info = None
+        self._mode = None
+
+    def close(self):
+        if getattr(self, "_ctx", None):
+            self._l.hj_destroy(self._ctx)
+            self._ctx = None
+
+    __del__ = close
+
+    def _check(self, st):
+        if st != abi.OK:
+            raise HjError(st, (self._l.hj_last_error(self._ctx) or b"").decode())
+
+    def join(self, build, probe, mode, stream=None):
+        """build/probe: abi.Relation after side selection; mode: abi.MODE_* or its name. Returns hj_result_info."""
+        if isinstance(mode, str):
+            mode = abi.MODES[mode]
+        info = abi.ResultInfo()
+        self._check(self._l.hj_join(self._ctx, C.byref(build), C.byref(probe), mode, stream, C.byref(info)))
+        self.info, self._mode = info, mode
+        return info
+
+    def join_sharded(self, build, probe, mode, stream=None):
+        if isinstance(mode, str):
+            mode = abi.MODES[mode]
+        info = abi.ResultInfo()
+        self._check(self._l.hj_join_sharded(self._ctx, C.byref(build), C.byref(probe), mode, stream, C.byref(info)))
+        self.info, self._mode = info, mode
+        return info
+
+    def fetch(self, out_build=None, out_probe=None):
+        """Copies the result PosLists to host. Returns (build_side or None, probe_side) as (n, 2) uint32 arrays."""
+        n = self.info.n_rows
+        two = self.info.n_sides == 2
+        if out_probe is None:
+            out_probe = np.empty((max(n, 1), 2), dtype=np.uint32)
+        if two and out_build is None:
+            out_build = np.empty((max(n, 1), 2), dtype=np.uint32)
+        self._check(self._l.hj_fetch(self._ctx, out_build.ctypes.data if two else None, out_probe.ctypes.data, n))
+        return (out_build[:n] if two else None), out_probe[:n]
+
+    def result_device(self):
+        """(build_side device ptr or None, probe_side device ptr, n_rows) of the last join."""
+        b, p, n = C.c_void_p(), C.c_void_p(), C.c_uint64()
+        self._check(self._l.hj_result_device(self._ctx, C.byref(b), C.byref(p), C.byref(n)))
+        return b.value, p.value, n.value
+
+    def translate(self, rowids, pos_lists):
+        """hj_translate: rowids (n,2) uint32 in place through per-chunk pos lists ((m,2) uint32 arrays)."""
+        n_chunks = len(pos_lists)
+        ptrs = (C.c_void_p * max(n_chunks, 1))(*[p.ctypes.data for p in pos_lists])
+        sizes = (C.c_uint32 * max(n_chunks, 1))(*[len(p) for p in pos_lists])
+        self._check(self._l.hj_translate(self._ctx, rowids.ctypes.data, len(rowids), ptrs, sizes, n_chunks))
+        return rowids
+
+    def timings(self):
+        t = abi.Timings()
+        self._check(self._l.hj_get_timings(self._ctx, C.byref(t)))
+        d = {name: t.ms[i] for i, name in enumerate(abi.PHASES)}
+        d.update(bytes_h2d=t.bytes_h2d, bytes_d2h=t.bytes_d2h, n_kernel_launches=t.n_kernel_launches)
+        return d
+
+    def release_scratch(self):
+        self._check(self._l.hj_release_scratch(self._ctx))
+
+    def comm_init(self, unique_id, n_ranks, rank):
+        buf = (C.c_uint8 * abi.NCCL_UNIQUE_ID_BYTES)(*unique_id)
+        self._check(self._l.hj_comm_init(self._ctx, buf, n_ranks, rank))
+
+
+def comm_unique_id():
+    buf = (C.c_uint8 * abi.NCCL_UNIQUE_ID_BYTES)()
+    st = lib().hj_comm_unique_id(buf)
+    if st != abi.OK:
+        raise HjError(st, "hj_comm_unique_id failed")
+    return bytes(buf)
+
+
+def radix_bits(n_build_rows, key_type=abi.KEY_INT32):
+    return lib().hj_radix_bits(n_build_rows, key_type)

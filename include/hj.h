@@ -1,0 +1,241 @@
+/*
+ * hj.h — C ABI of libhj, the B200 (sm_100a) CUDA library behind Hyrise's JoinHash operator.
+ *
+ * This header is the whole drop-in boundary. The host shim that keeps Hyrise's
+ * `JoinHash : AbstractJoinOperator` signature (src/lib/operators/join_hash.hpp:24-45 in the
+ * reference) calls these functions from `_on_execute()`; nothing else of the reference is
+ * rebuilt. Plain C: pointers and sizes only, no C++/torch types, no exceptions cross the ABI.
+ *
+ * What each entry point replaces in the reference (paths relative to /root/reference):
+ *   hj_join          materialize_input        src/lib/operators/join_hash.cpp:203-285
+ *                    partition_radix_parallel src/lib/operators/join_hash.cpp:287-355
+ *                    build                    src/lib/operators/join_hash.cpp:127-185
+ *                    probe                    src/lib/operators/join_hash.cpp:362-466
+ *                    probe_semi_anti          src/lib/operators/join_hash.cpp:468-527
+ *                    (orchestrated as JoinHashImpl::_on_execute, join_hash.cpp:686-800)
+ *   hj_fetch         the per-partition PosLists handed to write_output_columns,
+ *                    src/lib/operators/join_hash.cpp:829-855
+ *   hj_translate     PosList dereferencing for reference-table inputs in write_output_columns,
+ *                    src/lib/operators/join_hash.cpp:584-592
+ *   hj_radix_bits    JoinHashImpl ctor heuristic, src/lib/operators/join_hash.cpp:654-668
+ *                    (re-derived for 228 KB of shared memory instead of a 256 KB L2)
+ *
+ * There is NO CPU fallback in the library: every entry point that computes needs a CUDA device
+ * and returns HJ_ERR_CUDA otherwise.
+ */
+#ifndef HJ_H_
+#define HJ_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HJ_ABI_VERSION 1
+
+/* ---- ABI constants mirrored from the reference ------------------------------------------- */
+
+/* RowID, src/lib/types.hpp:97-99: {ChunkID uint32, ChunkOffset uint32}, 8 bytes.
+ * PosList = contiguous vector<RowID> (types.hpp:138) so an hj_row_id* may alias PosList::data(). */
+typedef struct hj_row_id {
+  uint32_t chunk_id;
+  uint32_t chunk_offset;
+} hj_row_id;
+
+#define HJ_INVALID_CHUNK_ID 0xFFFFFFFFu     /* types.hpp:95  INVALID_CHUNK_ID     */
+#define HJ_INVALID_CHUNK_OFFSET 0xFFFFFFFFu /* types.hpp:94  INVALID_CHUNK_OFFSET */
+/* NULL_ROW_ID = {INVALID_CHUNK_ID, INVALID_CHUNK_OFFSET}, types.hpp:150 */
+
+/* JoinMode, src/lib/types.hpp:189 — same integer values. Outer/Cross are rejected
+ * (join_hash.cpp never receives them: lqp_translator.cpp:329-336, abstract_join_operator.cpp:19). */
+enum hj_join_mode {
+  HJ_MODE_INNER = 0,
+  HJ_MODE_LEFT = 1,
+  HJ_MODE_RIGHT = 2,
+  HJ_MODE_OUTER = 3,
+  HJ_MODE_CROSS = 4,
+  HJ_MODE_SEMI = 5,
+  HJ_MODE_ANTI = 6
+};
+
+/* DataType of the key column (src/lib/all_type_variant.hpp:34-39). Int = int32, Long = int64.
+ * The hashed type of a mixed pair is the wider integer (join_hash/hash_traits.hpp:21-25). */
+enum hj_key_type { HJ_KEY_INT32 = 0, HJ_KEY_INT64 = 1 };
+
+/* How one chunk's key column is encoded. */
+enum hj_segment_kind {
+  /* ValueColumn<T>, src/lib/storage/value_column.hpp:15-73: values T[n_rows] (+ 1 byte/row null flags) */
+  HJ_SEG_VALUE = 0,
+  /* DictionaryColumn<T>, src/lib/storage/dictionary_column.hpp:20-72 with a
+   * FixedSizeByteAlignedVector<uint8|16|32> attribute vector
+   * (storage/vector_compression/fixed_size_byte_aligned/fixed_size_byte_aligned_vector.hpp:21-51);
+   * a row is NULL iff attr[i] == null_value_id (dictionary_column_iterable.hpp:76-80). */
+  HJ_SEG_DICT = 1,
+  /* ReferenceColumn, src/lib/storage/reference_column.hpp:19-50: the shim has gathered the keys
+   * through the PosList into `values` (+ `nulls`); `row_offsets` optionally overrides the
+   * ChunkOffset reported per row (quirk Q2, reference_column_iterable.hpp:60), NULL = 0,1,2,... */
+  HJ_SEG_GATHERED = 2
+};
+
+/* Where the arrays a segment points to live. */
+enum hj_location { HJ_LOC_HOST = 0, HJ_LOC_DEVICE = 1 };
+
+typedef struct hj_segment {
+  uint32_t chunk_id;      /* ChunkID reported in emitted RowIDs (join_hash.cpp:266)        */
+  uint32_t n_rows;        /* rows in this chunk's column                                    */
+  uint8_t kind;           /* hj_segment_kind                                                */
+  uint8_t key_type;       /* hj_key_type of `values`                                        */
+  uint8_t attr_width;     /* DICT: bytes per attribute-vector entry: 1, 2 or 4              */
+  uint8_t reserved0;
+  uint32_t dict_n;        /* DICT: entries in the dictionary                                */
+  uint32_t null_value_id; /* DICT: ValueID meaning NULL (== dict_n in the reference)        */
+  uint32_t reserved1;
+  const void* values;     /* VALUE/GATHERED: T[n_rows]; DICT: sorted dictionary T[dict_n]   */
+  const uint8_t* nulls;   /* VALUE/GATHERED: 1 byte per row (non-zero = NULL) or NULL ptr   */
+  const void* attr;       /* DICT: uintW[n_rows]                                            */
+  const uint32_t* row_offsets; /* GATHERED: ChunkOffset per row, or NULL for 0..n_rows-1   */
+} hj_segment;
+
+typedef struct hj_relation {
+  const hj_segment* segs; /* one per chunk, in chunk order (host memory)                    */
+  uint32_t n_segs;
+  uint32_t location;      /* hj_location of the arrays the segments point to                */
+  uint64_t n_rows;        /* sum of segs[i].n_rows                                          */
+} hj_relation;
+
+/* ---- options, results, timings ------------------------------------------------------------ */
+
+/* Flags selecting between the reference's literal behaviour and SQL semantics for the quirks
+ * SURVEY.md §8a lists. Default (0) reproduces the reference literally. */
+#define HJ_FLAG_SQL_NULL_PROBE 0x1u /* Q4: a NULL probe key in Left/Right never matches; default:
+                                       it is looked up as its stored value (VALUE/GATHERED) or
+                                       T{} = 0 (DICT), join_hash.cpp:253,409 */
+#define HJ_FLAG_TIMINGS 0x2u        /* record per-phase CUDA-event timings (adds event overhead) */
+
+typedef struct hj_options {
+  uint32_t abi_version;       /* HJ_ABI_VERSION                                              */
+  uint32_t flags;             /* HJ_FLAG_*                                                   */
+  int32_t radix_bits;         /* <0: library heuristic (hj_radix_bits); else forced (0..15).
+                                 The reference ignores its ctor argument (quirk Q1).         */
+  uint32_t reserved0;
+  uint64_t output_capacity;   /* 0: estimate; else initial capacity of the result buffers in
+                                 rows (the library grows and re-probes on overflow)          */
+  uint64_t reserved[4];
+} hj_options;
+
+typedef struct hj_result_info {
+  uint64_t n_rows;          /* emitted result rows (pairs, or single RowIDs for Semi/Anti)    */
+  uint32_t n_sides;         /* 2 for Inner/Left/Right, 1 for Semi/Anti                        */
+  uint32_t radix_bits;      /* bits actually used                                             */
+  uint64_t n_build_tuples;  /* build rows that entered the partitioning (non-NULL keys)       */
+  uint64_t n_probe_tuples;  /* probe rows that entered the partitioning                       */
+  uint32_t n_partitions;
+  uint32_t n_overflow_partitions; /* build partitions larger than one shared-memory table     */
+  uint32_t n_probe_passes;  /* 1, or 2 when the first output capacity estimate overflowed     */
+  uint32_t reserved;
+} hj_result_info;
+
+#define HJ_N_PHASES 8
+/* phase indices of hj_timings.ms[] */
+enum hj_phase {
+  HJ_PH_H2D = 0,          /* staging host-resident segments                                 */
+  HJ_PH_MATERIALIZE = 1,  /* decode + histogram, both relations                             */
+  HJ_PH_SCATTER1 = 2,     /* radix pass 1, both relations                                   */
+  HJ_PH_SCATTER2 = 3,     /* radix pass 2, both relations                                   */
+  HJ_PH_BUILD_PROBE = 4,  /* shared-memory build + probe + emit                             */
+  HJ_PH_FINALIZE = 5,     /* overflow-partition fix-up, NULL-probe emission                 */
+  HJ_PH_D2H = 6,          /* hj_fetch copies                                                */
+  HJ_PH_TOTAL = 7         /* whole hj_join, device side                                     */
+};
+typedef struct hj_timings {
+  float ms[HJ_N_PHASES];
+  uint64_t bytes_h2d;
+  uint64_t bytes_d2h;
+  uint32_t n_kernel_launches; /* kernels of this library launched by the last hj_join       */
+  uint32_t reserved;
+} hj_timings;
+
+/* ---- status codes -------------------------------------------------------------------------- */
+enum hj_status {
+  HJ_OK = 0,
+  HJ_ERR_INVALID = 1,     /* bad argument / unsupported mode or type (the shim turns it into Fail(), utils/assert.hpp:49) */
+  HJ_ERR_CUDA = 2,        /* CUDA runtime error, no device                                   */
+  HJ_ERR_OOM = 3,         /* device allocation failed                                        */
+  HJ_ERR_CAPACITY = 4,    /* hj_fetch capacity smaller than the result                       */
+  HJ_ERR_TOO_LARGE = 5,   /* a relation has >= 2^32-1 rows                                   */
+  HJ_ERR_STATE = 6,       /* hj_fetch without a preceding successful hj_join                 */
+  HJ_ERR_COMM = 7         /* multi-GPU exchange failed                                       */
+};
+
+typedef struct hj_ctx hj_ctx; /* opaque; all library state lives here (re-entrant, one ctx per calling thread) */
+
+/* ---- entry points -------------------------------------------------------------------------- */
+
+/* Library/ABI version of the loaded .so (== HJ_ABI_VERSION it was compiled with). */
+int hj_abi_version(void);
+
+/* Creates a context on CUDA device `device_id`. `opts` may be NULL (defaults). */
+int hj_create(int device_id, const hj_options* opts, hj_ctx** out_ctx);
+void hj_destroy(hj_ctx* ctx);
+
+/* Last error text of this context (never NULL). With ctx == NULL: error of the last failed hj_create
+ * on this thread. */
+const char* hj_last_error(const hj_ctx* ctx);
+
+/* Radix bits the library would use for `n_build_rows` keys of `key_type`
+ * (replaces join_hash.cpp:654-668). Pure host arithmetic. */
+int hj_radix_bits(uint64_t n_build_rows, int key_type);
+
+/* Runs the whole join on the device and keeps the result PosLists in device memory owned by ctx.
+ * `build`/`probe` are the relations AFTER the operator's side selection (join_hash.cpp:58-76);
+ * `mode` is the operator's JoinMode. NULL keys: dropped on the build side always; on the probe
+ * side kept only for Left/Right (join_hash.cpp:715,755). Synchronous: returns when the result
+ * count is known. `cuda_stream` is a cudaStream_t (NULL = the context's own stream). */
+int hj_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, int mode,
+            void* cuda_stream, hj_result_info* out_info);
+
+/* Copies the result into caller-allocated HOST buffers (PosList::resize(n) then data()).
+ * `build_side` receives the build relation's RowIDs (NULL_ROW_ID for unmatched probe rows in
+ * Left/Right) and must be NULL for Semi/Anti; `probe_side` receives the probe relation's RowIDs.
+ * `capacity` is in rows. */
+int hj_fetch(hj_ctx* ctx, hj_row_id* build_side, hj_row_id* probe_side, uint64_t capacity);
+
+/* Device pointers to the result of the last hj_join (valid until the next hj_join/hj_destroy).
+ * `build_side` is set to NULL for Semi/Anti. */
+int hj_result_device(hj_ctx* ctx, const hj_row_id** build_side, const hj_row_id** probe_side,
+                     uint64_t* n_rows);
+
+/* A7 for reference-table inputs (join_hash.cpp:584-592): inout[i] = pos_lists[inout[i].chunk_id]
+ * [inout[i].chunk_offset], NULL_ROW_ID stays NULL_ROW_ID. All pointers are HOST memory; the gather
+ * runs on the device. `pos_list_sizes[c]` bounds-checks chunk c. */
+int hj_translate(hj_ctx* ctx, hj_row_id* inout, uint64_t n, const hj_row_id* const* pos_lists,
+                 const uint32_t* pos_list_sizes, uint32_t n_chunks);
+
+/* Per-phase timings of the last hj_join/hj_fetch (needs HJ_FLAG_TIMINGS for the per-phase split). */
+int hj_get_timings(const hj_ctx* ctx, hj_timings* out);
+
+/* Frees cached device scratch (the context stays usable). JoinHash::_on_cleanup, join_hash.cpp:89. */
+int hj_release_scratch(hj_ctx* ctx);
+
+/* ---- multi-GPU (one process per GPU) ---------------------------------------- */
+/* The exchange has no reference counterpart: both relations are split by the high bits of the
+ * key hash so that every key's rows meet on one rank, exchanged with an NCCL all-to-all over
+ * NVLink, and joined locally. RowIDs stay global, so per-rank results simply concatenate. */
+
+#define HJ_NCCL_UNIQUE_ID_BYTES 128
+/* Rank 0 calls this and broadcasts the 128 bytes to the other ranks out of band. */
+int hj_comm_unique_id(uint8_t id[HJ_NCCL_UNIQUE_ID_BYTES]);
+/* Collective over all ranks: attaches an NCCL communicator to ctx. */
+int hj_comm_init(hj_ctx* ctx, const uint8_t id[HJ_NCCL_UNIQUE_ID_BYTES], int n_ranks, int rank);
+/* Collective: like hj_join, but `build`/`probe` are this rank's shard of the relations (segments
+ * carry GLOBAL chunk ids); afterwards hj_fetch/hj_result_device return this rank's share of the
+ * result. out_info counts are per rank. */
+int hj_join_sharded(hj_ctx* ctx, const hj_relation* build_shard, const hj_relation* probe_shard,
+                    int mode, void* cuda_stream, hj_result_info* out_info);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HJ_H_ */
