@@ -60,6 +60,7 @@ class Timings(C.Structure):
 # every symbol include/hj.h declares: name -> (restype, argtypes)
 SYMBOLS = {
     "hj_abi_version": (C.c_int, []),
+    "hj_abi_sizeof": (C.c_size_t, [C.c_int]),
     "hj_create": (C.c_int, [C.c_int, C.POINTER(Options), C.POINTER(C.c_void_p)]),
     "hj_destroy": (None, [C.c_void_p]),
     "hj_last_error": (C.c_char_p, [C.c_void_p]),

@@ -1,0 +1,722 @@
+// hj_api.cu — host side of libhj: the C ABI of include/hj.h, device-memory management and kernel orchestration.
+// No CPU fallback anywhere: every compute entry point launches the sm_100a kernels of hj_kernels.cuh.
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "hj.h"
+#include "hj_kernels.cuh"
+
+using namespace hj;
+
+namespace {
+
+// ---- tuning constants -----------------------------------------------------------------------------------
+template <typename K> struct Cfg;
+template <> struct Cfg<int32_t> {
+  static constexpr int kTile1 = 8192;     // rows per CTA tile in K1 / pass 1
+  static constexpr int kItems1 = 16;      // pass 1: 512 threads x 16
+  static constexpr int kNS = 16384;       // hash-table slots per shared-memory table
+  static constexpr int kCap = 12288;      // build tuples per table (load factor <= 0.75)
+};
+template <> struct Cfg<int64_t> {
+  static constexpr int kTile1 = 4096;
+  static constexpr int kItems1 = 8;
+  static constexpr int kNS = 8192;
+  static constexpr int kCap = 6144;
+};
+constexpr int kScatterThreads = 512;
+constexpr int kItems2 = 8;                 // pass 2: 512 threads x 8 = 4096 tuples per tile
+constexpr int kTile2 = kScatterThreads * kItems2;
+constexpr int kHistThreads = 1024;
+constexpr int kJoinThreads = 1024;
+constexpr int kProbeV = 4;
+constexpr uint32_t kProbeSlice = 128 * 1024;
+constexpr int kSinglePassMaxBits = 8;
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+};
+
+thread_local std::string g_create_error;
+
+}  // namespace
+
+struct hj_ctx {
+  int device = 0;
+  int n_sms = 0;
+  hj_options opts{};
+  cudaStream_t own_stream = nullptr;
+  std::string err;
+  std::vector<DevBuf*> all_bufs;
+  // per relation (0 = build, 1 = probe)
+  DevBuf stage_in[2], segs[2], tile_seg[2], seg_row_begin[2], keys_mat[2], valid_mask[2];
+  DevBuf hist[2], part_off[2], cur1[2], cur2[2], l1_tiles[2], tup_a[2], tup_b[2];
+  DevBuf items, fin, plan, queue, cursor, matched, out_build, out_probe, misc;
+  void* pinned = nullptr;  // small pinned readback area
+  cudaEvent_t ev[HJ_N_PHASES + 2] = {};
+  // result of the last join
+  bool has_result = false;
+  uint64_t n_result = 0;
+  int n_sides = 0;
+  hj_timings timings{};
+  // multi-GPU
+  void* nccl_comm = nullptr;
+  int n_ranks = 1, rank = 0;
+
+  hj_ctx() {
+    for (DevBuf* b : {&stage_in[0], &stage_in[1], &segs[0], &segs[1], &tile_seg[0], &tile_seg[1], &seg_row_begin[0],
+                      &seg_row_begin[1], &keys_mat[0], &keys_mat[1], &valid_mask[0], &valid_mask[1], &hist[0], &hist[1],
+                      &part_off[0], &part_off[1], &cur1[0], &cur1[1], &cur2[0], &cur2[1], &l1_tiles[0], &l1_tiles[1],
+                      &tup_a[0], &tup_a[1], &tup_b[0], &tup_b[1], &items, &fin, &plan, &queue, &cursor, &matched,
+                      &out_build, &out_probe, &misc})
+      all_bufs.push_back(b);
+  }
+};
+
+namespace {
+
+int fail(hj_ctx* ctx, int status, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  if (ctx) ctx->err = buf; else g_create_error = buf;
+  return status;
+}
+
+#define HJ_CUDA(ctx, call)                                                                              \
+  do {                                                                                                  \
+    cudaError_t e_ = (call);                                                                            \
+    if (e_ != cudaSuccess)                                                                              \
+      return fail(ctx, e_ == cudaErrorMemoryAllocation ? HJ_ERR_OOM : HJ_ERR_CUDA, "%s failed: %s (%s:%d)", #call, \
+                  cudaGetErrorString(e_), __FILE__, __LINE__);                                          \
+  } while (0)
+
+#define HJ_TRY(expr)          \
+  do {                        \
+    int st_ = (expr);         \
+    if (st_ != HJ_OK) return st_; \
+  } while (0)
+
+// grow-only device buffer
+int ensure(hj_ctx* ctx, DevBuf& b, size_t bytes) {
+  if (bytes <= b.cap) return HJ_OK;
+  if (b.p) HJ_CUDA(ctx, cudaFree(b.p));
+  b.p = nullptr;
+  b.cap = 0;
+  const size_t want = (bytes + 255) & ~size_t(255);
+  HJ_CUDA(ctx, cudaMalloc(&b.p, want));
+  b.cap = want;
+  return HJ_OK;
+}
+
+struct PreparedRel {
+  RelMeta meta{};
+  std::vector<DevSegment> segs;
+  bool has_dict = false;
+  bool has_int64 = false;
+  uint32_t mask_words = 0;
+  uint64_t h2d_bytes = 0;
+};
+
+int validate_relation(hj_ctx* ctx, const hj_relation* r, const char* name) {
+  if (!r) return fail(ctx, HJ_ERR_INVALID, "%s relation is NULL", name);
+  if (r->n_segs && !r->segs) return fail(ctx, HJ_ERR_INVALID, "%s relation has no segment array", name);
+  if (r->location != HJ_LOC_HOST && r->location != HJ_LOC_DEVICE)
+    return fail(ctx, HJ_ERR_INVALID, "%s relation: bad location %u", name, r->location);
+  uint64_t n = 0;
+  for (uint32_t i = 0; i < r->n_segs; ++i) {
+    const hj_segment& s = r->segs[i];
+    if (s.key_type != HJ_KEY_INT32 && s.key_type != HJ_KEY_INT64)
+      return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: key type %u unsupported (int32/int64 keys only)", name, i, s.key_type);
+    if (s.kind > HJ_SEG_GATHERED) return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: bad segment kind %u", name, i, s.kind);
+    if (s.kind == HJ_SEG_DICT) {
+      if (s.attr_width != 1 && s.attr_width != 2 && s.attr_width != 4)
+        return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: attribute vector width %u (FixedSizeByteAligned 1/2/4 only)", name, i,
+                    s.attr_width);
+      if (s.n_rows && !s.attr) return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: DICT without attribute vector", name, i);
+      if (s.dict_n && !s.values) return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: DICT without dictionary", name, i);
+    } else if (s.n_rows && !s.values) {
+      return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: no values", name, i);
+    }
+    n += s.n_rows;
+  }
+  if (n != r->n_rows) return fail(ctx, HJ_ERR_INVALID, "%s relation: n_rows %llu != sum of chunks %llu", name,
+                                  (unsigned long long)r->n_rows, (unsigned long long)n);
+  if (n >= 0xFFFFFFFFull) return fail(ctx, HJ_ERR_TOO_LARGE, "%s relation has %llu rows (limit 2^32-2 per GPU)", name,
+                                      (unsigned long long)n);
+  return HJ_OK;
+}
+
+// Builds the device-side description of one relation; stages host-resident arrays into ctx->stage_in[side].
+int prepare_relation(hj_ctx* ctx, const hj_relation* r, int side, uint32_t tile, cudaStream_t st, PreparedRel* out) {
+  PreparedRel& pr = *out;
+  const uint32_t n_segs = r->n_segs;
+  pr.segs.resize(n_segs);
+  std::vector<uint32_t> row_begin(n_segs + 1, 0), tile_seg;
+  uint32_t rows = 0, tiles = 0, words = 0;
+  bool identity = true;
+  auto key_bytes = [](const hj_segment& s) { return s.key_type == HJ_KEY_INT64 ? 8u : 4u; };
+
+  // staging plan for host-resident inputs: (src, bytes, offset)
+  struct Copy { const void* src; size_t bytes; size_t off; };
+  std::vector<Copy> copies;
+  size_t stage_bytes = 0;
+  auto plan_copy = [&](const void* src, size_t bytes) -> size_t {
+    const size_t off = stage_bytes;
+    copies.push_back({src, bytes, off});
+    stage_bytes += (bytes + 255) & ~size_t(255);
+    return off;
+  };
+  const bool host = r->location == HJ_LOC_HOST;
+  std::vector<size_t> off_values(n_segs, 0), off_nulls(n_segs, 0), off_attr(n_segs, 0), off_ro(n_segs, 0);
+
+  for (uint32_t i = 0; i < n_segs; ++i) {
+    const hj_segment& s = r->segs[i];
+    DevSegment& d = pr.segs[i];
+    std::memset(&d, 0, sizeof(d));
+    d.values = s.values;
+    d.nulls = s.kind == HJ_SEG_DICT ? nullptr : s.nulls;
+    d.attr = s.kind == HJ_SEG_DICT ? s.attr : nullptr;
+    d.row_offsets = s.kind == HJ_SEG_GATHERED ? s.row_offsets : nullptr;
+    d.row_begin = rows;
+    d.n_rows = s.n_rows;
+    d.chunk_id = s.chunk_id;
+    d.null_value_id = s.null_value_id;
+    d.tile_begin = tiles;
+    d.mask_word_begin = words;
+    d.kind = s.kind;
+    d.key_type = s.key_type;
+    d.attr_width = s.attr_width;
+    row_begin[i] = rows;
+    if (s.key_type == HJ_KEY_INT64) pr.has_int64 = true;
+    if (s.kind == HJ_SEG_DICT) {
+      pr.has_dict = true;
+      words += (s.n_rows + 31) / 32;
+    }
+    if (s.chunk_id != i || d.row_offsets) identity = false;
+    const uint32_t nt = (s.n_rows + tile - 1) / tile;
+    for (uint32_t t = 0; t < nt; ++t) tile_seg.push_back(i);
+    tiles += nt;
+    rows += s.n_rows;
+    if (host) {
+      if (s.kind == HJ_SEG_DICT) {
+        if (s.dict_n) off_values[i] = plan_copy(s.values, size_t(s.dict_n) * key_bytes(s));
+        if (s.n_rows) off_attr[i] = plan_copy(s.attr, size_t(s.n_rows) * s.attr_width);
+      } else {
+        if (s.n_rows) off_values[i] = plan_copy(s.values, size_t(s.n_rows) * key_bytes(s));
+        if (s.n_rows && d.nulls) off_nulls[i] = plan_copy(s.nulls, s.n_rows);
+        if (s.n_rows && d.row_offsets) off_ro[i] = plan_copy(s.row_offsets, size_t(s.n_rows) * 4);
+      }
+    }
+  }
+  row_begin[n_segs] = rows;
+
+  if (host && stage_bytes) {
+    HJ_TRY(ensure(ctx, ctx->stage_in[side], stage_bytes));
+    char* base = static_cast<char*>(ctx->stage_in[side].p);
+    for (const Copy& c : copies) HJ_CUDA(ctx, cudaMemcpyAsync(base + c.off, c.src, c.bytes, cudaMemcpyHostToDevice, st));
+    for (uint32_t i = 0; i < n_segs; ++i) {
+      const hj_segment& s = r->segs[i];
+      DevSegment& d = pr.segs[i];
+      if (s.kind == HJ_SEG_DICT) {
+        d.values = s.dict_n ? base + off_values[i] : nullptr;
+        d.attr = s.n_rows ? base + off_attr[i] : nullptr;
+      } else {
+        d.values = s.n_rows ? base + off_values[i] : nullptr;
+        if (d.nulls) d.nulls = s.n_rows ? reinterpret_cast<const uint8_t*>(base + off_nulls[i]) : nullptr;
+        if (d.row_offsets) d.row_offsets = s.n_rows ? reinterpret_cast<const uint32_t*>(base + off_ro[i]) : nullptr;
+      }
+    }
+    for (const Copy& c : copies) pr.h2d_bytes += c.bytes;
+  }
+
+  // every chunk but the last exactly 2^k rows, the last <= 2^k: position -> RowID is a shift
+  int shift = -1;
+  if (n_segs == 1) {
+    shift = rows <= (1u << 31) ? 31 : -1;
+  } else if (n_segs > 1) {
+    const uint32_t first = r->segs[0].n_rows;
+    if (first && (first & (first - 1)) == 0) {
+      shift = 0;
+      while ((1u << shift) != first) ++shift;
+      for (uint32_t i = 1; i < n_segs; ++i) {
+        const uint32_t n = r->segs[i].n_rows;
+        if ((i + 1 < n_segs && n != first) || n > first) {
+          shift = -1;
+          break;
+        }
+      }
+    }
+  }
+
+  HJ_TRY(ensure(ctx, ctx->segs[side], std::max<size_t>(1, n_segs) * sizeof(DevSegment)));
+  HJ_TRY(ensure(ctx, ctx->tile_seg[side], std::max<size_t>(1, tile_seg.size()) * 4));
+  HJ_TRY(ensure(ctx, ctx->seg_row_begin[side], (size_t(n_segs) + 1) * 4));
+  if (n_segs) HJ_CUDA(ctx, cudaMemcpyAsync(ctx->segs[side].p, pr.segs.data(), n_segs * sizeof(DevSegment), cudaMemcpyHostToDevice, st));
+  if (!tile_seg.empty()) HJ_CUDA(ctx, cudaMemcpyAsync(ctx->tile_seg[side].p, tile_seg.data(), tile_seg.size() * 4, cudaMemcpyHostToDevice, st));
+  HJ_CUDA(ctx, cudaMemcpyAsync(ctx->seg_row_begin[side].p, row_begin.data(), (size_t(n_segs) + 1) * 4, cudaMemcpyHostToDevice, st));
+  // the three vectors above are pageable: cudaMemcpyAsync returns after staging them, so they may die with this frame
+
+  pr.meta.segs = static_cast<const DevSegment*>(ctx->segs[side].p);
+  pr.meta.tile_seg = static_cast<const uint32_t*>(ctx->tile_seg[side].p);
+  pr.meta.seg_row_begin = static_cast<const uint32_t*>(ctx->seg_row_begin[side].p);
+  pr.meta.n_segs = n_segs;
+  pr.meta.n_rows = rows;
+  pr.meta.n_tiles = tiles;
+  pr.meta.uniform_shift = shift;
+  pr.meta.identity = identity ? 1u : 0u;
+  pr.mask_words = words;
+  return HJ_OK;
+}
+
+int radix_bits_for(uint64_t n_build, int key_type) {
+  const uint64_t cap = key_type == HJ_KEY_INT64 ? Cfg<int64_t>::kCap : Cfg<int32_t>::kCap;
+  const uint64_t target = cap / 2;  // mean build partition = half a table: headroom for hash imbalance
+  int bits = 0;
+  while (bits < kMaxRadixBits && (n_build >> bits) > target) ++bits;
+  return bits;
+}
+
+struct Launches {
+  uint32_t n = 0;
+};
+
+#define HJ_LAUNCH_CHECK(ctx, name)                                                                 \
+  do {                                                                                             \
+    cudaError_t e_ = cudaGetLastError();                                                           \
+    if (e_ != cudaSuccess) return fail(ctx, HJ_ERR_CUDA, "launch of %s failed: %s", name, cudaGetErrorString(e_)); \
+  } while (0)
+
+template <typename KernelT>
+int set_smem(hj_ctx* ctx, KernelT kernel, size_t bytes) {
+  if (bytes > 48 * 1024) HJ_CUDA(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  return HJ_OK;
+}
+
+// K1 -> K2 -> K3 (pass 1) -> K3 (pass 2) for one relation. Leaves the partitioned tuples in *out_tuples and the
+// partition offsets in ctx->part_off[side].
+template <typename K>
+int partition_relation(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int bits2, int null_policy,
+                       cudaStream_t st, Launches* nl, const Tuple<K>** out_tuples, const Tuple<K>** out_pass1,
+                       cudaEvent_t ev_after_hist, cudaEvent_t ev_after_pass1) {
+  const uint32_t P = 1u << radix_bits, F1 = P >> bits2;
+  const uint32_t n = pr.meta.n_rows;
+  HJ_TRY(ensure(ctx, ctx->hist[side], (size_t(P) + 1) * 4));
+  HJ_TRY(ensure(ctx, ctx->part_off[side], (size_t(P) + 2) * 4));
+  HJ_TRY(ensure(ctx, ctx->cur1[side], (size_t(F1) + 1) * 4));
+  HJ_TRY(ensure(ctx, ctx->cur2[side], size_t(P) * 4));
+  HJ_TRY(ensure(ctx, ctx->l1_tiles[side], (size_t(F1) + 1) * 4));
+  HJ_TRY(ensure(ctx, ctx->tup_a[side], std::max<size_t>(1, n) * sizeof(Tuple<K>)));
+  if (bits2) HJ_TRY(ensure(ctx, ctx->tup_b[side], std::max<size_t>(1, n) * sizeof(Tuple<K>)));
+  if (pr.has_dict) {
+    HJ_TRY(ensure(ctx, ctx->keys_mat[side], std::max<size_t>(1, n) * sizeof(K)));
+    HJ_TRY(ensure(ctx, ctx->valid_mask[side], std::max<size_t>(1, pr.mask_words) * 4));
+  }
+  auto* hist = static_cast<uint32_t*>(ctx->hist[side].p);
+  auto* part_off = static_cast<uint32_t*>(ctx->part_off[side].p);
+  auto* cur1 = static_cast<uint32_t*>(ctx->cur1[side].p);
+  auto* cur2 = static_cast<uint32_t*>(ctx->cur2[side].p);
+  auto* l1_tiles = static_cast<uint32_t*>(ctx->l1_tiles[side].p);
+  auto* keys_mat = static_cast<K*>(ctx->keys_mat[side].p);
+  auto* valid_mask = static_cast<uint32_t*>(ctx->valid_mask[side].p);
+  auto* tup_a = static_cast<Tuple<K>*>(ctx->tup_a[side].p);
+  auto* tup_b = static_cast<Tuple<K>*>(ctx->tup_b[side].p);
+
+  HJ_CUDA(ctx, cudaMemsetAsync(hist, 0, (size_t(P) + 1) * 4, st));
+  if (pr.meta.n_tiles) {
+    auto k1 = k_materialize_hist<K, kHistThreads, Cfg<K>::kTile1>;
+    const size_t smem = (size_t(P) + 1) * 4;
+    HJ_TRY(set_smem(ctx, k1, smem));
+    int occ = 1;
+    HJ_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k1, kHistThreads, smem));
+    const uint32_t grid = std::min<uint32_t>(pr.meta.n_tiles, uint32_t(std::max(1, occ)) * ctx->n_sms);
+    k1<<<grid, kHistThreads, smem, st>>>(pr.meta, keys_mat, valid_mask, hist, radix_bits, null_policy);
+    HJ_LAUNCH_CHECK(ctx, "k_materialize_hist");
+    nl->n++;
+  }
+  k_offsets<1024><<<1, 1024, 0, st>>>(hist, part_off, cur1, cur2, l1_tiles, radix_bits, bits2, kTile2);
+  HJ_LAUNCH_CHECK(ctx, "k_offsets");
+  nl->n++;
+  if (ev_after_hist) HJ_CUDA(ctx, cudaEventRecord(ev_after_hist, st));
+
+  if (pr.meta.n_tiles) {
+    ScatterArgs<K> a{};
+    a.rel = pr.meta;
+    a.keys_mat = keys_mat;
+    a.valid_mask = valid_mask;
+    a.in = nullptr;
+    a.out = tup_a;
+    a.cursors = cur1;
+    a.part_off = part_off;
+    a.l1_tiles = l1_tiles;
+    a.radix_bits = radix_bits;
+    a.bits2 = bits2;
+    a.null_policy = null_policy;
+    auto k3 = k_scatter<K, kScatterThreads, Cfg<K>::kItems1, true>;
+    const size_t smem = size_t(Cfg<K>::kTile1) * sizeof(Tuple<K>);
+    HJ_TRY(set_smem(ctx, k3, smem));
+    k3<<<pr.meta.n_tiles, kScatterThreads, smem, st>>>(a);
+    HJ_LAUNCH_CHECK(ctx, "k_scatter<pass1>");
+    nl->n++;
+    if (bits2) {
+      a.in = tup_a;
+      a.out = tup_b;
+      a.cursors = cur2;
+      a.null_policy = kNullAsValue;  // pass 2 sees tuples only
+      auto k3b = k_scatter<K, kScatterThreads, kItems2, false>;
+      const size_t smem2 = size_t(kTile2) * sizeof(Tuple<K>);
+      HJ_TRY(set_smem(ctx, k3b, smem2));
+      const uint32_t grid2 = (n + kTile2 - 1) / kTile2 + F1;  // upper bound on sum(ceil(part/tile))
+      if (ev_after_pass1) HJ_CUDA(ctx, cudaEventRecord(ev_after_pass1, st));
+      k3b<<<grid2, kScatterThreads, smem2, st>>>(a);
+      HJ_LAUNCH_CHECK(ctx, "k_scatter<pass2>");
+      nl->n++;
+    }
+  }
+  *out_pass1 = tup_a;
+  *out_tuples = bits2 ? tup_b : tup_a;
+  return HJ_OK;
+}
+
+struct Readback {  // layout of the pinned readback area
+  unsigned long long cursor;
+  PlanOut plan;
+  uint32_t n_build_tuples;
+  uint32_t n_probe_tuples;
+};
+
+float ev_ms(cudaEvent_t a, cudaEvent_t b) {
+  float ms = 0.f;
+  if (cudaEventElapsedTime(&ms, a, b) != cudaSuccess) {
+    (void)cudaGetLastError();
+    return 0.f;
+  }
+  return ms;
+}
+
+template <typename K>
+int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, int mode, cudaStream_t st,
+             hj_result_info* info) {
+  const bool timed = ctx->opts.flags & HJ_FLAG_TIMINGS;
+  const bool one_side = mode == HJ_MODE_SEMI || mode == HJ_MODE_ANTI;
+  const bool outer = mode == HJ_MODE_LEFT || mode == HJ_MODE_RIGHT;
+  Launches nl;
+  cudaEvent_t* ev = ctx->ev;
+  HJ_CUDA(ctx, cudaEventRecord(ev[0], st));  // start
+
+  PreparedRel pb, pp;
+  HJ_TRY(prepare_relation(ctx, build, 0, Cfg<K>::kTile1, st, &pb));
+  HJ_TRY(prepare_relation(ctx, probe, 1, Cfg<K>::kTile1, st, &pp));
+  HJ_CUDA(ctx, cudaEventRecord(ev[1], st));  // after H2D
+
+  int radix_bits = ctx->opts.radix_bits >= 0 ? std::min(ctx->opts.radix_bits, kMaxRadixBits)
+                                             : radix_bits_for(build->n_rows, sizeof(K) == 8 ? HJ_KEY_INT64 : HJ_KEY_INT32);
+  const int bits2 = radix_bits > kSinglePassMaxBits ? radix_bits / 2 : 0;
+  const uint32_t P = 1u << radix_bits;
+
+  const int probe_null_policy = !outer ? kNullDrop : ((ctx->opts.flags & HJ_FLAG_SQL_NULL_PROBE) ? kNullRoute : kNullAsValue);
+  const Tuple<K>*tb = nullptr, *tp = nullptr, *tb1 = nullptr, *tp1 = nullptr;
+  HJ_TRY(partition_relation<K>(ctx, pb, 0, radix_bits, bits2, kNullDrop, st, &nl, &tb, &tb1, nullptr, nullptr));
+  HJ_TRY(partition_relation<K>(ctx, pp, 1, radix_bits, bits2, probe_null_policy, st, &nl, &tp, &tp1,
+                               timed ? ev[2] : nullptr, timed ? ev[3] : nullptr));
+  HJ_CUDA(ctx, cudaEventRecord(ev[4], st));  // after partitioning
+
+  // ---- plan
+  const uint32_t cap = Cfg<K>::kCap;
+  const size_t items_capacity = size_t(P) + build->n_rows / cap + probe->n_rows / kProbeSlice + 64;
+  HJ_TRY(ensure(ctx, ctx->items, items_capacity * sizeof(WorkItem)));
+  HJ_TRY(ensure(ctx, ctx->fin, size_t(P) * sizeof(WorkItem)));
+  HJ_TRY(ensure(ctx, ctx->plan, sizeof(PlanOut)));
+  HJ_TRY(ensure(ctx, ctx->queue, 256));
+  HJ_TRY(ensure(ctx, ctx->cursor, 256));
+  const size_t matched_bytes = (size_t(probe->n_rows) / 32 + 2) * 4;
+  if (mode != HJ_MODE_INNER) HJ_TRY(ensure(ctx, ctx->matched, matched_bytes));
+  auto* off_b = static_cast<uint32_t*>(ctx->part_off[0].p);
+  auto* off_p = static_cast<uint32_t*>(ctx->part_off[1].p);
+  k_plan<1024><<<1, 1024, 0, st>>>(off_b, off_p, radix_bits, mode, cap, kProbeSlice, (uint32_t)std::min<size_t>(items_capacity, 0xFFFFFFFFu),
+                                   static_cast<WorkItem*>(ctx->items.p), static_cast<WorkItem*>(ctx->fin.p),
+                                   static_cast<PlanOut*>(ctx->plan.p));
+  HJ_LAUNCH_CHECK(ctx, "k_plan");
+  nl.n++;
+
+  // ---- output buffers
+  uint64_t capacity = ctx->opts.output_capacity ? ctx->opts.output_capacity
+                                                : (one_side ? probe->n_rows : probe->n_rows + 1024);
+  capacity = std::max<uint64_t>(capacity, 1);
+
+  JoinArgs<K> a{};
+  a.build = tb;
+  a.probe = tp;
+  a.items = static_cast<const WorkItem*>(ctx->items.p);
+  a.plan = static_cast<const PlanOut*>(ctx->plan.p);
+  a.queue_head = static_cast<uint32_t*>(ctx->queue.p);
+  a.build_rel = pb.meta;
+  a.probe_rel = pp.meta;
+  a.out_cursor = static_cast<unsigned long long*>(ctx->cursor.p);
+  a.matched = static_cast<uint32_t*>(ctx->matched.p);
+  a.radix_bits = radix_bits;
+  a.mode = mode;
+
+  auto k5 = k_build_probe<K, kJoinThreads, Cfg<K>::kNS, Cfg<K>::kCap, kProbeV>;
+  const size_t smem5 = (size_t(Cfg<K>::kNS) + 1) * sizeof(K) + (size_t(Cfg<K>::kNS) + 2) * 4 + size_t(Cfg<K>::kCap) * 4;
+  HJ_TRY(set_smem(ctx, k5, smem5));
+  auto* rb = static_cast<Readback*>(ctx->pinned);
+  int passes = 0;
+  for (;;) {
+    ++passes;
+    if (!one_side) HJ_TRY(ensure(ctx, ctx->out_build, capacity * 8));
+    HJ_TRY(ensure(ctx, ctx->out_probe, capacity * 8));
+    a.out_build = one_side ? nullptr : static_cast<uint64_t*>(ctx->out_build.p);
+    a.out_probe = static_cast<uint64_t*>(ctx->out_probe.p);
+    a.capacity = capacity;
+    HJ_CUDA(ctx, cudaMemsetAsync(ctx->queue.p, 0, 4, st));
+    HJ_CUDA(ctx, cudaMemsetAsync(ctx->cursor.p, 0, 8, st));
+    if (mode != HJ_MODE_INNER) HJ_CUDA(ctx, cudaMemsetAsync(ctx->matched.p, 0, matched_bytes, st));
+    k5<<<ctx->n_sms, kJoinThreads, smem5, st>>>(a);
+    HJ_LAUNCH_CHECK(ctx, "k_build_probe");
+    nl.n++;
+    if (passes == 1) HJ_CUDA(ctx, cudaEventRecord(ev[5], st));  // after build+probe
+    if (mode != HJ_MODE_INNER) {
+      k_finalize_multi<K, 256><<<ctx->n_sms * 4, 256, 0, st>>>(a, static_cast<const WorkItem*>(ctx->fin.p));
+      HJ_LAUNCH_CHECK(ctx, "k_finalize_multi");
+      nl.n++;
+    }
+    if (probe_null_policy == kNullRoute) {
+      k_emit_null_probe<K, 256><<<ctx->n_sms * 4, 256, 0, st>>>(a, tp1, off_p);
+      HJ_LAUNCH_CHECK(ctx, "k_emit_null_probe");
+      nl.n++;
+    }
+    HJ_CUDA(ctx, cudaMemcpyAsync(&rb->cursor, ctx->cursor.p, 8, cudaMemcpyDeviceToHost, st));
+    HJ_CUDA(ctx, cudaMemcpyAsync(&rb->plan, ctx->plan.p, sizeof(PlanOut), cudaMemcpyDeviceToHost, st));
+    HJ_CUDA(ctx, cudaMemcpyAsync(&rb->n_build_tuples, off_b + P, 4, cudaMemcpyDeviceToHost, st));
+    HJ_CUDA(ctx, cudaMemcpyAsync(&rb->n_probe_tuples, off_p + P + 1, 4, cudaMemcpyDeviceToHost, st));
+    HJ_CUDA(ctx, cudaEventRecord(ev[6], st));  // end
+    HJ_CUDA(ctx, cudaStreamSynchronize(st));
+    if (rb->cursor <= capacity) break;
+    if (passes >= 2) return fail(ctx, HJ_ERR_CUDA, "result count changed between probe passes (%llu > %llu)", rb->cursor,
+                                 (unsigned long long)capacity);
+    capacity = rb->cursor;  // exact size is known now: re-probe into buffers that fit
+  }
+
+  ctx->has_result = true;
+  ctx->n_result = rb->cursor;
+  ctx->n_sides = one_side ? 1 : 2;
+  info->n_rows = rb->cursor;
+  info->n_sides = ctx->n_sides;
+  info->radix_bits = radix_bits;
+  info->n_build_tuples = rb->n_build_tuples;
+  info->n_probe_tuples = rb->n_probe_tuples;
+  info->n_partitions = P;
+  info->n_overflow_partitions = rb->plan.n_overflow_parts;
+  info->n_probe_passes = passes;
+  info->reserved = 0;
+
+  hj_timings& t = ctx->timings;
+  std::memset(&t, 0, sizeof(t));
+  t.ms[HJ_PH_TOTAL] = ev_ms(ev[0], ev[6]);
+  t.ms[HJ_PH_H2D] = ev_ms(ev[0], ev[1]);
+  if (timed) {
+    // phases are recorded on the probe relation's partitioning (the larger side) + the common stages
+    t.ms[HJ_PH_MATERIALIZE] = ev_ms(ev[1], ev[2]);  // build relation entirely + probe K1/K2
+    t.ms[HJ_PH_SCATTER1] = bits2 ? ev_ms(ev[2], ev[3]) : ev_ms(ev[2], ev[4]);
+    t.ms[HJ_PH_SCATTER2] = bits2 ? ev_ms(ev[3], ev[4]) : 0.f;
+  }
+  t.ms[HJ_PH_BUILD_PROBE] = passes == 1 ? ev_ms(ev[4], ev[5]) : 0.f;
+  t.ms[HJ_PH_FINALIZE] = passes == 1 ? ev_ms(ev[5], ev[6]) : 0.f;
+  t.bytes_h2d = pb.h2d_bytes + pp.h2d_bytes;
+  t.n_kernel_launches = nl.n;
+  return HJ_OK;
+}
+
+int check_ctx(hj_ctx* ctx) {
+  if (!ctx) return HJ_ERR_INVALID;
+  cudaError_t e = cudaSetDevice(ctx->device);
+  if (e != cudaSuccess) return fail(ctx, HJ_ERR_CUDA, "cudaSetDevice(%d): %s", ctx->device, cudaGetErrorString(e));
+  return HJ_OK;
+}
+
+}  // namespace
+
+// ============================================================================================================= C ABI
+extern "C" {
+
+int hj_abi_version(void) { return HJ_ABI_VERSION; }
+
+size_t hj_abi_sizeof(int which) {
+  switch (which) {
+    case 0: return sizeof(hj_segment);
+    case 1: return sizeof(hj_relation);
+    case 2: return sizeof(hj_options);
+    case 3: return sizeof(hj_result_info);
+    case 4: return sizeof(hj_timings);
+    case 5: return sizeof(hj_row_id);
+    default: return 0;
+  }
+}
+
+int hj_create(int device_id, const hj_options* opts, hj_ctx** out_ctx) {
+  if (!out_ctx) return fail(nullptr, HJ_ERR_INVALID, "out_ctx is NULL");
+  *out_ctx = nullptr;
+  if (opts && opts->abi_version != HJ_ABI_VERSION)
+    return fail(nullptr, HJ_ERR_INVALID, "hj_options.abi_version %u != %u", opts->abi_version, HJ_ABI_VERSION);
+  if (opts && opts->radix_bits > kMaxRadixBits)
+    return fail(nullptr, HJ_ERR_INVALID, "radix_bits %d > %d", opts->radix_bits, kMaxRadixBits);
+  int n_dev = 0;
+  cudaError_t e = cudaGetDeviceCount(&n_dev);
+  if (e != cudaSuccess || n_dev == 0) {
+    (void)cudaGetLastError();
+    return fail(nullptr, HJ_ERR_CUDA, "no CUDA device: %s (libhj has no CPU fallback)", cudaGetErrorString(e));
+  }
+  if (device_id < 0 || device_id >= n_dev) return fail(nullptr, HJ_ERR_INVALID, "device %d out of range [0,%d)", device_id, n_dev);
+  auto* ctx = new hj_ctx();
+  ctx->device = device_id;
+  if (opts) ctx->opts = *opts; else { ctx->opts.abi_version = HJ_ABI_VERSION; ctx->opts.radix_bits = -1; }
+  cudaDeviceProp prop{};
+  bool ok = cudaSetDevice(device_id) == cudaSuccess && cudaGetDeviceProperties(&prop, device_id) == cudaSuccess;
+  if (ok && prop.major < 10) {
+    delete ctx;
+    return fail(nullptr, HJ_ERR_CUDA, "device %d is sm_%d%d; libhj is built for sm_100a only", device_id, prop.major, prop.minor);
+  }
+  ok = ok && cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) == cudaSuccess;
+  ok = ok && cudaHostAlloc(&ctx->pinned, 4096, cudaHostAllocDefault) == cudaSuccess;
+  for (auto& ev : ctx->ev) ok = ok && cudaEventCreate(&ev) == cudaSuccess;
+  if (!ok) {
+    const char* msg = cudaGetErrorString(cudaGetLastError());
+    hj_destroy(ctx);
+    return fail(nullptr, HJ_ERR_CUDA, "context setup failed: %s", msg);
+  }
+  ctx->n_sms = prop.multiProcessorCount;
+  *out_ctx = ctx;
+  return HJ_OK;
+}
+
+int hj_release_scratch(hj_ctx* ctx) {
+  if (check_ctx(ctx) != HJ_OK) return HJ_ERR_INVALID;
+  for (DevBuf* b : ctx->all_bufs) {
+    if (b->p) cudaFree(b->p);
+    b->p = nullptr;
+    b->cap = 0;
+  }
+  ctx->has_result = false;
+  return HJ_OK;
+}
+
+void hj_destroy(hj_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  hj_release_scratch(ctx);
+  for (auto& ev : ctx->ev)
+    if (ev) cudaEventDestroy(ev);
+  if (ctx->pinned) cudaFreeHost(ctx->pinned);
+  if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+  delete ctx;
+}
+
+const char* hj_last_error(const hj_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int hj_radix_bits(uint64_t n_build_rows, int key_type) { return radix_bits_for(n_build_rows, key_type); }
+
+int hj_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, int mode, void* cuda_stream,
+            hj_result_info* out_info) {
+  if (!ctx) return HJ_ERR_INVALID;
+  ctx->has_result = false;
+  if (!out_info) return fail(ctx, HJ_ERR_INVALID, "out_info is NULL");
+  std::memset(out_info, 0, sizeof(*out_info));
+  if (!(mode == HJ_MODE_INNER || mode == HJ_MODE_LEFT || mode == HJ_MODE_RIGHT || mode == HJ_MODE_SEMI || mode == HJ_MODE_ANTI))
+    return fail(ctx, HJ_ERR_INVALID, "JoinMode %d is not supported by JoinHash (Inner/Left/Right/Semi/Anti only)", mode);
+  HJ_TRY(validate_relation(ctx, build, "build"));
+  HJ_TRY(validate_relation(ctx, probe, "probe"));
+  HJ_TRY(check_ctx(ctx));
+  cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
+  bool wide = false;  // JoinHashTraits: the hashed type of an int32 x int64 pair is int64 (hash_traits.hpp:21-25)
+  for (const hj_relation* r : {build, probe})
+    for (uint32_t i = 0; i < r->n_segs; ++i) wide = wide || r->segs[i].key_type == HJ_KEY_INT64;
+  return wide ? run_join<int64_t>(ctx, build, probe, mode, st, out_info)
+              : run_join<int32_t>(ctx, build, probe, mode, st, out_info);
+}
+
+int hj_fetch(hj_ctx* ctx, hj_row_id* build_side, hj_row_id* probe_side, uint64_t capacity) {
+  if (!ctx) return HJ_ERR_INVALID;
+  if (!ctx->has_result) return fail(ctx, HJ_ERR_STATE, "hj_fetch without a successful hj_join");
+  if (capacity < ctx->n_result) return fail(ctx, HJ_ERR_CAPACITY, "capacity %llu < %llu result rows", (unsigned long long)capacity,
+                                            (unsigned long long)ctx->n_result);
+  if (ctx->n_sides == 1 && build_side) return fail(ctx, HJ_ERR_INVALID, "Semi/Anti joins have no build-side PosList");
+  if (ctx->n_result && (!probe_side || (ctx->n_sides == 2 && !build_side))) return fail(ctx, HJ_ERR_INVALID, "NULL output buffer");
+  HJ_TRY(check_ctx(ctx));
+  cudaStream_t st = ctx->own_stream;
+  HJ_CUDA(ctx, cudaEventRecord(ctx->ev[7], st));
+  const size_t bytes = ctx->n_result * 8;
+  if (bytes) {
+    if (ctx->n_sides == 2) HJ_CUDA(ctx, cudaMemcpyAsync(build_side, ctx->out_build.p, bytes, cudaMemcpyDeviceToHost, st));
+    HJ_CUDA(ctx, cudaMemcpyAsync(probe_side, ctx->out_probe.p, bytes, cudaMemcpyDeviceToHost, st));
+  }
+  HJ_CUDA(ctx, cudaEventRecord(ctx->ev[8], st));
+  HJ_CUDA(ctx, cudaStreamSynchronize(st));
+  ctx->timings.ms[HJ_PH_D2H] = ev_ms(ctx->ev[7], ctx->ev[8]);
+  ctx->timings.bytes_d2h = bytes * ctx->n_sides;
+  return HJ_OK;
+}
+
+int hj_result_device(hj_ctx* ctx, const hj_row_id** build_side, const hj_row_id** probe_side, uint64_t* n_rows) {
+  if (!ctx) return HJ_ERR_INVALID;
+  if (!ctx->has_result) return fail(ctx, HJ_ERR_STATE, "hj_result_device without a successful hj_join");
+  if (build_side) *build_side = ctx->n_sides == 2 ? static_cast<const hj_row_id*>(ctx->out_build.p) : nullptr;
+  if (probe_side) *probe_side = static_cast<const hj_row_id*>(ctx->out_probe.p);
+  if (n_rows) *n_rows = ctx->n_result;
+  return HJ_OK;
+}
+
+int hj_translate(hj_ctx* ctx, hj_row_id* inout, uint64_t n, const hj_row_id* const* pos_lists,
+                 const uint32_t* pos_list_sizes, uint32_t n_chunks) {
+  if (!ctx) return HJ_ERR_INVALID;
+  if (n == 0) return HJ_OK;
+  if (!inout || (n_chunks && (!pos_lists || !pos_list_sizes))) return fail(ctx, HJ_ERR_INVALID, "NULL argument");
+  HJ_TRY(check_ctx(ctx));
+  cudaStream_t st = ctx->own_stream;
+  std::vector<uint64_t> base(n_chunks + 1, 0);
+  for (uint32_t c = 0; c < n_chunks; ++c) base[c + 1] = base[c] + pos_list_sizes[c];
+  const size_t total = base[n_chunks];
+  // misc layout: [inout n*8][pos lists total*8][chunk_base (n_chunks+1)*8][chunk_size n_chunks*4][error 4]
+  const size_t o_pl = n * 8, o_base = o_pl + total * 8, o_size = o_base + (size_t(n_chunks) + 1) * 8,
+               o_err = o_size + size_t(n_chunks) * 4;
+  HJ_TRY(ensure(ctx, ctx->misc, o_err + 8));
+  char* d = static_cast<char*>(ctx->misc.p);
+  HJ_CUDA(ctx, cudaMemcpyAsync(d, inout, n * 8, cudaMemcpyHostToDevice, st));
+  for (uint32_t c = 0; c < n_chunks; ++c)
+    if (pos_list_sizes[c])
+      HJ_CUDA(ctx, cudaMemcpyAsync(d + o_pl + base[c] * 8, pos_lists[c], size_t(pos_list_sizes[c]) * 8, cudaMemcpyHostToDevice, st));
+  HJ_CUDA(ctx, cudaMemcpyAsync(d + o_base, base.data(), (size_t(n_chunks) + 1) * 8, cudaMemcpyHostToDevice, st));
+  if (n_chunks) HJ_CUDA(ctx, cudaMemcpyAsync(d + o_size, pos_list_sizes, size_t(n_chunks) * 4, cudaMemcpyHostToDevice, st));
+  HJ_CUDA(ctx, cudaMemsetAsync(d + o_err, 0, 4, st));
+  const uint32_t grid = (uint32_t)std::min<uint64_t>((n + 255) / 256, uint64_t(ctx->n_sms) * 8);
+  k_translate<<<grid, 256, 0, st>>>(reinterpret_cast<uint64_t*>(d), n, reinterpret_cast<const uint64_t*>(d + o_pl),
+                                    reinterpret_cast<const uint64_t*>(d + o_base),
+                                    reinterpret_cast<const uint32_t*>(d + o_size), n_chunks,
+                                    reinterpret_cast<uint32_t*>(d + o_err));
+  HJ_LAUNCH_CHECK(ctx, "k_translate");
+  uint32_t err = 0;
+  HJ_CUDA(ctx, cudaMemcpyAsync(inout, d, n * 8, cudaMemcpyDeviceToHost, st));
+  HJ_CUDA(ctx, cudaMemcpyAsync(&err, d + o_err, 4, cudaMemcpyDeviceToHost, st));
+  HJ_CUDA(ctx, cudaStreamSynchronize(st));
+  if (err) return fail(ctx, HJ_ERR_INVALID, "hj_translate: a RowID points outside its input PosList");
+  return HJ_OK;
+}
+
+int hj_get_timings(const hj_ctx* ctx, hj_timings* out) {
+  if (!ctx || !out) return HJ_ERR_INVALID;
+  *out = ctx->timings;
+  return HJ_OK;
+}
+
+}  // extern "C"
+
+// ============================================================================================================= multi-GPU
+// Implemented in hj_comm.cuh (included below) once the NCCL exchange is wired; see DESIGN.md §6.
+#include "hj_comm.cuh"

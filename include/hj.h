@@ -175,6 +175,9 @@ typedef struct hj_ctx hj_ctx; /* opaque; all library state lives here (re-entran
 
 /* Library/ABI version of the loaded .so (== HJ_ABI_VERSION it was compiled with). */
 int hj_abi_version(void);
+/* sizeof() of the ABI structs as compiled into the library, for binding generators to self-check:
+ * 0 hj_segment, 1 hj_relation, 2 hj_options, 3 hj_result_info, 4 hj_timings, 5 hj_row_id; 0 for other values. */
+size_t hj_abi_sizeof(int which);
 
 /* Creates a context on CUDA device `device_id`. `opts` may be NULL (defaults). */
 int hj_create(int device_id, const hj_options* opts, hj_ctx** out_ctx);

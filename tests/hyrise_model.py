@@ -9,6 +9,12 @@ test cases (tests/golden/join_fixtures.txt) can be replayed against any *join en
     engine(build: abi.Relation, probe: abi.Relation, mode: int) -> (build_side (n,2) uint32 | None, probe_side (n,2) uint32)
 The engine is either the CPU oracle (tests/oracle_binding.py) or libhj on the GPU (hyrise-1_b200.HashJoin).
 """
+import os as _os
+import sys as _sys
+
+_ROOT = _os.path.dirname(_os.path.dirname(_os.path.abspath(__file__)))
+if _ROOT not in _sys.path:
+    _sys.path.insert(0, _ROOT)
 import importlib
 import math
 import os

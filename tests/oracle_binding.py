@@ -1,6 +1,12 @@
 """ctypes binding of the CPU oracle (oracle/liboracle_joinhash.so). TEST INFRASTRUCTURE: imported only by tests/,
 __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs — never by the product package."""
 import ctypes as C
+import os as _os
+import sys as _sys
+
+_ROOT = _os.path.dirname(_os.path.dirname(_os.path.abspath(__file__)))
+if _ROOT not in _sys.path:
+    _sys.path.insert(0, _ROOT)
 import importlib
 import os
 import subprocess
