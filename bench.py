@@ -1,0 +1,348 @@
+#!/usr/bin/env python3
+"""bench.py — JoinHash input tuples/s on B200 (BASELINE.json metric), one JSON line on stdout.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c3|c1] [--scale F]
+
+A "step" is one complete hash join (hj_join: materialize+histogram -> radix scatter x2 -> shared-memory build+probe ->
+PosLists) over the synthetic workload BASELINE.json's metric is quoted on: C2 = 100 M x 1 B int32 rows, uniform keys,
+dictionary-encoded 1 Mi-row chunks, Inner. `value` is measured with the key columns already resident in
+HBM; `e2e` runs the same join through the C ABI from pinned HOST buffers (H2D of the columns and D2H of both PosLists
+inside the timed region). Inputs (8.8 GB) are far larger than L2, so no L2 flush is needed between steps.
+`--impl reference` times the reference's CPU algorithm (the oracle restatement, all host threads) on a bounded sample.
+"""
+import argparse
+import ctypes as C
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np
+
+CHUNK = 1 << 20  # rows per chunk (1 048 576)
+WORKLOADS = {
+    # name: (n_build, n_probe, key dtype, encoding, description)
+    "c2": (100_000_000, 1_000_000_000, "int32", "dict",
+           "C2 synthetic 1:N int32 inner equi-join, 100M build x 1B probe, uniform keys, dictionary-encoded"),
+    "c3": (200_000_000, 2_000_000_000, "int64", "value",
+           "C3 synthetic int64 join, Zipf(1.0) build keys, 200M x 2B, ValueColumns"),
+    "c1": (1_500_000, 6_001_215, "int32", "dict", "C1-shaped: 1.5M unique build x 6M probe int32 (TPC-H SF1 sizes)"),
+}
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+# ------------------------------------------------------------------------------------------------------------ data
+def gen_device_workload(name, scale, device, seed):
+    """Builds the workload's key columns on `device` with torch. Returns dict with per-relation lists of
+    (chunk_id, dictionary|values tensor, attr tensor|None) and row counts."""
+    import torch
+    n_build, n_probe, dtype, encoding, _ = WORKLOADS[name]
+    n_build, n_probe = max(1, int(n_build * scale)), max(1, int(n_probe * scale))
+    tdt = torch.int32 if dtype == "int32" else torch.int64
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    domain = n_build
+    if name == "c3":
+        # Zipf(1.0) ranks by inverse CDF of the continuous approximation, scrambled by a fixed odd multiplier
+        u = torch.rand(n_build, device=device, generator=g, dtype=torch.float64)
+        ranks = torch.exp(u * np.log(domain + 1.0)).floor().clamp_(1, domain).to(torch.int64)
+        build_keys = ((ranks * 0x9E3779B1) % domain + 1).to(tdt)
+        del u, ranks
+    else:
+        build_keys = (torch.randperm(domain, device=device, generator=g) + 1).to(tdt)  # unique: 1:N join
+
+    def chunks_of(keys_fn, n):
+        out = []
+        for c, start in enumerate(range(0, n, CHUNK)):
+            k = keys_fn(start, min(CHUNK, n - start))
+            if encoding == "dict":
+                d, inv = torch.unique(k, sorted=True, return_inverse=True)
+                # FixedSizeByteAligned width rule (fixed_size_byte_aligned_compressor.cpp:21-30); C2's 1 Mi-row chunks
+                # hold ~1 M distinct keys -> 4-byte attribute vectors
+                m = len(d) + 1
+                adt = torch.uint8 if m <= 0xFF else (torch.int16 if m <= 0xFFFF else torch.int32)
+                out.append((c, d.contiguous(), inv.to(adt).contiguous()))
+            else:
+                out.append((c, k.contiguous(), None))
+        return out
+
+    build = chunks_of(lambda s, m: build_keys[s:s + m], n_build)
+    probe = chunks_of(lambda s, m: torch.randint(1, domain + 1, (m,), device=device, generator=g, dtype=torch.int64).to(tdt),
+                      n_probe)
+    del build_keys
+    return dict(build=build, probe=probe, n_build=n_build, n_probe=n_probe, dtype=dtype, encoding=encoding)
+
+
+def relation_from_chunks(hj, chunks, location, attr_small=False):
+    rb = hj.RelationBuilder(location)
+    for cid, a, b in chunks:
+        if b is None:
+            rb.add_value(cid, a)
+        else:
+            rb.add_dict(cid, a, b)
+    return rb.build()
+
+
+def to_pinned_host(chunks):
+    """Pinned host copies of the device chunks (what a host-resident Hyrise table would hand the shim)."""
+    import torch
+    out = []
+    for cid, a, b in chunks:
+        ha = torch.empty(a.shape, dtype=a.dtype, pin_memory=True).copy_(a)
+        hb = None if b is None else torch.empty(b.shape, dtype=b.dtype, pin_memory=True).copy_(b)
+        out.append((cid, ha, hb))
+    return out
+
+
+def input_bytes(chunks):
+    return sum(a.numel() * a.element_size() + (0 if b is None else b.numel() * b.element_size()) for _, a, b in chunks)
+
+
+# ------------------------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    """Samples SM clocks and throttle reasons with nvidia-smi while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows, self.proc, self.gpu = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+        sm, mx, reasons = [], 0, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx = max(mx, float(r[1]))
+            except Exception:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------------------ CPU arm
+def cpu_reference_sample(name, scale_of_full, n_threads, steps, warmup, seed=0xB200 + 2):
+    """The reference's CPU JoinHash (oracle restatement, reference task granularity) on a bounded sample of the
+    workload; returns (tuples/s best-of-steps, sample description, mean seconds per step)."""
+    import oracle_binding as ob
+    import workloads as wl
+    n_build, n_probe, dtype, encoding, _ = WORKLOADS[name]
+    nb, npr = max(1, int(n_build * scale_of_full)), max(1, int(n_probe * scale_of_full))
+    rng = np.random.default_rng(seed)
+    npdt = np.int32 if dtype == "int32" else np.int64
+    if name == "c3":
+        bk = wl.zipf_keys(rng, nb, nb, 1.0, npdt)
+    else:
+        bk = (rng.permutation(nb) + 1).astype(npdt)
+    pk = rng.integers(1, nb + 1, npr, dtype=np.int64).astype(npdt)
+    build = wl.make_relation(bk, CHUNK, encoding)
+    probe = wl.make_relation(pk, CHUNK, encoding)
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        _, _, info = ob.oracle_join(build, probe, 0, n_threads=n_threads)
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+    best = min(times)
+    sample = f"{nb} x {npr} rows ({scale_of_full:g} of {name.upper()}), {encoding} chunks of {CHUNK}, Inner, {info['n_rows']} pairs"
+    return (nb + npr) / best, sample, float(np.mean(times))
+
+
+# ------------------------------------------------------------------------------------------------------------ main
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--scale", type=float, default=1.0, help="fraction of the workload's row counts (1.0 = as published)")
+    ap.add_argument("--cpu-scale", type=float, default=0.01, help="fraction of the workload the CPU baseline runs")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    n_build, n_probe, dtype, encoding, desc = WORKLOADS[args.workload]
+    metric = "JoinHash input tuples/s"
+    unit = "tuples/s"
+    n_threads = os.cpu_count() or 1
+
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        W = max(1, min(args.warmup, 1))
+        val, sample, sec = cpu_reference_sample(args.workload, args.cpu_scale, n_threads, args.steps, W)
+        line = {"impl": "reference", "metric": metric, "value": val, "unit": unit, "n_gpus": args.gpus, "steps": args.steps,
+                "warmup": W, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": dtype, "data": "synthetic",
+                "config": {"workload": desc, "sample": sample},
+                "cpu_baseline": {"value": val, "unit": unit, "cores": n_threads, "kind": "port", "sample": sample},
+                "e2e": {"value": val, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line), flush=True)
+        return 0
+
+    import torch
+    import torch.distributed as dist
+    hj = importlib.import_module("hyrise-1_b200")
+    abi = hj.abi
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- workload: at N > 1 every rank holds 1/N of both relations (strong partitioning of the same global join)
+    t0 = time.time()
+    shard_scale = args.scale / world
+    data = gen_device_workload(args.workload, shard_scale, dev, seed=0xB200 + 2 + 1000 * rank)
+    nb, npr = data["n_build"], data["n_probe"]
+    build_dev = relation_from_chunks(hj, data["build"], abi.LOC_DEVICE)
+    probe_dev = relation_from_chunks(hj, data["probe"], abi.LOC_DEVICE)
+    torch.cuda.synchronize()
+    log(f"[rank {rank}] generated {nb} x {npr} rows in {time.time() - t0:.1f}s; inputs "
+        f"{(input_bytes(data['build']) + input_bytes(data['probe'])) / 1e9:.2f} GB")
+
+    j = hj.HashJoin(device=local_rank, flags=abi.FLAG_TIMINGS)
+
+    def step():
+        return j.join(build_dev, probe_dev, abi.MODE_INNER)
+
+    for _ in range(max(3, args.warmup)):
+        info = step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    phase_ms, launches = [], 0
+    t_start = time.perf_counter()
+    for _ in range(args.steps):
+        info = step()
+        tm = j.timings()
+        phase_ms.append(tm)
+        launches += tm["n_kernel_launches"]
+    barrier()
+    elapsed = time.perf_counter() - t_start
+    clocks = sampler.stop()
+    dev_ms = float(np.mean([t["total"] for t in phase_ms]))  # CUDA events on the library's stream
+    if world > 1:
+        tt = torch.tensor([elapsed], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        elapsed = float(tt.item())
+        cnt = torch.tensor([nb + npr, info.n_rows], device=dev, dtype=torch.int64)
+        dist.all_reduce(cnt)
+        total_tuples, total_results = int(cnt[0]), int(cnt[1])
+    else:
+        total_tuples, total_results = nb + npr, info.n_rows
+    ms_per_step = elapsed / args.steps * 1e3
+    value = total_tuples / (elapsed / args.steps)
+
+    # ---- roofline of the dominant kernel (k_build_probe), live CUDA-event time of its phase
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        with open(peaks_path) as f:
+            peak, peak_src = json.load(f)["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    k = 4 if dtype == "int32" else 8
+    t_bytes = k + 8
+    w_in = {"dict": 4 + 4, "value": k}[encoding]  # attr + amortised dictionary bytes per row for 1 Mi-row chunks
+    bp_ms = float(np.mean([t["build_probe"] for t in phase_ms]))
+    bp_bytes = (nb + npr) * t_bytes + info.n_rows * 16  # read the partitioned tuple once + 16 B per result
+    whole_bytes = (nb + npr) * (2 * w_in + 2 * t_bytes) + info.n_rows * 16
+    roofline = {"bound": "hbm", "kernel": "k_build_probe", "achieved": bp_bytes / (bp_ms * 1e-3) / 1e9 if bp_ms else None,
+                "peak": peak, "unit": "GB/s", "frac": (bp_bytes / (bp_ms * 1e-3) / 1e9 / peak) if bp_ms else None,
+                "traffic": None, "peak_source": peak_src, "kernel_ms": bp_ms,
+                "whole_join": {"algorithmic_bytes": whole_bytes, "achieved": whole_bytes / (dev_ms * 1e-3) / 1e9,
+                               "frac": whole_bytes / (dev_ms * 1e-3) / 1e9 / peak, "frac_of_nominal_8TBs":
+                               whole_bytes / (dev_ms * 1e-3) / 1e9 / 8000.0, "device_ms": dev_ms},
+                "phase_ms": {p: float(np.mean([t[p] for t in phase_ms])) for p in abi.PHASES}}
+
+    # ---- e2e: same join through the C ABI from pinned host buffers, PosLists fetched to pinned host memory
+    e2e = None
+    if not args.no_e2e:
+        hb, hp = to_pinned_host(data["build"]), to_pinned_host(data["probe"])
+        build_host = relation_from_chunks(hj, [(c, a.numpy(), None if b is None else b.numpy()) for c, a, b in hb], abi.LOC_HOST)
+        probe_host = relation_from_chunks(hj, [(c, a.numpy(), None if b is None else b.numpy()) for c, a, b in hp], abi.LOC_HOST)
+        out_b = torch.empty((max(info.n_rows, 1), 2), dtype=torch.int32, pin_memory=True).numpy().view(np.uint32)
+        out_p = torch.empty((max(info.n_rows, 1), 2), dtype=torch.int32, pin_memory=True).numpy().view(np.uint32)
+        h2d = input_bytes(hb) + input_bytes(hp)
+
+        def e2e_step():
+            inf = j.join(build_host, probe_host, abi.MODE_INNER)
+            j.fetch(out_b, out_p)
+            return inf
+        e2e_step()
+        barrier()
+        n_e2e = max(1, min(args.steps, 3))
+        t1 = time.perf_counter()
+        for _ in range(n_e2e):
+            inf = e2e_step()
+        barrier()
+        e2e_s = (time.perf_counter() - t1) / n_e2e
+        if world > 1:
+            tt = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            e2e_s = float(tt.item())
+        e2e = {"value": total_tuples / e2e_s, "unit": unit, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": inf.n_rows * 16,
+               "ms_per_step": e2e_s * 1e3, "steps": n_e2e}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        val, sample, _ = cpu_reference_sample(args.workload, args.cpu_scale, n_threads, 2, 1)
+        cpu = {"value": val, "unit": unit, "cores": n_threads, "kind": "port", "sample": sample}
+
+    if rank == 0:
+        line = {"metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps,
+                "warmup": max(3, args.warmup), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if world > 1 else "weak",
+                "vs_baseline": None, "dtype": dtype, "data": "synthetic",
+                "config": {"workload": desc, "scale": args.scale, "n_build": nb * world, "n_probe": npr * world,
+                           "chunk_rows": CHUNK, "mode": "Inner", "result_rows": total_results,
+                           "radix_bits": info.radix_bits, "l2": "inputs larger than L2, no flush"},
+                "clocks": clocks, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e}
+        print(json.dumps(line), flush=True)
+    j.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

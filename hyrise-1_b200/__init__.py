@@ -147,6 +147,7 @@ class HashJoin:
         if isinstance(mode, str):
             mode = abi.MODES[mode]
         info = abi.ResultInfo()
+        self.info = None
         self._check(self._l.hj_join(self._ctx, C.byref(build), C.byref(probe), mode, stream, C.byref(info)))
         self.info, self._mode = info, mode
         return info
@@ -161,6 +162,8 @@ class HashJoin:
 
     def fetch(self, out_build=None, out_probe=None):
         """Copies the result PosLists to host. Returns (build_side or None, probe_side) as (n, 2) uint32 arrays."""
+        if self.info is None:
+            self._check(self._l.hj_fetch(self._ctx, None, None, 0))  # reports HJ_ERR_STATE
         n = self.info.n_rows
         two = self.info.n_sides == 2
         if out_probe is None:
