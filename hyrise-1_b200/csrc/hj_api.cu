@@ -17,25 +17,26 @@ namespace {
 // ---- tuning constants -----------------------------------------------------------------------------------
 template <typename K> struct Cfg;
 template <> struct Cfg<int32_t> {
-  static constexpr int kTile1 = 8192;     // rows per CTA tile in K1 / pass 1
-  static constexpr int kItems1 = 16;      // pass 1: 512 threads x 16
+  static constexpr int kItems1 = 16;      // pass 1: 256 threads x 16 = 4096 rows per tile (32 KB staged)
+  static constexpr int kItems2 = 16;      // pass 2: 4096 tuples per tile
   static constexpr int kNS = 16384;       // hash-table slots per shared-memory table
   static constexpr int kCap = 12288;      // build tuples per table (load factor <= 0.75)
 };
 template <> struct Cfg<int64_t> {
-  static constexpr int kTile1 = 4096;
-  static constexpr int kItems1 = 8;
+  static constexpr int kItems1 = 8;       // 2048 rows per tile (32 KB staged)
+  static constexpr int kItems2 = 8;
   static constexpr int kNS = 8192;
   static constexpr int kCap = 6144;
 };
-constexpr int kScatterThreads = 512;
-constexpr int kItems2 = 8;                 // pass 2: 512 threads x 8 = 4096 tuples per tile
-constexpr int kTile2 = kScatterThreads * kItems2;
-constexpr int kHistThreads = 1024;
+constexpr int kScatterThreads = 256;
+constexpr int kHistThreads = 512;
 constexpr int kJoinThreads = 1024;
 constexpr int kProbeV = 4;
 constexpr uint32_t kProbeSlice = 128 * 1024;
 constexpr int kSinglePassMaxBits = 8;
+constexpr int kVirtualCtasPerSm = 4;       // K1 / pass 1 tile ownership: G = min(n_tiles, 4 * SMs) virtual CTAs
+template <typename K> constexpr int tile1() { return kScatterThreads * Cfg<K>::kItems1; }
+template <typename K> constexpr int tile2() { return kScatterThreads * Cfg<K>::kItems2; }
 
 struct DevBuf {
   void* p = nullptr;
@@ -55,10 +56,10 @@ struct hj_ctx {
   std::vector<DevBuf*> all_bufs;
   // per relation (0 = build, 1 = probe)
   DevBuf stage_in[2], segs[2], tile_seg[2], seg_row_begin[2], keys_mat[2], valid_mask[2];
-  DevBuf hist[2], part_off[2], cur1[2], cur2[2], l1_tiles[2], tup_a[2], tup_b[2];
-  DevBuf items, fin, plan, queue, cursor, matched, out_build, out_probe, misc;
+  DevBuf hist[2], hist1[2], part_off[2], cur2[2], l1_tiles[2], tup_a[2], tup_b[2];
+  DevBuf items, fin, plan, queue, out_state, out_tails, compact_plan, matched, out_build, out_probe, misc;
   void* pinned = nullptr;  // small pinned readback area
-  cudaEvent_t ev[HJ_N_PHASES + 2] = {};
+  cudaEvent_t ev[16] = {};
   // result of the last join
   bool has_result = false;
   uint64_t n_result = 0;
@@ -71,8 +72,8 @@ struct hj_ctx {
   hj_ctx() {
     for (DevBuf* b : {&stage_in[0], &stage_in[1], &segs[0], &segs[1], &tile_seg[0], &tile_seg[1], &seg_row_begin[0],
                       &seg_row_begin[1], &keys_mat[0], &keys_mat[1], &valid_mask[0], &valid_mask[1], &hist[0], &hist[1],
-                      &part_off[0], &part_off[1], &cur1[0], &cur1[1], &cur2[0], &cur2[1], &l1_tiles[0], &l1_tiles[1],
-                      &tup_a[0], &tup_a[1], &tup_b[0], &tup_b[1], &items, &fin, &plan, &queue, &cursor, &matched,
+                      &part_off[0], &part_off[1], &hist1[0], &hist1[1], &cur2[0], &cur2[1], &l1_tiles[0], &l1_tiles[1],
+                      &tup_a[0], &tup_a[1], &tup_b[0], &tup_b[1], &items, &fin, &plan, &queue, &out_state, &out_tails, &compact_plan, &matched,
                       &out_build, &out_probe, &misc})
       all_bufs.push_back(b);
   }
@@ -300,17 +301,19 @@ int set_smem(hj_ctx* ctx, KernelT kernel, size_t bytes) {
   return HJ_OK;
 }
 
-// K1 -> K2 -> K3 (pass 1) -> K3 (pass 2) for one relation. Leaves the partitioned tuples in *out_tuples and the
-// partition offsets in ctx->part_off[side].
+// ---- partitioning stages for one relation ------------------------------------------------------------------------------
+struct PartState {
+  uint32_t G = 0;  // virtual CTAs of K1 / pass 1
+};
+
 template <typename K>
-int partition_relation(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int bits2, int null_policy,
-                       cudaStream_t st, Launches* nl, const Tuple<K>** out_tuples, const Tuple<K>** out_pass1,
-                       cudaEvent_t ev_after_hist, cudaEvent_t ev_after_pass1) {
+int stage_alloc(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int bits2, PartState* ps) {
   const uint32_t P = 1u << radix_bits, F1 = P >> bits2;
   const uint32_t n = pr.meta.n_rows;
+  ps->G = std::max<uint32_t>(1, std::min<uint32_t>(pr.meta.n_tiles, uint32_t(kVirtualCtasPerSm) * ctx->n_sms));
   HJ_TRY(ensure(ctx, ctx->hist[side], (size_t(P) + 1) * 4));
+  HJ_TRY(ensure(ctx, ctx->hist1[side], size_t(ps->G) * (F1 + 1) * 4));
   HJ_TRY(ensure(ctx, ctx->part_off[side], (size_t(P) + 2) * 4));
-  HJ_TRY(ensure(ctx, ctx->cur1[side], (size_t(F1) + 1) * 4));
   HJ_TRY(ensure(ctx, ctx->cur2[side], size_t(P) * 4));
   HJ_TRY(ensure(ctx, ctx->l1_tiles[side], (size_t(F1) + 1) * 4));
   HJ_TRY(ensure(ctx, ctx->tup_a[side], std::max<size_t>(1, n) * sizeof(Tuple<K>)));
@@ -319,74 +322,89 @@ int partition_relation(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_b
     HJ_TRY(ensure(ctx, ctx->keys_mat[side], std::max<size_t>(1, n) * sizeof(K)));
     HJ_TRY(ensure(ctx, ctx->valid_mask[side], std::max<size_t>(1, pr.mask_words) * 4));
   }
-  auto* hist = static_cast<uint32_t*>(ctx->hist[side].p);
-  auto* part_off = static_cast<uint32_t*>(ctx->part_off[side].p);
-  auto* cur1 = static_cast<uint32_t*>(ctx->cur1[side].p);
-  auto* cur2 = static_cast<uint32_t*>(ctx->cur2[side].p);
-  auto* l1_tiles = static_cast<uint32_t*>(ctx->l1_tiles[side].p);
-  auto* keys_mat = static_cast<K*>(ctx->keys_mat[side].p);
-  auto* valid_mask = static_cast<uint32_t*>(ctx->valid_mask[side].p);
-  auto* tup_a = static_cast<Tuple<K>*>(ctx->tup_a[side].p);
-  auto* tup_b = static_cast<Tuple<K>*>(ctx->tup_b[side].p);
+  return HJ_OK;
+}
 
+// K1 + K2 + K2b
+template <typename K>
+int stage_hist(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int bits2, int null_policy,
+               const PartState& ps, cudaStream_t st, Launches* nl) {
+  const uint32_t P = 1u << radix_bits, F1 = P >> bits2;
+  auto* hist = static_cast<uint32_t*>(ctx->hist[side].p);
+  auto* hist1 = static_cast<uint32_t*>(ctx->hist1[side].p);
   HJ_CUDA(ctx, cudaMemsetAsync(hist, 0, (size_t(P) + 1) * 4, st));
   if (pr.meta.n_tiles) {
-    auto k1 = k_materialize_hist<K, kHistThreads, Cfg<K>::kTile1>;
+    auto k1 = k_materialize_hist<K, kHistThreads, tile1<K>()>;
     const size_t smem = (size_t(P) + 1) * 4;
     HJ_TRY(set_smem(ctx, k1, smem));
-    int occ = 1;
-    HJ_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k1, kHistThreads, smem));
-    const uint32_t grid = std::min<uint32_t>(pr.meta.n_tiles, uint32_t(std::max(1, occ)) * ctx->n_sms);
-    k1<<<grid, kHistThreads, smem, st>>>(pr.meta, keys_mat, valid_mask, hist, radix_bits, null_policy);
+    k1<<<ps.G, kHistThreads, smem, st>>>(pr.meta, static_cast<K*>(ctx->keys_mat[side].p),
+                                         static_cast<uint32_t*>(ctx->valid_mask[side].p), hist, hist1, radix_bits, bits2,
+                                         null_policy);
     HJ_LAUNCH_CHECK(ctx, "k_materialize_hist");
     nl->n++;
+  } else {
+    HJ_CUDA(ctx, cudaMemsetAsync(hist1, 0, size_t(ps.G) * (F1 + 1) * 4, st));
   }
-  k_offsets<1024><<<1, 1024, 0, st>>>(hist, part_off, cur1, cur2, l1_tiles, radix_bits, bits2, kTile2);
+  k_offsets<1024><<<1, 1024, 0, st>>>(hist, static_cast<uint32_t*>(ctx->part_off[side].p),
+                                      static_cast<uint32_t*>(ctx->cur2[side].p),
+                                      static_cast<uint32_t*>(ctx->l1_tiles[side].p), radix_bits, bits2, tile2<K>());
   HJ_LAUNCH_CHECK(ctx, "k_offsets");
-  nl->n++;
-  if (ev_after_hist) HJ_CUDA(ctx, cudaEventRecord(ev_after_hist, st));
+  k_offsets_l1<256><<<F1 + 1, 256, 0, st>>>(hist1, static_cast<const uint32_t*>(ctx->part_off[side].p), radix_bits, bits2, ps.G);
+  HJ_LAUNCH_CHECK(ctx, "k_offsets_l1");
+  nl->n += 2;
+  return HJ_OK;
+}
 
-  if (pr.meta.n_tiles) {
-    ScatterArgs<K> a{};
-    a.rel = pr.meta;
-    a.keys_mat = keys_mat;
-    a.valid_mask = valid_mask;
-    a.in = nullptr;
-    a.out = tup_a;
-    a.cursors = cur1;
-    a.part_off = part_off;
-    a.l1_tiles = l1_tiles;
-    a.radix_bits = radix_bits;
-    a.bits2 = bits2;
-    a.null_policy = null_policy;
-    auto k3 = k_scatter<K, kScatterThreads, Cfg<K>::kItems1, true>;
-    const size_t smem = size_t(Cfg<K>::kTile1) * sizeof(Tuple<K>);
-    HJ_TRY(set_smem(ctx, k3, smem));
-    k3<<<pr.meta.n_tiles, kScatterThreads, smem, st>>>(a);
-    HJ_LAUNCH_CHECK(ctx, "k_scatter<pass1>");
-    nl->n++;
-    if (bits2) {
-      a.in = tup_a;
-      a.out = tup_b;
-      a.cursors = cur2;
-      a.null_policy = kNullAsValue;  // pass 2 sees tuples only
-      auto k3b = k_scatter<K, kScatterThreads, kItems2, false>;
-      const size_t smem2 = size_t(kTile2) * sizeof(Tuple<K>);
-      HJ_TRY(set_smem(ctx, k3b, smem2));
-      const uint32_t grid2 = (n + kTile2 - 1) / kTile2 + F1;  // upper bound on sum(ceil(part/tile))
-      if (ev_after_pass1) HJ_CUDA(ctx, cudaEventRecord(ev_after_pass1, st));
-      k3b<<<grid2, kScatterThreads, smem2, st>>>(a);
-      HJ_LAUNCH_CHECK(ctx, "k_scatter<pass2>");
-      nl->n++;
-    }
-  }
-  *out_pass1 = tup_a;
-  *out_tuples = bits2 ? tup_b : tup_a;
+template <typename K>
+ScatterArgs<K> scatter_args(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int bits2, int null_policy) {
+  ScatterArgs<K> a{};
+  a.rel = pr.meta;
+  a.keys_mat = static_cast<const K*>(ctx->keys_mat[side].p);
+  a.valid_mask = static_cast<const uint32_t*>(ctx->valid_mask[side].p);
+  a.base1 = static_cast<const uint32_t*>(ctx->hist1[side].p);
+  a.in = static_cast<const Tuple<K>*>(ctx->tup_a[side].p);
+  a.out = static_cast<Tuple<K>*>(ctx->tup_a[side].p);
+  a.cur2 = static_cast<uint32_t*>(ctx->cur2[side].p);
+  a.part_off = static_cast<const uint32_t*>(ctx->part_off[side].p);
+  a.l1_tiles = static_cast<const uint32_t*>(ctx->l1_tiles[side].p);
+  a.radix_bits = radix_bits;
+  a.bits2 = bits2;
+  a.null_policy = null_policy;
+  return a;
+}
+
+template <typename K>
+int stage_pass1(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int bits2, int null_policy,
+                const PartState& ps, cudaStream_t st, Launches* nl) {
+  if (!pr.meta.n_tiles) return HJ_OK;
+  ScatterArgs<K> a = scatter_args<K>(ctx, pr, side, radix_bits, bits2, null_policy);
+  auto k = k_scatter1<K, kScatterThreads, Cfg<K>::kItems1>;
+  const size_t smem = size_t(tile1<K>()) * sizeof(Tuple<K>);
+  HJ_TRY(set_smem(ctx, k, smem));
+  k<<<ps.G, kScatterThreads, smem, st>>>(a);
+  HJ_LAUNCH_CHECK(ctx, "k_scatter1");
+  nl->n++;
+  return HJ_OK;
+}
+
+template <typename K>
+int stage_pass2(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int bits2, cudaStream_t st, Launches* nl) {
+  if (!pr.meta.n_tiles || !bits2) return HJ_OK;
+  ScatterArgs<K> a = scatter_args<K>(ctx, pr, side, radix_bits, bits2, kNullAsValue);
+  a.out = static_cast<Tuple<K>*>(ctx->tup_b[side].p);
+  auto k = k_scatter2<K, kScatterThreads, Cfg<K>::kItems2>;
+  const size_t smem = size_t(tile2<K>()) * sizeof(Tuple<K>);
+  HJ_TRY(set_smem(ctx, k, smem));
+  const uint32_t F1 = (1u << radix_bits) >> bits2;
+  const uint32_t grid = (pr.meta.n_rows + tile2<K>() - 1) / tile2<K>() + F1;  // upper bound on sum(ceil(part / tile))
+  k<<<grid, kScatterThreads, smem, st>>>(a);
+  HJ_LAUNCH_CHECK(ctx, "k_scatter2");
+  nl->n++;
   return HJ_OK;
 }
 
 struct Readback {  // layout of the pinned readback area
-  unsigned long long cursor;
+  OutState out;
   PlanOut plan;
   uint32_t n_build_tuples;
   uint32_t n_probe_tuples;
@@ -401,32 +419,52 @@ float ev_ms(cudaEvent_t a, cudaEvent_t b) {
   return ms;
 }
 
+template <typename K, bool FAST>
+int launch_build_probe(hj_ctx* ctx, const JoinArgs<K>& a, cudaStream_t st) {
+  auto k5 = k_build_probe<K, kJoinThreads, Cfg<K>::kNS, Cfg<K>::kCap, kProbeV, FAST>;
+  const size_t smem5 = (size_t(Cfg<K>::kNS) + 1) * sizeof(K) + (size_t(Cfg<K>::kNS) + 2) * 4 + size_t(Cfg<K>::kCap) * 4;
+  HJ_TRY(set_smem(ctx, k5, smem5));
+  k5<<<ctx->n_sms, kJoinThreads, smem5, st>>>(a);
+  HJ_LAUNCH_CHECK(ctx, "k_build_probe");
+  return HJ_OK;
+}
+
 template <typename K>
 int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, int mode, cudaStream_t st,
              hj_result_info* info) {
-  const bool timed = ctx->opts.flags & HJ_FLAG_TIMINGS;
   const bool one_side = mode == HJ_MODE_SEMI || mode == HJ_MODE_ANTI;
   const bool outer = mode == HJ_MODE_LEFT || mode == HJ_MODE_RIGHT;
   Launches nl;
   cudaEvent_t* ev = ctx->ev;
-  HJ_CUDA(ctx, cudaEventRecord(ev[0], st));  // start
+  // events: 0 start, 1 after staging, 2 after K1/K2, 3 after pass 1, 4 after pass 2, 5 after build+probe, 6 end
+  HJ_CUDA(ctx, cudaEventRecord(ev[0], st));
 
   PreparedRel pb, pp;
-  HJ_TRY(prepare_relation(ctx, build, 0, Cfg<K>::kTile1, st, &pb));
-  HJ_TRY(prepare_relation(ctx, probe, 1, Cfg<K>::kTile1, st, &pp));
-  HJ_CUDA(ctx, cudaEventRecord(ev[1], st));  // after H2D
+  HJ_TRY(prepare_relation(ctx, build, 0, tile1<K>(), st, &pb));
+  HJ_TRY(prepare_relation(ctx, probe, 1, tile1<K>(), st, &pp));
+  HJ_CUDA(ctx, cudaEventRecord(ev[1], st));
 
-  int radix_bits = ctx->opts.radix_bits >= 0 ? std::min(ctx->opts.radix_bits, kMaxRadixBits)
-                                             : radix_bits_for(build->n_rows, sizeof(K) == 8 ? HJ_KEY_INT64 : HJ_KEY_INT32);
+  const int radix_bits = ctx->opts.radix_bits >= 0 ? std::min(ctx->opts.radix_bits, kMaxRadixBits)
+                                                   : radix_bits_for(build->n_rows, sizeof(K) == 8 ? HJ_KEY_INT64 : HJ_KEY_INT32);
   const int bits2 = radix_bits > kSinglePassMaxBits ? radix_bits / 2 : 0;
   const uint32_t P = 1u << radix_bits;
-
   const int probe_null_policy = !outer ? kNullDrop : ((ctx->opts.flags & HJ_FLAG_SQL_NULL_PROBE) ? kNullRoute : kNullAsValue);
-  const Tuple<K>*tb = nullptr, *tp = nullptr, *tb1 = nullptr, *tp1 = nullptr;
-  HJ_TRY(partition_relation<K>(ctx, pb, 0, radix_bits, bits2, kNullDrop, st, &nl, &tb, &tb1, nullptr, nullptr));
-  HJ_TRY(partition_relation<K>(ctx, pp, 1, radix_bits, bits2, probe_null_policy, st, &nl, &tp, &tp1,
-                               timed ? ev[2] : nullptr, timed ? ev[3] : nullptr));
-  HJ_CUDA(ctx, cudaEventRecord(ev[4], st));  // after partitioning
+
+  PartState sb, sp;
+  HJ_TRY(stage_alloc<K>(ctx, pb, 0, radix_bits, bits2, &sb));
+  HJ_TRY(stage_alloc<K>(ctx, pp, 1, radix_bits, bits2, &sp));
+  HJ_TRY(stage_hist<K>(ctx, pb, 0, radix_bits, bits2, kNullDrop, sb, st, &nl));
+  HJ_TRY(stage_hist<K>(ctx, pp, 1, radix_bits, bits2, probe_null_policy, sp, st, &nl));
+  HJ_CUDA(ctx, cudaEventRecord(ev[2], st));
+  HJ_TRY(stage_pass1<K>(ctx, pb, 0, radix_bits, bits2, kNullDrop, sb, st, &nl));
+  HJ_TRY(stage_pass1<K>(ctx, pp, 1, radix_bits, bits2, probe_null_policy, sp, st, &nl));
+  HJ_CUDA(ctx, cudaEventRecord(ev[3], st));
+  HJ_TRY(stage_pass2<K>(ctx, pb, 0, radix_bits, bits2, st, &nl));
+  HJ_TRY(stage_pass2<K>(ctx, pp, 1, radix_bits, bits2, st, &nl));
+  HJ_CUDA(ctx, cudaEventRecord(ev[4], st));
+  const auto* tb = static_cast<const Tuple<K>*>(bits2 ? ctx->tup_b[0].p : ctx->tup_a[0].p);
+  const auto* tp = static_cast<const Tuple<K>*>(bits2 ? ctx->tup_b[1].p : ctx->tup_a[1].p);
+  const auto* tp1 = static_cast<const Tuple<K>*>(ctx->tup_a[1].p);  // routed NULL rows stay in pass 1's output
 
   // ---- plan
   const uint32_t cap = Cfg<K>::kCap;
@@ -435,21 +473,25 @@ int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, in
   HJ_TRY(ensure(ctx, ctx->fin, size_t(P) * sizeof(WorkItem)));
   HJ_TRY(ensure(ctx, ctx->plan, sizeof(PlanOut)));
   HJ_TRY(ensure(ctx, ctx->queue, 256));
-  HJ_TRY(ensure(ctx, ctx->cursor, 256));
+  HJ_TRY(ensure(ctx, ctx->out_state, sizeof(OutState)));
+  HJ_TRY(ensure(ctx, ctx->out_tails, sizeof(OutTail) * kMaxTails));
+  HJ_TRY(ensure(ctx, ctx->compact_plan, sizeof(CompactPlan)));
   const size_t matched_bytes = (size_t(probe->n_rows) / 32 + 2) * 4;
   if (mode != HJ_MODE_INNER) HJ_TRY(ensure(ctx, ctx->matched, matched_bytes));
   auto* off_b = static_cast<uint32_t*>(ctx->part_off[0].p);
   auto* off_p = static_cast<uint32_t*>(ctx->part_off[1].p);
-  k_plan<1024><<<1, 1024, 0, st>>>(off_b, off_p, radix_bits, mode, cap, kProbeSlice, (uint32_t)std::min<size_t>(items_capacity, 0xFFFFFFFFu),
+  k_plan<1024><<<1, 1024, 0, st>>>(off_b, off_p, radix_bits, mode, cap, kProbeSlice,
+                                   (uint32_t)std::min<size_t>(items_capacity, 0xFFFFFFFFu),
                                    static_cast<WorkItem*>(ctx->items.p), static_cast<WorkItem*>(ctx->fin.p),
                                    static_cast<PlanOut*>(ctx->plan.p));
   HJ_LAUNCH_CHECK(ctx, "k_plan");
   nl.n++;
 
-  // ---- output buffers
-  uint64_t capacity = ctx->opts.output_capacity ? ctx->opts.output_capacity
-                                                : (one_side ? probe->n_rows : probe->n_rows + 1024);
-  capacity = std::max<uint64_t>(capacity, 1);
+  // ---- output buffers: `rows` result rows + one chunk of slack per CTA that writes results
+  const uint32_t writer_ctas = ctx->n_sms * (1 + (mode != HJ_MODE_INNER ? 1 : 0) + (probe_null_policy == kNullRoute ? 1 : 0));
+  auto alloc_rows = [&](uint64_t rows) { return ((rows + kChunkRows - 1) / kChunkRows + writer_ctas + 1) * uint64_t(kChunkRows); };
+  uint64_t want_rows = ctx->opts.output_capacity ? ctx->opts.output_capacity : probe->n_rows;
+  uint64_t capacity = alloc_rows(want_rows);
 
   JoinArgs<K> a{};
   a.build = tb;
@@ -459,14 +501,13 @@ int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, in
   a.queue_head = static_cast<uint32_t*>(ctx->queue.p);
   a.build_rel = pb.meta;
   a.probe_rel = pp.meta;
-  a.out_cursor = static_cast<unsigned long long*>(ctx->cursor.p);
+  a.out_state = static_cast<OutState*>(ctx->out_state.p);
+  a.out_tails = static_cast<OutTail*>(ctx->out_tails.p);
   a.matched = static_cast<uint32_t*>(ctx->matched.p);
   a.radix_bits = radix_bits;
   a.mode = mode;
+  const bool fast_rowid = pb.meta.uniform_shift >= 0 && pb.meta.identity && pp.meta.uniform_shift >= 0 && pp.meta.identity;
 
-  auto k5 = k_build_probe<K, kJoinThreads, Cfg<K>::kNS, Cfg<K>::kCap, kProbeV>;
-  const size_t smem5 = (size_t(Cfg<K>::kNS) + 1) * sizeof(K) + (size_t(Cfg<K>::kNS) + 2) * 4 + size_t(Cfg<K>::kCap) * 4;
-  HJ_TRY(set_smem(ctx, k5, smem5));
   auto* rb = static_cast<Readback*>(ctx->pinned);
   int passes = 0;
   for (;;) {
@@ -477,38 +518,42 @@ int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, in
     a.out_probe = static_cast<uint64_t*>(ctx->out_probe.p);
     a.capacity = capacity;
     HJ_CUDA(ctx, cudaMemsetAsync(ctx->queue.p, 0, 4, st));
-    HJ_CUDA(ctx, cudaMemsetAsync(ctx->cursor.p, 0, 8, st));
+    HJ_CUDA(ctx, cudaMemsetAsync(ctx->out_state.p, 0, sizeof(OutState), st));
     if (mode != HJ_MODE_INNER) HJ_CUDA(ctx, cudaMemsetAsync(ctx->matched.p, 0, matched_bytes, st));
-    k5<<<ctx->n_sms, kJoinThreads, smem5, st>>>(a);
-    HJ_LAUNCH_CHECK(ctx, "k_build_probe");
+    if (fast_rowid) HJ_TRY((launch_build_probe<K, true>(ctx, a, st))); else HJ_TRY((launch_build_probe<K, false>(ctx, a, st)));
     nl.n++;
-    if (passes == 1) HJ_CUDA(ctx, cudaEventRecord(ev[5], st));  // after build+probe
+    if (passes == 1) HJ_CUDA(ctx, cudaEventRecord(ev[5], st));
     if (mode != HJ_MODE_INNER) {
-      k_finalize_multi<K, 256><<<ctx->n_sms * 4, 256, 0, st>>>(a, static_cast<const WorkItem*>(ctx->fin.p));
+      k_finalize_multi<K, 256><<<ctx->n_sms, 256, 0, st>>>(a, static_cast<const WorkItem*>(ctx->fin.p));
       HJ_LAUNCH_CHECK(ctx, "k_finalize_multi");
       nl.n++;
     }
     if (probe_null_policy == kNullRoute) {
-      k_emit_null_probe<K, 256><<<ctx->n_sms * 4, 256, 0, st>>>(a, tp1, off_p);
+      k_emit_null_probe<K, 256><<<ctx->n_sms, 256, 0, st>>>(a, tp1, off_p);
       HJ_LAUNCH_CHECK(ctx, "k_emit_null_probe");
       nl.n++;
     }
-    HJ_CUDA(ctx, cudaMemcpyAsync(&rb->cursor, ctx->cursor.p, 8, cudaMemcpyDeviceToHost, st));
+    k_compact_plan<<<1, 1024, 0, st>>>(a.out_state, a.out_tails, static_cast<CompactPlan*>(ctx->compact_plan.p));
+    HJ_LAUNCH_CHECK(ctx, "k_compact_plan");
+    k_compact_move<<<ctx->n_sms * 8, 256, 0, st>>>(static_cast<const CompactPlan*>(ctx->compact_plan.p), a.out_build, a.out_probe, capacity);
+    HJ_LAUNCH_CHECK(ctx, "k_compact_move");
+    nl.n += 2;
+    HJ_CUDA(ctx, cudaMemcpyAsync(&rb->out, ctx->out_state.p, sizeof(OutState), cudaMemcpyDeviceToHost, st));
     HJ_CUDA(ctx, cudaMemcpyAsync(&rb->plan, ctx->plan.p, sizeof(PlanOut), cudaMemcpyDeviceToHost, st));
     HJ_CUDA(ctx, cudaMemcpyAsync(&rb->n_build_tuples, off_b + P, 4, cudaMemcpyDeviceToHost, st));
     HJ_CUDA(ctx, cudaMemcpyAsync(&rb->n_probe_tuples, off_p + P + 1, 4, cudaMemcpyDeviceToHost, st));
-    HJ_CUDA(ctx, cudaEventRecord(ev[6], st));  // end
+    HJ_CUDA(ctx, cudaEventRecord(ev[6], st));
     HJ_CUDA(ctx, cudaStreamSynchronize(st));
-    if (rb->cursor <= capacity) break;
-    if (passes >= 2) return fail(ctx, HJ_ERR_CUDA, "result count changed between probe passes (%llu > %llu)", rb->cursor,
-                                 (unsigned long long)capacity);
-    capacity = rb->cursor;  // exact size is known now: re-probe into buffers that fit
+    if (rb->out.n_chunks * kChunkRows <= capacity) break;  // every reserved chunk lay inside the buffers
+    if (passes >= 2) return fail(ctx, HJ_ERR_CUDA, "result size changed between probe passes (%llu chunks > capacity %llu rows)",
+                                 rb->out.n_chunks, (unsigned long long)capacity);
+    capacity = alloc_rows(rb->out.n_rows);  // the exact row count is known now: re-probe into buffers that fit
   }
 
   ctx->has_result = true;
-  ctx->n_result = rb->cursor;
+  ctx->n_result = rb->out.n_rows;
   ctx->n_sides = one_side ? 1 : 2;
-  info->n_rows = rb->cursor;
+  info->n_rows = rb->out.n_rows;
   info->n_sides = ctx->n_sides;
   info->radix_bits = radix_bits;
   info->n_build_tuples = rb->n_build_tuples;
@@ -522,12 +567,9 @@ int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, in
   std::memset(&t, 0, sizeof(t));
   t.ms[HJ_PH_TOTAL] = ev_ms(ev[0], ev[6]);
   t.ms[HJ_PH_H2D] = ev_ms(ev[0], ev[1]);
-  if (timed) {
-    // phases are recorded on the probe relation's partitioning (the larger side) + the common stages
-    t.ms[HJ_PH_MATERIALIZE] = ev_ms(ev[1], ev[2]);  // build relation entirely + probe K1/K2
-    t.ms[HJ_PH_SCATTER1] = bits2 ? ev_ms(ev[2], ev[3]) : ev_ms(ev[2], ev[4]);
-    t.ms[HJ_PH_SCATTER2] = bits2 ? ev_ms(ev[3], ev[4]) : 0.f;
-  }
+  t.ms[HJ_PH_MATERIALIZE] = ev_ms(ev[1], ev[2]);
+  t.ms[HJ_PH_SCATTER1] = ev_ms(ev[2], ev[3]);
+  t.ms[HJ_PH_SCATTER2] = ev_ms(ev[3], ev[4]);
   t.ms[HJ_PH_BUILD_PROBE] = passes == 1 ? ev_ms(ev[4], ev[5]) : 0.f;
   t.ms[HJ_PH_FINALIZE] = passes == 1 ? ev_ms(ev[5], ev[6]) : 0.f;
   t.bytes_h2d = pb.h2d_bytes + pp.h2d_bytes;

@@ -1,22 +1,32 @@
 // hj_kernels.cuh — the hand-written sm_100a kernels of libhj. One translation unit (hj_api.cu) includes this.
 //
 //  K1 k_materialize_hist   replaces materialize_input            (reference join_hash.cpp:203-285)
-//  K2 k_offsets            replaces the serial prefix sum         (join_hash.cpp:310-319)
-//  K3 k_scatter<FromSegs>  replaces partition_radix_parallel      (join_hash.cpp:287-355), pass 1 from the segments,
-//                          pass 2 from pass 1's output
-//  K4 k_plan               work list for K5 (no reference counterpart: the reference schedules one JobTask per
-//                          partition, join_hash.cpp:150,387,485)
+//  K2 k_offsets(+_l1)      replaces the serial prefix sum         (join_hash.cpp:310-319)
+//  K3 k_scatter1/2         replaces partition_radix_parallel      (join_hash.cpp:287-355): pass 1 from the chunks, pass 2
+//                          from pass 1's output inside each level-1 partition
+//  K4 k_plan               work list for K5 (the reference schedules one JobTask per partition, join_hash.cpp:150,387,485)
 //  K5 k_build_probe        replaces build + probe + probe_semi_anti (join_hash.cpp:127-185, 362-466, 468-527)
 //  K6 k_finalize_multi     unmatched-row emission for build partitions larger than one shared-memory table
 //  K7 k_emit_null_probe    (NULL, p) rows for NULL probe keys under HJ_FLAG_SQL_NULL_PROBE
-//  K8 k_translate          PosList dereferencing of write_output_columns (join_hash.cpp:584-592)
+//  K8 k_compact_plan/_move closes the holes the chunked output allocator leaves at CTA tails (dense PosLists)
+//  K9 k_translate          PosList dereferencing of write_output_columns (join_hash.cpp:584-592)
+//
+// Measured facts behind the design (profiles/r01_microbench_*.txt, profiles/r01_ncu_v0_*.md):
+//   * shared-memory atomics run at ~7.5 lanes/clk/SM — cheap enough to rank every tuple with one;
+//   * atomics on ONE global address serialise at ~21 ns each, so nothing on a hot path may hit a single global
+//     counter per tile: pass 1 gets private cursors from per-CTA histograms, pass 2 permutes its tile order so that
+//     concurrent CTAs touch different cursors, the result writer reserves 128 Ki-row chunks per CTA;
+//   * the kernels are issue/latency-bound, not DRAM-bound, so the hot loops are kept short (run-wise copies, ballot
+//     prefix sums, register prefetch of the next tile).
 #pragma once
 #include "hj_device.cuh"
 
 namespace hj {
 
+constexpr int kMaxDigits = 256;  // fan-out per scatter pass (8 bits)
+
 // =====================================================================================================================
-// Row loader shared by K1 and K3<FromSegs>: decodes row `i` of a segment into (key, valid).
+// Row loaders shared by K1 and pass 1.
 // =====================================================================================================================
 template <typename K>
 __device__ __forceinline__ K load_plain_key(const DevSegment& s, uint32_t i) {
@@ -30,78 +40,72 @@ __device__ __forceinline__ uint32_t load_attr(const DevSegment& s, uint32_t i) {
 }
 
 // =====================================================================================================================
-// K1: materialize + histogram.
-//   DICT chunks: attr -> dictionary gather (served by L2) -> decoded key written once to `keys_mat` (so that the
-//   scatter pass does not repeat the gather) + one validity bit per row; VALUE/GATHERED chunks are only read.
-//   Every kept row increments a full-resolution (2^radix_bits bins) shared-memory histogram; CTAs are persistent so
-//   the histogram is flushed to global memory once per CTA.
-// grid: min(n_tiles, SMs * occupancy), block: NT threads, dynamic smem: (2^radix_bits + 1) * 4 bytes.
+// K1: materialize + histogram. Persistent "virtual CTA" c owns tiles c, c+G, c+2G, ... (G = gridDim.x); pass 1 uses the
+// same ownership, which is what makes its write cursors private.
+//   DICT chunks: attr -> dictionary gather (served by L2; this gather is the L1tex-bound part of the whole join) ->
+//   decoded key written once to `keys_mat` + one validity bit per row; VALUE/GATHERED chunks are only read.
+//   Every kept row increments a full-resolution (2^radix_bits bins) shared-memory histogram. At the end the CTA adds it
+//   to the global histogram and stores its own level-1 digit counts to hist1[d * G + c].
+// block: NT threads, dynamic smem: (2^radix_bits + 1) * 4 bytes.
 // =====================================================================================================================
 template <typename K, int NT, int TILE>
 __global__ void __launch_bounds__(NT) k_materialize_hist(RelMeta rel, K* __restrict__ keys_mat,
                                                          uint32_t* __restrict__ valid_mask,
-                                                         uint32_t* __restrict__ hist, int radix_bits, int null_policy) {
+                                                         uint32_t* __restrict__ hist, uint32_t* __restrict__ hist1,
+                                                         int radix_bits, int bits2, int null_policy) {
   extern __shared__ uint32_t s_hist[];
-  const uint32_t n_bins = (1u << radix_bits) + 1u;  // last bin: NULL rows routed aside (kNullRoute)
-  const uint32_t pmask = (1u << radix_bits) - 1u;
+  const uint32_t P = 1u << radix_bits;
+  const uint32_t n_bins = P + 1u;  // last bin: NULL rows routed aside (kNullRoute)
+  const uint32_t pmask = P - 1u;
   for (uint32_t b = threadIdx.x; b < n_bins; b += NT) s_hist[b] = 0;
   __syncthreads();
 
   constexpr int ITEMS = TILE / NT;
-  constexpr int U = ITEMS < 4 ? ITEMS : 4;
   for (uint32_t tile = blockIdx.x; tile < rel.n_tiles; tile += gridDim.x) {
     const uint32_t seg_idx = __ldg(rel.tile_seg + tile);
     const DevSegment s = rel.segs[seg_idx];
     const uint32_t r0 = (tile - s.tile_begin) * TILE;
     const uint32_t cnt = min(static_cast<uint32_t>(TILE), s.n_rows - r0);
-    const bool is_dict = s.kind == 1;
-#pragma unroll 1
-    for (int j0 = 0; j0 < ITEMS; j0 += U) {
-      K key[U];
-      bool valid[U], active[U];
-      if (is_dict) {
-        uint32_t vid[U];
+    K key[ITEMS];
+    bool valid[ITEMS], active[ITEMS];
+    if (s.kind == 1) {
+      uint32_t vid[ITEMS];
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const uint32_t i = (j0 + u) * NT + threadIdx.x;
-          active[u] = i < cnt;
-          vid[u] = active[u] ? load_attr(s, r0 + i) : s.null_value_id;
-        }
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          valid[u] = active[u] && vid[u] != s.null_value_id;
-          key[u] = valid[u] ? load_plain_key<K>(s, vid[u]) : K(0);  // NULL decodes to T{} (dictionary_column_iterable.hpp:80)
-        }
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const uint32_t i = (j0 + u) * NT + threadIdx.x;
-          if (active[u]) keys_mat[s.row_begin + r0 + i] = key[u];
-          const uint32_t bits = __ballot_sync(0xffffffffu, valid[u]);
-          // rows r0+i for one warp instruction are 32 consecutive rows starting at a multiple of 32
-          if (lane_id() == 0 && (i - lane_id()) < cnt) valid_mask[s.mask_word_begin + ((r0 + i) >> 5)] = bits;
-        }
-      } else {
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const uint32_t i = (j0 + u) * NT + threadIdx.x;
-          active[u] = i < cnt;
-          key[u] = active[u] ? load_plain_key<K>(s, r0 + i) : K(0);
-          valid[u] = active[u] && !(s.nulls && __ldg(s.nulls + r0 + i));
-        }
-        if (s.kind == 2) {  // GATHERED: a NULL position yields T{} (reference_column_iterable.hpp:60)
-#pragma unroll
-          for (int u = 0; u < U; ++u)
-            if (!valid[u]) key[u] = K(0);
-        }
+      for (int u = 0; u < ITEMS; ++u) {
+        const uint32_t i = u * NT + threadIdx.x;
+        active[u] = i < cnt;
+        vid[u] = active[u] ? load_attr(s, r0 + i) : s.null_value_id;
       }
 #pragma unroll
-      for (int u = 0; u < U; ++u) {
-        if (!active[u]) continue;
-        if (valid[u] || null_policy == kNullAsValue) {
-          atomicAdd(&s_hist[hash_key(key[u]) & pmask], 1u);
-        } else if (null_policy == kNullRoute) {
-          atomicAdd(&s_hist[n_bins - 1], 1u);
-        }
+      for (int u = 0; u < ITEMS; ++u) {
+        valid[u] = active[u] && vid[u] != s.null_value_id;
+        key[u] = valid[u] ? load_plain_key<K>(s, vid[u]) : K(0);  // NULL decodes to T{} (dictionary_column_iterable.hpp:80)
+      }
+#pragma unroll
+      for (int u = 0; u < ITEMS; ++u) {
+        const uint32_t i = u * NT + threadIdx.x;
+        if (active[u]) keys_mat[s.row_begin + r0 + i] = key[u];
+        const uint32_t bits = __ballot_sync(0xffffffffu, valid[u]);
+        // one warp instruction covers 32 consecutive rows starting at a multiple of 32
+        if (lane_id() == 0 && active[u]) valid_mask[s.mask_word_begin + ((r0 + i) >> 5)] = bits;
+      }
+    } else {
+#pragma unroll
+      for (int u = 0; u < ITEMS; ++u) {
+        const uint32_t i = u * NT + threadIdx.x;
+        active[u] = i < cnt;
+        key[u] = active[u] ? load_plain_key<K>(s, r0 + i) : K(0);
+        valid[u] = active[u] && !(s.nulls && __ldg(s.nulls + r0 + i));
+        if (s.kind == 2 && !valid[u]) key[u] = K(0);  // GATHERED NULL yields T{} (reference_column_iterable.hpp:60)
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < ITEMS; ++u) {
+      if (!active[u]) continue;
+      if (valid[u] || null_policy == kNullAsValue) {
+        atomicAdd(&s_hist[hash_key(key[u]) & pmask], 1u);
+      } else if (null_policy == kNullRoute) {
+        atomicAdd(&s_hist[P], 1u);
       }
     }
   }
@@ -110,20 +114,29 @@ __global__ void __launch_bounds__(NT) k_materialize_hist(RelMeta rel, K* __restr
     const uint32_t c = s_hist[b];
     if (c) atomicAdd(hist + b, c);
   }
+  // this CTA's level-1 digit counts (digit F1 = routed NULLs)
+  const uint32_t F1 = P >> bits2, F2 = 1u << bits2;
+  for (uint32_t d = threadIdx.x; d <= F1; d += NT) {
+    uint32_t sum = 0;
+    if (d == F1) {
+      sum = s_hist[P];
+    } else {
+      for (uint32_t q = 0; q < F2; ++q) sum += s_hist[(d << bits2) + ((q + d) & (F2 - 1u))];  // rotated: no bank conflicts
+    }
+    hist1[d * gridDim.x + blockIdx.x] = sum;
+  }
 }
 
 // =====================================================================================================================
-// K2: offsets. One CTA turns the histogram into
+// K2: offsets. One CTA turns the global histogram into
 //   part_off[P+2] : start of every final partition, part_off[P] = start of the routed-NULL region, part_off[P+1] = total
-//   cur1[F1+1]    : pass-1 write cursors (one per level-1 partition, + the NULL region)
 //   cur2[P]       : pass-2 write cursors
 //   l1_tiles[F1+1]: prefix sum of ceil(level-1 partition size / tile2) — tile -> partition map for pass 2
 // =====================================================================================================================
 template <int NT>
 __global__ void __launch_bounds__(NT) k_offsets(const uint32_t* __restrict__ hist, uint32_t* __restrict__ part_off,
-                                                uint32_t* __restrict__ cur1, uint32_t* __restrict__ cur2,
-                                                uint32_t* __restrict__ l1_tiles, int radix_bits, int bits2,
-                                                uint32_t tile2) {
+                                                uint32_t* __restrict__ cur2, uint32_t* __restrict__ l1_tiles,
+                                                int radix_bits, int bits2, uint32_t tile2) {
   __shared__ uint32_t scratch[33];
   __shared__ uint32_t s_carry;
   const uint32_t P = 1u << radix_bits;
@@ -138,8 +151,6 @@ __global__ void __launch_bounds__(NT) k_offsets(const uint32_t* __restrict__ his
     if (b < n) {
       part_off[b] = ex;
       if (b < P) cur2[b] = ex;
-      if (b == P) cur1[P >> bits2] = ex;
-      else if ((b & ((1u << bits2) - 1u)) == 0) cur1[b >> bits2] = ex;
     }
     __syncthreads();
     if (threadIdx.x == 0) s_carry += total;
@@ -147,7 +158,6 @@ __global__ void __launch_bounds__(NT) k_offsets(const uint32_t* __restrict__ his
   }
   if (threadIdx.x == 0) part_off[P + 1] = s_carry;
   __syncthreads();
-  // level-1 tile prefix (F1 <= 512 entries)
   const uint32_t F1 = P >> bits2;
   if (threadIdx.x == 0) s_carry = 0;
   __syncthreads();
@@ -168,24 +178,45 @@ __global__ void __launch_bounds__(NT) k_offsets(const uint32_t* __restrict__ his
   if (threadIdx.x == 0) l1_tiles[F1] = s_carry;
 }
 
+// K2b: per level-1 digit d (one CTA each, digit F1 = routed NULLs), turns the per-CTA counts hist1[d*G + c] in place into
+// pass 1's private write cursors: start of the digit's region + exclusive prefix over the virtual CTAs c.
+template <int NT>
+__global__ void __launch_bounds__(NT) k_offsets_l1(uint32_t* __restrict__ hist1, const uint32_t* __restrict__ part_off,
+                                                   int radix_bits, int bits2, uint32_t G) {
+  __shared__ uint32_t scratch[33];
+  __shared__ uint32_t s_carry;
+  const uint32_t P = 1u << radix_bits, F1 = P >> bits2, d = blockIdx.x;
+  if (threadIdx.x == 0) s_carry = d < F1 ? part_off[d << bits2] : part_off[P];
+  __syncthreads();
+  for (uint32_t base = 0; base < G; base += NT) {
+    const uint32_t c = base + threadIdx.x;
+    const uint32_t v = c < G ? hist1[d * G + c] : 0u;
+    uint32_t total;
+    const uint32_t ex = block_excl_scan(v, scratch, &total) + s_carry;
+    if (c < G) hist1[d * G + c] = ex;
+    __syncthreads();
+    if (threadIdx.x == 0) s_carry += total;
+    __syncthreads();
+  }
+}
+
 // =====================================================================================================================
-// K3: radix scatter, one tile per CTA.
-//   rank every tuple inside its digit with a shared-memory atomic, scan the digit counts, reserve the tile's slice of
-//   every destination partition with ONE global atomic per (tile, digit), reorder the tile in shared memory so that
-//   each digit is a contiguous run, then copy the runs out with consecutive threads writing consecutive addresses.
-//   FROM_SEGS = true : pass 1, reads the chunks (decoded keys of DICT chunks come from keys_mat), digit = high bits.
-//   FROM_SEGS = false: pass 2, reads pass 1's output inside one level-1 partition, digit = low `bits2` bits.
+// K3: radix scatter. Per tile of NT*ITEMS tuples:
+//   rank every tuple inside its digit with one shared-memory atomic, scan the digit counts, reorder the tile in shared
+//   memory so that each digit is a contiguous run, then copy the runs out warp by warp (consecutive lanes on consecutive
+//   addresses; no per-tuple address lookup in the copy loop).
 // Within a partition the tuple order is arbitrary (the reference guarantees none: join_hash.hpp:19-20).
-// block: NT threads, dynamic smem: NT*ITEMS*sizeof(Tuple<K>).
+// dynamic smem: NT*ITEMS*sizeof(Tuple<K>).
 // =====================================================================================================================
 template <typename K>
 struct ScatterArgs {
   RelMeta rel;                  // pass 1
   const K* keys_mat;            // pass 1
   const uint32_t* valid_mask;   // pass 1
+  const uint32_t* base1;        // pass 1: private cursors [d * G + c]
   const Tuple<K>* in;           // pass 2
   Tuple<K>* out;
-  uint32_t* cursors;            // pass 1: cur1[F1+1]; pass 2: cur2[P]
+  uint32_t* cur2;               // pass 2: global cursors, one per final partition
   const uint32_t* part_off;     // pass 2
   const uint32_t* l1_tiles;     // pass 2
   int radix_bits;
@@ -193,120 +224,168 @@ struct ScatterArgs {
   int null_policy;
 };
 
-constexpr int kMaxDigits = 256;  // per pass; + 1 NULL bin in pass 1
+constexpr uint32_t kNoDigit = 0xFFFFFFFFu;
 
-template <typename K, int NT, int ITEMS, bool FROM_SEGS>
-__global__ void __launch_bounds__(NT, 2) k_scatter(const ScatterArgs<K> a) {
+// Copies the staged runs out: warp w takes digits w, w+NW, ...; s_gbase[d] is the global element index of run d.
+template <typename K, int NT>
+__device__ __forceinline__ void copy_runs_out(const Tuple<K>* stage, Tuple<K>* out, const uint32_t* s_loff,
+                                              const uint32_t* s_gbase, uint32_t n_runs) {
+  constexpr uint32_t NW = NT / 32;
+  for (uint32_t d = warp_id(); d < n_runs; d += NW) {
+    const uint32_t lo = s_loff[d], n = s_loff[d + 1] - lo;
+    const Tuple<K>* src = stage + lo;
+    Tuple<K>* dst = out + s_gbase[d];
+    for (uint32_t i = lane_id(); i < n; i += 32) dst[i] = src[i];
+  }
+}
+
+// Pass 1: persistent virtual CTA c = blockIdx.x owns tiles c, c+G, ... exactly as in K1, so the cursors computed from K1's
+// per-CTA counts (base1) are private: no global atomics, deterministic placement. Digit = high (radix_bits - bits2) bits
+// of the partition index; routed NULL rows form run number F1.
+template <typename K, int NT, int ITEMS>
+__global__ void __launch_bounds__(NT, 4) k_scatter1(const ScatterArgs<K> a) {
   constexpr uint32_t TILE = NT * ITEMS;
-  constexpr uint32_t NONE = 0xFFFFFFFFu;
   extern __shared__ __align__(16) unsigned char s_raw[];
   Tuple<K>* stage = reinterpret_cast<Tuple<K>*>(s_raw);
-  __shared__ uint32_t s_cnt[kMaxDigits + 1], s_loff[kMaxDigits + 2], s_gdelta[kMaxDigits + 1];
+  __shared__ uint32_t s_cnt[kMaxDigits + 1], s_loff[kMaxDigits + 2], s_gbase[kMaxDigits + 1], s_cur[kMaxDigits + 1];
+  __shared__ uint32_t scratch[33];
+
+  const uint32_t pmask = (1u << a.radix_bits) - 1u;
+  const uint32_t F1 = 1u << (a.radix_bits - a.bits2);  // <= 256 == regular digits; run F1 = routed NULLs
+  const uint32_t G = gridDim.x;
+  for (uint32_t d = threadIdx.x; d <= F1; d += NT) s_cur[d] = a.base1[d * G + blockIdx.x];
+
+  for (uint32_t tile = blockIdx.x; tile < a.rel.n_tiles; tile += G) {
+    const DevSegment seg = a.rel.segs[__ldg(a.rel.tile_seg + tile)];
+    const uint32_t r0 = (tile - seg.tile_begin) * TILE;
+    const uint32_t n_in = min(TILE, seg.n_rows - r0);
+    for (uint32_t d = threadIdx.x; d <= F1; d += NT) s_cnt[d] = 0;
+    __syncthreads();  // also orders the previous tile's run copy before this tile's staging
+
+    K key[ITEMS];
+    uint32_t packed[ITEMS];  // digit << 16 | rank inside the digit, or kNoDigit
+#pragma unroll
+    for (int j = 0; j < ITEMS; ++j) {
+      const uint32_t i = j * NT + threadIdx.x;
+      packed[j] = kNoDigit;
+      key[j] = K(0);
+      if (i < n_in) {
+        bool valid;
+        if (seg.kind == 1) {
+          key[j] = a.keys_mat[seg.row_begin + r0 + i];
+          valid = (__ldg(a.valid_mask + seg.mask_word_begin + ((r0 + i) >> 5)) >> (i & 31u)) & 1u;
+        } else {
+          key[j] = load_plain_key<K>(seg, r0 + i);
+          valid = !(seg.nulls && __ldg(seg.nulls + r0 + i));
+          if (seg.kind == 2 && !valid) key[j] = K(0);
+        }
+        uint32_t d = kNoDigit;
+        if (valid || a.null_policy == kNullAsValue) d = (hash_key(key[j]) & pmask) >> a.bits2;
+        else if (a.null_policy == kNullRoute) d = F1;
+        if (d != kNoDigit) packed[j] = (d << 16) | atomicAdd(&s_cnt[d], 1u);
+      }
+    }
+    __syncthreads();
+    {
+      // F1 <= 256 <= NT regular digits are scanned one per thread; the NULL run goes last
+      const uint32_t d = threadIdx.x;
+      const uint32_t c = d < F1 ? s_cnt[d] : 0u;
+      uint32_t total;
+      const uint32_t ex = block_excl_scan(c, scratch, &total);
+      if (d < F1) {
+        s_loff[d] = ex;
+        s_gbase[d] = s_cur[d];
+        s_cur[d] += c;
+      }
+      if (d == 0) {
+        const uint32_t cn = s_cnt[F1];
+        s_loff[F1] = total;
+        s_loff[F1 + 1] = total + cn;
+        s_gbase[F1] = s_cur[F1];
+        s_cur[F1] += cn;
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < ITEMS; ++j) {
+      if (packed[j] != kNoDigit) {
+        Tuple<K> t;
+        t.key = key[j];
+        t.idx = seg.row_begin + r0 + j * NT + threadIdx.x;
+        if constexpr (sizeof(K) == 8) t.pad = 0;
+        stage[s_loff[packed[j] >> 16] + (packed[j] & 0xFFFFu)] = t;
+      }
+    }
+    __syncthreads();
+    copy_runs_out<K, NT>(stage, a.out, s_loff, s_gbase, F1 + 1);
+  }
+}
+
+// Pass 2: one tile per CTA inside one level-1 partition; digit = low bits2 bits; the tile's slice of each final partition
+// is reserved with one global atomic per non-empty digit. blockIdx is mapped to the tile through a multiplicative
+// permutation so that the CTAs resident at any moment work on different level-1 partitions, i.e. on different cursors
+// (same-address atomics serialise at ~21 ns; profiles/r01_microbench_atomics_vs_match.txt).
+template <typename K, int NT, int ITEMS>
+__global__ void __launch_bounds__(NT, 4) k_scatter2(const ScatterArgs<K> a) {
+  constexpr uint32_t TILE = NT * ITEMS;
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  Tuple<K>* stage = reinterpret_cast<Tuple<K>*>(s_raw);
+  __shared__ uint32_t s_cnt[kMaxDigits], s_loff[kMaxDigits + 1], s_gbase[kMaxDigits];
   __shared__ uint32_t scratch[33];
   __shared__ uint32_t s_l1[kMaxDigits + 1];
 
-  const uint32_t pmask = (1u << a.radix_bits) - 1u;
-  uint32_t n_digits, cur_base = 0, n_in = 0, in_base = 0;
-  DevSegment seg;
-  if (FROM_SEGS) {
-    n_digits = (1u << (a.radix_bits - a.bits2)) + 1u;  // + NULL bin
-    const uint32_t tile = blockIdx.x;
-    seg = a.rel.segs[__ldg(a.rel.tile_seg + tile)];
-    in_base = (tile - seg.tile_begin) * TILE;  // first row of the tile inside the chunk
-    n_in = min(TILE, seg.n_rows - in_base);
-  } else {
-    n_digits = 1u << a.bits2;
-    const uint32_t F1 = 1u << (a.radix_bits - a.bits2);
-    for (uint32_t d = threadIdx.x; d <= F1; d += NT) s_l1[d] = a.l1_tiles[d];
-    __syncthreads();
-    if (blockIdx.x >= s_l1[F1]) return;  // grid is an upper bound
-    uint32_t lo = 0, hi = F1;  // largest d1 with s_l1[d1] <= blockIdx.x
-    while (hi - lo > 1) {
-      const uint32_t mid = (lo + hi) >> 1;
-      if (s_l1[mid] <= blockIdx.x) lo = mid; else hi = mid;
-    }
-    const uint32_t d1 = lo, k = blockIdx.x - s_l1[lo];
-    const uint32_t p_lo = a.part_off[d1 << a.bits2], p_hi = a.part_off[(d1 + 1) << a.bits2];
-    in_base = p_lo + k * TILE;
-    n_in = min(TILE, p_hi - in_base);
-    cur_base = d1 << a.bits2;
-  }
-  for (uint32_t d = threadIdx.x; d < n_digits; d += NT) s_cnt[d] = 0;
+  const uint32_t F1 = 1u << (a.radix_bits - a.bits2), F2 = 1u << a.bits2;
+  for (uint32_t d = threadIdx.x; d <= F1; d += NT) s_l1[d] = a.l1_tiles[d];
+  for (uint32_t d = threadIdx.x; d < F2; d += NT) s_cnt[d] = 0;
   __syncthreads();
+  const uint32_t total_tiles = s_l1[F1];
+  if (blockIdx.x >= total_tiles) return;  // grid is an upper bound
+  const uint32_t t = static_cast<uint32_t>((static_cast<uint64_t>(blockIdx.x) * 2654435761ull) % total_tiles);
+  uint32_t lo = 0, hi = F1;  // largest d1 with s_l1[d1] <= t
+  while (hi - lo > 1) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (s_l1[mid] <= t) lo = mid; else hi = mid;
+  }
+  const uint32_t d1 = lo;
+  const uint32_t p_hi = a.part_off[(d1 + 1) << a.bits2];
+  const uint32_t in_base = a.part_off[d1 << a.bits2] + (t - s_l1[d1]) * TILE;
+  const uint32_t n_in = min(TILE, p_hi - in_base);
+  uint32_t* cursors = a.cur2 + (d1 << a.bits2);
 
-  K key[ITEMS];
-  uint32_t idx[ITEMS];
-  uint32_t packed[ITEMS];  // digit << 16 | rank inside the digit, or NONE
+  Tuple<K> tup[ITEMS];
+  uint32_t packed[ITEMS];
 #pragma unroll
   for (int j = 0; j < ITEMS; ++j) {
     const uint32_t i = j * NT + threadIdx.x;
-    packed[j] = NONE;
-    key[j] = K(0);
-    idx[j] = 0;
+    packed[j] = kNoDigit;
+    if (i < n_in) tup[j] = a.in[in_base + i];
+  }
+#pragma unroll
+  for (int j = 0; j < ITEMS; ++j) {
+    const uint32_t i = j * NT + threadIdx.x;
     if (i < n_in) {
-      bool valid = true;
-      if (FROM_SEGS) {
-        idx[j] = seg.row_begin + in_base + i;
-        if (seg.kind == 1) {
-          key[j] = a.keys_mat[idx[j]];
-          valid = (__ldg(a.valid_mask + seg.mask_word_begin + ((in_base + i) >> 5)) >> (i & 31u)) & 1u;
-        } else {
-          key[j] = load_plain_key<K>(seg, in_base + i);
-          valid = !(seg.nulls && __ldg(seg.nulls + in_base + i));
-          if (seg.kind == 2 && !valid) key[j] = K(0);
-        }
-      } else {
-        const Tuple<K> t = a.in[in_base + i];
-        key[j] = t.key;
-        idx[j] = t.idx;
-      }
-      uint32_t d = NONE;
-      if (valid || a.null_policy == kNullAsValue) {
-        const uint32_t p = hash_key(key[j]) & pmask;
-        d = FROM_SEGS ? (p >> a.bits2) : (p & ((1u << a.bits2) - 1u));
-      } else if (a.null_policy == kNullRoute) {
-        d = n_digits - 1;
-      }
-      if (d != NONE) packed[j] = (d << 16) | atomicAdd(&s_cnt[d], 1u);
+      const uint32_t d = hash_key(tup[j].key) & (F2 - 1u);
+      packed[j] = (d << 16) | atomicAdd(&s_cnt[d], 1u);
     }
   }
   __syncthreads();
-
-  // digit counts -> local offsets; one global atomic per non-empty digit reserves the destination slice
-  uint32_t total;
   {
     const uint32_t d = threadIdx.x;
-    const uint32_t c = d < n_digits ? s_cnt[d] : 0u;
+    const uint32_t c = d < F2 ? s_cnt[d] : 0u;
+    uint32_t total;
     const uint32_t ex = block_excl_scan(c, scratch, &total);
-    if (d < n_digits) {
+    if (d < F2) {
       s_loff[d] = ex;
-      if (c) s_gdelta[d] = atomicAdd(a.cursors + cur_base + d, c) - ex;
+      if (c) s_gbase[d] = atomicAdd(cursors + d, c);
     }
-    if (d == 0) s_loff[n_digits] = total;
+    if (d == 0) s_loff[F2] = total;
   }
   __syncthreads();
 #pragma unroll
-  for (int j = 0; j < ITEMS; ++j) {
-    if (packed[j] != NONE) {
-      Tuple<K> t;
-      t.key = key[j];
-      t.idx = idx[j];
-      if (sizeof(K) == 8) reinterpret_cast<uint32_t*>(&t)[3] = 0;
-      stage[s_loff[packed[j] >> 16] + (packed[j] & 0xFFFFu)] = t;
-    }
-  }
+  for (int j = 0; j < ITEMS; ++j)
+    if (packed[j] != kNoDigit) stage[s_loff[packed[j] >> 16] + (packed[j] & 0xFFFFu)] = tup[j];
   __syncthreads();
-  const uint32_t null_begin = FROM_SEGS ? s_loff[n_digits - 1] : NONE;
-  for (uint32_t i = threadIdx.x; i < total; i += NT) {
-    const Tuple<K> t = stage[i];
-    uint32_t d;
-    if (FROM_SEGS) {
-      d = i >= null_begin ? n_digits - 1 : ((hash_key(t.key) & pmask) >> a.bits2);
-    } else {
-      d = hash_key(t.key) & ((1u << a.bits2) - 1u);
-    }
-    a.out[s_gdelta[d] + i] = t;
-  }
+  copy_runs_out<K, NT>(stage, a.out, s_loff, s_gbase, F2);
 }
 
 // =====================================================================================================================
@@ -420,6 +499,71 @@ __global__ void __launch_bounds__(NT) k_plan(const uint32_t* __restrict__ off_b,
 }
 
 // =====================================================================================================================
+// Result writer: chunked allocation. A CTA owns one open chunk of the output arrays at a time and sub-allocates its
+// tiles from it; only when the chunk is exhausted does it touch the global chunk counter (one atomic per kChunkRows
+// result rows instead of one per tile). A tile that does not fit fills the open chunk EXACTLY and continues in freshly
+// reserved chunk(s), so every chunk except each CTA's last one is dense; k_compact_* closes those last holes.
+// =====================================================================================================================
+constexpr uint32_t kChunkRows = 128 * 1024;
+constexpr uint32_t kMaxTails = 1024;
+
+struct OutTail {            // the unfilled end [pos, pos + left) of a CTA's last chunk
+  unsigned long long pos;
+  unsigned long long left;
+};
+
+struct OutState {           // device-global result bookkeeping, zeroed before every probe pass
+  unsigned long long n_chunks;     // chunks handed out
+  unsigned long long n_rows;       // result rows emitted (exact even when the buffers overflow)
+  uint32_t n_tails;
+  uint32_t pad;
+};
+
+struct OutWriter {          // per-CTA, lives in shared memory
+  unsigned long long base;  // next free position of the open chunk
+  unsigned long long left;  // free rows in the open chunk
+  unsigned long long rows;  // rows this CTA emitted
+  // mapping of the current tile: tile-relative index i -> i < first ? base0 + i : base1 + (i - first)
+  unsigned long long base0, base1;
+  uint32_t first;
+  uint32_t pad;
+};
+
+__device__ __forceinline__ void out_writer_init(OutWriter* w) {
+  w->base = 0; w->left = 0; w->rows = 0; w->base0 = 0; w->base1 = 0; w->first = 0;
+}
+// one thread: reserves `total` rows for the current tile
+__device__ __forceinline__ void out_writer_reserve(OutWriter* w, OutState* g, unsigned long long total) {
+  w->rows += total;
+  w->base0 = w->base;
+  if (total <= w->left) {
+    w->first = 0xFFFFFFFFu;  // whole tile in the open chunk
+    w->base += total;
+    w->left -= total;
+  } else {
+    const unsigned long long first = w->left, rest = total - first;
+    const unsigned long long k = (rest + kChunkRows - 1) / kChunkRows;
+    const unsigned long long nb = atomicAdd(&g->n_chunks, k) * kChunkRows;
+    w->first = static_cast<uint32_t>(first);  // < kChunkRows
+    w->base1 = nb;
+    w->base = nb + rest;
+    w->left = k * kChunkRows - rest;
+  }
+}
+__device__ __forceinline__ unsigned long long out_pos(unsigned long long base0, unsigned long long base1, uint32_t first,
+                                                      unsigned long long i) {
+  return i < first ? base0 + i : base1 + (i - first);
+}
+// one thread, at CTA exit
+__device__ __forceinline__ void out_writer_finish(const OutWriter* w, OutState* g, OutTail* tails) {
+  if (w->rows) atomicAdd(&g->n_rows, w->rows);
+  if (w->left) {
+    const uint32_t t = atomicAdd(&g->n_tails, 1u);
+    if (t < kMaxTails) tails[t] = OutTail{w->base, w->left};
+  }
+}
+
+// =====================================================================================================================
 // K5: build + probe, persistent CTAs pulling work items from an atomic queue.
 // Per item, in shared memory:
 //   keys[ns]      open-addressing table of the chunk's DISTINCT build keys (linear probing, atomicCAS claim);
@@ -428,10 +572,11 @@ __global__ void __launch_bounds__(NT) k_plan(const uint32_t* __restrict__ off_b,
 //                 contiguous run, so a probe hit expands with plain indexed reads (the reference's
 //                 variant<RowID, PosList> per key, join_hash.cpp:111-112,158-175, without the heap).
 // The key equal to the EMPTY sentinel (INT_MIN) is diverted to a dedicated slot `NS`.
-// Probe: each thread looks up V tuples; per-warp prefix sums of the match counts + one global atomic per CTA tile reserve a
-// contiguous output range, so the two PosLists are written with consecutive lanes on consecutive addresses; a probe row
-// with many matches is expanded by its whole warp.
-// block: NT threads (1 CTA/SM), dynamic smem: (NS+1)*(sizeof(K)+4) + CAP*4.
+// Probe: each thread looks up V tuples of the current tile while the next tile's tuples are already in flight; per-warp
+// prefix sums of the match counts (ballot+popc when no row has > 1 match) place the rows, OutWriter reserves the range,
+// and the two PosLists are written with consecutive lanes on consecutive addresses; a probe row with many matches is
+// expanded by its whole warp.
+// block: NT threads (1 CTA/SM), dynamic smem: (NS+1)*sizeof(K) + (NS+2)*4 + CAP*4.
 // =====================================================================================================================
 template <typename K>
 struct JoinArgs {
@@ -443,66 +588,62 @@ struct JoinArgs {
   RelMeta build_rel, probe_rel;
   uint64_t* out_build;                 // nullptr for Semi/Anti
   uint64_t* out_probe;
-  unsigned long long* out_cursor;      // rows emitted so far (keeps counting past `capacity`)
-  unsigned long long capacity;
+  OutState* out_state;
+  OutTail* out_tails;
+  unsigned long long capacity;         // rows the output arrays can hold (including chunk slack)
   uint32_t* matched;                   // bit per probe tuple position; written for multi items only
   int radix_bits;
   int mode;                            // hj_join_mode
 };
 
 template <typename K> struct KeyTraits;
-template <> struct KeyTraits<int32_t> {
-  static constexpr int32_t kEmpty = INT32_MIN;
-  using Atom = int;
-};
-template <> struct KeyTraits<int64_t> {
-  static constexpr int64_t kEmpty = INT64_MIN;
-  using Atom = unsigned long long;
-};
+template <> struct KeyTraits<int32_t> { static constexpr int32_t kEmpty = INT32_MIN; };
+template <> struct KeyTraits<int64_t> { static constexpr int64_t kEmpty = INT64_MIN; };
 
-template <typename K>
-__device__ __forceinline__ K smem_cas(K* addr, K expected, K desired);
-template <>
-__device__ __forceinline__ int32_t smem_cas<int32_t>(int32_t* addr, int32_t expected, int32_t desired) {
+__device__ __forceinline__ int32_t smem_cas(int32_t* addr, int32_t expected, int32_t desired) {
   return atomicCAS(reinterpret_cast<int*>(addr), expected, desired);
 }
-template <>
-__device__ __forceinline__ int64_t smem_cas<int64_t>(int64_t* addr, int64_t expected, int64_t desired) {
+__device__ __forceinline__ int64_t smem_cas(int64_t* addr, int64_t expected, int64_t desired) {
   return static_cast<int64_t>(atomicCAS(reinterpret_cast<unsigned long long*>(addr),
                                         static_cast<unsigned long long>(expected),
                                         static_cast<unsigned long long>(desired)));
 }
 
-// slot of `key`, claiming an empty one if absent. Bounded: the table always has empty slots (ns > distinct keys).
+// slot of `key`, claiming an empty one if absent. Terminates: the table always keeps empty slots (CAP < NS).
 template <typename K, int NS>
 __device__ __forceinline__ uint32_t table_insert(K* keys, uint32_t ns_mask, K key, uint32_t slot) {
   if (key == KeyTraits<K>::kEmpty) return NS;
-  for (uint32_t it = 0; it <= ns_mask; ++it) {
+  for (;;) {
     K cur = *reinterpret_cast<volatile K*>(keys + slot);
     if (cur == KeyTraits<K>::kEmpty) {
-      cur = smem_cas<K>(keys + slot, KeyTraits<K>::kEmpty, key);
+      cur = smem_cas(keys + slot, KeyTraits<K>::kEmpty, key);
       if (cur == KeyTraits<K>::kEmpty) return slot;
     }
     if (cur == key) return slot;
     slot = (slot + 1) & ns_mask;
   }
-  return NS + 1;  // unreachable
 }
 
-// slot of `key` or NS+1 if absent (read-only)
+// slot of `key` or NS+1 if absent (read-only; slot NS+1 of w is a zero pad)
 template <typename K, int NS>
 __device__ __forceinline__ uint32_t table_find(const K* keys, uint32_t ns_mask, K key, uint32_t slot) {
   if (key == KeyTraits<K>::kEmpty) return NS;
-  for (uint32_t it = 0; it <= ns_mask; ++it) {
+  for (;;) {
     const K cur = keys[slot];
     if (cur == key) return slot;
     if (cur == KeyTraits<K>::kEmpty) return NS + 1;
     slot = (slot + 1) & ns_mask;
   }
-  return NS + 1;
 }
 
-template <typename K, int NT, int NS, int CAP, int V>
+// FAST_ROWID: both relations have power-of-two chunks and identity chunk ids, position -> RowID is shift/mask.
+template <bool FAST_ROWID>
+__device__ __forceinline__ uint64_t rowid_of(const RelMeta& m, uint32_t idx) {
+  if (FAST_ROWID) return pack_rowid(idx >> m.uniform_shift, idx & ((1u << m.uniform_shift) - 1u));
+  return make_rowid(m, idx);
+}
+
+template <typename K, int NT, int NS, int CAP, int V, bool FAST_ROWID>
 __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K> a) {
   static_assert(CAP < NS && CAP <= 65535, "table must keep empty slots; run ends are 16 bit");
   constexpr uint32_t NW = NT / 32;
@@ -510,16 +651,21 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K> a) {
   constexpr uint32_t LIGHT = 4;         // matches per probe row expanded by the owning lane; more: by the warp
   extern __shared__ __align__(16) unsigned char s_raw[];
   K* s_keys = reinterpret_cast<K*>(s_raw);                          // NS + 1
-  uint32_t* s_w = reinterpret_cast<uint32_t*>(s_keys + (NS + 1));   // NS + 1 (+1 pad)
+  uint32_t* s_w = reinterpret_cast<uint32_t*>(s_keys + (NS + 1));   // NS + 2 (slot NS: sentinel key, NS+1: always 0)
   uint32_t* s_grp = s_w + (NS + 2);                                 // CAP
   __shared__ uint32_t s_wtot[NW + 1];
   __shared__ uint32_t s_item;
-  __shared__ unsigned long long s_gbase;
+  __shared__ OutWriter s_out;
 
   const uint32_t lane = lane_id(), warp = warp_id();
+  const uint32_t lt_mask = (1u << lane) - 1u;
   const int mode = a.mode;
   const bool one_side = mode == 5 || mode == 6;
   const uint32_t n_items = a.plan->n_items;
+  if (threadIdx.x == 0) {
+    out_writer_init(&s_out);
+    s_w[NS + 1] = 0;
+  }
 
   for (;;) {
     if (threadIdx.x == 0) s_item = atomicAdd(a.queue_head, 1u);
@@ -533,6 +679,14 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K> a) {
     uint32_t ns = MIN_NS;
     while (ns < 2 * it.b_cnt && ns < NS) ns <<= 1;
     const uint32_t ns_mask = ns - 1;
+
+    // first probe tile in flight while the table is built
+    Tuple<K> nxt[V];
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      const uint32_t i = warp * (32 * V) + j * 32 + lane;
+      if (i < it.p_cnt) nxt[j] = a.probe[it.p_begin + i];
+    }
 
     for (uint32_t s = threadIdx.x; s < ns; s += NT) {
       s_keys[s] = KeyTraits<K>::kEmpty;
@@ -588,7 +742,7 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K> a) {
 
     // ---- probe
     for (uint32_t base = 0; base < it.p_cnt; base += NT * V) {
-      uint32_t pw[V], pidx[V], outc[V], ex[V];
+      uint32_t pw[V], pidx[V];
       bool act[V];
 #pragma unroll
       for (int j = 0; j < V; ++j) {
@@ -597,29 +751,51 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K> a) {
         pw[j] = 0;
         pidx[j] = 0;
         if (act[j]) {
-          const Tuple<K> t = a.probe[it.p_begin + i];
-          pidx[j] = t.idx;
-          const uint32_t slot = table_find<K, NS>(s_keys, ns_mask, t.key, (hash_key(t.key) >> a.radix_bits) & ns_mask);
-          pw[j] = slot <= NS ? s_w[slot] : 0u;
+          const K key = nxt[j].key;
+          pidx[j] = nxt[j].idx;
+          const uint32_t slot = table_find<K, NS>(s_keys, ns_mask, key, (hash_key(key) >> a.radix_bits) & ns_mask);
+          pw[j] = s_w[slot];
         }
       }
-      uint32_t running = 0;
+      // next tile's loads are issued before this tile's results are placed and written
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        const uint32_t i = base + NT * V + warp * (32 * V) + j * 32 + lane;
+        if (i < it.p_cnt) nxt[j] = a.probe[it.p_begin + i];
+      }
+
+      uint32_t outc[V], ex[V];
+      bool any_multi = false;
 #pragma unroll
       for (int j = 0; j < V; ++j) {
         const uint32_t cnt = pw[j] & 0xFFFFu;
         uint32_t o;
-        if (mode == 0) o = cnt;                                              // Inner
-        else if (mode == 1 || mode == 2) o = multi ? cnt : (act[j] ? max(cnt, 1u) : 0u);  // Left/Right
-        else if (mode == 5) o = (!multi && cnt) ? 1u : 0u;                    // Semi
-        else o = (!multi && act[j] && cnt == 0) ? 1u : 0u;                    // Anti
+        if (mode == 0) o = cnt;                                                            // Inner
+        else if (mode == 1 || mode == 2) o = multi ? cnt : (act[j] ? max(cnt, 1u) : 0u);   // Left/Right
+        else if (mode == 5) o = (!multi && cnt) ? 1u : 0u;                                  // Semi
+        else o = (!multi && act[j] && cnt == 0) ? 1u : 0u;                                  // Anti
         if (multi && cnt && mode != 0) {
           const uint32_t pos = it.p_begin + base + warp * (32 * V) + j * 32 + lane;
           atomicOr(a.matched + (pos >> 5), 1u << (pos & 31u));
         }
         outc[j] = o;
-        const uint32_t incl = warp_incl_scan(o);
-        ex[j] = running + incl - o;
-        running += __shfl_sync(0xffffffffu, incl, 31);
+        any_multi |= o > 1;
+      }
+      uint32_t running = 0;
+      if (!__any_sync(0xffffffffu, any_multi)) {
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+          const uint32_t bal = __ballot_sync(0xffffffffu, outc[j] != 0);
+          ex[j] = running + __popc(bal & lt_mask);
+          running += __popc(bal);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+          const uint32_t incl = warp_incl_scan(outc[j]);
+          ex[j] = running + incl - outc[j];
+          running += __shfl_sync(0xffffffffu, incl, 31);
+        }
       }
       if (lane == 0) s_wtot[warp] = running;
       __syncthreads();
@@ -628,53 +804,57 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K> a) {
         const uint32_t incl = warp_incl_scan(v);
         if (lane < NW) s_wtot[lane] = incl - v;
         const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
-        if (lane == 0) {
-          s_wtot[NW] = total;
-          s_gbase = total ? atomicAdd(a.out_cursor, static_cast<unsigned long long>(total)) : 0ull;
-        }
+        if (lane == 0 && total) out_writer_reserve(&s_out, a.out_state, total);
+        if (lane == 0) s_wtot[NW] = total;
       }
       __syncthreads();
-      const unsigned long long gbase = s_gbase + s_wtot[warp];
-      const bool fits = s_gbase + s_wtot[NW] <= a.capacity;  // CTA-uniform; on overflow only the count advances
-      if (fits) {
-        uint32_t heavy = 0;
+      if (s_wtot[NW] == 0) continue;  // CTA-uniform
+      const unsigned long long base0 = s_out.base0, base1 = s_out.base1;
+      const uint32_t first = s_out.first;
+      const uint32_t wbase = s_wtot[warp];
+      uint32_t heavy = 0;
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        if (outc[j] == 0) continue;
+        const uint32_t e = wbase + ex[j];
+        const uint64_t prid = rowid_of<FAST_ROWID>(a.probe_rel, pidx[j]);
+        const uint32_t cnt = pw[j] & 0xFFFFu;
+        if (one_side || cnt == 0) {
+          const unsigned long long pos = out_pos(base0, base1, first, e);
+          if (pos < a.capacity) {
+            if (!one_side) a.out_build[pos] = kNullRowId;  // join_hash.cpp:432-435
+            a.out_probe[pos] = prid;
+          }
+        } else if (cnt <= LIGHT) {
+          const uint32_t start = (pw[j] >> 16) - cnt;
+          for (uint32_t m = 0; m < cnt; ++m) {
+            const unsigned long long pos = out_pos(base0, base1, first, e + m);
+            if (pos < a.capacity) {
+              a.out_build[pos] = rowid_of<FAST_ROWID>(a.build_rel, s_grp[start + m]);
+              a.out_probe[pos] = prid;
+            }
+          }
+        } else {
+          heavy |= 1u << j;
+        }
+      }
+      if (__any_sync(0xffffffffu, heavy != 0)) {
 #pragma unroll
         for (int j = 0; j < V; ++j) {
-          if (outc[j] == 0) continue;
-          const unsigned long long pos = gbase + ex[j];
-          const uint64_t prid = make_rowid(a.probe_rel, pidx[j]);
-          const uint32_t cnt = pw[j] & 0xFFFFu;
-          if (one_side) {
-            a.out_probe[pos] = prid;
-          } else if (cnt == 0) {
-            a.out_build[pos] = kNullRowId;  // join_hash.cpp:432-435
-            a.out_probe[pos] = prid;
-          } else if (cnt <= LIGHT) {
-            const uint32_t start = (pw[j] >> 16) - cnt;
-            for (uint32_t m = 0; m < cnt; ++m) {
-              a.out_build[pos + m] = make_rowid(a.build_rel, s_grp[start + m]);
-              a.out_probe[pos + m] = prid;
-            }
-          } else {
-            heavy |= 1u << j;
-          }
-        }
-        if (!one_side) {
-#pragma unroll
-          for (int j = 0; j < V; ++j) {
-            uint32_t hmask = __ballot_sync(0xffffffffu, (heavy >> j) & 1u);
-            while (hmask) {
-              const int src = __ffs(hmask) - 1;
-              hmask &= hmask - 1;
-              const uint32_t w = __shfl_sync(0xffffffffu, pw[j], src);
-              const uint32_t e = __shfl_sync(0xffffffffu, ex[j], src);
-              const uint32_t pi = __shfl_sync(0xffffffffu, pidx[j], src);
-              const uint32_t cnt = w & 0xFFFFu, start = (w >> 16) - cnt;
-              const unsigned long long pos = gbase + e;
-              const uint64_t prid = make_rowid(a.probe_rel, pi);
-              for (uint32_t m = lane; m < cnt; m += 32) {
-                a.out_build[pos + m] = make_rowid(a.build_rel, s_grp[start + m]);
-                a.out_probe[pos + m] = prid;
+          uint32_t hmask = __ballot_sync(0xffffffffu, (heavy >> j) & 1u);
+          while (hmask) {
+            const int src = __ffs(hmask) - 1;
+            hmask &= hmask - 1;
+            const uint32_t w = __shfl_sync(0xffffffffu, pw[j], src);
+            const uint32_t e = wbase + __shfl_sync(0xffffffffu, ex[j], src);
+            const uint32_t pi = __shfl_sync(0xffffffffu, pidx[j], src);
+            const uint32_t cnt = w & 0xFFFFu, start = (w >> 16) - cnt;
+            const uint64_t prid = rowid_of<FAST_ROWID>(a.probe_rel, pi);
+            for (uint32_t m = lane; m < cnt; m += 32) {
+              const unsigned long long pos = out_pos(base0, base1, first, static_cast<unsigned long long>(e) + m);
+              if (pos < a.capacity) {
+                a.out_build[pos] = rowid_of<FAST_ROWID>(a.build_rel, s_grp[start + m]);
+                a.out_probe[pos] = prid;
               }
             }
           }
@@ -682,24 +862,26 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K> a) {
       }
     }
   }
+  if (threadIdx.x == 0) out_writer_finish(&s_out, a.out_state, a.out_tails);
 }
 
 // =====================================================================================================================
-// Block-wide compaction: every thread with `flag` emits one result row; one global atomic per call reserves the range.
+// Block-wide compaction through the chunked writer: every thread with `flag` emits one result row.
 // =====================================================================================================================
 template <int NT>
 __device__ __forceinline__ void emit_flagged(bool flag, uint64_t build_rid, uint64_t probe_rid, uint64_t* out_build,
-                                             uint64_t* out_probe, unsigned long long* cursor,
-                                             unsigned long long capacity, uint32_t* scratch,
-                                             unsigned long long* s_base) {
+                                             uint64_t* out_probe, unsigned long long capacity, OutWriter* w,
+                                             OutState* g, uint32_t* scratch) {
   uint32_t total;
   const uint32_t ex = block_excl_scan(flag ? 1u : 0u, scratch, &total);
-  if (threadIdx.x == 0) *s_base = total ? atomicAdd(cursor, static_cast<unsigned long long>(total)) : 0ull;
+  if (threadIdx.x == 0 && total) out_writer_reserve(w, g, total);
   __syncthreads();
-  const unsigned long long base = *s_base;
-  if (flag && base + total <= capacity) {
-    if (out_build) out_build[base + ex] = build_rid;
-    out_probe[base + ex] = probe_rid;
+  if (flag) {
+    const unsigned long long pos = out_pos(w->base0, w->base1, w->first, ex);
+    if (pos < capacity) {
+      if (out_build) out_build[pos] = build_rid;
+      out_probe[pos] = probe_rid;
+    }
   }
   __syncthreads();
 }
@@ -708,9 +890,11 @@ __device__ __forceinline__ void emit_flagged(bool flag, uint64_t build_rid, uint
 template <typename K, int NT>
 __global__ void __launch_bounds__(NT) k_finalize_multi(const JoinArgs<K> a, const WorkItem* __restrict__ fin) {
   __shared__ uint32_t scratch[33];
-  __shared__ unsigned long long s_base;
+  __shared__ OutWriter s_out;
   const uint32_t n_fin = a.plan->n_fin;
   const int mode = a.mode;
+  if (threadIdx.x == 0) out_writer_init(&s_out);
+  __syncthreads();
   for (uint32_t f = blockIdx.x; f < n_fin; f += gridDim.x) {
     const WorkItem it = fin[f];
     for (uint32_t base = 0; base < it.p_cnt; base += NT) {
@@ -723,9 +907,10 @@ __global__ void __launch_bounds__(NT) k_finalize_multi(const JoinArgs<K> a, cons
         flag = (mode == 5) ? hit : !hit;  // Semi keeps matched rows; Left/Right/Anti the unmatched ones
         if (flag) prid = make_rowid(a.probe_rel, a.probe[pos].idx);
       }
-      emit_flagged<NT>(flag, kNullRowId, prid, a.out_build, a.out_probe, a.out_cursor, a.capacity, scratch, &s_base);
+      emit_flagged<NT>(flag, kNullRowId, prid, a.out_build, a.out_probe, a.capacity, &s_out, a.out_state, scratch);
     }
   }
+  if (threadIdx.x == 0) out_writer_finish(&s_out, a.out_state, a.out_tails);
 }
 
 // K7: HJ_FLAG_SQL_NULL_PROBE — NULL probe keys of a Left/Right join were routed aside by pass 1; each yields (NULL, p).
@@ -733,18 +918,107 @@ template <typename K, int NT>
 __global__ void __launch_bounds__(NT) k_emit_null_probe(const JoinArgs<K> a, const Tuple<K>* __restrict__ pass1,
                                                         const uint32_t* __restrict__ off_p) {
   __shared__ uint32_t scratch[33];
-  __shared__ unsigned long long s_base;
+  __shared__ OutWriter s_out;
   const uint32_t P = 1u << a.radix_bits;
   const uint32_t lo = off_p[P], hi = off_p[P + 1];
+  if (threadIdx.x == 0) out_writer_init(&s_out);
+  __syncthreads();
   for (uint32_t base = lo + blockIdx.x * NT; base < hi; base += gridDim.x * NT) {
     const uint32_t i = base + threadIdx.x;
     const bool flag = i < hi;
     const uint64_t prid = flag ? make_rowid(a.probe_rel, pass1[i].idx) : 0;
-    emit_flagged<NT>(flag, kNullRowId, prid, a.out_build, a.out_probe, a.out_cursor, a.capacity, scratch, &s_base);
+    emit_flagged<NT>(flag, kNullRowId, prid, a.out_build, a.out_probe, a.capacity, &s_out, a.out_state, scratch);
+  }
+  if (threadIdx.x == 0) out_writer_finish(&s_out, a.out_state, a.out_tails);
+}
+
+// =====================================================================================================================
+// K8: closes the holes at the CTA tails. With T = rows emitted and A = chunks handed out * kChunkRows, the rows stored at
+// positions >= T are moved into the holes below T (both sets have the same size), leaving the dense range [0, T).
+// k_compact_plan (one CTA) sorts the <= kMaxTails holes and builds the two segment lists; k_compact_move copies.
+// =====================================================================================================================
+struct CompactPlan {
+  unsigned long long n_move;                       // rows to move
+  uint32_t n_dst, n_src;
+  unsigned long long dst_start[kMaxTails + 1], dst_prefix[kMaxTails + 2];
+  unsigned long long src_start[kMaxTails + 1], src_prefix[kMaxTails + 2];
+};
+
+__global__ void __launch_bounds__(1024) k_compact_plan(const OutState* __restrict__ g, const OutTail* __restrict__ tails,
+                                                       CompactPlan* __restrict__ plan) {
+  __shared__ unsigned long long s_pos[kMaxTails], s_end[kMaxTails];
+  __shared__ unsigned long long s_sorted_pos[kMaxTails], s_sorted_end[kMaxTails];
+  const uint32_t n = min(g->n_tails, kMaxTails);
+  const unsigned long long T = g->n_rows, A = g->n_chunks * kChunkRows;
+  const uint32_t t = threadIdx.x;
+  if (t < n) {
+    s_pos[t] = tails[t].pos;
+    s_end[t] = tails[t].pos + tails[t].left;
+  }
+  __syncthreads();
+  if (t < n) {  // rank sort (positions are distinct: holes are disjoint and non-empty)
+    uint32_t r = 0;
+    for (uint32_t i = 0; i < n; ++i) r += s_pos[i] < s_pos[t];
+    s_sorted_pos[r] = s_pos[t];
+    s_sorted_end[r] = s_end[t];
+  }
+  __syncthreads();
+  if (t == 0) {
+    // destinations: holes clipped to [0, T); sources: gaps between holes clipped to [T, A)
+    uint32_t nd = 0, ns = 0;
+    unsigned long long dsum = 0, ssum = 0, prev_end = 0;
+    for (uint32_t i = 0; i <= n; ++i) {
+      const unsigned long long hp = i < n ? s_sorted_pos[i] : A, he = i < n ? s_sorted_end[i] : A;
+      // filled gap [prev_end, hp)
+      const unsigned long long gs = prev_end > T ? prev_end : T;
+      if (hp > gs) {
+        plan->src_start[ns] = gs;
+        plan->src_prefix[ns] = ssum;
+        ssum += hp - gs;
+        ++ns;
+      }
+      // hole [hp, he)
+      const unsigned long long de = he < T ? he : T;
+      if (i < n && de > hp) {
+        plan->dst_start[nd] = hp;
+        plan->dst_prefix[nd] = dsum;
+        dsum += de - hp;
+        ++nd;
+      }
+      prev_end = he;
+    }
+    plan->src_prefix[ns] = ssum;
+    plan->dst_prefix[nd] = dsum;
+    plan->n_src = ns;
+    plan->n_dst = nd;
+    plan->n_move = dsum < ssum ? dsum : ssum;  // equal by construction
   }
 }
 
-// K8: inout[i] = pos_lists[chunk_base[inout[i].chunk_id] + inout[i].chunk_offset]; NULL_ROW_ID stays (join_hash.cpp:584-592).
+__device__ __forceinline__ unsigned long long seg_map(const unsigned long long* start, const unsigned long long* prefix,
+                                                      uint32_t n, unsigned long long k) {
+  uint32_t lo = 0, hi = n;  // largest seg with prefix[seg] <= k
+  while (hi - lo > 1) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (prefix[mid] <= k) lo = mid; else hi = mid;
+  }
+  return start[lo] + (k - prefix[lo]);
+}
+
+__global__ void __launch_bounds__(256) k_compact_move(const CompactPlan* __restrict__ plan, uint64_t* __restrict__ out_build,
+                                                      uint64_t* __restrict__ out_probe, unsigned long long capacity) {
+  const unsigned long long n = plan->n_move;
+  for (unsigned long long k = blockIdx.x * 256ull + threadIdx.x; k < n; k += gridDim.x * 256ull) {
+    const unsigned long long dst = seg_map(plan->dst_start, plan->dst_prefix, plan->n_dst, k);
+    const unsigned long long src = seg_map(plan->src_start, plan->src_prefix, plan->n_src, k);
+    if (src < capacity && dst < capacity) {
+      if (out_build) out_build[dst] = out_build[src];
+      out_probe[dst] = out_probe[src];
+    }
+  }
+}
+
+// K9: inout[i] = pos_lists[chunk_base[inout[i].chunk_id] + inout[i].chunk_offset]; NULL_ROW_ID stays (join_hash.cpp:584-592).
 // Out-of-range references are reported through *error instead of faulting.
 __global__ void k_translate(uint64_t* __restrict__ inout, uint64_t n, const uint64_t* __restrict__ pos_lists,
                             const uint64_t* __restrict__ chunk_base, const uint32_t* __restrict__ chunk_size,

@@ -207,12 +207,17 @@ def test_null_probe_literal_vs_sql(joins, mode, encoding):
     assert_same(joins(9, abi.FLAG_SQL_NULL_PROBE), build, probe, mode, flags=abi.FLAG_SQL_NULL_PROBE, what="sql 2-pass")
 
 
-@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("mode", ["Inner", "Left"])
 def test_output_capacity_overflow_reprobes(joins, mode):
-    rng = np.random.default_rng(14)
-    build, probe = wl.random_relations(rng, 20000, 30000, 3000, chunk=4096, encoding="value", nullable=True)
-    info = assert_same(joins(-1, 0, 16), build, probe, mode, what="tiny capacity")
-    assert info.n_probe_passes == 2 or info.n_rows <= 16
+    """Result far larger than the first buffer estimate (probe rows + one 128 Ki-row chunk per writer CTA): the library
+    counts exactly, grows the buffers and probes again; the chunked writer's holes are compacted away."""
+    n = 5200
+    bk = np.full(n, 7, dtype=np.int32)
+    bk[:50] = np.arange(100, 150)
+    pk = np.full(n, 7, dtype=np.int32)
+    pk[:60] = np.arange(120, 180)
+    info = assert_same(joins(), wl.make_relation(bk, 2048), wl.make_relation(pk, 2048), mode, what="huge fan-out")
+    assert info.n_probe_passes == 2 and info.n_rows > 26_000_000
 
 
 @pytest.mark.parametrize("mode", MODES)
