@@ -297,7 +297,7 @@ struct Launches {
 
 template <typename KernelT>
 int set_smem(hj_ctx* ctx, KernelT kernel, size_t bytes) {
-  if (bytes > 48 * 1024) HJ_CUDA(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  if (bytes > 32 * 1024) HJ_CUDA(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
   return HJ_OK;
 }
 
@@ -419,14 +419,25 @@ float ev_ms(cudaEvent_t a, cudaEvent_t b) {
   return ms;
 }
 
-template <typename K, bool FAST>
-int launch_build_probe(hj_ctx* ctx, const JoinArgs<K>& a, cudaStream_t st) {
-  auto k5 = k_build_probe<K, kJoinThreads, Cfg<K>::kNS, Cfg<K>::kCap, kProbeV, FAST>;
+template <typename K, bool FAST, int CLS>
+int launch_build_probe_cls(hj_ctx* ctx, const JoinArgs<K>& a, cudaStream_t st) {
+  auto k5 = k_build_probe<K, kJoinThreads, Cfg<K>::kNS, Cfg<K>::kCap, kProbeV, FAST, CLS>;
   const size_t smem5 = (size_t(Cfg<K>::kNS) + 1) * sizeof(K) + (size_t(Cfg<K>::kNS) + 2) * 4 + size_t(Cfg<K>::kCap) * 4;
   HJ_TRY(set_smem(ctx, k5, smem5));
   k5<<<ctx->n_sms, kJoinThreads, smem5, st>>>(a);
   HJ_LAUNCH_CHECK(ctx, "k_build_probe");
   return HJ_OK;
+}
+
+template <typename K, bool FAST>
+int launch_build_probe(hj_ctx* ctx, const JoinArgs<K>& a, cudaStream_t st) {
+  switch (a.mode) {
+    case HJ_MODE_INNER: return launch_build_probe_cls<K, FAST, kClsInner>(ctx, a, st);
+    case HJ_MODE_LEFT:
+    case HJ_MODE_RIGHT: return launch_build_probe_cls<K, FAST, kClsOuter>(ctx, a, st);
+    case HJ_MODE_SEMI: return launch_build_probe_cls<K, FAST, kClsSemi>(ctx, a, st);
+    default: return launch_build_probe_cls<K, FAST, kClsAnti>(ctx, a, st);
+  }
 }
 
 template <typename K>

@@ -226,33 +226,44 @@ struct ScatterArgs {
 
 constexpr uint32_t kNoDigit = 0xFFFFFFFFu;
 
-// Copies the staged runs out: warp w takes digits w, w+NW, ...; s_gbase[d] is the global element index of run d.
-template <typename K, int NT>
-__device__ __forceinline__ void copy_runs_out(const Tuple<K>* stage, Tuple<K>* out, const uint32_t* s_loff,
-                                              const uint32_t* s_gbase, uint32_t n_runs) {
-  constexpr uint32_t NW = NT / 32;
-  for (uint32_t d = warp_id(); d < n_runs; d += NW) {
-    const uint32_t lo = s_loff[d], n = s_loff[d + 1] - lo;
-    const Tuple<K>* src = stage + lo;
-    Tuple<K>* dst = out + s_gbase[d];
-    for (uint32_t i = lane_id(); i < n; i += 32) dst[i] = src[i];
+// Staging + copy-out shared by both passes. A tuple that got (digit d, rank r inside the digit) is staged at
+// s_loff[d] + r; the copy-out is then one flat, fully unrolled loop: consecutive lanes read consecutive staged slots (one
+// digit's run is contiguous, so the stores coalesce per run), re-derive the digit from the key and add the digit's
+// (global - staged) delta, with no per-run control flow and no per-tuple destination array in shared memory. v1 copied run by run (a warp per digit) and spent ~120 thread-instructions per tuple on loop
+// overhead for the ~32-tuple runs (profiles/r01_ncu_v1_c2_full_summary.md).
+template <typename K, int NT, int ITEMS>
+__device__ __forceinline__ void copy_tile_out(const Tuple<K>* stage, const uint32_t* s_delta, Tuple<K>* out, uint32_t n,
+                                              uint32_t dmask, int shift, uint32_t null_start, uint32_t null_digit) {
+#pragma unroll
+  for (int j = 0; j < ITEMS; ++j) {
+    const uint32_t i = j * NT + threadIdx.x;
+    if (i < n) {
+      const Tuple<K> t = stage[i];
+      const uint32_t d = i >= null_start ? null_digit : (hash_key(t.key) & dmask) >> shift;
+      out[s_delta[d] + i] = t;  // s_delta[d] = global index of the digit's run - its offset in the staged tile (mod 2^32)
+    }
   }
 }
 
 // Pass 1: persistent virtual CTA c = blockIdx.x owns tiles c, c+G, ... exactly as in K1, so the cursors computed from K1's
 // per-CTA counts (base1) are private: no global atomics, deterministic placement. Digit = high (radix_bits - bits2) bits
 // of the partition index; routed NULL rows form run number F1.
+// dynamic smem: TILE * sizeof(Tuple<K>).
 template <typename K, int NT, int ITEMS>
 __global__ void __launch_bounds__(NT, 4) k_scatter1(const ScatterArgs<K> a) {
   constexpr uint32_t TILE = NT * ITEMS;
   extern __shared__ __align__(16) unsigned char s_raw[];
   Tuple<K>* stage = reinterpret_cast<Tuple<K>*>(s_raw);
-  __shared__ uint32_t s_cnt[kMaxDigits + 1], s_loff[kMaxDigits + 2], s_gbase[kMaxDigits + 1], s_cur[kMaxDigits + 1];
+  __shared__ uint32_t s_cnt[kMaxDigits + 1], s_cur[kMaxDigits + 1];
+  __shared__ uint32_t s_loff[kMaxDigits + 1], s_delta[kMaxDigits + 1];
   __shared__ uint32_t scratch[33];
+  __shared__ uint32_t s_total, s_null_start;
 
   const uint32_t pmask = (1u << a.radix_bits) - 1u;
   const uint32_t F1 = 1u << (a.radix_bits - a.bits2);  // <= 256 == regular digits; run F1 = routed NULLs
   const uint32_t G = gridDim.x;
+  const int bits2 = a.bits2;
+  const int null_policy = a.null_policy;
   for (uint32_t d = threadIdx.x; d <= F1; d += NT) s_cur[d] = a.base1[d * G + blockIdx.x];
 
   for (uint32_t tile = blockIdx.x; tile < a.rel.n_tiles; tile += G) {
@@ -260,28 +271,45 @@ __global__ void __launch_bounds__(NT, 4) k_scatter1(const ScatterArgs<K> a) {
     const uint32_t r0 = (tile - seg.tile_begin) * TILE;
     const uint32_t n_in = min(TILE, seg.n_rows - r0);
     for (uint32_t d = threadIdx.x; d <= F1; d += NT) s_cnt[d] = 0;
-    __syncthreads();  // also orders the previous tile's run copy before this tile's staging
+    __syncthreads();  // also orders the previous tile's copy-out before this tile's staging
 
     K key[ITEMS];
+    uint32_t vbits = 0;  // bit j: row j*NT+tid is a valid (non-NULL) row
+    if (seg.kind == 1) {
+      const K* km = a.keys_mat + seg.row_begin + r0;
+      const uint32_t* vm = a.valid_mask + seg.mask_word_begin + (r0 >> 5);
+#pragma unroll
+      for (int j = 0; j < ITEMS; ++j) {
+        const uint32_t i = j * NT + threadIdx.x;
+        key[j] = K(0);
+        if (i < n_in) {
+          key[j] = __ldcs(km + i);
+          vbits |= ((__ldg(vm + (i >> 5)) >> (i & 31u)) & 1u) << j;
+        }
+      }
+    } else {
+      const uint8_t* nl = seg.nulls ? seg.nulls + r0 : nullptr;
+#pragma unroll
+      for (int j = 0; j < ITEMS; ++j) {
+        const uint32_t i = j * NT + threadIdx.x;
+        key[j] = K(0);
+        if (i < n_in) {
+          key[j] = load_plain_key<K>(seg, r0 + i);
+          const bool valid = !(nl && __ldg(nl + i));
+          if (seg.kind == 2 && !valid) key[j] = K(0);
+          vbits |= (valid ? 1u : 0u) << j;
+        }
+      }
+    }
     uint32_t packed[ITEMS];  // digit << 16 | rank inside the digit, or kNoDigit
 #pragma unroll
     for (int j = 0; j < ITEMS; ++j) {
       const uint32_t i = j * NT + threadIdx.x;
       packed[j] = kNoDigit;
-      key[j] = K(0);
       if (i < n_in) {
-        bool valid;
-        if (seg.kind == 1) {
-          key[j] = a.keys_mat[seg.row_begin + r0 + i];
-          valid = (__ldg(a.valid_mask + seg.mask_word_begin + ((r0 + i) >> 5)) >> (i & 31u)) & 1u;
-        } else {
-          key[j] = load_plain_key<K>(seg, r0 + i);
-          valid = !(seg.nulls && __ldg(seg.nulls + r0 + i));
-          if (seg.kind == 2 && !valid) key[j] = K(0);
-        }
         uint32_t d = kNoDigit;
-        if (valid || a.null_policy == kNullAsValue) d = (hash_key(key[j]) & pmask) >> a.bits2;
-        else if (a.null_policy == kNullRoute) d = F1;
+        if (((vbits >> j) & 1u) || null_policy == kNullAsValue) d = (hash_key(key[j]) & pmask) >> bits2;
+        else if (null_policy == kNullRoute) d = F1;
         if (d != kNoDigit) packed[j] = (d << 16) | atomicAdd(&s_cnt[d], 1u);
       }
     }
@@ -294,30 +322,32 @@ __global__ void __launch_bounds__(NT, 4) k_scatter1(const ScatterArgs<K> a) {
       const uint32_t ex = block_excl_scan(c, scratch, &total);
       if (d < F1) {
         s_loff[d] = ex;
-        s_gbase[d] = s_cur[d];
+        s_delta[d] = s_cur[d] - ex;
         s_cur[d] += c;
       }
       if (d == 0) {
         const uint32_t cn = s_cnt[F1];
         s_loff[F1] = total;
-        s_loff[F1 + 1] = total + cn;
-        s_gbase[F1] = s_cur[F1];
+        s_delta[F1] = s_cur[F1] - total;
         s_cur[F1] += cn;
+        s_total = total + cn;
+        s_null_start = total;
       }
     }
     __syncthreads();
+    const uint32_t idx0 = seg.row_begin + r0 + threadIdx.x;
 #pragma unroll
     for (int j = 0; j < ITEMS; ++j) {
       if (packed[j] != kNoDigit) {
         Tuple<K> t;
         t.key = key[j];
-        t.idx = seg.row_begin + r0 + j * NT + threadIdx.x;
+        t.idx = idx0 + j * NT;
         if constexpr (sizeof(K) == 8) t.pad = 0;
         stage[s_loff[packed[j] >> 16] + (packed[j] & 0xFFFFu)] = t;
       }
     }
     __syncthreads();
-    copy_runs_out<K, NT>(stage, a.out, s_loff, s_gbase, F1 + 1);
+    copy_tile_out<K, NT, ITEMS>(stage, s_delta, a.out, s_total, pmask, bits2, s_null_start, F1);
   }
 }
 
@@ -325,12 +355,13 @@ __global__ void __launch_bounds__(NT, 4) k_scatter1(const ScatterArgs<K> a) {
 // is reserved with one global atomic per non-empty digit. blockIdx is mapped to the tile through a multiplicative
 // permutation so that the CTAs resident at any moment work on different level-1 partitions, i.e. on different cursors
 // (same-address atomics serialise at ~21 ns; profiles/r01_microbench_atomics_vs_match.txt).
+// dynamic smem: TILE * sizeof(Tuple<K>).
 template <typename K, int NT, int ITEMS>
 __global__ void __launch_bounds__(NT, 4) k_scatter2(const ScatterArgs<K> a) {
   constexpr uint32_t TILE = NT * ITEMS;
   extern __shared__ __align__(16) unsigned char s_raw[];
   Tuple<K>* stage = reinterpret_cast<Tuple<K>*>(s_raw);
-  __shared__ uint32_t s_cnt[kMaxDigits], s_loff[kMaxDigits + 1], s_gbase[kMaxDigits];
+  __shared__ uint32_t s_cnt[kMaxDigits], s_loff[kMaxDigits], s_delta[kMaxDigits];
   __shared__ uint32_t scratch[33];
   __shared__ uint32_t s_l1[kMaxDigits + 1];
 
@@ -351,18 +382,19 @@ __global__ void __launch_bounds__(NT, 4) k_scatter2(const ScatterArgs<K> a) {
   const uint32_t in_base = a.part_off[d1 << a.bits2] + (t - s_l1[d1]) * TILE;
   const uint32_t n_in = min(TILE, p_hi - in_base);
   uint32_t* cursors = a.cur2 + (d1 << a.bits2);
+  const Tuple<K>* in = a.in + in_base;
 
   Tuple<K> tup[ITEMS];
   uint32_t packed[ITEMS];
 #pragma unroll
   for (int j = 0; j < ITEMS; ++j) {
     const uint32_t i = j * NT + threadIdx.x;
-    packed[j] = kNoDigit;
-    if (i < n_in) tup[j] = a.in[in_base + i];
+    if (i < n_in) tup[j] = ld_stream(in + i);
   }
 #pragma unroll
   for (int j = 0; j < ITEMS; ++j) {
     const uint32_t i = j * NT + threadIdx.x;
+    packed[j] = kNoDigit;
     if (i < n_in) {
       const uint32_t d = hash_key(tup[j].key) & (F2 - 1u);
       packed[j] = (d << 16) | atomicAdd(&s_cnt[d], 1u);
@@ -376,16 +408,16 @@ __global__ void __launch_bounds__(NT, 4) k_scatter2(const ScatterArgs<K> a) {
     const uint32_t ex = block_excl_scan(c, scratch, &total);
     if (d < F2) {
       s_loff[d] = ex;
-      if (c) s_gbase[d] = atomicAdd(cursors + d, c);
+      if (c) s_delta[d] = atomicAdd(cursors + d, c) - ex;
     }
-    if (d == 0) s_loff[F2] = total;
   }
   __syncthreads();
 #pragma unroll
-  for (int j = 0; j < ITEMS; ++j)
+  for (int j = 0; j < ITEMS; ++j) {
     if (packed[j] != kNoDigit) stage[s_loff[packed[j] >> 16] + (packed[j] & 0xFFFFu)] = tup[j];
+  }
   __syncthreads();
-  copy_runs_out<K, NT>(stage, a.out, s_loff, s_gbase, F2);
+  copy_tile_out<K, NT, ITEMS>(stage, s_delta, a.out, n_in, F2 - 1u, 0, 0xFFFFFFFFu, 0u);
 }
 
 // =====================================================================================================================
@@ -643,25 +675,88 @@ __device__ __forceinline__ uint64_t rowid_of(const RelMeta& m, uint32_t idx) {
   return make_rowid(m, idx);
 }
 
-template <typename K, int NT, int NS, int CAP, int V, bool FAST_ROWID>
+// Mode classes the probe loop is specialised for (compile time: no per-row mode branches).
+constexpr int kClsInner = 0, kClsOuter = 1, kClsSemi = 2, kClsAnti = 3;
+
+// Writes the result rows of one probe tile. CONTIG: the tile's reserved range is one in-bounds contiguous piece of the
+// output arrays (the common case), so a row's position is ob/op + a 32-bit index; otherwise every row goes through
+// out_pos() and the capacity check (chunk boundary inside the tile, or the overflow pass that only counts).
+template <typename K, int V, int CLS, bool FAST_ROWID, bool CONTIG>
+__device__ __forceinline__ void emit_tile(const JoinArgs<K>& a, const uint32_t* s_grp, const uint32_t (&pw)[V],
+                                          const uint32_t (&pidx)[V], const uint32_t (&outc)[V], const uint32_t (&ex)[V],
+                                          uint32_t wbase, unsigned long long base0, unsigned long long base1, uint32_t first) {
+  constexpr bool one_side = CLS == kClsSemi || CLS == kClsAnti;
+  constexpr uint32_t LIGHT = 4;  // matches per probe row expanded by the owning lane; more: by the whole warp
+  uint64_t* ob = one_side ? nullptr : a.out_build + (CONTIG ? base0 : 0ull);
+  uint64_t* op = a.out_probe + (CONTIG ? base0 : 0ull);
+  auto put = [&](unsigned long long e, uint64_t brid, uint64_t prid) {
+    if (CONTIG) {
+      if (!one_side) ob[e] = brid;
+      op[e] = prid;
+    } else {
+      const unsigned long long pos = out_pos(base0, base1, first, e);
+      if (pos < a.capacity) {
+        if (!one_side) ob[pos] = brid;
+        op[pos] = prid;
+      }
+    }
+  };
+  const uint32_t lane = lane_id();
+  uint32_t heavy = 0;
+#pragma unroll
+  for (int j = 0; j < V; ++j) {
+    if (outc[j] == 0) continue;
+    const uint32_t e = wbase + ex[j];
+    const uint64_t prid = rowid_of<FAST_ROWID>(a.probe_rel, pidx[j]);
+    const uint32_t cnt = pw[j] & 0xFFFFu;
+    if (one_side || cnt == 0) {
+      put(e, kNullRowId, prid);  // Semi/Anti row, or an unmatched outer row (join_hash.cpp:432-435)
+    } else if (cnt == 1) {
+      put(e, rowid_of<FAST_ROWID>(a.build_rel, s_grp[(pw[j] >> 16) - 1u]), prid);
+    } else if (cnt <= LIGHT) {
+      const uint32_t start = (pw[j] >> 16) - cnt;
+      for (uint32_t m = 0; m < cnt; ++m) put(e + m, rowid_of<FAST_ROWID>(a.build_rel, s_grp[start + m]), prid);
+    } else {
+      heavy |= 1u << j;
+    }
+  }
+  if (one_side) return;
+  if (__any_sync(0xffffffffu, heavy != 0)) {
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      uint32_t hmask = __ballot_sync(0xffffffffu, (heavy >> j) & 1u);
+      while (hmask) {
+        const int src = __ffs(hmask) - 1;
+        hmask &= hmask - 1;
+        const uint32_t w = __shfl_sync(0xffffffffu, pw[j], src);
+        const uint32_t e = wbase + __shfl_sync(0xffffffffu, ex[j], src);
+        const uint32_t pi = __shfl_sync(0xffffffffu, pidx[j], src);
+        const uint32_t cnt = w & 0xFFFFu, start = (w >> 16) - cnt;
+        const uint64_t prid = rowid_of<FAST_ROWID>(a.probe_rel, pi);
+        for (uint32_t m = lane; m < cnt; m += 32)
+          put(static_cast<unsigned long long>(e) + m, rowid_of<FAST_ROWID>(a.build_rel, s_grp[start + m]), prid);
+      }
+    }
+  }
+}
+
+template <typename K, int NT, int NS, int CAP, int V, bool FAST_ROWID, int CLS>
 __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K> a) {
   static_assert(CAP < NS && CAP <= 65535, "table must keep empty slots; run ends are 16 bit");
   constexpr uint32_t NW = NT / 32;
   constexpr uint32_t MIN_NS = 32 * NW;  // every warp scans >= 32 slots
-  constexpr uint32_t LIGHT = 4;         // matches per probe row expanded by the owning lane; more: by the warp
   extern __shared__ __align__(16) unsigned char s_raw[];
   K* s_keys = reinterpret_cast<K*>(s_raw);                          // NS + 1
   uint32_t* s_w = reinterpret_cast<uint32_t*>(s_keys + (NS + 1));   // NS + 2 (slot NS: sentinel key, NS+1: always 0)
   uint32_t* s_grp = s_w + (NS + 2);                                 // CAP
-  __shared__ uint32_t s_wtot[NW + 1];
+  __shared__ uint32_t s_wtot[NW + 2];
   __shared__ uint32_t s_item;
   __shared__ OutWriter s_out;
 
   const uint32_t lane = lane_id(), warp = warp_id();
   const uint32_t lt_mask = (1u << lane) - 1u;
-  const int mode = a.mode;
-  const bool one_side = mode == 5 || mode == 6;
   const uint32_t n_items = a.plan->n_items;
+  const int radix_bits = a.radix_bits;
   if (threadIdx.x == 0) {
     out_writer_init(&s_out);
     s_w[NS + 1] = 0;
@@ -679,13 +774,15 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K> a) {
     uint32_t ns = MIN_NS;
     while (ns < 2 * it.b_cnt && ns < NS) ns <<= 1;
     const uint32_t ns_mask = ns - 1;
+    const Tuple<K>* probe = a.probe + it.p_begin;
+    const Tuple<K>* build = a.build + it.b_begin;
 
     // first probe tile in flight while the table is built
     Tuple<K> nxt[V];
 #pragma unroll
     for (int j = 0; j < V; ++j) {
       const uint32_t i = warp * (32 * V) + j * 32 + lane;
-      if (i < it.p_cnt) nxt[j] = a.probe[it.p_begin + i];
+      if (i < it.p_cnt) nxt[j] = ld_stream(probe + i);
     }
 
     for (uint32_t s = threadIdx.x; s < ns; s += NT) {
@@ -697,8 +794,8 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K> a) {
 
     // ---- build pass A: distinct keys + counts
     for (uint32_t i = threadIdx.x; i < it.b_cnt; i += NT) {
-      const K key = a.build[it.b_begin + i].key;
-      const uint32_t slot = table_insert<K, NS>(s_keys, ns_mask, key, (hash_key(key) >> a.radix_bits) & ns_mask);
+      const K key = build[i].key;
+      const uint32_t slot = table_insert<K, NS>(s_keys, ns_mask, key, (hash_key(key) >> radix_bits) & ns_mask);
       atomicAdd(&s_w[slot], 1u);
     }
     __syncthreads();
@@ -733,8 +830,8 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K> a) {
 
     // ---- build pass B: group the row positions by key
     for (uint32_t i = threadIdx.x; i < it.b_cnt; i += NT) {
-      const Tuple<K> t = a.build[it.b_begin + i];
-      const uint32_t slot = table_find<K, NS>(s_keys, ns_mask, t.key, (hash_key(t.key) >> a.radix_bits) & ns_mask);
+      const Tuple<K> t = build[i];
+      const uint32_t slot = table_find<K, NS>(s_keys, ns_mask, t.key, (hash_key(t.key) >> radix_bits) & ns_mask);
       const uint32_t old = atomicAdd(&s_w[slot], 0x10000u);
       s_grp[old >> 16] = t.idx;
     }
@@ -742,47 +839,40 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K> a) {
 
     // ---- probe
     for (uint32_t base = 0; base < it.p_cnt; base += NT * V) {
-      uint32_t pw[V], pidx[V];
-      bool act[V];
-#pragma unroll
-      for (int j = 0; j < V; ++j) {
-        const uint32_t i = base + warp * (32 * V) + j * 32 + lane;
-        act[j] = i < it.p_cnt;
-        pw[j] = 0;
-        pidx[j] = 0;
-        if (act[j]) {
-          const K key = nxt[j].key;
-          pidx[j] = nxt[j].idx;
-          const uint32_t slot = table_find<K, NS>(s_keys, ns_mask, key, (hash_key(key) >> a.radix_bits) & ns_mask);
-          pw[j] = s_w[slot];
-        }
-      }
-      // next tile's loads are issued before this tile's results are placed and written
-#pragma unroll
-      for (int j = 0; j < V; ++j) {
-        const uint32_t i = base + NT * V + warp * (32 * V) + j * 32 + lane;
-        if (i < it.p_cnt) nxt[j] = a.probe[it.p_begin + i];
-      }
-
-      uint32_t outc[V], ex[V];
+      uint32_t pw[V], pidx[V], outc[V], ex[V];
+      const uint32_t row0 = base + warp * (32 * V) + lane;
       bool any_multi = false;
 #pragma unroll
       for (int j = 0; j < V; ++j) {
+        const bool act = row0 + j * 32 < it.p_cnt;
+        pw[j] = 0;
+        pidx[j] = nxt[j].idx;
+        if (act) {
+          const K key = nxt[j].key;
+          const uint32_t slot = table_find<K, NS>(s_keys, ns_mask, key, (hash_key(key) >> radix_bits) & ns_mask);
+          pw[j] = s_w[slot];
+        }
         const uint32_t cnt = pw[j] & 0xFFFFu;
         uint32_t o;
-        if (mode == 0) o = cnt;                                                            // Inner
-        else if (mode == 1 || mode == 2) o = multi ? cnt : (act[j] ? max(cnt, 1u) : 0u);   // Left/Right
-        else if (mode == 5) o = (!multi && cnt) ? 1u : 0u;                                  // Semi
-        else o = (!multi && act[j] && cnt == 0) ? 1u : 0u;                                  // Anti
-        if (multi && cnt && mode != 0) {
-          const uint32_t pos = it.p_begin + base + warp * (32 * V) + j * 32 + lane;
+        if (CLS == kClsInner) o = cnt;
+        else if (CLS == kClsOuter) o = multi ? cnt : (act ? max(cnt, 1u) : 0u);
+        else if (CLS == kClsSemi) o = (!multi && cnt) ? 1u : 0u;
+        else o = (!multi && act && cnt == 0) ? 1u : 0u;
+        if (CLS != kClsInner && multi && cnt) {
+          const uint32_t pos = it.p_begin + row0 + j * 32;
           atomicOr(a.matched + (pos >> 5), 1u << (pos & 31u));
         }
         outc[j] = o;
         any_multi |= o > 1;
       }
+      // next tile's loads are issued before this tile's results are placed and written
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        const uint32_t i = row0 + NT * V + j * 32;
+        if (i < it.p_cnt) nxt[j] = ld_stream(probe + i);
+      }
       uint32_t running = 0;
-      if (!__any_sync(0xffffffffu, any_multi)) {
+      if ((CLS == kClsSemi || CLS == kClsAnti) || !__any_sync(0xffffffffu, any_multi)) {
 #pragma unroll
         for (int j = 0; j < V; ++j) {
           const uint32_t bal = __ballot_sync(0xffffffffu, outc[j] != 0);
@@ -804,62 +894,23 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K> a) {
         const uint32_t incl = warp_incl_scan(v);
         if (lane < NW) s_wtot[lane] = incl - v;
         const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
-        if (lane == 0 && total) out_writer_reserve(&s_out, a.out_state, total);
-        if (lane == 0) s_wtot[NW] = total;
+        if (lane == 0) {
+          uint32_t contig = 0;
+          if (total) {
+            out_writer_reserve(&s_out, a.out_state, total);
+            contig = (s_out.first == 0xFFFFFFFFu && s_out.base0 + total <= a.capacity) ? 1u : 0u;
+          }
+          s_wtot[NW] = total;
+          s_wtot[NW + 1] = contig;
+        }
       }
       __syncthreads();
       if (s_wtot[NW] == 0) continue;  // CTA-uniform
       const unsigned long long base0 = s_out.base0, base1 = s_out.base1;
       const uint32_t first = s_out.first;
       const uint32_t wbase = s_wtot[warp];
-      uint32_t heavy = 0;
-#pragma unroll
-      for (int j = 0; j < V; ++j) {
-        if (outc[j] == 0) continue;
-        const uint32_t e = wbase + ex[j];
-        const uint64_t prid = rowid_of<FAST_ROWID>(a.probe_rel, pidx[j]);
-        const uint32_t cnt = pw[j] & 0xFFFFu;
-        if (one_side || cnt == 0) {
-          const unsigned long long pos = out_pos(base0, base1, first, e);
-          if (pos < a.capacity) {
-            if (!one_side) a.out_build[pos] = kNullRowId;  // join_hash.cpp:432-435
-            a.out_probe[pos] = prid;
-          }
-        } else if (cnt <= LIGHT) {
-          const uint32_t start = (pw[j] >> 16) - cnt;
-          for (uint32_t m = 0; m < cnt; ++m) {
-            const unsigned long long pos = out_pos(base0, base1, first, e + m);
-            if (pos < a.capacity) {
-              a.out_build[pos] = rowid_of<FAST_ROWID>(a.build_rel, s_grp[start + m]);
-              a.out_probe[pos] = prid;
-            }
-          }
-        } else {
-          heavy |= 1u << j;
-        }
-      }
-      if (__any_sync(0xffffffffu, heavy != 0)) {
-#pragma unroll
-        for (int j = 0; j < V; ++j) {
-          uint32_t hmask = __ballot_sync(0xffffffffu, (heavy >> j) & 1u);
-          while (hmask) {
-            const int src = __ffs(hmask) - 1;
-            hmask &= hmask - 1;
-            const uint32_t w = __shfl_sync(0xffffffffu, pw[j], src);
-            const uint32_t e = wbase + __shfl_sync(0xffffffffu, ex[j], src);
-            const uint32_t pi = __shfl_sync(0xffffffffu, pidx[j], src);
-            const uint32_t cnt = w & 0xFFFFu, start = (w >> 16) - cnt;
-            const uint64_t prid = rowid_of<FAST_ROWID>(a.probe_rel, pi);
-            for (uint32_t m = lane; m < cnt; m += 32) {
-              const unsigned long long pos = out_pos(base0, base1, first, static_cast<unsigned long long>(e) + m);
-              if (pos < a.capacity) {
-                a.out_build[pos] = rowid_of<FAST_ROWID>(a.build_rel, s_grp[start + m]);
-                a.out_probe[pos] = prid;
-              }
-            }
-          }
-        }
-      }
+      if (s_wtot[NW + 1]) emit_tile<K, V, CLS, FAST_ROWID, true>(a, s_grp, pw, pidx, outc, ex, wbase, base0, base1, first);
+      else emit_tile<K, V, CLS, FAST_ROWID, false>(a, s_grp, pw, pidx, outc, ex, wbase, base0, base1, first);
     }
   }
   if (threadIdx.x == 0) out_writer_finish(&s_out, a.out_state, a.out_tails);
