@@ -34,6 +34,7 @@ constexpr int kJoinThreads = 1024;
 constexpr int kProbeV = 4;
 constexpr uint32_t kProbeSlice = 128 * 1024;
 constexpr int kSinglePassMaxBits = 8;
+constexpr int kMinChunkShift = 8, kMaxChunkShift = 14;  // result chunks of 256 .. 16 Ki rows
 constexpr int kVirtualCtasPerSm = 4;       // K1 / pass 1 tile ownership: G = min(n_tiles, 4 * SMs) virtual CTAs
 template <typename K> constexpr int tile1() { return kScatterThreads * Cfg<K>::kItems1; }
 template <typename K> constexpr int tile2() { return kScatterThreads * Cfg<K>::kItems2; }
@@ -57,7 +58,7 @@ struct hj_ctx {
   // per relation (0 = build, 1 = probe)
   DevBuf stage_in[2], segs[2], tile_seg[2], seg_row_begin[2], keys_mat[2], valid_mask[2];
   DevBuf hist[2], hist1[2], part_off[2], cur2[2], l1_tiles[2], tup_a[2], tup_b[2];
-  DevBuf items, fin, plan, queue, out_state, out_tails, compact_plan, matched, out_build, out_probe, misc;
+  DevBuf items, fin, plan, queue, out_state, out_tails, compact_plan, compact_used, compact_hole, compact_src, matched, out_build, out_probe, misc;
   void* pinned = nullptr;  // small pinned readback area
   cudaEvent_t ev[16] = {};
   // result of the last join
@@ -73,7 +74,7 @@ struct hj_ctx {
     for (DevBuf* b : {&stage_in[0], &stage_in[1], &segs[0], &segs[1], &tile_seg[0], &tile_seg[1], &seg_row_begin[0],
                       &seg_row_begin[1], &keys_mat[0], &keys_mat[1], &valid_mask[0], &valid_mask[1], &hist[0], &hist[1],
                       &part_off[0], &part_off[1], &hist1[0], &hist1[1], &cur2[0], &cur2[1], &l1_tiles[0], &l1_tiles[1],
-                      &tup_a[0], &tup_a[1], &tup_b[0], &tup_b[1], &items, &fin, &plan, &queue, &out_state, &out_tails, &compact_plan, &matched,
+                      &tup_a[0], &tup_a[1], &tup_b[0], &tup_b[1], &items, &fin, &plan, &queue, &out_state, &out_tails, &compact_plan, &compact_used, &compact_hole, &compact_src, &matched,
                       &out_build, &out_probe, &misc})
       all_bufs.push_back(b);
   }
@@ -486,7 +487,7 @@ int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, in
   HJ_TRY(ensure(ctx, ctx->queue, 256));
   HJ_TRY(ensure(ctx, ctx->out_state, sizeof(OutState)));
   HJ_TRY(ensure(ctx, ctx->out_tails, sizeof(OutTail) * kMaxTails));
-  HJ_TRY(ensure(ctx, ctx->compact_plan, sizeof(CompactPlan)));
+  HJ_TRY(ensure(ctx, ctx->compact_plan, sizeof(CompactHdr)));
   const size_t matched_bytes = (size_t(probe->n_rows) / 32 + 2) * 4;
   if (mode != HJ_MODE_INNER) HJ_TRY(ensure(ctx, ctx->matched, matched_bytes));
   auto* off_b = static_cast<uint32_t*>(ctx->part_off[0].p);
@@ -498,11 +499,19 @@ int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, in
   HJ_LAUNCH_CHECK(ctx, "k_plan");
   nl.n++;
 
-  // ---- output buffers: `rows` result rows + one chunk of slack per CTA that writes results
-  const uint32_t writer_ctas = ctx->n_sms * (1 + (mode != HJ_MODE_INNER ? 1 : 0) + (probe_null_policy == kNullRoute ? 1 : 0));
-  auto alloc_rows = [&](uint64_t rows) { return ((rows + kChunkRows - 1) / kChunkRows + writer_ctas + 1) * uint64_t(kChunkRows); };
+  // ---- output buffers: `rows` result rows + one chunk of slack per result writer (K5: every warp; K6/K7: every CTA).
+  // Chunk size: a writer should go through >= ~4 chunks so that the slack stays a fraction of the result.
+  const uint64_t n_writers = uint64_t(ctx->n_sms) * (kJoinThreads / 32) + (mode != HJ_MODE_INNER ? ctx->n_sms : 0) +
+                             (probe_null_policy == kNullRoute ? ctx->n_sms : 0);
+  auto chunk_shift_for = [&](uint64_t rows) {
+    int sh = kMinChunkShift;
+    while (sh < kMaxChunkShift && (uint64_t(1) << sh) * n_writers * 4 < rows) ++sh;
+    return sh;
+  };
+  auto alloc_rows = [&](uint64_t rows, int sh) { return (((rows + (uint64_t(1) << sh) - 1) >> sh) + n_writers + 1) << sh; };
   uint64_t want_rows = ctx->opts.output_capacity ? ctx->opts.output_capacity : probe->n_rows;
-  uint64_t capacity = alloc_rows(want_rows);
+  int chunk_shift = chunk_shift_for(want_rows);
+  uint64_t capacity = alloc_rows(want_rows, chunk_shift);
 
   JoinArgs<K> a{};
   a.build = tb;
@@ -528,6 +537,11 @@ int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, in
     a.out_build = one_side ? nullptr : static_cast<uint64_t*>(ctx->out_build.p);
     a.out_probe = static_cast<uint64_t*>(ctx->out_probe.p);
     a.capacity = capacity;
+    a.chunk_shift = chunk_shift;
+    const size_t max_chunks = size_t(capacity >> chunk_shift) + 1;
+    HJ_TRY(ensure(ctx, ctx->compact_used, max_chunks * 4));
+    HJ_TRY(ensure(ctx, ctx->compact_hole, (max_chunks + 1) * 4));
+    HJ_TRY(ensure(ctx, ctx->compact_src, (max_chunks + 1) * 4));
     HJ_CUDA(ctx, cudaMemsetAsync(ctx->queue.p, 0, 4, st));
     HJ_CUDA(ctx, cudaMemsetAsync(ctx->out_state.p, 0, sizeof(OutState), st));
     if (mode != HJ_MODE_INNER) HJ_CUDA(ctx, cudaMemsetAsync(ctx->matched.p, 0, matched_bytes, st));
@@ -544,9 +558,14 @@ int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, in
       HJ_LAUNCH_CHECK(ctx, "k_emit_null_probe");
       nl.n++;
     }
-    k_compact_plan<<<1, 1024, 0, st>>>(a.out_state, a.out_tails, static_cast<CompactPlan*>(ctx->compact_plan.p));
+    k_compact_plan<<<1, 1024, 0, st>>>(a.out_state, a.out_tails, chunk_shift, capacity, static_cast<uint32_t*>(ctx->compact_used.p),
+                                       static_cast<uint32_t*>(ctx->compact_hole.p), static_cast<uint32_t*>(ctx->compact_src.p),
+                                       static_cast<CompactHdr*>(ctx->compact_plan.p));
     HJ_LAUNCH_CHECK(ctx, "k_compact_plan");
-    k_compact_move<<<ctx->n_sms * 8, 256, 0, st>>>(static_cast<const CompactPlan*>(ctx->compact_plan.p), a.out_build, a.out_probe, capacity);
+    k_compact_move<<<ctx->n_sms * 8, 256, 0, st>>>(static_cast<const CompactHdr*>(ctx->compact_plan.p), a.out_state, chunk_shift,
+                                                   static_cast<const uint32_t*>(ctx->compact_used.p),
+                                                   static_cast<const uint32_t*>(ctx->compact_hole.p),
+                                                   static_cast<const uint32_t*>(ctx->compact_src.p), a.out_build, a.out_probe);
     HJ_LAUNCH_CHECK(ctx, "k_compact_move");
     nl.n += 2;
     HJ_CUDA(ctx, cudaMemcpyAsync(&rb->out, ctx->out_state.p, sizeof(OutState), cudaMemcpyDeviceToHost, st));
@@ -555,10 +574,11 @@ int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, in
     HJ_CUDA(ctx, cudaMemcpyAsync(&rb->n_probe_tuples, off_p + P + 1, 4, cudaMemcpyDeviceToHost, st));
     HJ_CUDA(ctx, cudaEventRecord(ev[6], st));
     HJ_CUDA(ctx, cudaStreamSynchronize(st));
-    if (rb->out.n_chunks * kChunkRows <= capacity) break;  // every reserved chunk lay inside the buffers
+    if ((rb->out.n_chunks << chunk_shift) <= capacity) break;  // every reserved chunk lay inside the buffers
     if (passes >= 2) return fail(ctx, HJ_ERR_CUDA, "result size changed between probe passes (%llu chunks > capacity %llu rows)",
                                  rb->out.n_chunks, (unsigned long long)capacity);
-    capacity = alloc_rows(rb->out.n_rows);  // the exact row count is known now: re-probe into buffers that fit
+    chunk_shift = chunk_shift_for(rb->out.n_rows);  // the exact row count is known now: re-probe into buffers that fit
+    capacity = alloc_rows(rb->out.n_rows, chunk_shift);
   }
 
   ctx->has_result = true;

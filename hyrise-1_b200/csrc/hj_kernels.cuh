@@ -531,15 +531,17 @@ __global__ void __launch_bounds__(NT) k_plan(const uint32_t* __restrict__ off_b,
 }
 
 // =====================================================================================================================
-// Result writer: chunked allocation. A CTA owns one open chunk of the output arrays at a time and sub-allocates its
-// tiles from it; only when the chunk is exhausted does it touch the global chunk counter (one atomic per kChunkRows
-// result rows instead of one per tile). A tile that does not fit fills the open chunk EXACTLY and continues in freshly
-// reserved chunk(s), so every chunk except each CTA's last one is dense; k_compact_* closes those last holes.
+// Result writer: chunked allocation. A writer (one WARP of K5's probe loop, one CTA of K6/K7) owns one open chunk of the
+// output arrays at a time and sub-allocates its batches from it with plain register/shared arithmetic; only when the
+// chunk is exhausted does it touch the global chunk counter (one atomic per `chunk_rows` result rows per writer instead
+// of one per batch; same-address atomics serialise at ~21 ns). A batch that does not fit fills the open chunk EXACTLY and
+// continues in freshly reserved chunk(s), so every chunk except each writer's last one is dense; k_compact_* closes
+// those last holes. The chunk size is chosen per join (2^chunk_shift rows, 256..16 Ki) from the expected result size so
+// that the slack of the ~4.9 K writers stays small for small joins.
 // =====================================================================================================================
-constexpr uint32_t kChunkRows = 128 * 1024;
-constexpr uint32_t kMaxTails = 1024;
+constexpr uint32_t kMaxTails = 8192;  // >= writers: 148 SMs x 32 warps (K5) + 148 (K6) + 148 (K7)
 
-struct OutTail {            // the unfilled end [pos, pos + left) of a CTA's last chunk
+struct OutTail {            // the unfilled end [pos, pos + left) of a writer's last chunk
   unsigned long long pos;
   unsigned long long left;
 };
@@ -551,11 +553,11 @@ struct OutState {           // device-global result bookkeeping, zeroed before e
   uint32_t pad;
 };
 
-struct OutWriter {          // per-CTA, lives in shared memory
+struct OutWriter {          // one writer's state (registers for a warp, shared memory for a CTA)
   unsigned long long base;  // next free position of the open chunk
   unsigned long long left;  // free rows in the open chunk
-  unsigned long long rows;  // rows this CTA emitted
-  // mapping of the current tile: tile-relative index i -> i < first ? base0 + i : base1 + (i - first)
+  unsigned long long rows;  // rows this writer emitted
+  // mapping of the current batch: batch-relative index i -> i < first ? base0 + i : base1 + (i - first)
   unsigned long long base0, base1;
   uint32_t first;
   uint32_t pad;
@@ -564,29 +566,49 @@ struct OutWriter {          // per-CTA, lives in shared memory
 __device__ __forceinline__ void out_writer_init(OutWriter* w) {
   w->base = 0; w->left = 0; w->rows = 0; w->base0 = 0; w->base1 = 0; w->first = 0;
 }
-// one thread: reserves `total` rows for the current tile
-__device__ __forceinline__ void out_writer_reserve(OutWriter* w, OutState* g, unsigned long long total) {
+// one thread: reserves `total` rows for the current batch
+__device__ __forceinline__ void out_writer_reserve(OutWriter* w, OutState* g, unsigned long long total, int chunk_shift) {
   w->rows += total;
   w->base0 = w->base;
   if (total <= w->left) {
-    w->first = 0xFFFFFFFFu;  // whole tile in the open chunk
+    w->first = 0xFFFFFFFFu;  // whole batch in the open chunk
     w->base += total;
     w->left -= total;
   } else {
     const unsigned long long first = w->left, rest = total - first;
-    const unsigned long long k = (rest + kChunkRows - 1) / kChunkRows;
-    const unsigned long long nb = atomicAdd(&g->n_chunks, k) * kChunkRows;
-    w->first = static_cast<uint32_t>(first);  // < kChunkRows
+    const unsigned long long k = (rest + (1ull << chunk_shift) - 1) >> chunk_shift;
+    const unsigned long long nb = atomicAdd(&g->n_chunks, k) << chunk_shift;
+    w->first = static_cast<uint32_t>(first);  // < chunk rows
     w->base1 = nb;
     w->base = nb + rest;
-    w->left = k * kChunkRows - rest;
+    w->left = (k << chunk_shift) - rest;
+  }
+}
+// whole warp, writer state replicated in every lane: lane 0 takes fresh chunks, all lanes learn their position
+__device__ __forceinline__ void warp_writer_reserve(OutWriter* w, OutState* g, unsigned long long total, int chunk_shift) {
+  w->rows += total;
+  w->base0 = w->base;
+  if (total <= w->left) {  // warp-uniform
+    w->first = 0xFFFFFFFFu;
+    w->base += total;
+    w->left -= total;
+  } else {
+    const unsigned long long first = w->left, rest = total - first;
+    const unsigned long long k = (rest + (1ull << chunk_shift) - 1) >> chunk_shift;
+    unsigned long long nb = 0;
+    if (lane_id() == 0) nb = atomicAdd(&g->n_chunks, k) << chunk_shift;
+    nb = __shfl_sync(0xffffffffu, nb, 0);
+    w->first = static_cast<uint32_t>(first);
+    w->base1 = nb;
+    w->base = nb + rest;
+    w->left = (k << chunk_shift) - rest;
   }
 }
 __device__ __forceinline__ unsigned long long out_pos(unsigned long long base0, unsigned long long base1, uint32_t first,
                                                       unsigned long long i) {
   return i < first ? base0 + i : base1 + (i - first);
 }
-// one thread, at CTA exit
+// one thread, when the writer is done
 __device__ __forceinline__ void out_writer_finish(const OutWriter* w, OutState* g, OutTail* tails) {
   if (w->rows) atomicAdd(&g->n_rows, w->rows);
   if (w->left) {
@@ -626,6 +648,7 @@ struct JoinArgs {
   uint32_t* matched;                   // bit per probe tuple position; written for multi items only
   int radix_bits;
   int mode;                            // hj_join_mode
+  int chunk_shift;                     // result chunks are 2^chunk_shift rows
 };
 
 template <typename K> struct KeyTraits;
@@ -745,22 +768,24 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K> a) {
   static_assert(CAP < NS && CAP <= 65535, "table must keep empty slots; run ends are 16 bit");
   constexpr uint32_t NW = NT / 32;
   constexpr uint32_t MIN_NS = 32 * NW;  // every warp scans >= 32 slots
+  constexpr int BU = 2 * (sizeof(K) == 4 ? 2 : 1) + 0;  // build tuples per thread in flight at a time
+  constexpr int BR = ((CAP + NT - 1) / NT + BU - 1) / BU * BU;  // build tuples per thread, padded to whole rounds
+  static_assert(BU % 2 == 0 && NS + 1 < 65536, "slots are kept as 16-bit halves");
   extern __shared__ __align__(16) unsigned char s_raw[];
   K* s_keys = reinterpret_cast<K*>(s_raw);                          // NS + 1
   uint32_t* s_w = reinterpret_cast<uint32_t*>(s_keys + (NS + 1));   // NS + 2 (slot NS: sentinel key, NS+1: always 0)
   uint32_t* s_grp = s_w + (NS + 2);                                 // CAP
-  __shared__ uint32_t s_wtot[NW + 2];
+  __shared__ uint32_t s_wtot[NW + 1];
   __shared__ uint32_t s_item;
-  __shared__ OutWriter s_out;
 
   const uint32_t lane = lane_id(), warp = warp_id();
   const uint32_t lt_mask = (1u << lane) - 1u;
   const uint32_t n_items = a.plan->n_items;
   const int radix_bits = a.radix_bits;
-  if (threadIdx.x == 0) {
-    out_writer_init(&s_out);
-    s_w[NS + 1] = 0;
-  }
+  const int chunk_shift = a.chunk_shift;
+  OutWriter wr;  // every warp is its own result writer (state replicated in the lanes' registers, lane 0 allocates)
+  out_writer_init(&wr);
+  if (threadIdx.x == 0) s_w[NS + 1] = 0;
 
   for (;;) {
     if (threadIdx.x == 0) s_item = atomicAdd(a.queue_head, 1u);
@@ -777,7 +802,7 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K> a) {
     const Tuple<K>* probe = a.probe + it.p_begin;
     const Tuple<K>* build = a.build + it.b_begin;
 
-    // first probe tile in flight while the table is built
+    // the warp's first probe rows go in flight before the table is built
     Tuple<K> nxt[V];
 #pragma unroll
     for (int j = 0; j < V; ++j) {
@@ -792,11 +817,28 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K> a) {
     if (threadIdx.x == 0) s_w[NS] = 0;
     __syncthreads();
 
-    // ---- build pass A: distinct keys + counts
-    for (uint32_t i = threadIdx.x; i < it.b_cnt; i += NT) {
-      const K key = build[i].key;
-      const uint32_t slot = table_insert<K, NS>(s_keys, ns_mask, key, (hash_key(key) >> radix_bits) & ns_mask);
-      atomicAdd(&s_w[slot], 1u);
+    // ---- build pass A: distinct keys + counts, BU tuples per thread in flight at a time (v1 loaded one tuple per loop
+    // iteration and paid the DRAM latency CAP/NT times); the slot of every tuple is kept (16 bit) for pass B
+    uint32_t bslot[BR / 2];
+#pragma unroll
+    for (int r0 = 0; r0 < BR; r0 += BU) {
+      if (r0 * NT >= it.b_cnt) break;  // CTA-uniform
+      K bk[BU];
+#pragma unroll
+      for (int u = 0; u < BU; ++u) {
+        const uint32_t i = (r0 + u) * NT + threadIdx.x;
+        bk[u] = i < it.b_cnt ? build[i].key : K(0);
+      }
+#pragma unroll
+      for (int u = 0; u < BU; ++u) {
+        const uint32_t i = (r0 + u) * NT + threadIdx.x;
+        uint32_t slot = NS + 1;
+        if (i < it.b_cnt) {
+          slot = table_insert<K, NS>(s_keys, ns_mask, bk[u], (hash_key(bk[u]) >> radix_bits) & ns_mask);
+          atomicAdd(&s_w[slot], 1u);
+        }
+        if ((u & 1) == 0) bslot[(r0 + u) / 2] = slot; else bslot[(r0 + u) / 2] |= slot << 16;
+      }
     }
     __syncthreads();
 
@@ -828,19 +870,32 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K> a) {
     }
     __syncthreads();
 
-    // ---- build pass B: group the row positions by key
-    for (uint32_t i = threadIdx.x; i < it.b_cnt; i += NT) {
-      const Tuple<K> t = build[i];
-      const uint32_t slot = table_find<K, NS>(s_keys, ns_mask, t.key, (hash_key(t.key) >> radix_bits) & ns_mask);
-      const uint32_t old = atomicAdd(&s_w[slot], 0x10000u);
-      s_grp[old >> 16] = t.idx;
+    // ---- build pass B: group the row positions by key (the tuples come from L2 this time)
+#pragma unroll
+    for (int r0 = 0; r0 < BR; r0 += BU) {
+      if (r0 * NT >= it.b_cnt) break;  // CTA-uniform
+      uint32_t bi[BU];
+#pragma unroll
+      for (int u = 0; u < BU; ++u) {
+        const uint32_t i = (r0 + u) * NT + threadIdx.x;
+        bi[u] = i < it.b_cnt ? build[i].idx : 0u;
+      }
+#pragma unroll
+      for (int u = 0; u < BU; ++u) {
+        const uint32_t i = (r0 + u) * NT + threadIdx.x;
+        if (i < it.b_cnt) {
+          const uint32_t slot = (bslot[(r0 + u) / 2] >> ((u & 1) * 16)) & 0xFFFFu;
+          const uint32_t old = atomicAdd(&s_w[slot], 0x10000u);
+          s_grp[old >> 16] = bi[u];
+        }
+      }
     }
     __syncthreads();  // s_w[slot] is now (end of run << 16) | count
 
-    // ---- probe
-    for (uint32_t base = 0; base < it.p_cnt; base += NT * V) {
+    // ---- probe: every warp walks its own rows (warp w: rows w*32V .. +32V of every NT*V-row stripe) without CTA barriers
+    for (uint32_t base = warp * (32 * V); base < it.p_cnt; base += NT * V) {
       uint32_t pw[V], pidx[V], outc[V], ex[V];
-      const uint32_t row0 = base + warp * (32 * V) + lane;
+      const uint32_t row0 = base + lane;
       bool any_multi = false;
 #pragma unroll
       for (int j = 0; j < V; ++j) {
@@ -865,7 +920,7 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K> a) {
         outc[j] = o;
         any_multi |= o > 1;
       }
-      // next tile's loads are issued before this tile's results are placed and written
+      // the warp's next rows are in flight before this batch's results are placed and written
 #pragma unroll
       for (int j = 0; j < V; ++j) {
         const uint32_t i = row0 + NT * V + j * 32;
@@ -887,33 +942,15 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K> a) {
           running += __shfl_sync(0xffffffffu, incl, 31);
         }
       }
-      if (lane == 0) s_wtot[warp] = running;
-      __syncthreads();
-      if (warp == 0) {
-        const uint32_t v = lane < NW ? s_wtot[lane] : 0u;
-        const uint32_t incl = warp_incl_scan(v);
-        if (lane < NW) s_wtot[lane] = incl - v;
-        const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
-        if (lane == 0) {
-          uint32_t contig = 0;
-          if (total) {
-            out_writer_reserve(&s_out, a.out_state, total);
-            contig = (s_out.first == 0xFFFFFFFFu && s_out.base0 + total <= a.capacity) ? 1u : 0u;
-          }
-          s_wtot[NW] = total;
-          s_wtot[NW + 1] = contig;
-        }
-      }
-      __syncthreads();
-      if (s_wtot[NW] == 0) continue;  // CTA-uniform
-      const unsigned long long base0 = s_out.base0, base1 = s_out.base1;
-      const uint32_t first = s_out.first;
-      const uint32_t wbase = s_wtot[warp];
-      if (s_wtot[NW + 1]) emit_tile<K, V, CLS, FAST_ROWID, true>(a, s_grp, pw, pidx, outc, ex, wbase, base0, base1, first);
-      else emit_tile<K, V, CLS, FAST_ROWID, false>(a, s_grp, pw, pidx, outc, ex, wbase, base0, base1, first);
+      if (running == 0) continue;  // warp-uniform
+      warp_writer_reserve(&wr, a.out_state, running, chunk_shift);
+      if (wr.first == 0xFFFFFFFFu && wr.base0 + running <= a.capacity)
+        emit_tile<K, V, CLS, FAST_ROWID, true>(a, s_grp, pw, pidx, outc, ex, 0u, wr.base0, wr.base1, wr.first);
+      else
+        emit_tile<K, V, CLS, FAST_ROWID, false>(a, s_grp, pw, pidx, outc, ex, 0u, wr.base0, wr.base1, wr.first);
     }
   }
-  if (threadIdx.x == 0) out_writer_finish(&s_out, a.out_state, a.out_tails);
+  if (lane == 0) out_writer_finish(&wr, a.out_state, a.out_tails);
 }
 
 // =====================================================================================================================
@@ -922,10 +959,10 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K> a) {
 template <int NT>
 __device__ __forceinline__ void emit_flagged(bool flag, uint64_t build_rid, uint64_t probe_rid, uint64_t* out_build,
                                              uint64_t* out_probe, unsigned long long capacity, OutWriter* w,
-                                             OutState* g, uint32_t* scratch) {
+                                             OutState* g, uint32_t* scratch, int chunk_shift) {
   uint32_t total;
   const uint32_t ex = block_excl_scan(flag ? 1u : 0u, scratch, &total);
-  if (threadIdx.x == 0 && total) out_writer_reserve(w, g, total);
+  if (threadIdx.x == 0 && total) out_writer_reserve(w, g, total, chunk_shift);
   __syncthreads();
   if (flag) {
     const unsigned long long pos = out_pos(w->base0, w->base1, w->first, ex);
@@ -958,7 +995,7 @@ __global__ void __launch_bounds__(NT) k_finalize_multi(const JoinArgs<K> a, cons
         flag = (mode == 5) ? hit : !hit;  // Semi keeps matched rows; Left/Right/Anti the unmatched ones
         if (flag) prid = make_rowid(a.probe_rel, a.probe[pos].idx);
       }
-      emit_flagged<NT>(flag, kNullRowId, prid, a.out_build, a.out_probe, a.capacity, &s_out, a.out_state, scratch);
+      emit_flagged<NT>(flag, kNullRowId, prid, a.out_build, a.out_probe, a.capacity, &s_out, a.out_state, scratch, a.chunk_shift);
     }
   }
   if (threadIdx.x == 0) out_writer_finish(&s_out, a.out_state, a.out_tails);
@@ -978,94 +1015,103 @@ __global__ void __launch_bounds__(NT) k_emit_null_probe(const JoinArgs<K> a, con
     const uint32_t i = base + threadIdx.x;
     const bool flag = i < hi;
     const uint64_t prid = flag ? make_rowid(a.probe_rel, pass1[i].idx) : 0;
-    emit_flagged<NT>(flag, kNullRowId, prid, a.out_build, a.out_probe, a.capacity, &s_out, a.out_state, scratch);
+    emit_flagged<NT>(flag, kNullRowId, prid, a.out_build, a.out_probe, a.capacity, &s_out, a.out_state, scratch, a.chunk_shift);
   }
   if (threadIdx.x == 0) out_writer_finish(&s_out, a.out_state, a.out_tails);
 }
 
 // =====================================================================================================================
-// K8: closes the holes at the CTA tails. With T = rows emitted and A = chunks handed out * kChunkRows, the rows stored at
-// positions >= T are moved into the holes below T (both sets have the same size), leaving the dense range [0, T).
-// k_compact_plan (one CTA) sorts the <= kMaxTails holes and builds the two segment lists; k_compact_move copies.
+// K8: closes the holes at the writers' tails. With T = rows emitted, C = chunk rows and A = chunks handed out * C, the rows
+// stored at positions >= T are moved into the holes below T (both sets have the same size), leaving the dense range
+// [0, T). Every chunk is dense except the last chunk of each writer, and a chunk has at most one writer, so
+// k_compact_plan (one CTA) first fills used[c] = C, lets every tail overwrite its chunk's entry, and then scans the
+// per-chunk hole lengths below T and the per-chunk filled lengths above T; k_compact_move maps move k to its
+// (source, destination) pair with two binary searches over those prefix arrays. No sorting of the tails.
 // =====================================================================================================================
-struct CompactPlan {
-  unsigned long long n_move;                       // rows to move
-  uint32_t n_dst, n_src;
-  unsigned long long dst_start[kMaxTails + 1], dst_prefix[kMaxTails + 2];
-  unsigned long long src_start[kMaxTails + 1], src_prefix[kMaxTails + 2];
+struct CompactHdr {
+  uint32_t n_move;    // rows to move
+  uint32_t n_chunks;  // entries of used/hole_pre/src_pre (+1 for the prefixes)
 };
 
 __global__ void __launch_bounds__(1024) k_compact_plan(const OutState* __restrict__ g, const OutTail* __restrict__ tails,
-                                                       CompactPlan* __restrict__ plan) {
-  __shared__ unsigned long long s_pos[kMaxTails], s_end[kMaxTails];
-  __shared__ unsigned long long s_sorted_pos[kMaxTails], s_sorted_end[kMaxTails];
-  const uint32_t n = min(g->n_tails, kMaxTails);
-  const unsigned long long T = g->n_rows, A = g->n_chunks * kChunkRows;
-  const uint32_t t = threadIdx.x;
-  if (t < n) {
-    s_pos[t] = tails[t].pos;
-    s_end[t] = tails[t].pos + tails[t].left;
+                                                       int chunk_shift, unsigned long long capacity,
+                                                       uint32_t* __restrict__ used, uint32_t* __restrict__ hole_pre,
+                                                       uint32_t* __restrict__ src_pre, CompactHdr* __restrict__ hdr) {
+  __shared__ uint32_t scratch[33];
+  __shared__ uint32_t s_carry_h, s_carry_s;
+  const unsigned long long T = g->n_rows, nc64 = g->n_chunks;
+  const uint32_t C = 1u << chunk_shift;
+  if ((nc64 << chunk_shift) > capacity) {  // the buffers overflowed: the host probes again, nothing to compact
+    if (threadIdx.x == 0) { hdr->n_move = 0; hdr->n_chunks = 0; }
+    return;
+  }
+  const uint32_t nc = static_cast<uint32_t>(nc64);
+  for (uint32_t c = threadIdx.x; c < nc; c += blockDim.x) used[c] = C;
+  if (threadIdx.x == 0) { s_carry_h = 0; s_carry_s = 0; }
+  __syncthreads();
+  const uint32_t nt = min(g->n_tails, kMaxTails);
+  for (uint32_t t = threadIdx.x; t < nt; t += blockDim.x) {
+    const unsigned long long pos = tails[t].pos;
+    const unsigned long long c = pos >> chunk_shift;
+    if (c < nc) used[c] = static_cast<uint32_t>(pos & (C - 1u));
   }
   __syncthreads();
-  if (t < n) {  // rank sort (positions are distinct: holes are disjoint and non-empty)
-    uint32_t r = 0;
-    for (uint32_t i = 0; i < n; ++i) r += s_pos[i] < s_pos[t];
-    s_sorted_pos[r] = s_pos[t];
-    s_sorted_end[r] = s_end[t];
-  }
-  __syncthreads();
-  if (t == 0) {
-    // destinations: holes clipped to [0, T); sources: gaps between holes clipped to [T, A)
-    uint32_t nd = 0, ns = 0;
-    unsigned long long dsum = 0, ssum = 0, prev_end = 0;
-    for (uint32_t i = 0; i <= n; ++i) {
-      const unsigned long long hp = i < n ? s_sorted_pos[i] : A, he = i < n ? s_sorted_end[i] : A;
-      // filled gap [prev_end, hp)
-      const unsigned long long gs = prev_end > T ? prev_end : T;
-      if (hp > gs) {
-        plan->src_start[ns] = gs;
-        plan->src_prefix[ns] = ssum;
-        ssum += hp - gs;
-        ++ns;
-      }
-      // hole [hp, he)
-      const unsigned long long de = he < T ? he : T;
-      if (i < n && de > hp) {
-        plan->dst_start[nd] = hp;
-        plan->dst_prefix[nd] = dsum;
-        dsum += de - hp;
-        ++nd;
-      }
-      prev_end = he;
+  for (uint32_t base = 0; base < nc; base += blockDim.x) {
+    const uint32_t c = base + threadIdx.x;
+    uint32_t hole = 0, src = 0;
+    if (c < nc) {
+      const unsigned long long lo = static_cast<unsigned long long>(c) << chunk_shift, fe = lo + used[c], ce = lo + C;
+      const unsigned long long he = ce < T ? ce : T;       // holes count below T only: [fe, min(ce, T))
+      if (fe < he) hole = static_cast<uint32_t>(he - fe);
+      const unsigned long long sb = lo > T ? lo : T;        // rows to move lie at or above T: [max(lo, T), fe)
+      if (fe > sb) src = static_cast<uint32_t>(fe - sb);
     }
-    plan->src_prefix[ns] = ssum;
-    plan->dst_prefix[nd] = dsum;
-    plan->n_src = ns;
-    plan->n_dst = nd;
-    plan->n_move = dsum < ssum ? dsum : ssum;  // equal by construction
+    uint32_t th, ts;
+    const uint32_t eh = block_excl_scan(hole, scratch, &th) + s_carry_h;
+    const uint32_t es = block_excl_scan(src, scratch, &ts) + s_carry_s;
+    if (c < nc) {
+      hole_pre[c] = eh;
+      src_pre[c] = es;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      s_carry_h += th;
+      s_carry_s += ts;
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    hole_pre[nc] = s_carry_h;
+    src_pre[nc] = s_carry_s;
+    hdr->n_move = min(s_carry_h, s_carry_s);  // equal by construction
+    hdr->n_chunks = nc;
   }
 }
 
-__device__ __forceinline__ unsigned long long seg_map(const unsigned long long* start, const unsigned long long* prefix,
-                                                      uint32_t n, unsigned long long k) {
-  uint32_t lo = 0, hi = n;  // largest seg with prefix[seg] <= k
+// largest c in [0, n) with pre[c] <= k (entries of zero length share their successor's prefix, so the result has pre[c+1] > k)
+__device__ __forceinline__ uint32_t seg_of(const uint32_t* pre, uint32_t n, uint32_t k) {
+  uint32_t lo = 0, hi = n;
   while (hi - lo > 1) {
     const uint32_t mid = (lo + hi) >> 1;
-    if (prefix[mid] <= k) lo = mid; else hi = mid;
+    if (pre[mid] <= k) lo = mid; else hi = mid;
   }
-  return start[lo] + (k - prefix[lo]);
+  return lo;
 }
 
-__global__ void __launch_bounds__(256) k_compact_move(const CompactPlan* __restrict__ plan, uint64_t* __restrict__ out_build,
-                                                      uint64_t* __restrict__ out_probe, unsigned long long capacity) {
-  const unsigned long long n = plan->n_move;
-  for (unsigned long long k = blockIdx.x * 256ull + threadIdx.x; k < n; k += gridDim.x * 256ull) {
-    const unsigned long long dst = seg_map(plan->dst_start, plan->dst_prefix, plan->n_dst, k);
-    const unsigned long long src = seg_map(plan->src_start, plan->src_prefix, plan->n_src, k);
-    if (src < capacity && dst < capacity) {
-      if (out_build) out_build[dst] = out_build[src];
-      out_probe[dst] = out_probe[src];
-    }
+__global__ void __launch_bounds__(256) k_compact_move(const CompactHdr* __restrict__ hdr, const OutState* __restrict__ g,
+                                                      int chunk_shift, const uint32_t* __restrict__ used,
+                                                      const uint32_t* __restrict__ hole_pre,
+                                                      const uint32_t* __restrict__ src_pre, uint64_t* __restrict__ out_build,
+                                                      uint64_t* __restrict__ out_probe) {
+  const uint32_t n = hdr->n_move, nc = hdr->n_chunks;
+  const unsigned long long T = g->n_rows;
+  for (uint32_t k = blockIdx.x * 256u + threadIdx.x; k < n; k += gridDim.x * 256u) {
+    const uint32_t cd = seg_of(hole_pre, nc, k), cs = seg_of(src_pre, nc, k);
+    const unsigned long long dst = (static_cast<unsigned long long>(cd) << chunk_shift) + used[cd] + (k - hole_pre[cd]);
+    const unsigned long long slo = static_cast<unsigned long long>(cs) << chunk_shift;
+    const unsigned long long src = (slo > T ? slo : T) + (k - src_pre[cs]);
+    if (out_build) out_build[dst] = out_build[src];
+    out_probe[dst] = out_probe[src];
   }
 }
 
