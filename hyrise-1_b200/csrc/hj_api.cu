@@ -106,6 +106,12 @@ int fail(hj_ctx* ctx, int status, const char* fmt, ...) {
     if (st_ != HJ_OK) return st_; \
   } while (0)
 
+#define HJ_LAUNCH_CHECK(ctx, name)                                                                 \
+  do {                                                                                             \
+    cudaError_t e_ = cudaGetLastError();                                                           \
+    if (e_ != cudaSuccess) return fail(ctx, HJ_ERR_CUDA, "launch of %s failed: %s", name, cudaGetErrorString(e_)); \
+  } while (0)
+
 // grow-only device buffer
 int ensure(hj_ctx* ctx, DevBuf& b, size_t bytes) {
   if (bytes <= b.cap) return HJ_OK;
@@ -161,7 +167,7 @@ int prepare_relation(hj_ctx* ctx, const hj_relation* r, int side, uint32_t tile,
   PreparedRel& pr = *out;
   const uint32_t n_segs = r->n_segs;
   pr.segs.resize(n_segs);
-  std::vector<uint32_t> row_begin(n_segs + 1, 0), tile_seg;
+  std::vector<uint32_t> row_begin(n_segs + 1, 0);
   uint32_t rows = 0, tiles = 0, words = 0;
   bool identity = true;
   auto key_bytes = [](const hj_segment& s) { return s.key_type == HJ_KEY_INT64 ? 8u : 4u; };
@@ -204,7 +210,6 @@ int prepare_relation(hj_ctx* ctx, const hj_relation* r, int side, uint32_t tile,
     }
     if (s.chunk_id != i || d.row_offsets) identity = false;
     const uint32_t nt = (s.n_rows + tile - 1) / tile;
-    for (uint32_t t = 0; t < nt; ++t) tile_seg.push_back(i);
     tiles += nt;
     rows += s.n_rows;
     if (host) {
@@ -259,10 +264,14 @@ int prepare_relation(hj_ctx* ctx, const hj_relation* r, int side, uint32_t tile,
   }
 
   HJ_TRY(ensure(ctx, ctx->segs[side], std::max<size_t>(1, n_segs) * sizeof(DevSegment)));
-  HJ_TRY(ensure(ctx, ctx->tile_seg[side], std::max<size_t>(1, tile_seg.size()) * 4));
+  HJ_TRY(ensure(ctx, ctx->tile_seg[side], std::max<size_t>(1, tiles) * 4));
   HJ_TRY(ensure(ctx, ctx->seg_row_begin[side], (size_t(n_segs) + 1) * 4));
   if (n_segs) HJ_CUDA(ctx, cudaMemcpyAsync(ctx->segs[side].p, pr.segs.data(), n_segs * sizeof(DevSegment), cudaMemcpyHostToDevice, st));
-  if (!tile_seg.empty()) HJ_CUDA(ctx, cudaMemcpyAsync(ctx->tile_seg[side].p, tile_seg.data(), tile_seg.size() * 4, cudaMemcpyHostToDevice, st));
+  if (tiles) {
+    k_fill_tile_seg<<<std::min<uint32_t>(n_segs, 1024), 128, 0, st>>>(static_cast<const DevSegment*>(ctx->segs[side].p), n_segs, tile,
+                                                                    static_cast<uint32_t*>(ctx->tile_seg[side].p));
+    HJ_LAUNCH_CHECK(ctx, "k_fill_tile_seg");
+  }
   HJ_CUDA(ctx, cudaMemcpyAsync(ctx->seg_row_begin[side].p, row_begin.data(), (size_t(n_segs) + 1) * 4, cudaMemcpyHostToDevice, st));
   // the three vectors above are pageable: cudaMemcpyAsync returns after staging them, so they may die with this frame
 
@@ -289,12 +298,6 @@ int radix_bits_for(uint64_t n_build, int key_type) {
 struct Launches {
   uint32_t n = 0;
 };
-
-#define HJ_LAUNCH_CHECK(ctx, name)                                                                 \
-  do {                                                                                             \
-    cudaError_t e_ = cudaGetLastError();                                                           \
-    if (e_ != cudaSuccess) return fail(ctx, HJ_ERR_CUDA, "launch of %s failed: %s", name, cudaGetErrorString(e_)); \
-  } while (0)
 
 template <typename KernelT>
 int set_smem(hj_ctx* ctx, KernelT kernel, size_t bytes) {

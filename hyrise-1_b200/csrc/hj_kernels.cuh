@@ -33,10 +33,20 @@ __device__ __forceinline__ K load_plain_key(const DevSegment& s, uint32_t i) {
   if (s.key_type == 0) return static_cast<K>(__ldg(static_cast<const int32_t*>(s.values) + i));
   return static_cast<K>(__ldg(static_cast<const int64_t*>(s.values) + i));
 }
+
 __device__ __forceinline__ uint32_t load_attr(const DevSegment& s, uint32_t i) {
   if (s.attr_width == 4) return __ldg(static_cast<const uint32_t*>(s.attr) + i);
   if (s.attr_width == 2) return __ldg(static_cast<const uint16_t*>(s.attr) + i);
   return __ldg(static_cast<const uint8_t*>(s.attr) + i);
+}
+
+// K0: tile -> segment map, filled on the device from the segments' tile ranges (uploading it cost 0.7 ms per C2 join).
+__global__ void k_fill_tile_seg(const DevSegment* __restrict__ segs, uint32_t n_segs, uint32_t tile_rows,
+                                uint32_t* __restrict__ tile_seg) {
+  for (uint32_t sidx = blockIdx.x; sidx < n_segs; sidx += gridDim.x) {
+    const uint32_t t0 = segs[sidx].tile_begin, nt = (segs[sidx].n_rows + tile_rows - 1) / tile_rows;
+    for (uint32_t t = threadIdx.x; t < nt; t += blockDim.x) tile_seg[t0 + t] = sidx;
+  }
 }
 
 // =====================================================================================================================
@@ -283,7 +293,7 @@ __global__ void __launch_bounds__(NT, 4) k_scatter1(const ScatterArgs<K> a) {
         const uint32_t i = j * NT + threadIdx.x;
         key[j] = K(0);
         if (i < n_in) {
-          key[j] = __ldcs(km + i);
+          key[j] = __ldg(km + i);
           vbits |= ((__ldg(vm + (i >> 5)) >> (i & 31u)) & 1u) << j;
         }
       }
