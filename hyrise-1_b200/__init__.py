@@ -191,7 +191,8 @@ class HashJoin:
         t = abi.Timings()
         self._check(self._l.hj_get_timings(self._ctx, C.byref(t)))
         d = {name: t.ms[i] for i, name in enumerate(abi.PHASES)}
-        d.update(bytes_h2d=t.bytes_h2d, bytes_d2h=t.bytes_d2h, n_kernel_launches=t.n_kernel_launches)
+        d.update(bytes_h2d=t.bytes_h2d, bytes_d2h=t.bytes_d2h, n_kernel_launches=t.n_kernel_launches,
+                 bytes_nvlink_sent=t.bytes_nvlink_sent)
         return d
 
     def release_scratch(self):
@@ -208,6 +209,11 @@ def comm_unique_id():
     if st != abi.OK:
         raise HjError(st, "hj_comm_unique_id failed")
     return bytes(buf)
+
+
+def exchange_rank_of(key, key_type, n_ranks):
+    """Rank on which all rows with `key` meet in hj_join_sharded (host arithmetic, no GPU needed)."""
+    return lib().hj_exchange_rank_of(int(key), key_type, n_ranks)
 
 
 def radix_bits(n_build_rows, key_type=abi.KEY_INT32):

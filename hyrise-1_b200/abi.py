@@ -2,7 +2,7 @@
 tests/test_abi.py checks the struct sizes against the values compiled into the library (hj_abi_sizeof)."""
 import ctypes as C
 
-HJ_ABI_VERSION = 1
+HJ_ABI_VERSION = 2
 
 # JoinMode, src/lib/types.hpp:189 of the reference
 MODE_INNER, MODE_LEFT, MODE_RIGHT, MODE_OUTER, MODE_CROSS, MODE_SEMI, MODE_ANTI = range(7)
@@ -15,8 +15,9 @@ FLAG_SQL_NULL_PROBE = 0x1
 FLAG_TIMINGS = 0x2
 INVALID_CHUNK_ID = 0xFFFFFFFF
 INVALID_CHUNK_OFFSET = 0xFFFFFFFF
-N_PHASES = 8
-PHASES = ["h2d", "materialize", "scatter1", "scatter2", "build_probe", "finalize", "d2h", "total"]
+N_PHASES = 10
+PHASES = ["h2d", "materialize", "scatter1", "scatter2", "build_probe", "finalize", "d2h", "total", "xchg_partition",
+          "xchg_transfer"]
 NCCL_UNIQUE_ID_BYTES = 128
 
 OK, ERR_INVALID, ERR_CUDA, ERR_OOM, ERR_CAPACITY, ERR_TOO_LARGE, ERR_STATE, ERR_COMM = range(8)
@@ -54,7 +55,7 @@ class ResultInfo(C.Structure):
 
 class Timings(C.Structure):
     _fields_ = [("ms", C.c_float * N_PHASES), ("bytes_h2d", C.c_uint64), ("bytes_d2h", C.c_uint64),
-                ("n_kernel_launches", C.c_uint32), ("reserved", C.c_uint32)]
+                ("n_kernel_launches", C.c_uint32), ("reserved", C.c_uint32), ("bytes_nvlink_sent", C.c_uint64)]
 
 
 # every symbol include/hj.h declares: name -> (restype, argtypes)
@@ -73,6 +74,7 @@ SYMBOLS = {
                                C.c_uint32]),
     "hj_get_timings": (C.c_int, [C.c_void_p, C.POINTER(Timings)]),
     "hj_release_scratch": (C.c_int, [C.c_void_p]),
+    "hj_exchange_rank_of": (C.c_uint32, [C.c_int64, C.c_int, C.c_uint32]),
     "hj_comm_unique_id": (C.c_int, [C.POINTER(C.c_uint8)]),
     "hj_comm_init": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint8), C.c_int, C.c_int]),
     "hj_join_sharded": (C.c_int, [C.c_void_p, C.POINTER(Relation), C.POINTER(Relation), C.c_int, C.c_void_p,

@@ -69,13 +69,20 @@ struct hj_ctx {
   // multi-GPU
   void* nccl_comm = nullptr;
   int n_ranks = 1, rank = 0;
+  DevBuf xchg_counts[2], xchg_cnt_dev, xchg_send_keys[2], xchg_send_rids[2], xchg_send_nulls[2], xchg_recv_keys[2],
+      xchg_recv_rids[2], xchg_recv_nulls[2];
+  const uint64_t* xchg_rowids[2] = {nullptr, nullptr};  // set while hj_join_sharded runs its local join
+  uint64_t xchg_bytes_sent[2] = {0, 0};
 
   hj_ctx() {
     for (DevBuf* b : {&stage_in[0], &stage_in[1], &segs[0], &segs[1], &tile_seg[0], &tile_seg[1], &seg_row_begin[0],
                       &seg_row_begin[1], &keys_mat[0], &keys_mat[1], &valid_mask[0], &valid_mask[1], &hist[0], &hist[1],
                       &part_off[0], &part_off[1], &hist1[0], &hist1[1], &cur2[0], &cur2[1], &l1_tiles[0], &l1_tiles[1],
                       &tup_a[0], &tup_a[1], &tup_b[0], &tup_b[1], &items, &fin, &plan, &queue, &out_state, &out_tails, &compact_plan, &compact_used, &compact_hole, &compact_src, &matched,
-                      &out_build, &out_probe, &misc})
+                      &out_build, &out_probe, &misc, &xchg_counts[0], &xchg_counts[1], &xchg_cnt_dev, &xchg_send_keys[0],
+                      &xchg_send_keys[1], &xchg_send_rids[0], &xchg_send_rids[1], &xchg_send_nulls[0], &xchg_send_nulls[1],
+                      &xchg_recv_keys[0], &xchg_recv_keys[1], &xchg_recv_rids[0], &xchg_recv_rids[1], &xchg_recv_nulls[0],
+                      &xchg_recv_nulls[1]})
       all_bufs.push_back(b);
   }
 };
@@ -200,6 +207,10 @@ int prepare_relation(hj_ctx* ctx, const hj_relation* r, int side, uint32_t tile,
     d.tile_begin = tiles;
     d.mask_word_begin = words;
     d.kind = s.kind;
+    if (ctx->xchg_rowids[side]) {  // local join of hj_join_sharded: the rows carry their RowIDs
+      d.kind = kSegExchanged;
+      d.attr = ctx->xchg_rowids[side];
+    }
     d.key_type = s.key_type;
     d.attr_width = s.attr_width;
     row_begin[i] = rows;
@@ -208,7 +219,7 @@ int prepare_relation(hj_ctx* ctx, const hj_relation* r, int side, uint32_t tile,
       pr.has_dict = true;
       words += (s.n_rows + 31) / 32;
     }
-    if (s.chunk_id != i || d.row_offsets) identity = false;
+    if (s.chunk_id != i || d.row_offsets || d.kind == kSegExchanged) identity = false;
     const uint32_t nt = (s.n_rows + tile - 1) / tile;
     tiles += nt;
     rows += s.n_rows;
@@ -661,7 +672,7 @@ int hj_create(int device_id, const hj_options* opts, hj_ctx** out_ctx) {
     return fail(nullptr, HJ_ERR_CUDA, "device %d is sm_%d%d; libhj is built for sm_100a only", device_id, prop.major, prop.minor);
   }
   ok = ok && cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) == cudaSuccess;
-  ok = ok && cudaHostAlloc(&ctx->pinned, 4096, cudaHostAllocDefault) == cudaSuccess;
+  ok = ok && cudaHostAlloc(&ctx->pinned, 16384, cudaHostAllocDefault) == cudaSuccess;
   for (auto& ev : ctx->ev) ok = ok && cudaEventCreate(&ev) == cudaSuccess;
   if (!ok) {
     const char* msg = cudaGetErrorString(cudaGetLastError());
@@ -684,9 +695,12 @@ int hj_release_scratch(hj_ctx* ctx) {
   return HJ_OK;
 }
 
+void hj_comm_release(hj_ctx* ctx);  // hj_comm.cuh
+
 void hj_destroy(hj_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
+  hj_comm_release(ctx);
   hj_release_scratch(ctx);
   for (auto& ev : ctx->ev)
     if (ev) cudaEventDestroy(ev);
@@ -794,5 +808,4 @@ int hj_get_timings(const hj_ctx* ctx, hj_timings* out) {
 }  // extern "C"
 
 // ============================================================================================================= multi-GPU
-// Implemented in hj_comm.cuh (included below) once the NCCL exchange is wired; see DESIGN.md §6.
 #include "hj_comm.cuh"

@@ -1,23 +1,552 @@
-// hj_comm.cuh — multi-GPU exchange. Placeholder until the NCCL all-to-all lands: the entry points exist
-// (include/hj.h declares them) and fail loudly.
+// hj_comm.cuh — multi-GPU exchange (no reference counterpart: the reference is single-process).
+//
+// One process per GPU. Both relations are split by dest_rank_of_hash(hash(key)) so that every key's build and probe rows
+// meet on exactly one rank; after the exchange each rank runs the unchanged single-GPU join on what it received. RowIDs
+// travel with the keys (they are global), so per-rank results simply concatenate.
+//
+//   X1 k_xchg_count    decode (dictionary gather once, decoded keys kept like K1) + per-CTA counts per destination rank
+//   X2 k_xchg_offsets  counts -> private send cursors per (destination, CTA) + totals per destination
+//   X3 k_xchg_scatter  shared-memory-staged scatter of (key, RowID[, null flag]) into per-destination send regions (SoA)
+//   all-to-all         counts: one ncclAllGather; data: one ncclGroup of ncclSend/ncclRecv per relation over NVLink
+//
+// NCCL is loaded with dlopen at hj_comm_init (the process usually has torch's libnccl.so.2 mapped already; linking a
+// second copy at build time would pin a version).
 #pragma once
+#include <dlfcn.h>
+
+namespace hj {
+
+constexpr int kMaxRanks = 16;
+
+struct XchgArgs {
+  RelMeta rel;
+  void* keys_mat;            // decoded keys of DICT chunks (written by X1, read by X3)
+  uint32_t* valid_mask;
+  uint32_t* counts;          // [d * G + c]; X2 turns them into send cursors in place
+  unsigned long long* send_cnt;  // [n_ranks] rows per destination
+  void* out_keys;            // X3: send buffer, K per row
+  uint64_t* out_rids;        // X3: packed global RowIDs
+  uint8_t* out_nulls;        // X3: null flags (kNullRoute only) or nullptr
+  uint32_t n_ranks;
+  uint32_t my_rank;
+  int null_policy;
+};
+
+// Loads one tile's keys. DICT chunks go through the dictionary when `from_mat` is false (and the decoded key + validity
+// bit are stored), else they are read back from keys_mat/valid_mask.
+template <typename K, int NT, int ITEMS>
+__device__ __forceinline__ void xchg_load_tile(const XchgArgs& a, const DevSegment& s, uint32_t r0, uint32_t cnt, bool from_mat,
+                                               K (&key)[ITEMS], uint32_t& vbits) {
+  K* keys_mat = static_cast<K*>(a.keys_mat);
+  vbits = 0;
+  if (s.kind == 1 && !from_mat) {
+    uint32_t vid[ITEMS];
+#pragma unroll
+    for (int u = 0; u < ITEMS; ++u) {
+      const uint32_t i = u * NT + threadIdx.x;
+      vid[u] = i < cnt ? load_attr(s, r0 + i) : s.null_value_id;
+    }
+#pragma unroll
+    for (int u = 0; u < ITEMS; ++u) {
+      const bool valid = vid[u] != s.null_value_id;  // inactive rows carry null_value_id
+      key[u] = valid ? load_plain_key<K>(s, vid[u]) : K(0);
+      vbits |= (valid ? 1u : 0u) << u;
+    }
+#pragma unroll
+    for (int u = 0; u < ITEMS; ++u) {
+      const uint32_t i = u * NT + threadIdx.x;
+      if (i < cnt) keys_mat[s.row_begin + r0 + i] = key[u];
+      const uint32_t bits = __ballot_sync(0xffffffffu, (vbits >> u) & 1u);
+      if (lane_id() == 0 && i < cnt) a.valid_mask[s.mask_word_begin + ((r0 + i) >> 5)] = bits;
+    }
+  } else if (s.kind == 1) {
+#pragma unroll
+    for (int u = 0; u < ITEMS; ++u) {
+      const uint32_t i = u * NT + threadIdx.x;
+      key[u] = K(0);
+      if (i < cnt) {
+        key[u] = keys_mat[s.row_begin + r0 + i];
+        vbits |= ((__ldg(a.valid_mask + s.mask_word_begin + ((r0 + i) >> 5)) >> (i & 31u)) & 1u) << u;
+      }
+    }
+  } else {
+#pragma unroll
+    for (int u = 0; u < ITEMS; ++u) {
+      const uint32_t i = u * NT + threadIdx.x;
+      key[u] = K(0);
+      if (i < cnt) {
+        key[u] = load_plain_key<K>(s, r0 + i);
+        const bool valid = !(s.nulls && __ldg(s.nulls + r0 + i));
+        if (s.kind == 2 && !valid) key[u] = K(0);
+        vbits |= (valid ? 1u : 0u) << u;
+      }
+    }
+  }
+}
+
+// destination of one row, or kNoDigit when the row is dropped
+template <typename K>
+__device__ __forceinline__ uint32_t xchg_dest(const XchgArgs& a, K key, bool valid) {
+  if (valid || a.null_policy == kNullAsValue) return dest_rank_of_hash(hash_key(key), a.n_ranks);
+  if (a.null_policy == kNullRoute) return a.my_rank;  // stays here and is emitted as (NULL, p) by the local join
+  return kNoDigit;
+}
+
+// X1. Persistent virtual CTA c owns tiles c, c+G, ... (X3 uses the same ownership: private cursors, no atomics).
+template <typename K, int NT, int ITEMS>
+__global__ void __launch_bounds__(NT) k_xchg_count(const XchgArgs a) {
+  constexpr uint32_t TILE = NT * ITEMS;
+  __shared__ uint32_t s_cnt[kMaxRanks];
+  if (threadIdx.x < kMaxRanks) s_cnt[threadIdx.x] = 0;
+  __syncthreads();
+  uint32_t cnt[kMaxRanks];
+#pragma unroll
+  for (int d = 0; d < kMaxRanks; ++d) cnt[d] = 0;
+  for (uint32_t tile = blockIdx.x; tile < a.rel.n_tiles; tile += gridDim.x) {
+    const DevSegment s = a.rel.segs[__ldg(a.rel.tile_seg + tile)];
+    const uint32_t r0 = (tile - s.tile_begin) * TILE;
+    const uint32_t n_in = min(TILE, s.n_rows - r0);
+    K key[ITEMS];
+    uint32_t vbits;
+    xchg_load_tile<K, NT, ITEMS>(a, s, r0, n_in, false, key, vbits);
+#pragma unroll
+    for (int u = 0; u < ITEMS; ++u) {
+      if (u * NT + threadIdx.x < n_in) {
+        const uint32_t d = xchg_dest<K>(a, key[u], (vbits >> u) & 1u);
+#pragma unroll
+        for (int q = 0; q < kMaxRanks; ++q) cnt[q] += (d == static_cast<uint32_t>(q)) ? 1u : 0u;
+      }
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < kMaxRanks; ++q) {
+    uint32_t v = cnt[q];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane_id() == 0 && v) atomicAdd(&s_cnt[q], v);
+  }
+  __syncthreads();
+  if (threadIdx.x < a.n_ranks) a.counts[threadIdx.x * gridDim.x + blockIdx.x] = s_cnt[threadIdx.x];
+}
+
+// X2. One CTA: totals per destination, exclusive scan over destinations (send region starts), then per destination the
+// exclusive scan over the virtual CTAs (private cursors, in place).
+template <int NT>
+__global__ void __launch_bounds__(NT) k_xchg_offsets(uint32_t* __restrict__ counts, unsigned long long* __restrict__ send_cnt,
+                                                     uint32_t n_ranks, uint32_t G) {
+  __shared__ uint32_t scratch[33];
+  __shared__ uint32_t s_carry;
+  if (threadIdx.x == 0) s_carry = 0;
+  __syncthreads();
+  for (uint32_t d = 0; d < n_ranks; ++d) {
+    const uint32_t start = s_carry;
+    for (uint32_t base = 0; base < G; base += NT) {
+      const uint32_t c = base + threadIdx.x;
+      const uint32_t v = c < G ? counts[d * G + c] : 0u;
+      uint32_t total;
+      const uint32_t ex = block_excl_scan(v, scratch, &total) + s_carry;
+      if (c < G) counts[d * G + c] = ex;
+      __syncthreads();
+      if (threadIdx.x == 0) s_carry += total;
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) send_cnt[d] = s_carry - start;
+  }
+}
+
+// X3. Per tile: rank every row inside its destination with a shared-memory atomic, stage (key, RowID, flag) grouped by
+// destination, copy the groups out with consecutive lanes on consecutive addresses.
+// dynamic smem: TILE * (sizeof(K) + 8 + 1 + 1).
+template <typename K, int NT, int ITEMS>
+__global__ void __launch_bounds__(NT) k_xchg_scatter(const XchgArgs a) {
+  constexpr uint32_t TILE = NT * ITEMS;
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  uint64_t* s_rid = reinterpret_cast<uint64_t*>(s_raw);
+  K* s_key = reinterpret_cast<K*>(s_rid + TILE);
+  uint8_t* s_dig = reinterpret_cast<uint8_t*>(s_key + TILE);
+  uint8_t* s_nul = s_dig + TILE;
+  __shared__ uint32_t s_cnt[kMaxRanks], s_loff[kMaxRanks + 1], s_delta[kMaxRanks], s_cur[kMaxRanks];
+  K* out_keys = static_cast<K*>(a.out_keys);
+  const uint32_t G = gridDim.x;
+  if (threadIdx.x < a.n_ranks) s_cur[threadIdx.x] = a.counts[threadIdx.x * G + blockIdx.x];
+
+  for (uint32_t tile = blockIdx.x; tile < a.rel.n_tiles; tile += G) {
+    const DevSegment s = a.rel.segs[__ldg(a.rel.tile_seg + tile)];
+    const uint32_t r0 = (tile - s.tile_begin) * TILE;
+    const uint32_t n_in = min(TILE, s.n_rows - r0);
+    if (threadIdx.x < kMaxRanks) s_cnt[threadIdx.x] = 0;
+    __syncthreads();  // also orders the previous tile's copy-out before this tile's staging
+    K key[ITEMS];
+    uint32_t vbits;
+    xchg_load_tile<K, NT, ITEMS>(a, s, r0, n_in, true, key, vbits);
+    uint32_t packed[ITEMS];
+#pragma unroll
+    for (int u = 0; u < ITEMS; ++u) {
+      packed[u] = kNoDigit;
+      if (u * NT + threadIdx.x < n_in) {
+        const uint32_t d = xchg_dest<K>(a, key[u], (vbits >> u) & 1u);
+        if (d != kNoDigit) packed[u] = (d << 16) | atomicAdd(&s_cnt[d], 1u);
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      uint32_t run = 0;
+      for (uint32_t d = 0; d < a.n_ranks; ++d) {
+        const uint32_t c = s_cnt[d];
+        s_loff[d] = run;
+        s_delta[d] = s_cur[d] - run;
+        s_cur[d] += c;
+        run += c;
+      }
+      s_loff[a.n_ranks] = run;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int u = 0; u < ITEMS; ++u) {
+      if (packed[u] != kNoDigit) {
+        const uint32_t d = packed[u] >> 16, pos = s_loff[d] + (packed[u] & 0xFFFFu);
+        s_key[pos] = key[u];
+        s_rid[pos] = make_rowid(a.rel, s.row_begin + r0 + u * NT + threadIdx.x);
+        s_dig[pos] = static_cast<uint8_t>(d);
+        s_nul[pos] = ((vbits >> u) & 1u) ? 0 : 1;
+      }
+    }
+    __syncthreads();
+    const uint32_t n_out = s_loff[a.n_ranks];
+#pragma unroll
+    for (int u = 0; u < ITEMS; ++u) {
+      const uint32_t i = u * NT + threadIdx.x;
+      if (i < n_out) {
+        const uint32_t g = s_delta[s_dig[i]] + i;
+        out_keys[g] = s_key[i];
+        a.out_rids[g] = s_rid[i];
+        if (a.out_nulls) a.out_nulls[g] = s_nul[i];
+      }
+    }
+  }
+}
+
+}  // namespace hj
+
+// ============================================================================================================= host side
+#include <nccl.h>
+
+namespace {
+
+struct NcclApi {
+  void* handle = nullptr;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
+  const char* (*GetErrorString)(ncclResult_t) = nullptr;
+  std::string error;
+};
+
+NcclApi* nccl_api() {
+  static NcclApi api;
+  static bool tried = false;
+  if (tried) return &api;
+  tried = true;
+  for (const char* name : {"libnccl.so.2", "libnccl.so"}) {
+    api.handle = dlopen(name, RTLD_NOW | RTLD_GLOBAL);
+    if (api.handle) break;
+  }
+  if (!api.handle) {
+    api.error = std::string("dlopen(libnccl.so.2) failed: ") + dlerror();
+    return &api;
+  }
+  bool ok = true;
+  auto sym = [&](const char* n) {
+    void* p = dlsym(api.handle, n);
+    if (!p) { ok = false; api.error = std::string("libnccl lacks ") + n; }
+    return p;
+  };
+  api.GetUniqueId = reinterpret_cast<decltype(api.GetUniqueId)>(sym("ncclGetUniqueId"));
+  api.CommInitRank = reinterpret_cast<decltype(api.CommInitRank)>(sym("ncclCommInitRank"));
+  api.CommDestroy = reinterpret_cast<decltype(api.CommDestroy)>(sym("ncclCommDestroy"));
+  api.AllGather = reinterpret_cast<decltype(api.AllGather)>(sym("ncclAllGather"));
+  api.Send = reinterpret_cast<decltype(api.Send)>(sym("ncclSend"));
+  api.Recv = reinterpret_cast<decltype(api.Recv)>(sym("ncclRecv"));
+  api.GroupStart = reinterpret_cast<decltype(api.GroupStart)>(sym("ncclGroupStart"));
+  api.GroupEnd = reinterpret_cast<decltype(api.GroupEnd)>(sym("ncclGroupEnd"));
+  api.GetErrorString = reinterpret_cast<decltype(api.GetErrorString)>(sym("ncclGetErrorString"));
+  if (!ok) { dlclose(api.handle); api.handle = nullptr; }
+  return &api;
+}
+
+#define HJ_NCCL(ctx, call)                                                                                   \
+  do {                                                                                                       \
+    ncclResult_t r_ = (call);                                                                                \
+    if (r_ != ncclSuccess)                                                                                   \
+      return fail(ctx, HJ_ERR_COMM, "%s failed: %s (%s:%d)", #call, nccl_api()->GetErrorString(r_), __FILE__, __LINE__); \
+  } while (0)
+
+static_assert(sizeof(ncclUniqueId) == HJ_NCCL_UNIQUE_ID_BYTES, "hj.h carries the NCCL unique id as 128 opaque bytes");
+
+struct XchgSide {          // per relation, filled by the partition step
+  PreparedRel pr;
+  uint32_t G = 0;
+  int null_policy = kNullDrop;
+  bool send_nulls = false;
+};
+
+constexpr int kXchgThreads = 256;
+template <typename K> constexpr int xchg_items() { return sizeof(K) == 4 ? 16 : 8; }
+template <typename K> constexpr int xchg_tile() { return kXchgThreads * xchg_items<K>(); }
+
+template <typename K>
+XchgArgs xchg_args(hj_ctx* ctx, const XchgSide& xs, int side) {
+  XchgArgs a{};
+  a.rel = xs.pr.meta;
+  a.keys_mat = ctx->keys_mat[side].p;
+  a.valid_mask = static_cast<uint32_t*>(ctx->valid_mask[side].p);
+  a.counts = static_cast<uint32_t*>(ctx->xchg_counts[side].p);
+  a.send_cnt = static_cast<unsigned long long*>(ctx->xchg_cnt_dev.p) + size_t(side) * kMaxRanks;
+  a.out_keys = ctx->xchg_send_keys[side].p;
+  a.out_rids = static_cast<uint64_t*>(ctx->xchg_send_rids[side].p);
+  a.out_nulls = xs.send_nulls ? static_cast<uint8_t*>(ctx->xchg_send_nulls[side].p) : nullptr;
+  a.n_ranks = ctx->n_ranks;
+  a.my_rank = ctx->rank;
+  a.null_policy = xs.null_policy;
+  return a;
+}
+
+// X1 + X2 for one relation shard
+template <typename K>
+int xchg_count(hj_ctx* ctx, const hj_relation* rel, int side, XchgSide* xs, cudaStream_t st, uint32_t* n_launch) {
+  HJ_TRY(prepare_relation(ctx, rel, side, xchg_tile<K>(), st, &xs->pr));
+  const uint32_t n = xs->pr.meta.n_rows;
+  xs->G = std::max<uint32_t>(1, std::min<uint32_t>(xs->pr.meta.n_tiles, uint32_t(kVirtualCtasPerSm) * ctx->n_sms));
+  HJ_TRY(ensure(ctx, ctx->xchg_counts[side], size_t(xs->G) * kMaxRanks * 4));
+  if (xs->pr.has_dict) {
+    HJ_TRY(ensure(ctx, ctx->keys_mat[side], std::max<size_t>(1, n) * sizeof(K)));
+    HJ_TRY(ensure(ctx, ctx->valid_mask[side], std::max<size_t>(1, xs->pr.mask_words) * 4));
+  }
+  XchgArgs a = xchg_args<K>(ctx, *xs, side);
+  HJ_CUDA(ctx, cudaMemsetAsync(a.counts, 0, size_t(xs->G) * kMaxRanks * 4, st));
+  if (xs->pr.meta.n_tiles) {
+    k_xchg_count<K, kXchgThreads, xchg_items<K>()><<<xs->G, kXchgThreads, 0, st>>>(a);
+    HJ_LAUNCH_CHECK(ctx, "k_xchg_count");
+    ++*n_launch;
+  }
+  k_xchg_offsets<256><<<1, 256, 0, st>>>(a.counts, a.send_cnt, ctx->n_ranks, xs->G);
+  HJ_LAUNCH_CHECK(ctx, "k_xchg_offsets");
+  ++*n_launch;
+  return HJ_OK;
+}
+
+}  // namespace
+
+namespace {
+
+// The whole sharded join for hashed key type K (agreed on by all ranks).
+template <typename K>
+int run_join_sharded(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, int mode, cudaStream_t st,
+                     hj_result_info* info) {
+  NcclApi* nc = nccl_api();
+  ncclComm_t comm = static_cast<ncclComm_t>(ctx->nccl_comm);
+  const uint32_t R = ctx->n_ranks, me = ctx->rank;
+  const bool outer = mode == HJ_MODE_LEFT || mode == HJ_MODE_RIGHT;
+  const int probe_null_policy = !outer ? kNullDrop : ((ctx->opts.flags & HJ_FLAG_SQL_NULL_PROBE) ? kNullRoute : kNullAsValue);
+  uint32_t n_launch = 0;
+  cudaEvent_t* ev = ctx->ev;
+  HJ_CUDA(ctx, cudaEventRecord(ev[9], st));
+
+  // ---- X1/X2 for both relations, then one all-gather of the 2 x R send counts
+  XchgSide xs[2];
+  xs[0].null_policy = kNullDrop;
+  xs[1].null_policy = probe_null_policy;
+  xs[1].send_nulls = probe_null_policy == kNullRoute;
+  HJ_TRY(ensure(ctx, ctx->xchg_cnt_dev, size_t(2) * kMaxRanks * 8 * (1 + kMaxRanks)));
+  auto* cnt_dev = static_cast<unsigned long long*>(ctx->xchg_cnt_dev.p);       // [2][kMaxRanks] mine
+  auto* mat_dev = cnt_dev + 2 * kMaxRanks;                                     // [R][2][kMaxRanks] everybody's
+  HJ_CUDA(ctx, cudaMemsetAsync(cnt_dev, 0, size_t(2) * kMaxRanks * 8, st));
+  HJ_TRY(xchg_count<K>(ctx, build, 0, &xs[0], st, &n_launch));
+  HJ_TRY(xchg_count<K>(ctx, probe, 1, &xs[1], st, &n_launch));
+  HJ_NCCL(ctx, nc->AllGather(cnt_dev, mat_dev, 2 * kMaxRanks, ncclUint64, comm, st));
+  auto* mat = reinterpret_cast<unsigned long long*>(static_cast<char*>(ctx->pinned) + 4096);
+  HJ_CUDA(ctx, cudaMemcpyAsync(mat, mat_dev, size_t(R) * 2 * kMaxRanks * 8, cudaMemcpyDeviceToHost, st));
+  HJ_CUDA(ctx, cudaStreamSynchronize(st));
+  auto cnt = [&](uint32_t src, int side, uint32_t dst) { return mat[(size_t(src) * 2 + side) * kMaxRanks + dst]; };
+
+  // ---- X3 + all-to-all per relation
+  uint64_t n_recv[2] = {0, 0};
+  for (int side = 0; side < 2; ++side) {
+    uint64_t send_off[kMaxRanks + 1] = {0}, recv_off[kMaxRanks + 1] = {0};
+    for (uint32_t p = 0; p < R; ++p) {
+      send_off[p + 1] = send_off[p] + cnt(me, side, p);
+      recv_off[p + 1] = recv_off[p] + cnt(p, side, me);
+    }
+    const uint64_t n_send = send_off[R];
+    n_recv[side] = recv_off[R];
+    if (n_recv[side] >= 0xFFFFFFFFull)
+      return fail(ctx, HJ_ERR_TOO_LARGE, "rank %u would receive %llu %s rows (limit 2^32-2 per GPU)", me,
+                  (unsigned long long)n_recv[side], side ? "probe" : "build");
+    const bool nulls = xs[side].send_nulls;
+    HJ_TRY(ensure(ctx, ctx->xchg_send_keys[side], std::max<uint64_t>(1, n_send) * sizeof(K)));
+    HJ_TRY(ensure(ctx, ctx->xchg_send_rids[side], std::max<uint64_t>(1, n_send) * 8));
+    HJ_TRY(ensure(ctx, ctx->xchg_recv_keys[side], std::max<uint64_t>(1, n_recv[side]) * sizeof(K)));
+    HJ_TRY(ensure(ctx, ctx->xchg_recv_rids[side], std::max<uint64_t>(1, n_recv[side]) * 8));
+    if (nulls) {
+      HJ_TRY(ensure(ctx, ctx->xchg_send_nulls[side], std::max<uint64_t>(1, n_send)));
+      HJ_TRY(ensure(ctx, ctx->xchg_recv_nulls[side], std::max<uint64_t>(1, n_recv[side])));
+    }
+    if (xs[side].pr.meta.n_tiles) {
+      XchgArgs a = xchg_args<K>(ctx, xs[side], side);
+      auto k = k_xchg_scatter<K, kXchgThreads, xchg_items<K>()>;
+      const size_t smem = size_t(xchg_tile<K>()) * (sizeof(K) + 8 + 2);
+      HJ_TRY(set_smem(ctx, k, smem));
+      k<<<xs[side].G, kXchgThreads, smem, st>>>(a);
+      HJ_LAUNCH_CHECK(ctx, "k_xchg_scatter");
+      ++n_launch;
+    }
+    if (side == 0) HJ_CUDA(ctx, cudaEventRecord(ev[10], st));  // (build partitioned; probe partition overlaps nothing yet)
+    char* sk = static_cast<char*>(ctx->xchg_send_keys[side].p);
+    char* sr = static_cast<char*>(ctx->xchg_send_rids[side].p);
+    char* sn = static_cast<char*>(ctx->xchg_send_nulls[side].p);
+    char* rk = static_cast<char*>(ctx->xchg_recv_keys[side].p);
+    char* rr = static_cast<char*>(ctx->xchg_recv_rids[side].p);
+    char* rn = static_cast<char*>(ctx->xchg_recv_nulls[side].p);
+    // own share: device-to-device copy; everything else: one grouped send/recv (= all-to-all-v)
+    {
+      const uint64_t c = cnt(me, side, me);
+      if (c) {
+        HJ_CUDA(ctx, cudaMemcpyAsync(rk + recv_off[me] * sizeof(K), sk + send_off[me] * sizeof(K), c * sizeof(K), cudaMemcpyDeviceToDevice, st));
+        HJ_CUDA(ctx, cudaMemcpyAsync(rr + recv_off[me] * 8, sr + send_off[me] * 8, c * 8, cudaMemcpyDeviceToDevice, st));
+        if (nulls) HJ_CUDA(ctx, cudaMemcpyAsync(rn + recv_off[me], sn + send_off[me], c, cudaMemcpyDeviceToDevice, st));
+      }
+    }
+    HJ_NCCL(ctx, nc->GroupStart());
+    for (uint32_t p = 0; p < R; ++p) {
+      if (p == me) continue;
+      const uint64_t cs = cnt(me, side, p), cr = cnt(p, side, me);
+      if (cs) {
+        HJ_NCCL(ctx, nc->Send(sk + send_off[p] * sizeof(K), cs * sizeof(K), ncclUint8, (int)p, comm, st));
+        HJ_NCCL(ctx, nc->Send(sr + send_off[p] * 8, cs * 8, ncclUint8, (int)p, comm, st));
+        if (nulls) HJ_NCCL(ctx, nc->Send(sn + send_off[p], cs, ncclUint8, (int)p, comm, st));
+      }
+      if (cr) {
+        HJ_NCCL(ctx, nc->Recv(rk + recv_off[p] * sizeof(K), cr * sizeof(K), ncclUint8, (int)p, comm, st));
+        HJ_NCCL(ctx, nc->Recv(rr + recv_off[p] * 8, cr * 8, ncclUint8, (int)p, comm, st));
+        if (nulls) HJ_NCCL(ctx, nc->Recv(rn + recv_off[p], cr, ncclUint8, (int)p, comm, st));
+      }
+    }
+    HJ_NCCL(ctx, nc->GroupEnd());
+    ctx->xchg_bytes_sent[side] = (n_send - cnt(me, side, me)) * (sizeof(K) + 8 + (nulls ? 1 : 0));
+  }
+  HJ_CUDA(ctx, cudaEventRecord(ev[11], st));
+
+  // ---- local join over what arrived: one device-resident VALUE segment per relation whose RowIDs come from the exchange
+  hj_segment seg[2];
+  hj_relation rel[2];
+  for (int side = 0; side < 2; ++side) {
+    std::memset(&seg[side], 0, sizeof(hj_segment));
+    seg[side].chunk_id = 0;
+    seg[side].n_rows = static_cast<uint32_t>(n_recv[side]);
+    seg[side].kind = HJ_SEG_VALUE;
+    seg[side].key_type = sizeof(K) == 8 ? HJ_KEY_INT64 : HJ_KEY_INT32;
+    seg[side].values = ctx->xchg_recv_keys[side].p;
+    seg[side].nulls = xs[side].send_nulls ? static_cast<const uint8_t*>(ctx->xchg_recv_nulls[side].p) : nullptr;
+    rel[side].segs = &seg[side];
+    rel[side].n_segs = 1;
+    rel[side].location = HJ_LOC_DEVICE;
+    rel[side].n_rows = n_recv[side];
+    ctx->xchg_rowids[side] = static_cast<const uint64_t*>(ctx->xchg_recv_rids[side].p);
+  }
+  const int st_join = run_join<K>(ctx, &rel[0], &rel[1], mode, st, info);
+  ctx->xchg_rowids[0] = ctx->xchg_rowids[1] = nullptr;
+  HJ_TRY(st_join);
+  hj_timings& t = ctx->timings;
+  t.ms[HJ_PH_XCHG_PARTITION] = ev_ms(ev[9], ev[10]);   // shard prepare + X1/X2 (both) + build X3
+  t.ms[HJ_PH_XCHG_TRANSFER] = ev_ms(ev[10], ev[11]);   // build all-to-all, probe X3, probe all-to-all
+  t.ms[HJ_PH_TOTAL] += ev_ms(ev[9], ev[11]);
+  t.n_kernel_launches += n_launch;
+  t.bytes_nvlink_sent = ctx->xchg_bytes_sent[0] + ctx->xchg_bytes_sent[1];
+  return HJ_OK;
+}
+
+}  // namespace
 
 extern "C" {
 
+uint32_t hj_exchange_rank_of(int64_t key, int key_type, uint32_t n_ranks) {
+  if (n_ranks == 0) return 0;
+  const uint32_t h = key_type == HJ_KEY_INT64 ? hash_key(static_cast<int64_t>(key)) : hash_key(static_cast<int32_t>(key));
+  return dest_rank_of_hash(h, n_ranks);
+}
+
 int hj_comm_unique_id(uint8_t id[HJ_NCCL_UNIQUE_ID_BYTES]) {
-  (void)id;
-  return HJ_ERR_COMM;
+  NcclApi* nc = nccl_api();
+  if (!nc->handle) return fail(nullptr, HJ_ERR_COMM, "%s", nc->error.c_str());
+  ncclUniqueId uid;
+  if (nc->GetUniqueId(&uid) != ncclSuccess) return fail(nullptr, HJ_ERR_COMM, "ncclGetUniqueId failed");
+  std::memcpy(id, &uid, HJ_NCCL_UNIQUE_ID_BYTES);
+  return HJ_OK;
 }
 
 int hj_comm_init(hj_ctx* ctx, const uint8_t id[HJ_NCCL_UNIQUE_ID_BYTES], int n_ranks, int rank) {
-  (void)id; (void)n_ranks; (void)rank;
-  return fail(ctx, HJ_ERR_COMM, "multi-GPU exchange not built yet");
+  if (!ctx) return HJ_ERR_INVALID;
+  if (n_ranks < 1 || n_ranks > kMaxRanks || rank < 0 || rank >= n_ranks)
+    return fail(ctx, HJ_ERR_INVALID, "hj_comm_init: rank %d of %d (1..%d ranks supported)", rank, n_ranks, kMaxRanks);
+  HJ_TRY(check_ctx(ctx));
+  NcclApi* nc = nccl_api();
+  if (!nc->handle) return fail(ctx, HJ_ERR_COMM, "%s", nc->error.c_str());
+  if (ctx->nccl_comm) {
+    nc->CommDestroy(static_cast<ncclComm_t>(ctx->nccl_comm));
+    ctx->nccl_comm = nullptr;
+  }
+  ncclUniqueId uid;
+  std::memcpy(&uid, id, HJ_NCCL_UNIQUE_ID_BYTES);
+  ncclComm_t comm = nullptr;
+  HJ_NCCL(ctx, nc->CommInitRank(&comm, n_ranks, uid, rank));
+  ctx->nccl_comm = comm;
+  ctx->n_ranks = n_ranks;
+  ctx->rank = rank;
+  return HJ_OK;
 }
 
 int hj_join_sharded(hj_ctx* ctx, const hj_relation* build_shard, const hj_relation* probe_shard, int mode,
                     void* cuda_stream, hj_result_info* out_info) {
-  (void)build_shard; (void)probe_shard; (void)mode; (void)cuda_stream; (void)out_info;
-  return fail(ctx, HJ_ERR_COMM, "multi-GPU exchange not built yet");
+  if (!ctx) return HJ_ERR_INVALID;
+  ctx->has_result = false;
+  if (!out_info) return fail(ctx, HJ_ERR_INVALID, "out_info is NULL");
+  std::memset(out_info, 0, sizeof(*out_info));
+  if (!(mode == HJ_MODE_INNER || mode == HJ_MODE_LEFT || mode == HJ_MODE_RIGHT || mode == HJ_MODE_SEMI || mode == HJ_MODE_ANTI))
+    return fail(ctx, HJ_ERR_INVALID, "JoinMode %d is not supported by JoinHash (Inner/Left/Right/Semi/Anti only)", mode);
+  if (!ctx->nccl_comm) return fail(ctx, HJ_ERR_COMM, "hj_join_sharded without hj_comm_init");
+  HJ_TRY(validate_relation(ctx, build_shard, "build"));
+  HJ_TRY(validate_relation(ctx, probe_shard, "probe"));
+  HJ_TRY(check_ctx(ctx));
+  cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
+  // the hashed key type must be the same on every rank (the destination of a key depends on it): all-gather "I hold int64"
+  unsigned long long wide = 0;
+  for (const hj_relation* r : {build_shard, probe_shard})
+    for (uint32_t i = 0; i < r->n_segs; ++i) wide |= r->segs[i].key_type == HJ_KEY_INT64 ? 1ull : 0ull;
+  HJ_TRY(ensure(ctx, ctx->xchg_cnt_dev, size_t(2) * kMaxRanks * 8 * (1 + kMaxRanks)));
+  auto* dev = static_cast<unsigned long long*>(ctx->xchg_cnt_dev.p);
+  auto* host = reinterpret_cast<unsigned long long*>(static_cast<char*>(ctx->pinned) + 4096);
+  NcclApi* nc = nccl_api();
+  HJ_CUDA(ctx, cudaMemcpyAsync(dev, &wide, 8, cudaMemcpyHostToDevice, st));
+  HJ_NCCL(ctx, nc->AllGather(dev, dev + kMaxRanks, 1, ncclUint64, static_cast<ncclComm_t>(ctx->nccl_comm), st));
+  HJ_CUDA(ctx, cudaMemcpyAsync(host, dev + kMaxRanks, size_t(ctx->n_ranks) * 8, cudaMemcpyDeviceToHost, st));
+  HJ_CUDA(ctx, cudaStreamSynchronize(st));
+  for (int r = 0; r < ctx->n_ranks; ++r) wide |= host[r];
+  return wide ? run_join_sharded<int64_t>(ctx, build_shard, probe_shard, mode, st, out_info)
+              : run_join_sharded<int32_t>(ctx, build_shard, probe_shard, mode, st, out_info);
 }
 
 }  // extern "C"
+
+extern "C" void hj_comm_release(hj_ctx* ctx) {
+  if (ctx && ctx->nccl_comm) {
+    nccl_api()->CommDestroy(static_cast<ncclComm_t>(ctx->nccl_comm));
+    ctx->nccl_comm = nullptr;
+    ctx->n_ranks = 1;
+    ctx->rank = 0;
+  }
+}

@@ -22,6 +22,10 @@ enum NullPolicy : int {
   kNullRoute = 2    // probe side of Left/Right with HJ_FLAG_SQL_NULL_PROBE: routed to a side list, emitted unmatched
 };
 
+// Internal segment kind (after hj_segment_kind 0..2): tuples received from the multi-GPU exchange. `values` = keys,
+// `nulls` = optional flags, `attr` = the rows' packed global RowIDs (uint64), which replace the position -> RowID mapping.
+constexpr uint8_t kSegExchanged = 3;
+
 // One chunk's key column on the device. 64 bytes.
 struct DevSegment {
   const void* values;           // VALUE/GATHERED: T[n_rows]; DICT: dictionary
@@ -87,7 +91,7 @@ __device__ __forceinline__ Tuple<int64_t> ld_stream(const Tuple<int64_t>* p) {
 // The reference partitions on MurmurHash2(seed 17) (join_hash.cpp:254); the result multiset does not depend on the hash,
 // so the device uses the cheaper murmur3 finaliser. Low `radix_bits` bits select the partition, the bits above them
 // the hash-table slot, so the two are independent.
-__device__ __forceinline__ uint32_t fmix32(uint32_t h) {
+__host__ __device__ __forceinline__ uint32_t fmix32(uint32_t h) {
   h ^= h >> 16;
   h *= 0x85ebca6bu;
   h ^= h >> 13;
@@ -95,10 +99,17 @@ __device__ __forceinline__ uint32_t fmix32(uint32_t h) {
   h ^= h >> 16;
   return h;
 }
-__device__ __forceinline__ uint32_t hash_key(int32_t k) { return fmix32(static_cast<uint32_t>(k)); }
-__device__ __forceinline__ uint32_t hash_key(int64_t k) {
+__host__ __device__ __forceinline__ uint32_t hash_key(int32_t k) { return fmix32(static_cast<uint32_t>(k)); }
+__host__ __device__ __forceinline__ uint32_t hash_key(int64_t k) {
   const uint32_t lo = static_cast<uint32_t>(k), hi = static_cast<uint32_t>(static_cast<uint64_t>(k) >> 32);
   return fmix32(lo ^ fmix32(hi + 0x9e3779b9u));
+}
+
+// Multi-GPU exchange: the rank that joins a key. Derived from a second mix of the key hash so that it is independent of
+// both the local partition (low radix bits) and the hash-table slot (the bits above them); mulhi maps it to [0, n_ranks).
+__host__ __device__ __forceinline__ uint32_t dest_rank_of_hash(uint32_t h, uint32_t n_ranks) {
+  const uint32_t g = fmix32(h ^ 0x9e3779b9u);
+  return static_cast<uint32_t>((static_cast<uint64_t>(g) * n_ranks) >> 32);
 }
 
 // ---------------------------------------------------------------------------------------------------------- RowID
@@ -126,6 +137,7 @@ __device__ __forceinline__ uint64_t make_rowid(const RelMeta& m, uint32_t idx) {
   }
   if (m.identity) return pack_rowid(seg, off);
   const DevSegment* s = m.segs + seg;
+  if (s->kind == kSegExchanged) return __ldg(static_cast<const uint64_t*>(s->attr) + off);
   const uint32_t* ro = s->row_offsets;
   return pack_rowid(s->chunk_id, ro ? __ldg(ro + off) : off);
 }

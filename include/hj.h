@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define HJ_ABI_VERSION 1
+#define HJ_ABI_VERSION 2
 
 /* ---- ABI constants mirrored from the reference ------------------------------------------- */
 
@@ -137,7 +137,7 @@ typedef struct hj_result_info {
   uint32_t reserved;
 } hj_result_info;
 
-#define HJ_N_PHASES 8
+#define HJ_N_PHASES 10
 /* phase indices of hj_timings.ms[] */
 enum hj_phase {
   HJ_PH_H2D = 0,          /* staging host-resident segments                                 */
@@ -147,7 +147,9 @@ enum hj_phase {
   HJ_PH_BUILD_PROBE = 4,  /* shared-memory build + probe + emit                             */
   HJ_PH_FINALIZE = 5,     /* overflow-partition fix-up, NULL-probe emission                 */
   HJ_PH_D2H = 6,          /* hj_fetch copies                                                */
-  HJ_PH_TOTAL = 7         /* whole hj_join, device side                                     */
+  HJ_PH_TOTAL = 7,        /* whole hj_join / hj_join_sharded, device side                   */
+  HJ_PH_XCHG_PARTITION = 8, /* hj_join_sharded: split by destination rank (count + scatter)  */
+  HJ_PH_XCHG_TRANSFER = 9   /* hj_join_sharded: all-to-all over NVLink                        */
 };
 typedef struct hj_timings {
   float ms[HJ_N_PHASES];
@@ -155,6 +157,7 @@ typedef struct hj_timings {
   uint64_t bytes_d2h;
   uint32_t n_kernel_launches; /* kernels of this library launched by the last hj_join       */
   uint32_t reserved;
+  uint64_t bytes_nvlink_sent; /* hj_join_sharded: bytes this rank sent to its peers         */
 } hj_timings;
 
 /* ---- status codes -------------------------------------------------------------------------- */
@@ -226,6 +229,10 @@ int hj_release_scratch(hj_ctx* ctx);
 /* The exchange has no reference counterpart: both relations are split by the high bits of the
  * key hash so that every key's rows meet on one rank, exchanged with an NCCL all-to-all over
  * NVLink, and joined locally. RowIDs stay global, so per-rank results simply concatenate. */
+
+/* The rank (0..n_ranks-1) on which all rows with this key meet. Pure host arithmetic; the same function runs on the
+ * device. `key_type` is the HASHED key type of the join (HJ_KEY_INT64 if either column is int64). */
+uint32_t hj_exchange_rank_of(int64_t key, int key_type, uint32_t n_ranks);
 
 #define HJ_NCCL_UNIQUE_ID_BYTES 128
 /* Rank 0 calls this and broadcasts the 128 bytes to the other ranks out of band. */
