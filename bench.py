@@ -43,38 +43,50 @@ def log(*a):
 
 
 # ------------------------------------------------------------------------------------------------------------ data
-def gen_device_workload(name, scale, device, seed):
-    """Builds the workload's key columns on `device` with torch. Returns dict with per-relation lists of
-    (chunk_id, dictionary|values tensor, attr tensor|None) and row counts."""
+def gen_device_workload(name, scale, device, seed, rank=0, world=1):
+    """Builds this rank's shard of the workload's key columns on `device` with torch: `scale` x the published row counts
+    PER RANK (weak scaling), keys drawn from the GLOBAL domain of world x n_build, chunk ids global. Returns dict with
+    per-relation lists of (chunk_id, dictionary|values tensor, attr tensor|None) and row counts."""
+    import math
     import torch
     n_build, n_probe, dtype, encoding, _ = WORKLOADS[name]
     n_build, n_probe = max(1, int(n_build * scale)), max(1, int(n_probe * scale))
     tdt = torch.int32 if dtype == "int32" else torch.int64
     g = torch.Generator(device=device)
     g.manual_seed(seed)
-    domain = n_build
+    domain = n_build * world
     if name == "c3":
         # Zipf(1.0) ranks by inverse CDF of the continuous approximation, scrambled by a fixed odd multiplier
         u = torch.rand(n_build, device=device, generator=g, dtype=torch.float64)
         ranks = torch.exp(u * np.log(domain + 1.0)).floor().clamp_(1, domain).to(torch.int64)
         build_keys = ((ranks * 0x9E3779B1) % domain + 1).to(tdt)
         del u, ranks
-    else:
+    elif world == 1:
         build_keys = (torch.randperm(domain, device=device, generator=g) + 1).to(tdt)  # unique: 1:N join
+    else:
+        # this rank's slice of ONE global permutation of 1..domain: x -> (x * A) mod domain with gcd(A, domain) = 1
+        a = 2654435761 % domain or 1
+        while math.gcd(a, domain) != 1:
+            a += 1
+        x = torch.arange(rank * n_build, (rank + 1) * n_build, device=device, dtype=torch.int64)
+        build_keys = ((x * a) % domain + 1).to(tdt)
+        del x
 
     def chunks_of(keys_fn, n):
         out = []
+        n_chunks = (n + CHUNK - 1) // CHUNK
         for c, start in enumerate(range(0, n, CHUNK)):
             k = keys_fn(start, min(CHUNK, n - start))
+            cid = rank * n_chunks + c
             if encoding == "dict":
                 d, inv = torch.unique(k, sorted=True, return_inverse=True)
                 # FixedSizeByteAligned width rule (fixed_size_byte_aligned_compressor.cpp:21-30); C2's 1 Mi-row chunks
                 # hold ~1 M distinct keys -> 4-byte attribute vectors
                 m = len(d) + 1
                 adt = torch.uint8 if m <= 0xFF else (torch.int16 if m <= 0xFFFF else torch.int32)
-                out.append((c, d.contiguous(), inv.to(adt).contiguous()))
+                out.append((cid, d.contiguous(), inv.to(adt).contiguous()))
             else:
-                out.append((c, k.contiguous(), None))
+                out.append((cid, k.contiguous(), None))
         return out
 
     build = chunks_of(lambda s, m: build_keys[s:s + m], n_build)
@@ -189,7 +201,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--scale", type=float, default=1.0, help="fraction of the workload's row counts (1.0 = as published)")
-    ap.add_argument("--cpu-scale", type=float, default=0.01, help="fraction of the workload the CPU baseline runs")
+    ap.add_argument("--cpu-scale", type=float, default=0.05, help="fraction of the workload the CPU baseline runs")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
@@ -230,10 +242,9 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- workload: at N > 1 every rank holds 1/N of both relations (strong partitioning of the same global join)
+    # ---- workload: weak scaling — every rank holds `scale` x C2 rows of ONE global join (global key domain and chunk ids)
     t0 = time.time()
-    shard_scale = args.scale / world
-    data = gen_device_workload(args.workload, shard_scale, dev, seed=0xB200 + 2 + 1000 * rank)
+    data = gen_device_workload(args.workload, args.scale, dev, seed=0xB200 + 2 + 1000 * rank, rank=rank, world=world)
     nb, npr = data["n_build"], data["n_probe"]
     build_dev = relation_from_chunks(hj, data["build"], abi.LOC_DEVICE)
     probe_dev = relation_from_chunks(hj, data["probe"], abi.LOC_DEVICE)
@@ -242,26 +253,37 @@ def main():
         f"{(input_bytes(data['build']) + input_bytes(data['probe'])) / 1e9:.2f} GB")
 
     j = hj.HashJoin(device=local_rank, flags=abi.FLAG_TIMINGS)
+    if world > 1:
+        uid = [hj.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        j.comm_init(uid[0], world, rank)
+    # the library's kernels are launched on torch's current stream so that torch.cuda.Event brackets them
+    stream = torch.cuda.current_stream().cuda_stream
 
     def step():
-        return j.join(build_dev, probe_dev, abi.MODE_INNER)
+        if world > 1:
+            return j.join_sharded(build_dev, probe_dev, abi.MODE_INNER, stream=stream)
+        return j.join(build_dev, probe_dev, abi.MODE_INNER, stream=stream)
 
-    for _ in range(max(3, args.warmup)):
+    W = max(3, args.warmup)
+    for _ in range(W):
         info = step()
     barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
     phase_ms, launches = [], 0
-    t_start = time.perf_counter()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
     for _ in range(args.steps):
         info = step()
         tm = j.timings()
         phase_ms.append(tm)
         launches += tm["n_kernel_launches"]
+    ev1.record()
     barrier()
-    elapsed = time.perf_counter() - t_start
+    elapsed = ev0.elapsed_time(ev1) * 1e-3  # device time of exactly K steps, CUDA events on the launching stream
     clocks = sampler.stop()
-    dev_ms = float(np.mean([t["total"] for t in phase_ms]))  # CUDA events on the library's stream
+    dev_ms = float(np.mean([t["total"] for t in phase_ms]))  # the library's own CUDA events
     if world > 1:
         tt = torch.tensor([elapsed], device=dev, dtype=torch.float64)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
@@ -274,26 +296,47 @@ def main():
     ms_per_step = elapsed / args.steps * 1e3
     value = total_tuples / (elapsed / args.steps)
 
-    # ---- roofline of the dominant kernel (k_build_probe), live CUDA-event time of its phase
+    # ---- roofline of the dominant kernel (the phase with the largest live CUDA-event time), DESIGN.md §5:
+    # algorithmic bytes of a phase = the bytes that phase must move in the SURVEY §8d model, for this rank's rows
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(peaks_path):
         with open(peaks_path) as f:
-            peak, peak_src = json.load(f)["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)"
+            peak, peak_src = json.load(f)["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs, burst)"
     else:
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
     k = 4 if dtype == "int32" else 8
     t_bytes = k + 8
     w_in = {"dict": 4 + 4, "value": k}[encoding]  # attr + amortised dictionary bytes per row for 1 Mi-row chunks
-    bp_ms = float(np.mean([t["build_probe"] for t in phase_ms]))
-    bp_bytes = (nb + npr) * t_bytes + info.n_rows * 16  # read the partitioned tuple once + 16 B per result
+    mean_ms = {p_: float(np.mean([t[p_] for t in phase_ms])) for p_ in abi.PHASES}
+    n_local = info.n_build_tuples + info.n_probe_tuples  # rows this rank partitions and joins (after the exchange)
+    phase_bytes = {"materialize": n_local * w_in, "scatter1": n_local * (w_in + t_bytes), "scatter2": n_local * 2 * t_bytes,
+                   "build_probe": n_local * t_bytes + info.n_rows * 16}
+    phase_kernel = {"materialize": "k_materialize_hist", "scatter1": "k_scatter1", "scatter2": "k_scatter2",
+                    "build_probe": "k_build_probe"}
+    dom = max(phase_bytes, key=lambda p_: mean_ms[p_])
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic_c2_full.json")  # dram bytes per launch from the committed ncu capture
+    if os.path.exists(tpath) and args.workload == "c2" and args.scale == 1.0 and world == 1:
+        with open(tpath) as f:
+            traffic = json.load(f).get(phase_kernel[dom])
     whole_bytes = (nb + npr) * (2 * w_in + 2 * t_bytes) + info.n_rows * 16
-    roofline = {"bound": "hbm", "kernel": "k_build_probe", "achieved": bp_bytes / (bp_ms * 1e-3) / 1e9 if bp_ms else None,
-                "peak": peak, "unit": "GB/s", "frac": (bp_bytes / (bp_ms * 1e-3) / 1e9 / peak) if bp_ms else None,
-                "traffic": None, "peak_source": peak_src, "kernel_ms": bp_ms,
+    ach = phase_bytes[dom] / (mean_ms[dom] * 1e-3) / 1e9 if mean_ms[dom] else None
+    roofline = {"bound": "hbm", "kernel": phase_kernel[dom], "achieved": ach, "peak": peak, "unit": "GB/s",
+                "frac": ach / peak if ach else None, "traffic": traffic, "peak_source": peak_src, "kernel_ms": mean_ms[dom],
+                "algorithmic_bytes_per_launch_set": phase_bytes[dom],
+                "per_phase": {p_: {"ms": mean_ms[p_], "algorithmic_bytes": phase_bytes[p_],
+                                   "frac": phase_bytes[p_] / (mean_ms[p_] * 1e-3) / 1e9 / peak if mean_ms[p_] else None}
+                              for p_ in phase_bytes},
                 "whole_join": {"algorithmic_bytes": whole_bytes, "achieved": whole_bytes / (dev_ms * 1e-3) / 1e9,
                                "frac": whole_bytes / (dev_ms * 1e-3) / 1e9 / peak, "frac_of_nominal_8TBs":
                                whole_bytes / (dev_ms * 1e-3) / 1e9 / 8000.0, "device_ms": dev_ms},
-                "phase_ms": {p: float(np.mean([t[p] for t in phase_ms])) for p in abi.PHASES}}
+                "phase_ms": mean_ms}
+    if world > 1:
+        sent = float(np.mean([t["bytes_nvlink_sent"] for t in phase_ms]))
+        xms = mean_ms["xchg_transfer"]
+        roofline["nvlink"] = {"bytes_sent_per_rank": sent, "transfer_ms": xms, "achieved": sent / (xms * 1e-3) / 1e9 if xms else None,
+                              "peak": 900.0, "unit": "GB/s per direction",
+                              "note": "transfer_ms also contains the probe side's destination scatter kernel"}
 
     # ---- e2e: same join through the C ABI from pinned host buffers, PosLists fetched to pinned host memory
     e2e = None
@@ -301,12 +344,16 @@ def main():
         hb, hp = to_pinned_host(data["build"]), to_pinned_host(data["probe"])
         build_host = relation_from_chunks(hj, [(c, a.numpy(), None if b is None else b.numpy()) for c, a, b in hb], abi.LOC_HOST)
         probe_host = relation_from_chunks(hj, [(c, a.numpy(), None if b is None else b.numpy()) for c, a, b in hp], abi.LOC_HOST)
-        out_b = torch.empty((max(info.n_rows, 1), 2), dtype=torch.int32, pin_memory=True).numpy().view(np.uint32)
-        out_p = torch.empty((max(info.n_rows, 1), 2), dtype=torch.int32, pin_memory=True).numpy().view(np.uint32)
+        out_rows = int(info.n_rows * 1.05) + 1024  # per-rank result sizes vary a little between exchanges of equal data
+        out_b = torch.empty((out_rows, 2), dtype=torch.int32, pin_memory=True).numpy().view(np.uint32)
+        out_p = torch.empty((out_rows, 2), dtype=torch.int32, pin_memory=True).numpy().view(np.uint32)
         h2d = input_bytes(hb) + input_bytes(hp)
 
         def e2e_step():
-            inf = j.join(build_host, probe_host, abi.MODE_INNER)
+            if world > 1:
+                inf = j.join_sharded(build_host, probe_host, abi.MODE_INNER, stream=stream)
+            else:
+                inf = j.join(build_host, probe_host, abi.MODE_INNER, stream=stream)
             j.fetch(out_b, out_p)
             return inf
         e2e_step()
@@ -331,9 +378,11 @@ def main():
 
     if rank == 0:
         line = {"metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps,
-                "warmup": max(3, args.warmup), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if world > 1 else "weak",
+                "warmup": W, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": dtype, "data": "synthetic",
-                "config": {"workload": desc, "scale": args.scale, "n_build": nb * world, "n_probe": npr * world,
+                "config": {"workload": desc + (f"; {world} ranks each hold that many rows of one global join (hash exchange over NCCL)"
+                                               if world > 1 else ""),
+                           "scale": args.scale, "n_build": nb * world, "n_probe": npr * world,
                            "chunk_rows": CHUNK, "mode": "Inner", "result_rows": total_results,
                            "radix_bits": info.radix_bits, "l2": "inputs larger than L2, no flush"},
                 "clocks": clocks, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e}

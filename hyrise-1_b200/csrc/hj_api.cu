@@ -434,9 +434,9 @@ float ev_ms(cudaEvent_t a, cudaEvent_t b) {
   return ms;
 }
 
-template <typename K, bool FAST, int CLS>
+template <typename K, int RM, int CLS>
 int launch_build_probe_cls(hj_ctx* ctx, const JoinArgs<K>& a, cudaStream_t st) {
-  auto k5 = k_build_probe<K, kJoinThreads, Cfg<K>::kNS, Cfg<K>::kCap, kProbeV, FAST, CLS>;
+  auto k5 = k_build_probe<K, kJoinThreads, Cfg<K>::kNS, Cfg<K>::kCap, kProbeV, RM, CLS>;
   const size_t smem5 = (size_t(Cfg<K>::kNS) + 1) * sizeof(K) + (size_t(Cfg<K>::kNS) + 2) * 4 + size_t(Cfg<K>::kCap) * 4;
   HJ_TRY(set_smem(ctx, k5, smem5));
   k5<<<ctx->n_sms, kJoinThreads, smem5, st>>>(a);
@@ -444,20 +444,20 @@ int launch_build_probe_cls(hj_ctx* ctx, const JoinArgs<K>& a, cudaStream_t st) {
   return HJ_OK;
 }
 
-template <typename K, bool FAST>
+template <typename K, int RM>
 int launch_build_probe(hj_ctx* ctx, const JoinArgs<K>& a, cudaStream_t st) {
   switch (a.mode) {
-    case HJ_MODE_INNER: return launch_build_probe_cls<K, FAST, kClsInner>(ctx, a, st);
+    case HJ_MODE_INNER: return launch_build_probe_cls<K, RM, kClsInner>(ctx, a, st);
     case HJ_MODE_LEFT:
-    case HJ_MODE_RIGHT: return launch_build_probe_cls<K, FAST, kClsOuter>(ctx, a, st);
-    case HJ_MODE_SEMI: return launch_build_probe_cls<K, FAST, kClsSemi>(ctx, a, st);
-    default: return launch_build_probe_cls<K, FAST, kClsAnti>(ctx, a, st);
+    case HJ_MODE_RIGHT: return launch_build_probe_cls<K, RM, kClsOuter>(ctx, a, st);
+    case HJ_MODE_SEMI: return launch_build_probe_cls<K, RM, kClsSemi>(ctx, a, st);
+    default: return launch_build_probe_cls<K, RM, kClsAnti>(ctx, a, st);
   }
 }
 
 template <typename K>
 int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, int mode, cudaStream_t st,
-             hj_result_info* info) {
+             hj_result_info* info, bool payload = false) {
   const bool one_side = mode == HJ_MODE_SEMI || mode == HJ_MODE_ANTI;
   const bool outer = mode == HJ_MODE_LEFT || mode == HJ_MODE_RIGHT;
   Launches nl;
@@ -540,6 +540,7 @@ int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, in
   a.matched = static_cast<uint32_t*>(ctx->matched.p);
   a.radix_bits = radix_bits;
   a.mode = mode;
+  a.payload = payload ? 1 : 0;
   const bool fast_rowid = pb.meta.uniform_shift >= 0 && pb.meta.identity && pp.meta.uniform_shift >= 0 && pp.meta.identity;
 
   auto* rb = static_cast<Readback*>(ctx->pinned);
@@ -559,7 +560,14 @@ int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, in
     HJ_CUDA(ctx, cudaMemsetAsync(ctx->queue.p, 0, 4, st));
     HJ_CUDA(ctx, cudaMemsetAsync(ctx->out_state.p, 0, sizeof(OutState), st));
     if (mode != HJ_MODE_INNER) HJ_CUDA(ctx, cudaMemsetAsync(ctx->matched.p, 0, matched_bytes, st));
-    if (fast_rowid) HJ_TRY((launch_build_probe<K, true>(ctx, a, st))); else HJ_TRY((launch_build_probe<K, false>(ctx, a, st)));
+    if (payload) {
+      if constexpr (sizeof(K) == 8) HJ_TRY((launch_build_probe<K, kRidPayload>(ctx, a, st)));
+      else return fail(ctx, HJ_ERR_INVALID, "RowID-carrying tuples need the int64 pipeline");
+    } else if (fast_rowid) {
+      HJ_TRY((launch_build_probe<K, kRidFast>(ctx, a, st)));
+    } else {
+      HJ_TRY((launch_build_probe<K, kRidGeneric>(ctx, a, st)));
+    }
     nl.n++;
     if (passes == 1) HJ_CUDA(ctx, cudaEventRecord(ev[5], st));
     if (mode != HJ_MODE_INNER) {

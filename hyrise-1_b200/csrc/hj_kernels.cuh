@@ -346,13 +346,23 @@ __global__ void __launch_bounds__(NT, 4) k_scatter1(const ScatterArgs<K> a) {
     }
     __syncthreads();
     const uint32_t idx0 = seg.row_begin + r0 + threadIdx.x;
+    // rows that arrived through the multi-GPU exchange carry their global RowID in the tuple (idx = ChunkID, pad =
+    // ChunkOffset) instead of a position: positions of received rows mean nothing to the RowID mapping
+    const uint64_t* rids = seg.kind == kSegExchanged ? static_cast<const uint64_t*>(seg.attr) + r0 + threadIdx.x : nullptr;
 #pragma unroll
     for (int j = 0; j < ITEMS; ++j) {
       if (packed[j] != kNoDigit) {
         Tuple<K> t;
         t.key = key[j];
         t.idx = idx0 + j * NT;
-        if constexpr (sizeof(K) == 8) t.pad = 0;
+        if constexpr (sizeof(K) == 8) {
+          t.pad = 0;
+          if (rids) {
+            const uint64_t r = __ldg(rids + j * NT);
+            t.idx = static_cast<uint32_t>(r);
+            t.pad = static_cast<uint32_t>(r >> 32);
+          }
+        }
         stage[s_loff[packed[j] >> 16] + (packed[j] & 0xFFFFu)] = t;
       }
     }
@@ -659,6 +669,7 @@ struct JoinArgs {
   int radix_bits;
   int mode;                            // hj_join_mode
   int chunk_shift;                     // result chunks are 2^chunk_shift rows
+  int payload;                         // 1: tuples carry their RowID (idx, pad) — local join of hj_join_sharded
 };
 
 template <typename K> struct KeyTraits;
@@ -701,11 +712,23 @@ __device__ __forceinline__ uint32_t table_find(const K* keys, uint32_t ns_mask, 
   }
 }
 
-// FAST_ROWID: both relations have power-of-two chunks and identity chunk ids, position -> RowID is shift/mask.
-template <bool FAST_ROWID>
+// How a tuple becomes a RowID when a result row is emitted:
+//   kRidGeneric  position -> RowID through the relation's chunk table (make_rowid)
+//   kRidFast     both relations have power-of-two chunks and identity chunk ids: shift/mask
+//   kRidPayload  the tuple carries the RowID itself (idx = ChunkID, pad = ChunkOffset); int64-key tuples only
+constexpr int kRidGeneric = 0, kRidFast = 1, kRidPayload = 2;
+template <int RM>
 __device__ __forceinline__ uint64_t rowid_of(const RelMeta& m, uint32_t idx) {
-  if (FAST_ROWID) return pack_rowid(idx >> m.uniform_shift, idx & ((1u << m.uniform_shift) - 1u));
+  if (RM == kRidFast) return pack_rowid(idx >> m.uniform_shift, idx & ((1u << m.uniform_shift) - 1u));
   return make_rowid(m, idx);
+}
+template <typename K>
+__device__ __forceinline__ uint32_t tuple_hi(const Tuple<K>& t) {
+  if constexpr (sizeof(K) == 8) return t.pad; else return 0u;
+}
+template <typename K>
+__device__ __forceinline__ uint64_t tuple_rowid(const RelMeta& m, const Tuple<K>& t, int payload) {
+  return payload ? pack_rowid(t.idx, tuple_hi(t)) : make_rowid(m, t.idx);
 }
 
 // Mode classes the probe loop is specialised for (compile time: no per-row mode branches).
@@ -714,10 +737,11 @@ constexpr int kClsInner = 0, kClsOuter = 1, kClsSemi = 2, kClsAnti = 3;
 // Writes the result rows of one probe tile. CONTIG: the tile's reserved range is one in-bounds contiguous piece of the
 // output arrays (the common case), so a row's position is ob/op + a 32-bit index; otherwise every row goes through
 // out_pos() and the capacity check (chunk boundary inside the tile, or the overflow pass that only counts).
-template <typename K, int V, int CLS, bool FAST_ROWID, bool CONTIG>
-__device__ __forceinline__ void emit_tile(const JoinArgs<K>& a, const uint32_t* s_grp, const uint32_t (&pw)[V],
-                                          const uint32_t (&pidx)[V], const uint32_t (&outc)[V], const uint32_t (&ex)[V],
-                                          uint32_t wbase, unsigned long long base0, unsigned long long base1, uint32_t first) {
+template <typename K, int V, int CLS, int RM, bool CONTIG>
+__device__ __forceinline__ void emit_tile(const JoinArgs<K>& a, const uint32_t* s_grp, const Tuple<K>* bchunk,
+                                          const uint32_t (&pw)[V], const uint32_t (&pidx)[V], const uint32_t (&ppad)[V],
+                                          const uint32_t (&outc)[V], const uint32_t (&ex)[V], uint32_t wbase,
+                                          unsigned long long base0, unsigned long long base1, uint32_t first) {
   constexpr bool one_side = CLS == kClsSemi || CLS == kClsAnti;
   constexpr uint32_t LIGHT = 4;  // matches per probe row expanded by the owning lane; more: by the whole warp
   uint64_t* ob = one_side ? nullptr : a.out_build + (CONTIG ? base0 : 0ull);
@@ -734,21 +758,33 @@ __device__ __forceinline__ void emit_tile(const JoinArgs<K>& a, const uint32_t* 
       }
     }
   };
+  // build-side RowID of grouped entry g: s_grp holds relation positions, or (payload mode) positions inside this build
+  // chunk, whose tuples (<= CAP x 16 B, read by every probe row of the partition) stay cache-resident
+  auto brid = [&](uint32_t g) -> uint64_t {
+    if (RM == kRidPayload) {
+      const Tuple<K> t = bchunk[s_grp[g]];
+      return pack_rowid(t.idx, tuple_hi(t));
+    }
+    return rowid_of<RM>(a.build_rel, s_grp[g]);
+  };
+  auto prid_of = [&](uint32_t idx, uint32_t pad) -> uint64_t {
+    return RM == kRidPayload ? pack_rowid(idx, pad) : rowid_of<RM>(a.probe_rel, idx);
+  };
   const uint32_t lane = lane_id();
   uint32_t heavy = 0;
 #pragma unroll
   for (int j = 0; j < V; ++j) {
     if (outc[j] == 0) continue;
     const uint32_t e = wbase + ex[j];
-    const uint64_t prid = rowid_of<FAST_ROWID>(a.probe_rel, pidx[j]);
+    const uint64_t prid = prid_of(pidx[j], ppad[j]);
     const uint32_t cnt = pw[j] & 0xFFFFu;
     if (one_side || cnt == 0) {
       put(e, kNullRowId, prid);  // Semi/Anti row, or an unmatched outer row (join_hash.cpp:432-435)
     } else if (cnt == 1) {
-      put(e, rowid_of<FAST_ROWID>(a.build_rel, s_grp[(pw[j] >> 16) - 1u]), prid);
+      put(e, brid((pw[j] >> 16) - 1u), prid);
     } else if (cnt <= LIGHT) {
       const uint32_t start = (pw[j] >> 16) - cnt;
-      for (uint32_t m = 0; m < cnt; ++m) put(e + m, rowid_of<FAST_ROWID>(a.build_rel, s_grp[start + m]), prid);
+      for (uint32_t m = 0; m < cnt; ++m) put(e + m, brid(start + m), prid);
     } else {
       heavy |= 1u << j;
     }
@@ -764,16 +800,16 @@ __device__ __forceinline__ void emit_tile(const JoinArgs<K>& a, const uint32_t* 
         const uint32_t w = __shfl_sync(0xffffffffu, pw[j], src);
         const uint32_t e = wbase + __shfl_sync(0xffffffffu, ex[j], src);
         const uint32_t pi = __shfl_sync(0xffffffffu, pidx[j], src);
+        const uint32_t pp = __shfl_sync(0xffffffffu, ppad[j], src);
         const uint32_t cnt = w & 0xFFFFu, start = (w >> 16) - cnt;
-        const uint64_t prid = rowid_of<FAST_ROWID>(a.probe_rel, pi);
-        for (uint32_t m = lane; m < cnt; m += 32)
-          put(static_cast<unsigned long long>(e) + m, rowid_of<FAST_ROWID>(a.build_rel, s_grp[start + m]), prid);
+        const uint64_t prid = prid_of(pi, pp);
+        for (uint32_t m = lane; m < cnt; m += 32) put(static_cast<unsigned long long>(e) + m, brid(start + m), prid);
       }
     }
   }
 }
 
-template <typename K, int NT, int NS, int CAP, int V, bool FAST_ROWID, int CLS>
+template <typename K, int NT, int NS, int CAP, int V, int RM, int CLS>
 __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K> a) {
   static_assert(CAP < NS && CAP <= 65535, "table must keep empty slots; run ends are 16 bit");
   constexpr uint32_t NW = NT / 32;
@@ -888,7 +924,7 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K> a) {
 #pragma unroll
       for (int u = 0; u < BU; ++u) {
         const uint32_t i = (r0 + u) * NT + threadIdx.x;
-        bi[u] = i < it.b_cnt ? build[i].idx : 0u;
+        bi[u] = RM == kRidPayload ? i : (i < it.b_cnt ? build[i].idx : 0u);
       }
 #pragma unroll
       for (int u = 0; u < BU; ++u) {
@@ -904,7 +940,7 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K> a) {
 
     // ---- probe: every warp walks its own rows (warp w: rows w*32V .. +32V of every NT*V-row stripe) without CTA barriers
     for (uint32_t base = warp * (32 * V); base < it.p_cnt; base += NT * V) {
-      uint32_t pw[V], pidx[V], outc[V], ex[V];
+      uint32_t pw[V], pidx[V], ppad[V], outc[V], ex[V];
       const uint32_t row0 = base + lane;
       bool any_multi = false;
 #pragma unroll
@@ -912,6 +948,7 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K> a) {
         const bool act = row0 + j * 32 < it.p_cnt;
         pw[j] = 0;
         pidx[j] = nxt[j].idx;
+        ppad[j] = RM == kRidPayload ? tuple_hi(nxt[j]) : 0u;
         if (act) {
           const K key = nxt[j].key;
           const uint32_t slot = table_find<K, NS>(s_keys, ns_mask, key, (hash_key(key) >> radix_bits) & ns_mask);
@@ -955,9 +992,9 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K> a) {
       if (running == 0) continue;  // warp-uniform
       warp_writer_reserve(&wr, a.out_state, running, chunk_shift);
       if (wr.first == 0xFFFFFFFFu && wr.base0 + running <= a.capacity)
-        emit_tile<K, V, CLS, FAST_ROWID, true>(a, s_grp, pw, pidx, outc, ex, 0u, wr.base0, wr.base1, wr.first);
+        emit_tile<K, V, CLS, RM, true>(a, s_grp, build, pw, pidx, ppad, outc, ex, 0u, wr.base0, wr.base1, wr.first);
       else
-        emit_tile<K, V, CLS, FAST_ROWID, false>(a, s_grp, pw, pidx, outc, ex, 0u, wr.base0, wr.base1, wr.first);
+        emit_tile<K, V, CLS, RM, false>(a, s_grp, build, pw, pidx, ppad, outc, ex, 0u, wr.base0, wr.base1, wr.first);
     }
   }
   if (lane == 0) out_writer_finish(&wr, a.out_state, a.out_tails);
@@ -1003,7 +1040,7 @@ __global__ void __launch_bounds__(NT) k_finalize_multi(const JoinArgs<K> a, cons
         const uint32_t pos = it.p_begin + i;
         const bool hit = (a.matched[pos >> 5] >> (pos & 31u)) & 1u;
         flag = (mode == 5) ? hit : !hit;  // Semi keeps matched rows; Left/Right/Anti the unmatched ones
-        if (flag) prid = make_rowid(a.probe_rel, a.probe[pos].idx);
+        if (flag) prid = tuple_rowid<K>(a.probe_rel, a.probe[pos], a.payload);
       }
       emit_flagged<NT>(flag, kNullRowId, prid, a.out_build, a.out_probe, a.capacity, &s_out, a.out_state, scratch, a.chunk_shift);
     }
@@ -1024,7 +1061,7 @@ __global__ void __launch_bounds__(NT) k_emit_null_probe(const JoinArgs<K> a, con
   for (uint32_t base = lo + blockIdx.x * NT; base < hi; base += gridDim.x * NT) {
     const uint32_t i = base + threadIdx.x;
     const bool flag = i < hi;
-    const uint64_t prid = flag ? make_rowid(a.probe_rel, pass1[i].idx) : 0;
+    const uint64_t prid = flag ? tuple_rowid<K>(a.probe_rel, pass1[i], a.payload) : 0;
     emit_flagged<NT>(flag, kNullRowId, prid, a.out_build, a.out_probe, a.capacity, &s_out, a.out_state, scratch, a.chunk_shift);
   }
   if (threadIdx.x == 0) out_writer_finish(&s_out, a.out_state, a.out_tails);
