@@ -1,0 +1,159 @@
+"""BASELINE.json's configs as GPU parity cases.
+
+C1/C3/C4 shapes run at sizes the oracle finishes in seconds and are compared bit-exactly (sorted multiset of RowID pairs);
+C2 and C3 additionally run at (or near) their published sizes, where the result is checked through size-independent
+properties computed independently with torch: exact row count, a checksum over the emitted RowIDs, and key equality of
+sampled result rows. Everything goes through the C ABI (`-m gpu`)."""
+import importlib
+import os
+import sys
+
+import numpy as np
+import pytest
+
+import oracle_binding as ob
+import workloads as wl
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+hj = importlib.import_module("hyrise-1_b200")
+abi = hj.abi
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def join():
+    j = hj.HashJoin(device=0)
+    yield j
+    j.close()
+
+
+def assert_same(j, build, probe, mode, what):
+    mode_id = abi.MODES[mode]
+    info = j.join(build, probe, mode_id)
+    b, p = j.fetch()
+    ob_b, ob_p, oinfo = ob.oracle_join(build, probe, mode_id, n_threads=os.cpu_count() or 1)
+    assert info.n_rows == oinfo["n_rows"], f"{what} {mode}: {info.n_rows} rows, oracle {oinfo['n_rows']}"
+    got, want = ob.canonical(b, p), ob.canonical(ob_b, ob_p)
+    assert np.array_equal(got, want), f"{what} {mode}: sorted result rows differ"
+    return info
+
+
+# ------------------------------------------------------------------------------------------------------------------ C1
+def dbgen_orderkeys(n_orders):
+    """o_orderkey as dbgen makes it: mk_sparse keeps the low 3 bits of the order index and spreads the rest so that 8 of
+    every 32 key values are used (third_party/tpch-dbgen/build.c:142-146, dss.h:144-145; SF1: 1.5 M orders, max 6 000 000)."""
+    i = np.arange(1, n_orders + 1, dtype=np.int64)
+    return (((i >> 3) << 5) | (i & 7)).astype(np.int32)
+
+
+@pytest.mark.parametrize("encoding", ["value", "dict"])
+def test_c1_tpch_sf1_lineitem_orders(join, encoding):
+    """C1: TPC-H SF1 lineitem x orders on l_orderkey = o_orderkey, Inner, int32, chunk size 100 000
+    (tpch_db_generator.cpp:219-236 shapes: 1.5 M unique sparse order keys, 1..7 lineitems per order)."""
+    rng = np.random.default_rng(0xB201)
+    okeys = dbgen_orderkeys(1_500_000)
+    lines = rng.integers(1, 8, size=len(okeys))
+    lkeys = np.repeat(okeys, lines)  # lineitem is generated order by order
+    build = wl.make_relation(okeys, 100_000, encoding)
+    probe = wl.make_relation(lkeys, 100_000, encoding)
+    info = assert_same(join, build, probe, "Inner", f"C1 {encoding}")
+    assert info.n_rows == len(lkeys)  # every lineitem has exactly one order
+
+
+# ------------------------------------------------------------------------------------------------------------------ C3
+@pytest.mark.parametrize("mode", ["Inner", "Left", "Semi", "Anti"])
+def test_c3_zipf_int64_scaled(join, mode):
+    """C3 shape at 1/100: Zipf(1.0)-skewed int64 build keys (hottest key ~5 % of the rows => build partitions far larger
+    than one shared-memory table, heavy duplicate expansion), uniform probe."""
+    rng = np.random.default_rng(0xB203)
+    n_b, n_p = 2_000_000, 20_000_000 // (1 if mode != "Inner" else 4)
+    bk = wl.zipf_keys(rng, n_b, n_b, 1.0, np.int64)
+    pk = rng.integers(1, n_b + 1, n_p, dtype=np.int64)
+    info = assert_same(join, wl.make_relation(bk, 1 << 20), wl.make_relation(pk, 1 << 20), mode, "C3/100")
+    assert info.n_overflow_partitions >= 1
+
+
+# ------------------------------------------------------------------------------------------------------------------ C4
+@pytest.mark.parametrize("encoding", ["value", "dict"])
+@pytest.mark.parametrize("mode", ["Left", "Semi", "Anti"])
+def test_c4_customer_orders_nulls(join, mode, encoding):
+    """C4 shape at 1/10 (TPC-H SF10 sizes): customer (1.5 M unique c_custkey, left input = probe side for Left/Semi/Anti)
+    x orders (15 M o_custkey; customers with custkey % 3 == 0 never order, dss.h:371 CUST_MORTALITY), 1 % NULL keys on
+    both sides."""
+    rng = np.random.default_rng(0xB204)
+    n_cust, n_ord = 1_500_000, 15_000_000
+    ckeys = np.arange(1, n_cust + 1, dtype=np.int32)
+    okeys = rng.integers(1, n_cust + 1, n_ord).astype(np.int32)
+    okeys[okeys % 3 == 0] -= 1  # never 0: 3 -> 2, ...
+    cn = (rng.random(n_cust) < 0.01).astype(np.uint8)
+    on = (rng.random(n_ord) < 0.01).astype(np.uint8)
+    build = wl.make_relation(okeys, 1 << 20, encoding, on)   # orders build, customer probes (join_hash.cpp:58-70)
+    probe = wl.make_relation(ckeys, 1 << 20, encoding, cn)
+    info = assert_same(join, build, probe, mode, f"C4/10 {encoding}")
+    non_null_c = int((cn == 0).sum())
+    if mode == "Anti":  # NULL customers are NOT returned (quirk Q5); about 1/3 of the others never ordered
+        assert 0.30 * non_null_c < info.n_rows < 0.37 * non_null_c
+    if mode == "Semi":
+        assert 0.63 * non_null_c < info.n_rows < 0.70 * non_null_c
+
+
+# ------------------------------------------------------------------------------------------------------- full-size properties
+def _device_case(name, scale):
+    import torch
+    import bench
+    dev = torch.device("cuda", 0)
+    data = bench.gen_device_workload(name, scale, dev, seed=0xB200 + 7)
+    b = bench.relation_from_chunks(hj, data["build"], abi.LOC_DEVICE)
+    p = bench.relation_from_chunks(hj, data["probe"], abi.LOC_DEVICE)
+
+    def flat_keys(chunks):
+        return torch.cat([(a if at is None else a[at.long() & (0xFFFFFFFF if at.dtype == torch.int32 else 0xFFFF if at.dtype == torch.int16 else 0xFF)])
+                          for _, a, at in chunks]).to(torch.int64)
+    return data, b, p, flat_keys
+
+
+def _check_properties(j, data, b, p, flat_keys, sample=2_000_000):
+    """Exact row count, RowID checksum and sampled key equality of an Inner join, computed independently with torch."""
+    import torch
+    info = j.join(b, p, abi.MODE_INNER)
+    bk, pk = flat_keys(data["build"]), flat_keys(data["probe"])
+    domain = int(max(bk.max(), pk.max())) + 1
+    cb = torch.bincount(bk, minlength=domain)
+    matches_per_probe = cb[pk]                      # how many build rows every probe row joins with
+    want_rows = int(matches_per_probe.sum())
+    assert info.n_rows == want_rows, f"row count {info.n_rows} != {want_rows}"
+    bs, ps = j.fetch()
+    chunk = 1 << 20                                  # bench.CHUNK: position = chunk_id * 2^20 + offset
+    ppos = torch.from_numpy(ps.astype(np.int64)).cuda()
+    ppos = ppos[:, 0] * chunk + ppos[:, 1]
+    # checksum: every probe row appears exactly matches_per_probe times
+    want_sum = int((torch.arange(len(pk), device=pk.device) * matches_per_probe).sum())
+    assert int(ppos.sum()) == want_sum, "probe-side RowID checksum differs"
+    bpos = torch.from_numpy(bs.astype(np.int64)).cuda()
+    bpos = bpos[:, 0] * chunk + bpos[:, 1]
+    cp = torch.bincount(pk, minlength=domain)
+    want_bsum = int((torch.arange(len(bk), device=bk.device) * cp[bk]).sum())
+    assert int(bpos.sum()) == want_bsum, "build-side RowID checksum differs"
+    idx = torch.randint(0, info.n_rows, (min(sample, info.n_rows),), device=bk.device)
+    assert bool((bk[bpos[idx]] == pk[ppos[idx]]).all()), "a sampled result row joins unequal keys"
+    return info
+
+
+@pytest.mark.parametrize("scale", [1.0])
+def test_c2_full_size_properties(join, scale):
+    """C2 as published: 100 M x 1 B int32, dictionary-encoded, 1 e9 result pairs."""
+    data, b, p, flat_keys = _device_case("c2", scale)
+    info = _check_properties(join, data, b, p, flat_keys)
+    assert info.n_rows == data["n_probe"] and info.n_probe_passes == 1
+    join.release_scratch()
+
+
+def test_c3_tenth_size_properties(join):
+    """C3 at 1/10 (20 M x 200 M int64, Zipf build): ~2e8 pairs, hottest key ~1e6 duplicates expanded by whole warps."""
+    data, b, p, flat_keys = _device_case("c3", 0.1)
+    info = _check_properties(join, data, b, p, flat_keys)
+    assert info.n_overflow_partitions >= 1
+    join.release_scratch()
