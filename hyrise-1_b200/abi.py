@@ -13,6 +13,7 @@ SEG_VALUE, SEG_DICT, SEG_GATHERED = 0, 1, 2
 LOC_HOST, LOC_DEVICE = 0, 1
 FLAG_SQL_NULL_PROBE = 0x1
 FLAG_TIMINGS = 0x2
+FLAG_XCHG_STAGED = 0x4
 INVALID_CHUNK_ID = 0xFFFFFFFF
 INVALID_CHUNK_OFFSET = 0xFFFFFFFF
 N_PHASES = 10

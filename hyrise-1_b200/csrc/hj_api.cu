@@ -71,6 +71,11 @@ struct hj_ctx {
   int n_ranks = 1, rank = 0;
   DevBuf xchg_counts[2], xchg_cnt_dev, xchg_send_keys[2], xchg_send_rids[2], xchg_send_nulls[2], xchg_recv_keys[2],
       xchg_recv_rids[2], xchg_recv_nulls[2];
+  struct PeerMap { cudaIpcMemHandle_t handle; void* ptr = nullptr; };
+  PeerMap xchg_peer[16][6];        // peers' receive buffers mapped into this process (direct exchange)
+  std::vector<void*> xchg_graveyard;  // exported buffers that were outgrown; freed once no peer can have them mapped
+  DevBuf xchg_hdl_dev;
+  bool p2p_ok = false;
   const uint64_t* xchg_rowids[2] = {nullptr, nullptr};  // set while hj_join_sharded runs its local join
   uint64_t xchg_bytes_sent[2] = {0, 0};
 
@@ -82,7 +87,7 @@ struct hj_ctx {
                       &out_build, &out_probe, &misc, &xchg_counts[0], &xchg_counts[1], &xchg_cnt_dev, &xchg_send_keys[0],
                       &xchg_send_keys[1], &xchg_send_rids[0], &xchg_send_rids[1], &xchg_send_nulls[0], &xchg_send_nulls[1],
                       &xchg_recv_keys[0], &xchg_recv_keys[1], &xchg_recv_rids[0], &xchg_recv_rids[1], &xchg_recv_nulls[0],
-                      &xchg_recv_nulls[1]})
+                      &xchg_recv_nulls[1], &xchg_hdl_dev})
       all_bufs.push_back(b);
   }
 };
@@ -680,7 +685,7 @@ int hj_create(int device_id, const hj_options* opts, hj_ctx** out_ctx) {
     return fail(nullptr, HJ_ERR_CUDA, "device %d is sm_%d%d; libhj is built for sm_100a only", device_id, prop.major, prop.minor);
   }
   ok = ok && cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) == cudaSuccess;
-  ok = ok && cudaHostAlloc(&ctx->pinned, 16384, cudaHostAllocDefault) == cudaSuccess;
+  ok = ok && cudaHostAlloc(&ctx->pinned, 32768, cudaHostAllocDefault) == cudaSuccess;
   for (auto& ev : ctx->ev) ok = ok && cudaEventCreate(&ev) == cudaSuccess;
   if (!ok) {
     const char* msg = cudaGetErrorString(cudaGetLastError());

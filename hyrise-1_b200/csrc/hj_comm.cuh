@@ -24,9 +24,14 @@ struct XchgArgs {
   uint32_t* valid_mask;
   uint32_t* counts;          // [d * G + c]; X2 turns them into send cursors in place
   unsigned long long* send_cnt;  // [n_ranks] rows per destination
-  void* out_keys;            // X3: send buffer, K per row
-  uint64_t* out_rids;        // X3: packed global RowIDs
-  uint8_t* out_nulls;        // X3: null flags (kNullRoute only) or nullptr
+  // X3 destinations, one set per destination rank. Staged mode: all point into this rank's send buffers (adj = 0).
+  // Direct mode: dst_*[d] is rank d's RECEIVE buffer, mapped into this process with CUDA IPC (own rank: the local
+  // pointer), and adj[d] = (start of my region in d's buffer) - (start of region d in my send numbering), so that the
+  // scatter kernel stores straight over NVLink and no send buffer, NCCL copy or staging pass exists.
+  void* dst_keys[kMaxRanks];       // K per row
+  uint64_t* dst_rids[kMaxRanks];   // packed global RowIDs
+  uint8_t* dst_nulls[kMaxRanks];   // null flags (kNullRoute only) or nullptr
+  uint32_t adj[kMaxRanks];
   uint32_t n_ranks;
   uint32_t my_rank;
   int null_policy;
@@ -166,9 +171,16 @@ __global__ void __launch_bounds__(NT) k_xchg_scatter(const XchgArgs a) {
   uint8_t* s_dig = reinterpret_cast<uint8_t*>(s_key + TILE);
   uint8_t* s_nul = s_dig + TILE;
   __shared__ uint32_t s_cnt[kMaxRanks], s_loff[kMaxRanks + 1], s_delta[kMaxRanks], s_cur[kMaxRanks];
-  K* out_keys = static_cast<K*>(a.out_keys);
+  __shared__ K* s_dk[kMaxRanks];
+  __shared__ uint64_t* s_dr[kMaxRanks];
+  __shared__ uint8_t* s_dn[kMaxRanks];
   const uint32_t G = gridDim.x;
-  if (threadIdx.x < a.n_ranks) s_cur[threadIdx.x] = a.counts[threadIdx.x * G + blockIdx.x];
+  if (threadIdx.x < a.n_ranks) {
+    s_cur[threadIdx.x] = a.counts[threadIdx.x * G + blockIdx.x] + a.adj[threadIdx.x];
+    s_dk[threadIdx.x] = static_cast<K*>(a.dst_keys[threadIdx.x]);
+    s_dr[threadIdx.x] = a.dst_rids[threadIdx.x];
+    s_dn[threadIdx.x] = a.dst_nulls[threadIdx.x];
+  }
 
   for (uint32_t tile = blockIdx.x; tile < a.rel.n_tiles; tile += G) {
     const DevSegment s = a.rel.segs[__ldg(a.rel.tile_seg + tile)];
@@ -217,13 +229,15 @@ __global__ void __launch_bounds__(NT) k_xchg_scatter(const XchgArgs a) {
     for (int u = 0; u < ITEMS; ++u) {
       const uint32_t i = u * NT + threadIdx.x;
       if (i < n_out) {
-        const uint32_t g = s_delta[s_dig[i]] + i;
-        out_keys[g] = s_key[i];
-        a.out_rids[g] = s_rid[i];
-        if (a.out_nulls) a.out_nulls[g] = s_nul[i];
+        const uint32_t d = s_dig[i];
+        const uint32_t g = s_delta[d] + i;
+        s_dk[d][g] = s_key[i];
+        s_dr[d][g] = s_rid[i];
+        if (s_dn[d]) s_dn[d][g] = s_nul[i];
       }
     }
   }
+  __threadfence_system();  // direct mode: the stores went to peer memory; the ranks meet at a barrier after this kernel
 }
 
 }  // namespace hj
@@ -307,9 +321,12 @@ XchgArgs xchg_args(hj_ctx* ctx, const XchgSide& xs, int side) {
   a.valid_mask = static_cast<uint32_t*>(ctx->valid_mask[side].p);
   a.counts = static_cast<uint32_t*>(ctx->xchg_counts[side].p);
   a.send_cnt = static_cast<unsigned long long*>(ctx->xchg_cnt_dev.p) + size_t(side) * kMaxRanks;
-  a.out_keys = ctx->xchg_send_keys[side].p;
-  a.out_rids = static_cast<uint64_t*>(ctx->xchg_send_rids[side].p);
-  a.out_nulls = xs.send_nulls ? static_cast<uint8_t*>(ctx->xchg_send_nulls[side].p) : nullptr;
+  for (int d = 0; d < kMaxRanks; ++d) {  // staged mode; run_join_sharded overwrites these in direct mode
+    a.dst_keys[d] = ctx->xchg_send_keys[side].p;
+    a.dst_rids[d] = static_cast<uint64_t*>(ctx->xchg_send_rids[side].p);
+    a.dst_nulls[d] = xs.send_nulls ? static_cast<uint8_t*>(ctx->xchg_send_nulls[side].p) : nullptr;
+    a.adj[d] = 0;
+  }
   a.n_ranks = ctx->n_ranks;
   a.my_rank = ctx->rank;
   a.null_policy = xs.null_policy;
@@ -344,6 +361,115 @@ int xchg_count(hj_ctx* ctx, const hj_relation* rel, int side, XchgSide* xs, cuda
 
 namespace {
 
+// ---- direct (peer-mapped) exchange: CUDA IPC plumbing ------------------------------------------------------------------
+constexpr int kXchgBufKinds = 6;  // [side][keys, rids, nulls]
+struct HandleRec {                // what every rank publishes before X3 in direct mode (512 bytes)
+  cudaIpcMemHandle_t h[kXchgBufKinds];
+  uint8_t valid[kXchgBufKinds];
+  uint8_t pad[512 - kXchgBufKinds * sizeof(cudaIpcMemHandle_t) - kXchgBufKinds];
+};
+static_assert(sizeof(HandleRec) == 512, "HandleRec layout");
+
+DevBuf* xchg_recv_buf(hj_ctx* ctx, int side, int kind) {
+  return kind == 0 ? &ctx->xchg_recv_keys[side] : kind == 1 ? &ctx->xchg_recv_rids[side] : &ctx->xchg_recv_nulls[side];
+}
+
+// Grow-only like ensure(), but a buffer peers may still have mapped is parked (freed once every rank has entered the next
+// sharded join, i.e. has dropped its mapping) and the new one gets 1/8 slack so that re-exports stay rare.
+int ensure_exported(hj_ctx* ctx, DevBuf& b, size_t bytes) {
+  if (bytes <= b.cap) return HJ_OK;
+  if (b.p) ctx->xchg_graveyard.push_back(b.p);
+  b.p = nullptr;
+  b.cap = 0;
+  const size_t want = ((bytes + bytes / 8) + 255) & ~size_t(255);
+  HJ_CUDA(ctx, cudaMalloc(&b.p, want));
+  b.cap = want;
+  return HJ_OK;
+}
+
+void close_peer_maps(hj_ctx* ctx) {
+  for (auto& per_rank : ctx->xchg_peer)
+    for (auto& m : per_rank) {
+      if (m.ptr) cudaIpcCloseMemHandle(m.ptr);
+      m.ptr = nullptr;
+    }
+  (void)cudaGetLastError();
+}
+
+// All ranks publish the IPC handles of their receive buffers; every rank maps what changed. Collective.
+int exchange_handles(hj_ctx* ctx, cudaStream_t st) {
+  NcclApi* nc = nccl_api();
+  const uint32_t R = ctx->n_ranks, me = ctx->rank;
+  HJ_TRY(ensure(ctx, ctx->xchg_hdl_dev, sizeof(HandleRec) * (1 + kMaxRanks)));
+  auto* dev = static_cast<HandleRec*>(ctx->xchg_hdl_dev.p);
+  auto* host = reinterpret_cast<HandleRec*>(static_cast<char*>(ctx->pinned) + 16384);  // [0] mine, [1..R] everybody's
+  std::memset(&host[0], 0, sizeof(HandleRec));
+  for (int side = 0; side < 2; ++side)
+    for (int kind = 0; kind < 3; ++kind) {
+      DevBuf* b = xchg_recv_buf(ctx, side, kind);
+      if (!b->p) continue;
+      HJ_CUDA(ctx, cudaIpcGetMemHandle(&host[0].h[side * 3 + kind], b->p));
+      host[0].valid[side * 3 + kind] = 1;
+    }
+  HJ_CUDA(ctx, cudaMemcpyAsync(dev, &host[0], sizeof(HandleRec), cudaMemcpyHostToDevice, st));
+  HJ_NCCL(ctx, nc->AllGather(dev, dev + 1, sizeof(HandleRec), ncclUint8, static_cast<ncclComm_t>(ctx->nccl_comm), st));
+  HJ_CUDA(ctx, cudaMemcpyAsync(&host[1], dev + 1, sizeof(HandleRec) * R, cudaMemcpyDeviceToHost, st));
+  HJ_CUDA(ctx, cudaStreamSynchronize(st));
+  for (uint32_t p = 0; p < R; ++p) {
+    if (p == me) continue;
+    for (int k = 0; k < kXchgBufKinds; ++k) {
+      auto& m = ctx->xchg_peer[p][k];
+      const HandleRec& rec = host[1 + p];
+      if (!rec.valid[k]) continue;
+      if (m.ptr && std::memcmp(&m.handle, &rec.h[k], sizeof(cudaIpcMemHandle_t)) == 0) continue;
+      if (m.ptr) HJ_CUDA(ctx, cudaIpcCloseMemHandle(m.ptr));
+      m.ptr = nullptr;
+      HJ_CUDA(ctx, cudaIpcOpenMemHandle(&m.ptr, rec.h[k], cudaIpcMemLazyEnablePeerAccess));
+      m.handle = rec.h[k];
+    }
+  }
+  return HJ_OK;
+}
+
+// hj_comm_init: can every rank map every other rank's memory? (false e.g. for ranks that are threads of one process)
+bool probe_p2p(hj_ctx* ctx) {
+  NcclApi* nc = nccl_api();
+  const uint32_t R = ctx->n_ranks, me = ctx->rank;
+  cudaStream_t st = ctx->own_stream;
+  void* test = nullptr;
+  unsigned long long ok = 1;
+  if (cudaMalloc(&test, 256) != cudaSuccess) ok = 0;
+  if (ensure(ctx, ctx->xchg_hdl_dev, sizeof(HandleRec) * (1 + kMaxRanks)) != HJ_OK) return false;
+  auto* dev = static_cast<HandleRec*>(ctx->xchg_hdl_dev.p);
+  auto* host = reinterpret_cast<HandleRec*>(static_cast<char*>(ctx->pinned) + 16384);
+  std::memset(&host[0], 0, sizeof(HandleRec));
+  if (ok && cudaIpcGetMemHandle(&host[0].h[0], test) != cudaSuccess) ok = 0;
+  host[0].valid[0] = ok ? 1 : 0;
+  bool comm_ok = cudaMemcpyAsync(dev, &host[0], sizeof(HandleRec), cudaMemcpyHostToDevice, st) == cudaSuccess &&
+                 nc->AllGather(dev, dev + 1, sizeof(HandleRec), ncclUint8, static_cast<ncclComm_t>(ctx->nccl_comm), st) == ncclSuccess &&
+                 cudaMemcpyAsync(&host[1], dev + 1, sizeof(HandleRec) * R, cudaMemcpyDeviceToHost, st) == cudaSuccess &&
+                 cudaStreamSynchronize(st) == cudaSuccess;
+  if (!comm_ok) ok = 0;
+  for (uint32_t p = 0; p < R && ok; ++p) {
+    if (p == me) continue;
+    void* mapped = nullptr;
+    if (!host[1 + p].valid[0] || cudaIpcOpenMemHandle(&mapped, host[1 + p].h[0], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) ok = 0;
+    else cudaIpcCloseMemHandle(mapped);
+  }
+  (void)cudaGetLastError();
+  // agree: direct mode only if EVERY rank can map every peer (the ranks must take the same branch later)
+  auto* flag_dev = reinterpret_cast<unsigned long long*>(dev);
+  auto* flag_host = reinterpret_cast<unsigned long long*>(host);
+  bool all = comm_ok && cudaMemcpyAsync(flag_dev, &ok, 8, cudaMemcpyHostToDevice, st) == cudaSuccess &&
+             nc->AllGather(flag_dev, flag_dev + 8, 1, ncclUint64, static_cast<ncclComm_t>(ctx->nccl_comm), st) == ncclSuccess &&
+             cudaMemcpyAsync(flag_host, flag_dev + 8, 8 * R, cudaMemcpyDeviceToHost, st) == cudaSuccess &&
+             cudaStreamSynchronize(st) == cudaSuccess;
+  for (uint32_t p = 0; p < R && all; ++p) all = flag_host[p] != 0;
+  // peers may still be opening `test`: keep it until the communicator goes away
+  if (test) ctx->xchg_graveyard.push_back(test);
+  return all;
+}
+
 // The whole sharded join for hashed key type K (agreed on by all ranks).
 template <typename K>
 int run_join_sharded(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, int mode, cudaStream_t st,
@@ -374,8 +500,62 @@ int run_join_sharded(hj_ctx* ctx, const hj_relation* build, const hj_relation* p
   HJ_CUDA(ctx, cudaStreamSynchronize(st));
   auto cnt = [&](uint32_t src, int side, uint32_t dst) { return mat[(size_t(src) * 2 + side) * kMaxRanks + dst]; };
 
-  // ---- X3 + all-to-all per relation
+  // buffers outgrown during earlier sharded joins: every rank has entered this join, so nobody maps them any more
+  for (void* p : ctx->xchg_graveyard) cudaFree(p);
+  ctx->xchg_graveyard.clear();
+
   uint64_t n_recv[2] = {0, 0};
+  const bool direct = ctx->p2p_ok && !(ctx->opts.flags & HJ_FLAG_XCHG_STAGED);
+  if (direct) {
+    // ---- X3 stores straight into the peers' receive buffers (CUDA IPC mappings over NVLink): no send buffers, no NCCL
+    // copy; the only collectives are the count all-gather above, the handle all-gather and a 1-word barrier.
+    for (int side = 0; side < 2; ++side) {
+      for (uint32_t p = 0; p < R; ++p) n_recv[side] += cnt(p, side, me);
+      if (n_recv[side] >= 0xFFFFFFFFull)
+        return fail(ctx, HJ_ERR_TOO_LARGE, "rank %u would receive %llu %s rows (limit 2^32-2 per GPU)", me,
+                    (unsigned long long)n_recv[side], side ? "probe" : "build");
+      HJ_TRY(ensure_exported(ctx, ctx->xchg_recv_keys[side], std::max<uint64_t>(1, n_recv[side]) * sizeof(K)));
+      HJ_TRY(ensure_exported(ctx, ctx->xchg_recv_rids[side], std::max<uint64_t>(1, n_recv[side]) * 8));
+      if (xs[side].send_nulls) HJ_TRY(ensure_exported(ctx, ctx->xchg_recv_nulls[side], std::max<uint64_t>(1, n_recv[side])));
+    }
+    HJ_TRY(exchange_handles(ctx, st));
+    for (int side = 0; side < 2; ++side) {
+      uint64_t n_send = 0;
+      if (xs[side].pr.meta.n_tiles) {
+        XchgArgs a = xchg_args<K>(ctx, xs[side], side);
+        uint64_t send_off = 0;
+        for (uint32_t d = 0; d < R; ++d) {
+          uint64_t base_in_d = 0;  // where my rows start in rank d's receive buffer: after the rows of the ranks before me
+          for (uint32_t s2 = 0; s2 < me; ++s2) base_in_d += cnt(s2, side, d);
+          a.adj[d] = static_cast<uint32_t>(base_in_d - send_off);
+          send_off += cnt(me, side, d);
+          if (d == me) {
+            a.dst_keys[d] = ctx->xchg_recv_keys[side].p;
+            a.dst_rids[d] = static_cast<uint64_t*>(ctx->xchg_recv_rids[side].p);
+            a.dst_nulls[d] = xs[side].send_nulls ? static_cast<uint8_t*>(ctx->xchg_recv_nulls[side].p) : nullptr;
+          } else {
+            a.dst_keys[d] = ctx->xchg_peer[d][side * 3 + 0].ptr;
+            a.dst_rids[d] = static_cast<uint64_t*>(ctx->xchg_peer[d][side * 3 + 1].ptr);
+            a.dst_nulls[d] = xs[side].send_nulls ? static_cast<uint8_t*>(ctx->xchg_peer[d][side * 3 + 2].ptr) : nullptr;
+            if (cnt(me, side, d) && (!a.dst_keys[d] || !a.dst_rids[d] || (xs[side].send_nulls && !a.dst_nulls[d])))
+              return fail(ctx, HJ_ERR_COMM, "rank %u has no mapping of rank %u's receive buffers", me, d);
+          }
+        }
+        n_send = send_off;
+        auto k = k_xchg_scatter<K, kXchgThreads, xchg_items<K>()>;
+        const size_t smem = size_t(xchg_tile<K>()) * (sizeof(K) + 8 + 2);
+        HJ_TRY(set_smem(ctx, k, smem));
+        k<<<xs[side].G, kXchgThreads, smem, st>>>(a);
+        HJ_LAUNCH_CHECK(ctx, "k_xchg_scatter");
+        ++n_launch;
+      }
+      if (side == 0) HJ_CUDA(ctx, cudaEventRecord(ev[10], st));
+      ctx->xchg_bytes_sent[side] = (n_send - cnt(me, side, me)) * (sizeof(K) + 8 + (xs[side].send_nulls ? 1 : 0));
+    }
+    // barrier: a rank may read its receive buffers only after EVERY rank's X3 has finished storing into them
+    HJ_NCCL(ctx, nc->AllGather(cnt_dev, mat_dev, 1, ncclUint64, comm, st));
+  } else {
+    // ---- staged: X3 into send buffers, then one grouped ncclSend/ncclRecv (= all-to-all-v) per relation
   for (int side = 0; side < 2; ++side) {
     uint64_t send_off[kMaxRanks + 1] = {0}, recv_off[kMaxRanks + 1] = {0};
     for (uint32_t p = 0; p < R; ++p) {
@@ -438,6 +618,7 @@ int run_join_sharded(hj_ctx* ctx, const hj_relation* build, const hj_relation* p
     }
     HJ_NCCL(ctx, nc->GroupEnd());
     ctx->xchg_bytes_sent[side] = (n_send - cnt(me, side, me)) * (sizeof(K) + 8 + (nulls ? 1 : 0));
+  }
   }
   HJ_CUDA(ctx, cudaEventRecord(ev[11], st));
 
@@ -508,6 +689,7 @@ int hj_comm_init(hj_ctx* ctx, const uint8_t id[HJ_NCCL_UNIQUE_ID_BYTES], int n_r
   ctx->nccl_comm = comm;
   ctx->n_ranks = n_ranks;
   ctx->rank = rank;
+  ctx->p2p_ok = n_ranks > 1 && probe_p2p(ctx);
   return HJ_OK;
 }
 
@@ -545,6 +727,10 @@ int hj_join_sharded(hj_ctx* ctx, const hj_relation* build_shard, const hj_relati
 
 extern "C" void hj_comm_release(hj_ctx* ctx) {
   if (ctx && ctx->nccl_comm) {
+    close_peer_maps(ctx);
+    for (void* p : ctx->xchg_graveyard) cudaFree(p);
+    ctx->xchg_graveyard.clear();
+    ctx->p2p_ok = false;
     nccl_api()->CommDestroy(static_cast<ncclComm_t>(ctx->nccl_comm));
     ctx->nccl_comm = nullptr;
     ctx->n_ranks = 1;

@@ -113,6 +113,9 @@ typedef struct hj_relation {
                                        it is looked up as its stored value (VALUE/GATHERED) or
                                        T{} = 0 (DICT), join_hash.cpp:253,409 */
 #define HJ_FLAG_TIMINGS 0x2u        /* record per-phase CUDA-event timings (adds event overhead) */
+#define HJ_FLAG_XCHG_STAGED 0x4u    /* hj_join_sharded: exchange through send buffers + NCCL send/recv even when the
+                                       ranks can map each other's memory (default: the scatter kernel stores straight
+                                       into the peers' receive buffers over NVLink)                               */
 
 typedef struct hj_options {
   uint32_t abi_version;       /* HJ_ABI_VERSION                                              */

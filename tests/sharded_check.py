@@ -102,6 +102,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--backend", default="nccl", choices=["nccl", "gloo"])
     ap.add_argument("--big", action="store_true", help="nccl only: add a 2 M x 8 M case")
+    ap.add_argument("--staged", action="store_true", help="nccl only: HJ_FLAG_XCHG_STAGED (send buffers + ncclSend/Recv)")
     args = ap.parse_args()
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local_rank = int(os.environ.get("LOCAL_RANK", rank))
@@ -113,7 +114,7 @@ def main():
 
     j = None
     if args.backend == "nccl":
-        j = hj.HashJoin(device=local_rank)
+        j = hj.HashJoin(device=local_rank, flags=abi.FLAG_XCHG_STAGED if args.staged else 0)
         uid = [hj.comm_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(uid, src=0)
         j.comm_init(uid[0], world, rank)

@@ -69,6 +69,7 @@ def test_sharded_join_nccl_2gpus():
     n = torch.cuda.device_count()
     if n < 2:
         pytest.skip("needs >= 2 GPUs (run with gpurun --gpus 2)")
-    r = _torchrun(2, "--backend", "nccl", "--big")
-    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
-    assert "MISMATCH" not in r.stdout and r.stdout.count(" OK") == 25
+    for extra in ([], ["--staged"]):  # direct peer-mapped exchange (default) and the NCCL-staged one
+        r = _torchrun(2, "--backend", "nccl", "--big", *extra)
+        assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+        assert "MISMATCH" not in r.stdout and r.stdout.count(" OK") == 25
