@@ -112,9 +112,9 @@ int fail(hj_ctx* ctx, int status, const char* fmt, ...) {
                   cudaGetErrorString(e_), __FILE__, __LINE__);                                          \
   } while (0)
 
-#define HJ_TRY(expr)          \
+#define HJ_TRY(...)           \
   do {                        \
-    int st_ = (expr);         \
+    int st_ = (__VA_ARGS__);  \
     if (st_ != HJ_OK) return st_; \
   } while (0)
 
@@ -326,7 +326,7 @@ struct PartState {
   uint32_t G = 0;  // virtual CTAs of K1 / pass 1
 };
 
-template <typename K>
+template <typename K, bool PAY>
 int stage_alloc(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int bits2, PartState* ps) {
   const uint32_t P = 1u << radix_bits, F1 = P >> bits2;
   const uint32_t n = pr.meta.n_rows;
@@ -336,8 +336,8 @@ int stage_alloc(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, in
   HJ_TRY(ensure(ctx, ctx->part_off[side], (size_t(P) + 2) * 4));
   HJ_TRY(ensure(ctx, ctx->cur2[side], size_t(P) * 4));
   HJ_TRY(ensure(ctx, ctx->l1_tiles[side], (size_t(F1) + 1) * 4));
-  HJ_TRY(ensure(ctx, ctx->tup_a[side], std::max<size_t>(1, n) * sizeof(Tuple<K>)));
-  if (bits2) HJ_TRY(ensure(ctx, ctx->tup_b[side], std::max<size_t>(1, n) * sizeof(Tuple<K>)));
+  HJ_TRY(ensure(ctx, ctx->tup_a[side], std::max<size_t>(1, n) * sizeof(Tuple<K, PAY>)));
+  if (bits2) HJ_TRY(ensure(ctx, ctx->tup_b[side], std::max<size_t>(1, n) * sizeof(Tuple<K, PAY>)));
   if (pr.has_dict) {
     HJ_TRY(ensure(ctx, ctx->keys_mat[side], std::max<size_t>(1, n) * sizeof(K)));
     HJ_TRY(ensure(ctx, ctx->valid_mask[side], std::max<size_t>(1, pr.mask_words) * 4));
@@ -375,15 +375,15 @@ int stage_hist(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int
   return HJ_OK;
 }
 
-template <typename K>
-ScatterArgs<K> scatter_args(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int bits2, int null_policy) {
-  ScatterArgs<K> a{};
+template <typename K, bool PAY>
+ScatterArgs<K, PAY> scatter_args(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int bits2, int null_policy) {
+  ScatterArgs<K, PAY> a{};
   a.rel = pr.meta;
   a.keys_mat = static_cast<const K*>(ctx->keys_mat[side].p);
   a.valid_mask = static_cast<const uint32_t*>(ctx->valid_mask[side].p);
   a.base1 = static_cast<const uint32_t*>(ctx->hist1[side].p);
-  a.in = static_cast<const Tuple<K>*>(ctx->tup_a[side].p);
-  a.out = static_cast<Tuple<K>*>(ctx->tup_a[side].p);
+  a.in = static_cast<const Tuple<K, PAY>*>(ctx->tup_a[side].p);
+  a.out = static_cast<Tuple<K, PAY>*>(ctx->tup_a[side].p);
   a.cur2 = static_cast<uint32_t*>(ctx->cur2[side].p);
   a.part_off = static_cast<const uint32_t*>(ctx->part_off[side].p);
   a.l1_tiles = static_cast<const uint32_t*>(ctx->l1_tiles[side].p);
@@ -393,13 +393,13 @@ ScatterArgs<K> scatter_args(hj_ctx* ctx, const PreparedRel& pr, int side, int ra
   return a;
 }
 
-template <typename K>
+template <typename K, bool PAY>
 int stage_pass1(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int bits2, int null_policy,
                 const PartState& ps, cudaStream_t st, Launches* nl) {
   if (!pr.meta.n_tiles) return HJ_OK;
-  ScatterArgs<K> a = scatter_args<K>(ctx, pr, side, radix_bits, bits2, null_policy);
-  auto k = k_scatter1<K, kScatterThreads, Cfg<K>::kItems1>;
-  const size_t smem = size_t(tile1<K>()) * sizeof(Tuple<K>);
+  ScatterArgs<K, PAY> a = scatter_args<K, PAY>(ctx, pr, side, radix_bits, bits2, null_policy);
+  auto k = k_scatter1<K, PAY, kScatterThreads, Cfg<K>::kItems1>;
+  const size_t smem = size_t(tile1<K>()) * sizeof(Tuple<K, PAY>);
   HJ_TRY(set_smem(ctx, k, smem));
   k<<<ps.G, kScatterThreads, smem, st>>>(a);
   HJ_LAUNCH_CHECK(ctx, "k_scatter1");
@@ -407,13 +407,13 @@ int stage_pass1(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, in
   return HJ_OK;
 }
 
-template <typename K>
+template <typename K, bool PAY>
 int stage_pass2(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int bits2, cudaStream_t st, Launches* nl) {
   if (!pr.meta.n_tiles || !bits2) return HJ_OK;
-  ScatterArgs<K> a = scatter_args<K>(ctx, pr, side, radix_bits, bits2, kNullAsValue);
-  a.out = static_cast<Tuple<K>*>(ctx->tup_b[side].p);
-  auto k = k_scatter2<K, kScatterThreads, Cfg<K>::kItems2>;
-  const size_t smem = size_t(tile2<K>()) * sizeof(Tuple<K>);
+  ScatterArgs<K, PAY> a = scatter_args<K, PAY>(ctx, pr, side, radix_bits, bits2, kNullAsValue);
+  a.out = static_cast<Tuple<K, PAY>*>(ctx->tup_b[side].p);
+  auto k = k_scatter2<K, PAY, kScatterThreads, Cfg<K>::kItems2>;
+  const size_t smem = size_t(tile2<K>()) * sizeof(Tuple<K, PAY>);
   HJ_TRY(set_smem(ctx, k, smem));
   const uint32_t F1 = (1u << radix_bits) >> bits2;
   const uint32_t grid = (pr.meta.n_rows + tile2<K>() - 1) / tile2<K>() + F1;  // upper bound on sum(ceil(part / tile))
@@ -439,9 +439,9 @@ float ev_ms(cudaEvent_t a, cudaEvent_t b) {
   return ms;
 }
 
-template <typename K, int RM, int CLS>
-int launch_build_probe_cls(hj_ctx* ctx, const JoinArgs<K>& a, cudaStream_t st) {
-  auto k5 = k_build_probe<K, kJoinThreads, Cfg<K>::kNS, Cfg<K>::kCap, kProbeV, RM, CLS>;
+template <typename K, bool PAY, int RM, int CLS>
+int launch_build_probe_cls(hj_ctx* ctx, const JoinArgs<K, PAY>& a, cudaStream_t st) {
+  auto k5 = k_build_probe<K, PAY, kJoinThreads, Cfg<K>::kNS, Cfg<K>::kCap, kProbeV, RM, CLS>;
   const size_t smem5 = (size_t(Cfg<K>::kNS) + 1) * sizeof(K) + (size_t(Cfg<K>::kNS) + 2) * 4 + size_t(Cfg<K>::kCap) * 4;
   HJ_TRY(set_smem(ctx, k5, smem5));
   k5<<<ctx->n_sms, kJoinThreads, smem5, st>>>(a);
@@ -449,18 +449,18 @@ int launch_build_probe_cls(hj_ctx* ctx, const JoinArgs<K>& a, cudaStream_t st) {
   return HJ_OK;
 }
 
-template <typename K, int RM>
-int launch_build_probe(hj_ctx* ctx, const JoinArgs<K>& a, cudaStream_t st) {
+template <typename K, bool PAY, int RM>
+int launch_build_probe(hj_ctx* ctx, const JoinArgs<K, PAY>& a, cudaStream_t st) {
   switch (a.mode) {
-    case HJ_MODE_INNER: return launch_build_probe_cls<K, RM, kClsInner>(ctx, a, st);
+    case HJ_MODE_INNER: return launch_build_probe_cls<K, PAY, RM, kClsInner>(ctx, a, st);
     case HJ_MODE_LEFT:
-    case HJ_MODE_RIGHT: return launch_build_probe_cls<K, RM, kClsOuter>(ctx, a, st);
-    case HJ_MODE_SEMI: return launch_build_probe_cls<K, RM, kClsSemi>(ctx, a, st);
-    default: return launch_build_probe_cls<K, RM, kClsAnti>(ctx, a, st);
+    case HJ_MODE_RIGHT: return launch_build_probe_cls<K, PAY, RM, kClsOuter>(ctx, a, st);
+    case HJ_MODE_SEMI: return launch_build_probe_cls<K, PAY, RM, kClsSemi>(ctx, a, st);
+    default: return launch_build_probe_cls<K, PAY, RM, kClsAnti>(ctx, a, st);
   }
 }
 
-template <typename K>
+template <typename K, bool PAY = false>
 int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, int mode, cudaStream_t st,
              hj_result_info* info, bool payload = false) {
   const bool one_side = mode == HJ_MODE_SEMI || mode == HJ_MODE_ANTI;
@@ -482,20 +482,20 @@ int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, in
   const int probe_null_policy = !outer ? kNullDrop : ((ctx->opts.flags & HJ_FLAG_SQL_NULL_PROBE) ? kNullRoute : kNullAsValue);
 
   PartState sb, sp;
-  HJ_TRY(stage_alloc<K>(ctx, pb, 0, radix_bits, bits2, &sb));
-  HJ_TRY(stage_alloc<K>(ctx, pp, 1, radix_bits, bits2, &sp));
+  HJ_TRY(stage_alloc<K, PAY>(ctx, pb, 0, radix_bits, bits2, &sb));
+  HJ_TRY(stage_alloc<K, PAY>(ctx, pp, 1, radix_bits, bits2, &sp));
   HJ_TRY(stage_hist<K>(ctx, pb, 0, radix_bits, bits2, kNullDrop, sb, st, &nl));
   HJ_TRY(stage_hist<K>(ctx, pp, 1, radix_bits, bits2, probe_null_policy, sp, st, &nl));
   HJ_CUDA(ctx, cudaEventRecord(ev[2], st));
-  HJ_TRY(stage_pass1<K>(ctx, pb, 0, radix_bits, bits2, kNullDrop, sb, st, &nl));
-  HJ_TRY(stage_pass1<K>(ctx, pp, 1, radix_bits, bits2, probe_null_policy, sp, st, &nl));
+  HJ_TRY(stage_pass1<K, PAY>(ctx, pb, 0, radix_bits, bits2, kNullDrop, sb, st, &nl));
+  HJ_TRY(stage_pass1<K, PAY>(ctx, pp, 1, radix_bits, bits2, probe_null_policy, sp, st, &nl));
   HJ_CUDA(ctx, cudaEventRecord(ev[3], st));
-  HJ_TRY(stage_pass2<K>(ctx, pb, 0, radix_bits, bits2, st, &nl));
-  HJ_TRY(stage_pass2<K>(ctx, pp, 1, radix_bits, bits2, st, &nl));
+  HJ_TRY(stage_pass2<K, PAY>(ctx, pb, 0, radix_bits, bits2, st, &nl));
+  HJ_TRY(stage_pass2<K, PAY>(ctx, pp, 1, radix_bits, bits2, st, &nl));
   HJ_CUDA(ctx, cudaEventRecord(ev[4], st));
-  const auto* tb = static_cast<const Tuple<K>*>(bits2 ? ctx->tup_b[0].p : ctx->tup_a[0].p);
-  const auto* tp = static_cast<const Tuple<K>*>(bits2 ? ctx->tup_b[1].p : ctx->tup_a[1].p);
-  const auto* tp1 = static_cast<const Tuple<K>*>(ctx->tup_a[1].p);  // routed NULL rows stay in pass 1's output
+  const auto* tb = static_cast<const Tuple<K, PAY>*>(bits2 ? ctx->tup_b[0].p : ctx->tup_a[0].p);
+  const auto* tp = static_cast<const Tuple<K, PAY>*>(bits2 ? ctx->tup_b[1].p : ctx->tup_a[1].p);
+  const auto* tp1 = static_cast<const Tuple<K, PAY>*>(ctx->tup_a[1].p);  // routed NULL rows stay in pass 1's output
 
   // ---- plan
   const uint32_t cap = Cfg<K>::kCap;
@@ -532,7 +532,7 @@ int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, in
   int chunk_shift = chunk_shift_for(want_rows);
   uint64_t capacity = alloc_rows(want_rows, chunk_shift);
 
-  JoinArgs<K> a{};
+  JoinArgs<K, PAY> a{};
   a.build = tb;
   a.probe = tp;
   a.items = static_cast<const WorkItem*>(ctx->items.p);
@@ -566,22 +566,22 @@ int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, in
     HJ_CUDA(ctx, cudaMemsetAsync(ctx->out_state.p, 0, sizeof(OutState), st));
     if (mode != HJ_MODE_INNER) HJ_CUDA(ctx, cudaMemsetAsync(ctx->matched.p, 0, matched_bytes, st));
     if (payload) {
-      if constexpr (sizeof(K) == 8) HJ_TRY((launch_build_probe<K, kRidPayload>(ctx, a, st)));
-      else return fail(ctx, HJ_ERR_INVALID, "RowID-carrying tuples need the int64 pipeline");
+      if constexpr (sizeof(Tuple<K, PAY>) > 8) HJ_TRY((launch_build_probe<K, PAY, kRidPayload>(ctx, a, st)));
+      else return fail(ctx, HJ_ERR_INVALID, "RowID-carrying tuples need a tuple type with a payload");
     } else if (fast_rowid) {
-      HJ_TRY((launch_build_probe<K, kRidFast>(ctx, a, st)));
+      HJ_TRY((launch_build_probe<K, PAY, kRidFast>(ctx, a, st)));
     } else {
-      HJ_TRY((launch_build_probe<K, kRidGeneric>(ctx, a, st)));
+      HJ_TRY((launch_build_probe<K, PAY, kRidGeneric>(ctx, a, st)));
     }
     nl.n++;
     if (passes == 1) HJ_CUDA(ctx, cudaEventRecord(ev[5], st));
     if (mode != HJ_MODE_INNER) {
-      k_finalize_multi<K, 256><<<ctx->n_sms, 256, 0, st>>>(a, static_cast<const WorkItem*>(ctx->fin.p));
+      k_finalize_multi<K, PAY, 256><<<ctx->n_sms, 256, 0, st>>>(a, static_cast<const WorkItem*>(ctx->fin.p));
       HJ_LAUNCH_CHECK(ctx, "k_finalize_multi");
       nl.n++;
     }
     if (probe_null_policy == kNullRoute) {
-      k_emit_null_probe<K, 256><<<ctx->n_sms, 256, 0, st>>>(a, tp1, off_p);
+      k_emit_null_probe<K, PAY, 256><<<ctx->n_sms, 256, 0, st>>>(a, tp1, off_p);
       HJ_LAUNCH_CHECK(ctx, "k_emit_null_probe");
       nl.n++;
     }

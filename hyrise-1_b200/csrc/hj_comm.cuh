@@ -639,8 +639,8 @@ int run_join_sharded(hj_ctx* ctx, const hj_relation* build, const hj_relation* p
     rel[side].n_rows = n_recv[side];
     ctx->xchg_rowids[side] = static_cast<const uint64_t*>(ctx->xchg_recv_rids[side].p);
   }
-  // always the int64 pipeline: its 16-byte tuple has room for the RowID next to the key (K = int32 keys are widened)
-  const int st_join = run_join<int64_t>(ctx, &rel[0], &rel[1], mode, st, info, /*payload=*/true);
+  // the tuples carry the RowID next to the key: 12 bytes for int32 keys, the 16-byte int64 tuple has room anyway
+  const int st_join = run_join<K, sizeof(K) == 4>(ctx, &rel[0], &rel[1], mode, st, info, /*payload=*/true);
   ctx->xchg_rowids[0] = ctx->xchg_rowids[1] = nullptr;
   HJ_TRY(st_join);
   hj_timings& t = ctx->timings;

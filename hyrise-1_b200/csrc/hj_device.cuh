@@ -56,31 +56,51 @@ struct RelMeta {
   uint32_t pad;
 };
 
-template <typename K>
+// PAY: the tuple carries a 64-bit payload (idx, pad) — the row's global RowID after the multi-GPU exchange — instead of a
+// 32-bit position. int64-key tuples have room for it anyway (16 B); int32-key tuples grow from 8 to 12 bytes.
+template <typename K, bool PAY = false>
 struct Tuple;
 template <>
-struct __align__(8) Tuple<int32_t> {
+struct __align__(8) Tuple<int32_t, false> {
   int32_t key;
   uint32_t idx;
 };
 template <>
-struct __align__(16) Tuple<int64_t> {
+struct Tuple<int32_t, true> {
+  int32_t key;
+  uint32_t idx;
+  uint32_t pad;
+};
+template <bool PAY>
+struct __align__(16) Tuple<int64_t, PAY> {
   int64_t key;
   uint32_t idx;
   uint32_t pad;
 };
+static_assert(sizeof(Tuple<int32_t, false>) == 8 && sizeof(Tuple<int32_t, true>) == 12 && sizeof(Tuple<int64_t, false>) == 16 &&
+                  sizeof(Tuple<int64_t, true>) == 16, "tuple layouts");
 
-// vector loads of a partitioned tuple through the read-only path (evict-first .cs hints measured slower on B200: K1 +12 ms with st.cs, passes +0.1..0.4 ms with ld.cs)
-__device__ __forceinline__ Tuple<int32_t> ld_stream(const Tuple<int32_t>* p) {
+// vector loads of a partitioned tuple through the read-only path (evict-first .cs hints measured slower on B200: K1 +12 ms
+// with st.cs, passes +0.1..0.4 ms with ld.cs)
+__device__ __forceinline__ Tuple<int32_t, false> ld_stream(const Tuple<int32_t, false>* p) {
   const uint2 v = __ldg(reinterpret_cast<const uint2*>(p));
-  Tuple<int32_t> t;
+  Tuple<int32_t, false> t;
   t.key = static_cast<int32_t>(v.x);
   t.idx = v.y;
   return t;
 }
-__device__ __forceinline__ Tuple<int64_t> ld_stream(const Tuple<int64_t>* p) {
+__device__ __forceinline__ Tuple<int32_t, true> ld_stream(const Tuple<int32_t, true>* p) {
+  const uint32_t* w = reinterpret_cast<const uint32_t*>(p);
+  Tuple<int32_t, true> t;
+  t.key = static_cast<int32_t>(__ldg(w));
+  t.idx = __ldg(w + 1);
+  t.pad = __ldg(w + 2);
+  return t;
+}
+template <bool PAY>
+__device__ __forceinline__ Tuple<int64_t, PAY> ld_stream(const Tuple<int64_t, PAY>* p) {
   const uint4 v = __ldg(reinterpret_cast<const uint4*>(p));
-  Tuple<int64_t> t;
+  Tuple<int64_t, PAY> t;
   t.key = static_cast<int64_t>(static_cast<uint64_t>(v.x) | (static_cast<uint64_t>(v.y) << 32));
   t.idx = v.z;
   t.pad = v.w;

@@ -216,16 +216,16 @@ __global__ void __launch_bounds__(NT) k_offsets_l1(uint32_t* __restrict__ hist1,
 //   memory so that each digit is a contiguous run, then copy the runs out warp by warp (consecutive lanes on consecutive
 //   addresses; no per-tuple address lookup in the copy loop).
 // Within a partition the tuple order is arbitrary (the reference guarantees none: join_hash.hpp:19-20).
-// dynamic smem: NT*ITEMS*sizeof(Tuple<K>).
+// dynamic smem: NT*ITEMS*sizeof(Tuple<K, PAY>).
 // =====================================================================================================================
-template <typename K>
+template <typename K, bool PAY>
 struct ScatterArgs {
   RelMeta rel;                  // pass 1
   const K* keys_mat;            // pass 1
   const uint32_t* valid_mask;   // pass 1
   const uint32_t* base1;        // pass 1: private cursors [d * G + c]
-  const Tuple<K>* in;           // pass 2
-  Tuple<K>* out;
+  const Tuple<K, PAY>* in;           // pass 2
+  Tuple<K, PAY>* out;
   uint32_t* cur2;               // pass 2: global cursors, one per final partition
   const uint32_t* part_off;     // pass 2
   const uint32_t* l1_tiles;     // pass 2
@@ -241,14 +241,14 @@ constexpr uint32_t kNoDigit = 0xFFFFFFFFu;
 // digit's run is contiguous, so the stores coalesce per run), re-derive the digit from the key and add the digit's
 // (global - staged) delta, with no per-run control flow and no per-tuple destination array in shared memory. v1 copied run by run (a warp per digit) and spent ~120 thread-instructions per tuple on loop
 // overhead for the ~32-tuple runs (profiles/r01_ncu_v1_c2_full_summary.md).
-template <typename K, int NT, int ITEMS>
-__device__ __forceinline__ void copy_tile_out(const Tuple<K>* stage, const uint32_t* s_delta, Tuple<K>* out, uint32_t n,
+template <typename K, bool PAY, int NT, int ITEMS>
+__device__ __forceinline__ void copy_tile_out(const Tuple<K, PAY>* stage, const uint32_t* s_delta, Tuple<K, PAY>* out, uint32_t n,
                                               uint32_t dmask, int shift, uint32_t null_start, uint32_t null_digit) {
 #pragma unroll
   for (int j = 0; j < ITEMS; ++j) {
     const uint32_t i = j * NT + threadIdx.x;
     if (i < n) {
-      const Tuple<K> t = stage[i];
+      const Tuple<K, PAY> t = stage[i];
       const uint32_t d = i >= null_start ? null_digit : (hash_key(t.key) & dmask) >> shift;
       out[s_delta[d] + i] = t;  // s_delta[d] = global index of the digit's run - its offset in the staged tile (mod 2^32)
     }
@@ -258,12 +258,12 @@ __device__ __forceinline__ void copy_tile_out(const Tuple<K>* stage, const uint3
 // Pass 1: persistent virtual CTA c = blockIdx.x owns tiles c, c+G, ... exactly as in K1, so the cursors computed from K1's
 // per-CTA counts (base1) are private: no global atomics, deterministic placement. Digit = high (radix_bits - bits2) bits
 // of the partition index; routed NULL rows form run number F1.
-// dynamic smem: TILE * sizeof(Tuple<K>).
-template <typename K, int NT, int ITEMS>
-__global__ void __launch_bounds__(NT, 4) k_scatter1(const ScatterArgs<K> a) {
+// dynamic smem: TILE * sizeof(Tuple<K, PAY>).
+template <typename K, bool PAY, int NT, int ITEMS>
+__global__ void __launch_bounds__(NT, 4) k_scatter1(const ScatterArgs<K, PAY> a) {
   constexpr uint32_t TILE = NT * ITEMS;
   extern __shared__ __align__(16) unsigned char s_raw[];
-  Tuple<K>* stage = reinterpret_cast<Tuple<K>*>(s_raw);
+  Tuple<K, PAY>* stage = reinterpret_cast<Tuple<K, PAY>*>(s_raw);
   __shared__ uint32_t s_cnt[kMaxDigits + 1], s_cur[kMaxDigits + 1];
   __shared__ uint32_t s_loff[kMaxDigits + 1], s_delta[kMaxDigits + 1];
   __shared__ uint32_t scratch[33];
@@ -352,10 +352,10 @@ __global__ void __launch_bounds__(NT, 4) k_scatter1(const ScatterArgs<K> a) {
 #pragma unroll
     for (int j = 0; j < ITEMS; ++j) {
       if (packed[j] != kNoDigit) {
-        Tuple<K> t;
+        Tuple<K, PAY> t;
         t.key = key[j];
         t.idx = idx0 + j * NT;
-        if constexpr (sizeof(K) == 8) {
+        if constexpr (sizeof(Tuple<K, PAY>) > 8) {
           t.pad = 0;
           if (rids) {
             const uint64_t r = __ldg(rids + j * NT);
@@ -367,7 +367,7 @@ __global__ void __launch_bounds__(NT, 4) k_scatter1(const ScatterArgs<K> a) {
       }
     }
     __syncthreads();
-    copy_tile_out<K, NT, ITEMS>(stage, s_delta, a.out, s_total, pmask, bits2, s_null_start, F1);
+    copy_tile_out<K, PAY, NT, ITEMS>(stage, s_delta, a.out, s_total, pmask, bits2, s_null_start, F1);
   }
 }
 
@@ -375,12 +375,12 @@ __global__ void __launch_bounds__(NT, 4) k_scatter1(const ScatterArgs<K> a) {
 // is reserved with one global atomic per non-empty digit. blockIdx is mapped to the tile through a multiplicative
 // permutation so that the CTAs resident at any moment work on different level-1 partitions, i.e. on different cursors
 // (same-address atomics serialise at ~21 ns; profiles/r01_microbench_atomics_vs_match.txt).
-// dynamic smem: TILE * sizeof(Tuple<K>).
-template <typename K, int NT, int ITEMS>
-__global__ void __launch_bounds__(NT, 4) k_scatter2(const ScatterArgs<K> a) {
+// dynamic smem: TILE * sizeof(Tuple<K, PAY>).
+template <typename K, bool PAY, int NT, int ITEMS>
+__global__ void __launch_bounds__(NT, 4) k_scatter2(const ScatterArgs<K, PAY> a) {
   constexpr uint32_t TILE = NT * ITEMS;
   extern __shared__ __align__(16) unsigned char s_raw[];
-  Tuple<K>* stage = reinterpret_cast<Tuple<K>*>(s_raw);
+  Tuple<K, PAY>* stage = reinterpret_cast<Tuple<K, PAY>*>(s_raw);
   __shared__ uint32_t s_cnt[kMaxDigits], s_loff[kMaxDigits], s_delta[kMaxDigits];
   __shared__ uint32_t scratch[33];
   __shared__ uint32_t s_l1[kMaxDigits + 1];
@@ -402,9 +402,9 @@ __global__ void __launch_bounds__(NT, 4) k_scatter2(const ScatterArgs<K> a) {
   const uint32_t in_base = a.part_off[d1 << a.bits2] + (t - s_l1[d1]) * TILE;
   const uint32_t n_in = min(TILE, p_hi - in_base);
   uint32_t* cursors = a.cur2 + (d1 << a.bits2);
-  const Tuple<K>* in = a.in + in_base;
+  const Tuple<K, PAY>* in = a.in + in_base;
 
-  Tuple<K> tup[ITEMS];
+  Tuple<K, PAY> tup[ITEMS];
   uint32_t packed[ITEMS];
 #pragma unroll
   for (int j = 0; j < ITEMS; ++j) {
@@ -437,7 +437,7 @@ __global__ void __launch_bounds__(NT, 4) k_scatter2(const ScatterArgs<K> a) {
     if (packed[j] != kNoDigit) stage[s_loff[packed[j] >> 16] + (packed[j] & 0xFFFFu)] = tup[j];
   }
   __syncthreads();
-  copy_tile_out<K, NT, ITEMS>(stage, s_delta, a.out, n_in, F2 - 1u, 0, 0xFFFFFFFFu, 0u);
+  copy_tile_out<K, PAY, NT, ITEMS>(stage, s_delta, a.out, n_in, F2 - 1u, 0, 0xFFFFFFFFu, 0u);
 }
 
 // =====================================================================================================================
@@ -652,10 +652,10 @@ __device__ __forceinline__ void out_writer_finish(const OutWriter* w, OutState* 
 // expanded by its whole warp.
 // block: NT threads (1 CTA/SM), dynamic smem: (NS+1)*sizeof(K) + (NS+2)*4 + CAP*4.
 // =====================================================================================================================
-template <typename K>
+template <typename K, bool PAY>
 struct JoinArgs {
-  const Tuple<K>* build;
-  const Tuple<K>* probe;
+  const Tuple<K, PAY>* build;
+  const Tuple<K, PAY>* probe;
   const WorkItem* items;
   const PlanOut* plan;
   uint32_t* queue_head;
@@ -722,12 +722,12 @@ __device__ __forceinline__ uint64_t rowid_of(const RelMeta& m, uint32_t idx) {
   if (RM == kRidFast) return pack_rowid(idx >> m.uniform_shift, idx & ((1u << m.uniform_shift) - 1u));
   return make_rowid(m, idx);
 }
-template <typename K>
-__device__ __forceinline__ uint32_t tuple_hi(const Tuple<K>& t) {
-  if constexpr (sizeof(K) == 8) return t.pad; else return 0u;
+template <typename K, bool PAY>
+__device__ __forceinline__ uint32_t tuple_hi(const Tuple<K, PAY>& t) {
+  if constexpr (sizeof(Tuple<K, PAY>) > 8) return t.pad; else return 0u;
 }
-template <typename K>
-__device__ __forceinline__ uint64_t tuple_rowid(const RelMeta& m, const Tuple<K>& t, int payload) {
+template <typename K, bool PAY>
+__device__ __forceinline__ uint64_t tuple_rowid(const RelMeta& m, const Tuple<K, PAY>& t, int payload) {
   return payload ? pack_rowid(t.idx, tuple_hi(t)) : make_rowid(m, t.idx);
 }
 
@@ -737,8 +737,8 @@ constexpr int kClsInner = 0, kClsOuter = 1, kClsSemi = 2, kClsAnti = 3;
 // Writes the result rows of one probe tile. CONTIG: the tile's reserved range is one in-bounds contiguous piece of the
 // output arrays (the common case), so a row's position is ob/op + a 32-bit index; otherwise every row goes through
 // out_pos() and the capacity check (chunk boundary inside the tile, or the overflow pass that only counts).
-template <typename K, int V, int CLS, int RM, bool CONTIG>
-__device__ __forceinline__ void emit_tile(const JoinArgs<K>& a, const uint32_t* s_grp, const Tuple<K>* bchunk,
+template <typename K, bool PAY, int V, int CLS, int RM, bool CONTIG>
+__device__ __forceinline__ void emit_tile(const JoinArgs<K, PAY>& a, const uint32_t* s_grp, const Tuple<K, PAY>* bchunk,
                                           const uint32_t (&pw)[V], const uint32_t (&pidx)[V], const uint32_t (&ppad)[V],
                                           const uint32_t (&outc)[V], const uint32_t (&ex)[V], uint32_t wbase,
                                           unsigned long long base0, unsigned long long base1, uint32_t first) {
@@ -762,7 +762,7 @@ __device__ __forceinline__ void emit_tile(const JoinArgs<K>& a, const uint32_t* 
   // chunk, whose tuples (<= CAP x 16 B, read by every probe row of the partition) stay cache-resident
   auto brid = [&](uint32_t g) -> uint64_t {
     if (RM == kRidPayload) {
-      const Tuple<K> t = bchunk[s_grp[g]];
+      const Tuple<K, PAY> t = bchunk[s_grp[g]];
       return pack_rowid(t.idx, tuple_hi(t));
     }
     return rowid_of<RM>(a.build_rel, s_grp[g]);
@@ -809,8 +809,8 @@ __device__ __forceinline__ void emit_tile(const JoinArgs<K>& a, const uint32_t* 
   }
 }
 
-template <typename K, int NT, int NS, int CAP, int V, int RM, int CLS>
-__global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K> a) {
+template <typename K, bool PAY, int NT, int NS, int CAP, int V, int RM, int CLS>
+__global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K, PAY> a) {
   static_assert(CAP < NS && CAP <= 65535, "table must keep empty slots; run ends are 16 bit");
   constexpr uint32_t NW = NT / 32;
   constexpr uint32_t MIN_NS = 32 * NW;  // every warp scans >= 32 slots
@@ -845,11 +845,11 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K> a) {
     uint32_t ns = MIN_NS;
     while (ns < 2 * it.b_cnt && ns < NS) ns <<= 1;
     const uint32_t ns_mask = ns - 1;
-    const Tuple<K>* probe = a.probe + it.p_begin;
-    const Tuple<K>* build = a.build + it.b_begin;
+    const Tuple<K, PAY>* probe = a.probe + it.p_begin;
+    const Tuple<K, PAY>* build = a.build + it.b_begin;
 
     // the warp's first probe rows go in flight before the table is built
-    Tuple<K> nxt[V];
+    Tuple<K, PAY> nxt[V];
 #pragma unroll
     for (int j = 0; j < V; ++j) {
       const uint32_t i = warp * (32 * V) + j * 32 + lane;
@@ -992,9 +992,9 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K> a) {
       if (running == 0) continue;  // warp-uniform
       warp_writer_reserve(&wr, a.out_state, running, chunk_shift);
       if (wr.first == 0xFFFFFFFFu && wr.base0 + running <= a.capacity)
-        emit_tile<K, V, CLS, RM, true>(a, s_grp, build, pw, pidx, ppad, outc, ex, 0u, wr.base0, wr.base1, wr.first);
+        emit_tile<K, PAY, V, CLS, RM, true>(a, s_grp, build, pw, pidx, ppad, outc, ex, 0u, wr.base0, wr.base1, wr.first);
       else
-        emit_tile<K, V, CLS, RM, false>(a, s_grp, build, pw, pidx, ppad, outc, ex, 0u, wr.base0, wr.base1, wr.first);
+        emit_tile<K, PAY, V, CLS, RM, false>(a, s_grp, build, pw, pidx, ppad, outc, ex, 0u, wr.base0, wr.base1, wr.first);
     }
   }
   if (lane == 0) out_writer_finish(&wr, a.out_state, a.out_tails);
@@ -1022,8 +1022,8 @@ __device__ __forceinline__ void emit_flagged(bool flag, uint64_t build_rid, uint
 }
 
 // K6: unmatched/matched decisions for multi partitions, from the bitmap K5 filled over all chunks.
-template <typename K, int NT>
-__global__ void __launch_bounds__(NT) k_finalize_multi(const JoinArgs<K> a, const WorkItem* __restrict__ fin) {
+template <typename K, bool PAY, int NT>
+__global__ void __launch_bounds__(NT) k_finalize_multi(const JoinArgs<K, PAY> a, const WorkItem* __restrict__ fin) {
   __shared__ uint32_t scratch[33];
   __shared__ OutWriter s_out;
   const uint32_t n_fin = a.plan->n_fin;
@@ -1040,7 +1040,7 @@ __global__ void __launch_bounds__(NT) k_finalize_multi(const JoinArgs<K> a, cons
         const uint32_t pos = it.p_begin + i;
         const bool hit = (a.matched[pos >> 5] >> (pos & 31u)) & 1u;
         flag = (mode == 5) ? hit : !hit;  // Semi keeps matched rows; Left/Right/Anti the unmatched ones
-        if (flag) prid = tuple_rowid<K>(a.probe_rel, a.probe[pos], a.payload);
+        if (flag) prid = tuple_rowid<K, PAY>(a.probe_rel, a.probe[pos], a.payload);
       }
       emit_flagged<NT>(flag, kNullRowId, prid, a.out_build, a.out_probe, a.capacity, &s_out, a.out_state, scratch, a.chunk_shift);
     }
@@ -1049,8 +1049,8 @@ __global__ void __launch_bounds__(NT) k_finalize_multi(const JoinArgs<K> a, cons
 }
 
 // K7: HJ_FLAG_SQL_NULL_PROBE — NULL probe keys of a Left/Right join were routed aside by pass 1; each yields (NULL, p).
-template <typename K, int NT>
-__global__ void __launch_bounds__(NT) k_emit_null_probe(const JoinArgs<K> a, const Tuple<K>* __restrict__ pass1,
+template <typename K, bool PAY, int NT>
+__global__ void __launch_bounds__(NT) k_emit_null_probe(const JoinArgs<K, PAY> a, const Tuple<K, PAY>* __restrict__ pass1,
                                                         const uint32_t* __restrict__ off_p) {
   __shared__ uint32_t scratch[33];
   __shared__ OutWriter s_out;
@@ -1061,7 +1061,7 @@ __global__ void __launch_bounds__(NT) k_emit_null_probe(const JoinArgs<K> a, con
   for (uint32_t base = lo + blockIdx.x * NT; base < hi; base += gridDim.x * NT) {
     const uint32_t i = base + threadIdx.x;
     const bool flag = i < hi;
-    const uint64_t prid = flag ? tuple_rowid<K>(a.probe_rel, pass1[i], a.payload) : 0;
+    const uint64_t prid = flag ? tuple_rowid<K, PAY>(a.probe_rel, pass1[i], a.payload) : 0;
     emit_flagged<NT>(flag, kNullRowId, prid, a.out_build, a.out_probe, a.capacity, &s_out, a.out_state, scratch, a.chunk_shift);
   }
   if (threadIdx.x == 0) out_writer_finish(&s_out, a.out_state, a.out_tails);
