@@ -38,6 +38,9 @@ constexpr int kMinChunkShift = 8, kMaxChunkShift = 14;  // result chunks of 256 
 constexpr int kVirtualCtasPerSm = 4;       // K1 / pass 1 tile ownership: G = min(n_tiles, 4 * SMs) virtual CTAs
 template <typename K> constexpr int tile1() { return kScatterThreads * Cfg<K>::kItems1; }
 template <typename K> constexpr int tile2() { return kScatterThreads * Cfg<K>::kItems2; }
+// 12-byte RowID-carrying tuples of int32 keys: same tile sizes with twice the threads and half the rows per thread, so that
+// a thread's keys + RowIDs (pass 1) / three-word tuples (pass 2) fit the register file without spilling
+template <typename K, bool PAY> constexpr int scatter_threads() { return (PAY && sizeof(K) == 4) ? 2 * kScatterThreads : kScatterThreads; }
 
 struct DevBuf {
   void* p = nullptr;
@@ -398,10 +401,11 @@ int stage_pass1(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, in
                 const PartState& ps, cudaStream_t st, Launches* nl) {
   if (!pr.meta.n_tiles) return HJ_OK;
   ScatterArgs<K, PAY> a = scatter_args<K, PAY>(ctx, pr, side, radix_bits, bits2, null_policy);
-  auto k = k_scatter1<K, PAY, kScatterThreads, Cfg<K>::kItems1>;
+  constexpr int NT1 = scatter_threads<K, PAY>();
+  auto k = k_scatter1<K, PAY, NT1, tile1<K>() / NT1>;
   const size_t smem = size_t(tile1<K>()) * sizeof(Tuple<K, PAY>);
   HJ_TRY(set_smem(ctx, k, smem));
-  k<<<ps.G, kScatterThreads, smem, st>>>(a);
+  k<<<ps.G, NT1, smem, st>>>(a);
   HJ_LAUNCH_CHECK(ctx, "k_scatter1");
   nl->n++;
   return HJ_OK;
@@ -412,12 +416,13 @@ int stage_pass2(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, in
   if (!pr.meta.n_tiles || !bits2) return HJ_OK;
   ScatterArgs<K, PAY> a = scatter_args<K, PAY>(ctx, pr, side, radix_bits, bits2, kNullAsValue);
   a.out = static_cast<Tuple<K, PAY>*>(ctx->tup_b[side].p);
-  auto k = k_scatter2<K, PAY, kScatterThreads, Cfg<K>::kItems2>;
+  constexpr int NT2 = scatter_threads<K, PAY>();
+  auto k = k_scatter2<K, PAY, NT2, tile2<K>() / NT2>;
   const size_t smem = size_t(tile2<K>()) * sizeof(Tuple<K, PAY>);
   HJ_TRY(set_smem(ctx, k, smem));
   const uint32_t F1 = (1u << radix_bits) >> bits2;
   const uint32_t grid = (pr.meta.n_rows + tile2<K>() - 1) / tile2<K>() + F1;  // upper bound on sum(ceil(part / tile))
-  k<<<grid, kScatterThreads, smem, st>>>(a);
+  k<<<grid, NT2, smem, st>>>(a);
   HJ_LAUNCH_CHECK(ctx, "k_scatter2");
   nl->n++;
   return HJ_OK;
@@ -568,6 +573,8 @@ int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, in
     if (payload) {
       if constexpr (sizeof(Tuple<K, PAY>) > 8) HJ_TRY((launch_build_probe<K, PAY, kRidPayload>(ctx, a, st)));
       else return fail(ctx, HJ_ERR_INVALID, "RowID-carrying tuples need a tuple type with a payload");
+    } else if constexpr (PAY) {
+      return fail(ctx, HJ_ERR_INVALID, "payload tuples are only used by the sharded local join");
     } else if (fast_rowid) {
       HJ_TRY((launch_build_probe<K, PAY, kRidFast>(ctx, a, st)));
     } else {

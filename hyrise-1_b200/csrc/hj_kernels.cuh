@@ -260,7 +260,7 @@ __device__ __forceinline__ void copy_tile_out(const Tuple<K, PAY>* stage, const 
 // of the partition index; routed NULL rows form run number F1.
 // dynamic smem: TILE * sizeof(Tuple<K, PAY>).
 template <typename K, bool PAY, int NT, int ITEMS>
-__global__ void __launch_bounds__(NT, 4) k_scatter1(const ScatterArgs<K, PAY> a) {
+__global__ void __launch_bounds__(NT, 1024 / NT) k_scatter1(const ScatterArgs<K, PAY> a) {
   constexpr uint32_t TILE = NT * ITEMS;
   extern __shared__ __align__(16) unsigned char s_raw[];
   Tuple<K, PAY>* stage = reinterpret_cast<Tuple<K, PAY>*>(s_raw);
@@ -311,6 +311,17 @@ __global__ void __launch_bounds__(NT, 4) k_scatter1(const ScatterArgs<K, PAY> a)
         }
       }
     }
+    // rows that arrived through the multi-GPU exchange carry their global RowID in the tuple (idx = ChunkID, pad =
+    // ChunkOffset) instead of a position: positions of received rows mean nothing to the RowID mapping. The RowIDs are
+    // loaded together with the keys so that the tile pays the DRAM latency once.
+    constexpr bool kHasPayload = sizeof(Tuple<K, PAY>) > 8;
+    uint64_t rid[kHasPayload ? ITEMS : 1];
+    const bool exchanged = kHasPayload && seg.kind == kSegExchanged;
+    if (exchanged) {
+      const uint64_t* rids = static_cast<const uint64_t*>(seg.attr) + r0 + threadIdx.x;
+#pragma unroll
+      for (int j = 0; j < (kHasPayload ? ITEMS : 1); ++j) rid[j] = j * NT + threadIdx.x < n_in ? __ldg(rids + j * NT) : 0ull;
+    }
     uint32_t packed[ITEMS];  // digit << 16 | rank inside the digit, or kNoDigit
 #pragma unroll
     for (int j = 0; j < ITEMS; ++j) {
@@ -346,21 +357,17 @@ __global__ void __launch_bounds__(NT, 4) k_scatter1(const ScatterArgs<K, PAY> a)
     }
     __syncthreads();
     const uint32_t idx0 = seg.row_begin + r0 + threadIdx.x;
-    // rows that arrived through the multi-GPU exchange carry their global RowID in the tuple (idx = ChunkID, pad =
-    // ChunkOffset) instead of a position: positions of received rows mean nothing to the RowID mapping
-    const uint64_t* rids = seg.kind == kSegExchanged ? static_cast<const uint64_t*>(seg.attr) + r0 + threadIdx.x : nullptr;
 #pragma unroll
     for (int j = 0; j < ITEMS; ++j) {
       if (packed[j] != kNoDigit) {
         Tuple<K, PAY> t;
         t.key = key[j];
         t.idx = idx0 + j * NT;
-        if constexpr (sizeof(Tuple<K, PAY>) > 8) {
+        if constexpr (kHasPayload) {
           t.pad = 0;
-          if (rids) {
-            const uint64_t r = __ldg(rids + j * NT);
-            t.idx = static_cast<uint32_t>(r);
-            t.pad = static_cast<uint32_t>(r >> 32);
+          if (exchanged) {
+            t.idx = static_cast<uint32_t>(rid[j]);
+            t.pad = static_cast<uint32_t>(rid[j] >> 32);
           }
         }
         stage[s_loff[packed[j] >> 16] + (packed[j] & 0xFFFFu)] = t;
@@ -377,7 +384,7 @@ __global__ void __launch_bounds__(NT, 4) k_scatter1(const ScatterArgs<K, PAY> a)
 // (same-address atomics serialise at ~21 ns; profiles/r01_microbench_atomics_vs_match.txt).
 // dynamic smem: TILE * sizeof(Tuple<K, PAY>).
 template <typename K, bool PAY, int NT, int ITEMS>
-__global__ void __launch_bounds__(NT, 4) k_scatter2(const ScatterArgs<K, PAY> a) {
+__global__ void __launch_bounds__(NT, 1024 / NT) k_scatter2(const ScatterArgs<K, PAY> a) {
   constexpr uint32_t TILE = NT * ITEMS;
   extern __shared__ __align__(16) unsigned char s_raw[];
   Tuple<K, PAY>* stage = reinterpret_cast<Tuple<K, PAY>*>(s_raw);
