@@ -341,35 +341,44 @@ def main():
     # ---- e2e: same join through the C ABI from pinned host buffers, PosLists fetched to pinned host memory
     e2e = None
     if not args.no_e2e:
-        hb, hp = to_pinned_host(data["build"]), to_pinned_host(data["probe"])
-        build_host = relation_from_chunks(hj, [(c, a.numpy(), None if b is None else b.numpy()) for c, a, b in hb], abi.LOC_HOST)
-        probe_host = relation_from_chunks(hj, [(c, a.numpy(), None if b is None else b.numpy()) for c, a, b in hp], abi.LOC_HOST)
-        out_rows = int(info.n_rows * 1.05) + 1024  # per-rank result sizes vary a little between exchanges of equal data
-        out_b = torch.empty((out_rows, 2), dtype=torch.int32, pin_memory=True).numpy().view(np.uint32)
-        out_p = torch.empty((out_rows, 2), dtype=torch.int32, pin_memory=True).numpy().view(np.uint32)
-        h2d = input_bytes(hb) + input_bytes(hp)
-
-        def e2e_step():
+        ok = 1
+        try:
+            hb, hp = to_pinned_host(data["build"]), to_pinned_host(data["probe"])
+            build_host = relation_from_chunks(hj, [(c, a.numpy(), None if b is None else b.numpy()) for c, a, b in hb], abi.LOC_HOST)
+            probe_host = relation_from_chunks(hj, [(c, a.numpy(), None if b is None else b.numpy()) for c, a, b in hp], abi.LOC_HOST)
+            out_rows = int(info.n_rows * 1.05) + 1024  # per-rank result sizes vary a little between exchanges of equal data
+            out_b = torch.empty((out_rows, 2), dtype=torch.int32, pin_memory=True).numpy().view(np.uint32)
+            out_p = torch.empty((out_rows, 2), dtype=torch.int32, pin_memory=True).numpy().view(np.uint32)
+            h2d = input_bytes(hb) + input_bytes(hp)
+        except (RuntimeError, MemoryError) as exc:  # not enough pinnable host memory for N ranks x 25 GB
+            log(f"[rank {rank}] e2e leg: cannot pin the host buffers: {exc}")
+            ok = 0
+        if world > 1:  # every rank takes the same branch
+            okt = torch.tensor([ok], device=dev, dtype=torch.int32)
+            dist.all_reduce(okt, op=dist.ReduceOp.MIN)
+            ok = int(okt.item())
+        if ok:
+            def e2e_step():
+                if world > 1:
+                    inf_ = j.join_sharded(build_host, probe_host, abi.MODE_INNER, stream=stream)
+                else:
+                    inf_ = j.join(build_host, probe_host, abi.MODE_INNER, stream=stream)
+                j.fetch(out_b, out_p)
+                return inf_
+            e2e_step()
+            barrier()
+            n_e2e = max(1, min(args.steps, 3))
+            t1 = time.perf_counter()
+            for _ in range(n_e2e):
+                inf = e2e_step()
+            barrier()
+            e2e_s = (time.perf_counter() - t1) / n_e2e
             if world > 1:
-                inf = j.join_sharded(build_host, probe_host, abi.MODE_INNER, stream=stream)
-            else:
-                inf = j.join(build_host, probe_host, abi.MODE_INNER, stream=stream)
-            j.fetch(out_b, out_p)
-            return inf
-        e2e_step()
-        barrier()
-        n_e2e = max(1, min(args.steps, 3))
-        t1 = time.perf_counter()
-        for _ in range(n_e2e):
-            inf = e2e_step()
-        barrier()
-        e2e_s = (time.perf_counter() - t1) / n_e2e
-        if world > 1:
-            tt = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            e2e_s = float(tt.item())
-        e2e = {"value": total_tuples / e2e_s, "unit": unit, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": inf.n_rows * 16,
-               "ms_per_step": e2e_s * 1e3, "steps": n_e2e}
+                tt = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                e2e_s = float(tt.item())
+            e2e = {"value": total_tuples / e2e_s, "unit": unit, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": inf.n_rows * 16,
+                   "ms_per_step": e2e_s * 1e3, "steps": n_e2e}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
