@@ -309,8 +309,9 @@ def main():
     w_in = {"dict": 4 + 4, "value": k}[encoding]  # attr + amortised dictionary bytes per row for 1 Mi-row chunks
     mean_ms = {p_: float(np.mean([t[p_] for t in phase_ms])) for p_ in abi.PHASES}
     n_local = info.n_build_tuples + info.n_probe_tuples  # rows this rank partitions and joins (after the exchange)
-    phase_bytes = {"materialize": n_local * w_in, "scatter1": n_local * (w_in + t_bytes), "scatter2": n_local * 2 * t_bytes,
-                   "build_probe": n_local * t_bytes + info.n_rows * 16}
+    t_real = 8 if dtype == "int32" else 16  # this implementation's partitioned tuple: (key, 4-byte position)
+    phase_bytes = {"materialize": n_local * w_in, "scatter1": n_local * (w_in + t_real), "scatter2": n_local * 2 * t_real,
+                   "build_probe": n_local * t_real + info.n_rows * 16}
     phase_kernel = {"materialize": "k_materialize_hist", "scatter1": "k_scatter1", "scatter2": "k_scatter2",
                     "build_probe": "k_build_probe"}
     dom = max(phase_bytes, key=lambda p_: mean_ms[p_])
