@@ -29,7 +29,8 @@ template <> struct Cfg<int64_t> {
   static constexpr int kCap = 6144;
 };
 constexpr int kScatterThreads = 256;
-constexpr int kHistThreads = 512;
+constexpr int kHistThreads = 1024;        // K1: one physical CTA per SM ...
+constexpr int kHistVirtual = 4;           // ... hosting 4 virtual CTAs of 256 threads (one wave of all 4 x #SM tile owners)
 constexpr int kJoinThreads = 1024;
 constexpr int kProbeV = 4;
 constexpr uint32_t kProbeSlice = 128 * 1024;
@@ -334,6 +335,7 @@ int stage_alloc(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, in
   const uint32_t P = 1u << radix_bits, F1 = P >> bits2;
   const uint32_t n = pr.meta.n_rows;
   ps->G = std::max<uint32_t>(1, std::min<uint32_t>(pr.meta.n_tiles, uint32_t(kVirtualCtasPerSm) * ctx->n_sms));
+  ps->G = (ps->G + kHistVirtual - 1) / kHistVirtual * kHistVirtual;  // K1 hosts kHistVirtual virtual CTAs per physical CTA
   HJ_TRY(ensure(ctx, ctx->hist[side], (size_t(P) + 1) * 4));
   HJ_TRY(ensure(ctx, ctx->hist1[side], size_t(ps->G) * (F1 + 1) * 4));
   HJ_TRY(ensure(ctx, ctx->part_off[side], (size_t(P) + 2) * 4));
@@ -357,10 +359,10 @@ int stage_hist(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int
   auto* hist1 = static_cast<uint32_t*>(ctx->hist1[side].p);
   HJ_CUDA(ctx, cudaMemsetAsync(hist, 0, (size_t(P) + 1) * 4, st));
   if (pr.meta.n_tiles) {
-    auto k1 = k_materialize_hist<K, kHistThreads, tile1<K>()>;
+    auto k1 = k_materialize_hist<K, kHistThreads, kHistVirtual, tile1<K>()>;
     const size_t smem = (size_t(P) + 1) * 4;
     HJ_TRY(set_smem(ctx, k1, smem));
-    k1<<<ps.G, kHistThreads, smem, st>>>(pr.meta, static_cast<K*>(ctx->keys_mat[side].p),
+    k1<<<ps.G / kHistVirtual, kHistThreads, smem, st>>>(pr.meta, static_cast<K*>(ctx->keys_mat[side].p),
                                          static_cast<uint32_t*>(ctx->valid_mask[side].p), hist, hist1, radix_bits, bits2,
                                          null_policy);
     HJ_LAUNCH_CHECK(ctx, "k_materialize_hist");

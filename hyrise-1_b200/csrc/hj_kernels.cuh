@@ -58,82 +58,103 @@ __global__ void k_fill_tile_seg(const DevSegment* __restrict__ segs, uint32_t n_
 //   to the global histogram and stores its own level-1 digit counts to hist1[d * G + c].
 // block: NT threads, dynamic smem: (2^radix_bits + 1) * 4 bytes.
 // =====================================================================================================================
-template <typename K, int NT, int TILE>
+// One physical CTA of NT threads hosts VC virtual CTAs of NT/VC threads that share ONE full-resolution histogram (it is
+// summed globally anyway) and keep their own level-1 digit counts. With VC = 4 and 1024 threads all 4 x #SM virtual CTAs
+// are resident at once, so they sweep the chunks together and a chunk's dictionary is pulled into L2 once instead of
+// once per wave (v1: 2 CTAs/SM because of the 64 KB histogram => two waves => 15.6 GB of DRAM reads for 1 G probe rows).
+template <typename K, int NT, int VC, int TILE>
 __global__ void __launch_bounds__(NT) k_materialize_hist(RelMeta rel, K* __restrict__ keys_mat,
                                                          uint32_t* __restrict__ valid_mask,
                                                          uint32_t* __restrict__ hist, uint32_t* __restrict__ hist1,
                                                          int radix_bits, int bits2, int null_policy) {
+  constexpr int VT = NT / VC;         // threads per virtual CTA
+  constexpr int ITEMS = TILE / VT;
   extern __shared__ uint32_t s_hist[];
+  __shared__ uint32_t s_dcnt[VC > 1 ? VC : 1][kMaxDigits + 1];
   const uint32_t P = 1u << radix_bits;
   const uint32_t n_bins = P + 1u;  // last bin: NULL rows routed aside (kNullRoute)
   const uint32_t pmask = P - 1u;
+  const uint32_t F1 = P >> bits2;
+  const uint32_t v = threadIdx.x / VT, vt = threadIdx.x % VT;
+  const uint32_t G = gridDim.x * VC, c = blockIdx.x * VC + v;  // virtual grid / this thread's virtual CTA
   for (uint32_t b = threadIdx.x; b < n_bins; b += NT) s_hist[b] = 0;
+  if (VC > 1)
+    for (uint32_t d = vt; d <= F1; d += VT) s_dcnt[v][d] = 0;
   __syncthreads();
 
-  constexpr int ITEMS = TILE / NT;
-  for (uint32_t tile = blockIdx.x; tile < rel.n_tiles; tile += gridDim.x) {
+  for (uint32_t tile = c; tile < rel.n_tiles; tile += G) {
     const uint32_t seg_idx = __ldg(rel.tile_seg + tile);
     const DevSegment s = rel.segs[seg_idx];
     const uint32_t r0 = (tile - s.tile_begin) * TILE;
     const uint32_t cnt = min(static_cast<uint32_t>(TILE), s.n_rows - r0);
     K key[ITEMS];
-    bool valid[ITEMS], active[ITEMS];
+    uint32_t vbits = 0;  // bit u: row u*VT+vt is valid (non-NULL)
     if (s.kind == 1) {
       uint32_t vid[ITEMS];
 #pragma unroll
       for (int u = 0; u < ITEMS; ++u) {
-        const uint32_t i = u * NT + threadIdx.x;
-        active[u] = i < cnt;
-        vid[u] = active[u] ? load_attr(s, r0 + i) : s.null_value_id;
+        const uint32_t i = u * VT + vt;
+        vid[u] = i < cnt ? load_attr(s, r0 + i) : s.null_value_id;
       }
 #pragma unroll
       for (int u = 0; u < ITEMS; ++u) {
-        valid[u] = active[u] && vid[u] != s.null_value_id;
-        key[u] = valid[u] ? load_plain_key<K>(s, vid[u]) : K(0);  // NULL decodes to T{} (dictionary_column_iterable.hpp:80)
+        const bool valid = vid[u] != s.null_value_id;  // rows past the end carry null_value_id
+        key[u] = valid ? load_plain_key<K>(s, vid[u]) : K(0);  // NULL decodes to T{} (dictionary_column_iterable.hpp:80)
+        vbits |= (valid ? 1u : 0u) << u;
       }
 #pragma unroll
       for (int u = 0; u < ITEMS; ++u) {
-        const uint32_t i = u * NT + threadIdx.x;
-        if (active[u]) keys_mat[s.row_begin + r0 + i] = key[u];
-        const uint32_t bits = __ballot_sync(0xffffffffu, valid[u]);
+        const uint32_t i = u * VT + vt;
+        if (i < cnt) keys_mat[s.row_begin + r0 + i] = key[u];
+        const uint32_t bits = __ballot_sync(0xffffffffu, (vbits >> u) & 1u);
         // one warp instruction covers 32 consecutive rows starting at a multiple of 32
-        if (lane_id() == 0 && active[u]) valid_mask[s.mask_word_begin + ((r0 + i) >> 5)] = bits;
+        if (lane_id() == 0 && i < cnt) valid_mask[s.mask_word_begin + ((r0 + i) >> 5)] = bits;
       }
     } else {
 #pragma unroll
       for (int u = 0; u < ITEMS; ++u) {
-        const uint32_t i = u * NT + threadIdx.x;
-        active[u] = i < cnt;
-        key[u] = active[u] ? load_plain_key<K>(s, r0 + i) : K(0);
-        valid[u] = active[u] && !(s.nulls && __ldg(s.nulls + r0 + i));
-        if (s.kind == 2 && !valid[u]) key[u] = K(0);  // GATHERED NULL yields T{} (reference_column_iterable.hpp:60)
+        const uint32_t i = u * VT + vt;
+        key[u] = K(0);
+        if (i < cnt) {
+          key[u] = load_plain_key<K>(s, r0 + i);
+          const bool valid = !(s.nulls && __ldg(s.nulls + r0 + i));
+          if (s.kind == 2 && !valid) key[u] = K(0);  // GATHERED NULL yields T{} (reference_column_iterable.hpp:60)
+          vbits |= (valid ? 1u : 0u) << u;
+        }
       }
     }
 #pragma unroll
     for (int u = 0; u < ITEMS; ++u) {
-      if (!active[u]) continue;
-      if (valid[u] || null_policy == kNullAsValue) {
-        atomicAdd(&s_hist[hash_key(key[u]) & pmask], 1u);
+      if (u * VT + vt >= cnt) continue;
+      if (((vbits >> u) & 1u) || null_policy == kNullAsValue) {
+        const uint32_t p = hash_key(key[u]) & pmask;
+        atomicAdd(&s_hist[p], 1u);
+        if (VC > 1) atomicAdd(&s_dcnt[v][p >> bits2], 1u);
       } else if (null_policy == kNullRoute) {
         atomicAdd(&s_hist[P], 1u);
+        if (VC > 1) atomicAdd(&s_dcnt[v][F1], 1u);
       }
     }
   }
   __syncthreads();
   for (uint32_t b = threadIdx.x; b < n_bins; b += NT) {
-    const uint32_t c = s_hist[b];
-    if (c) atomicAdd(hist + b, c);
+    const uint32_t cb = s_hist[b];
+    if (cb) atomicAdd(hist + b, cb);
   }
-  // this CTA's level-1 digit counts (digit F1 = routed NULLs)
-  const uint32_t F1 = P >> bits2, F2 = 1u << bits2;
-  for (uint32_t d = threadIdx.x; d <= F1; d += NT) {
-    uint32_t sum = 0;
-    if (d == F1) {
-      sum = s_hist[P];
-    } else {
-      for (uint32_t q = 0; q < F2; ++q) sum += s_hist[(d << bits2) + ((q + d) & (F2 - 1u))];  // rotated: no bank conflicts
+  // the virtual CTAs' level-1 digit counts (digit F1 = routed NULLs)
+  if (VC > 1) {
+    for (uint32_t d = vt; d <= F1; d += VT) hist1[d * G + c] = s_dcnt[v][d];
+  } else {
+    const uint32_t F2 = 1u << bits2;
+    for (uint32_t d = threadIdx.x; d <= F1; d += NT) {
+      uint32_t sum = 0;
+      if (d == F1) {
+        sum = s_hist[P];
+      } else {
+        for (uint32_t q = 0; q < F2; ++q) sum += s_hist[(d << bits2) + ((q + d) & (F2 - 1u))];  // rotated: no bank conflicts
+      }
+      hist1[d * G + c] = sum;
     }
-    hist1[d * gridDim.x + blockIdx.x] = sum;
   }
 }
 
