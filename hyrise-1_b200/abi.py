@@ -14,6 +14,7 @@ LOC_HOST, LOC_DEVICE = 0, 1
 FLAG_SQL_NULL_PROBE = 0x1
 FLAG_TIMINGS = 0x2
 FLAG_XCHG_STAGED = 0x4
+FLAG_TWO_SWEEP_PARTITION = 0x8
 INVALID_CHUNK_ID = 0xFFFFFFFF
 INVALID_CHUNK_OFFSET = 0xFFFFFFFF
 N_PHASES = 10

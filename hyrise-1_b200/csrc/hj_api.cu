@@ -9,6 +9,7 @@
 
 #include "hj.h"
 #include "hj_kernels.cuh"
+#include "hj_fused.cuh"
 
 using namespace hj;
 
@@ -36,6 +37,7 @@ constexpr int kProbeV = 4;
 constexpr uint32_t kProbeSlice = 128 * 1024;
 constexpr int kSinglePassMaxBits = 8;
 constexpr int kMinChunkShift = 8, kMaxChunkShift = 14;  // result chunks of 256 .. 16 Ki rows
+constexpr int kPart1Virtual = 2;             // fused P1: 2 virtual CTAs of 512 threads (shared memory is L1 taken from the gather)
 constexpr int kVirtualCtasPerSm = 4;       // K1 / pass 1 tile ownership: G = min(n_tiles, 4 * SMs) virtual CTAs
 template <typename K> constexpr int tile1() { return kScatterThreads * Cfg<K>::kItems1; }
 template <typename K> constexpr int tile2() { return kScatterThreads * Cfg<K>::kItems2; }
@@ -61,7 +63,7 @@ struct hj_ctx {
   std::vector<DevBuf*> all_bufs;
   // per relation (0 = build, 1 = probe)
   DevBuf stage_in[2], segs[2], tile_seg[2], seg_row_begin[2], keys_mat[2], valid_mask[2];
-  DevBuf hist[2], hist1[2], part_off[2], cur2[2], l1_tiles[2], tup_a[2], tup_b[2];
+  DevBuf hist[2], hist1[2], part_off[2], cur2[2], l1_tiles[2], tup_a[2], tup_b[2], frag[2];
   DevBuf items, fin, plan, queue, out_state, out_tails, compact_plan, compact_used, compact_hole, compact_src, matched, out_build, out_probe, misc;
   void* pinned = nullptr;  // small pinned readback area
   cudaEvent_t ev[16] = {};
@@ -87,7 +89,7 @@ struct hj_ctx {
     for (DevBuf* b : {&stage_in[0], &stage_in[1], &segs[0], &segs[1], &tile_seg[0], &tile_seg[1], &seg_row_begin[0],
                       &seg_row_begin[1], &keys_mat[0], &keys_mat[1], &valid_mask[0], &valid_mask[1], &hist[0], &hist[1],
                       &part_off[0], &part_off[1], &hist1[0], &hist1[1], &cur2[0], &cur2[1], &l1_tiles[0], &l1_tiles[1],
-                      &tup_a[0], &tup_a[1], &tup_b[0], &tup_b[1], &items, &fin, &plan, &queue, &out_state, &out_tails, &compact_plan, &compact_used, &compact_hole, &compact_src, &matched,
+                      &tup_a[0], &tup_a[1], &tup_b[0], &tup_b[1], &frag[0], &frag[1], &items, &fin, &plan, &queue, &out_state, &out_tails, &compact_plan, &compact_used, &compact_hole, &compact_src, &matched,
                       &out_build, &out_probe, &misc, &xchg_counts[0], &xchg_counts[1], &xchg_cnt_dev, &xchg_send_keys[0],
                       &xchg_send_keys[1], &xchg_send_rids[0], &xchg_send_rids[1], &xchg_send_nulls[0], &xchg_send_nulls[1],
                       &xchg_recv_keys[0], &xchg_recv_keys[1], &xchg_recv_rids[0], &xchg_recv_rids[1], &xchg_recv_nulls[0],
@@ -327,8 +329,16 @@ int set_smem(hj_ctx* ctx, KernelT kernel, size_t bytes) {
 
 // ---- partitioning stages for one relation ------------------------------------------------------------------------------
 struct PartState {
-  uint32_t G = 0;  // virtual CTAs of K1 / pass 1
+  uint32_t G = 0;      // virtual CTAs of K1 / pass 1
+  bool fused = false;  // hj_fused.cuh: slab-local pass 1 inside the histogram kernel, fragment-gathering pass 2
+  uint32_t gs = 0;     // fused: slabs per pass-2 work item
 };
+
+// P1's dynamic shared memory: the full-resolution histogram + one staging tile per virtual CTA
+template <typename K>
+size_t part1_smem(int radix_bits) {
+  return ((((size_t(1) << radix_bits) + 1) * 4 + 15) & ~size_t(15)) + size_t(kPart1Virtual) * tile1<K>() * (sizeof(K) + 2);
+}
 
 template <typename K, bool PAY>
 int stage_alloc(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int bits2, PartState* ps) {
@@ -336,14 +346,19 @@ int stage_alloc(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, in
   const uint32_t n = pr.meta.n_rows;
   ps->G = std::max<uint32_t>(1, std::min<uint32_t>(pr.meta.n_tiles, uint32_t(kVirtualCtasPerSm) * ctx->n_sms));
   ps->G = (ps->G + kHistVirtual - 1) / kHistVirtual * kHistVirtual;  // K1 hosts kHistVirtual virtual CTAs per physical CTA
+  ps->fused = !PAY && bits2 > 0 && !(ctx->opts.flags & HJ_FLAG_TWO_SWEEP_PARTITION);
+  if (ps->fused) {
+    ps->gs = std::max<uint32_t>(1, F1 * 7 / 8);  // an item gathers gs fragments of tile1/F1 tuples on average: 7/8 of a tile
+    HJ_TRY(ensure(ctx, ctx->frag[side], std::max<size_t>(1, pr.meta.n_tiles) * (F1 + 2) * 2));
+  }
   HJ_TRY(ensure(ctx, ctx->hist[side], (size_t(P) + 1) * 4));
-  HJ_TRY(ensure(ctx, ctx->hist1[side], size_t(ps->G) * (F1 + 1) * 4));
+  if (!ps->fused) HJ_TRY(ensure(ctx, ctx->hist1[side], size_t(ps->G) * (F1 + 1) * 4));
   HJ_TRY(ensure(ctx, ctx->part_off[side], (size_t(P) + 2) * 4));
-  HJ_TRY(ensure(ctx, ctx->cur2[side], size_t(P) * 4));
+  HJ_TRY(ensure(ctx, ctx->cur2[side], (size_t(P) + 1) * 4));
   HJ_TRY(ensure(ctx, ctx->l1_tiles[side], (size_t(F1) + 1) * 4));
   HJ_TRY(ensure(ctx, ctx->tup_a[side], std::max<size_t>(1, n) * sizeof(Tuple<K, PAY>)));
   if (bits2) HJ_TRY(ensure(ctx, ctx->tup_b[side], std::max<size_t>(1, n) * sizeof(Tuple<K, PAY>)));
-  if (pr.has_dict) {
+  if (pr.has_dict && !ps->fused) {
     HJ_TRY(ensure(ctx, ctx->keys_mat[side], std::max<size_t>(1, n) * sizeof(K)));
     HJ_TRY(ensure(ctx, ctx->valid_mask[side], std::max<size_t>(1, pr.mask_words) * 4));
   }
@@ -358,6 +373,24 @@ int stage_hist(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int
   auto* hist = static_cast<uint32_t*>(ctx->hist[side].p);
   auto* hist1 = static_cast<uint32_t*>(ctx->hist1[side].p);
   HJ_CUDA(ctx, cudaMemsetAsync(hist, 0, (size_t(P) + 1) * 4, st));
+  if (ps.fused) {
+    if (pr.meta.n_tiles) {
+      auto k = k_part1<K, kHistThreads, kPart1Virtual, tile1<K>()>;
+      const size_t smem = part1_smem<K>(radix_bits);
+      HJ_TRY(set_smem(ctx, k, smem));
+      const uint32_t grid = std::min<uint32_t>((pr.meta.n_tiles + kPart1Virtual - 1) / kPart1Virtual, ctx->n_sms);
+      k<<<grid, kHistThreads, smem, st>>>(pr.meta, static_cast<Tuple<K, false>*>(ctx->tup_a[side].p),
+                                          static_cast<uint16_t*>(ctx->frag[side].p), hist, radix_bits, bits2, null_policy);
+      HJ_LAUNCH_CHECK(ctx, "k_part1");
+      nl->n++;
+    }
+    k_offsets<1024><<<1, 1024, 0, st>>>(hist, static_cast<uint32_t*>(ctx->part_off[side].p),
+                                        static_cast<uint32_t*>(ctx->cur2[side].p),
+                                        static_cast<uint32_t*>(ctx->l1_tiles[side].p), radix_bits, bits2, tile2<K>());
+    HJ_LAUNCH_CHECK(ctx, "k_offsets");
+    nl->n++;
+    return HJ_OK;
+  }
   if (pr.meta.n_tiles) {
     auto k1 = k_materialize_hist<K, kHistThreads, kHistVirtual, tile1<K>()>;
     const size_t smem = (size_t(P) + 1) * 4;
@@ -401,7 +434,7 @@ ScatterArgs<K, PAY> scatter_args(hj_ctx* ctx, const PreparedRel& pr, int side, i
 template <typename K, bool PAY>
 int stage_pass1(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int bits2, int null_policy,
                 const PartState& ps, cudaStream_t st, Launches* nl) {
-  if (!pr.meta.n_tiles) return HJ_OK;
+  if (!pr.meta.n_tiles || ps.fused) return HJ_OK;
   ScatterArgs<K, PAY> a = scatter_args<K, PAY>(ctx, pr, side, radix_bits, bits2, null_policy);
   constexpr int NT1 = scatter_threads<K, PAY>();
   auto k = k_scatter1<K, PAY, NT1, tile1<K>() / NT1>;
@@ -414,8 +447,28 @@ int stage_pass1(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, in
 }
 
 template <typename K, bool PAY>
-int stage_pass2(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int bits2, cudaStream_t st, Launches* nl) {
+int stage_pass2(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int bits2, int null_policy,
+                const PartState& ps, cudaStream_t st, Launches* nl) {
   if (!pr.meta.n_tiles || !bits2) return HJ_OK;
+  if constexpr (!PAY) {
+    if (ps.fused) {
+      constexpr int NT = kScatterThreads;
+      auto k = k_scatter2f<K, NT, tile2<K>() / NT>;
+      const size_t smem = size_t(tile2<K>()) * sizeof(Tuple<K, false>);
+      HJ_TRY(set_smem(ctx, k, smem));
+      const uint32_t F1 = (1u << radix_bits) >> bits2;
+      const uint32_t n_digits = F1 + (null_policy == kNullRoute ? 1u : 0u);
+      const uint64_t grid = uint64_t((pr.meta.n_tiles + ps.gs - 1) / ps.gs) * n_digits;
+      if (grid > 0x7FFFFFFFull) return fail(ctx, HJ_ERR_TOO_LARGE, "pass 2: %llu work items", (unsigned long long)grid);
+      k<<<uint32_t(grid), NT, smem, st>>>(static_cast<const Tuple<K, false>*>(ctx->tup_a[side].p),
+                                          static_cast<const uint16_t*>(ctx->frag[side].p), pr.meta, uint32_t(tile1<K>()),
+                                          static_cast<Tuple<K, false>*>(ctx->tup_b[side].p),
+                                          static_cast<uint32_t*>(ctx->cur2[side].p), radix_bits, bits2, ps.gs, n_digits);
+      HJ_LAUNCH_CHECK(ctx, "k_scatter2f");
+      nl->n++;
+      return HJ_OK;
+    }
+  }
   ScatterArgs<K, PAY> a = scatter_args<K, PAY>(ctx, pr, side, radix_bits, bits2, kNullAsValue);
   a.out = static_cast<Tuple<K, PAY>*>(ctx->tup_b[side].p);
   constexpr int NT2 = scatter_threads<K, PAY>();
@@ -497,12 +550,13 @@ int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, in
   HJ_TRY(stage_pass1<K, PAY>(ctx, pb, 0, radix_bits, bits2, kNullDrop, sb, st, &nl));
   HJ_TRY(stage_pass1<K, PAY>(ctx, pp, 1, radix_bits, bits2, probe_null_policy, sp, st, &nl));
   HJ_CUDA(ctx, cudaEventRecord(ev[3], st));
-  HJ_TRY(stage_pass2<K, PAY>(ctx, pb, 0, radix_bits, bits2, st, &nl));
-  HJ_TRY(stage_pass2<K, PAY>(ctx, pp, 1, radix_bits, bits2, st, &nl));
+  HJ_TRY(stage_pass2<K, PAY>(ctx, pb, 0, radix_bits, bits2, kNullDrop, sb, st, &nl));
+  HJ_TRY(stage_pass2<K, PAY>(ctx, pp, 1, radix_bits, bits2, probe_null_policy, sp, st, &nl));
   HJ_CUDA(ctx, cudaEventRecord(ev[4], st));
   const auto* tb = static_cast<const Tuple<K, PAY>*>(bits2 ? ctx->tup_b[0].p : ctx->tup_a[0].p);
   const auto* tp = static_cast<const Tuple<K, PAY>*>(bits2 ? ctx->tup_b[1].p : ctx->tup_a[1].p);
-  const auto* tp1 = static_cast<const Tuple<K, PAY>*>(ctx->tup_a[1].p);  // routed NULL rows stay in pass 1's output
+  // routed NULL rows stay in pass 1's output; the fused path's pass 2 moves them behind the last partition of ITS output
+  const auto* tp1 = sp.fused ? tp : static_cast<const Tuple<K, PAY>*>(ctx->tup_a[1].p);
 
   // ---- plan
   const uint32_t cap = Cfg<K>::kCap;

@@ -196,4 +196,31 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* scratc
   return r;
 }
 
+// ---- virtual CTAs: one physical CTA hosts several groups of VT threads that synchronise among themselves only
+// barrier over the VT threads of virtual CTA v (hardware barriers 1..15; 0 is __syncthreads)
+__device__ __forceinline__ void vbar(uint32_t v, uint32_t n_threads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(v + 1u), "r"(n_threads) : "memory");
+}
+
+// block_excl_scan over one virtual CTA (vt = thread index inside it); scratch: 33 words per virtual CTA
+template <int VT>
+__device__ __forceinline__ uint32_t vblock_excl_scan(uint32_t val, uint32_t v, uint32_t vt, uint32_t* scratch, uint32_t* total) {
+  const uint32_t incl = warp_incl_scan(val);
+  const uint32_t w = vt >> 5;
+  if ((vt & 31u) == 31u) scratch[w] = incl;
+  vbar(v, VT);
+  if (w == 0) {
+    constexpr uint32_t nw = VT / 32;
+    const uint32_t x = (vt & 31u) < nw ? scratch[vt & 31u] : 0u;
+    const uint32_t xi = warp_incl_scan(x);
+    scratch[vt & 31u] = xi - x;
+    if ((vt & 31u) == 31u) scratch[32] = xi;
+  }
+  vbar(v, VT);
+  *total = scratch[32];
+  const uint32_t r = scratch[w] + incl - val;
+  vbar(v, VT);
+  return r;
+}
+
 }  // namespace hj

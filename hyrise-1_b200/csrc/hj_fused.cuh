@@ -1,0 +1,245 @@
+// hj_fused.cuh — the two-pass partitioning path for radix_bits > 8 without a separate histogram pass over the input.
+//
+//  P1 k_part1     replaces materialize_input + the first half of partition_radix_parallel (join_hash.cpp:203-355):
+//                 decode (dictionary gather ONCE), full-resolution histogram, and a SLAB-LOCAL level-1 partitioning:
+//                 every 4096-row tile is grouped by its level-1 digit in shared memory and written back to the tile's
+//                 own place in the tuple buffer, plus a 130-entry offset table per tile ("fragments"). Grouping a tile
+//                 needs no global offsets, hence no histogram BEFORE the scatter: K1's decoded-key round trip (4 B
+//                 written + 4 B read per row) and pass 1's second sweep over the input disappear.
+//  P2 k_scatter2f replaces the second half: a CTA gathers the fragments of ONE level-1 digit from a group of consecutive
+//                 slabs (expected 4096 tuples), ranks them by the low digit, reserves the runs with one global atomic per
+//                 final partition and writes them out — the final layout is the same contiguous partition array the
+//                 one-histogram path produces, so K4/K5 are unchanged.
+//  P3 k_emit_null_probe_frag  K7 for this layout (routed NULL probe rows live in each slab's last fragment).
+//
+// v1/v2 of the library (K1 + k_scatter1 + k_scatter2) spent 6.3 + 5.0 + 4.0 ms here on C2; see DESIGN.md §4.
+#pragma once
+#include "hj_kernels.cuh"
+
+namespace hj {
+
+// =====================================================================================================================
+// P1. One physical CTA of NT threads hosts VC virtual CTAs of VT = NT/VC threads (as K1 does) that share the
+// full-resolution histogram; every virtual CTA has its own staging tile. Virtual CTA c owns tiles c, c+G, ...
+// frag[tile * (F1 + 2) + d]: offset of digit d's fragment inside the slab; [F1] = routed NULL rows; [F1 + 1] = rows kept.
+// A tile is staged as keys + 16-bit row numbers inside the tile (6 instead of 8 bytes per int32 row): shared memory is L1
+// taken away from the dictionary gather, whose rate is set by the L1 lines that can be in flight — measured on C2 (14
+// radix bits, 64 KB histogram): 4 virtual CTAs with 8-byte staging (228 KB carve-out) 28 ms, 2 virtual CTAs 8.9 ms.
+// dynamic smem: (2^radix_bits + 1) * 4 (rounded up to 16) + VC * TILE * (sizeof(K) + 2).
+// =====================================================================================================================
+template <typename K, int NT, int VC, int TILE>
+__global__ void __launch_bounds__(NT) k_part1(RelMeta rel, Tuple<K, false>* __restrict__ out1, uint16_t* __restrict__ frag,
+                                              uint32_t* __restrict__ hist, int radix_bits, int bits2, int null_policy) {
+  using T = Tuple<K, false>;
+  constexpr int VT = NT / VC;
+  constexpr int ITEMS = TILE / VT;
+  static_assert(VT >= kMaxDigits && TILE <= 65535, "one thread per digit in the scan; 16-bit fragment offsets");
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  uint32_t* s_hist = reinterpret_cast<uint32_t*>(s_raw);
+  const uint32_t P = 1u << radix_bits;
+  const uint32_t n_bins = P + 1u;
+  unsigned char* stage_raw = s_raw + ((n_bins * 4u + 15u) & ~15u);
+  __shared__ uint32_t s_cnt[VC][kMaxDigits + 1], s_loff[VC][kMaxDigits + 2], s_scratch[VC][33];
+  const uint32_t pmask = P - 1u;
+  const uint32_t F1 = P >> bits2, FS = F1 + 2u;
+  const uint32_t v = threadIdx.x / VT, vt = threadIdx.x % VT;
+  const uint32_t G = gridDim.x * VC, c = blockIdx.x * VC + v;
+  K* skey = reinterpret_cast<K*>(stage_raw) + v * TILE;
+  uint16_t* srow = reinterpret_cast<uint16_t*>(stage_raw + VC * TILE * sizeof(K)) + v * TILE;
+  for (uint32_t b = threadIdx.x; b < n_bins; b += NT) s_hist[b] = 0;
+  __syncthreads();
+
+  for (uint32_t tile = c; tile < rel.n_tiles; tile += G) {
+    const DevSegment s = rel.segs[__ldg(rel.tile_seg + tile)];
+    const uint32_t r0 = (tile - s.tile_begin) * TILE;
+    const uint32_t cnt = min(static_cast<uint32_t>(TILE), s.n_rows - r0);
+    for (uint32_t d = vt; d <= F1; d += VT) s_cnt[v][d] = 0;
+    vbar(v, VT);  // also orders the previous tile's copy-out before this tile's staging
+
+    K key[ITEMS];
+    uint32_t vbits = 0;  // bit u: row u*VT+vt is valid (non-NULL)
+    if (s.kind == 1) {
+      uint32_t vid[ITEMS];
+#pragma unroll
+      for (int u = 0; u < ITEMS; ++u) {
+        const uint32_t i = u * VT + vt;
+        vid[u] = i < cnt ? load_attr(s, r0 + i) : s.null_value_id;
+      }
+#pragma unroll
+      for (int u = 0; u < ITEMS; ++u) {
+        const bool valid = vid[u] != s.null_value_id;  // rows past the end carry null_value_id
+        key[u] = valid ? load_plain_key<K>(s, vid[u]) : K(0);  // NULL decodes to T{} (dictionary_column_iterable.hpp:80)
+        vbits |= (valid ? 1u : 0u) << u;
+      }
+    } else {
+#pragma unroll
+      for (int u = 0; u < ITEMS; ++u) {
+        const uint32_t i = u * VT + vt;
+        key[u] = K(0);
+        if (i < cnt) {
+          key[u] = load_plain_key<K>(s, r0 + i);
+          const bool valid = !(s.nulls && __ldg(s.nulls + r0 + i));
+          if (s.kind == 2 && !valid) key[u] = K(0);  // GATHERED NULL yields T{} (reference_column_iterable.hpp:60)
+          vbits |= (valid ? 1u : 0u) << u;
+        }
+      }
+    }
+    uint32_t packed[ITEMS];  // digit << 16 | rank inside the digit, or kNoDigit
+#pragma unroll
+    for (int u = 0; u < ITEMS; ++u) {
+      packed[u] = kNoDigit;
+      if (u * VT + vt < cnt) {
+        uint32_t d = kNoDigit;
+        if (((vbits >> u) & 1u) || null_policy == kNullAsValue) {
+          const uint32_t p = hash_key(key[u]) & pmask;
+          atomicAdd(&s_hist[p], 1u);
+          d = p >> bits2;
+        } else if (null_policy == kNullRoute) {
+          atomicAdd(&s_hist[P], 1u);
+          d = F1;
+        }
+        if (d != kNoDigit) packed[u] = (d << 16) | atomicAdd(&s_cnt[v][d], 1u);
+      }
+    }
+    vbar(v, VT);
+    {
+      const uint32_t cd = vt < F1 ? s_cnt[v][vt] : 0u;
+      uint32_t total;
+      const uint32_t ex = vblock_excl_scan<VT>(cd, v, vt, s_scratch[v], &total);
+      if (vt < F1) s_loff[v][vt] = ex;
+      if (vt == 0) {
+        s_loff[v][F1] = total;
+        s_loff[v][F1 + 1] = total + s_cnt[v][F1];
+      }
+    }
+    vbar(v, VT);
+#pragma unroll
+    for (int u = 0; u < ITEMS; ++u) {
+      if (packed[u] != kNoDigit) {
+        const uint32_t pos = s_loff[v][packed[u] >> 16] + (packed[u] & 0xFFFFu);
+        skey[pos] = key[u];
+        srow[pos] = static_cast<uint16_t>(u * VT + vt);
+      }
+    }
+    for (uint32_t d = vt; d < FS; d += VT) frag[static_cast<size_t>(tile) * FS + d] = static_cast<uint16_t>(s_loff[v][d]);
+    vbar(v, VT);
+    const uint32_t n_out = s_loff[v][F1 + 1];
+    T* dst = out1 + s.row_begin + r0;  // the slab: this tile's own rows' place
+    const uint32_t idx0 = s.row_begin + r0;
+#pragma unroll
+    for (int u = 0; u < ITEMS; ++u) {
+      const uint32_t i = u * VT + vt;
+      if (i < n_out) {
+        T t;
+        t.key = skey[i];
+        t.idx = idx0 + srow[i];
+        if constexpr (sizeof(K) == 8) t.pad = 0;
+        dst[i] = t;
+      }
+    }
+  }
+  __syncthreads();
+  for (uint32_t b = threadIdx.x; b < n_bins; b += NT) {
+    const uint32_t cb = s_hist[b];
+    if (cb) atomicAdd(hist + b, cb);
+  }
+}
+
+// =====================================================================================================================
+// P2. Work item = (group of `gs` consecutive slabs, level-1 digit d1); the grid is n_groups * n_digits with d1 running
+// fastest, so the CTAs resident at one moment read the same slabs (frag table and slab lines are shared through L2) and
+// add to different cursors. The item's tuples are addressed through a flat index over its fragments: s_pre[] is the prefix
+// sum of the fragment lengths, s_own[k] the fragment holding flat index 32k, so a thread finds its fragment with one
+// lookup and a step or two, and all ITEMS loads of a thread are independent. gs is chosen so that an item holds 7/8 of
+// TILE tuples on average; an item that holds more (skew) is worked off in batches of TILE.
+// d1 == F1 (only with kNullRoute): the routed NULL probe rows, copied behind the last partition (part_off[P]).
+// dynamic smem: TILE * sizeof(Tuple<K>).
+// =====================================================================================================================
+template <typename K, int NT, int ITEMS>
+__global__ void __launch_bounds__(NT, 1024 / NT) k_scatter2f(const Tuple<K, false>* __restrict__ in, const uint16_t* __restrict__ frag,
+                                                            RelMeta rel, uint32_t tile1, Tuple<K, false>* __restrict__ out,
+                                                            uint32_t* __restrict__ cur2, int radix_bits, int bits2, uint32_t gs,
+                                                            uint32_t n_digits) {
+  using T = Tuple<K, false>;
+  constexpr uint32_t TILE = NT * ITEMS;
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  T* stage = reinterpret_cast<T*>(s_raw);
+  __shared__ uint32_t s_cnt[kMaxDigits], s_loff[kMaxDigits], s_delta[kMaxDigits];
+  __shared__ uint32_t s_pre[NT + 1], s_dsrc[NT];
+  __shared__ uint8_t s_own[TILE / 32];
+  __shared__ uint32_t scratch[33];
+
+  const uint32_t P = 1u << radix_bits, F1 = P >> bits2, FS = F1 + 2u;
+  const uint32_t group = blockIdx.x / n_digits, d1 = blockIdx.x % n_digits;
+  const uint32_t s0 = group * gs, ns = min(gs, rel.n_tiles - s0);  // gs < NT
+  const bool null_item = d1 == F1;
+  const uint32_t F2 = null_item ? 1u : 1u << bits2;
+  uint32_t* cursors = cur2 + (null_item ? P : d1 << bits2);
+
+  uint32_t len = 0, src = 0;
+  if (threadIdx.x < ns) {
+    const uint32_t tile = s0 + threadIdx.x;
+    const uint16_t* f = frag + static_cast<size_t>(tile) * FS + d1;
+    const uint32_t f0 = __ldg(f), f1 = __ldg(f + 1);
+    const DevSegment* sg = rel.segs + __ldg(rel.tile_seg + tile);
+    src = sg->row_begin + (tile - sg->tile_begin) * tile1 + f0;
+    len = f1 - f0;
+  }
+  uint32_t total;
+  const uint32_t pre = block_excl_scan(len, scratch, &total);
+  s_pre[threadIdx.x] = pre;  // threads >= ns hold `total`: s_pre[ns] closes the last fragment
+  s_dsrc[threadIdx.x] = src - pre;
+  if (threadIdx.x == NT - 1) s_pre[NT] = total;
+
+  for (uint32_t lo = 0; lo < total; lo += TILE) {
+    const uint32_t n_in = min(TILE, total - lo);
+    for (uint32_t d = threadIdx.x; d < F2; d += NT) s_cnt[d] = 0;
+    if (len) {
+      const uint32_t a = max(pre, lo), b = min(pre + len, lo + TILE);
+      for (uint32_t k = (a - lo + 31u) >> 5; lo + (k << 5) < b; ++k) s_own[k] = static_cast<uint8_t>(threadIdx.x);
+    }
+    __syncthreads();  // also orders the previous batch's copy-out before this batch's staging
+
+    T tup[ITEMS];
+    uint32_t packed[ITEMS];
+#pragma unroll
+    for (int j = 0; j < ITEMS; ++j) {
+      const uint32_t i = j * NT + threadIdx.x;
+      if (i < n_in) {
+        const uint32_t fi = lo + i;
+        uint32_t s = s_own[i >> 5];
+        while (fi >= s_pre[s + 1]) ++s;
+        tup[j] = ld_stream(in + static_cast<uint32_t>(s_dsrc[s] + fi));
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < ITEMS; ++j) {
+      const uint32_t i = j * NT + threadIdx.x;
+      packed[j] = kNoDigit;
+      if (i < n_in) {
+        const uint32_t d = hash_key(tup[j].key) & (F2 - 1u);
+        packed[j] = (d << 16) | atomicAdd(&s_cnt[d], 1u);
+      }
+    }
+    __syncthreads();
+    {
+      const uint32_t d = threadIdx.x;
+      const uint32_t c = d < F2 ? s_cnt[d] : 0u;
+      uint32_t tot;
+      const uint32_t ex = block_excl_scan(c, scratch, &tot);
+      if (d < F2) {
+        s_loff[d] = ex;
+        if (c) s_delta[d] = atomicAdd(cursors + d, c) - ex;
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < ITEMS; ++j) {
+      if (packed[j] != kNoDigit) stage[s_loff[packed[j] >> 16] + (packed[j] & 0xFFFFu)] = tup[j];
+    }
+    __syncthreads();
+    copy_tile_out<K, false, NT, ITEMS>(stage, s_delta, out, n_in, F2 - 1u, 0, 0xFFFFFFFFu, 0u);
+  }
+}
+
+}  // namespace hj

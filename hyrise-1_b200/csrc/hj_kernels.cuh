@@ -181,7 +181,7 @@ __global__ void __launch_bounds__(NT) k_offsets(const uint32_t* __restrict__ his
     const uint32_t ex = block_excl_scan(c, scratch, &total) + s_carry;
     if (b < n) {
       part_off[b] = ex;
-      if (b < P) cur2[b] = ex;
+      if (b <= P) cur2[b] = ex;  // [P]: cursor of the routed-NULL region (fused pass 2)
     }
     __syncthreads();
     if (threadIdx.x == 0) s_carry += total;

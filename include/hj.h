@@ -116,6 +116,9 @@ typedef struct hj_relation {
 #define HJ_FLAG_XCHG_STAGED 0x4u    /* hj_join_sharded: exchange through send buffers + NCCL send/recv even when the
                                        ranks can map each other's memory (default: the scatter kernel stores straight
                                        into the peers' receive buffers over NVLink)                               */
+#define HJ_FLAG_TWO_SWEEP_PARTITION 0x8u /* two-pass partitioning (radix_bits > 8) by the v2 kernels: histogram sweep
+                                       that stores decoded keys, then two scatter passes. Default: pass 1 is done
+                                       slab-locally inside the histogram kernel (hj_fused.cuh). Same results.    */
 
 typedef struct hj_options {
   uint32_t abi_version;       /* HJ_ABI_VERSION                                              */

@@ -18,6 +18,7 @@ ap.add_argument("--workload", default="c2")
 ap.add_argument("--scale", type=float, default=0.1)
 ap.add_argument("--mode", default="Inner")
 ap.add_argument("--joins", type=int, default=2)
+ap.add_argument("--flags", type=lambda x: int(x, 0), default=0, help="extra HJ_FLAG_* bits")
 args = ap.parse_args()
 hj = importlib.import_module("hyrise-1_b200")
 dev = torch.device("cuda", 0)
@@ -25,7 +26,7 @@ data = bench.gen_device_workload(args.workload, args.scale, dev, seed=0xB202)
 b = bench.relation_from_chunks(hj, data["build"], hj.abi.LOC_DEVICE)
 p = bench.relation_from_chunks(hj, data["probe"], hj.abi.LOC_DEVICE)
 torch.cuda.synchronize()
-j = hj.HashJoin(device=0, flags=hj.abi.FLAG_TIMINGS)
+j = hj.HashJoin(device=0, flags=hj.abi.FLAG_TIMINGS | args.flags)
 for i in range(args.joins):
     info = j.join(b, p, args.mode)
     t = j.timings()

@@ -206,6 +206,28 @@ def test_null_probe_literal_vs_sql(joins, mode, encoding):
     assert lit.n_rows > sql.n_rows
     assert_same(joins(9, abi.FLAG_SQL_NULL_PROBE), build, probe, mode, flags=abi.FLAG_SQL_NULL_PROBE, what="sql 2-pass")
 
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("radix_bits", [9, 14, 15])
+@pytest.mark.parametrize("dtype", [np.int32, np.int64])
+def test_two_pass_partition_paths_agree(joins, mode, radix_bits, dtype):
+    """Two-pass partitioning has two implementations with identical results: the default slab-local pass 1 fused into the
+    histogram kernel + fragment-gathering pass 2 (hj_fused.cuh), and HJ_FLAG_TWO_SWEEP_PARTITION (K1 + scatter1 + scatter2,
+    what the sharded local join uses). Skewed keys make single pass-2 work items exceed one tile (batched)."""
+    rng = np.random.default_rng(radix_bits * 7 + (dtype == np.int64))
+    n_b, n_p = 150_000, 400_000
+    bk = wl.zipf_keys(rng, n_b, 5000, 1.1, dtype)
+    pk = rng.integers(1, 5001, n_p).astype(dtype)
+    pk[: n_p // 2] = 6000  # half of the probe rows (no build partner) in ONE level-1 fragment per slab
+    bn = (rng.random(n_b) < 0.03).astype(np.uint8)
+    pn = (rng.random(n_p) < 0.03).astype(np.uint8)
+    build, probe = wl.make_relation(bk, 1 << 15, "dict", bn), wl.make_relation(pk, 30_000, "mixed", pn)
+    assert_same(joins(radix_bits), build, probe, mode, what="fused")
+    assert_same(joins(radix_bits, abi.FLAG_TWO_SWEEP_PARTITION), build, probe, mode, what="two-sweep")
+    if mode in ("Left", "Right"):
+        f = abi.FLAG_SQL_NULL_PROBE
+        assert_same(joins(radix_bits, f), build, probe, mode, flags=f, what="fused, routed NULLs")
+        assert_same(joins(radix_bits, f | abi.FLAG_TWO_SWEEP_PARTITION), build, probe, mode, flags=f, what="two-sweep, routed NULLs")
+
 
 @pytest.mark.parametrize("mode", ["Inner", "Left"])
 def test_output_capacity_overflow_reprobes(joins, mode):
