@@ -314,6 +314,12 @@ def main():
                    "build_probe": n_local * t_real + info.n_rows * 16}
     phase_kernel = {"materialize": "k_materialize_hist", "scatter1": "k_scatter1", "scatter2": "k_scatter2",
                     "build_probe": "k_build_probe"}
+    if mean_ms["scatter1"] < 0.05 * mean_ms["scatter2"]:
+        # default two-pass path (hj_fused.cuh): pass 1 runs inside the histogram kernel — the "materialize" phase reads the
+        # input and writes the slab-local tuples, there is no separate scatter1 kernel, pass 2 gathers fragments
+        phase_bytes["materialize"] = n_local * (w_in + t_real)
+        del phase_bytes["scatter1"]
+        phase_kernel.update({"materialize": "k_part1", "scatter2": "k_scatter2f"})
     dom = max(phase_bytes, key=lambda p_: mean_ms[p_])
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "traffic_c2_full.json")  # dram bytes per launch from the committed ncu capture
@@ -363,6 +369,9 @@ def main():
                 if world > 1:
                     inf_ = j.join_sharded(build_host, probe_host, abi.MODE_INNER, stream=stream)
                 else:
+                    # the operator's call sequence for host tables: bind the PosLists, join (streamed: copy-in, join and
+                    # copy-out of probe slices overlap), fetch (a no-op after a bound join)
+                    j.bind_output(out_b, out_p)
                     inf_ = j.join(build_host, probe_host, abi.MODE_INNER, stream=stream)
                 j.fetch(out_b, out_p)
                 return inf_
@@ -379,7 +388,7 @@ def main():
                 dist.all_reduce(tt, op=dist.ReduceOp.MAX)
                 e2e_s = float(tt.item())
             e2e = {"value": total_tuples / e2e_s, "unit": unit, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": inf.n_rows * 16,
-                   "ms_per_step": e2e_s * 1e3, "steps": n_e2e}
+                   "ms_per_step": e2e_s * 1e3, "steps": n_e2e, "probe_slices": int(inf.n_probe_slices)}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:

@@ -117,13 +117,14 @@ def rowids_to_numpy(buf, n):
 class HashJoin:
     """One hj_ctx. Mirrors the call sequence of the C++ shim's JoinHash::_on_execute: join -> fetch."""
 
-    def __init__(self, device=0, flags=0, radix_bits=-1, output_capacity=0):
+    def __init__(self, device=0, flags=0, radix_bits=-1, output_capacity=0, stream_slice_rows=0):
         self._l = lib()
         opts = abi.Options()
         opts.abi_version = abi.HJ_ABI_VERSION
         opts.flags = flags
         opts.radix_bits = radix_bits
         opts.output_capacity = output_capacity
+        opts.stream_slice_rows = stream_slice_rows
         self._ctx = C.c_void_p()
         st = self._l.hj_create(device, C.byref(opts), C.byref(self._ctx))
         if st != abi.OK:
@@ -159,6 +160,17 @@ class HashJoin:
         self._check(self._l.hj_join_sharded(self._ctx, C.byref(build), C.byref(probe), mode, stream, C.byref(info)))
         self.info, self._mode = info, mode
         return info
+
+    def bind_output(self, out_build, out_probe):
+        """hj_bind_output: the NEXT join writes its PosLists straight into these host arrays ((cap, 2) uint32, ideally
+        pinned); with host inputs of many chunks the join is streamed (copy-in, join and copy-out overlap).
+        Afterwards fetch(out_build, out_probe) just returns the filled views."""
+        cap = len(out_probe)
+        if out_build is not None:
+            cap = min(cap, len(out_build))
+        self._bound = (out_build, out_probe)  # keep the arrays alive until the join has run
+        self._check(self._l.hj_bind_output(self._ctx, None if out_build is None else out_build.ctypes.data,
+                                           out_probe.ctypes.data, cap))
 
     def fetch(self, out_build=None, out_probe=None):
         """Copies the result PosLists to host. Returns (build_side or None, probe_side) as (n, 2) uint32 arrays."""

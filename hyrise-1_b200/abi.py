@@ -2,7 +2,7 @@
 tests/test_abi.py checks the struct sizes against the values compiled into the library (hj_abi_sizeof)."""
 import ctypes as C
 
-HJ_ABI_VERSION = 2
+HJ_ABI_VERSION = 3
 
 # JoinMode, src/lib/types.hpp:189 of the reference
 MODE_INNER, MODE_LEFT, MODE_RIGHT, MODE_OUTER, MODE_CROSS, MODE_SEMI, MODE_ANTI = range(7)
@@ -45,14 +45,15 @@ class Relation(C.Structure):
 
 class Options(C.Structure):
     _fields_ = [("abi_version", C.c_uint32), ("flags", C.c_uint32), ("radix_bits", C.c_int32),
-                ("reserved0", C.c_uint32), ("output_capacity", C.c_uint64), ("reserved", C.c_uint64 * 4)]
+                ("reserved0", C.c_uint32), ("output_capacity", C.c_uint64), ("stream_slice_rows", C.c_uint64),
+                ("reserved", C.c_uint64 * 3)]
 
 
 class ResultInfo(C.Structure):
     _fields_ = [("n_rows", C.c_uint64), ("n_sides", C.c_uint32), ("radix_bits", C.c_uint32),
                 ("n_build_tuples", C.c_uint64), ("n_probe_tuples", C.c_uint64),
                 ("n_partitions", C.c_uint32), ("n_overflow_partitions", C.c_uint32),
-                ("n_probe_passes", C.c_uint32), ("reserved", C.c_uint32)]
+                ("n_probe_passes", C.c_uint32), ("n_probe_slices", C.c_uint32)]
 
 
 class Timings(C.Structure):
@@ -71,6 +72,7 @@ SYMBOLS = {
     "hj_join": (C.c_int, [C.c_void_p, C.POINTER(Relation), C.POINTER(Relation), C.c_int, C.c_void_p,
                           C.POINTER(ResultInfo)]),
     "hj_fetch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]),
+    "hj_bind_output": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]),
     "hj_result_device": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]),
     "hj_translate": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_void_p), C.POINTER(C.c_uint32),
                                C.c_uint32]),

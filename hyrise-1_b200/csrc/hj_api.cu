@@ -36,6 +36,7 @@ constexpr int kJoinThreads = 1024;
 constexpr int kProbeV = 4;
 constexpr uint32_t kProbeSlice = 128 * 1024;
 constexpr int kSinglePassMaxBits = 8;
+constexpr uint64_t kMinSliceRows = 32u << 20;  // streamed join: probe slices of at least 32 Mi rows
 constexpr int kMinChunkShift = 8, kMaxChunkShift = 14;  // result chunks of 256 .. 16 Ki rows
 constexpr int kPart1Virtual = 2;             // fused P1: 2 virtual CTAs of 512 threads (shared memory is L1 taken from the gather)
 constexpr int kVirtualCtasPerSm = 4;       // K1 / pass 1 tile ownership: G = min(n_tiles, 4 * SMs) virtual CTAs
@@ -62,11 +63,19 @@ struct hj_ctx {
   std::string err;
   std::vector<DevBuf*> all_bufs;
   // per relation (0 = build, 1 = probe)
-  DevBuf stage_in[2], segs[2], tile_seg[2], seg_row_begin[2], keys_mat[2], valid_mask[2];
-  DevBuf hist[2], hist1[2], part_off[2], cur2[2], l1_tiles[2], tup_a[2], tup_b[2], frag[2];
-  DevBuf items, fin, plan, queue, out_state, out_tails, compact_plan, compact_used, compact_hole, compact_src, matched, out_build, out_probe, misc;
+  DevBuf stage_in[3], segs[3], tile_seg[3], seg_row_begin[3], keys_mat[3], valid_mask[3];  // [2]: second probe slice set (streamed join)
+  DevBuf hist[3], hist1[3], part_off[3], cur2[3], l1_tiles[3], tup_a[3], tup_b[3], frag[3];
+  DevBuf items, fin, plan, queue, out_state, out_tails, compact_plan, compact_used, compact_hole, compact_src, matched, out_build[2], out_probe[2], misc;
   void* pinned = nullptr;  // small pinned readback area
   cudaEvent_t ev[16] = {};
+  // streamed host join (hj_bind_output): copy streams and per-slice-set events (staged / joined / downloaded)
+  cudaStream_t copy_in = nullptr, copy_out = nullptr;
+  cudaEvent_t ev_in[2] = {}, ev_done[2] = {}, ev_out[2] = {};
+  hj_row_id* bound_build = nullptr;
+  hj_row_id* bound_probe = nullptr;
+  uint64_t bound_capacity = 0;
+  bool bound = false;            // outputs bound for the next hj_join
+  bool result_in_bound = false;  // the last join delivered its result into the bound host buffers
   // result of the last join
   bool has_result = false;
   uint64_t n_result = 0;
@@ -82,15 +91,15 @@ struct hj_ctx {
   std::vector<void*> xchg_graveyard;  // exported buffers that were outgrown; freed once no peer can have them mapped
   DevBuf xchg_hdl_dev;
   bool p2p_ok = false;
-  const uint64_t* xchg_rowids[2] = {nullptr, nullptr};  // set while hj_join_sharded runs its local join
+  const uint64_t* xchg_rowids[3] = {nullptr, nullptr, nullptr};  // set while hj_join_sharded runs its local join
   uint64_t xchg_bytes_sent[2] = {0, 0};
 
   hj_ctx() {
-    for (DevBuf* b : {&stage_in[0], &stage_in[1], &segs[0], &segs[1], &tile_seg[0], &tile_seg[1], &seg_row_begin[0],
-                      &seg_row_begin[1], &keys_mat[0], &keys_mat[1], &valid_mask[0], &valid_mask[1], &hist[0], &hist[1],
-                      &part_off[0], &part_off[1], &hist1[0], &hist1[1], &cur2[0], &cur2[1], &l1_tiles[0], &l1_tiles[1],
-                      &tup_a[0], &tup_a[1], &tup_b[0], &tup_b[1], &frag[0], &frag[1], &items, &fin, &plan, &queue, &out_state, &out_tails, &compact_plan, &compact_used, &compact_hole, &compact_src, &matched,
-                      &out_build, &out_probe, &misc, &xchg_counts[0], &xchg_counts[1], &xchg_cnt_dev, &xchg_send_keys[0],
+    for (auto* arr : {stage_in, segs, tile_seg, seg_row_begin, keys_mat, valid_mask, hist, hist1, part_off, cur2, l1_tiles, tup_a,
+                      tup_b, frag})
+      for (int i = 0; i < 3; ++i) all_bufs.push_back(&arr[i]);
+    for (DevBuf* b : {&items, &fin, &plan, &queue, &out_state, &out_tails, &compact_plan, &compact_used, &compact_hole, &compact_src, &matched,
+                      &out_build[0], &out_build[1], &out_probe[0], &out_probe[1], &misc, &xchg_counts[0], &xchg_counts[1], &xchg_cnt_dev, &xchg_send_keys[0],
                       &xchg_send_keys[1], &xchg_send_rids[0], &xchg_send_rids[1], &xchg_send_nulls[0], &xchg_send_nulls[1],
                       &xchg_recv_keys[0], &xchg_recv_keys[1], &xchg_recv_rids[0], &xchg_recv_rids[1], &xchg_recv_nulls[0],
                       &xchg_recv_nulls[1], &xchg_hdl_dev})
@@ -520,6 +529,139 @@ int launch_build_probe(hj_ctx* ctx, const JoinArgs<K, PAY>& a, cudaStream_t st) 
   }
 }
 
+// K4..K8 for one (partitioned build, partitioned probe) pair: plan, build+probe, finalize, compaction; re-probes once with
+// exact buffers when the first estimate was too small. `sp` = which per-side buffer set holds the probe partitions (1, or
+// 1/2 alternating for the slices of a streamed join), `oset` = which result buffers to fill. Leaves the counters in the
+// pinned Readback area.
+template <typename K, bool PAY>
+int probe_phase(hj_ctx* ctx, const PreparedRel& pb, const PreparedRel& pp, const PartState& pst, int sp, int oset,
+                int radix_bits, int bits2, int mode, int probe_null_policy, bool payload, uint64_t n_build_rows,
+                uint64_t n_probe_rows, cudaStream_t st, Launches* nl, int* passes_out, cudaEvent_t ev_probe,
+                cudaEvent_t ev_end) {
+  const bool one_side = mode == HJ_MODE_SEMI || mode == HJ_MODE_ANTI;
+  const uint32_t P = 1u << radix_bits;
+  const auto* tb = static_cast<const Tuple<K, PAY>*>(bits2 ? ctx->tup_b[0].p : ctx->tup_a[0].p);
+  const auto* tp = static_cast<const Tuple<K, PAY>*>(bits2 ? ctx->tup_b[sp].p : ctx->tup_a[sp].p);
+  // routed NULL rows stay in pass 1's output; the fused path's pass 2 moves them behind the last partition of ITS output
+  const auto* tp1 = pst.fused ? tp : static_cast<const Tuple<K, PAY>*>(ctx->tup_a[sp].p);
+
+  // ---- plan
+  const uint32_t cap = Cfg<K>::kCap;
+  const size_t items_capacity = size_t(P) + n_build_rows / cap + n_probe_rows / kProbeSlice + 64;
+  HJ_TRY(ensure(ctx, ctx->items, items_capacity * sizeof(WorkItem)));
+  HJ_TRY(ensure(ctx, ctx->fin, size_t(P) * sizeof(WorkItem)));
+  HJ_TRY(ensure(ctx, ctx->plan, sizeof(PlanOut)));
+  HJ_TRY(ensure(ctx, ctx->queue, 256));
+  HJ_TRY(ensure(ctx, ctx->out_state, sizeof(OutState)));
+  HJ_TRY(ensure(ctx, ctx->out_tails, sizeof(OutTail) * kMaxTails));
+  HJ_TRY(ensure(ctx, ctx->compact_plan, sizeof(CompactHdr)));
+  const size_t matched_bytes = (size_t(n_probe_rows) / 32 + 2) * 4;
+  if (mode != HJ_MODE_INNER) HJ_TRY(ensure(ctx, ctx->matched, matched_bytes));
+  auto* off_b = static_cast<uint32_t*>(ctx->part_off[0].p);
+  auto* off_p = static_cast<uint32_t*>(ctx->part_off[sp].p);
+  k_plan<1024><<<1, 1024, 0, st>>>(off_b, off_p, radix_bits, mode, cap, kProbeSlice,
+                                   (uint32_t)std::min<size_t>(items_capacity, 0xFFFFFFFFu),
+                                   static_cast<WorkItem*>(ctx->items.p), static_cast<WorkItem*>(ctx->fin.p),
+                                   static_cast<PlanOut*>(ctx->plan.p));
+  HJ_LAUNCH_CHECK(ctx, "k_plan");
+  nl->n++;
+
+  // ---- output buffers: `rows` result rows + one chunk of slack per result writer (K5: every warp; K6/K7: every CTA).
+  // Chunk size: a writer should go through >= ~4 chunks so that the slack stays a fraction of the result.
+  const uint64_t n_writers = uint64_t(ctx->n_sms) * (kJoinThreads / 32) + (mode != HJ_MODE_INNER ? ctx->n_sms : 0) +
+                             (probe_null_policy == kNullRoute ? ctx->n_sms : 0);
+  auto chunk_shift_for = [&](uint64_t rows) {
+    int sh = kMinChunkShift;
+    while (sh < kMaxChunkShift && (uint64_t(1) << sh) * n_writers * 4 < rows) ++sh;
+    return sh;
+  };
+  auto alloc_rows = [&](uint64_t rows, int sh) { return (((rows + (uint64_t(1) << sh) - 1) >> sh) + n_writers + 1) << sh; };
+  uint64_t want_rows = ctx->opts.output_capacity ? ctx->opts.output_capacity : n_probe_rows;
+  int chunk_shift = chunk_shift_for(want_rows);
+  uint64_t capacity = alloc_rows(want_rows, chunk_shift);
+
+  JoinArgs<K, PAY> a{};
+  a.build = tb;
+  a.probe = tp;
+  a.items = static_cast<const WorkItem*>(ctx->items.p);
+  a.plan = static_cast<const PlanOut*>(ctx->plan.p);
+  a.queue_head = static_cast<uint32_t*>(ctx->queue.p);
+  a.build_rel = pb.meta;
+  a.probe_rel = pp.meta;
+  a.out_state = static_cast<OutState*>(ctx->out_state.p);
+  a.out_tails = static_cast<OutTail*>(ctx->out_tails.p);
+  a.matched = static_cast<uint32_t*>(ctx->matched.p);
+  a.radix_bits = radix_bits;
+  a.mode = mode;
+  a.payload = payload ? 1 : 0;
+  const bool fast_rowid = pb.meta.uniform_shift >= 0 && pb.meta.identity && pp.meta.uniform_shift >= 0 && pp.meta.identity;
+
+  auto* rb = static_cast<Readback*>(ctx->pinned);
+  int passes = 0;
+  for (;;) {
+    ++passes;
+    if (!one_side) HJ_TRY(ensure(ctx, ctx->out_build[oset], capacity * 8));
+    HJ_TRY(ensure(ctx, ctx->out_probe[oset], capacity * 8));
+    a.out_build = one_side ? nullptr : static_cast<uint64_t*>(ctx->out_build[oset].p);
+    a.out_probe = static_cast<uint64_t*>(ctx->out_probe[oset].p);
+    a.capacity = capacity;
+    a.chunk_shift = chunk_shift;
+    const size_t max_chunks = size_t(capacity >> chunk_shift) + 1;
+    HJ_TRY(ensure(ctx, ctx->compact_used, max_chunks * 4));
+    HJ_TRY(ensure(ctx, ctx->compact_hole, (max_chunks + 1) * 4));
+    HJ_TRY(ensure(ctx, ctx->compact_src, (max_chunks + 1) * 4));
+    HJ_CUDA(ctx, cudaMemsetAsync(ctx->queue.p, 0, 4, st));
+    HJ_CUDA(ctx, cudaMemsetAsync(ctx->out_state.p, 0, sizeof(OutState), st));
+    if (mode != HJ_MODE_INNER) HJ_CUDA(ctx, cudaMemsetAsync(ctx->matched.p, 0, matched_bytes, st));
+    if (payload) {
+      if constexpr (sizeof(Tuple<K, PAY>) > 8) HJ_TRY((launch_build_probe<K, PAY, kRidPayload>(ctx, a, st)));
+      else return fail(ctx, HJ_ERR_INVALID, "RowID-carrying tuples need a tuple type with a payload");
+    } else if constexpr (PAY) {
+      return fail(ctx, HJ_ERR_INVALID, "payload tuples are only used by the sharded local join");
+    } else if (fast_rowid) {
+      HJ_TRY((launch_build_probe<K, PAY, kRidFast>(ctx, a, st)));
+    } else {
+      HJ_TRY((launch_build_probe<K, PAY, kRidGeneric>(ctx, a, st)));
+    }
+    nl->n++;
+    if (passes == 1 && ev_probe) HJ_CUDA(ctx, cudaEventRecord(ev_probe, st));
+    if (mode != HJ_MODE_INNER) {
+      k_finalize_multi<K, PAY, 256><<<ctx->n_sms, 256, 0, st>>>(a, static_cast<const WorkItem*>(ctx->fin.p));
+      HJ_LAUNCH_CHECK(ctx, "k_finalize_multi");
+      nl->n++;
+    }
+    if (probe_null_policy == kNullRoute) {
+      k_emit_null_probe<K, PAY, 256><<<ctx->n_sms, 256, 0, st>>>(a, tp1, off_p);
+      HJ_LAUNCH_CHECK(ctx, "k_emit_null_probe");
+      nl->n++;
+    }
+    k_compact_plan<<<1, 1024, 0, st>>>(a.out_state, a.out_tails, chunk_shift, capacity, static_cast<uint32_t*>(ctx->compact_used.p),
+                                       static_cast<uint32_t*>(ctx->compact_hole.p), static_cast<uint32_t*>(ctx->compact_src.p),
+                                       static_cast<CompactHdr*>(ctx->compact_plan.p));
+    HJ_LAUNCH_CHECK(ctx, "k_compact_plan");
+    k_compact_move<<<ctx->n_sms * 8, 256, 0, st>>>(static_cast<const CompactHdr*>(ctx->compact_plan.p), a.out_state, chunk_shift,
+                                                   static_cast<const uint32_t*>(ctx->compact_used.p),
+                                                   static_cast<const uint32_t*>(ctx->compact_hole.p),
+                                                   static_cast<const uint32_t*>(ctx->compact_src.p), a.out_build, a.out_probe);
+    HJ_LAUNCH_CHECK(ctx, "k_compact_move");
+    nl->n += 2;
+    HJ_CUDA(ctx, cudaMemcpyAsync(&rb->out, ctx->out_state.p, sizeof(OutState), cudaMemcpyDeviceToHost, st));
+    HJ_CUDA(ctx, cudaMemcpyAsync(&rb->plan, ctx->plan.p, sizeof(PlanOut), cudaMemcpyDeviceToHost, st));
+    HJ_CUDA(ctx, cudaMemcpyAsync(&rb->n_build_tuples, off_b + P, 4, cudaMemcpyDeviceToHost, st));
+    HJ_CUDA(ctx, cudaMemcpyAsync(&rb->n_probe_tuples, off_p + P + 1, 4, cudaMemcpyDeviceToHost, st));
+    if (ev_end) HJ_CUDA(ctx, cudaEventRecord(ev_end, st));
+    HJ_CUDA(ctx, cudaStreamSynchronize(st));
+    if ((rb->out.n_chunks << chunk_shift) <= capacity) break;  // every reserved chunk lay inside the buffers
+    if (passes >= 2) return fail(ctx, HJ_ERR_CUDA, "result size changed between probe passes (%llu chunks > capacity %llu rows)",
+                                 rb->out.n_chunks, (unsigned long long)capacity);
+    chunk_shift = chunk_shift_for(rb->out.n_rows);  // the exact row count is known now: re-probe into buffers that fit
+    capacity = alloc_rows(rb->out.n_rows, chunk_shift);
+  }
+
+  *passes_out = passes;
+  return HJ_OK;
+}
+
 template <typename K, bool PAY = false>
 int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, int mode, cudaStream_t st,
              hj_result_info* info, bool payload = false) {
@@ -553,124 +695,10 @@ int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, in
   HJ_TRY(stage_pass2<K, PAY>(ctx, pb, 0, radix_bits, bits2, kNullDrop, sb, st, &nl));
   HJ_TRY(stage_pass2<K, PAY>(ctx, pp, 1, radix_bits, bits2, probe_null_policy, sp, st, &nl));
   HJ_CUDA(ctx, cudaEventRecord(ev[4], st));
-  const auto* tb = static_cast<const Tuple<K, PAY>*>(bits2 ? ctx->tup_b[0].p : ctx->tup_a[0].p);
-  const auto* tp = static_cast<const Tuple<K, PAY>*>(bits2 ? ctx->tup_b[1].p : ctx->tup_a[1].p);
-  // routed NULL rows stay in pass 1's output; the fused path's pass 2 moves them behind the last partition of ITS output
-  const auto* tp1 = sp.fused ? tp : static_cast<const Tuple<K, PAY>*>(ctx->tup_a[1].p);
-
-  // ---- plan
-  const uint32_t cap = Cfg<K>::kCap;
-  const size_t items_capacity = size_t(P) + build->n_rows / cap + probe->n_rows / kProbeSlice + 64;
-  HJ_TRY(ensure(ctx, ctx->items, items_capacity * sizeof(WorkItem)));
-  HJ_TRY(ensure(ctx, ctx->fin, size_t(P) * sizeof(WorkItem)));
-  HJ_TRY(ensure(ctx, ctx->plan, sizeof(PlanOut)));
-  HJ_TRY(ensure(ctx, ctx->queue, 256));
-  HJ_TRY(ensure(ctx, ctx->out_state, sizeof(OutState)));
-  HJ_TRY(ensure(ctx, ctx->out_tails, sizeof(OutTail) * kMaxTails));
-  HJ_TRY(ensure(ctx, ctx->compact_plan, sizeof(CompactHdr)));
-  const size_t matched_bytes = (size_t(probe->n_rows) / 32 + 2) * 4;
-  if (mode != HJ_MODE_INNER) HJ_TRY(ensure(ctx, ctx->matched, matched_bytes));
-  auto* off_b = static_cast<uint32_t*>(ctx->part_off[0].p);
-  auto* off_p = static_cast<uint32_t*>(ctx->part_off[1].p);
-  k_plan<1024><<<1, 1024, 0, st>>>(off_b, off_p, radix_bits, mode, cap, kProbeSlice,
-                                   (uint32_t)std::min<size_t>(items_capacity, 0xFFFFFFFFu),
-                                   static_cast<WorkItem*>(ctx->items.p), static_cast<WorkItem*>(ctx->fin.p),
-                                   static_cast<PlanOut*>(ctx->plan.p));
-  HJ_LAUNCH_CHECK(ctx, "k_plan");
-  nl.n++;
-
-  // ---- output buffers: `rows` result rows + one chunk of slack per result writer (K5: every warp; K6/K7: every CTA).
-  // Chunk size: a writer should go through >= ~4 chunks so that the slack stays a fraction of the result.
-  const uint64_t n_writers = uint64_t(ctx->n_sms) * (kJoinThreads / 32) + (mode != HJ_MODE_INNER ? ctx->n_sms : 0) +
-                             (probe_null_policy == kNullRoute ? ctx->n_sms : 0);
-  auto chunk_shift_for = [&](uint64_t rows) {
-    int sh = kMinChunkShift;
-    while (sh < kMaxChunkShift && (uint64_t(1) << sh) * n_writers * 4 < rows) ++sh;
-    return sh;
-  };
-  auto alloc_rows = [&](uint64_t rows, int sh) { return (((rows + (uint64_t(1) << sh) - 1) >> sh) + n_writers + 1) << sh; };
-  uint64_t want_rows = ctx->opts.output_capacity ? ctx->opts.output_capacity : probe->n_rows;
-  int chunk_shift = chunk_shift_for(want_rows);
-  uint64_t capacity = alloc_rows(want_rows, chunk_shift);
-
-  JoinArgs<K, PAY> a{};
-  a.build = tb;
-  a.probe = tp;
-  a.items = static_cast<const WorkItem*>(ctx->items.p);
-  a.plan = static_cast<const PlanOut*>(ctx->plan.p);
-  a.queue_head = static_cast<uint32_t*>(ctx->queue.p);
-  a.build_rel = pb.meta;
-  a.probe_rel = pp.meta;
-  a.out_state = static_cast<OutState*>(ctx->out_state.p);
-  a.out_tails = static_cast<OutTail*>(ctx->out_tails.p);
-  a.matched = static_cast<uint32_t*>(ctx->matched.p);
-  a.radix_bits = radix_bits;
-  a.mode = mode;
-  a.payload = payload ? 1 : 0;
-  const bool fast_rowid = pb.meta.uniform_shift >= 0 && pb.meta.identity && pp.meta.uniform_shift >= 0 && pp.meta.identity;
-
-  auto* rb = static_cast<Readback*>(ctx->pinned);
   int passes = 0;
-  for (;;) {
-    ++passes;
-    if (!one_side) HJ_TRY(ensure(ctx, ctx->out_build, capacity * 8));
-    HJ_TRY(ensure(ctx, ctx->out_probe, capacity * 8));
-    a.out_build = one_side ? nullptr : static_cast<uint64_t*>(ctx->out_build.p);
-    a.out_probe = static_cast<uint64_t*>(ctx->out_probe.p);
-    a.capacity = capacity;
-    a.chunk_shift = chunk_shift;
-    const size_t max_chunks = size_t(capacity >> chunk_shift) + 1;
-    HJ_TRY(ensure(ctx, ctx->compact_used, max_chunks * 4));
-    HJ_TRY(ensure(ctx, ctx->compact_hole, (max_chunks + 1) * 4));
-    HJ_TRY(ensure(ctx, ctx->compact_src, (max_chunks + 1) * 4));
-    HJ_CUDA(ctx, cudaMemsetAsync(ctx->queue.p, 0, 4, st));
-    HJ_CUDA(ctx, cudaMemsetAsync(ctx->out_state.p, 0, sizeof(OutState), st));
-    if (mode != HJ_MODE_INNER) HJ_CUDA(ctx, cudaMemsetAsync(ctx->matched.p, 0, matched_bytes, st));
-    if (payload) {
-      if constexpr (sizeof(Tuple<K, PAY>) > 8) HJ_TRY((launch_build_probe<K, PAY, kRidPayload>(ctx, a, st)));
-      else return fail(ctx, HJ_ERR_INVALID, "RowID-carrying tuples need a tuple type with a payload");
-    } else if constexpr (PAY) {
-      return fail(ctx, HJ_ERR_INVALID, "payload tuples are only used by the sharded local join");
-    } else if (fast_rowid) {
-      HJ_TRY((launch_build_probe<K, PAY, kRidFast>(ctx, a, st)));
-    } else {
-      HJ_TRY((launch_build_probe<K, PAY, kRidGeneric>(ctx, a, st)));
-    }
-    nl.n++;
-    if (passes == 1) HJ_CUDA(ctx, cudaEventRecord(ev[5], st));
-    if (mode != HJ_MODE_INNER) {
-      k_finalize_multi<K, PAY, 256><<<ctx->n_sms, 256, 0, st>>>(a, static_cast<const WorkItem*>(ctx->fin.p));
-      HJ_LAUNCH_CHECK(ctx, "k_finalize_multi");
-      nl.n++;
-    }
-    if (probe_null_policy == kNullRoute) {
-      k_emit_null_probe<K, PAY, 256><<<ctx->n_sms, 256, 0, st>>>(a, tp1, off_p);
-      HJ_LAUNCH_CHECK(ctx, "k_emit_null_probe");
-      nl.n++;
-    }
-    k_compact_plan<<<1, 1024, 0, st>>>(a.out_state, a.out_tails, chunk_shift, capacity, static_cast<uint32_t*>(ctx->compact_used.p),
-                                       static_cast<uint32_t*>(ctx->compact_hole.p), static_cast<uint32_t*>(ctx->compact_src.p),
-                                       static_cast<CompactHdr*>(ctx->compact_plan.p));
-    HJ_LAUNCH_CHECK(ctx, "k_compact_plan");
-    k_compact_move<<<ctx->n_sms * 8, 256, 0, st>>>(static_cast<const CompactHdr*>(ctx->compact_plan.p), a.out_state, chunk_shift,
-                                                   static_cast<const uint32_t*>(ctx->compact_used.p),
-                                                   static_cast<const uint32_t*>(ctx->compact_hole.p),
-                                                   static_cast<const uint32_t*>(ctx->compact_src.p), a.out_build, a.out_probe);
-    HJ_LAUNCH_CHECK(ctx, "k_compact_move");
-    nl.n += 2;
-    HJ_CUDA(ctx, cudaMemcpyAsync(&rb->out, ctx->out_state.p, sizeof(OutState), cudaMemcpyDeviceToHost, st));
-    HJ_CUDA(ctx, cudaMemcpyAsync(&rb->plan, ctx->plan.p, sizeof(PlanOut), cudaMemcpyDeviceToHost, st));
-    HJ_CUDA(ctx, cudaMemcpyAsync(&rb->n_build_tuples, off_b + P, 4, cudaMemcpyDeviceToHost, st));
-    HJ_CUDA(ctx, cudaMemcpyAsync(&rb->n_probe_tuples, off_p + P + 1, 4, cudaMemcpyDeviceToHost, st));
-    HJ_CUDA(ctx, cudaEventRecord(ev[6], st));
-    HJ_CUDA(ctx, cudaStreamSynchronize(st));
-    if ((rb->out.n_chunks << chunk_shift) <= capacity) break;  // every reserved chunk lay inside the buffers
-    if (passes >= 2) return fail(ctx, HJ_ERR_CUDA, "result size changed between probe passes (%llu chunks > capacity %llu rows)",
-                                 rb->out.n_chunks, (unsigned long long)capacity);
-    chunk_shift = chunk_shift_for(rb->out.n_rows);  // the exact row count is known now: re-probe into buffers that fit
-    capacity = alloc_rows(rb->out.n_rows, chunk_shift);
-  }
-
+  HJ_TRY((probe_phase<K, PAY>(ctx, pb, pp, sp, 1, 0, radix_bits, bits2, mode, probe_null_policy, payload, build->n_rows,
+                              probe->n_rows, st, &nl, &passes, ev[5], ev[6])));
+  auto* rb = static_cast<Readback*>(ctx->pinned);
   ctx->has_result = true;
   ctx->n_result = rb->out.n_rows;
   ctx->n_sides = one_side ? 1 : 2;
@@ -682,7 +710,7 @@ int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, in
   info->n_partitions = P;
   info->n_overflow_partitions = rb->plan.n_overflow_parts;
   info->n_probe_passes = passes;
-  info->reserved = 0;
+  info->n_probe_slices = 0;
 
   hj_timings& t = ctx->timings;
   std::memset(&t, 0, sizeof(t));
@@ -694,6 +722,133 @@ int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, in
   t.ms[HJ_PH_BUILD_PROBE] = passes == 1 ? ev_ms(ev[4], ev[5]) : 0.f;
   t.ms[HJ_PH_FINALIZE] = passes == 1 ? ev_ms(ev[5], ev[6]) : 0.f;
   t.bytes_h2d = pb.h2d_bytes + pp.h2d_bytes;
+  t.n_kernel_launches = nl.n;
+  return HJ_OK;
+}
+
+// Streamed join for HOST-resident inputs with bound HOST outputs (hj_bind_output): the probe relation is cut into slices of
+// whole chunks; while slice i is partitioned and probed, slice i+1 is copied in and the PosLists of slice i-1 are copied
+// out, so the PCIe link runs in both directions at once and the join hides behind the result download. Valid for every
+// mode: the build side is complete before the first probe, and every decision of Left/Right/Semi/Anti is per probe row.
+template <typename K>
+int run_join_streamed(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, int mode, cudaStream_t st,
+                      hj_result_info* info, uint32_t n_slices) {
+  const bool one_side = mode == HJ_MODE_SEMI || mode == HJ_MODE_ANTI;
+  const bool outer = mode == HJ_MODE_LEFT || mode == HJ_MODE_RIGHT;
+  Launches nl;
+  HJ_CUDA(ctx, cudaEventRecord(ctx->ev[0], st));
+  const int radix_bits = ctx->opts.radix_bits >= 0 ? std::min(ctx->opts.radix_bits, kMaxRadixBits)
+                                                   : radix_bits_for(build->n_rows, sizeof(K) == 8 ? HJ_KEY_INT64 : HJ_KEY_INT32);
+  const int bits2 = radix_bits > kSinglePassMaxBits ? radix_bits / 2 : 0;
+  const int probe_null_policy = !outer ? kNullDrop : ((ctx->opts.flags & HJ_FLAG_SQL_NULL_PROBE) ? kNullRoute : kNullAsValue);
+
+  // slices: runs of whole chunks with about the same number of rows
+  std::vector<uint32_t> cut{0};
+  {
+    const uint64_t per = (probe->n_rows + n_slices - 1) / n_slices;
+    uint64_t acc = 0;
+    for (uint32_t i = 0; i < probe->n_segs; ++i) {
+      acc += probe->segs[i].n_rows;
+      if (acc >= per && i + 1 < probe->n_segs) {
+        cut.push_back(i + 1);
+        acc = 0;
+      }
+    }
+    cut.push_back(probe->n_segs);
+  }
+  const uint32_t n = uint32_t(cut.size()) - 1;
+  auto slice_rel = [&](uint32_t i) {
+    hj_relation r{};
+    r.segs = probe->segs + cut[i];
+    r.n_segs = cut[i + 1] - cut[i];
+    r.location = probe->location;
+    r.n_rows = 0;
+    for (uint32_t k = 0; k < r.n_segs; ++k) r.n_rows += r.segs[k].n_rows;
+    return r;
+  };
+
+  PreparedRel pb, pp[2];
+  PartState sb, sp[2];
+  hj_relation rel[2];
+  // stage slice 0 while the build side is copied in and partitioned
+  rel[0] = slice_rel(0);
+  HJ_TRY(prepare_relation(ctx, &rel[0], 1, tile1<K>(), ctx->copy_in, &pp[0]));
+  HJ_CUDA(ctx, cudaEventRecord(ctx->ev_in[0], ctx->copy_in));
+  HJ_TRY(prepare_relation(ctx, build, 0, tile1<K>(), st, &pb));
+  HJ_TRY((stage_alloc<K, false>(ctx, pb, 0, radix_bits, bits2, &sb)));
+  HJ_TRY(stage_hist<K>(ctx, pb, 0, radix_bits, bits2, kNullDrop, sb, st, &nl));
+  HJ_TRY((stage_pass1<K, false>(ctx, pb, 0, radix_bits, bits2, kNullDrop, sb, st, &nl)));
+  HJ_TRY((stage_pass2<K, false>(ctx, pb, 0, radix_bits, bits2, kNullDrop, sb, st, &nl)));
+
+  auto* rb = static_cast<Readback*>(ctx->pinned);
+  uint64_t total = 0, probe_tuples = 0, h2d = pb.h2d_bytes;
+  uint32_t overflow_parts = 0;
+  int max_passes = 0;
+  int status = HJ_OK;
+  for (uint32_t i = 0; i < n; ++i) {
+    const int cur = i & 1, nxt = (i + 1) & 1;
+    if (i + 1 < n) {  // stage the next slice into the other buffer set, once the slice that used it has been joined
+      if (i >= 1) HJ_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_in, ctx->ev_done[nxt], 0));
+      rel[nxt] = slice_rel(i + 1);
+      pp[nxt] = PreparedRel{};
+      HJ_TRY(prepare_relation(ctx, &rel[nxt], 1 + nxt, tile1<K>(), ctx->copy_in, &pp[nxt]));
+      HJ_CUDA(ctx, cudaEventRecord(ctx->ev_in[nxt], ctx->copy_in));
+    }
+    HJ_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_in[cur], 0));
+    if (i >= 2) HJ_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_out[cur], 0));  // result buffers of this set are free again
+    const int side = 1 + cur;
+    HJ_TRY((stage_alloc<K, false>(ctx, pp[cur], side, radix_bits, bits2, &sp[cur])));
+    HJ_TRY(stage_hist<K>(ctx, pp[cur], side, radix_bits, bits2, probe_null_policy, sp[cur], st, &nl));
+    HJ_TRY((stage_pass1<K, false>(ctx, pp[cur], side, radix_bits, bits2, probe_null_policy, sp[cur], st, &nl)));
+    HJ_TRY((stage_pass2<K, false>(ctx, pp[cur], side, radix_bits, bits2, probe_null_policy, sp[cur], st, &nl)));
+    int passes = 0;
+    HJ_TRY((probe_phase<K, false>(ctx, pb, pp[cur], sp[cur], side, cur, radix_bits, bits2, mode, probe_null_policy, false,
+                                  build->n_rows, rel[cur].n_rows, st, &nl, &passes, nullptr, nullptr)));
+    HJ_CUDA(ctx, cudaEventRecord(ctx->ev_done[cur], st));
+    const uint64_t rows = rb->out.n_rows;  // probe_phase synchronised the stream
+    probe_tuples += rb->n_probe_tuples;
+    overflow_parts = std::max(overflow_parts, rb->plan.n_overflow_parts);
+    max_passes = std::max(max_passes, passes);
+    h2d += pp[cur].h2d_bytes;
+    if (total + rows > ctx->bound_capacity) {
+      status = fail(ctx, HJ_ERR_CAPACITY, "bound output holds %llu rows, the result has more (>= %llu after %u of %u probe slices); "
+                    "join again without hj_bind_output and size the buffers from hj_result_info.n_rows",
+                    (unsigned long long)ctx->bound_capacity, (unsigned long long)(total + rows), i + 1, n);
+      break;
+    }
+    if (rows) {
+      HJ_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_out, ctx->ev_done[cur], 0));
+      if (!one_side)
+        HJ_CUDA(ctx, cudaMemcpyAsync(ctx->bound_build + total, ctx->out_build[cur].p, rows * 8, cudaMemcpyDeviceToHost, ctx->copy_out));
+      HJ_CUDA(ctx, cudaMemcpyAsync(ctx->bound_probe + total, ctx->out_probe[cur].p, rows * 8, cudaMemcpyDeviceToHost, ctx->copy_out));
+    }
+    HJ_CUDA(ctx, cudaEventRecord(ctx->ev_out[cur], ctx->copy_out));
+    total += rows;
+  }
+  HJ_CUDA(ctx, cudaEventRecord(ctx->ev[6], ctx->copy_out));
+  HJ_CUDA(ctx, cudaStreamSynchronize(ctx->copy_in));
+  HJ_CUDA(ctx, cudaStreamSynchronize(ctx->copy_out));
+  HJ_CUDA(ctx, cudaStreamSynchronize(st));
+  if (status != HJ_OK) return status;
+
+  ctx->has_result = false;  // nothing left on the device: the PosLists are in the bound buffers
+  ctx->result_in_bound = true;
+  ctx->n_result = total;
+  ctx->n_sides = one_side ? 1 : 2;
+  info->n_rows = total;
+  info->n_sides = ctx->n_sides;
+  info->radix_bits = radix_bits;
+  info->n_build_tuples = rb->n_build_tuples;
+  info->n_probe_tuples = probe_tuples;
+  info->n_partitions = 1u << radix_bits;
+  info->n_overflow_partitions = overflow_parts;
+  info->n_probe_passes = max_passes;
+  info->n_probe_slices = n;
+  hj_timings& t = ctx->timings;
+  std::memset(&t, 0, sizeof(t));
+  t.ms[HJ_PH_TOTAL] = ev_ms(ctx->ev[0], ctx->ev[6]);
+  t.bytes_h2d = h2d;
+  t.bytes_d2h = total * 8 * ctx->n_sides;
   t.n_kernel_launches = nl.n;
   return HJ_OK;
 }
@@ -750,6 +905,10 @@ int hj_create(int device_id, const hj_options* opts, hj_ctx** out_ctx) {
   ok = ok && cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) == cudaSuccess;
   ok = ok && cudaHostAlloc(&ctx->pinned, 32768, cudaHostAllocDefault) == cudaSuccess;
   for (auto& ev : ctx->ev) ok = ok && cudaEventCreate(&ev) == cudaSuccess;
+  ok = ok && cudaStreamCreateWithFlags(&ctx->copy_in, cudaStreamNonBlocking) == cudaSuccess;
+  ok = ok && cudaStreamCreateWithFlags(&ctx->copy_out, cudaStreamNonBlocking) == cudaSuccess;
+  for (auto* arr : {ctx->ev_in, ctx->ev_done, ctx->ev_out})
+    for (int i = 0; i < 2; ++i) ok = ok && cudaEventCreateWithFlags(&arr[i], cudaEventDisableTiming) == cudaSuccess;
   if (!ok) {
     const char* msg = cudaGetErrorString(cudaGetLastError());
     hj_destroy(ctx);
@@ -780,6 +939,11 @@ void hj_destroy(hj_ctx* ctx) {
   hj_release_scratch(ctx);
   for (auto& ev : ctx->ev)
     if (ev) cudaEventDestroy(ev);
+  for (auto* arr : {ctx->ev_in, ctx->ev_done, ctx->ev_out})
+    for (int i = 0; i < 2; ++i)
+      if (arr[i]) cudaEventDestroy(arr[i]);
+  if (ctx->copy_in) cudaStreamDestroy(ctx->copy_in);
+  if (ctx->copy_out) cudaStreamDestroy(ctx->copy_out);
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
   if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
   delete ctx;
@@ -804,12 +968,43 @@ int hj_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, int
   bool wide = false;  // JoinHashTraits: the hashed type of an int32 x int64 pair is int64 (hash_traits.hpp:21-25)
   for (const hj_relation* r : {build, probe})
     for (uint32_t i = 0; i < r->n_segs; ++i) wide = wide || r->segs[i].key_type == HJ_KEY_INT64;
-  return wide ? run_join<int64_t>(ctx, build, probe, mode, st, out_info)
-              : run_join<int32_t>(ctx, build, probe, mode, st, out_info);
+  const bool bound = ctx->bound;
+  ctx->bound = false;  // a binding holds for one join
+  ctx->result_in_bound = false;
+  if (!bound) return wide ? run_join<int64_t>(ctx, build, probe, mode, st, out_info)
+                          : run_join<int32_t>(ctx, build, probe, mode, st, out_info);
+  const bool one_side = mode == HJ_MODE_SEMI || mode == HJ_MODE_ANTI;
+  if (!ctx->bound_probe || (!one_side && !ctx->bound_build)) return fail(ctx, HJ_ERR_INVALID, "hj_bind_output: NULL output buffer");
+  // enough probe chunks to overlap the copies with the join? (slices of >= ~32 M rows, at most 24)
+  const uint64_t min_slice = ctx->opts.stream_slice_rows ? ctx->opts.stream_slice_rows : kMinSliceRows;
+  uint32_t n_slices = uint32_t(std::min<uint64_t>(24, probe->n_rows / min_slice));
+  n_slices = std::min(n_slices, probe->n_segs);
+  if (probe->location == HJ_LOC_HOST && n_slices >= 2)
+    return wide ? run_join_streamed<int64_t>(ctx, build, probe, mode, st, out_info, n_slices)
+                : run_join_streamed<int32_t>(ctx, build, probe, mode, st, out_info, n_slices);
+  // small or device-resident probe side: plain join, then the download into the bound buffers
+  HJ_TRY(wide ? run_join<int64_t>(ctx, build, probe, mode, st, out_info) : run_join<int32_t>(ctx, build, probe, mode, st, out_info));
+  if (out_info->n_rows > ctx->bound_capacity)
+    return fail(ctx, HJ_ERR_CAPACITY, "bound output holds %llu rows, the result has %llu (still on the device: hj_fetch it)",
+                (unsigned long long)ctx->bound_capacity, (unsigned long long)out_info->n_rows);
+  HJ_TRY(hj_fetch(ctx, one_side ? nullptr : ctx->bound_build, ctx->bound_probe, ctx->bound_capacity));
+  ctx->result_in_bound = true;
+  return HJ_OK;
+}
+
+int hj_bind_output(hj_ctx* ctx, hj_row_id* build_side, hj_row_id* probe_side, uint64_t capacity_rows) {
+  if (!ctx) return HJ_ERR_INVALID;
+  ctx->bound_build = build_side;
+  ctx->bound_probe = probe_side;
+  ctx->bound_capacity = capacity_rows;
+  ctx->bound = probe_side != nullptr;
+  return HJ_OK;
 }
 
 int hj_fetch(hj_ctx* ctx, hj_row_id* build_side, hj_row_id* probe_side, uint64_t capacity) {
   if (!ctx) return HJ_ERR_INVALID;
+  if (ctx->result_in_bound && probe_side == ctx->bound_probe && (ctx->n_sides == 1 || build_side == ctx->bound_build))
+    return HJ_OK;  // the join already delivered into these buffers (hj_bind_output)
   if (!ctx->has_result) return fail(ctx, HJ_ERR_STATE, "hj_fetch without a successful hj_join");
   if (capacity < ctx->n_result) return fail(ctx, HJ_ERR_CAPACITY, "capacity %llu < %llu result rows", (unsigned long long)capacity,
                                             (unsigned long long)ctx->n_result);
@@ -820,8 +1015,8 @@ int hj_fetch(hj_ctx* ctx, hj_row_id* build_side, hj_row_id* probe_side, uint64_t
   HJ_CUDA(ctx, cudaEventRecord(ctx->ev[7], st));
   const size_t bytes = ctx->n_result * 8;
   if (bytes) {
-    if (ctx->n_sides == 2) HJ_CUDA(ctx, cudaMemcpyAsync(build_side, ctx->out_build.p, bytes, cudaMemcpyDeviceToHost, st));
-    HJ_CUDA(ctx, cudaMemcpyAsync(probe_side, ctx->out_probe.p, bytes, cudaMemcpyDeviceToHost, st));
+    if (ctx->n_sides == 2) HJ_CUDA(ctx, cudaMemcpyAsync(build_side, ctx->out_build[0].p, bytes, cudaMemcpyDeviceToHost, st));
+    HJ_CUDA(ctx, cudaMemcpyAsync(probe_side, ctx->out_probe[0].p, bytes, cudaMemcpyDeviceToHost, st));
   }
   HJ_CUDA(ctx, cudaEventRecord(ctx->ev[8], st));
   HJ_CUDA(ctx, cudaStreamSynchronize(st));
@@ -833,8 +1028,8 @@ int hj_fetch(hj_ctx* ctx, hj_row_id* build_side, hj_row_id* probe_side, uint64_t
 int hj_result_device(hj_ctx* ctx, const hj_row_id** build_side, const hj_row_id** probe_side, uint64_t* n_rows) {
   if (!ctx) return HJ_ERR_INVALID;
   if (!ctx->has_result) return fail(ctx, HJ_ERR_STATE, "hj_result_device without a successful hj_join");
-  if (build_side) *build_side = ctx->n_sides == 2 ? static_cast<const hj_row_id*>(ctx->out_build.p) : nullptr;
-  if (probe_side) *probe_side = static_cast<const hj_row_id*>(ctx->out_probe.p);
+  if (build_side) *build_side = ctx->n_sides == 2 ? static_cast<const hj_row_id*>(ctx->out_build[0].p) : nullptr;
+  if (probe_side) *probe_side = static_cast<const hj_row_id*>(ctx->out_probe[0].p);
   if (n_rows) *n_rows = ctx->n_result;
   return HJ_OK;
 }

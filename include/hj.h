@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define HJ_ABI_VERSION 2
+#define HJ_ABI_VERSION 3
 
 /* ---- ABI constants mirrored from the reference ------------------------------------------- */
 
@@ -128,7 +128,8 @@ typedef struct hj_options {
   uint32_t reserved0;
   uint64_t output_capacity;   /* 0: estimate; else initial capacity of the result buffers in
                                  rows (the library grows and re-probes on overflow)          */
-  uint64_t reserved[4];
+  uint64_t stream_slice_rows; /* streamed join (hj_bind_output): minimum probe rows per slice; 0: 32 Mi */
+  uint64_t reserved[3];
 } hj_options;
 
 typedef struct hj_result_info {
@@ -140,7 +141,7 @@ typedef struct hj_result_info {
   uint32_t n_partitions;
   uint32_t n_overflow_partitions; /* build partitions larger than one shared-memory table     */
   uint32_t n_probe_passes;  /* 1, or 2 when the first output capacity estimate overflowed     */
-  uint32_t reserved;
+  uint32_t n_probe_slices;  /* > 0: the join was streamed in that many probe slices (hj_bind_output) */
 } hj_result_info;
 
 #define HJ_N_PHASES 10
@@ -213,6 +214,18 @@ int hj_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, int
  * Left/Right) and must be NULL for Semi/Anti; `probe_side` receives the probe relation's RowIDs.
  * `capacity` is in rows. */
 int hj_fetch(hj_ctx* ctx, hj_row_id* build_side, hj_row_id* probe_side, uint64_t capacity);
+
+/* Optional, before hj_join: binds caller-allocated HOST buffers (capacity in rows; PosList::reserve/resize to an
+ * upper estimate, e.g. the probe row count of a foreign-key join) that the NEXT hj_join fills directly; the binding
+ * then lapses. With host-resident inputs of many chunks the join is streamed: the probe relation is processed in
+ * slices of whole chunks, and while one slice is joined the next one is copied in and the PosLists of the previous
+ * one are copied out, so both PCIe directions and the GPU work at the same time (the operator's end-to-end time
+ * is then that of the result download). Result rows of a slice are contiguous; order across slices follows the
+ * probe chunks. After such a join hj_fetch with the same pointers is a no-op and hj_result_device has nothing to
+ * return. HJ_ERR_CAPACITY if the result does not fit: join again unbound. `build_side` may be NULL for Semi/Anti.
+ * Pinned (page-locked) buffers are needed for the copies to overlap. Replaces nothing in the reference — its
+ * PosLists are written in place (join_hash.cpp:829-855); this is the device-side equivalent of that. */
+int hj_bind_output(hj_ctx* ctx, hj_row_id* build_side, hj_row_id* probe_side, uint64_t capacity_rows);
 
 /* Device pointers to the result of the last hj_join (valid until the next hj_join/hj_destroy).
  * `build_side` is set to NULL for Semi/Anti. */
