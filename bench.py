@@ -203,6 +203,7 @@ def main():
     ap.add_argument("--scale", type=float, default=1.0, help="fraction of the workload's row counts (1.0 = as published)")
     ap.add_argument("--cpu-scale", type=float, default=0.05, help="fraction of the workload the CPU baseline runs")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--slice-rows", type=int, default=0, help="hj_options.stream_slice_rows (0 = library default)")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
 
@@ -252,7 +253,7 @@ def main():
     log(f"[rank {rank}] generated {nb} x {npr} rows in {time.time() - t0:.1f}s; inputs "
         f"{(input_bytes(data['build']) + input_bytes(data['probe'])) / 1e9:.2f} GB")
 
-    j = hj.HashJoin(device=local_rank, flags=abi.FLAG_TIMINGS)
+    j = hj.HashJoin(device=local_rank, flags=abi.FLAG_TIMINGS, stream_slice_rows=args.slice_rows)
     if world > 1:
         uid = [hj.comm_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(uid, src=0)

@@ -55,6 +55,10 @@ thread_local std::string g_create_error;
 
 }  // namespace
 
+constexpr int kSides = 5;
+// pinned readback area: Readback at 0, exchange count matrices at kPinnedCounts, IPC handle records at kPinnedHandles
+constexpr size_t kPinnedBytes = 96 * 1024, kPinnedCounts = 4096, kPinnedHandles = 64 * 1024;
+
 struct hj_ctx {
   int device = 0;
   int n_sms = 0;
@@ -63,8 +67,10 @@ struct hj_ctx {
   std::string err;
   std::vector<DevBuf*> all_bufs;
   // per relation (0 = build, 1 = probe)
-  DevBuf stage_in[3], segs[3], tile_seg[3], seg_row_begin[3], keys_mat[3], valid_mask[3];  // [2]: second probe slice set (streamed join)
-  DevBuf hist[3], hist1[3], part_off[3], cur2[3], l1_tiles[3], tup_a[3], tup_b[3], frag[3];
+  // per relation: 0 = build, 1 = probe, 2 = second probe slice set (streamed join);
+  // sliced sharded join: 0/1 = the shards being exchanged, 2 = received build rows, 3/4 = received probe slices
+  DevBuf stage_in[kSides], segs[kSides], tile_seg[kSides], seg_row_begin[kSides], keys_mat[kSides], valid_mask[kSides];
+  DevBuf hist[kSides], hist1[kSides], part_off[kSides], cur2[kSides], l1_tiles[kSides], tup_a[kSides], tup_b[kSides], frag[kSides];
   DevBuf items, fin, plan, queue, out_state, out_tails, compact_plan, compact_used, compact_hole, compact_src, matched, out_build[2], out_probe[2], misc;
   void* pinned = nullptr;  // small pinned readback area
   cudaEvent_t ev[16] = {};
@@ -78,31 +84,37 @@ struct hj_ctx {
   bool result_in_bound = false;  // the last join delivered its result into the bound host buffers
   // result of the last join
   bool has_result = false;
+  const void* res_build = nullptr;  // device PosLists of the last join (out_build[0]/out_probe[0], or acc_* after a sliced
+  const void* res_probe = nullptr;  // sharded join)
   uint64_t n_result = 0;
   int n_sides = 0;
   hj_timings timings{};
   // multi-GPU
   void* nccl_comm = nullptr;
   int n_ranks = 1, rank = 0;
-  DevBuf xchg_counts[2], xchg_cnt_dev, xchg_send_keys[2], xchg_send_rids[2], xchg_send_nulls[2], xchg_recv_keys[2],
-      xchg_recv_rids[2], xchg_recv_nulls[2];
+  // receive sets: 0 = build, 1 = probe (or probe slices 0, 2, ..), 2 = probe slices 1, 3, ..
+  DevBuf xchg_counts[2], xchg_cnt_dev, xchg_send_keys[2], xchg_send_rids[2], xchg_send_nulls[2], xchg_recv_keys[3],
+      xchg_recv_rids[3], xchg_recv_nulls[3];
+  DevBuf acc_build, acc_probe;      // sliced sharded join: the slices' PosLists, appended
+  cudaEvent_t ev_x[2] = {};         // sliced sharded join: slice set exchanged (recorded on copy_in, the exchange stream)
   struct PeerMap { cudaIpcMemHandle_t handle; void* ptr = nullptr; };
-  PeerMap xchg_peer[16][6];        // peers' receive buffers mapped into this process (direct exchange)
+  PeerMap xchg_peer[16][9];        // peers' receive buffers mapped into this process (direct exchange)
   std::vector<void*> xchg_graveyard;  // exported buffers that were outgrown; freed once no peer can have them mapped
   DevBuf xchg_hdl_dev;
   bool p2p_ok = false;
-  const uint64_t* xchg_rowids[3] = {nullptr, nullptr, nullptr};  // set while hj_join_sharded runs its local join
+  const uint64_t* xchg_rowids[kSides] = {};  // set while hj_join_sharded runs its local join
   uint64_t xchg_bytes_sent[2] = {0, 0};
 
   hj_ctx() {
     for (auto* arr : {stage_in, segs, tile_seg, seg_row_begin, keys_mat, valid_mask, hist, hist1, part_off, cur2, l1_tiles, tup_a,
                       tup_b, frag})
-      for (int i = 0; i < 3; ++i) all_bufs.push_back(&arr[i]);
+      for (int i = 0; i < kSides; ++i) all_bufs.push_back(&arr[i]);
     for (DevBuf* b : {&items, &fin, &plan, &queue, &out_state, &out_tails, &compact_plan, &compact_used, &compact_hole, &compact_src, &matched,
                       &out_build[0], &out_build[1], &out_probe[0], &out_probe[1], &misc, &xchg_counts[0], &xchg_counts[1], &xchg_cnt_dev, &xchg_send_keys[0],
                       &xchg_send_keys[1], &xchg_send_rids[0], &xchg_send_rids[1], &xchg_send_nulls[0], &xchg_send_nulls[1],
                       &xchg_recv_keys[0], &xchg_recv_keys[1], &xchg_recv_rids[0], &xchg_recv_rids[1], &xchg_recv_nulls[0],
-                      &xchg_recv_nulls[1], &xchg_hdl_dev})
+                      &xchg_recv_nulls[1], &xchg_recv_keys[2], &xchg_recv_rids[2], &xchg_recv_nulls[2], &acc_build, &acc_probe,
+                      &xchg_hdl_dev})
       all_bufs.push_back(b);
   }
 };
@@ -355,7 +367,8 @@ int stage_alloc(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, in
   const uint32_t n = pr.meta.n_rows;
   ps->G = std::max<uint32_t>(1, std::min<uint32_t>(pr.meta.n_tiles, uint32_t(kVirtualCtasPerSm) * ctx->n_sms));
   ps->G = (ps->G + kHistVirtual - 1) / kHistVirtual * kHistVirtual;  // K1 hosts kHistVirtual virtual CTAs per physical CTA
-  ps->fused = !PAY && bits2 > 0 && !(ctx->opts.flags & HJ_FLAG_TWO_SWEEP_PARTITION);
+  // rows received through the exchange carry RowIDs that only the two-sweep kernels load (k_scatter1)
+  ps->fused = !PAY && bits2 > 0 && !(ctx->opts.flags & HJ_FLAG_TWO_SWEEP_PARTITION) && !ctx->xchg_rowids[side];
   if (ps->fused) {
     ps->gs = std::max<uint32_t>(1, F1 * 7 / 8);  // an item gathers gs fragments of tile1/F1 tuples on average: 7/8 of a tile
     HJ_TRY(ensure(ctx, ctx->frag[side], std::max<size_t>(1, pr.meta.n_tiles) * (F1 + 2) * 2));
@@ -530,17 +543,17 @@ int launch_build_probe(hj_ctx* ctx, const JoinArgs<K, PAY>& a, cudaStream_t st) 
 }
 
 // K4..K8 for one (partitioned build, partitioned probe) pair: plan, build+probe, finalize, compaction; re-probes once with
-// exact buffers when the first estimate was too small. `sp` = which per-side buffer set holds the probe partitions (1, or
+// exact buffers when the first estimate was too small. `sb`/`sp` = which per-side buffer sets hold the build / probe partitions (sp: 1, or
 // 1/2 alternating for the slices of a streamed join), `oset` = which result buffers to fill. Leaves the counters in the
 // pinned Readback area.
 template <typename K, bool PAY>
-int probe_phase(hj_ctx* ctx, const PreparedRel& pb, const PreparedRel& pp, const PartState& pst, int sp, int oset,
+int probe_phase(hj_ctx* ctx, const PreparedRel& pb, const PreparedRel& pp, const PartState& pst, int sb, int sp, int oset,
                 int radix_bits, int bits2, int mode, int probe_null_policy, bool payload, uint64_t n_build_rows,
                 uint64_t n_probe_rows, cudaStream_t st, Launches* nl, int* passes_out, cudaEvent_t ev_probe,
                 cudaEvent_t ev_end) {
   const bool one_side = mode == HJ_MODE_SEMI || mode == HJ_MODE_ANTI;
   const uint32_t P = 1u << radix_bits;
-  const auto* tb = static_cast<const Tuple<K, PAY>*>(bits2 ? ctx->tup_b[0].p : ctx->tup_a[0].p);
+  const auto* tb = static_cast<const Tuple<K, PAY>*>(bits2 ? ctx->tup_b[sb].p : ctx->tup_a[sb].p);
   const auto* tp = static_cast<const Tuple<K, PAY>*>(bits2 ? ctx->tup_b[sp].p : ctx->tup_a[sp].p);
   // routed NULL rows stay in pass 1's output; the fused path's pass 2 moves them behind the last partition of ITS output
   const auto* tp1 = pst.fused ? tp : static_cast<const Tuple<K, PAY>*>(ctx->tup_a[sp].p);
@@ -557,7 +570,7 @@ int probe_phase(hj_ctx* ctx, const PreparedRel& pb, const PreparedRel& pp, const
   HJ_TRY(ensure(ctx, ctx->compact_plan, sizeof(CompactHdr)));
   const size_t matched_bytes = (size_t(n_probe_rows) / 32 + 2) * 4;
   if (mode != HJ_MODE_INNER) HJ_TRY(ensure(ctx, ctx->matched, matched_bytes));
-  auto* off_b = static_cast<uint32_t*>(ctx->part_off[0].p);
+  auto* off_b = static_cast<uint32_t*>(ctx->part_off[sb].p);
   auto* off_p = static_cast<uint32_t*>(ctx->part_off[sp].p);
   k_plan<1024><<<1, 1024, 0, st>>>(off_b, off_p, radix_bits, mode, cap, kProbeSlice,
                                    (uint32_t)std::min<size_t>(items_capacity, 0xFFFFFFFFu),
@@ -696,10 +709,12 @@ int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, in
   HJ_TRY(stage_pass2<K, PAY>(ctx, pp, 1, radix_bits, bits2, probe_null_policy, sp, st, &nl));
   HJ_CUDA(ctx, cudaEventRecord(ev[4], st));
   int passes = 0;
-  HJ_TRY((probe_phase<K, PAY>(ctx, pb, pp, sp, 1, 0, radix_bits, bits2, mode, probe_null_policy, payload, build->n_rows,
+  HJ_TRY((probe_phase<K, PAY>(ctx, pb, pp, sp, 0, 1, 0, radix_bits, bits2, mode, probe_null_policy, payload, build->n_rows,
                               probe->n_rows, st, &nl, &passes, ev[5], ev[6])));
   auto* rb = static_cast<Readback*>(ctx->pinned);
   ctx->has_result = true;
+  ctx->res_build = ctx->out_build[0].p;
+  ctx->res_probe = ctx->out_probe[0].p;
   ctx->n_result = rb->out.n_rows;
   ctx->n_sides = one_side ? 1 : 2;
   info->n_rows = rb->out.n_rows;
@@ -802,7 +817,7 @@ int run_join_streamed(hj_ctx* ctx, const hj_relation* build, const hj_relation* 
     HJ_TRY((stage_pass1<K, false>(ctx, pp[cur], side, radix_bits, bits2, probe_null_policy, sp[cur], st, &nl)));
     HJ_TRY((stage_pass2<K, false>(ctx, pp[cur], side, radix_bits, bits2, probe_null_policy, sp[cur], st, &nl)));
     int passes = 0;
-    HJ_TRY((probe_phase<K, false>(ctx, pb, pp[cur], sp[cur], side, cur, radix_bits, bits2, mode, probe_null_policy, false,
+    HJ_TRY((probe_phase<K, false>(ctx, pb, pp[cur], sp[cur], 0, side, cur, radix_bits, bits2, mode, probe_null_policy, false,
                                   build->n_rows, rel[cur].n_rows, st, &nl, &passes, nullptr, nullptr)));
     HJ_CUDA(ctx, cudaEventRecord(ctx->ev_done[cur], st));
     const uint64_t rows = rb->out.n_rows;  // probe_phase synchronised the stream
@@ -903,11 +918,11 @@ int hj_create(int device_id, const hj_options* opts, hj_ctx** out_ctx) {
     return fail(nullptr, HJ_ERR_CUDA, "device %d is sm_%d%d; libhj is built for sm_100a only", device_id, prop.major, prop.minor);
   }
   ok = ok && cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) == cudaSuccess;
-  ok = ok && cudaHostAlloc(&ctx->pinned, 32768, cudaHostAllocDefault) == cudaSuccess;
+  ok = ok && cudaHostAlloc(&ctx->pinned, kPinnedBytes, cudaHostAllocDefault) == cudaSuccess;
   for (auto& ev : ctx->ev) ok = ok && cudaEventCreate(&ev) == cudaSuccess;
   ok = ok && cudaStreamCreateWithFlags(&ctx->copy_in, cudaStreamNonBlocking) == cudaSuccess;
   ok = ok && cudaStreamCreateWithFlags(&ctx->copy_out, cudaStreamNonBlocking) == cudaSuccess;
-  for (auto* arr : {ctx->ev_in, ctx->ev_done, ctx->ev_out})
+  for (auto* arr : {ctx->ev_in, ctx->ev_done, ctx->ev_out, ctx->ev_x})
     for (int i = 0; i < 2; ++i) ok = ok && cudaEventCreateWithFlags(&arr[i], cudaEventDisableTiming) == cudaSuccess;
   if (!ok) {
     const char* msg = cudaGetErrorString(cudaGetLastError());
@@ -939,7 +954,7 @@ void hj_destroy(hj_ctx* ctx) {
   hj_release_scratch(ctx);
   for (auto& ev : ctx->ev)
     if (ev) cudaEventDestroy(ev);
-  for (auto* arr : {ctx->ev_in, ctx->ev_done, ctx->ev_out})
+  for (auto* arr : {ctx->ev_in, ctx->ev_done, ctx->ev_out, ctx->ev_x})
     for (int i = 0; i < 2; ++i)
       if (arr[i]) cudaEventDestroy(arr[i]);
   if (ctx->copy_in) cudaStreamDestroy(ctx->copy_in);
@@ -1015,8 +1030,8 @@ int hj_fetch(hj_ctx* ctx, hj_row_id* build_side, hj_row_id* probe_side, uint64_t
   HJ_CUDA(ctx, cudaEventRecord(ctx->ev[7], st));
   const size_t bytes = ctx->n_result * 8;
   if (bytes) {
-    if (ctx->n_sides == 2) HJ_CUDA(ctx, cudaMemcpyAsync(build_side, ctx->out_build[0].p, bytes, cudaMemcpyDeviceToHost, st));
-    HJ_CUDA(ctx, cudaMemcpyAsync(probe_side, ctx->out_probe[0].p, bytes, cudaMemcpyDeviceToHost, st));
+    if (ctx->n_sides == 2) HJ_CUDA(ctx, cudaMemcpyAsync(build_side, ctx->res_build, bytes, cudaMemcpyDeviceToHost, st));
+    HJ_CUDA(ctx, cudaMemcpyAsync(probe_side, ctx->res_probe, bytes, cudaMemcpyDeviceToHost, st));
   }
   HJ_CUDA(ctx, cudaEventRecord(ctx->ev[8], st));
   HJ_CUDA(ctx, cudaStreamSynchronize(st));
@@ -1028,8 +1043,8 @@ int hj_fetch(hj_ctx* ctx, hj_row_id* build_side, hj_row_id* probe_side, uint64_t
 int hj_result_device(hj_ctx* ctx, const hj_row_id** build_side, const hj_row_id** probe_side, uint64_t* n_rows) {
   if (!ctx) return HJ_ERR_INVALID;
   if (!ctx->has_result) return fail(ctx, HJ_ERR_STATE, "hj_result_device without a successful hj_join");
-  if (build_side) *build_side = ctx->n_sides == 2 ? static_cast<const hj_row_id*>(ctx->out_build[0].p) : nullptr;
-  if (probe_side) *probe_side = static_cast<const hj_row_id*>(ctx->out_probe[0].p);
+  if (build_side) *build_side = ctx->n_sides == 2 ? static_cast<const hj_row_id*>(ctx->res_build) : nullptr;
+  if (probe_side) *probe_side = static_cast<const hj_row_id*>(ctx->res_probe);
   if (n_rows) *n_rows = ctx->n_result;
   return HJ_OK;
 }

@@ -17,6 +17,7 @@
 namespace hj {
 
 constexpr int kMaxRanks = 16;
+constexpr uint64_t kMaxXchgSlices = 8;  // probe slices of the sliced sharded join
 
 struct XchgArgs {
   RelMeta rel;
@@ -32,6 +33,7 @@ struct XchgArgs {
   uint64_t* dst_rids[kMaxRanks];   // packed global RowIDs
   uint8_t* dst_nulls[kMaxRanks];   // null flags (kNullRoute only) or nullptr
   uint32_t adj[kMaxRanks];
+  uint32_t tile_begin, tile_end;   // the tiles of this launch (a slice of the shard; whole shard: 0 .. n_tiles)
   uint32_t n_ranks;
   uint32_t my_rank;
   int null_policy;
@@ -107,7 +109,7 @@ __global__ void __launch_bounds__(NT) k_xchg_count(const XchgArgs a) {
   uint32_t cnt[kMaxRanks];
 #pragma unroll
   for (int d = 0; d < kMaxRanks; ++d) cnt[d] = 0;
-  for (uint32_t tile = blockIdx.x; tile < a.rel.n_tiles; tile += gridDim.x) {
+  for (uint32_t tile = a.tile_begin + blockIdx.x; tile < a.tile_end; tile += gridDim.x) {
     const DevSegment s = a.rel.segs[__ldg(a.rel.tile_seg + tile)];
     const uint32_t r0 = (tile - s.tile_begin) * TILE;
     const uint32_t n_in = min(TILE, s.n_rows - r0);
@@ -182,7 +184,7 @@ __global__ void __launch_bounds__(NT) k_xchg_scatter(const XchgArgs a) {
     s_dn[threadIdx.x] = a.dst_nulls[threadIdx.x];
   }
 
-  for (uint32_t tile = blockIdx.x; tile < a.rel.n_tiles; tile += G) {
+  for (uint32_t tile = a.tile_begin + blockIdx.x; tile < a.tile_end; tile += G) {
     const DevSegment s = a.rel.segs[__ldg(a.rel.tile_seg + tile)];
     const uint32_t r0 = (tile - s.tile_begin) * TILE;
     const uint32_t n_in = min(TILE, s.n_rows - r0);
@@ -327,6 +329,8 @@ XchgArgs xchg_args(hj_ctx* ctx, const XchgSide& xs, int side) {
     a.dst_nulls[d] = xs.send_nulls ? static_cast<uint8_t*>(ctx->xchg_send_nulls[side].p) : nullptr;
     a.adj[d] = 0;
   }
+  a.tile_begin = 0;
+  a.tile_end = xs.pr.meta.n_tiles;
   a.n_ranks = ctx->n_ranks;
   a.my_rank = ctx->rank;
   a.null_policy = xs.null_policy;
@@ -362,13 +366,13 @@ int xchg_count(hj_ctx* ctx, const hj_relation* rel, int side, XchgSide* xs, cuda
 namespace {
 
 // ---- direct (peer-mapped) exchange: CUDA IPC plumbing ------------------------------------------------------------------
-constexpr int kXchgBufKinds = 6;  // [side][keys, rids, nulls]
-struct HandleRec {                // what every rank publishes before X3 in direct mode (512 bytes)
+constexpr int kXchgBufKinds = 9;  // [receive set][keys, rids, nulls]
+struct HandleRec {                // what every rank publishes before X3 in direct mode (1 KB)
   cudaIpcMemHandle_t h[kXchgBufKinds];
   uint8_t valid[kXchgBufKinds];
-  uint8_t pad[512 - kXchgBufKinds * sizeof(cudaIpcMemHandle_t) - kXchgBufKinds];
+  uint8_t pad[1024 - kXchgBufKinds * sizeof(cudaIpcMemHandle_t) - kXchgBufKinds];
 };
-static_assert(sizeof(HandleRec) == 512, "HandleRec layout");
+static_assert(sizeof(HandleRec) == 1024 && kPinnedHandles + (1 + kMaxRanks) * sizeof(HandleRec) <= kPinnedBytes, "HandleRec layout");
 
 DevBuf* xchg_recv_buf(hj_ctx* ctx, int side, int kind) {
   return kind == 0 ? &ctx->xchg_recv_keys[side] : kind == 1 ? &ctx->xchg_recv_rids[side] : &ctx->xchg_recv_nulls[side];
@@ -402,9 +406,9 @@ int exchange_handles(hj_ctx* ctx, cudaStream_t st) {
   const uint32_t R = ctx->n_ranks, me = ctx->rank;
   HJ_TRY(ensure(ctx, ctx->xchg_hdl_dev, sizeof(HandleRec) * (1 + kMaxRanks)));
   auto* dev = static_cast<HandleRec*>(ctx->xchg_hdl_dev.p);
-  auto* host = reinterpret_cast<HandleRec*>(static_cast<char*>(ctx->pinned) + 16384);  // [0] mine, [1..R] everybody's
+  auto* host = reinterpret_cast<HandleRec*>(static_cast<char*>(ctx->pinned) + kPinnedHandles);  // [0] mine, [1..R] everybody's
   std::memset(&host[0], 0, sizeof(HandleRec));
-  for (int side = 0; side < 2; ++side)
+  for (int side = 0; side < 3; ++side)
     for (int kind = 0; kind < 3; ++kind) {
       DevBuf* b = xchg_recv_buf(ctx, side, kind);
       if (!b->p) continue;
@@ -441,7 +445,7 @@ bool probe_p2p(hj_ctx* ctx) {
   if (cudaMalloc(&test, 256) != cudaSuccess) ok = 0;
   if (ensure(ctx, ctx->xchg_hdl_dev, sizeof(HandleRec) * (1 + kMaxRanks)) != HJ_OK) return false;
   auto* dev = static_cast<HandleRec*>(ctx->xchg_hdl_dev.p);
-  auto* host = reinterpret_cast<HandleRec*>(static_cast<char*>(ctx->pinned) + 16384);
+  auto* host = reinterpret_cast<HandleRec*>(static_cast<char*>(ctx->pinned) + kPinnedHandles);
   std::memset(&host[0], 0, sizeof(HandleRec));
   if (ok && cudaIpcGetMemHandle(&host[0].h[0], test) != cudaSuccess) ok = 0;
   host[0].valid[0] = ok ? 1 : 0;
@@ -495,7 +499,7 @@ int run_join_sharded(hj_ctx* ctx, const hj_relation* build, const hj_relation* p
   HJ_TRY(xchg_count<K>(ctx, build, 0, &xs[0], st, &n_launch));
   HJ_TRY(xchg_count<K>(ctx, probe, 1, &xs[1], st, &n_launch));
   HJ_NCCL(ctx, nc->AllGather(cnt_dev, mat_dev, 2 * kMaxRanks, ncclUint64, comm, st));
-  auto* mat = reinterpret_cast<unsigned long long*>(static_cast<char*>(ctx->pinned) + 4096);
+  auto* mat = reinterpret_cast<unsigned long long*>(static_cast<char*>(ctx->pinned) + kPinnedCounts);
   HJ_CUDA(ctx, cudaMemcpyAsync(mat, mat_dev, size_t(R) * 2 * kMaxRanks * 8, cudaMemcpyDeviceToHost, st));
   HJ_CUDA(ctx, cudaStreamSynchronize(st));
   auto cnt = [&](uint32_t src, int side, uint32_t dst) { return mat[(size_t(src) * 2 + side) * kMaxRanks + dst]; };
@@ -652,6 +656,295 @@ int run_join_sharded(hj_ctx* ctx, const hj_relation* build, const hj_relation* p
   return HJ_OK;
 }
 
+// Grow-only device buffer that keeps its first `keep` bytes (result accumulators).
+int ensure_preserve(hj_ctx* ctx, DevBuf& b, size_t bytes, size_t keep, cudaStream_t st) {
+  if (bytes <= b.cap) return HJ_OK;
+  void* old = b.p;
+  const size_t want = ((bytes + bytes / 2) + 255) & ~size_t(255);
+  void* fresh = nullptr;
+  HJ_CUDA(ctx, cudaMalloc(&fresh, want));
+  if (old && keep) HJ_CUDA(ctx, cudaMemcpyAsync(fresh, old, keep, cudaMemcpyDeviceToDevice, st));
+  HJ_CUDA(ctx, cudaStreamSynchronize(st));
+  if (old) HJ_CUDA(ctx, cudaFree(old));
+  b.p = fresh;
+  b.cap = want;
+  return HJ_OK;
+}
+
+// The sharded join with the probe side cut into S slices (tile ranges of every rank's probe shard): while the rows of
+// slice s are partitioned and probed locally (stream `st`), slice s+1 is stored into the peers' other receive set over
+// NVLink (exchange stream `cs`). All counting (X1/X2 for the build shard and all S slices) happens up front with ONE
+// count all-gather, so the loop has no host synchronisation on the exchange stream; the 1-word all-gather after each X3
+// is the barrier "everybody's stores for this slice have landed", and because a rank only enters it after its local join
+// of the slice that last used the receive set, it also protects that set from being overwritten too early.
+// Direct (peer-mapped) exchange only; S is the same on every rank.
+template <typename K>
+int run_join_sharded_sliced(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, int mode, cudaStream_t st,
+                            hj_result_info* info, uint32_t S) {
+  constexpr bool PAY = sizeof(K) == 4;
+  NcclApi* nc = nccl_api();
+  ncclComm_t comm = static_cast<ncclComm_t>(ctx->nccl_comm);
+  cudaStream_t cs = ctx->copy_in;
+  const uint32_t R = ctx->n_ranks, me = ctx->rank;
+  const bool one_side = mode == HJ_MODE_SEMI || mode == HJ_MODE_ANTI;
+  const bool outer = mode == HJ_MODE_LEFT || mode == HJ_MODE_RIGHT;
+  const int probe_null_policy = !outer ? kNullDrop : ((ctx->opts.flags & HJ_FLAG_SQL_NULL_PROBE) ? kNullRoute : kNullAsValue);
+  uint32_t n_launch = 0;
+  cudaEvent_t* ev = ctx->ev;
+  HJ_CUDA(ctx, cudaEventRecord(ev[9], st));
+  HJ_CUDA(ctx, cudaStreamWaitEvent(cs, ev[9], 0));
+
+  // ---- X1/X2: the build shard (slot 0) and the S probe slices (slots 1..S), then one all-gather of (S+1) x R counts
+  const uint32_t n_slots = S + 1;
+  XchgSide xs[2];
+  xs[0].null_policy = kNullDrop;
+  xs[1].null_policy = probe_null_policy;
+  xs[1].send_nulls = probe_null_policy == kNullRoute;
+  HJ_TRY(ensure(ctx, ctx->xchg_cnt_dev, size_t(n_slots) * kMaxRanks * 8 * (1 + kMaxRanks)));
+  auto* cnt_dev = static_cast<unsigned long long*>(ctx->xchg_cnt_dev.p);   // [n_slots][kMaxRanks] mine
+  auto* mat_dev = cnt_dev + size_t(n_slots) * kMaxRanks;                   // [R][n_slots][kMaxRanks] everybody's
+  HJ_CUDA(ctx, cudaMemsetAsync(cnt_dev, 0, size_t(n_slots) * kMaxRanks * 8, cs));
+  HJ_TRY(xchg_count<K>(ctx, build, 0, &xs[0], cs, &n_launch));  // send_cnt = cnt_dev + 0
+  HJ_TRY(prepare_relation(ctx, probe, 1, xchg_tile<K>(), cs, &xs[1].pr));
+  const uint32_t T = xs[1].pr.meta.n_tiles;
+  if (xs[1].pr.has_dict) {
+    HJ_TRY(ensure(ctx, ctx->keys_mat[1], std::max<size_t>(1, xs[1].pr.meta.n_rows) * sizeof(K)));
+    HJ_TRY(ensure(ctx, ctx->valid_mask[1], std::max<size_t>(1, xs[1].pr.mask_words) * 4));
+  }
+  std::vector<uint32_t> t0(S + 1), Gs(S), coff(S + 1, 0);
+  for (uint32_t q = 0; q <= S; ++q) t0[q] = uint32_t(uint64_t(T) * q / S);
+  for (uint32_t q = 0; q < S; ++q) {
+    Gs[q] = std::max<uint32_t>(1, std::min<uint32_t>(t0[q + 1] - t0[q], uint32_t(kVirtualCtasPerSm) * ctx->n_sms));
+    coff[q + 1] = coff[q] + Gs[q] * kMaxRanks;
+  }
+  HJ_TRY(ensure(ctx, ctx->xchg_counts[1], size_t(coff[S]) * 4));
+  HJ_CUDA(ctx, cudaMemsetAsync(ctx->xchg_counts[1].p, 0, size_t(coff[S]) * 4, cs));
+  auto slice_args = [&](uint32_t q) {
+    XchgArgs a = xchg_args<K>(ctx, xs[1], 1);
+    a.counts = static_cast<uint32_t*>(ctx->xchg_counts[1].p) + coff[q];
+    a.send_cnt = cnt_dev + size_t(1 + q) * kMaxRanks;
+    a.tile_begin = t0[q];
+    a.tile_end = t0[q + 1];
+    return a;
+  };
+  for (uint32_t q = 0; q < S; ++q) {
+    XchgArgs a = slice_args(q);
+    if (a.tile_end > a.tile_begin) {
+      k_xchg_count<K, kXchgThreads, xchg_items<K>()><<<Gs[q], kXchgThreads, 0, cs>>>(a);
+      HJ_LAUNCH_CHECK(ctx, "k_xchg_count");
+      ++n_launch;
+    }
+    k_xchg_offsets<256><<<1, 256, 0, cs>>>(a.counts, a.send_cnt, R, Gs[q]);
+    HJ_LAUNCH_CHECK(ctx, "k_xchg_offsets");
+    ++n_launch;
+  }
+  HJ_NCCL(ctx, nc->AllGather(cnt_dev, mat_dev, size_t(n_slots) * kMaxRanks, ncclUint64, comm, cs));
+  auto* mat = reinterpret_cast<unsigned long long*>(static_cast<char*>(ctx->pinned) + kPinnedCounts);
+  if (size_t(R) * n_slots * kMaxRanks * 8 > kPinnedHandles - kPinnedCounts)
+    return fail(ctx, HJ_ERR_INVALID, "%u probe slices x %u ranks exceed the count readback area", S, R);
+  HJ_CUDA(ctx, cudaMemcpyAsync(mat, mat_dev, size_t(R) * n_slots * kMaxRanks * 8, cudaMemcpyDeviceToHost, cs));
+  HJ_CUDA(ctx, cudaStreamSynchronize(cs));
+  auto cnt = [&](uint32_t src, uint32_t slot, uint32_t dst) { return mat[(size_t(src) * n_slots + slot) * kMaxRanks + dst]; };
+
+  for (void* p : ctx->xchg_graveyard) cudaFree(p);  // every rank has entered this join: nobody maps the outgrown buffers
+  ctx->xchg_graveyard.clear();
+
+  // ---- receive sets: 0 = build rows, 1/2 = probe slices (alternating), sized for the largest slice they will hold
+  std::vector<uint64_t> n_recv(n_slots, 0);
+  uint64_t set_rows[3] = {0, 0, 0}, probe_recv_total = 0;
+  for (uint32_t slot = 0; slot < n_slots; ++slot) {
+    for (uint32_t p = 0; p < R; ++p) n_recv[slot] += cnt(p, slot, me);
+    if (n_recv[slot] >= 0xFFFFFFFFull)
+      return fail(ctx, HJ_ERR_TOO_LARGE, "rank %u would receive %llu rows in one piece (limit 2^32-2 per GPU)", me,
+                  (unsigned long long)n_recv[slot]);
+    const int set = slot == 0 ? 0 : 1 + int((slot - 1) & 1u);
+    set_rows[set] = std::max(set_rows[set], n_recv[slot]);
+    if (slot) probe_recv_total += n_recv[slot];
+  }
+  for (int set = 0; set < 3; ++set) {
+    HJ_TRY(ensure_exported(ctx, ctx->xchg_recv_keys[set], std::max<uint64_t>(1, set_rows[set]) * sizeof(K)));
+    HJ_TRY(ensure_exported(ctx, ctx->xchg_recv_rids[set], std::max<uint64_t>(1, set_rows[set]) * 8));
+    if (set && xs[1].send_nulls) HJ_TRY(ensure_exported(ctx, ctx->xchg_recv_nulls[set], std::max<uint64_t>(1, set_rows[set])));
+  }
+  HJ_TRY(exchange_handles(ctx, cs));
+
+  uint64_t bytes_sent = 0;
+  // X3 of one slot into receive set `set` of every rank, then the barrier
+  auto scatter_slot = [&](uint32_t slot, int side, int set, XchgArgs a, uint32_t G) -> int {
+    const bool nulls = xs[side].send_nulls;
+    uint64_t send_off = 0;
+    for (uint32_t d = 0; d < R; ++d) {
+      uint64_t base_in_d = 0;  // where my rows start in rank d's receive set: after the rows of the ranks before me
+      for (uint32_t s2 = 0; s2 < me; ++s2) base_in_d += cnt(s2, slot, d);
+      a.adj[d] = static_cast<uint32_t>(base_in_d - send_off);
+      send_off += cnt(me, slot, d);
+      if (d == me) {
+        a.dst_keys[d] = ctx->xchg_recv_keys[set].p;
+        a.dst_rids[d] = static_cast<uint64_t*>(ctx->xchg_recv_rids[set].p);
+        a.dst_nulls[d] = nulls ? static_cast<uint8_t*>(ctx->xchg_recv_nulls[set].p) : nullptr;
+      } else {
+        a.dst_keys[d] = ctx->xchg_peer[d][set * 3 + 0].ptr;
+        a.dst_rids[d] = static_cast<uint64_t*>(ctx->xchg_peer[d][set * 3 + 1].ptr);
+        a.dst_nulls[d] = nulls ? static_cast<uint8_t*>(ctx->xchg_peer[d][set * 3 + 2].ptr) : nullptr;
+        if (cnt(me, slot, d) && (!a.dst_keys[d] || !a.dst_rids[d] || (nulls && !a.dst_nulls[d])))
+          return fail(ctx, HJ_ERR_COMM, "rank %u has no mapping of rank %u's receive set %d", me, d, set);
+      }
+    }
+    if (a.tile_end > a.tile_begin) {
+      auto k = k_xchg_scatter<K, kXchgThreads, xchg_items<K>()>;
+      const size_t smem = size_t(xchg_tile<K>()) * (sizeof(K) + 8 + 2);
+      HJ_TRY(set_smem(ctx, k, smem));
+      k<<<G, kXchgThreads, smem, cs>>>(a);
+      HJ_LAUNCH_CHECK(ctx, "k_xchg_scatter");
+      ++n_launch;
+    }
+    bytes_sent += (send_off - cnt(me, slot, me)) * (sizeof(K) + 8 + (nulls ? 1 : 0));
+    HJ_NCCL(ctx, nc->AllGather(cnt_dev, mat_dev, 1, ncclUint64, comm, cs));  // barrier
+    return HJ_OK;
+  };
+
+  // ---- build rows: exchange, then partition them locally (per-side set 2)
+  HJ_TRY(scatter_slot(0, 0, 0, xchg_args<K>(ctx, xs[0], 0), xs[0].G));
+  HJ_CUDA(ctx, cudaEventRecord(ev[10], cs));
+  HJ_TRY(scatter_slot(1, 1, 1, slice_args(0), Gs[0]));  // first probe slice right behind it
+  HJ_CUDA(ctx, cudaEventRecord(ctx->ev_x[0], cs));
+
+  auto recv_relation = [&](int set, uint64_t rows, bool nulls, hj_segment* seg, hj_relation* rel) {
+    std::memset(seg, 0, sizeof(hj_segment));
+    seg->n_rows = static_cast<uint32_t>(rows);
+    seg->kind = HJ_SEG_VALUE;
+    seg->key_type = sizeof(K) == 8 ? HJ_KEY_INT64 : HJ_KEY_INT32;
+    seg->values = ctx->xchg_recv_keys[set].p;
+    seg->nulls = nulls ? static_cast<const uint8_t*>(ctx->xchg_recv_nulls[set].p) : nullptr;
+    rel->segs = seg;
+    rel->n_segs = 1;
+    rel->location = HJ_LOC_DEVICE;
+    rel->n_rows = rows;
+  };
+  struct RowidGuard {  // prepare_relation marks a relation "exchanged" through ctx->xchg_rowids[side]
+    hj_ctx* c;
+    ~RowidGuard() { for (auto& r : c->xchg_rowids) r = nullptr; }
+  } guard{ctx};
+
+  const int radix_bits = ctx->opts.radix_bits >= 0 ? std::min(ctx->opts.radix_bits, kMaxRadixBits)
+                                                   : radix_bits_for(n_recv[0], sizeof(K) == 8 ? HJ_KEY_INT64 : HJ_KEY_INT32);
+  const int bits2 = radix_bits > kSinglePassMaxBits ? radix_bits / 2 : 0;
+  Launches nl;
+  hj_segment seg_b, seg_p[2];
+  hj_relation rel_b, rel_p[2];
+  PreparedRel pb, pp[2];
+  PartState sb, sp[2];
+  HJ_CUDA(ctx, cudaStreamWaitEvent(st, ev[10], 0));
+  recv_relation(0, n_recv[0], false, &seg_b, &rel_b);
+  ctx->xchg_rowids[2] = static_cast<const uint64_t*>(ctx->xchg_recv_rids[0].p);
+  HJ_TRY(prepare_relation(ctx, &rel_b, 2, tile1<K>(), st, &pb));
+  HJ_TRY((stage_alloc<K, PAY>(ctx, pb, 2, radix_bits, bits2, &sb)));
+  HJ_CUDA(ctx, cudaEventRecord(ev[12], st));
+  HJ_TRY(stage_hist<K>(ctx, pb, 2, radix_bits, bits2, kNullDrop, sb, st, &nl));
+  HJ_CUDA(ctx, cudaEventRecord(ev[13], st));
+  HJ_TRY((stage_pass1<K, PAY>(ctx, pb, 2, radix_bits, bits2, kNullDrop, sb, st, &nl)));
+  HJ_CUDA(ctx, cudaEventRecord(ev[14], st));
+  HJ_TRY((stage_pass2<K, PAY>(ctx, pb, 2, radix_bits, bits2, kNullDrop, sb, st, &nl)));
+  HJ_CUDA(ctx, cudaEventRecord(ev[15], st));
+  float ph_ms[HJ_N_PHASES] = {};  // local-join phases, summed over the build side and all slices (they run while the next
+                                  // slice is being exchanged, so they include that interference)
+
+  // ---- probe slices: exchange slice q+1 while slice q is joined
+  HJ_TRY(ensure_preserve(ctx, ctx->acc_probe, std::max<uint64_t>(1, probe_recv_total) * 8, 0, st));
+  if (!one_side) HJ_TRY(ensure_preserve(ctx, ctx->acc_build, std::max<uint64_t>(1, probe_recv_total) * 8, 0, st));
+  auto* rb = static_cast<Readback*>(ctx->pinned);
+  uint64_t total = 0, probe_tuples = 0, build_tuples = 0;
+  uint32_t overflow_parts = 0;
+  int max_passes = 0;
+  for (uint32_t q = 0; q < S; ++q) {
+    const int cur = q & 1, nxt = (q + 1) & 1;
+    if (q + 1 < S) {
+      if (q >= 1) {
+        // receive set `nxt` is about to be overwritten on EVERY rank: each rank enters this barrier only after its own
+        // join of slice q-1 (the last reader of that set) has finished
+        HJ_CUDA(ctx, cudaStreamWaitEvent(cs, ctx->ev_done[nxt], 0));
+        HJ_NCCL(ctx, nc->AllGather(cnt_dev, mat_dev, 1, ncclUint64, comm, cs));
+      }
+      HJ_TRY(scatter_slot(q + 2, 1, 1 + nxt, slice_args(q + 1), Gs[q + 1]));
+      HJ_CUDA(ctx, cudaEventRecord(ctx->ev_x[nxt], cs));
+    }
+    if (q + 1 == S) HJ_CUDA(ctx, cudaEventRecord(ev[11], cs));
+    HJ_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_x[cur], 0));
+    const int side = 3 + cur;
+    recv_relation(1 + cur, n_recv[1 + q], xs[1].send_nulls, &seg_p[cur], &rel_p[cur]);
+    ctx->xchg_rowids[side] = static_cast<const uint64_t*>(ctx->xchg_recv_rids[1 + cur].p);
+    pp[cur] = PreparedRel{};
+    HJ_TRY(prepare_relation(ctx, &rel_p[cur], side, tile1<K>(), st, &pp[cur]));
+    HJ_TRY((stage_alloc<K, PAY>(ctx, pp[cur], side, radix_bits, bits2, &sp[cur])));
+    HJ_CUDA(ctx, cudaEventRecord(ev[1], st));
+    HJ_TRY(stage_hist<K>(ctx, pp[cur], side, radix_bits, bits2, probe_null_policy, sp[cur], st, &nl));
+    HJ_CUDA(ctx, cudaEventRecord(ev[2], st));
+    HJ_TRY((stage_pass1<K, PAY>(ctx, pp[cur], side, radix_bits, bits2, probe_null_policy, sp[cur], st, &nl)));
+    HJ_CUDA(ctx, cudaEventRecord(ev[3], st));
+    HJ_TRY((stage_pass2<K, PAY>(ctx, pp[cur], side, radix_bits, bits2, probe_null_policy, sp[cur], st, &nl)));
+    HJ_CUDA(ctx, cudaEventRecord(ev[4], st));
+    int passes = 0;
+    HJ_TRY((probe_phase<K, PAY>(ctx, pb, pp[cur], sp[cur], 2, side, cur, radix_bits, bits2, mode, probe_null_policy, true,
+                                n_recv[0], n_recv[1 + q], st, &nl, &passes, ev[5], ev[6])));
+    if (q == 0) {
+      ph_ms[HJ_PH_MATERIALIZE] += ev_ms(ev[12], ev[13]);
+      ph_ms[HJ_PH_SCATTER1] += ev_ms(ev[13], ev[14]);
+      ph_ms[HJ_PH_SCATTER2] += ev_ms(ev[14], ev[15]);
+    }
+    ph_ms[HJ_PH_MATERIALIZE] += ev_ms(ev[1], ev[2]);
+    ph_ms[HJ_PH_SCATTER1] += ev_ms(ev[2], ev[3]);
+    ph_ms[HJ_PH_SCATTER2] += ev_ms(ev[3], ev[4]);
+    if (passes == 1) {
+      ph_ms[HJ_PH_BUILD_PROBE] += ev_ms(ev[4], ev[5]);
+      ph_ms[HJ_PH_FINALIZE] += ev_ms(ev[5], ev[6]);
+    }
+    const uint64_t rows = rb->out.n_rows;  // probe_phase synchronised `st`
+    build_tuples = rb->n_build_tuples;
+    probe_tuples += rb->n_probe_tuples;
+    overflow_parts = std::max(overflow_parts, rb->plan.n_overflow_parts);
+    max_passes = std::max(max_passes, passes);
+    if (rows) {
+      HJ_TRY(ensure_preserve(ctx, ctx->acc_probe, (total + rows) * 8, total * 8, st));
+      HJ_CUDA(ctx, cudaMemcpyAsync(static_cast<char*>(ctx->acc_probe.p) + total * 8, ctx->out_probe[cur].p, rows * 8,
+                                   cudaMemcpyDeviceToDevice, st));
+      if (!one_side) {
+        HJ_TRY(ensure_preserve(ctx, ctx->acc_build, (total + rows) * 8, total * 8, st));
+        HJ_CUDA(ctx, cudaMemcpyAsync(static_cast<char*>(ctx->acc_build.p) + total * 8, ctx->out_build[cur].p, rows * 8,
+                                     cudaMemcpyDeviceToDevice, st));
+      }
+    }
+    HJ_CUDA(ctx, cudaEventRecord(ctx->ev_done[cur], st));
+    total += rows;
+  }
+  HJ_CUDA(ctx, cudaEventRecord(ev[6], st));
+  HJ_CUDA(ctx, cudaStreamSynchronize(cs));
+  HJ_CUDA(ctx, cudaStreamSynchronize(st));
+
+  ctx->has_result = true;
+  ctx->res_build = ctx->acc_build.p;
+  ctx->res_probe = ctx->acc_probe.p;
+  ctx->n_result = total;
+  ctx->n_sides = one_side ? 1 : 2;
+  info->n_rows = total;
+  info->n_sides = ctx->n_sides;
+  info->radix_bits = radix_bits;
+  info->n_build_tuples = build_tuples;
+  info->n_probe_tuples = probe_tuples;
+  info->n_partitions = 1u << radix_bits;
+  info->n_overflow_partitions = overflow_parts;
+  info->n_probe_passes = max_passes;
+  info->n_probe_slices = S;
+  hj_timings& t = ctx->timings;
+  std::memset(&t, 0, sizeof(t));
+  for (int ph : {HJ_PH_MATERIALIZE, HJ_PH_SCATTER1, HJ_PH_SCATTER2, HJ_PH_BUILD_PROBE, HJ_PH_FINALIZE}) t.ms[ph] = ph_ms[ph];
+  t.ms[HJ_PH_XCHG_PARTITION] = ev_ms(ev[9], ev[10]);  // shard prepare + all X1/X2 + build X3
+  t.ms[HJ_PH_XCHG_TRANSFER] = ev_ms(ev[10], ev[11]);  // probe slices' X3 (overlaps the local joins of the earlier slices)
+  t.ms[HJ_PH_TOTAL] = ev_ms(ev[9], ev[6]);
+  t.n_kernel_launches = nl.n + n_launch;
+  t.bytes_nvlink_sent = bytes_sent;
+  return HJ_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -712,13 +1005,26 @@ int hj_join_sharded(hj_ctx* ctx, const hj_relation* build_shard, const hj_relati
     for (uint32_t i = 0; i < r->n_segs; ++i) wide |= r->segs[i].key_type == HJ_KEY_INT64 ? 1ull : 0ull;
   HJ_TRY(ensure(ctx, ctx->xchg_cnt_dev, size_t(2) * kMaxRanks * 8 * (1 + kMaxRanks)));
   auto* dev = static_cast<unsigned long long*>(ctx->xchg_cnt_dev.p);
-  auto* host = reinterpret_cast<unsigned long long*>(static_cast<char*>(ctx->pinned) + 4096);
+  auto* host = reinterpret_cast<unsigned long long*>(static_cast<char*>(ctx->pinned) + kPinnedCounts);
   NcclApi* nc = nccl_api();
-  HJ_CUDA(ctx, cudaMemcpyAsync(dev, &wide, 8, cudaMemcpyHostToDevice, st));
+  unsigned long long word = (static_cast<unsigned long long>(probe_shard->n_rows) << 1) | wide;  // + my probe rows (slicing)
+  HJ_CUDA(ctx, cudaMemcpyAsync(dev, &word, 8, cudaMemcpyHostToDevice, st));
   HJ_NCCL(ctx, nc->AllGather(dev, dev + kMaxRanks, 1, ncclUint64, static_cast<ncclComm_t>(ctx->nccl_comm), st));
   HJ_CUDA(ctx, cudaMemcpyAsync(host, dev + kMaxRanks, size_t(ctx->n_ranks) * 8, cudaMemcpyDeviceToHost, st));
   HJ_CUDA(ctx, cudaStreamSynchronize(st));
-  for (int r = 0; r < ctx->n_ranks; ++r) wide |= host[r];
+  for (int r = 0; r < ctx->n_ranks; ++r) wide |= host[r] & 1ull;
+  // Probe slices (same S on every rank): opt-in through hj_options.stream_slice_rows. Slicing bounds the receive buffers
+  // to two slices (what a 4 B x 4 B join needs to fit), but it is NOT faster: measured on 2 x B200, C2 per rank,
+  // unsliced 54.8 ms, S=2 60.0 ms, S=4 66.4 ms — the persistent X3 CTAs hold their SMs, so the 1024-thread join kernels
+  // of the previous slice wait instead of overlapping, and every slice rebuilds the build-side hash tables.
+  uint64_t max_probe_rows = 0;
+  for (int r = 0; r < ctx->n_ranks; ++r) max_probe_rows = std::max<uint64_t>(max_probe_rows, host[r] >> 1);
+  const uint32_t S = ctx->opts.stream_slice_rows
+                         ? uint32_t(std::min<uint64_t>(kMaxXchgSlices, max_probe_rows / ctx->opts.stream_slice_rows)) : 1u;
+  const bool direct = ctx->p2p_ok && !(ctx->opts.flags & HJ_FLAG_XCHG_STAGED);
+  if (direct && S >= 2)
+    return wide ? run_join_sharded_sliced<int64_t>(ctx, build_shard, probe_shard, mode, st, out_info, S)
+                : run_join_sharded_sliced<int32_t>(ctx, build_shard, probe_shard, mode, st, out_info, S);
   return wide ? run_join_sharded<int64_t>(ctx, build_shard, probe_shard, mode, st, out_info)
               : run_join_sharded<int32_t>(ctx, build_shard, probe_shard, mode, st, out_info);
 }

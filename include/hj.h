@@ -128,7 +128,11 @@ typedef struct hj_options {
   uint32_t reserved0;
   uint64_t output_capacity;   /* 0: estimate; else initial capacity of the result buffers in
                                  rows (the library grows and re-probes on overflow)          */
-  uint64_t stream_slice_rows; /* streamed join (hj_bind_output): minimum probe rows per slice; 0: 32 Mi */
+  uint64_t stream_slice_rows; /* streamed join (hj_bind_output): minimum probe rows per slice; 0: 32 Mi.
+                                 hj_join_sharded: != 0 cuts every rank's probe shard into up to 8 slices of at
+                                 least this many rows (same value on all ranks) that are exchanged one after the
+                                 other, so the receive buffers hold two slices instead of the whole relation;
+                                 0: one piece (faster) */
   uint64_t reserved[3];
 } hj_options;
 

@@ -103,6 +103,9 @@ def main():
     ap.add_argument("--backend", default="nccl", choices=["nccl", "gloo"])
     ap.add_argument("--big", action="store_true", help="nccl only: add a 2 M x 8 M case")
     ap.add_argument("--staged", action="store_true", help="nccl only: HJ_FLAG_XCHG_STAGED (send buffers + ncclSend/Recv)")
+    ap.add_argument("--slice-rows", type=int, default=0,
+                    help="nccl only: hj_options.stream_slice_rows — small values force the sliced exchange (probe slices "
+                         "exchanged while the previous slice is joined) on these small cases")
     args = ap.parse_args()
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local_rank = int(os.environ.get("LOCAL_RANK", rank))
@@ -114,7 +117,8 @@ def main():
 
     j = None
     if args.backend == "nccl":
-        j = hj.HashJoin(device=local_rank, flags=abi.FLAG_XCHG_STAGED if args.staged else 0)
+        j = hj.HashJoin(device=local_rank, flags=abi.FLAG_XCHG_STAGED if args.staged else 0,
+                        stream_slice_rows=args.slice_rows)
         uid = [hj.comm_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(uid, src=0)
         j.comm_init(uid[0], world, rank)
@@ -152,8 +156,9 @@ def main():
                 ob_b, ob_p, oinfo = ob.oracle_join(full_b, full_p, abi.MODES[mode])
                 got, want = ob.canonical(gb, gp), ob.canonical(ob_b, ob_p)
                 ok = got.shape == want.shape and np.array_equal(got, want)
+                slices = info.n_probe_slices if args.backend == "nccl" else 0
                 print(f"[{args.backend} x{world}] {name:14s} {mode:5s} rows={len(want):8d} per-rank={[len(x[1]) for x in parts]} "
-                      f"{'OK' if ok else 'MISMATCH'}", flush=True)
+                      f"slices={slices} {'OK' if ok else 'MISMATCH'}", flush=True)
                 failures += 0 if ok else 1
     res = [failures]
     dist.broadcast_object_list(res, src=0)

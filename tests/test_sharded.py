@@ -69,7 +69,11 @@ def test_sharded_join_nccl_2gpus():
     n = torch.cuda.device_count()
     if n < 2:
         pytest.skip("needs >= 2 GPUs (run with gpurun --gpus 2)")
-    for extra in ([], ["--staged"]):  # direct peer-mapped exchange (default) and the NCCL-staged one
+    # direct peer-mapped exchange (default), the NCCL-staged one, and the sliced exchange (slice s+1 travels while slice s
+    # is joined) forced onto these small cases
+    for extra in ([], ["--staged"], ["--slice-rows", "700"]):
         r = _torchrun(2, "--backend", "nccl", "--big", *extra)
         assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
         assert "MISMATCH" not in r.stdout and r.stdout.count(" OK") == 25
+        if extra and extra[0] == "--slice-rows":
+            assert "slices=8" in r.stdout and "slices=0" in r.stdout  # big cases sliced, the empty-build case not
