@@ -97,6 +97,17 @@ class RelationBuilder:
         s.attr, k2 = _ptr_and_keep(attr)
         return self._add(s, k1, k2)
 
+    def add_reference(self, chunk_id, pos_list, referenced, key_type):
+        """ReferenceColumn as stored: pos_list = (n, 2) uint32 [chunk_id, chunk_offset] rows (NULL_ROW_ID = NULL key) into
+        `referenced`, a built relation describing the key column of the data table (same location). The library gathers
+        the keys on the device (HJ_SEG_REFERENCE)."""
+        s = abi.Segment()
+        s.chunk_id, s.n_rows, s.kind = chunk_id, len(pos_list), abi.SEG_REFERENCE
+        s.key_type = key_type
+        s.attr, k1 = _ptr_and_keep(pos_list)
+        s.values = C.cast(C.pointer(referenced), C.c_void_p)
+        return self._add(s, k1, referenced)
+
     def build(self):
         n = len(self._segs)
         arr = (abi.Segment * max(n, 1))(*self._segs)

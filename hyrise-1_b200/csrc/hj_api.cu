@@ -57,7 +57,7 @@ thread_local std::string g_create_error;
 
 constexpr int kSides = 5;
 // pinned readback area: Readback at 0, exchange count matrices at kPinnedCounts, IPC handle records at kPinnedHandles
-constexpr size_t kPinnedBytes = 96 * 1024, kPinnedCounts = 4096, kPinnedHandles = 64 * 1024;
+constexpr size_t kPinnedBytes = 96 * 1024, kPinnedRefFlags = 3584, kPinnedCounts = 4096, kPinnedHandles = 64 * 1024;
 
 struct hj_ctx {
   int device = 0;
@@ -95,6 +95,8 @@ struct hj_ctx {
   // receive sets: 0 = build, 1 = probe (or probe slices 0, 2, ..), 2 = probe slices 1, 3, ..
   DevBuf xchg_counts[2], xchg_cnt_dev, xchg_send_keys[2], xchg_send_rids[2], xchg_send_nulls[2], xchg_recv_keys[3],
       xchg_recv_rids[3], xchg_recv_nulls[3];
+  DevBuf ref_arena[2], ref_out[2];  // REFERENCE segments: staged referenced columns + PosLists / gathered keys + flags
+  uint64_t ref_h2d_bytes = 0;
   DevBuf acc_build, acc_probe;      // sliced sharded join: the slices' PosLists, appended
   cudaEvent_t ev_x[2] = {};         // sliced sharded join: slice set exchanged (recorded on copy_in, the exchange stream)
   struct PeerMap { cudaIpcMemHandle_t handle; void* ptr = nullptr; };
@@ -113,7 +115,7 @@ struct hj_ctx {
                       &out_build[0], &out_build[1], &out_probe[0], &out_probe[1], &misc, &xchg_counts[0], &xchg_counts[1], &xchg_cnt_dev, &xchg_send_keys[0],
                       &xchg_send_keys[1], &xchg_send_rids[0], &xchg_send_rids[1], &xchg_send_nulls[0], &xchg_send_nulls[1],
                       &xchg_recv_keys[0], &xchg_recv_keys[1], &xchg_recv_rids[0], &xchg_recv_rids[1], &xchg_recv_nulls[0],
-                      &xchg_recv_nulls[1], &xchg_recv_keys[2], &xchg_recv_rids[2], &xchg_recv_nulls[2], &acc_build, &acc_probe,
+                      &xchg_recv_nulls[1], &xchg_recv_keys[2], &xchg_recv_rids[2], &xchg_recv_nulls[2], &acc_build, &acc_probe, &ref_arena[0], &ref_arena[1], &ref_out[0], &ref_out[1],
                       &xchg_hdl_dev})
       all_bufs.push_back(b);
   }
@@ -182,7 +184,29 @@ int validate_relation(hj_ctx* ctx, const hj_relation* r, const char* name) {
     const hj_segment& s = r->segs[i];
     if (s.key_type != HJ_KEY_INT32 && s.key_type != HJ_KEY_INT64)
       return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: key type %u unsupported (int32/int64 keys only)", name, i, s.key_type);
-    if (s.kind > HJ_SEG_GATHERED) return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: bad segment kind %u", name, i, s.kind);
+    if (s.kind > HJ_SEG_REFERENCE) return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: bad segment kind %u", name, i, s.kind);
+    if (s.reserved0) return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: reserved0 must be 0", name, i);
+    if (s.kind == HJ_SEG_REFERENCE) {
+      const auto* ref = static_cast<const hj_relation*>(s.values);
+      if (!ref) return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: REFERENCE without the referenced column", name, i);
+      if (s.n_rows && !s.attr) return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: REFERENCE without a PosList", name, i);
+      if (ref->location != r->location)
+        return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: referenced column and PosList must live in the same place", name, i);
+      if (ref->n_segs && !ref->segs) return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: referenced column has no segment array", name, i);
+      for (uint32_t c = 0; c < ref->n_segs; ++c) {
+        const hj_segment& q = ref->segs[c];
+        if (q.kind != HJ_SEG_VALUE && q.kind != HJ_SEG_DICT)
+          return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: referenced chunk %u must be a VALUE or DICT column (a ReferenceColumn "
+                      "never points at another reference table)", name, i, c);
+        if (q.key_type != s.key_type) return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: referenced chunk %u has another key type", name, i, c);
+        if (q.kind == HJ_SEG_DICT && q.attr_width != 1 && q.attr_width != 2 && q.attr_width != 4)
+          return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: referenced chunk %u: attribute vector width %u", name, i, c, q.attr_width);
+        if (q.n_rows && (q.kind == HJ_SEG_DICT ? !q.attr || (q.dict_n && !q.values) : !q.values))
+          return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: referenced chunk %u has no data", name, i, c);
+      }
+      n += s.n_rows;
+      continue;
+    }
     if (s.kind == HJ_SEG_DICT) {
       if (s.attr_width != 1 && s.attr_width != 2 && s.attr_width != 4)
         return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: attribute vector width %u (FixedSizeByteAligned 1/2/4 only)", name, i,
@@ -255,7 +279,7 @@ int prepare_relation(hj_ctx* ctx, const hj_relation* r, int side, uint32_t tile,
     const uint32_t nt = (s.n_rows + tile - 1) / tile;
     tiles += nt;
     rows += s.n_rows;
-    if (host) {
+    if (host && !s.reserved0) {  // reserved0 = 1: arrays already on the device (gathered REFERENCE segment)
       if (s.kind == HJ_SEG_DICT) {
         if (s.dict_n) off_values[i] = plan_copy(s.values, size_t(s.dict_n) * key_bytes(s));
         if (s.n_rows) off_attr[i] = plan_copy(s.attr, size_t(s.n_rows) * s.attr_width);
@@ -275,6 +299,7 @@ int prepare_relation(hj_ctx* ctx, const hj_relation* r, int side, uint32_t tile,
     for (uint32_t i = 0; i < n_segs; ++i) {
       const hj_segment& s = r->segs[i];
       DevSegment& d = pr.segs[i];
+      if (s.reserved0) continue;
       if (s.kind == HJ_SEG_DICT) {
         d.values = s.dict_n ? base + off_values[i] : nullptr;
         d.attr = s.n_rows ? base + off_attr[i] : nullptr;
@@ -327,6 +352,183 @@ int prepare_relation(hj_ctx* ctx, const hj_relation* r, int side, uint32_t tile,
   pr.meta.uniform_shift = shift;
   pr.meta.identity = identity ? 1u : 0u;
   pr.mask_words = words;
+  return HJ_OK;
+}
+
+// N1: turns every HJ_SEG_REFERENCE segment of `in` into a device-resident GATHERED segment (keys + null flags gathered
+// through the PosList by k_gather_refs). `out->rel` is the relation to join instead of `in`.
+struct RefRewrite {
+  std::vector<hj_segment> segs;
+  hj_relation rel{};
+  bool any = false;
+};
+
+int gather_references(hj_ctx* ctx, const hj_relation* in, int side, cudaStream_t st, RefRewrite* out) {
+  out->rel = *in;
+  out->any = false;
+  std::vector<uint32_t> ref_segs;
+  for (uint32_t i = 0; i < in->n_segs; ++i)
+    if (in->segs[i].kind == HJ_SEG_REFERENCE) ref_segs.push_back(i);
+  if (ref_segs.empty()) return HJ_OK;
+  out->any = true;
+  out->segs.assign(in->segs, in->segs + in->n_segs);
+  const bool host = in->location == HJ_LOC_HOST;
+  auto key_bytes = [](uint8_t key_type) { return key_type == HJ_KEY_INT64 ? size_t(8) : size_t(4); };
+  auto align = [](size_t x) { return (x + 255) & ~size_t(255); };
+
+  // distinct referenced columns (normally one: all chunks of a reference table point at the same data table)
+  std::vector<const hj_relation*> refs;
+  std::vector<uint32_t> ref_of(ref_segs.size());
+  for (size_t j = 0; j < ref_segs.size(); ++j) {
+    const auto* r = static_cast<const hj_relation*>(in->segs[ref_segs[j]].values);
+    size_t k = 0;
+    while (k < refs.size() && refs[k] != r) ++k;
+    if (k == refs.size()) refs.push_back(r);
+    ref_of[j] = uint32_t(k);
+  }
+  // arena: [error flag][DevSegment tables][RefJob table][host data: referenced arrays, PosLists]
+  struct Copy { const void* src; size_t bytes; size_t off; };
+  std::vector<Copy> copies;
+  size_t arena = 256;
+  std::vector<size_t> seg_tab_off(refs.size());
+  for (size_t k = 0; k < refs.size(); ++k) {
+    seg_tab_off[k] = arena;
+    arena += align(std::max<size_t>(1, refs[k]->n_segs) * sizeof(DevSegment));
+  }
+  const size_t job_off = arena;
+  arena += align(ref_segs.size() * sizeof(RefJob));
+  auto plan = [&](const void* src, size_t bytes) {
+    const size_t off = arena;
+    copies.push_back({src, bytes, off});
+    arena += align(bytes);
+    return off;
+  };
+  std::vector<std::vector<DevSegment>> tabs(refs.size());
+  std::vector<std::vector<size_t>> o_val(refs.size()), o_nul(refs.size()), o_att(refs.size());
+  for (size_t k = 0; k < refs.size(); ++k) {
+    const hj_relation* r = refs[k];
+    tabs[k].resize(r->n_segs);
+    o_val[k].assign(r->n_segs, 0);
+    o_nul[k].assign(r->n_segs, 0);
+    o_att[k].assign(r->n_segs, 0);
+    for (uint32_t c = 0; c < r->n_segs; ++c) {
+      const hj_segment& q = r->segs[c];
+      DevSegment& d = tabs[k][c];
+      std::memset(&d, 0, sizeof(d));
+      d.values = q.values;
+      d.nulls = q.kind == HJ_SEG_DICT ? nullptr : q.nulls;
+      d.attr = q.kind == HJ_SEG_DICT ? q.attr : nullptr;
+      d.n_rows = q.n_rows;
+      d.chunk_id = q.chunk_id;
+      d.null_value_id = q.null_value_id;
+      d.kind = q.kind;
+      d.key_type = q.key_type;
+      d.attr_width = q.attr_width;
+      if (host) {
+        if (q.kind == HJ_SEG_DICT) {
+          if (q.dict_n) o_val[k][c] = plan(q.values, size_t(q.dict_n) * key_bytes(q.key_type));
+          if (q.n_rows) o_att[k][c] = plan(q.attr, size_t(q.n_rows) * q.attr_width);
+        } else {
+          if (q.n_rows) o_val[k][c] = plan(q.values, size_t(q.n_rows) * key_bytes(q.key_type));
+          if (q.n_rows && q.nulls) o_nul[k][c] = plan(q.nulls, q.n_rows);
+        }
+      }
+    }
+  }
+  std::vector<size_t> o_pos(ref_segs.size(), 0), o_out(ref_segs.size(), 0), o_outn(ref_segs.size(), 0);
+  size_t out_bytes = 0;
+  uint64_t total_rows = 0;
+  for (size_t j = 0; j < ref_segs.size(); ++j) {
+    const hj_segment& s = in->segs[ref_segs[j]];
+    if (host && s.n_rows) o_pos[j] = plan(s.attr, size_t(s.n_rows) * 8);
+    o_out[j] = out_bytes;
+    out_bytes += align(size_t(s.n_rows) * key_bytes(s.key_type));
+    o_outn[j] = out_bytes;
+    out_bytes += align(s.n_rows);
+    total_rows += s.n_rows;
+  }
+  HJ_TRY(ensure(ctx, ctx->ref_arena[side], arena));
+  HJ_TRY(ensure(ctx, ctx->ref_out[side], std::max<size_t>(256, out_bytes)));
+  char* base = static_cast<char*>(ctx->ref_arena[side].p);
+  char* obase = static_cast<char*>(ctx->ref_out[side].p);
+  HJ_CUDA(ctx, cudaMemsetAsync(base, 0, 256, st));
+  for (const Copy& c : copies) {
+    HJ_CUDA(ctx, cudaMemcpyAsync(base + c.off, c.src, c.bytes, cudaMemcpyHostToDevice, st));
+    ctx->ref_h2d_bytes += c.bytes;
+  }
+  for (size_t k = 0; k < refs.size(); ++k) {
+    if (host)
+      for (uint32_t c = 0; c < refs[k]->n_segs; ++c) {
+        const hj_segment& q = refs[k]->segs[c];
+        DevSegment& d = tabs[k][c];
+        if (q.kind == HJ_SEG_DICT) {
+          d.values = q.dict_n ? base + o_val[k][c] : nullptr;
+          d.attr = q.n_rows ? base + o_att[k][c] : nullptr;
+        } else {
+          d.values = q.n_rows ? base + o_val[k][c] : nullptr;
+          d.nulls = (q.n_rows && q.nulls) ? reinterpret_cast<const uint8_t*>(base + o_nul[k][c]) : nullptr;
+        }
+      }
+    if (refs[k]->n_segs)
+      HJ_CUDA(ctx, cudaMemcpyAsync(base + seg_tab_off[k], tabs[k].data(), refs[k]->n_segs * sizeof(DevSegment),
+                                   cudaMemcpyHostToDevice, st));
+  }
+  std::vector<RefJob> jobs(ref_segs.size());
+  uint32_t row_begin = 0;
+  for (size_t j = 0; j < ref_segs.size(); ++j) {
+    hj_segment& s = out->segs[ref_segs[j]];
+    RefJob& jb = jobs[j];
+    jb.pos = host ? reinterpret_cast<const uint64_t*>(base + o_pos[j]) : static_cast<const uint64_t*>(s.attr);
+    jb.ref = reinterpret_cast<const DevSegment*>(base + seg_tab_off[ref_of[j]]);
+    jb.out_values = obase + o_out[j];
+    jb.out_nulls = reinterpret_cast<uint8_t*>(obase + o_outn[j]);
+    jb.n_ref = refs[ref_of[j]]->n_segs;
+    jb.n_rows = s.n_rows;
+    jb.row_begin = row_begin;
+    jb.key_type = s.key_type;
+    row_begin += s.n_rows;
+    // the segment the join sees: gathered keys + flags on the device, RowIDs (chunk_id, 0..n_rows-1)
+    s.kind = HJ_SEG_GATHERED;
+    s.reserved0 = 1;
+    s.values = jb.out_values;
+    s.nulls = jb.out_nulls;
+    s.attr = nullptr;
+    s.row_offsets = nullptr;
+  }
+  HJ_CUDA(ctx, cudaMemcpyAsync(base + job_off, jobs.data(), jobs.size() * sizeof(RefJob), cudaMemcpyHostToDevice, st));
+  if (total_rows) {
+    const uint32_t grid = uint32_t(std::min<uint64_t>((total_rows + 255) / 256, uint64_t(ctx->n_sms) * 16));
+    k_gather_refs<<<grid, 256, 0, st>>>(reinterpret_cast<const RefJob*>(base + job_off), uint32_t(jobs.size()),
+                                        uint32_t(total_rows), reinterpret_cast<uint32_t*>(base));
+    HJ_LAUNCH_CHECK(ctx, "k_gather_refs");
+  }
+  // jobs/tabs are pageable vectors: cudaMemcpyAsync has staged them when it returns, so they may die with this frame
+  auto* flag = reinterpret_cast<uint32_t*>(static_cast<char*>(ctx->pinned) + kPinnedRefFlags) + side;
+  HJ_CUDA(ctx, cudaMemcpyAsync(flag, base, 4, cudaMemcpyDeviceToHost, st));
+  out->rel.segs = out->segs.data();
+  return HJ_OK;
+}
+
+// REFERENCE gather for both relations of a join; the join then runs over rw[i].rel where rw[i].any.
+int gather_both(hj_ctx* ctx, const hj_relation*& build, const hj_relation*& probe, cudaStream_t st, RefRewrite* rw) {
+  ctx->ref_h2d_bytes = 0;
+  std::memset(static_cast<char*>(ctx->pinned) + kPinnedRefFlags, 0, 8);
+  HJ_TRY(gather_references(ctx, build, 0, st, &rw[0]));
+  HJ_TRY(gather_references(ctx, probe, 1, st, &rw[1]));
+  if (rw[0].any) build = &rw[0].rel;
+  if (rw[1].any) probe = &rw[1].rel;
+  return HJ_OK;
+}
+
+// after the join has synchronised the stream: did k_gather_refs meet a RowID outside the referenced table?
+int check_reference_flags(hj_ctx* ctx, const RefRewrite* rw) {
+  if (!rw[0].any && !rw[1].any) return HJ_OK;
+  const auto* flag = reinterpret_cast<const uint32_t*>(static_cast<const char*>(ctx->pinned) + kPinnedRefFlags);
+  ctx->timings.bytes_h2d += ctx->ref_h2d_bytes;
+  if (flag[0] || flag[1]) {
+    ctx->has_result = false;
+    return fail(ctx, HJ_ERR_INVALID, "%s relation: a PosList entry points outside the referenced table", flag[0] ? "build" : "probe");
+  }
   return HJ_OK;
 }
 
@@ -505,7 +707,7 @@ int stage_pass2(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, in
   return HJ_OK;
 }
 
-struct Readback {  // layout of the pinned readback area
+struct Readback {  // layout of the pinned readback area (offset 0; REFERENCE error flags live at kPinnedRefFlags)
   OutState out;
   PlanOut plan;
   uint32_t n_build_tuples;
@@ -968,6 +1170,9 @@ const char* hj_last_error(const hj_ctx* ctx) { return ctx ? ctx->err.c_str() : g
 
 int hj_radix_bits(uint64_t n_build_rows, int key_type) { return radix_bits_for(n_build_rows, key_type); }
 
+int join_dispatch(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, int mode, cudaStream_t st,
+                  hj_result_info* out_info, bool wide, bool bound);
+
 int hj_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, int mode, void* cuda_stream,
             hj_result_info* out_info) {
   if (!ctx) return HJ_ERR_INVALID;
@@ -986,6 +1191,16 @@ int hj_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, int
   const bool bound = ctx->bound;
   ctx->bound = false;  // a binding holds for one join
   ctx->result_in_bound = false;
+  RefRewrite rw[2];  // REFERENCE segments -> gathered on the device (N1)
+  HJ_TRY(gather_both(ctx, build, probe, st, rw));
+  const int status = join_dispatch(ctx, build, probe, mode, st, out_info, wide, bound);
+  if (status != HJ_OK) return status;
+  return check_reference_flags(ctx, rw);
+}
+
+// hj_join after argument checks and the REFERENCE gather
+int join_dispatch(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, int mode, cudaStream_t st,
+                  hj_result_info* out_info, bool wide, bool bound) {
   if (!bound) return wide ? run_join<int64_t>(ctx, build, probe, mode, st, out_info)
                           : run_join<int32_t>(ctx, build, probe, mode, st, out_info);
   const bool one_side = mode == HJ_MODE_SEMI || mode == HJ_MODE_ANTI;

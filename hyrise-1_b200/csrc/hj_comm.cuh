@@ -999,6 +999,8 @@ int hj_join_sharded(hj_ctx* ctx, const hj_relation* build_shard, const hj_relati
   HJ_TRY(validate_relation(ctx, probe_shard, "probe"));
   HJ_TRY(check_ctx(ctx));
   cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
+  RefRewrite rw[2];  // REFERENCE segments -> gathered on the device (N1)
+  HJ_TRY(gather_both(ctx, build_shard, probe_shard, st, rw));
   // the hashed key type must be the same on every rank (the destination of a key depends on it): all-gather "I hold int64"
   unsigned long long wide = 0;
   for (const hj_relation* r : {build_shard, probe_shard})
@@ -1022,11 +1024,15 @@ int hj_join_sharded(hj_ctx* ctx, const hj_relation* build_shard, const hj_relati
   const uint32_t S = ctx->opts.stream_slice_rows
                          ? uint32_t(std::min<uint64_t>(kMaxXchgSlices, max_probe_rows / ctx->opts.stream_slice_rows)) : 1u;
   const bool direct = ctx->p2p_ok && !(ctx->opts.flags & HJ_FLAG_XCHG_STAGED);
+  int status;
   if (direct && S >= 2)
-    return wide ? run_join_sharded_sliced<int64_t>(ctx, build_shard, probe_shard, mode, st, out_info, S)
-                : run_join_sharded_sliced<int32_t>(ctx, build_shard, probe_shard, mode, st, out_info, S);
-  return wide ? run_join_sharded<int64_t>(ctx, build_shard, probe_shard, mode, st, out_info)
-              : run_join_sharded<int32_t>(ctx, build_shard, probe_shard, mode, st, out_info);
+    status = wide ? run_join_sharded_sliced<int64_t>(ctx, build_shard, probe_shard, mode, st, out_info, S)
+                  : run_join_sharded_sliced<int32_t>(ctx, build_shard, probe_shard, mode, st, out_info, S);
+  else
+    status = wide ? run_join_sharded<int64_t>(ctx, build_shard, probe_shard, mode, st, out_info)
+                  : run_join_sharded<int32_t>(ctx, build_shard, probe_shard, mode, st, out_info);
+  if (status != HJ_OK) return status;
+  return check_reference_flags(ctx, rw);
 }
 
 }  // extern "C"

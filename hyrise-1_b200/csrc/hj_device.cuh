@@ -22,9 +22,10 @@ enum NullPolicy : int {
   kNullRoute = 2    // probe side of Left/Right with HJ_FLAG_SQL_NULL_PROBE: routed to a side list, emitted unmatched
 };
 
-// Internal segment kind (after hj_segment_kind 0..2): tuples received from the multi-GPU exchange. `values` = keys,
+// Internal segment kind (outside hj_segment_kind 0..3; HJ_SEG_REFERENCE never reaches the device, it is gathered into a
+// GATHERED segment first): tuples received from the multi-GPU exchange. `values` = keys,
 // `nulls` = optional flags, `attr` = the rows' packed global RowIDs (uint64), which replace the position -> RowID mapping.
-constexpr uint8_t kSegExchanged = 3;
+constexpr uint8_t kSegExchanged = 15;
 
 // One chunk's key column on the device. 64 bytes.
 struct DevSegment {

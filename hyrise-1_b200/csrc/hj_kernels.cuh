@@ -1190,6 +1190,59 @@ __global__ void __launch_bounds__(256) k_compact_move(const CompactHdr* __restri
   }
 }
 
+// =====================================================================================================================
+// K10: ReferenceColumn inputs (reference_column_iterable.hpp:59-90, what materialize_input sees through
+// a ReferenceColumn): key = referenced_table.chunk[pos.chunk_id].column[pos.chunk_offset], NULL for NULL_ROW_ID and for
+// NULL values; NULL rows carry T{} like the reference's iterator. One job per REFERENCE segment; rows of all jobs are
+// numbered consecutively (row_begin). Out-of-range RowIDs are reported through *error and treated as NULL.
+// =====================================================================================================================
+struct RefJob {
+  const uint64_t* pos;     // the segment's PosList (packed RowIDs)
+  const DevSegment* ref;   // chunks of the referenced key column (VALUE or DICT)
+  void* out_values;        // int32[n_rows] or int64[n_rows] (key_type)
+  uint8_t* out_nulls;      // 1 byte per row
+  uint32_t n_ref;
+  uint32_t n_rows;
+  uint32_t row_begin;
+  uint32_t key_type;
+};
+
+__global__ void __launch_bounds__(256) k_gather_refs(const RefJob* __restrict__ jobs, uint32_t n_jobs, uint32_t total_rows,
+                                                     uint32_t* __restrict__ error) {
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total_rows; i += gridDim.x * blockDim.x) {
+    uint32_t lo = 0, hi = n_jobs;  // last job with row_begin <= i
+    while (hi - lo > 1) {
+      const uint32_t mid = (lo + hi) >> 1;
+      if (jobs[mid].row_begin <= i) lo = mid; else hi = mid;
+    }
+    const RefJob& jb = jobs[lo];
+    const uint32_t r = i - jb.row_begin;
+    const uint64_t rid = __ldg(jb.pos + r);
+    const uint32_t chunk = static_cast<uint32_t>(rid), off = static_cast<uint32_t>(rid >> 32);
+    int64_t val = 0;
+    bool is_null = off == kInvalid;
+    if (!is_null) {
+      if (chunk >= jb.n_ref || off >= jb.ref[chunk].n_rows) {
+        *error = 1;
+        is_null = true;
+      } else {
+        const DevSegment s = jb.ref[chunk];
+        if (s.kind == 1) {
+          const uint32_t vid = load_attr(s, off);
+          if (vid == s.null_value_id) is_null = true; else val = load_plain_key<int64_t>(s, vid);
+        } else if (s.nulls && __ldg(s.nulls + off)) {
+          is_null = true;
+        } else {
+          val = load_plain_key<int64_t>(s, off);
+        }
+      }
+    }
+    if (jb.key_type == 0) static_cast<int32_t*>(jb.out_values)[r] = static_cast<int32_t>(val);
+    else static_cast<int64_t*>(jb.out_values)[r] = val;
+    jb.out_nulls[r] = is_null ? 1 : 0;
+  }
+}
+
 // K9: inout[i] = pos_lists[chunk_base[inout[i].chunk_id] + inout[i].chunk_offset]; NULL_ROW_ID stays (join_hash.cpp:584-592).
 // Out-of-range references are reported through *error instead of faulting.
 __global__ void k_translate(uint64_t* __restrict__ inout, uint64_t n, const uint64_t* __restrict__ pos_lists,

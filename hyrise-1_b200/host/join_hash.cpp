@@ -6,6 +6,8 @@
 #include <atomic>
 #include <cstring>
 #include <map>
+#include <memory>
+#include <tuple>
 
 #include "hj.h"
 
@@ -56,64 +58,39 @@ hj_ctx* acquire_ctx() {
   return tc.ctx;
 }
 
-// The key column of `table`, one hj_segment per chunk. ReferenceColumns are gathered through their
-// PosList into `owned` staging vectors (reference_column_iterable.hpp:59-90: NULL RowID / NULL value -> T{} + null flag).
+// The key column of `table`, one hj_segment per chunk. A ReferenceColumn is handed over as it is stored:
+// its PosList plus the flattened key column of the referenced data table (HJ_SEG_REFERENCE); the library gathers
+// (value, is_null) on the device (reference_column_iterable.hpp:59-90: NULL RowID / NULL value -> T{} + null flag).
 struct FlatColumn {
   std::vector<hj_segment> segs;
-  std::vector<std::vector<uint8_t>> owned;  // gathered values / null flags, alive until the join returns
   hj_relation rel{};
+  // referenced data tables' key columns, flattened once per (table, column)
+  std::vector<std::tuple<const Table*, ColumnID, std::unique_ptr<FlatColumn>>> referenced;
 };
 
 template <typename T>
-void gather_reference_column(const ReferenceColumn& ref, hj_segment& seg, FlatColumn& out) {
-  const auto& pos = *ref.pos_list();
-  const size_t n = pos.size();
-  out.owned.emplace_back(n * sizeof(T));
-  auto* values = reinterpret_cast<T*>(out.owned.back().data());
-  out.owned.emplace_back(n);
-  auto* nulls = out.owned.back().data();
-  bool any_null = false;
-  ChunkID cached_chunk = INVALID_CHUNK_ID;
-  const ValueColumn<T>* vc = nullptr;
-  const DictionaryColumn<T>* dc = nullptr;
-  std::shared_ptr<BaseColumn> holder;
-  const auto table = ref.referenced_table();
-  for (size_t i = 0; i < n; ++i) {
-    const RowID r = pos[i];
-    values[i] = T{};
-    nulls[i] = 0;
-    if (r.is_null()) {
-      nulls[i] = 1;
-      any_null = true;
-      continue;
-    }
-    if (r.chunk_id != cached_chunk) {
-      cached_chunk = r.chunk_id;
-      holder = table->get_chunk(r.chunk_id)->get_column(ref.referenced_column_id());  // taken once per chunk (chunk.hpp:69-78)
-      vc = dynamic_cast<const ValueColumn<T>*>(holder.get());
-      dc = dynamic_cast<const DictionaryColumn<T>*>(holder.get());
-      Assert(vc || dc, "JoinHash: unsupported column encoding behind a ReferenceColumn");
-    }
-    if (vc) {
-      if (vc->is_nullable() && vc->null_values()[r.chunk_offset]) {
-        nulls[i] = 1;
-        any_null = true;
-      } else {
-        values[i] = vc->values()[r.chunk_offset];
-      }
-    } else {
-      const auto value_id = dc->attribute_vector_raw()->get(r.chunk_offset);
-      if (value_id == dc->null_value_id()) {
-        nulls[i] = 1;
-        any_null = true;
-      } else {
-        values[i] = (*dc->dictionary())[value_id];
-      }
-    }
+void flatten_typed(const Table& table, ColumnID column_id, FlatColumn& out);
+
+template <typename T>
+void reference_segment(const ReferenceColumn& ref, hj_segment& seg, FlatColumn& out) {
+  const Table* table = ref.referenced_table().get();
+  const ColumnID ref_column = ref.referenced_column_id();
+  FlatColumn* flat = nullptr;
+  for (auto& [t, c, f] : out.referenced)
+    if (t == table && c == ref_column) flat = f.get();
+  if (!flat) {
+    auto fresh = std::make_unique<FlatColumn>();
+    flatten_typed<T>(*table, ref_column, *fresh);
+    for (const hj_segment& q : fresh->segs)
+      Assert(q.kind == HJ_SEG_VALUE || q.kind == HJ_SEG_DICT, "JoinHash: a ReferenceColumn must reference a data table");
+    flat = fresh.get();
+    out.referenced.emplace_back(table, ref_column, std::move(fresh));
   }
-  seg.kind = HJ_SEG_GATHERED;
-  seg.values = values;
-  seg.nulls = any_null ? nulls : nullptr;
+  static_assert(sizeof(RowID) == sizeof(hj_row_id), "PosList::data() is handed to the library as hj_row_id[]");
+  seg.kind = HJ_SEG_REFERENCE;
+  seg.values = &flat->rel;
+  seg.attr = ref.pos_list()->data();
+  seg.nulls = nullptr;
   seg.row_offsets = nullptr;  // RowIDs carry the index inside the ReferenceColumn (the intent of join_hash.cpp:257-263; quirk Q2)
 }
 
@@ -141,7 +118,7 @@ void flatten_typed(const Table& table, ColumnID column_id, FlatColumn& out) {
       seg.attr = dc->attribute_vector_raw()->raw_data();
       seg.attr_width = dc->attribute_vector_raw()->width_bytes();
     } else if (const auto* rc = dynamic_cast<const ReferenceColumn*>(column.get())) {
-      gather_reference_column<T>(*rc, seg, out);
+      reference_segment<T>(*rc, seg, out);
     } else {
       Fail("JoinHash: unsupported column encoding for the join key (Value, Dictionary/FixedSizeByteAligned and Reference "
            "columns are supported)");

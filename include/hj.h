@@ -76,7 +76,14 @@ enum hj_segment_kind {
   /* ReferenceColumn, src/lib/storage/reference_column.hpp:19-50: the shim has gathered the keys
    * through the PosList into `values` (+ `nulls`); `row_offsets` optionally overrides the
    * ChunkOffset reported per row (quirk Q2, reference_column_iterable.hpp:60), NULL = 0,1,2,... */
-  HJ_SEG_GATHERED = 2
+  HJ_SEG_GATHERED = 2,
+  /* ReferenceColumn handed over as it is stored (reference_column.hpp:19-50): `attr` is the PosList
+   * (hj_row_id[n_rows], NULL_ROW_ID = NULL key), `values` points to an hj_relation describing the key
+   * column of the REFERENCED data table (segs[c] = its chunk c, VALUE or DICT, same hj_location as this
+   * relation). The library gathers (value, is_null) through the PosList on the device
+   * (reference_column_iterable.hpp:59-90) — SURVEY §8(f) N1. Emitted RowIDs are (chunk_id, 0..n_rows-1),
+   * to be mapped to the data table with hj_translate like those of GATHERED segments. */
+  HJ_SEG_REFERENCE = 3
 };
 
 /* Where the arrays a segment points to live. */
@@ -92,9 +99,10 @@ typedef struct hj_segment {
   uint32_t dict_n;        /* DICT: entries in the dictionary                                */
   uint32_t null_value_id; /* DICT: ValueID meaning NULL (== dict_n in the reference)        */
   uint32_t reserved1;
-  const void* values;     /* VALUE/GATHERED: T[n_rows]; DICT: sorted dictionary T[dict_n]   */
+  const void* values;     /* VALUE/GATHERED: T[n_rows]; DICT: sorted dictionary T[dict_n];
+                             REFERENCE: const hj_relation* of the referenced key column      */
   const uint8_t* nulls;   /* VALUE/GATHERED: 1 byte per row (non-zero = NULL) or NULL ptr   */
-  const void* attr;       /* DICT: uintW[n_rows]                                            */
+  const void* attr;       /* DICT: uintW[n_rows]; REFERENCE: hj_row_id[n_rows] (the PosList) */
   const uint32_t* row_offsets; /* GATHERED: ChunkOffset per row, or NULL for 0..n_rows-1   */
 } hj_segment;
 
