@@ -97,6 +97,30 @@ class RelationBuilder:
         s.attr, k2 = _ptr_and_keep(attr)
         return self._add(s, k1, k2)
 
+    def add_for(self, chunk_id, block_minima, offsets, nulls=None):
+        """FrameOfReferenceColumn<T>: minima T[ceil(n/2048)], FixedSizeByteAligned offsets uint8/16/32[n], 1 byte/row flags."""
+        s = abi.Segment()
+        s.chunk_id, s.n_rows, s.kind = chunk_id, len(offsets), abi.SEG_FOR
+        s.key_type = _KEY_DTYPES[_dtype_name(block_minima)]
+        s.attr_width = {"uint8": 1, "uint16": 2, "int16": 2, "uint32": 4, "int32": 4}[_dtype_name(offsets)]
+        assert len(block_minima) == (len(offsets) + 2047) // 2048
+        s.values, k1 = _ptr_and_keep(block_minima)
+        s.attr, k2 = _ptr_and_keep(offsets)
+        s.nulls, k3 = _ptr_and_keep(nulls)
+        return self._add(s, k1, k2, k3)
+
+    def add_rle(self, chunk_id, n_rows, run_values, end_positions, run_nulls=None):
+        """RunLengthColumn<T>: run values T[runs], inclusive end positions uint32[runs], 1 byte per run flags."""
+        s = abi.Segment()
+        s.chunk_id, s.n_rows, s.kind = chunk_id, n_rows, abi.SEG_RLE
+        s.key_type = _KEY_DTYPES[_dtype_name(run_values)]
+        s.dict_n = len(run_values)
+        assert len(end_positions) == len(run_values) and _dtype_name(end_positions) in ("uint32", "int32")
+        s.values, k1 = _ptr_and_keep(run_values)
+        s.attr, k2 = _ptr_and_keep(end_positions)
+        s.nulls, k3 = _ptr_and_keep(run_nulls)
+        return self._add(s, k1, k2, k3)
+
     def add_reference(self, chunk_id, pos_list, referenced, key_type):
         """ReferenceColumn as stored: pos_list = (n, 2) uint32 [chunk_id, chunk_offset] rows (NULL_ROW_ID = NULL key) into
         `referenced`, a built relation describing the key column of the data table (same location). The library gathers

@@ -174,6 +174,17 @@ struct PreparedRel {
   uint64_t h2d_bytes = 0;
 };
 
+// FOR / RLE chunk descriptors
+const char* encoded_segment_problem(const hj_segment& s) {
+  if (s.kind == HJ_SEG_FOR) {
+    if (s.attr_width != 1 && s.attr_width != 2 && s.attr_width != 4) return "FOR: offset vector width must be 1, 2 or 4 (FixedSizeByteAligned)";
+    if (s.n_rows && (!s.values || !s.attr)) return "FOR without block minima / offsets";
+  } else {
+    if (s.n_rows && (!s.dict_n || !s.values || !s.attr)) return "RLE without runs";
+  }
+  return nullptr;
+}
+
 int validate_relation(hj_ctx* ctx, const hj_relation* r, const char* name) {
   if (!r) return fail(ctx, HJ_ERR_INVALID, "%s relation is NULL", name);
   if (r->n_segs && !r->segs) return fail(ctx, HJ_ERR_INVALID, "%s relation has no segment array", name);
@@ -184,7 +195,12 @@ int validate_relation(hj_ctx* ctx, const hj_relation* r, const char* name) {
     const hj_segment& s = r->segs[i];
     if (s.key_type != HJ_KEY_INT32 && s.key_type != HJ_KEY_INT64)
       return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: key type %u unsupported (int32/int64 keys only)", name, i, s.key_type);
-    if (s.kind > HJ_SEG_REFERENCE) return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: bad segment kind %u", name, i, s.kind);
+    if (s.kind > HJ_SEG_RLE) return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: bad segment kind %u", name, i, s.kind);
+    if (s.kind == HJ_SEG_FOR || s.kind == HJ_SEG_RLE) {
+      if (const char* why = encoded_segment_problem(s)) return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: %s", name, i, why);
+      n += s.n_rows;
+      continue;
+    }
     if (s.reserved0) return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: reserved0 must be 0", name, i);
     if (s.kind == HJ_SEG_REFERENCE) {
       const auto* ref = static_cast<const hj_relation*>(s.values);
@@ -195,9 +211,15 @@ int validate_relation(hj_ctx* ctx, const hj_relation* r, const char* name) {
       if (ref->n_segs && !ref->segs) return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: referenced column has no segment array", name, i);
       for (uint32_t c = 0; c < ref->n_segs; ++c) {
         const hj_segment& q = ref->segs[c];
-        if (q.kind != HJ_SEG_VALUE && q.kind != HJ_SEG_DICT)
-          return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: referenced chunk %u must be a VALUE or DICT column (a ReferenceColumn "
-                      "never points at another reference table)", name, i, c);
+        if (q.kind != HJ_SEG_VALUE && q.kind != HJ_SEG_DICT && q.kind != HJ_SEG_FOR && q.kind != HJ_SEG_RLE)
+          return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: referenced chunk %u must be a data column (a ReferenceColumn never "
+                      "points at another reference table)", name, i, c);
+        if (q.kind == HJ_SEG_FOR || q.kind == HJ_SEG_RLE) {
+          if (const char* why = encoded_segment_problem(q))
+            return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: referenced chunk %u: %s", name, i, c, why);
+          if (q.key_type != s.key_type) return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: referenced chunk %u has another key type", name, i, c);
+          continue;
+        }
         if (q.key_type != s.key_type) return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: referenced chunk %u has another key type", name, i, c);
         if (q.kind == HJ_SEG_DICT && q.attr_width != 1 && q.attr_width != 2 && q.attr_width != 4)
           return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: referenced chunk %u: attribute vector width %u", name, i, c, q.attr_width);
@@ -355,8 +377,9 @@ int prepare_relation(hj_ctx* ctx, const hj_relation* r, int side, uint32_t tile,
   return HJ_OK;
 }
 
-// N1: turns every HJ_SEG_REFERENCE segment of `in` into a device-resident GATHERED segment (keys + null flags gathered
-// through the PosList by k_gather_refs). `out->rel` is the relation to join instead of `in`.
+// N1/N2: turns every HJ_SEG_REFERENCE segment of `in` (keys gathered through the PosList) and every HJ_SEG_FOR /
+// HJ_SEG_RLE segment (decoded row by row) into a device-resident GATHERED / VALUE segment written by k_gather_refs.
+// `out->rel` is the relation to join instead of `in`.
 struct RefRewrite {
   std::vector<hj_segment> segs;
   hj_relation rel{};
@@ -366,87 +389,103 @@ struct RefRewrite {
 int gather_references(hj_ctx* ctx, const hj_relation* in, int side, cudaStream_t st, RefRewrite* out) {
   out->rel = *in;
   out->any = false;
-  std::vector<uint32_t> ref_segs;
-  for (uint32_t i = 0; i < in->n_segs; ++i)
-    if (in->segs[i].kind == HJ_SEG_REFERENCE) ref_segs.push_back(i);
-  if (ref_segs.empty()) return HJ_OK;
+  std::vector<uint32_t> job_segs;
+  for (uint32_t i = 0; i < in->n_segs; ++i) {
+    const uint8_t kind = in->segs[i].kind;
+    if (kind == HJ_SEG_REFERENCE || kind == HJ_SEG_FOR || kind == HJ_SEG_RLE) job_segs.push_back(i);
+  }
+  if (job_segs.empty()) return HJ_OK;
   out->any = true;
   out->segs.assign(in->segs, in->segs + in->n_segs);
   const bool host = in->location == HJ_LOC_HOST;
   auto key_bytes = [](uint8_t key_type) { return key_type == HJ_KEY_INT64 ? size_t(8) : size_t(4); };
   auto align = [](size_t x) { return (x + 255) & ~size_t(255); };
 
-  // distinct referenced columns (normally one: all chunks of a reference table point at the same data table)
-  std::vector<const hj_relation*> refs;
-  std::vector<uint32_t> ref_of(ref_segs.size());
-  for (size_t j = 0; j < ref_segs.size(); ++j) {
-    const auto* r = static_cast<const hj_relation*>(in->segs[ref_segs[j]].values);
+  // chunk tables the jobs read from: one per distinct referenced column (normally one: all chunks of a reference table
+  // point at the same data table) and a one-entry table per FOR/RLE segment (the segment itself)
+  struct Table { const hj_segment* segs; uint32_t n; };
+  std::vector<Table> tables;
+  std::vector<uint32_t> table_of(job_segs.size());
+  for (size_t j = 0; j < job_segs.size(); ++j) {
+    const hj_segment& s = in->segs[job_segs[j]];
+    Table t;
+    if (s.kind == HJ_SEG_REFERENCE) {
+      const auto* r = static_cast<const hj_relation*>(s.values);
+      t = Table{r->segs, r->n_segs};
+    } else {
+      t = Table{&s, 1};
+    }
     size_t k = 0;
-    while (k < refs.size() && refs[k] != r) ++k;
-    if (k == refs.size()) refs.push_back(r);
-    ref_of[j] = uint32_t(k);
+    while (k < tables.size() && tables[k].segs != t.segs) ++k;
+    if (k == tables.size()) tables.push_back(t);
+    table_of[j] = uint32_t(k);
   }
-  // arena: [error flag][DevSegment tables][RefJob table][host data: referenced arrays, PosLists]
-  struct Copy { const void* src; size_t bytes; size_t off; };
+  // arena: [error flag][DevSegment tables][RefJob table][host data: the tables' arrays, PosLists]
+  struct Copy { const void* src; size_t bytes; size_t off; const void** fix; };
   std::vector<Copy> copies;
   size_t arena = 256;
-  std::vector<size_t> seg_tab_off(refs.size());
-  for (size_t k = 0; k < refs.size(); ++k) {
-    seg_tab_off[k] = arena;
-    arena += align(std::max<size_t>(1, refs[k]->n_segs) * sizeof(DevSegment));
+  std::vector<size_t> tab_off(tables.size());
+  for (size_t k = 0; k < tables.size(); ++k) {
+    tab_off[k] = arena;
+    arena += align(std::max<size_t>(1, tables[k].n) * sizeof(DevSegment));
   }
   const size_t job_off = arena;
-  arena += align(ref_segs.size() * sizeof(RefJob));
-  auto plan = [&](const void* src, size_t bytes) {
-    const size_t off = arena;
-    copies.push_back({src, bytes, off});
+  arena += align(job_segs.size() * sizeof(RefJob));
+  auto plan = [&](const void* src, size_t bytes, const void** fix) {
+    copies.push_back({src, bytes, arena, fix});
     arena += align(bytes);
-    return off;
   };
-  std::vector<std::vector<DevSegment>> tabs(refs.size());
-  std::vector<std::vector<size_t>> o_val(refs.size()), o_nul(refs.size()), o_att(refs.size());
-  for (size_t k = 0; k < refs.size(); ++k) {
-    const hj_relation* r = refs[k];
-    tabs[k].resize(r->n_segs);
-    o_val[k].assign(r->n_segs, 0);
-    o_nul[k].assign(r->n_segs, 0);
-    o_att[k].assign(r->n_segs, 0);
-    for (uint32_t c = 0; c < r->n_segs; ++c) {
-      const hj_segment& q = r->segs[c];
+  std::vector<std::vector<DevSegment>> tabs(tables.size());
+  for (size_t k = 0; k < tables.size(); ++k) {
+    tabs[k].resize(tables[k].n);
+    for (uint32_t c = 0; c < tables[k].n; ++c) {
+      const hj_segment& q = tables[k].segs[c];
       DevSegment& d = tabs[k][c];
       std::memset(&d, 0, sizeof(d));
-      d.values = q.values;
-      d.nulls = q.kind == HJ_SEG_DICT ? nullptr : q.nulls;
-      d.attr = q.kind == HJ_SEG_DICT ? q.attr : nullptr;
       d.n_rows = q.n_rows;
       d.chunk_id = q.chunk_id;
-      d.null_value_id = q.null_value_id;
       d.kind = q.kind;
       d.key_type = q.key_type;
-      d.attr_width = q.attr_width;
+      d.attr_width = q.kind == HJ_SEG_RLE ? 4 : q.attr_width;
+      // array lengths per encoding: values / attr / nulls
+      size_t n_val = q.n_rows, n_attr = 0, n_null = q.nulls ? q.n_rows : 0;
+      if (q.kind == HJ_SEG_DICT) {
+        n_val = q.dict_n; n_attr = q.n_rows; n_null = 0;
+        d.null_value_id = q.null_value_id;
+      } else if (q.kind == HJ_SEG_FOR) {
+        n_val = (size_t(q.n_rows) + 2047) / 2048; n_attr = q.n_rows;
+      } else if (q.kind == HJ_SEG_RLE) {
+        n_val = q.dict_n; n_attr = q.dict_n; n_null = q.nulls ? q.dict_n : 0;
+        d.null_value_id = q.dict_n;  // number of runs (decode_point)
+      }
+      d.values = n_val ? q.values : nullptr;
+      d.attr = n_attr ? q.attr : nullptr;
+      d.nulls = n_null ? q.nulls : nullptr;
       if (host) {
-        if (q.kind == HJ_SEG_DICT) {
-          if (q.dict_n) o_val[k][c] = plan(q.values, size_t(q.dict_n) * key_bytes(q.key_type));
-          if (q.n_rows) o_att[k][c] = plan(q.attr, size_t(q.n_rows) * q.attr_width);
-        } else {
-          if (q.n_rows) o_val[k][c] = plan(q.values, size_t(q.n_rows) * key_bytes(q.key_type));
-          if (q.n_rows && q.nulls) o_nul[k][c] = plan(q.nulls, q.n_rows);
-        }
+        if (n_val) plan(q.values, n_val * key_bytes(q.key_type), &d.values);
+        if (n_attr) plan(q.attr, n_attr * d.attr_width, &d.attr);
+        if (n_null) plan(q.nulls, n_null, reinterpret_cast<const void**>(&d.nulls));
       }
     }
   }
-  std::vector<size_t> o_pos(ref_segs.size(), 0), o_out(ref_segs.size(), 0), o_outn(ref_segs.size(), 0);
+  std::vector<RefJob> jobs(job_segs.size());
+  std::vector<size_t> o_out(job_segs.size(), 0), o_outn(job_segs.size(), 0);
   size_t out_bytes = 0;
   uint64_t total_rows = 0;
-  for (size_t j = 0; j < ref_segs.size(); ++j) {
-    const hj_segment& s = in->segs[ref_segs[j]];
-    if (host && s.n_rows) o_pos[j] = plan(s.attr, size_t(s.n_rows) * 8);
+  for (size_t j = 0; j < job_segs.size(); ++j) {
+    const hj_segment& s = in->segs[job_segs[j]];
+    jobs[j].pos = nullptr;
+    if (s.kind == HJ_SEG_REFERENCE) {
+      jobs[j].pos = static_cast<const uint64_t*>(s.attr);
+      if (host && s.n_rows) plan(s.attr, size_t(s.n_rows) * 8, reinterpret_cast<const void**>(&jobs[j].pos));
+    }
     o_out[j] = out_bytes;
     out_bytes += align(size_t(s.n_rows) * key_bytes(s.key_type));
     o_outn[j] = out_bytes;
     out_bytes += align(s.n_rows);
     total_rows += s.n_rows;
   }
+  if (total_rows >= 0xFFFFFFFFull) return fail(ctx, HJ_ERR_TOO_LARGE, "%llu rows behind REFERENCE/FOR/RLE chunks", (unsigned long long)total_rows);
   HJ_TRY(ensure(ctx, ctx->ref_arena[side], arena));
   HJ_TRY(ensure(ctx, ctx->ref_out[side], std::max<size_t>(256, out_bytes)));
   char* base = static_cast<char*>(ctx->ref_arena[side].p);
@@ -454,46 +493,32 @@ int gather_references(hj_ctx* ctx, const hj_relation* in, int side, cudaStream_t
   HJ_CUDA(ctx, cudaMemsetAsync(base, 0, 256, st));
   for (const Copy& c : copies) {
     HJ_CUDA(ctx, cudaMemcpyAsync(base + c.off, c.src, c.bytes, cudaMemcpyHostToDevice, st));
+    *c.fix = base + c.off;  // the table entry / job now points at the staged copy
     ctx->ref_h2d_bytes += c.bytes;
   }
-  for (size_t k = 0; k < refs.size(); ++k) {
-    if (host)
-      for (uint32_t c = 0; c < refs[k]->n_segs; ++c) {
-        const hj_segment& q = refs[k]->segs[c];
-        DevSegment& d = tabs[k][c];
-        if (q.kind == HJ_SEG_DICT) {
-          d.values = q.dict_n ? base + o_val[k][c] : nullptr;
-          d.attr = q.n_rows ? base + o_att[k][c] : nullptr;
-        } else {
-          d.values = q.n_rows ? base + o_val[k][c] : nullptr;
-          d.nulls = (q.n_rows && q.nulls) ? reinterpret_cast<const uint8_t*>(base + o_nul[k][c]) : nullptr;
-        }
-      }
-    if (refs[k]->n_segs)
-      HJ_CUDA(ctx, cudaMemcpyAsync(base + seg_tab_off[k], tabs[k].data(), refs[k]->n_segs * sizeof(DevSegment),
-                                   cudaMemcpyHostToDevice, st));
-  }
-  std::vector<RefJob> jobs(ref_segs.size());
+  for (size_t k = 0; k < tables.size(); ++k)
+    if (tables[k].n)
+      HJ_CUDA(ctx, cudaMemcpyAsync(base + tab_off[k], tabs[k].data(), tables[k].n * sizeof(DevSegment), cudaMemcpyHostToDevice, st));
   uint32_t row_begin = 0;
-  for (size_t j = 0; j < ref_segs.size(); ++j) {
-    hj_segment& s = out->segs[ref_segs[j]];
+  for (size_t j = 0; j < job_segs.size(); ++j) {
+    hj_segment& s = out->segs[job_segs[j]];
     RefJob& jb = jobs[j];
-    jb.pos = host ? reinterpret_cast<const uint64_t*>(base + o_pos[j]) : static_cast<const uint64_t*>(s.attr);
-    jb.ref = reinterpret_cast<const DevSegment*>(base + seg_tab_off[ref_of[j]]);
+    jb.ref = reinterpret_cast<const DevSegment*>(base + tab_off[table_of[j]]);
     jb.out_values = obase + o_out[j];
     jb.out_nulls = reinterpret_cast<uint8_t*>(obase + o_outn[j]);
-    jb.n_ref = refs[ref_of[j]]->n_segs;
+    jb.n_ref = tables[table_of[j]].n;
     jb.n_rows = s.n_rows;
     jb.row_begin = row_begin;
     jb.key_type = s.key_type;
     row_begin += s.n_rows;
-    // the segment the join sees: gathered keys + flags on the device, RowIDs (chunk_id, 0..n_rows-1)
-    s.kind = HJ_SEG_GATHERED;
+    // the segment the join sees: keys + flags on the device; a gathered ReferenceColumn reports RowIDs (chunk_id, 0..n-1)
+    s.kind = s.kind == HJ_SEG_REFERENCE ? HJ_SEG_GATHERED : HJ_SEG_VALUE;
     s.reserved0 = 1;
     s.values = jb.out_values;
     s.nulls = jb.out_nulls;
     s.attr = nullptr;
     s.row_offsets = nullptr;
+    s.dict_n = 0;
   }
   HJ_CUDA(ctx, cudaMemcpyAsync(base + job_off, jobs.data(), jobs.size() * sizeof(RefJob), cudaMemcpyHostToDevice, st));
   if (total_rows) {

@@ -1196,8 +1196,35 @@ __global__ void __launch_bounds__(256) k_compact_move(const CompactHdr* __restri
 // NULL values; NULL rows carry T{} like the reference's iterator. One job per REFERENCE segment; rows of all jobs are
 // numbered consecutively (row_begin). Out-of-range RowIDs are reported through *error and treated as NULL.
 // =====================================================================================================================
+// Point access into one chunk of a data table's key column: VALUE, DICT, FOR (frame of reference, 2048-row blocks) or
+// RLE (binary search over the inclusive run ends; null_value_id holds the number of runs).
+constexpr uint8_t kSegFor = 4, kSegRle = 5;  // == HJ_SEG_FOR / HJ_SEG_RLE
+__device__ __forceinline__ void decode_point(const DevSegment& s, uint32_t off, int64_t* val, bool* is_null) {
+  *val = 0;
+  *is_null = false;
+  if (s.kind == 1) {
+    const uint32_t vid = load_attr(s, off);
+    if (vid == s.null_value_id) *is_null = true; else *val = load_plain_key<int64_t>(s, vid);
+  } else if (s.kind == kSegFor) {
+    *is_null = s.nulls && __ldg(s.nulls + off);
+    *val = load_plain_key<int64_t>(s, off >> 11) + static_cast<int64_t>(load_attr(s, off));
+  } else if (s.kind == kSegRle) {
+    const uint32_t* ends = static_cast<const uint32_t*>(s.attr);
+    uint32_t lo = 0, hi = s.null_value_id;  // first run with ends[run] >= off
+    while (lo < hi) {
+      const uint32_t mid = (lo + hi) >> 1;
+      if (__ldg(ends + mid) < off) lo = mid + 1; else hi = mid;
+    }
+    *is_null = s.nulls && __ldg(s.nulls + lo);
+    *val = load_plain_key<int64_t>(s, lo);
+  } else {
+    *is_null = s.nulls && __ldg(s.nulls + off);
+    *val = load_plain_key<int64_t>(s, off);
+  }
+}
+
 struct RefJob {
-  const uint64_t* pos;     // the segment's PosList (packed RowIDs)
+  const uint64_t* pos;     // the segment's PosList (packed RowIDs); nullptr: decode chunk ref[0] row by row (FOR/RLE)
   const DevSegment* ref;   // chunks of the referenced key column (VALUE or DICT)
   void* out_values;        // int32[n_rows] or int64[n_rows] (key_type)
   uint8_t* out_nulls;      // 1 byte per row
@@ -1217,7 +1244,7 @@ __global__ void __launch_bounds__(256) k_gather_refs(const RefJob* __restrict__ 
     }
     const RefJob& jb = jobs[lo];
     const uint32_t r = i - jb.row_begin;
-    const uint64_t rid = __ldg(jb.pos + r);
+    const uint64_t rid = jb.pos ? __ldg(jb.pos + r) : static_cast<uint64_t>(r) << 32;
     const uint32_t chunk = static_cast<uint32_t>(rid), off = static_cast<uint32_t>(rid >> 32);
     int64_t val = 0;
     bool is_null = off == kInvalid;
@@ -1226,15 +1253,10 @@ __global__ void __launch_bounds__(256) k_gather_refs(const RefJob* __restrict__ 
         *error = 1;
         is_null = true;
       } else {
-        const DevSegment s = jb.ref[chunk];
-        if (s.kind == 1) {
-          const uint32_t vid = load_attr(s, off);
-          if (vid == s.null_value_id) is_null = true; else val = load_plain_key<int64_t>(s, vid);
-        } else if (s.nulls && __ldg(s.nulls + off)) {
-          is_null = true;
-        } else {
-          val = load_plain_key<int64_t>(s, off);
-        }
+        decode_point(jb.ref[chunk], off, &val, &is_null);
+        // through a ReferenceColumn a NULL yields T{} (reference_column_iterable.hpp:60); a decoded FOR/RLE chunk keeps
+        // the stored value like ValueColumnIterable does (it matters for quirk Q4 only)
+        if (is_null && jb.pos) val = 0;
       }
     }
     if (jb.key_type == 0) static_cast<int32_t*>(jb.out_values)[r] = static_cast<int32_t>(val);

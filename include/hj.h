@@ -83,7 +83,16 @@ enum hj_segment_kind {
    * relation). The library gathers (value, is_null) through the PosList on the device
    * (reference_column_iterable.hpp:59-90) — SURVEY §8(f) N1. Emitted RowIDs are (chunk_id, 0..n_rows-1),
    * to be mapped to the data table with hj_translate like those of GATHERED segments. */
-  HJ_SEG_REFERENCE = 3
+  HJ_SEG_REFERENCE = 3,
+  /* FrameOfReferenceColumn<int32|int64>, src/lib/storage/frame_of_reference_column.hpp:33-80 with a
+   * FixedSizeByteAligned offset vector: `values` = block minima T[ceil(n_rows / 2048)], `attr` = offsets
+   * uintW[n_rows] (attr_width 1/2/4), `nulls` = 1 byte per row or NULL (the shim expands the column's
+   * vector<bool>). key = minima[i / 2048] + offsets[i] (frame_of_reference_iterable.hpp). SURVEY §8(f) N2. */
+  HJ_SEG_FOR = 4,
+  /* RunLengthColumn<T>, src/lib/storage/run_length_column.hpp:29-66: `values` = run values T[dict_n],
+   * `attr` = inclusive end positions uint32[dict_n], `nulls` = 1 byte per RUN or NULL; dict_n = number of
+   * runs. Row i belongs to the first run whose end position is >= i (run_length_column_iterable.hpp). */
+  HJ_SEG_RLE = 5
 };
 
 /* Where the arrays a segment points to live. */
@@ -96,7 +105,7 @@ typedef struct hj_segment {
   uint8_t key_type;       /* hj_key_type of `values`                                        */
   uint8_t attr_width;     /* DICT: bytes per attribute-vector entry: 1, 2 or 4              */
   uint8_t reserved0;
-  uint32_t dict_n;        /* DICT: entries in the dictionary                                */
+  uint32_t dict_n;        /* DICT: entries in the dictionary; RLE: number of runs           */
   uint32_t null_value_id; /* DICT: ValueID meaning NULL (== dict_n in the reference)        */
   uint32_t reserved1;
   const void* values;     /* VALUE/GATHERED: T[n_rows]; DICT: sorted dictionary T[dict_n];
