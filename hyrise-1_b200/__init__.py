@@ -50,7 +50,7 @@ def _ptr_and_keep(x):
     return x.data_ptr(), x
 
 
-_KEY_DTYPES = {"int32": abi.KEY_INT32, "int64": abi.KEY_INT64}
+_KEY_DTYPES = {"int32": abi.KEY_INT32, "int64": abi.KEY_INT64, "float32": abi.KEY_FLOAT, "float64": abi.KEY_DOUBLE}
 
 
 def _dtype_name(x):

@@ -8,7 +8,7 @@ HJ_ABI_VERSION = 3
 MODE_INNER, MODE_LEFT, MODE_RIGHT, MODE_OUTER, MODE_CROSS, MODE_SEMI, MODE_ANTI = range(7)
 MODES = {"Inner": MODE_INNER, "Left": MODE_LEFT, "Right": MODE_RIGHT, "Outer": MODE_OUTER, "Cross": MODE_CROSS,
          "Semi": MODE_SEMI, "Anti": MODE_ANTI}
-KEY_INT32, KEY_INT64 = 0, 1
+KEY_INT32, KEY_INT64, KEY_FLOAT, KEY_DOUBLE = 0, 1, 2, 3
 SEG_VALUE, SEG_DICT, SEG_GATHERED, SEG_REFERENCE, SEG_FOR, SEG_RLE = 0, 1, 2, 3, 4, 5
 LOC_HOST, LOC_DEVICE = 0, 1
 FLAG_SQL_NULL_PROBE = 0x1

@@ -177,6 +177,7 @@ struct PreparedRel {
 // FOR / RLE chunk descriptors
 const char* encoded_segment_problem(const hj_segment& s) {
   if (s.kind == HJ_SEG_FOR) {
+    if (s.key_type > HJ_KEY_INT64) return "FOR encodes int32/int64 columns only (encoding_type.hpp:34)";
     if (s.attr_width != 1 && s.attr_width != 2 && s.attr_width != 4) return "FOR: offset vector width must be 1, 2 or 4 (FixedSizeByteAligned)";
     if (s.n_rows && (!s.values || !s.attr)) return "FOR without block minima / offsets";
   } else {
@@ -193,8 +194,9 @@ int validate_relation(hj_ctx* ctx, const hj_relation* r, const char* name) {
   uint64_t n = 0;
   for (uint32_t i = 0; i < r->n_segs; ++i) {
     const hj_segment& s = r->segs[i];
-    if (s.key_type != HJ_KEY_INT32 && s.key_type != HJ_KEY_INT64)
-      return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: key type %u unsupported (int32/int64 keys only)", name, i, s.key_type);
+    if (s.key_type > HJ_KEY_DOUBLE)
+      return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: key type %u unsupported (int32/int64/float/double keys; string keys: SURVEY 8f N3)",
+                  name, i, s.key_type);
     if (s.kind > HJ_SEG_RLE) return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: bad segment kind %u", name, i, s.kind);
     if (s.kind == HJ_SEG_FOR || s.kind == HJ_SEG_RLE) {
       if (const char* why = encoded_segment_problem(s)) return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: %s", name, i, why);
@@ -386,20 +388,27 @@ struct RefRewrite {
   bool any = false;
 };
 
-int gather_references(hj_ctx* ctx, const hj_relation* in, int side, cudaStream_t st, RefRewrite* out) {
+// hash_type (hj_key_type): the type the join hashes in. For float/double joins (N3) EVERY chunk goes through the kernel,
+// which converts the keys to the hashed type and hands the pipeline their bit patterns as int32 / int64 keys.
+int gather_references(hj_ctx* ctx, const hj_relation* in, int side, cudaStream_t st, RefRewrite* out, uint32_t hash_type) {
   out->rel = *in;
   out->any = false;
+  const bool floating = hash_type >= HJ_KEY_FLOAT;
   std::vector<uint32_t> job_segs;
   for (uint32_t i = 0; i < in->n_segs; ++i) {
     const uint8_t kind = in->segs[i].kind;
-    if (kind == HJ_SEG_REFERENCE || kind == HJ_SEG_FOR || kind == HJ_SEG_RLE) job_segs.push_back(i);
+    if (floating || kind == HJ_SEG_REFERENCE || kind == HJ_SEG_FOR || kind == HJ_SEG_RLE) job_segs.push_back(i);
   }
   if (job_segs.empty()) return HJ_OK;
   out->any = true;
   out->segs.assign(in->segs, in->segs + in->n_segs);
   const bool host = in->location == HJ_LOC_HOST;
-  auto key_bytes = [](uint8_t key_type) { return key_type == HJ_KEY_INT64 ? size_t(8) : size_t(4); };
+  auto key_bytes = [](uint8_t key_type) { return (key_type == HJ_KEY_INT64 || key_type == HJ_KEY_DOUBLE) ? size_t(8) : size_t(4); };
   auto align = [](size_t x) { return (x + 255) & ~size_t(255); };
+  // what the pipeline gets: the chunk's own integer type, or the bit pattern of the hashed floating type
+  auto out_key_type = [&](const hj_segment& s) -> uint8_t {
+    return !floating ? s.key_type : hash_type == HJ_KEY_FLOAT ? uint8_t(HJ_KEY_INT32) : uint8_t(HJ_KEY_INT64);
+  };
 
   // chunk tables the jobs read from: one per distinct referenced column (normally one: all chunks of a reference table
   // point at the same data table) and a one-entry table per FOR/RLE segment (the segment itself)
@@ -469,6 +478,7 @@ int gather_references(hj_ctx* ctx, const hj_relation* in, int side, cudaStream_t
     }
   }
   std::vector<RefJob> jobs(job_segs.size());
+  std::vector<const void*> row_offsets(job_segs.size(), nullptr);  // GATHERED chunks keep their reported offsets
   std::vector<size_t> o_out(job_segs.size(), 0), o_outn(job_segs.size(), 0);
   size_t out_bytes = 0;
   uint64_t total_rows = 0;
@@ -479,8 +489,12 @@ int gather_references(hj_ctx* ctx, const hj_relation* in, int side, cudaStream_t
       jobs[j].pos = static_cast<const uint64_t*>(s.attr);
       if (host && s.n_rows) plan(s.attr, size_t(s.n_rows) * 8, reinterpret_cast<const void**>(&jobs[j].pos));
     }
+    if (s.kind == HJ_SEG_GATHERED && s.row_offsets) {
+      row_offsets[j] = s.row_offsets;
+      if (host && s.n_rows) plan(s.row_offsets, size_t(s.n_rows) * 4, &row_offsets[j]);
+    }
     o_out[j] = out_bytes;
-    out_bytes += align(size_t(s.n_rows) * key_bytes(s.key_type));
+    out_bytes += align(size_t(s.n_rows) * key_bytes(out_key_type(s)));
     o_outn[j] = out_bytes;
     out_bytes += align(s.n_rows);
     total_rows += s.n_rows;
@@ -509,15 +523,18 @@ int gather_references(hj_ctx* ctx, const hj_relation* in, int side, cudaStream_t
     jb.n_ref = tables[table_of[j]].n;
     jb.n_rows = s.n_rows;
     jb.row_begin = row_begin;
-    jb.key_type = s.key_type;
+    jb.key_type = out_key_type(s);
+    jb.hash_type = hash_type;
+    jb.build_side = side == 0 ? 1u : 0u;
     row_begin += s.n_rows;
     // the segment the join sees: keys + flags on the device; a gathered ReferenceColumn reports RowIDs (chunk_id, 0..n-1)
-    s.kind = s.kind == HJ_SEG_REFERENCE ? HJ_SEG_GATHERED : HJ_SEG_VALUE;
+    s.kind = (s.kind == HJ_SEG_REFERENCE || s.kind == HJ_SEG_GATHERED) ? HJ_SEG_GATHERED : HJ_SEG_VALUE;
+    s.key_type = jb.key_type;
     s.reserved0 = 1;
     s.values = jb.out_values;
     s.nulls = jb.out_nulls;
     s.attr = nullptr;
-    s.row_offsets = nullptr;
+    s.row_offsets = static_cast<const uint32_t*>(row_offsets[j]);
     s.dict_n = 0;
   }
   HJ_CUDA(ctx, cudaMemcpyAsync(base + job_off, jobs.data(), jobs.size() * sizeof(RefJob), cudaMemcpyHostToDevice, st));
@@ -535,11 +552,27 @@ int gather_references(hj_ctx* ctx, const hj_relation* in, int side, cudaStream_t
 }
 
 // REFERENCE gather for both relations of a join; the join then runs over rw[i].rel where rw[i].any.
-int gather_both(hj_ctx* ctx, const hj_relation*& build, const hj_relation*& probe, cudaStream_t st, RefRewrite* rw) {
+// JoinHashTraits (hash_traits.hpp:14-35) over the key columns of both relations, as an hj_key_type
+uint32_t hashed_type_of(const hj_relation* build, const hj_relation* probe) {
+  uint32_t t = HJ_KEY_INT32;
+  bool any_float = false, any_double = false, any_long = false;
+  for (const hj_relation* r : {build, probe})
+    for (uint32_t i = 0; i < r->n_segs; ++i) {
+      const uint8_t k = r->segs[i].key_type;
+      any_long = any_long || k == HJ_KEY_INT64;
+      any_float = any_float || k == HJ_KEY_FLOAT;
+      any_double = any_double || k == HJ_KEY_DOUBLE;
+    }
+  if (any_double) t = HJ_KEY_DOUBLE; else if (any_float) t = HJ_KEY_FLOAT; else if (any_long) t = HJ_KEY_INT64;
+  return t;
+}
+
+int gather_both(hj_ctx* ctx, const hj_relation*& build, const hj_relation*& probe, cudaStream_t st, RefRewrite* rw,
+                uint32_t hash_type) {
   ctx->ref_h2d_bytes = 0;
   std::memset(static_cast<char*>(ctx->pinned) + kPinnedRefFlags, 0, 8);
-  HJ_TRY(gather_references(ctx, build, 0, st, &rw[0]));
-  HJ_TRY(gather_references(ctx, probe, 1, st, &rw[1]));
+  HJ_TRY(gather_references(ctx, build, 0, st, &rw[0], hash_type));
+  HJ_TRY(gather_references(ctx, probe, 1, st, &rw[1], hash_type));
   if (rw[0].any) build = &rw[0].rel;
   if (rw[1].any) probe = &rw[1].rel;
   return HJ_OK;
@@ -1210,14 +1243,14 @@ int hj_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, int
   HJ_TRY(validate_relation(ctx, probe, "probe"));
   HJ_TRY(check_ctx(ctx));
   cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
-  bool wide = false;  // JoinHashTraits: the hashed type of an int32 x int64 pair is int64 (hash_traits.hpp:21-25)
-  for (const hj_relation* r : {build, probe})
-    for (uint32_t i = 0; i < r->n_segs; ++i) wide = wide || r->segs[i].key_type == HJ_KEY_INT64;
+  // JoinHashTraits: int32 x int64 hashes as int64, anything with a float/double column as that floating type
+  const uint32_t hash_type = hashed_type_of(build, probe);
+  const bool wide = hash_type == HJ_KEY_INT64 || hash_type == HJ_KEY_DOUBLE;  // 8-byte keys in the pipeline
   const bool bound = ctx->bound;
   ctx->bound = false;  // a binding holds for one join
   ctx->result_in_bound = false;
   RefRewrite rw[2];  // REFERENCE segments -> gathered on the device (N1)
-  HJ_TRY(gather_both(ctx, build, probe, st, rw));
+  HJ_TRY(gather_both(ctx, build, probe, st, rw, hash_type));
   const int status = join_dispatch(ctx, build, probe, mode, st, out_info, wide, bound);
   if (status != HJ_OK) return status;
   return check_reference_flags(ctx, rw);

@@ -999,8 +999,10 @@ int hj_join_sharded(hj_ctx* ctx, const hj_relation* build_shard, const hj_relati
   HJ_TRY(validate_relation(ctx, probe_shard, "probe"));
   HJ_TRY(check_ctx(ctx));
   cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
-  RefRewrite rw[2];  // REFERENCE segments -> gathered on the device (N1)
-  HJ_TRY(gather_both(ctx, build_shard, probe_shard, st, rw));
+  if (hashed_type_of(build_shard, probe_shard) >= HJ_KEY_FLOAT)
+    return fail(ctx, HJ_ERR_INVALID, "hj_join_sharded: float/double keys are joined by hj_join only");
+  RefRewrite rw[2];  // REFERENCE / FOR / RLE segments -> gathered or decoded on the device (N1, N2)
+  HJ_TRY(gather_both(ctx, build_shard, probe_shard, st, rw, hashed_type_of(build_shard, probe_shard)));
   // the hashed key type must be the same on every rank (the destination of a key depends on it): all-gather "I hold int64"
   unsigned long long wide = 0;
   for (const hj_relation* r : {build_shard, probe_shard})

@@ -1199,15 +1199,42 @@ __global__ void __launch_bounds__(256) k_compact_move(const CompactHdr* __restri
 // Point access into one chunk of a data table's key column: VALUE, DICT, FOR (frame of reference, 2048-row blocks) or
 // RLE (binary search over the inclusive run ends; null_value_id holds the number of runs).
 constexpr uint8_t kSegFor = 4, kSegRle = 5;  // == HJ_SEG_FOR / HJ_SEG_RLE
+// element i of a chunk's value array as a 64-bit container: integers sign-extended, float/double as their bit patterns
+__device__ __forceinline__ int64_t load_raw(const DevSegment& s, uint32_t i) {
+  if (s.key_type == 0) return __ldg(static_cast<const int32_t*>(s.values) + i);
+  if (s.key_type == 2) return static_cast<int64_t>(__ldg(static_cast<const uint32_t*>(s.values) + i));
+  return __ldg(static_cast<const int64_t*>(s.values) + i);
+}
+
+// key of source type `src` (hj_key_type) as the join's hashed type `hash_type`, returned as the integer the pipeline
+// partitions and compares: the value itself for integer joins, the IEEE bit pattern for float/double joins. NaN equals
+// nothing in the reference (operator== on the hashed type), so build-side and probe-side NaNs get two different
+// canonical patterns.
+__device__ __forceinline__ int64_t to_hashed_type(int64_t raw, uint32_t src, uint32_t hash_type, bool build_side) {
+  if (hash_type < 2) return raw;
+  if (hash_type == 2) {
+    float f = src == 2 ? __uint_as_float(static_cast<uint32_t>(raw)) : src == 0 ? __int2float_rn(static_cast<int>(raw)) : __ll2float_rn(raw);
+    uint32_t bits = __float_as_uint(f);
+    if (f != f) bits = build_side ? 0x7FC00001u : 0x7FC00000u;
+    return static_cast<int64_t>(static_cast<int32_t>(bits));
+  }
+  double d = src == 3 ? __longlong_as_double(raw)
+           : src == 2 ? static_cast<double>(__uint_as_float(static_cast<uint32_t>(raw)))
+           : src == 0 ? __int2double_rn(static_cast<int>(raw)) : __ll2double_rn(raw);
+  long long bits = __double_as_longlong(d);
+  if (d != d) bits = build_side ? 0x7FF8000000000001ll : 0x7FF8000000000000ll;
+  return bits;
+}
+
 __device__ __forceinline__ void decode_point(const DevSegment& s, uint32_t off, int64_t* val, bool* is_null) {
   *val = 0;
   *is_null = false;
   if (s.kind == 1) {
     const uint32_t vid = load_attr(s, off);
-    if (vid == s.null_value_id) *is_null = true; else *val = load_plain_key<int64_t>(s, vid);
+    if (vid == s.null_value_id) *is_null = true; else *val = load_raw(s, vid);
   } else if (s.kind == kSegFor) {
     *is_null = s.nulls && __ldg(s.nulls + off);
-    *val = load_plain_key<int64_t>(s, off >> 11) + static_cast<int64_t>(load_attr(s, off));
+    *val = load_raw(s, off >> 11) + static_cast<int64_t>(load_attr(s, off));
   } else if (s.kind == kSegRle) {
     const uint32_t* ends = static_cast<const uint32_t*>(s.attr);
     uint32_t lo = 0, hi = s.null_value_id;  // first run with ends[run] >= off
@@ -1216,10 +1243,10 @@ __device__ __forceinline__ void decode_point(const DevSegment& s, uint32_t off, 
       if (__ldg(ends + mid) < off) lo = mid + 1; else hi = mid;
     }
     *is_null = s.nulls && __ldg(s.nulls + lo);
-    *val = load_plain_key<int64_t>(s, lo);
+    *val = load_raw(s, lo);
   } else {
     *is_null = s.nulls && __ldg(s.nulls + off);
-    *val = load_plain_key<int64_t>(s, off);
+    *val = load_raw(s, off);
   }
 }
 
@@ -1231,7 +1258,9 @@ struct RefJob {
   uint32_t n_ref;
   uint32_t n_rows;
   uint32_t row_begin;
-  uint32_t key_type;
+  uint32_t key_type;       // of out_values: 0 = 4-byte keys, 1 = 8-byte keys
+  uint32_t hash_type;      // hj_key_type the join hashes in (to_hashed_type)
+  uint32_t build_side;
 };
 
 __global__ void __launch_bounds__(256) k_gather_refs(const RefJob* __restrict__ jobs, uint32_t n_jobs, uint32_t total_rows,
@@ -1257,6 +1286,7 @@ __global__ void __launch_bounds__(256) k_gather_refs(const RefJob* __restrict__ 
         // through a ReferenceColumn a NULL yields T{} (reference_column_iterable.hpp:60); a decoded FOR/RLE chunk keeps
         // the stored value like ValueColumnIterable does (it matters for quirk Q4 only)
         if (is_null && jb.pos) val = 0;
+        else val = to_hashed_type(val, jb.ref[chunk].key_type, jb.hash_type, jb.build_side != 0);
       }
     }
     if (jb.key_type == 0) static_cast<int32_t*>(jb.out_values)[r] = static_cast<int32_t>(val);

@@ -299,8 +299,8 @@ int main(int argc, char** argv) {
   for (const auto& c : cases) {
     if (!filter.empty() && c.name.find(filter) == std::string::npos) continue;
     bool in_scope = true;
-    for (const auto& op : c.ops) in_scope = in_scope && op[0] != "scope";
-    if (!in_scope) { ++skipped; continue; }  // float/double/string keys: SURVEY §8f N3
+    for (const auto& op : c.ops) in_scope = in_scope && !(op[0] == "scope" && op.size() > 1 && op[1] == "string");
+    if (!in_scope) { ++skipped; continue; }  // string keys: SURVEY §8f N3 (float/double and int x float pairs run)
     std::map<std::string, std::shared_ptr<const Table>> env;
     std::string msg;
     bool ok = false;

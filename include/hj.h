@@ -60,9 +60,15 @@ enum hj_join_mode {
   HJ_MODE_ANTI = 6
 };
 
-/* DataType of the key column (src/lib/all_type_variant.hpp:34-39). Int = int32, Long = int64.
- * The hashed type of a mixed pair is the wider integer (join_hash/hash_traits.hpp:21-25). */
-enum hj_key_type { HJ_KEY_INT32 = 0, HJ_KEY_INT64 = 1 };
+/* DataType of the key column (src/lib/all_type_variant.hpp:34-39). Int = int32, Long = int64, Float, Double.
+ * The hashed type of a join follows JoinHashTraits (join_hash/hash_traits.hpp:14-35): two integer columns hash as the
+ * wider integer; if either column is floating point the join hashes in the floating type (the wider one of two),
+ * and integer keys are converted to it — the reference goes through boost::lexical_cast (type_cast.hpp:44-48),
+ * which for an integer's exact decimal text is the correctly rounded conversion, i.e. the IEEE cast done here.
+ * Float keys compare like in the reference: by value through the hash of their bytes, so NaN matches nothing and
+ * -0.0 does not meet +0.0. A FLOAT x DOUBLE pair is widened with the IEEE cast, NOT with the reference's 9-digit
+ * decimal round trip (the shim refuses that pair). Float keys: hj_join only (not hj_join_sharded). */
+enum hj_key_type { HJ_KEY_INT32 = 0, HJ_KEY_INT64 = 1, HJ_KEY_FLOAT = 2, HJ_KEY_DOUBLE = 3 };
 
 /* How one chunk's key column is encoded. */
 enum hj_segment_kind {

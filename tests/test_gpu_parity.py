@@ -18,6 +18,7 @@ pytestmark = pytest.mark.gpu
 
 FX = hm.Fixtures()
 IN_SCOPE = [(n, c, ops) for n, c, ops in FX.cases if hm.case_in_scope(ops)]
+FLOAT_CASES = [(n, c, ops) for n, c, ops in FX.cases if hm.case_in_scope(ops, numeric_floats=True) and not hm.case_in_scope(ops)]
 MODES = ["Inner", "Left", "Right", "Semi", "Anti"]
 
 
@@ -69,6 +70,15 @@ def test_reference_case_on_gpu(joins, name, cite, ops, radix_bits):
 
 
 # ------------------------------------------------------------------------------------------------ randomized differential
+@pytest.mark.parametrize("name,cite,ops", FLOAT_CASES, ids=[c[0] for c in FLOAT_CASES])
+def test_reference_float_key_cases_on_gpu(joins, name, cite, ops):
+    """join_equi_test.cpp:51-94 (InnerJoinIntFloat/IntDouble, both orders) against the reference's own expected tables
+    (int_float_inner.tbl, float_int_inner.tbl, int_double_inner.tbl, double_int_inner.tbl): SURVEY §8f N3."""
+    assert len(FLOAT_CASES) == 4
+    ok, msg = hm.run_case(FX, ops, gpu_engine(joins()))
+    assert ok, f"{name} ({cite}): {msg}"
+
+
 @pytest.mark.parametrize("mode", MODES)
 @pytest.mark.parametrize("encoding", ["value", "dict", "mixed", "gathered"])
 @pytest.mark.parametrize("nullable", [False, True])
