@@ -4,6 +4,7 @@
 #include "join_hash.hpp"
 
 #include <atomic>
+#include <cstdio>
 #include <cstring>
 #include <map>
 #include <memory>
@@ -133,6 +134,68 @@ void flatten_typed(const Table& table, ColumnID column_id, FlatColumn& out) {
   out.rel.n_rows = rows;
 }
 
+// ---- string keys (hash_traits.hpp:37-41: a join with a string column hashes std::string; the other side is
+// lexical_cast to text) -------------------------------------------------------------------------------------------------
+// The library joins fixed-width keys, so the operator codes the texts: one dictionary over BOTH key columns maps each
+// distinct text to an int32, the device joins the codes. Equal texts <=> equal codes, so the result is the reference's.
+// This is the one place where key values are touched on the host (SURVEY §8f N3 asks for dictionary-code joins).
+struct CodedColumn {
+  std::vector<std::vector<int32_t>> codes;   // per chunk
+  std::vector<std::vector<uint8_t>> nulls;   // per chunk, 1 = NULL
+  std::vector<hj_segment> segs;
+  hj_relation rel{};
+};
+
+std::string key_text(const AllTypeVariant& v) {
+  // boost::lexical_cast<std::string> of the variant's value (type_cast.hpp:44-48): integers as decimal text, floating
+  // point with lcast_precision digits (9 for float, 17 for double)
+  if (const auto* s = std::get_if<std::string>(&v)) return *s;
+  if (const auto* i = std::get_if<int32_t>(&v)) return std::to_string(*i);
+  if (const auto* l = std::get_if<int64_t>(&v)) return std::to_string(*l);
+  char buf[64];
+  if (const auto* f = std::get_if<float>(&v)) std::snprintf(buf, sizeof(buf), "%.9g", static_cast<double>(*f));
+  else std::snprintf(buf, sizeof(buf), "%.17g", std::get<double>(v));
+  return buf;
+}
+
+void code_column(const Table& table, ColumnID column_id, std::map<std::string, int32_t>& dictionary, CodedColumn& out) {
+  const auto n_chunks = table.chunk_count();
+  out.codes.resize(n_chunks);
+  out.nulls.resize(n_chunks);
+  out.segs.resize(n_chunks);
+  uint64_t rows = 0;
+  for (ChunkID chunk_id = 0; chunk_id < n_chunks; ++chunk_id) {
+    const auto column = table.get_chunk(chunk_id)->get_column(column_id);
+    const auto n = static_cast<uint32_t>(column->size());
+    auto& codes = out.codes[chunk_id];
+    auto& nulls = out.nulls[chunk_id];
+    codes.assign(n, 0);
+    nulls.assign(n, 0);
+    for (ChunkOffset i = 0; i < n; ++i) {
+      const AllTypeVariant v = (*column)[i];
+      if (std::holds_alternative<NullValue>(v)) {
+        nulls[i] = 1;
+        continue;
+      }
+      const auto it = dictionary.emplace(key_text(v), static_cast<int32_t>(dictionary.size())).first;
+      codes[i] = it->second;
+    }
+    hj_segment& seg = out.segs[chunk_id];
+    std::memset(&seg, 0, sizeof(seg));
+    seg.chunk_id = chunk_id;
+    seg.n_rows = n;
+    seg.kind = dynamic_cast<const ReferenceColumn*>(column.get()) ? HJ_SEG_GATHERED : HJ_SEG_VALUE;
+    seg.key_type = HJ_KEY_INT32;
+    seg.values = codes.data();
+    seg.nulls = nulls.data();
+    rows += n;
+  }
+  out.rel.segs = out.segs.data();
+  out.rel.n_segs = n_chunks;
+  out.rel.location = HJ_LOC_HOST;
+  out.rel.n_rows = rows;
+}
+
 void flatten(const Table& table, ColumnID column_id, FlatColumn& out) {
   switch (table.column_data_type(column_id)) {
     case DataType::Int: flatten_typed<int32_t>(table, column_id, out); break;
@@ -140,8 +203,7 @@ void flatten(const Table& table, ColumnID column_id, FlatColumn& out) {
     case DataType::Float: flatten_typed<float>(table, column_id, out); break;    // hashed as float/double, hash_traits.hpp:14-35
     case DataType::Double: flatten_typed<double>(table, column_id, out); break;
     default:
-      Fail("JoinHash: the B200 path joins int, long, float and double keys; string keys are not supported yet "
-           "(hash_traits.hpp:37-41)");
+      Fail("JoinHash: string key columns are dictionary-coded by _on_execute, not flattened");
   }
 }
 
@@ -259,11 +321,23 @@ std::shared_ptr<const Table> JoinHash::_on_execute() {
   }
   _ctx = acquire_ctx();
   FlatColumn build_flat, probe_flat;
-  flatten(*build_input, build_column_id, build_flat);
-  flatten(*probe_input, probe_column_id, probe_flat);
+  CodedColumn build_coded, probe_coded;
+  const hj_relation* build_rel = &build_flat.rel;
+  const hj_relation* probe_rel = &probe_flat.rel;
+  if (build_input->column_data_type(build_column_id) == DataType::String ||
+      probe_input->column_data_type(probe_column_id) == DataType::String) {
+    std::map<std::string, int32_t> dictionary;  // shared by both sides
+    code_column(*build_input, build_column_id, dictionary, build_coded);
+    code_column(*probe_input, probe_column_id, dictionary, probe_coded);
+    build_rel = &build_coded.rel;
+    probe_rel = &probe_coded.rel;
+  } else {
+    flatten(*build_input, build_column_id, build_flat);
+    flatten(*probe_input, probe_column_id, probe_flat);
+  }
 
   hj_result_info info;
-  if (hj_join(_ctx, &build_flat.rel, &probe_flat.rel, static_cast<int>(_mode), nullptr, &info) != HJ_OK)
+  if (hj_join(_ctx, build_rel, probe_rel, static_cast<int>(_mode), nullptr, &info) != HJ_OK)
     Fail(std::string("JoinHash: ") + hj_last_error(_ctx));
   if (info.n_rows == 0) return output_table;  // no empty chunks (abstract_operator.cpp:57-67)
 
