@@ -97,6 +97,29 @@ class RelationBuilder:
         s.attr, k2 = _ptr_and_keep(attr)
         return self._add(s, k1, k2)
 
+    def add_dict_bp128(self, chunk_id, dictionary, stream, n_rows, null_value_id=None):
+        """DictionaryColumn<T> whose attribute vector is SimdBp128-compressed: `stream` = the uint128 words as uint32[4*words]."""
+        s = abi.Segment()
+        s.chunk_id, s.n_rows, s.kind = chunk_id, n_rows, abi.SEG_DICT
+        s.key_type = _KEY_DTYPES[_dtype_name(dictionary)]
+        s.attr_width = 0
+        s.dict_n = len(dictionary)
+        s.null_value_id = len(dictionary) if null_value_id is None else null_value_id
+        s.values, k1 = _ptr_and_keep(dictionary)
+        s.attr, k2 = _ptr_and_keep(stream)
+        return self._add(s, k1, k2)
+
+    def add_for_bp128(self, chunk_id, block_minima, stream, n_rows, nulls=None):
+        """FrameOfReferenceColumn<T> with SimdBp128-compressed offsets."""
+        s = abi.Segment()
+        s.chunk_id, s.n_rows, s.kind = chunk_id, n_rows, abi.SEG_FOR
+        s.key_type = _KEY_DTYPES[_dtype_name(block_minima)]
+        s.attr_width = 0
+        s.values, k1 = _ptr_and_keep(block_minima)
+        s.attr, k2 = _ptr_and_keep(stream)
+        s.nulls, k3 = _ptr_and_keep(nulls)
+        return self._add(s, k1, k2, k3)
+
     def add_for(self, chunk_id, block_minima, offsets, nulls=None):
         """FrameOfReferenceColumn<T>: minima T[ceil(n/2048)], FixedSizeByteAligned offsets uint8/16/32[n], 1 byte/row flags."""
         s = abi.Segment()

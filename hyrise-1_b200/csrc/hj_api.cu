@@ -4,6 +4,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <list>
 #include <string>
 #include <vector>
 
@@ -178,7 +179,8 @@ struct PreparedRel {
 const char* encoded_segment_problem(const hj_segment& s) {
   if (s.kind == HJ_SEG_FOR) {
     if (s.key_type > HJ_KEY_INT64) return "FOR encodes int32/int64 columns only (encoding_type.hpp:34)";
-    if (s.attr_width != 1 && s.attr_width != 2 && s.attr_width != 4) return "FOR: offset vector width must be 1, 2 or 4 (FixedSizeByteAligned)";
+    if (s.attr_width != 0 && s.attr_width != 1 && s.attr_width != 2 && s.attr_width != 4)
+      return "FOR: offset vector width must be 1, 2 or 4 (FixedSizeByteAligned) or 0 (SimdBp128)";
     if (s.n_rows && (!s.values || !s.attr)) return "FOR without block minima / offsets";
   } else {
     if (s.n_rows && (!s.dict_n || !s.values || !s.attr)) return "RLE without runs";
@@ -223,7 +225,7 @@ int validate_relation(hj_ctx* ctx, const hj_relation* r, const char* name) {
           continue;
         }
         if (q.key_type != s.key_type) return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: referenced chunk %u has another key type", name, i, c);
-        if (q.kind == HJ_SEG_DICT && q.attr_width != 1 && q.attr_width != 2 && q.attr_width != 4)
+        if (q.kind == HJ_SEG_DICT && q.attr_width != 0 && q.attr_width != 1 && q.attr_width != 2 && q.attr_width != 4)
           return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: referenced chunk %u: attribute vector width %u", name, i, c, q.attr_width);
         if (q.n_rows && (q.kind == HJ_SEG_DICT ? !q.attr || (q.dict_n && !q.values) : !q.values))
           return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: referenced chunk %u has no data", name, i, c);
@@ -232,8 +234,8 @@ int validate_relation(hj_ctx* ctx, const hj_relation* r, const char* name) {
       continue;
     }
     if (s.kind == HJ_SEG_DICT) {
-      if (s.attr_width != 1 && s.attr_width != 2 && s.attr_width != 4)
-        return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: attribute vector width %u (FixedSizeByteAligned 1/2/4 only)", name, i,
+      if (s.attr_width != 0 && s.attr_width != 1 && s.attr_width != 2 && s.attr_width != 4)
+        return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: attribute vector width %u (FixedSizeByteAligned 1/2/4, or 0 = SimdBp128)", name, i,
                     s.attr_width);
       if (s.n_rows && !s.attr) return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: DICT without attribute vector", name, i);
       if (s.dict_n && !s.values) return fail(ctx, HJ_ERR_INVALID, "%s chunk %u: DICT without dictionary", name, i);
@@ -397,7 +399,8 @@ int gather_references(hj_ctx* ctx, const hj_relation* in, int side, cudaStream_t
   std::vector<uint32_t> job_segs;
   for (uint32_t i = 0; i < in->n_segs; ++i) {
     const uint8_t kind = in->segs[i].kind;
-    if (floating || kind == HJ_SEG_REFERENCE || kind == HJ_SEG_FOR || kind == HJ_SEG_RLE) job_segs.push_back(i);
+    const bool bp128 = (kind == HJ_SEG_DICT || kind == HJ_SEG_FOR) && in->segs[i].attr_width == 0;  // decoded here, too
+    if (floating || bp128 || kind == HJ_SEG_REFERENCE || kind == HJ_SEG_FOR || kind == HJ_SEG_RLE) job_segs.push_back(i);
   }
   if (job_segs.empty()) return HJ_OK;
   out->any = true;
@@ -445,6 +448,9 @@ int gather_references(hj_ctx* ctx, const hj_relation* in, int side, cudaStream_t
     arena += align(bytes);
   };
   std::vector<std::vector<DevSegment>> tabs(tables.size());
+  std::list<std::vector<uint32_t>> bp_meta;  // host-walked SimdBp128 meta-block offsets, alive until they are copied
+  struct BpWalk { const uint32_t* data; uint32_t n_rows; size_t off; const void** fix; };
+  std::vector<BpWalk> bp_walks;              // device-resident streams: offsets computed by k_bp128_meta_offsets
   for (size_t k = 0; k < tables.size(); ++k) {
     tabs[k].resize(tables[k].n);
     for (uint32_t c = 0; c < tables[k].n; ++c) {
@@ -470,9 +476,32 @@ int gather_references(hj_ctx* ctx, const hj_relation* in, int side, cudaStream_t
       d.values = n_val ? q.values : nullptr;
       d.attr = n_attr ? q.attr : nullptr;
       d.nulls = n_null ? q.nulls : nullptr;
+      size_t attr_bytes = n_attr * d.attr_width;
+      if (d.attr_width == 0 && n_attr) {  // SimdBp128 stream: the start of every 2048-value meta block is needed
+        const uint32_t M = (q.n_rows + 2047u) >> 11;
+        if (host) {
+          bp_meta.emplace_back(M);
+          std::vector<uint32_t>& off = bp_meta.back();
+          const auto* words = static_cast<const uint8_t*>(q.attr);
+          uint32_t pos = 0;
+          for (uint32_t m = 0; m < M; ++m) {
+            off[m] = pos;
+            const uint8_t* widths = words + size_t(pos) * 16;
+            const uint32_t blocks = m + 1 < M ? 16u : (q.n_rows - (m << 11) + 127u) >> 7;
+            uint32_t len = 1;
+            for (uint32_t b = 0; b < blocks; ++b) len += widths[b];
+            pos += len;
+          }
+          attr_bytes = size_t(pos) * 16;
+          plan(off.data(), size_t(M) * 4, reinterpret_cast<const void**>(&d.row_offsets));
+        } else {
+          bp_walks.push_back({static_cast<const uint32_t*>(q.attr), q.n_rows, arena, reinterpret_cast<const void**>(&d.row_offsets)});
+          arena += align(size_t(M) * 4);
+        }
+      }
       if (host) {
         if (n_val) plan(q.values, n_val * key_bytes(q.key_type), &d.values);
-        if (n_attr) plan(q.attr, n_attr * d.attr_width, &d.attr);
+        if (n_attr) plan(q.attr, attr_bytes, &d.attr);
         if (n_null) plan(q.nulls, n_null, reinterpret_cast<const void**>(&d.nulls));
       }
     }
@@ -509,6 +538,11 @@ int gather_references(hj_ctx* ctx, const hj_relation* in, int side, cudaStream_t
     HJ_CUDA(ctx, cudaMemcpyAsync(base + c.off, c.src, c.bytes, cudaMemcpyHostToDevice, st));
     *c.fix = base + c.off;  // the table entry / job now points at the staged copy
     ctx->ref_h2d_bytes += c.bytes;
+  }
+  for (const BpWalk& w : bp_walks) {
+    k_bp128_meta_offsets<<<1, 32, 0, st>>>(w.data, w.n_rows, reinterpret_cast<uint32_t*>(base + w.off));
+    HJ_LAUNCH_CHECK(ctx, "k_bp128_meta_offsets");
+    *w.fix = base + w.off;
   }
   for (size_t k = 0; k < tables.size(); ++k)
     if (tables[k].n)

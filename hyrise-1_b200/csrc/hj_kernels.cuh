@@ -1199,6 +1199,46 @@ __global__ void __launch_bounds__(256) k_compact_move(const CompactHdr* __restri
 // Point access into one chunk of a data table's key column: VALUE, DICT, FOR (frame of reference, 2048-row blocks) or
 // RLE (binary search over the inclusive run ends; null_value_id holds the number of runs).
 constexpr uint8_t kSegFor = 4, kSegRle = 5;  // == HJ_SEG_FOR / HJ_SEG_RLE
+// SimdBp128 (simd_bp128_packing.cpp): data is a sequence of 16-byte words; meta block m (2048 values) starts at word
+// meta_off[m] with one word holding the bit widths of its 16 blocks, block b then takes width[b] words; value j of a
+// block lives in 32-bit lane j % 4 at bit (j / 4) * width of that lane's stream, possibly split over two words.
+__device__ __forceinline__ uint32_t bp128_get(const uint32_t* data, const uint32_t* meta_off, uint32_t i) {
+  const uint32_t m = i >> 11, b = (i >> 7) & 15u, j = i & 127u;
+  const uint32_t base = __ldg(meta_off + m);
+  const uint8_t* widths = reinterpret_cast<const uint8_t*>(data + static_cast<size_t>(base) * 4);
+  uint32_t start = base + 1u;
+  for (uint32_t q = 0; q < b; ++q) start += widths[q];
+  const uint32_t width = widths[b];
+  if (width == 0) return 0u;
+  const uint32_t lane = j & 3u, bit = (j >> 2) * width, w = bit >> 5, o = bit & 31u;
+  const uint32_t* p = data + (static_cast<size_t>(start) + w) * 4 + lane;
+  uint32_t v = __ldg(p) >> o;
+  if (o + width > 32u) v |= __ldg(p + 4) << (32u - o);
+  return width == 32u ? v : v & ((1u << width) - 1u);
+}
+
+// start word of every meta block (one thread walks the stream: n_rows / 2048 steps)
+__global__ void k_bp128_meta_offsets(const uint32_t* __restrict__ data, uint32_t n_rows, uint32_t* __restrict__ meta_off) {
+  if (blockIdx.x || threadIdx.x) return;
+  const uint32_t M = (n_rows + 2047u) >> 11;
+  uint32_t pos = 0;
+  for (uint32_t m = 0; m < M; ++m) {
+    meta_off[m] = pos;
+    const uint8_t* widths = reinterpret_cast<const uint8_t*>(data + static_cast<size_t>(pos) * 4);
+    const uint32_t blocks = m + 1 < M ? 16u : (n_rows - (m << 11) + 127u) >> 7;
+    uint32_t words = 1;
+    for (uint32_t q = 0; q < blocks; ++q) words += widths[q];
+    pos += words;
+  }
+}
+
+// attribute-vector / offset entry i of a DICT or FOR chunk, FixedSizeByteAligned or SimdBp128 (attr_width 0; the meta
+// block offsets hang on row_offsets, which these kinds do not use otherwise)
+__device__ __forceinline__ uint32_t load_attr_any(const DevSegment& s, uint32_t i) {
+  if (s.attr_width == 0) return bp128_get(static_cast<const uint32_t*>(s.attr), s.row_offsets, i);
+  return load_attr(s, i);
+}
+
 // element i of a chunk's value array as a 64-bit container: integers sign-extended, float/double as their bit patterns
 __device__ __forceinline__ int64_t load_raw(const DevSegment& s, uint32_t i) {
   if (s.key_type == 0) return __ldg(static_cast<const int32_t*>(s.values) + i);
@@ -1230,11 +1270,11 @@ __device__ __forceinline__ void decode_point(const DevSegment& s, uint32_t off, 
   *val = 0;
   *is_null = false;
   if (s.kind == 1) {
-    const uint32_t vid = load_attr(s, off);
+    const uint32_t vid = load_attr_any(s, off);
     if (vid == s.null_value_id) *is_null = true; else *val = load_raw(s, vid);
   } else if (s.kind == kSegFor) {
     *is_null = s.nulls && __ldg(s.nulls + off);
-    *val = load_raw(s, off >> 11) + static_cast<int64_t>(load_attr(s, off));
+    *val = load_raw(s, off >> 11) + static_cast<int64_t>(load_attr_any(s, off));
   } else if (s.kind == kSegRle) {
     const uint32_t* ends = static_cast<const uint32_t*>(s.attr);
     uint32_t lo = 0, hi = s.null_value_id;  // first run with ends[run] >= off

@@ -109,7 +109,11 @@ typedef struct hj_segment {
   uint32_t n_rows;        /* rows in this chunk's column                                    */
   uint8_t kind;           /* hj_segment_kind                                                */
   uint8_t key_type;       /* hj_key_type of `values`                                        */
-  uint8_t attr_width;     /* DICT: bytes per attribute-vector entry: 1, 2 or 4              */
+  uint8_t attr_width;     /* DICT/FOR: bytes per attribute-vector / offset entry: 1, 2 or 4
+                             (FixedSizeByteAligned), or 0: `attr` is a SimdBp128 stream
+                             (vector_compression/simd_bp128/simd_bp128_packing.hpp:17-21: per 2048
+                             values one 16-byte word of 16 bit widths, then for each block of 128
+                             values `width` 16-byte words, four interleaved 32-bit lanes) — N2  */
   uint8_t reserved0;
   uint32_t dict_n;        /* DICT: entries in the dictionary; RLE: number of runs           */
   uint32_t null_value_id; /* DICT: ValueID meaning NULL (== dict_n in the reference)        */

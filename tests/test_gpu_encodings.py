@@ -44,6 +44,9 @@ def rle_encode(values, nulls):
     return np.ascontiguousarray(values[starts]), ends, np.ascontiguousarray(nl[starts]), starts
 
 
+bp128_pack = wl.bp128_pack
+
+
 def encoded_relation(keys, nulls, chunk, encoding):
     """(relation of FOR / RLE / mixed chunks, the equivalent ValueColumn relation for the oracle)"""
     rb = hj.RelationBuilder(abi.LOC_HOST)
@@ -52,7 +55,18 @@ def encoded_relation(keys, nulls, chunk, encoding):
         v = np.ascontiguousarray(keys[start:start + chunk])
         nl = None if nulls is None else np.ascontiguousarray(nulls[start:start + chunk])
         enc = encoding if encoding != "mixed" else ("for", "rle", "value")[c % 3]
-        if enc == "for":
+        if enc == "dict_bp128":
+            d, attr, nv = wl.dict_encode(v, nl)
+            rb.add_dict_bp128(c, d, bp128_pack(attr), len(v), nv)
+            if nl is not None:  # a NULL row of a dictionary column decodes to T{} (dictionary_column_iterable.hpp:80)
+                stored = v.copy()
+                stored[nl != 0] = 0
+                plain[start:start + chunk] = stored
+        elif enc == "for_bp128":
+            minima, off, stored = for_encode(v, nl)
+            rb.add_for_bp128(c, minima, bp128_pack(off), len(v), nl)
+            plain[start:start + chunk] = stored
+        elif enc == "for":
             minima, off, stored = for_encode(v, nl)
             rb.add_for(c, minima, off, nl)
             plain[start:start + chunk] = stored
@@ -101,6 +115,45 @@ def test_for_and_rle_key_columns(join, mode, encoding, dtype):
     build, o_build = encoded_relation(bk, bn, 4500, encoding)
     probe, o_probe = encoded_relation(pk, pn, 6000, encoding)
     check(join, build, probe, o_build, o_probe, mode, encoding)
+
+
+@pytest.mark.parametrize("mode", ["Inner", "Left", "Anti"])
+@pytest.mark.parametrize("encoding", ["dict_bp128", "for_bp128"])
+@pytest.mark.parametrize("dtype", [np.int32, np.int64])
+def test_simd_bp128_vectors(join, mode, encoding, dtype):
+    """SimdBp128-compressed attribute vectors (DictionaryColumn) and offset vectors (FrameOfReferenceColumn): ragged last
+    meta block and last block, blocks of width 0, and wide blocks whose values straddle 32-bit words"""
+    rng = np.random.default_rng(hash((mode, encoding, dtype.__name__)) % 2**32)
+    bk = np.sort(wl.random_keys(rng, 9_000, 3000, dtype))
+    pk = wl.random_keys(rng, 2 * 2048 + 700 + 45, 3500, dtype)   # 2 full meta blocks + 5 full blocks + 105 values
+    pk[300:428] = pk[300]                                          # one block of equal values (small width)
+    pk[2048:2048 + 256] += 3_000_000                               # wide offsets in two blocks
+    bn = (rng.random(len(bk)) < 0.03).astype(np.uint8)
+    pn = (rng.random(len(pk)) < 0.03).astype(np.uint8)
+    build, o_build = encoded_relation(bk, bn, 4100, encoding)
+    probe, o_probe = encoded_relation(pk, pn, len(pk), encoding)
+    check(join, build, probe, o_build, o_probe, mode, encoding)
+
+
+def test_simd_bp128_device_resident_and_referenced(join):
+    """the stream already on the device (meta-block offsets computed by a kernel), and behind a ReferenceColumn"""
+    import torch
+    rng = np.random.default_rng(21)
+    keys = wl.random_keys(rng, 5000, 900, np.int32)
+    d, attr, nv = wl.dict_encode(keys, None)
+    stream = bp128_pack(attr)
+    dev = torch.device("cuda", 0)
+    data_dev = hj.RelationBuilder(abi.LOC_DEVICE).add_dict_bp128(
+        0, torch.from_numpy(d.copy()).to(dev), torch.from_numpy(stream.view(np.int32).copy()).to(dev), len(keys), nv).build()
+    bk = wl.random_keys(rng, 700, 900, np.int32)
+    build_dev = hj.RelationBuilder(abi.LOC_DEVICE).add_value(0, torch.from_numpy(bk.copy()).to(dev)).build()
+    o_build, o_probe = wl.make_relation(bk, 700), wl.make_relation(keys, 5000)
+    check(join, build_dev, data_dev, o_build, o_probe, "Inner", "bp128 on device")
+    g = rng.integers(0, len(keys), 8000)
+    pos = np.stack([np.zeros_like(g), g], axis=1).astype(np.uint32)
+    data_host = hj.RelationBuilder().add_dict_bp128(0, d, stream, len(keys), nv).build()
+    ref = hj.RelationBuilder().add_reference(0, pos, data_host, abi.KEY_INT32).build()
+    check(join, wl.make_relation(bk, 700), ref, o_build, wl.make_relation(keys[g], 8000, "gathered"), "Inner", "ref over bp128")
 
 
 def test_reference_over_encoded_table(join):

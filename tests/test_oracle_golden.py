@@ -50,3 +50,32 @@ def test_reference_radix_bits():
     assert rb(100_000_000, 0) == 15
     assert rb(200_000_000, 1) == 16
     assert rb(0, 0) == 0 and rb(10, 0) == 0
+
+
+def test_simd_bp128_layout_matches_reference():
+    """The numpy SimdBp128 packer the GPU tests feed libhj with (workloads.bp128_pack) against the reference's own
+    SimdBp128Packing::pack_block / unpack_block, compiled in place into oracle/_ref/libref_bp128.so (all 33 bit widths)."""
+    import numpy as np
+    import workloads as wl
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    so = os.path.join(root, "oracle", "_ref", "libref_bp128.so")
+    if not os.path.exists(so):
+        pytest.skip("oracle/_ref/libref_bp128.so not built (needs /root/reference at build time)")
+    ref = C.CDLL(so)
+    rng = np.random.default_rng(128)
+    for width in range(33):
+        vals = (rng.integers(0, 2**63, 128, dtype=np.uint64) & np.uint64((1 << width) - 1)).astype(np.uint32)
+        if width:
+            vals[5] = (1 << width) - 1  # make sure the block needs exactly `width` bits
+        words = np.zeros(max(width, 1) * 4 + 4, dtype=np.uint32)
+        buf = np.ascontiguousarray(np.concatenate([np.zeros(0, np.uint32), words]))
+        aligned = np.zeros(len(buf) + 4, dtype=np.uint32)
+        off = (-aligned.ctypes.data // 4) % 4          # 16-byte aligned start for _mm_store_si128
+        out = aligned[off:off + max(width, 1) * 4]
+        ref.ref_bp128_pack_block(vals.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p), C.c_uint8(width))
+        mine = wl.bp128_pack(vals)                      # [meta word][width words]
+        assert bytes(mine[:4].view(np.uint8))[0] == width and not any(bytes(mine[:4].view(np.uint8))[1:])
+        assert np.array_equal(mine[4:], out[:width * 4]), f"width {width}: packed words differ from the reference's"
+        back = np.zeros(128, dtype=np.uint32)
+        ref.ref_bp128_unpack_block(out.ctypes.data_as(C.c_void_p), back.ctypes.data_as(C.c_void_p), C.c_uint8(width))
+        assert np.array_equal(back, vals)

@@ -84,3 +84,31 @@ def zipf_keys(rng, n, domain, s=1.0, dtype=np.int64):
     cdf /= cdf[-1]
     r = np.searchsorted(cdf, rng.random(n)).astype(np.int64)  # 0-based rank
     return ((r * 2654435761) % domain + 1).astype(dtype) if np.gcd(2654435761, domain) == 1 else (r + 1).astype(dtype)
+
+
+def bp128_pack(values):
+    """SimdBp128Compressor (simd_bp128_compressor.cpp:33-110) + Pack128Bit (simd_bp128_packing.cpp:30-95): per meta block
+    of 2048 values (zero-padded) one 16-byte word of 16 bit widths, then per packed block of 128 values `width` 16-byte
+    words; value j sits in 32-bit lane j % 4, at bit (j / 4) * width of the lane's little-endian bit stream."""
+    v = np.asarray(values, dtype=np.uint64)
+    n = len(v)
+    out = []
+    for m0 in range(0, n, 2048):
+        meta = np.zeros(2048, dtype=np.uint64)
+        cnt = min(2048, n - m0)
+        meta[:cnt] = v[m0:m0 + cnt]
+        widths = [int(np.bitwise_or.reduce(meta[b * 128:(b + 1) * 128])).bit_length() for b in range(16)]
+        out.append(np.frombuffer(bytes(widths), dtype=np.uint32))
+        for b in range((cnt + 127) // 128):
+            w = widths[b]
+            if w == 0:
+                continue
+            words = np.zeros((w, 4), dtype=np.uint32)
+            for lane in range(4):
+                stream = 0
+                for k, x in enumerate(meta[b * 128 + lane:(b + 1) * 128:4]):
+                    stream |= int(x) << (k * w)
+                for i in range(w):
+                    words[i, lane] = (stream >> (32 * i)) & 0xFFFFFFFF
+            out.append(words.reshape(-1))
+    return np.concatenate(out) if out else np.zeros(4, dtype=np.uint32)
