@@ -17,16 +17,41 @@ using namespace hj;
 namespace {
 
 // ---- tuning constants -----------------------------------------------------------------------------------
+// The HJ_TUNE_* macros exist for tests/sweep_variants.py, which builds the library several times with -D overrides and
+// times the variants side by side on the GPU; the defaults below are what ships.
+#ifndef HJ_TUNE_ITEMS1_32
+#define HJ_TUNE_ITEMS1_32 16
+#endif
+#ifndef HJ_TUNE_P1_VIRTUAL
+#define HJ_TUNE_P1_VIRTUAL 2
+#endif
+#ifndef HJ_TUNE_P2_THREADS
+#define HJ_TUNE_P2_THREADS 256
+#endif
+#ifndef HJ_TUNE_P2_ITEMS32
+#define HJ_TUNE_P2_ITEMS32 16
+#endif
+#ifndef HJ_TUNE_P2_ITEMS64
+#define HJ_TUNE_P2_ITEMS64 8
+#endif
+#ifndef HJ_TUNE_P2_MINBLOCKS
+#define HJ_TUNE_P2_MINBLOCKS (1024 / HJ_TUNE_P2_THREADS)
+#endif
+#ifndef HJ_TUNE_PROBE_V
+#define HJ_TUNE_PROBE_V 4
+#endif
 template <typename K> struct Cfg;
 template <> struct Cfg<int32_t> {
-  static constexpr int kItems1 = 16;      // pass 1: 256 threads x 16 = 4096 rows per tile (32 KB staged)
+  static constexpr int kItems1 = HJ_TUNE_ITEMS1_32;  // pass 1: 256 threads x 16 = 4096 rows per tile (32 KB staged)
   static constexpr int kItems2 = 16;      // pass 2: 4096 tuples per tile
+  static constexpr int kP2Items = HJ_TUNE_P2_ITEMS32;  // fused pass 2 (k_scatter2f): tuples per thread and batch
   static constexpr int kNS = 16384;       // hash-table slots per shared-memory table
   static constexpr int kCap = 12288;      // build tuples per table (load factor <= 0.75)
 };
 template <> struct Cfg<int64_t> {
   static constexpr int kItems1 = 8;       // 2048 rows per tile (32 KB staged)
   static constexpr int kItems2 = 8;
+  static constexpr int kP2Items = HJ_TUNE_P2_ITEMS64;
   static constexpr int kNS = 8192;
   static constexpr int kCap = 6144;
 };
@@ -34,15 +59,17 @@ constexpr int kScatterThreads = 256;
 constexpr int kHistThreads = 1024;        // K1: one physical CTA per SM ...
 constexpr int kHistVirtual = 4;           // ... hosting 4 virtual CTAs of 256 threads (one wave of all 4 x #SM tile owners)
 constexpr int kJoinThreads = 1024;
-constexpr int kProbeV = 4;
+constexpr int kProbeV = HJ_TUNE_PROBE_V;
 constexpr uint32_t kProbeSlice = 128 * 1024;
 constexpr int kSinglePassMaxBits = 8;
 constexpr uint64_t kMinSliceRows = 32u << 20;  // streamed join: probe slices of at least 32 Mi rows
 constexpr int kMinChunkShift = 8, kMaxChunkShift = 14;  // result chunks of 256 .. 16 Ki rows
-constexpr int kPart1Virtual = 2;             // fused P1: 2 virtual CTAs of 512 threads (shared memory is L1 taken from the gather)
+constexpr int kPart1Virtual = HJ_TUNE_P1_VIRTUAL;             // fused P1: 2 virtual CTAs of 512 threads (shared memory is L1 taken from the gather)
 constexpr int kVirtualCtasPerSm = 4;       // K1 / pass 1 tile ownership: G = min(n_tiles, 4 * SMs) virtual CTAs
 template <typename K> constexpr int tile1() { return kScatterThreads * Cfg<K>::kItems1; }
 template <typename K> constexpr int tile2() { return kScatterThreads * Cfg<K>::kItems2; }
+constexpr int kP2Threads = HJ_TUNE_P2_THREADS, kP2MinBlocks = HJ_TUNE_P2_MINBLOCKS;  // fused pass 2: CTA size and CTAs per SM
+template <typename K> constexpr int p2_tile() { return kP2Threads * Cfg<K>::kP2Items; }
 // 12-byte RowID-carrying tuples of int32 keys: same tile sizes with twice the threads and half the rows per thread, so that
 // a thread's keys + RowIDs (pass 1) / three-word tuples (pass 2) fit the register file without spilling
 template <typename K, bool PAY> constexpr int scatter_threads() { return (PAY && sizeof(K) == 4) ? 2 * kScatterThreads : kScatterThreads; }
@@ -768,9 +795,9 @@ int stage_pass2(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, in
   if (!pr.meta.n_tiles || !bits2) return HJ_OK;
   if constexpr (!PAY) {
     if (ps.fused) {
-      constexpr int NT = kScatterThreads;
-      auto k = k_scatter2f<K, NT, tile2<K>() / NT>;
-      const size_t smem = size_t(tile2<K>()) * sizeof(Tuple<K, false>);
+      constexpr int NT = kP2Threads;
+      auto k = k_scatter2f<K, NT, Cfg<K>::kP2Items, kP2MinBlocks>;
+      const size_t smem = size_t(p2_tile<K>()) * sizeof(Tuple<K, false>);
       HJ_TRY(set_smem(ctx, k, smem));
       const uint32_t F1 = (1u << radix_bits) >> bits2;
       const uint32_t n_digits = F1 + (null_policy == kNullRoute ? 1u : 0u);

@@ -16,6 +16,10 @@
 #pragma once
 #include "hj_kernels.cuh"
 
+#ifndef HJ_TUNE_P1_PREFETCH
+#define HJ_TUNE_P1_PREFETCH 0
+#endif
+
 namespace hj {
 
 // =====================================================================================================================
@@ -84,6 +88,18 @@ __global__ void __launch_bounds__(NT) k_part1(RelMeta rel, Tuple<K, false>* __re
         }
       }
     }
+#if HJ_TUNE_P1_PREFETCH
+    // the virtual CTA's next tile: pull its attribute vector / value lines into L2 while this tile is ranked and staged
+    // (no registers held across the tile, unlike a software-pipelined load)
+    if (tile + G < rel.n_tiles && vt < TILE * sizeof(K) / 128) {
+      const DevSegment* ns = rel.segs + __ldg(rel.tile_seg + tile + G);
+      const uint32_t nr0 = (tile + G - ns->tile_begin) * TILE;
+      const uint32_t width = ns->kind == 1 ? ns->attr_width : static_cast<uint32_t>(sizeof(K));
+      const char* base = static_cast<const char*>(ns->kind == 1 ? ns->attr : ns->values) + static_cast<size_t>(nr0) * width;
+      const uint32_t bytes = min(static_cast<uint32_t>(TILE), ns->n_rows - nr0) * width;
+      if (vt * 128u < bytes) asm volatile("prefetch.global.L2 [%0];" ::"l"(base + vt * 128u));
+    }
+#endif
     uint32_t packed[ITEMS];  // digit << 16 | rank inside the digit, or kNoDigit
 #pragma unroll
     for (int u = 0; u < ITEMS; ++u) {
@@ -155,8 +171,8 @@ __global__ void __launch_bounds__(NT) k_part1(RelMeta rel, Tuple<K, false>* __re
 // d1 == F1 (only with kNullRoute): the routed NULL probe rows, copied behind the last partition (part_off[P]).
 // dynamic smem: TILE * sizeof(Tuple<K>).
 // =====================================================================================================================
-template <typename K, int NT, int ITEMS>
-__global__ void __launch_bounds__(NT, 1024 / NT) k_scatter2f(const Tuple<K, false>* __restrict__ in, const uint16_t* __restrict__ frag,
+template <typename K, int NT, int ITEMS, int MINB>
+__global__ void __launch_bounds__(NT, MINB) k_scatter2f(const Tuple<K, false>* __restrict__ in, const uint16_t* __restrict__ frag,
                                                             RelMeta rel, uint32_t tile1, Tuple<K, false>* __restrict__ out,
                                                             uint32_t* __restrict__ cur2, int radix_bits, int bits2, uint32_t gs,
                                                             uint32_t n_digits) {
