@@ -22,8 +22,14 @@ namespace {
 #ifndef HJ_TUNE_ITEMS1_32
 #define HJ_TUNE_ITEMS1_32 16
 #endif
-#ifndef HJ_TUNE_P1_VIRTUAL
-#define HJ_TUNE_P1_VIRTUAL 2
+#ifndef HJ_TUNE_P1_TILE32
+#define HJ_TUNE_P1_TILE32 2048
+#endif
+#ifndef HJ_TUNE_P1_VIRTUAL32
+#define HJ_TUNE_P1_VIRTUAL32 4
+#endif
+#ifndef HJ_TUNE_P1_VIRTUAL64
+#define HJ_TUNE_P1_VIRTUAL64 2
 #endif
 #ifndef HJ_TUNE_P2_THREADS
 #define HJ_TUNE_P2_THREADS 256
@@ -37,6 +43,9 @@ namespace {
 #ifndef HJ_TUNE_P2_MINBLOCKS
 #define HJ_TUNE_P2_MINBLOCKS (1024 / HJ_TUNE_P2_THREADS)
 #endif
+#ifndef HJ_TUNE_P2_FILL16
+#define HJ_TUNE_P2_FILL16 14  // a pass-2 work item holds FILL16/16 of a batch on average
+#endif
 #ifndef HJ_TUNE_PROBE_V
 #define HJ_TUNE_PROBE_V 4
 #endif
@@ -45,6 +54,10 @@ template <> struct Cfg<int32_t> {
   static constexpr int kItems1 = HJ_TUNE_ITEMS1_32;  // pass 1: 256 threads x 16 = 4096 rows per tile (32 KB staged)
   static constexpr int kItems2 = 16;      // pass 2: 4096 tuples per tile
   static constexpr int kP2Items = HJ_TUNE_P2_ITEMS32;  // fused pass 2 (k_scatter2f): tuples per thread and batch
+  // fused pass 1 (k_part1): 4 virtual CTAs of 256 threads with 2048-row tiles. Same shared memory as 2 x 4096 (L1 left to
+  // the dictionary gather), but four independent tile streams per SM keep the gather pipeline busier: C2 P1 8.54 -> 7.88 ms,
+  // pass 2 +0.12 ms for the shorter fragments (profiles/r01_sweep_variants_c2_full.json)
+  static constexpr int kP1Tile = HJ_TUNE_P1_TILE32, kP1Virtual = HJ_TUNE_P1_VIRTUAL32;
   static constexpr int kNS = 16384;       // hash-table slots per shared-memory table
   static constexpr int kCap = 12288;      // build tuples per table (load factor <= 0.75)
 };
@@ -52,6 +65,7 @@ template <> struct Cfg<int64_t> {
   static constexpr int kItems1 = 8;       // 2048 rows per tile (32 KB staged)
   static constexpr int kItems2 = 8;
   static constexpr int kP2Items = HJ_TUNE_P2_ITEMS64;
+  static constexpr int kP1Tile = 2048, kP1Virtual = HJ_TUNE_P1_VIRTUAL64;
   static constexpr int kNS = 8192;
   static constexpr int kCap = 6144;
 };
@@ -64,12 +78,12 @@ constexpr uint32_t kProbeSlice = 128 * 1024;
 constexpr int kSinglePassMaxBits = 8;
 constexpr uint64_t kMinSliceRows = 32u << 20;  // streamed join: probe slices of at least 32 Mi rows
 constexpr int kMinChunkShift = 8, kMaxChunkShift = 14;  // result chunks of 256 .. 16 Ki rows
-constexpr int kPart1Virtual = HJ_TUNE_P1_VIRTUAL;             // fused P1: 2 virtual CTAs of 512 threads (shared memory is L1 taken from the gather)
 constexpr int kVirtualCtasPerSm = 4;       // K1 / pass 1 tile ownership: G = min(n_tiles, 4 * SMs) virtual CTAs
 template <typename K> constexpr int tile1() { return kScatterThreads * Cfg<K>::kItems1; }
 template <typename K> constexpr int tile2() { return kScatterThreads * Cfg<K>::kItems2; }
 constexpr int kP2Threads = HJ_TUNE_P2_THREADS, kP2MinBlocks = HJ_TUNE_P2_MINBLOCKS;  // fused pass 2: CTA size and CTAs per SM
 template <typename K> constexpr int p2_tile() { return kP2Threads * Cfg<K>::kP2Items; }
+template <typename K> constexpr int p1_tile() { return Cfg<K>::kP1Tile; }
 // 12-byte RowID-carrying tuples of int32 keys: same tile sizes with twice the threads and half the rows per thread, so that
 // a thread's keys + RowIDs (pass 1) / three-word tuples (pass 2) fit the register file without spilling
 template <typename K, bool PAY> constexpr int scatter_threads() { return (PAY && sizeof(K) == 4) ? 2 * kScatterThreads : kScatterThreads; }
@@ -670,6 +684,18 @@ int set_smem(hj_ctx* ctx, KernelT kernel, size_t bytes) {
 }
 
 // ---- partitioning stages for one relation ------------------------------------------------------------------------------
+// The fused path (hj_fused.cuh) and the two-sweep path cut a relation into tiles of different sizes, so the choice is made
+// before prepare_relation builds the tile map. Rows received through the exchange carry RowIDs that only the two-sweep
+// kernels load (k_scatter1).
+template <bool PAY>
+bool use_fused(const hj_ctx* ctx, int bits2, int side) {
+  return !PAY && bits2 > 0 && !(ctx->opts.flags & HJ_FLAG_TWO_SWEEP_PARTITION) && !ctx->xchg_rowids[side];
+}
+template <typename K, bool PAY>
+uint32_t tile_rows(const hj_ctx* ctx, int bits2, int side) {
+  return use_fused<PAY>(ctx, bits2, side) ? uint32_t(p1_tile<K>()) : uint32_t(tile1<K>());
+}
+
 struct PartState {
   uint32_t G = 0;      // virtual CTAs of K1 / pass 1
   bool fused = false;  // hj_fused.cuh: slab-local pass 1 inside the histogram kernel, fragment-gathering pass 2
@@ -679,7 +705,7 @@ struct PartState {
 // P1's dynamic shared memory: the full-resolution histogram + one staging tile per virtual CTA
 template <typename K>
 size_t part1_smem(int radix_bits) {
-  return ((((size_t(1) << radix_bits) + 1) * 4 + 15) & ~size_t(15)) + size_t(kPart1Virtual) * tile1<K>() * (sizeof(K) + 2);
+  return ((((size_t(1) << radix_bits) + 1) * 4 + 15) & ~size_t(15)) + size_t(Cfg<K>::kP1Virtual) * p1_tile<K>() * (sizeof(K) + 2);
 }
 
 template <typename K, bool PAY>
@@ -688,10 +714,10 @@ int stage_alloc(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, in
   const uint32_t n = pr.meta.n_rows;
   ps->G = std::max<uint32_t>(1, std::min<uint32_t>(pr.meta.n_tiles, uint32_t(kVirtualCtasPerSm) * ctx->n_sms));
   ps->G = (ps->G + kHistVirtual - 1) / kHistVirtual * kHistVirtual;  // K1 hosts kHistVirtual virtual CTAs per physical CTA
-  // rows received through the exchange carry RowIDs that only the two-sweep kernels load (k_scatter1)
-  ps->fused = !PAY && bits2 > 0 && !(ctx->opts.flags & HJ_FLAG_TWO_SWEEP_PARTITION) && !ctx->xchg_rowids[side];
+  ps->fused = use_fused<PAY>(ctx, bits2, side);
   if (ps->fused) {
-    ps->gs = std::max<uint32_t>(1, F1 * 7 / 8);  // an item gathers gs fragments of tile1/F1 tuples on average: 7/8 of a tile
+    // an item gathers gs fragments of p1_tile/F1 tuples on average: HJ_TUNE_P2_FILL16/16 = 7/8 of a pass-2 batch (k_scatter2f needs gs < its CTA size and keeps fragment owners in 8 bits)
+    ps->gs = std::min<uint32_t>(std::min(kP2Threads - 1, 255), std::max<uint64_t>(1, uint64_t(p2_tile<K>()) * HJ_TUNE_P2_FILL16 / 16 * F1 / p1_tile<K>()));
     HJ_TRY(ensure(ctx, ctx->frag[side], std::max<size_t>(1, pr.meta.n_tiles) * (F1 + 2) * 2));
   }
   HJ_TRY(ensure(ctx, ctx->hist[side], (size_t(P) + 1) * 4));
@@ -718,10 +744,11 @@ int stage_hist(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int
   HJ_CUDA(ctx, cudaMemsetAsync(hist, 0, (size_t(P) + 1) * 4, st));
   if (ps.fused) {
     if (pr.meta.n_tiles) {
-      auto k = k_part1<K, kHistThreads, kPart1Virtual, tile1<K>()>;
+      constexpr int VC = Cfg<K>::kP1Virtual;
+      auto k = k_part1<K, kHistThreads, VC, p1_tile<K>()>;
       const size_t smem = part1_smem<K>(radix_bits);
       HJ_TRY(set_smem(ctx, k, smem));
-      const uint32_t grid = std::min<uint32_t>((pr.meta.n_tiles + kPart1Virtual - 1) / kPart1Virtual, ctx->n_sms);
+      const uint32_t grid = std::min<uint32_t>((pr.meta.n_tiles + VC - 1) / VC, ctx->n_sms);
       k<<<grid, kHistThreads, smem, st>>>(pr.meta, static_cast<Tuple<K, false>*>(ctx->tup_a[side].p),
                                           static_cast<uint16_t*>(ctx->frag[side].p), hist, radix_bits, bits2, null_policy);
       HJ_LAUNCH_CHECK(ctx, "k_part1");
@@ -804,7 +831,7 @@ int stage_pass2(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, in
       const uint64_t grid = uint64_t((pr.meta.n_tiles + ps.gs - 1) / ps.gs) * n_digits;
       if (grid > 0x7FFFFFFFull) return fail(ctx, HJ_ERR_TOO_LARGE, "pass 2: %llu work items", (unsigned long long)grid);
       k<<<uint32_t(grid), NT, smem, st>>>(static_cast<const Tuple<K, false>*>(ctx->tup_a[side].p),
-                                          static_cast<const uint16_t*>(ctx->frag[side].p), pr.meta, uint32_t(tile1<K>()),
+                                          static_cast<const uint16_t*>(ctx->frag[side].p), pr.meta, uint32_t(p1_tile<K>()),
                                           static_cast<Tuple<K, false>*>(ctx->tup_b[side].p),
                                           static_cast<uint32_t*>(ctx->cur2[side].p), radix_bits, bits2, ps.gs, n_digits);
       HJ_LAUNCH_CHECK(ctx, "k_scatter2f");
@@ -1006,14 +1033,15 @@ int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, in
   // events: 0 start, 1 after staging, 2 after K1/K2, 3 after pass 1, 4 after pass 2, 5 after build+probe, 6 end
   HJ_CUDA(ctx, cudaEventRecord(ev[0], st));
 
-  PreparedRel pb, pp;
-  HJ_TRY(prepare_relation(ctx, build, 0, tile1<K>(), st, &pb));
-  HJ_TRY(prepare_relation(ctx, probe, 1, tile1<K>(), st, &pp));
-  HJ_CUDA(ctx, cudaEventRecord(ev[1], st));
-
   const int radix_bits = ctx->opts.radix_bits >= 0 ? std::min(ctx->opts.radix_bits, kMaxRadixBits)
                                                    : radix_bits_for(build->n_rows, sizeof(K) == 8 ? HJ_KEY_INT64 : HJ_KEY_INT32);
   const int bits2 = radix_bits > kSinglePassMaxBits ? radix_bits / 2 : 0;
+
+  PreparedRel pb, pp;
+  HJ_TRY(prepare_relation(ctx, build, 0, tile_rows<K, PAY>(ctx, bits2, 0), st, &pb));
+  HJ_TRY(prepare_relation(ctx, probe, 1, tile_rows<K, PAY>(ctx, bits2, 1), st, &pp));
+  HJ_CUDA(ctx, cudaEventRecord(ev[1], st));
+
   const uint32_t P = 1u << radix_bits;
   const int probe_null_policy = !outer ? kNullDrop : ((ctx->opts.flags & HJ_FLAG_SQL_NULL_PROBE) ? kNullRoute : kNullAsValue);
 
@@ -1108,9 +1136,9 @@ int run_join_streamed(hj_ctx* ctx, const hj_relation* build, const hj_relation* 
   hj_relation rel[2];
   // stage slice 0 while the build side is copied in and partitioned
   rel[0] = slice_rel(0);
-  HJ_TRY(prepare_relation(ctx, &rel[0], 1, tile1<K>(), ctx->copy_in, &pp[0]));
+  HJ_TRY(prepare_relation(ctx, &rel[0], 1, tile_rows<K, false>(ctx, bits2, 1), ctx->copy_in, &pp[0]));
   HJ_CUDA(ctx, cudaEventRecord(ctx->ev_in[0], ctx->copy_in));
-  HJ_TRY(prepare_relation(ctx, build, 0, tile1<K>(), st, &pb));
+  HJ_TRY(prepare_relation(ctx, build, 0, tile_rows<K, false>(ctx, bits2, 0), st, &pb));
   HJ_TRY((stage_alloc<K, false>(ctx, pb, 0, radix_bits, bits2, &sb)));
   HJ_TRY(stage_hist<K>(ctx, pb, 0, radix_bits, bits2, kNullDrop, sb, st, &nl));
   HJ_TRY((stage_pass1<K, false>(ctx, pb, 0, radix_bits, bits2, kNullDrop, sb, st, &nl)));
@@ -1127,7 +1155,7 @@ int run_join_streamed(hj_ctx* ctx, const hj_relation* build, const hj_relation* 
       if (i >= 1) HJ_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_in, ctx->ev_done[nxt], 0));
       rel[nxt] = slice_rel(i + 1);
       pp[nxt] = PreparedRel{};
-      HJ_TRY(prepare_relation(ctx, &rel[nxt], 1 + nxt, tile1<K>(), ctx->copy_in, &pp[nxt]));
+      HJ_TRY(prepare_relation(ctx, &rel[nxt], 1 + nxt, tile_rows<K, false>(ctx, bits2, 1 + nxt), ctx->copy_in, &pp[nxt]));
       HJ_CUDA(ctx, cudaEventRecord(ctx->ev_in[nxt], ctx->copy_in));
     }
     HJ_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_in[cur], 0));

@@ -19,6 +19,12 @@
 #ifndef HJ_TUNE_P1_PREFETCH
 #define HJ_TUNE_P1_PREFETCH 0
 #endif
+#ifndef HJ_TUNE_P2_STEPS
+#define HJ_TUNE_P2_STEPS 0
+#endif
+#ifndef HJ_TUNE_P2_OWN_SHIFT
+#define HJ_TUNE_P2_OWN_SHIFT 5  // s_own[k] = fragment holding flat index k << shift
+#endif
 
 namespace hj {
 
@@ -182,7 +188,8 @@ __global__ void __launch_bounds__(NT, MINB) k_scatter2f(const Tuple<K, false>* _
   T* stage = reinterpret_cast<T*>(s_raw);
   __shared__ uint32_t s_cnt[kMaxDigits], s_loff[kMaxDigits], s_delta[kMaxDigits];
   __shared__ uint32_t s_pre[NT + 1], s_dsrc[NT];
-  __shared__ uint8_t s_own[TILE / 32];
+  constexpr int OS = HJ_TUNE_P2_OWN_SHIFT;
+  __shared__ uint8_t s_own[TILE >> OS];
   __shared__ uint32_t scratch[33];
 
   const uint32_t P = 1u << radix_bits, F1 = P >> bits2, FS = F1 + 2u;
@@ -212,7 +219,7 @@ __global__ void __launch_bounds__(NT, MINB) k_scatter2f(const Tuple<K, false>* _
     for (uint32_t d = threadIdx.x; d < F2; d += NT) s_cnt[d] = 0;
     if (len) {
       const uint32_t a = max(pre, lo), b = min(pre + len, lo + TILE);
-      for (uint32_t k = (a - lo + 31u) >> 5; lo + (k << 5) < b; ++k) s_own[k] = static_cast<uint8_t>(threadIdx.x);
+      for (uint32_t k = (a - lo + (1u << OS) - 1u) >> OS; lo + (k << OS) < b; ++k) s_own[k] = static_cast<uint8_t>(threadIdx.x);
     }
     __syncthreads();  // also orders the previous batch's copy-out before this batch's staging
 
@@ -223,7 +230,12 @@ __global__ void __launch_bounds__(NT, MINB) k_scatter2f(const Tuple<K, false>* _
       const uint32_t i = j * NT + threadIdx.x;
       if (i < n_in) {
         const uint32_t fi = lo + i;
-        uint32_t s = s_own[i >> 5];
+        uint32_t s = s_own[i >> OS];
+        // fragments hold ~32 tuples, so the owner of flat index 32k is a step or two behind. HJ_TUNE_P2_STEPS predicated
+        // steps before the loop were measured SLOWER (C2 pass 2: 5.21 -> 5.34 ms with 2 steps) although the divergent loop
+        // is 16 % of the kernel's instructions: the steps add two dependent shared-memory loads to every lane
+#pragma unroll
+        for (int step = 0; step < HJ_TUNE_P2_STEPS; ++step) s += fi >= s_pre[s + 1] ? 1u : 0u;
         while (fi >= s_pre[s + 1]) ++s;
         tup[j] = ld_stream(in + static_cast<uint32_t>(s_dsrc[s] + fi));
       }

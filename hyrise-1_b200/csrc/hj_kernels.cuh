@@ -728,16 +728,51 @@ __device__ __forceinline__ uint32_t table_insert(K* keys, uint32_t ns_mask, K ke
   }
 }
 
-// slot of `key` or NS+1 if absent (read-only; slot NS+1 of w is a zero pad)
+// Linear probing starts at a 16-byte aligned slot (the low kBucketShift<K> bits of the start are zero), so that a lookup
+// tests a whole 16-byte bucket (4 int32 / 2 int64 keys) per shared-memory load: with a load factor <= 0.75 almost every
+// probe row is answered by its first bucket and the lanes of a warp stay together (with one-slot steps a warp made as
+// many loop trips as the longest cluster walk among its 32 lanes: 2.8 extra trips per row on C2, ncu source counters in
+// profiles/r01_ncu_reentry_c2_full_summary.md).
+#ifndef HJ_TUNE_BUCKET_FIND
+#define HJ_TUNE_BUCKET_FIND 1
+#endif
+template <typename K> constexpr int kBucketShift = HJ_TUNE_BUCKET_FIND ? (sizeof(K) == 4 ? 2 : 1) : 0;
+template <typename K>
+__device__ __forceinline__ uint32_t table_start(uint32_t hash_above_radix, uint32_t ns_mask) {
+  return (hash_above_radix << kBucketShift<K>) & ns_mask;
+}
+
+// slot of `key` or NS+1 if absent (read-only; slot NS+1 of w is a zero pad). `slot` comes from table_start().
 template <typename K, int NS>
 __device__ __forceinline__ uint32_t table_find(const K* keys, uint32_t ns_mask, K key, uint32_t slot) {
   if (key == KeyTraits<K>::kEmpty) return NS;
+#if HJ_TUNE_BUCKET_FIND
+  // a key sits before the first empty slot of its probe sequence (insertions claim the first empty slot, nothing is
+  // ever removed), so "no match in this bucket and an empty slot in it" means absent
+  constexpr K E = KeyTraits<K>::kEmpty;
+  for (;;) {
+    if constexpr (sizeof(K) == 4) {
+      const int4 q = *reinterpret_cast<const int4*>(keys + slot);
+      const bool m0 = q.x == key, m1 = q.y == key, m2 = q.z == key, m3 = q.w == key;
+      if (m0 | m1 | m2 | m3) return slot + (m0 ? 0u : m1 ? 1u : m2 ? 2u : 3u);
+      if ((q.x == E) | (q.y == E) | (q.z == E) | (q.w == E)) return NS + 1;
+      slot = (slot + 4) & ns_mask;
+    } else {
+      const longlong2 q = *reinterpret_cast<const longlong2*>(keys + slot);
+      const bool m0 = q.x == key, m1 = q.y == key;
+      if (m0 | m1) return slot + (m0 ? 0u : 1u);
+      if ((q.x == E) | (q.y == E)) return NS + 1;
+      slot = (slot + 2) & ns_mask;
+    }
+  }
+#else
   for (;;) {
     const K cur = keys[slot];
     if (cur == key) return slot;
     if (cur == KeyTraits<K>::kEmpty) return NS + 1;
     slot = (slot + 1) & ns_mask;
   }
+#endif
 }
 
 // How a tuple becomes a RowID when a result row is emitted:
@@ -908,7 +943,7 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K, PAY> a)
         const uint32_t i = (r0 + u) * NT + threadIdx.x;
         uint32_t slot = NS + 1;
         if (i < it.b_cnt) {
-          slot = table_insert<K, NS>(s_keys, ns_mask, bk[u], (hash_key(bk[u]) >> radix_bits) & ns_mask);
+          slot = table_insert<K, NS>(s_keys, ns_mask, bk[u], table_start<K>(hash_key(bk[u]) >> radix_bits, ns_mask));
           atomicAdd(&s_w[slot], 1u);
         }
         if ((u & 1) == 0) bslot[(r0 + u) / 2] = slot; else bslot[(r0 + u) / 2] |= slot << 16;
@@ -979,7 +1014,7 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K, PAY> a)
         ppad[j] = RM == kRidPayload ? tuple_hi(nxt[j]) : 0u;
         if (act) {
           const K key = nxt[j].key;
-          const uint32_t slot = table_find<K, NS>(s_keys, ns_mask, key, (hash_key(key) >> radix_bits) & ns_mask);
+          const uint32_t slot = table_find<K, NS>(s_keys, ns_mask, key, table_start<K>(hash_key(key) >> radix_bits, ns_mask));
           pw[j] = s_w[slot];
         }
         const uint32_t cnt = pw[j] & 0xFFFFu;

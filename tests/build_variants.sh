@@ -16,3 +16,8 @@ build probe_v8 -DHJ_TUNE_PROBE_V=8 &
 build p1_v4_t2048 -DHJ_TUNE_ITEMS1_32=8 -DHJ_TUNE_P1_VIRTUAL=4 &
 build p1_prefetch -DHJ_TUNE_P1_PREFETCH=1 &
 wait
+build p1_v2_t2048 -DHJ_TUNE_ITEMS1_32=8 -DHJ_TUNE_P1_VIRTUAL=2 &
+build p1_v4_t2048_pf -DHJ_TUNE_ITEMS1_32=8 -DHJ_TUNE_P1_VIRTUAL=4 -DHJ_TUNE_P1_PREFETCH=1 &
+build old_find_steps -DHJ_TUNE_BUCKET_FIND=0 -DHJ_TUNE_P2_STEPS=0 &
+build p2_512x8_mb3_pf -DHJ_TUNE_P2_THREADS=512 -DHJ_TUNE_P2_ITEMS32=8 -DHJ_TUNE_P2_ITEMS64=4 -DHJ_TUNE_P2_MINBLOCKS=3 -DHJ_TUNE_P1_PREFETCH=1 &
+wait

@@ -76,11 +76,13 @@ for name, bits in runs:
                 t = j.timings()
                 if best is None or t["total"] < best["total"]:
                     best = t
+            rec.update(bits=int(info.radix_bits), **{k: round(v, 3) for k, v in best.items() if isinstance(v, float)})
             _, pp, n = j.result_device()
+            rec.update(rows=int(n))
             ok = n == want_rows
             if ok and n:
                 class _W:  # the device PosList as a torch tensor (cuda array interface; int32 view: ids < 2^31)
-                    __cuda_array_interface__ = {"shape": (n, 2), "typestr": "<i4", "data": (pp, True), "version": 2}
+                    __cuda_array_interface__ = {"shape": (n, 2), "typestr": "<i4", "data": (pp, False), "version": 2}
                 rid = torch.as_tensor(_W(), device=dev)
                 got = 0
                 for lo in range(0, n, 1 << 28):
@@ -88,8 +90,7 @@ for name, bits in runs:
                     got += int((part[:, 0].to(torch.int64) * bench.CHUNK + part[:, 1].to(torch.int64)).sum())
                 ok = got == want_sum
                 del rid, part
-            rec.update(ok=bool(ok), rows=int(n), bits=int(info.radix_bits),
-                       **{k: round(v, 3) for k, v in best.items() if isinstance(v, float)})
+            rec.update(ok=bool(ok))
             j.close()
             torch.cuda.empty_cache()
         except Exception as e:  # a variant that fails must not stop the sweep
