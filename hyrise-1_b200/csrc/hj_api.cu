@@ -72,12 +72,18 @@ template <> struct Cfg<int64_t> {
 constexpr int kScatterThreads = 256;
 constexpr int kHistThreads = 1024;        // K1: one physical CTA per SM ...
 constexpr int kHistVirtual = 4;           // ... hosting 4 virtual CTAs of 256 threads (one wave of all 4 x #SM tile owners)
-constexpr int kJoinThreads = 1024;
+#ifndef HJ_TUNE_JOIN_THREADS
+#define HJ_TUNE_JOIN_THREADS 1024
+#endif
+#ifndef HJ_TUNE_MAX_CHUNK_SHIFT
+#define HJ_TUNE_MAX_CHUNK_SHIFT 14
+#endif
+constexpr int kJoinThreads = HJ_TUNE_JOIN_THREADS;
 constexpr int kProbeV = HJ_TUNE_PROBE_V;
 constexpr uint32_t kProbeSlice = 128 * 1024;
 constexpr int kSinglePassMaxBits = 8;
 constexpr uint64_t kMinSliceRows = 32u << 20;  // streamed join: probe slices of at least 32 Mi rows
-constexpr int kMinChunkShift = 8, kMaxChunkShift = 14;  // result chunks of 256 .. 16 Ki rows
+constexpr int kMinChunkShift = 8, kMaxChunkShift = HJ_TUNE_MAX_CHUNK_SHIFT;  // result chunks of 256 .. 16 Ki rows
 constexpr int kVirtualCtasPerSm = 4;       // K1 / pass 1 tile ownership: G = min(n_tiles, 4 * SMs) virtual CTAs
 template <typename K> constexpr int tile1() { return kScatterThreads * Cfg<K>::kItems1; }
 template <typename K> constexpr int tile2() { return kScatterThreads * Cfg<K>::kItems2; }
@@ -336,6 +342,7 @@ int prepare_relation(hj_ctx* ctx, const hj_relation* r, int side, uint32_t tile,
     }
     d.key_type = s.key_type;
     d.attr_width = s.attr_width;
+    d.pad1 = d.kind == HJ_SEG_DICT ? s.dict_n : 0u;  // dictionary entries (k_part1 prefetches the next chunk's dictionary)
     row_begin[i] = rows;
     if (s.key_type == HJ_KEY_INT64) pr.has_int64 = true;
     if (s.kind == HJ_SEG_DICT) {

@@ -19,11 +19,14 @@
 #ifndef HJ_TUNE_P1_PREFETCH
 #define HJ_TUNE_P1_PREFETCH 0
 #endif
+#ifndef HJ_TUNE_P1_DICT_PREFETCH
+#define HJ_TUNE_P1_DICT_PREFETCH 0
+#endif
 #ifndef HJ_TUNE_P2_STEPS
-#define HJ_TUNE_P2_STEPS 0
+#define HJ_TUNE_P2_STEPS 1
 #endif
 #ifndef HJ_TUNE_P2_OWN_SHIFT
-#define HJ_TUNE_P2_OWN_SHIFT 5  // s_own[k] = fragment holding flat index k << shift
+#define HJ_TUNE_P2_OWN_SHIFT 3  // s_own[k] = fragment holding flat index k << shift
 #endif
 
 namespace hj {
@@ -60,8 +63,26 @@ __global__ void __launch_bounds__(NT) k_part1(RelMeta rel, Tuple<K, false>* __re
   __syncthreads();
 
   for (uint32_t tile = c; tile < rel.n_tiles; tile += G) {
-    const DevSegment s = rel.segs[__ldg(rel.tile_seg + tile)];
+    const uint32_t seg_idx = __ldg(rel.tile_seg + tile);
+    const DevSegment s = rel.segs[seg_idx];
     const uint32_t r0 = (tile - s.tile_begin) * TILE;
+#if HJ_TUNE_P1_DICT_PREFETCH
+    // A chunk's dictionary is first touched by that chunk's own gathers: random 32-byte DRAM reads that every warp of
+    // the wave waits for. The tiles of chunk c therefore pull the dictionary of chunk c+1 into L2 with coalesced
+    // prefetches, one slice per tile, a wave ahead of its first use.
+    if (seg_idx + 1 < rel.n_segs) {
+      const DevSegment* nx = rel.segs + seg_idx + 1;
+      const uint32_t dict_n = nx->pad1;  // 0 unless the chunk is dictionary-encoded
+      if (dict_n) {
+        const unsigned long long bytes = static_cast<unsigned long long>(dict_n) * (nx->key_type == 0 ? 4u : 8u);
+        const uint32_t nt = (s.n_rows + TILE - 1) / TILE, t = tile - s.tile_begin;
+        const unsigned long long lo = (bytes * t / nt) & ~127ull, hi = bytes * (t + 1) / nt;
+        const char* base = static_cast<const char*>(nx->values);
+        for (unsigned long long off = lo + vt * 128ull; off < hi; off += VT * 128ull)
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(base + off));
+      }
+    }
+#endif
     const uint32_t cnt = min(static_cast<uint32_t>(TILE), s.n_rows - r0);
     for (uint32_t d = vt; d <= F1; d += VT) s_cnt[v][d] = 0;
     vbar(v, VT);  // also orders the previous tile's copy-out before this tile's staging

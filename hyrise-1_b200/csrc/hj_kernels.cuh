@@ -733,8 +733,17 @@ __device__ __forceinline__ uint32_t table_insert(K* keys, uint32_t ns_mask, K ke
 // probe row is answered by its first bucket and the lanes of a warp stay together (with one-slot steps a warp made as
 // many loop trips as the longest cluster walk among its 32 lanes: 2.8 extra trips per row on C2, ncu source counters in
 // profiles/r01_ncu_reentry_c2_full_summary.md).
+#ifndef HJ_TUNE_OUT_CS
+#define HJ_TUNE_OUT_CS 0  // 1: result rows stored with st.global.cs (evict-first)
+#endif
+#ifndef HJ_TUNE_FIND_ILP
+#define HJ_TUNE_FIND_ILP 1  // 1: first-bucket lookups of a warp's V rows in straight-line code (needs HJ_TUNE_BUCKET_FIND)
+#endif
 #ifndef HJ_TUNE_BUCKET_FIND
 #define HJ_TUNE_BUCKET_FIND 1
+#endif
+#if HJ_TUNE_FIND_ILP && !HJ_TUNE_BUCKET_FIND
+#error "HJ_TUNE_FIND_ILP needs HJ_TUNE_BUCKET_FIND"
 #endif
 template <typename K> constexpr int kBucketShift = HJ_TUNE_BUCKET_FIND ? (sizeof(K) == 4 ? 2 : 1) : 0;
 template <typename K>
@@ -775,6 +784,27 @@ __device__ __forceinline__ uint32_t table_find(const K* keys, uint32_t ns_mask, 
 #endif
 }
 
+// First bucket only: the slot of `key`, NS + 1 if the bucket proves it absent, kFindPending if the search must go on.
+constexpr uint32_t kFindPending = 0xFFFFFFFFu;
+template <typename K> constexpr uint32_t kBucketKeys = 16 / sizeof(K);
+template <typename K, int NS>
+__device__ __forceinline__ uint32_t table_find_first(const K* keys, K key, uint32_t slot) {
+  constexpr K E = KeyTraits<K>::kEmpty;
+  uint32_t r;
+  if constexpr (sizeof(K) == 4) {
+    const int4 q = *reinterpret_cast<const int4*>(keys + slot);
+    const bool m0 = q.x == key, m1 = q.y == key, m2 = q.z == key, m3 = q.w == key;
+    const bool e = (q.x == E) | (q.y == E) | (q.z == E) | (q.w == E);
+    r = (m0 | m1 | m2 | m3) ? slot + (m0 ? 0u : m1 ? 1u : m2 ? 2u : 3u) : (e ? NS + 1u : kFindPending);
+  } else {
+    const longlong2 q = *reinterpret_cast<const longlong2*>(keys + slot);
+    const bool m0 = q.x == key, m1 = q.y == key;
+    const bool e = (q.x == E) | (q.y == E);
+    r = (m0 | m1) ? slot + (m0 ? 0u : 1u) : (e ? NS + 1u : kFindPending);
+  }
+  return key == E ? static_cast<uint32_t>(NS) : r;
+}
+
 // How a tuple becomes a RowID when a result row is emitted:
 //   kRidGeneric  position -> RowID through the relation's chunk table (make_rowid)
 //   kRidFast     both relations have power-of-two chunks and identity chunk ids: shift/mask
@@ -811,8 +841,13 @@ __device__ __forceinline__ void emit_tile(const JoinArgs<K, PAY>& a, const uint3
   uint64_t* op = a.out_probe + (CONTIG ? base0 : 0ull);
   auto put = [&](unsigned long long e, uint64_t brid, uint64_t prid) {
     if (CONTIG) {
+#if HJ_TUNE_OUT_CS
+      if (!one_side) __stcs(reinterpret_cast<unsigned long long*>(ob + e), brid);
+      __stcs(reinterpret_cast<unsigned long long*>(op + e), prid);
+#else
       if (!one_side) ob[e] = brid;
       op[e] = prid;
+#endif
     } else {
       const unsigned long long pos = out_pos(base0, base1, first, e);
       if (pos < a.capacity) {
@@ -1006,17 +1041,32 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K, PAY> a)
       uint32_t pw[V], pidx[V], ppad[V], outc[V], ex[V];
       const uint32_t row0 = base + lane;
       bool any_multi = false;
+#if HJ_TUNE_FIND_ILP
+      // first buckets of all V rows in straight-line code (the loads are independent and can be in flight together);
+      // only a row whose first bucket is full of other keys falls back to the loop
+      uint32_t fstart[V], fslot[V];
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        fstart[j] = table_start<K>(hash_key(nxt[j].key) >> radix_bits, ns_mask);
+        fslot[j] = table_find_first<K, NS>(s_keys, nxt[j].key, fstart[j]);
+      }
+#endif
 #pragma unroll
       for (int j = 0; j < V; ++j) {
         const bool act = row0 + j * 32 < it.p_cnt;
         pw[j] = 0;
         pidx[j] = nxt[j].idx;
         ppad[j] = RM == kRidPayload ? tuple_hi(nxt[j]) : 0u;
+#if HJ_TUNE_FIND_ILP
+        if (act) pw[j] = s_w[fslot[j] != kFindPending ? fslot[j]
+                                 : table_find<K, NS>(s_keys, ns_mask, nxt[j].key, (fstart[j] + kBucketKeys<K>) & ns_mask)];
+#else
         if (act) {
           const K key = nxt[j].key;
           const uint32_t slot = table_find<K, NS>(s_keys, ns_mask, key, table_start<K>(hash_key(key) >> radix_bits, ns_mask));
           pw[j] = s_w[slot];
         }
+#endif
         const uint32_t cnt = pw[j] & 0xFFFFu;
         uint32_t o;
         if (CLS == kClsInner) o = cnt;
