@@ -34,7 +34,9 @@ WORKLOADS = {
            "C2 synthetic 1:N int32 inner equi-join, 100M build x 1B probe, uniform keys, dictionary-encoded"),
     "c3": (200_000_000, 2_000_000_000, "int64", "value",
            "C3 synthetic int64 join, Zipf(1.0) build keys, 200M x 2B, ValueColumns"),
-    "c1": (1_500_000, 6_001_215, "int32", "dict", "C1-shaped: 1.5M unique build x 6M probe int32 (TPC-H SF1 sizes)"),
+    "c1": (1_500_000, 6_001_215, "int32", "dict",
+           "C1 TPC-H SF1 lineitem x orders on l_orderkey = o_orderkey (dbgen keys when oracle/_ref/libref_dbgen.so is present, "
+           "else 1.5M unique x 6M uniform), dictionary-encoded"),
 }
 
 
@@ -89,6 +91,17 @@ def gen_device_workload(name, scale, device, seed, rank=0, world=1):
                 out.append((cid, k.contiguous(), None))
         return out
 
+    if name == "c1" and world == 1 and scale == 1.0:
+        # C1 on the key columns the reference's own dbgen generates at SF1 (oracle/_ref/libref_dbgen.so, test
+        # infrastructure built where /root/reference exists; it only GENERATES the input here). Absent: C1-shaped synthetic.
+        import dbgen_binding as db
+        if db.available():
+            k = db.tpch_keys(1.0)
+            okeys = torch.from_numpy(k["o_orderkey"]).to(device)
+            lkeys = torch.from_numpy(k["l_orderkey"]).to(device)
+            return dict(build=chunks_of(lambda s, m: okeys[s:s + m], len(okeys)),
+                        probe=chunks_of(lambda s, m: lkeys[s:s + m], len(lkeys)), n_build=len(okeys), n_probe=len(lkeys),
+                        dtype=dtype, encoding=encoding, source="dbgen (reference's tpch-dbgen, SF1: orders x lineitem keys)")
     build = chunks_of(lambda s, m: build_keys[s:s + m], n_build)
     probe = chunks_of(lambda s, m: torch.randint(1, domain + 1, (m,), device=device, generator=g, dtype=torch.int64).to(tdt),
                       n_probe)
@@ -399,7 +412,7 @@ def main():
     if rank == 0:
         line = {"metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps,
                 "warmup": W, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": dtype, "data": "synthetic",
+                "vs_baseline": None, "dtype": dtype, "data": data.get("source", "synthetic"),
                 "config": {"workload": desc + (f"; {world} ranks each hold that many rows of one global join (hash exchange over NCCL)"
                                                if world > 1 else ""),
                            "scale": args.scale, "n_build": nb * world, "n_probe": npr * world,

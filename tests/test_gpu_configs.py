@@ -63,6 +63,27 @@ def test_c1_tpch_sf1_lineitem_orders(join, encoding):
     assert info.n_rows == len(lkeys)  # every lineitem has exactly one order
 
 
+@pytest.fixture(scope="module")
+def dbgen_sf1():
+    import dbgen_binding as db
+    if not db.available():
+        pytest.skip("oracle/_ref/libref_dbgen.so not built")
+    return db.tpch_keys(1.0)
+
+
+@pytest.mark.parametrize("encoding", ["value", "dict"])
+def test_c1_tpch_sf1_dbgen_keys(join, dbgen_sf1, encoding):
+    """C1 on the key columns the reference's own dbgen generates at SF1 (oracle/_ref/libref_dbgen.so = third_party/tpch-dbgen
+    compiled in place and driven like tpch_db_generator.cpp:203-237; it travels to the GPU box as a built file):
+    1 500 000 orders x 6 001 215 lineitems, chunk size 100 000, bit-exact vs the oracle."""
+    k = dbgen_sf1
+    assert len(k["l_orderkey"]) == 6_001_215
+    build = wl.make_relation(k["o_orderkey"], 100_000, encoding)
+    probe = wl.make_relation(k["l_orderkey"], 100_000, encoding)
+    info = assert_same(join, build, probe, "Inner", f"C1 dbgen {encoding}")
+    assert info.n_rows == 6_001_215
+
+
 # ------------------------------------------------------------------------------------------------------------------ C3
 @pytest.mark.parametrize("mode", ["Inner", "Left", "Semi", "Anti"])
 def test_c3_zipf_int64_scaled(join, mode):
