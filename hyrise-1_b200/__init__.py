@@ -257,6 +257,35 @@ class HashJoin:
         self._check(self._l.hj_translate(self._ctx, rowids.ctypes.data, len(rowids), ptrs, sizes, n_chunks))
         return rowids
 
+    # ---- TableScan on the device -------------------------------------------------------------------
+    def scan(self, column, predicate, value=None, slot=0, dereference=False, stream=None):
+        """hj_scan: `column <predicate> value` (value None = NULL literal). Returns hj_scan_info; the PosLists stay on the
+        device in `slot`."""
+        if isinstance(predicate, str):
+            predicate = abi.PREDICATES[predicate]
+        info = abi.ScanInfo()
+        self._check(self._l.hj_scan(self._ctx, C.byref(column), predicate, 0 if value is None else int(value),
+                                    1 if value is None else 0, slot, abi.SCAN_DEREFERENCE if dereference else 0, stream,
+                                    C.byref(info)))
+        return info
+
+    def scan_fetch(self, slot=0):
+        """(pos (n, 2) uint32 [chunk_id, chunk_offset], chunk_begin (n_chunks + 1,) uint32) of the scan result in `slot`."""
+        _, _, n, n_chunks = self.scan_result_device(slot)
+        pos = np.empty((max(n, 1), 2), dtype=np.uint32)
+        begin = np.empty(n_chunks + 1, dtype=np.uint32)
+        self._check(self._l.hj_scan_fetch(self._ctx, slot, pos.ctypes.data, n, begin.ctypes.data))
+        return pos[:n], begin
+
+    def scan_result_device(self, slot=0):
+        """(pos device ptr, chunk_begin device ptr, n_rows, n_chunks) of the scan result in `slot`."""
+        p, b, n, c = C.c_void_p(), C.c_void_p(), C.c_uint64(), C.c_uint32()
+        self._check(self._l.hj_scan_result_device(self._ctx, slot, C.byref(p), C.byref(b), C.byref(n), C.byref(c)))
+        return p.value, b.value, n.value, c.value
+
+    def scan_release(self, slot=-1):
+        self._check(self._l.hj_scan_release(self._ctx, slot))
+
     def timings(self):
         t = abi.Timings()
         self._check(self._l.hj_get_timings(self._ctx, C.byref(t)))

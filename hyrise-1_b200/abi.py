@@ -56,6 +56,21 @@ class ResultInfo(C.Structure):
                 ("n_probe_passes", C.c_uint32), ("n_probe_slices", C.c_uint32)]
 
 
+class ScanInfo(C.Structure):
+    _fields_ = [("n_rows", C.c_uint64), ("n_chunks", C.c_uint32), ("n_nonempty_chunks", C.c_uint32)]
+
+
+# PredicateCondition, src/lib/types.hpp:166-179 of the reference
+PRED_EQUALS, PRED_NOT_EQUALS, PRED_LESS_THAN, PRED_LESS_THAN_EQUALS, PRED_GREATER_THAN, PRED_GREATER_THAN_EQUALS, \
+    PRED_BETWEEN, PRED_IN, PRED_LIKE, PRED_NOT_LIKE, PRED_IS_NULL, PRED_IS_NOT_NULL = range(12)
+PREDICATES = {"Equals": PRED_EQUALS, "NotEquals": PRED_NOT_EQUALS, "LessThan": PRED_LESS_THAN,
+              "LessThanEquals": PRED_LESS_THAN_EQUALS, "GreaterThan": PRED_GREATER_THAN,
+              "GreaterThanEquals": PRED_GREATER_THAN_EQUALS, "Between": PRED_BETWEEN, "In": PRED_IN, "Like": PRED_LIKE,
+              "NotLike": PRED_NOT_LIKE, "IsNull": PRED_IS_NULL, "IsNotNull": PRED_IS_NOT_NULL}
+SCAN_SLOTS = 4
+SCAN_DEREFERENCE = 0x1
+
+
 class Timings(C.Structure):
     _fields_ = [("ms", C.c_float * N_PHASES), ("bytes_h2d", C.c_uint64), ("bytes_d2h", C.c_uint64),
                 ("n_kernel_launches", C.c_uint32), ("reserved", C.c_uint32), ("bytes_nvlink_sent", C.c_uint64)]
@@ -78,6 +93,12 @@ SYMBOLS = {
                                C.c_uint32]),
     "hj_get_timings": (C.c_int, [C.c_void_p, C.POINTER(Timings)]),
     "hj_release_scratch": (C.c_int, [C.c_void_p]),
+    "hj_scan": (C.c_int, [C.c_void_p, C.POINTER(Relation), C.c_int, C.c_int64, C.c_int, C.c_int, C.c_uint32, C.c_void_p,
+                          C.POINTER(ScanInfo)]),
+    "hj_scan_result_device": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+                                        C.POINTER(C.c_uint64), C.POINTER(C.c_uint32)]),
+    "hj_scan_fetch": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_uint64, C.c_void_p]),
+    "hj_scan_release": (C.c_int, [C.c_void_p, C.c_int]),
     "hj_exchange_rank_of": (C.c_uint32, [C.c_int64, C.c_int, C.c_uint32]),
     "hj_comm_unique_id": (C.c_int, [C.POINTER(C.c_uint8)]),
     "hj_comm_init": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint8), C.c_int, C.c_int]),

@@ -11,6 +11,7 @@
 #include "hj.h"
 #include "hj_kernels.cuh"
 #include "hj_fused.cuh"
+#include "hj_scan.cuh"
 
 using namespace hj;
 
@@ -152,6 +153,12 @@ struct hj_ctx {
   std::vector<void*> xchg_graveyard;  // exported buffers that were outgrown; freed once no peer can have them mapped
   DevBuf xchg_hdl_dev;
   bool p2p_ok = false;
+  // TableScan (N4): scratch (freed by hj_release_scratch) and the result slots (owned by the scan's caller)
+  DevBuf scan_bounds, scan_mask, scan_tile_count, scan_tile_base, scan_ref_ptrs, scan_totals;
+  DevBuf scan_pos[HJ_SCAN_SLOTS], scan_chunk_begin[HJ_SCAN_SLOTS];
+  uint64_t scan_rows[HJ_SCAN_SLOTS] = {};
+  uint32_t scan_chunks[HJ_SCAN_SLOTS] = {};
+  bool scan_valid[HJ_SCAN_SLOTS] = {};
   const uint64_t* xchg_rowids[kSides] = {};  // set while hj_join_sharded runs its local join
   uint64_t xchg_bytes_sent[2] = {0, 0};
 
@@ -164,7 +171,7 @@ struct hj_ctx {
                       &xchg_send_keys[1], &xchg_send_rids[0], &xchg_send_rids[1], &xchg_send_nulls[0], &xchg_send_nulls[1],
                       &xchg_recv_keys[0], &xchg_recv_keys[1], &xchg_recv_rids[0], &xchg_recv_rids[1], &xchg_recv_nulls[0],
                       &xchg_recv_nulls[1], &xchg_recv_keys[2], &xchg_recv_rids[2], &xchg_recv_nulls[2], &acc_build, &acc_probe, &ref_arena[0], &ref_arena[1], &ref_out[0], &ref_out[1],
-                      &xchg_hdl_dev})
+                      &xchg_hdl_dev, &scan_bounds, &scan_mask, &scan_tile_count, &scan_tile_base, &scan_ref_ptrs, &scan_totals})
       all_bufs.push_back(b);
   }
 };
@@ -1231,6 +1238,78 @@ int check_ctx(hj_ctx* ctx) {
   return HJ_OK;
 }
 
+// ------------------------------------------------------------------------------------------------ TableScan (N4)
+
+constexpr size_t kPinnedScanTotals = 3616;  // two words inside the pinned readback area (behind kPinnedRefFlags)
+
+template <typename K>
+int run_scan(hj_ctx* ctx, const hj_relation* column, const hj_relation* original, int predicate, int64_t value, int slot,
+             uint32_t scan_flags, cudaStream_t st, hj_scan_info* info) {
+  PreparedRel pr;
+  HJ_TRY(prepare_relation(ctx, column, 1, kScanTile, st, &pr));
+  const uint32_t n_segs = pr.meta.n_segs, n_tiles = pr.meta.n_tiles;
+  HJ_TRY(ensure(ctx, ctx->scan_bounds, std::max<size_t>(1, n_segs) * 8));
+  HJ_TRY(ensure(ctx, ctx->scan_mask, std::max<size_t>(1, n_tiles) * kScanWordsPerTile * 4));
+  HJ_TRY(ensure(ctx, ctx->scan_tile_count, std::max<size_t>(1, n_tiles) * 4));
+  HJ_TRY(ensure(ctx, ctx->scan_tile_base, (size_t(n_tiles) + 1) * 4));
+  HJ_TRY(ensure(ctx, ctx->scan_totals, 8));
+  HJ_TRY(ensure(ctx, ctx->scan_chunk_begin[slot], (size_t(n_segs) + 1) * 4));
+  auto* bounds = static_cast<uint32_t*>(ctx->scan_bounds.p);
+  auto* mask = static_cast<uint32_t*>(ctx->scan_mask.p);
+  auto* tile_count = static_cast<uint32_t*>(ctx->scan_tile_count.p);
+  auto* tile_base = static_cast<uint32_t*>(ctx->scan_tile_base.p);
+  auto* totals = static_cast<uint32_t*>(ctx->scan_totals.p);
+  auto* chunk_begin = static_cast<uint32_t*>(ctx->scan_chunk_begin[slot].p);
+
+  // HJ_SCAN_DEREFERENCE: REFERENCE chunks emit their own PosList entries — the device address of every such chunk's PosList
+  const uint64_t* const* ref_ptrs = nullptr;
+  if (scan_flags & HJ_SCAN_DEREFERENCE) {
+    std::vector<const uint64_t*> ptrs(n_segs, nullptr);
+    bool any = false;
+    for (uint32_t i = 0; i < n_segs; ++i)
+      if (original->segs[i].kind == HJ_SEG_REFERENCE) {
+        ptrs[i] = static_cast<const uint64_t*>(original->segs[i].attr);
+        any = true;
+      }
+    if (any) {
+      HJ_TRY(ensure(ctx, ctx->scan_ref_ptrs, size_t(n_segs) * sizeof(void*)));
+      HJ_CUDA(ctx, cudaMemcpyAsync(ctx->scan_ref_ptrs.p, ptrs.data(), size_t(n_segs) * sizeof(void*), cudaMemcpyHostToDevice, st));
+      HJ_CUDA(ctx, cudaStreamSynchronize(st));  // `ptrs` is pageable and dies with this block
+      ref_ptrs = static_cast<const uint64_t* const*>(ctx->scan_ref_ptrs.p);
+    }
+  }
+
+  const uint32_t grid = std::max<uint32_t>(1, std::min<uint32_t>(n_tiles, uint32_t(ctx->n_sms) * 8));
+  if (n_segs) {
+    k_scan_bounds<<<(n_segs + 127) / 128, 128, 0, st>>>(pr.meta.segs, n_segs, static_cast<long long>(value), bounds);
+    HJ_LAUNCH_CHECK(ctx, "k_scan_bounds");
+  }
+  if (n_tiles) {
+    k_scan_mask<K><<<grid, kScanThreads, 0, st>>>(pr.meta, predicate, static_cast<K>(value), bounds, mask, tile_count);
+    HJ_LAUNCH_CHECK(ctx, "k_scan_mask");
+  }
+  k_scan_prefix<1024><<<1, 1024, 0, st>>>(tile_count, n_tiles, pr.meta.segs, n_segs, tile_base, chunk_begin, totals);
+  HJ_LAUNCH_CHECK(ctx, "k_scan_prefix");
+  auto* host_totals = reinterpret_cast<uint32_t*>(static_cast<char*>(ctx->pinned) + kPinnedScanTotals);
+  HJ_CUDA(ctx, cudaMemcpyAsync(host_totals, totals, 8, cudaMemcpyDeviceToHost, st));
+  HJ_CUDA(ctx, cudaStreamSynchronize(st));
+  const uint64_t n_rows = host_totals[0];
+  HJ_TRY(ensure(ctx, ctx->scan_pos[slot], std::max<uint64_t>(1, n_rows) * 8));
+  if (n_rows) {
+    k_scan_write<<<grid, kScanThreads, 0, st>>>(pr.meta, mask, tile_base, ref_ptrs, static_cast<uint64_t*>(ctx->scan_pos[slot].p));
+    HJ_LAUNCH_CHECK(ctx, "k_scan_write");
+    HJ_CUDA(ctx, cudaStreamSynchronize(st));
+  }
+  ctx->scan_rows[slot] = n_rows;
+  ctx->scan_chunks[slot] = n_segs;
+  ctx->scan_valid[slot] = true;
+  info->n_rows = n_rows;
+  info->n_chunks = n_segs;
+  info->n_nonempty_chunks = host_totals[1];
+  return HJ_OK;
+}
+
+
 }  // namespace
 
 // ============================================================================================================= C ABI
@@ -1308,6 +1387,7 @@ void hj_destroy(hj_ctx* ctx) {
   cudaSetDevice(ctx->device);
   hj_comm_release(ctx);
   hj_release_scratch(ctx);
+  hj_scan_release(ctx, -1);
   for (auto& ev : ctx->ev)
     if (ev) cudaEventDestroy(ev);
   for (auto* arr : {ctx->ev_in, ctx->ev_done, ctx->ev_out, ctx->ev_x})
@@ -1323,6 +1403,109 @@ void hj_destroy(hj_ctx* ctx) {
 const char* hj_last_error(const hj_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
 
 int hj_radix_bits(uint64_t n_build_rows, int key_type) { return radix_bits_for(n_build_rows, key_type); }
+
+// ------------------------------------------------------------------------------------------------ TableScan (N4)
+int hj_scan(hj_ctx* ctx, const hj_relation* column, int predicate, int64_t value, int value_is_null, int slot,
+            uint32_t scan_flags, void* cuda_stream, hj_scan_info* out_info) {
+  if (!ctx) return HJ_ERR_INVALID;
+  if (!out_info) return fail(ctx, HJ_ERR_INVALID, "out_info is NULL");
+  std::memset(out_info, 0, sizeof(*out_info));
+  if (slot < 0 || slot >= HJ_SCAN_SLOTS) return fail(ctx, HJ_ERR_INVALID, "scan slot %d outside 0..%d", slot, HJ_SCAN_SLOTS - 1);
+  ctx->scan_valid[slot] = false;
+  const bool null_test = predicate == HJ_PRED_IS_NULL || predicate == HJ_PRED_IS_NOT_NULL;
+  if (!null_test && (predicate < HJ_PRED_EQUALS || predicate > HJ_PRED_GREATER_THAN_EQUALS))
+    return fail(ctx, HJ_ERR_INVALID, "PredicateCondition %d is not a single-column comparison (Between/In/Like are refused, as "
+                "SingleColumnTableScanImpl fails on them)", predicate);
+  HJ_TRY(validate_relation(ctx, column, "scan"));
+  bool wide = false;
+  for (uint32_t i = 0; i < column->n_segs; ++i) {
+    const hj_segment& sg = column->segs[i];
+    if (sg.key_type == HJ_KEY_FLOAT || sg.key_type == HJ_KEY_DOUBLE)
+      return fail(ctx, HJ_ERR_INVALID, "scan chunk %u: float/double columns are not scanned on the device yet", i);
+    wide = wide || sg.key_type == HJ_KEY_INT64;
+    if (sg.kind == HJ_SEG_REFERENCE && (scan_flags & HJ_SCAN_DEREFERENCE) && column->location != HJ_LOC_DEVICE)
+      return fail(ctx, HJ_ERR_INVALID, "scan chunk %u: HJ_SCAN_DEREFERENCE needs a device-resident relation (the kernel reads the "
+                  "chunk's PosList where it lies)", i);
+  }
+  if (!null_test && !value_is_null && !wide && (value < INT32_MIN || value > INT32_MAX))
+    return fail(ctx, HJ_ERR_INVALID, "literal %lld does not fit the int32 column (the reference's type_cast fails on it too)",
+                (long long)value);
+  HJ_TRY(check_ctx(ctx));
+  cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
+  if (!null_test && value_is_null) {
+    // comparing with NULL yields NULL: always the empty PosList (single_column_table_scan_impl.cpp:25-34)
+    HJ_TRY(ensure(ctx, ctx->scan_chunk_begin[slot], (size_t(column->n_segs) + 1) * 4));
+    HJ_TRY(ensure(ctx, ctx->scan_pos[slot], 8));
+    HJ_CUDA(ctx, cudaMemsetAsync(ctx->scan_chunk_begin[slot].p, 0, (size_t(column->n_segs) + 1) * 4, st));
+    HJ_CUDA(ctx, cudaStreamSynchronize(st));
+    ctx->scan_rows[slot] = 0;
+    ctx->scan_chunks[slot] = column->n_segs;
+    ctx->scan_valid[slot] = true;
+    out_info->n_chunks = column->n_segs;
+    return HJ_OK;
+  }
+  // REFERENCE / FOR / RLE / SimdBp128 chunks become GATHERED / VALUE chunks on the device first (k_gather_refs)
+  ctx->ref_h2d_bytes = 0;
+  std::memset(static_cast<char*>(ctx->pinned) + kPinnedRefFlags, 0, 8);
+  RefRewrite rw;
+  HJ_TRY(gather_references(ctx, column, 1, st, &rw, wide ? HJ_KEY_INT64 : HJ_KEY_INT32));
+  const hj_relation* rel = rw.any ? &rw.rel : column;
+  HJ_TRY(wide ? run_scan<int64_t>(ctx, rel, column, predicate, value, slot, scan_flags, st, out_info)
+              : run_scan<int32_t>(ctx, rel, column, predicate, value, slot, scan_flags, st, out_info));
+  if (rw.any) {
+    const auto* flag = reinterpret_cast<const uint32_t*>(static_cast<const char*>(ctx->pinned) + kPinnedRefFlags);
+    if (flag[0] || flag[1]) {
+      ctx->scan_valid[slot] = false;
+      return fail(ctx, HJ_ERR_INVALID, "scan: a PosList entry points outside the referenced table");
+    }
+  }
+  return HJ_OK;
+}
+
+int hj_scan_result_device(hj_ctx* ctx, int slot, const hj_row_id** pos, const uint32_t** chunk_begin, uint64_t* n_rows,
+                          uint32_t* n_chunks) {
+  if (!ctx) return HJ_ERR_INVALID;
+  if (slot < 0 || slot >= HJ_SCAN_SLOTS || !ctx->scan_valid[slot]) return fail(ctx, HJ_ERR_STATE, "no scan result in slot %d", slot);
+  if (pos) *pos = static_cast<const hj_row_id*>(ctx->scan_pos[slot].p);
+  if (chunk_begin) *chunk_begin = static_cast<const uint32_t*>(ctx->scan_chunk_begin[slot].p);
+  if (n_rows) *n_rows = ctx->scan_rows[slot];
+  if (n_chunks) *n_chunks = ctx->scan_chunks[slot];
+  return HJ_OK;
+}
+
+int hj_scan_fetch(hj_ctx* ctx, int slot, hj_row_id* pos, uint64_t capacity_rows, uint32_t* chunk_begin) {
+  if (!ctx) return HJ_ERR_INVALID;
+  if (slot < 0 || slot >= HJ_SCAN_SLOTS || !ctx->scan_valid[slot]) return fail(ctx, HJ_ERR_STATE, "no scan result in slot %d", slot);
+  const uint64_t n = ctx->scan_rows[slot];
+  if (capacity_rows < n) return fail(ctx, HJ_ERR_CAPACITY, "capacity %llu < %llu scan result rows", (unsigned long long)capacity_rows,
+                                     (unsigned long long)n);
+  if (n && !pos) return fail(ctx, HJ_ERR_INVALID, "NULL output buffer");
+  HJ_TRY(check_ctx(ctx));
+  cudaStream_t st = ctx->own_stream;
+  if (n) HJ_CUDA(ctx, cudaMemcpyAsync(pos, ctx->scan_pos[slot].p, n * 8, cudaMemcpyDeviceToHost, st));
+  if (chunk_begin)
+    HJ_CUDA(ctx, cudaMemcpyAsync(chunk_begin, ctx->scan_chunk_begin[slot].p, (size_t(ctx->scan_chunks[slot]) + 1) * 4,
+                                 cudaMemcpyDeviceToHost, st));
+  HJ_CUDA(ctx, cudaStreamSynchronize(st));
+  return HJ_OK;
+}
+
+int hj_scan_release(hj_ctx* ctx, int slot) {
+  if (!ctx) return HJ_ERR_INVALID;
+  if (slot >= HJ_SCAN_SLOTS) return fail(ctx, HJ_ERR_INVALID, "scan slot %d outside 0..%d", slot, HJ_SCAN_SLOTS - 1);
+  if (check_ctx(ctx) != HJ_OK) return HJ_ERR_INVALID;
+  for (int i = 0; i < HJ_SCAN_SLOTS; ++i) {
+    if (slot >= 0 && i != slot) continue;
+    for (DevBuf* b : {&ctx->scan_pos[i], &ctx->scan_chunk_begin[i]}) {
+      if (b->p) cudaFree(b->p);
+      b->p = nullptr;
+      b->cap = 0;
+    }
+    ctx->scan_valid[i] = false;
+    ctx->scan_rows[i] = 0;
+  }
+  return HJ_OK;
+}
 
 int join_dispatch(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, int mode, cudaStream_t st,
                   hj_result_info* out_info, bool wide, bool bound);

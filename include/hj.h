@@ -275,6 +275,67 @@ int hj_get_timings(const hj_ctx* ctx, hj_timings* out);
 /* Frees cached device scratch (the context stays usable). JoinHash::_on_cleanup, join_hash.cpp:89. */
 int hj_release_scratch(hj_ctx* ctx);
 
+/* ---- TableScan on the device --------------------------------------------- */
+/* Replaces the single-column-vs-literal scan of the reference — TableScan::_on_execute
+ * (src/lib/operators/table_scan.cpp:84-171) with SingleColumnTableScanImpl
+ * (operators/table_scan/single_column_table_scan_impl.cpp:23-133) and IsNullTableScanImpl
+ * (is_null_table_scan_impl.cpp) — for integer columns, so that a join input filtered by a scan never
+ * leaves the GPU: the scan's PosLists stay in device memory and are handed to hj_join as
+ * HJ_SEG_REFERENCE segments of a device-resident relation.
+ * Values are the reference's PredicateCondition (src/lib/types.hpp:166-179). */
+enum hj_predicate {
+  HJ_PRED_EQUALS = 0,
+  HJ_PRED_NOT_EQUALS = 1,
+  HJ_PRED_LESS_THAN = 2,
+  HJ_PRED_LESS_THAN_EQUALS = 3,
+  HJ_PRED_GREATER_THAN = 4,
+  HJ_PRED_GREATER_THAN_EQUALS = 5,
+  HJ_PRED_BETWEEN = 6,  /* refused: the reference's single-column scan fails on it too (table_scan_test.cpp:236) */
+  HJ_PRED_IN = 7,       /* refused */
+  HJ_PRED_LIKE = 8,     /* refused (string columns) */
+  HJ_PRED_NOT_LIKE = 9, /* refused */
+  HJ_PRED_IS_NULL = 10,
+  HJ_PRED_IS_NOT_NULL = 11
+};
+
+#define HJ_SCAN_SLOTS 4 /* results a context keeps at a time (e.g. the two filtered inputs of a join) */
+#define HJ_SCAN_DEREFERENCE 0x1u /* hj_scan scan_flags: REFERENCE chunks emit pos_list[offset], not (chunk_id, offset) */
+
+typedef struct hj_scan_info {
+  uint64_t n_rows;            /* matching rows over all chunks                                  */
+  uint32_t n_chunks;          /* = column->n_segs                                               */
+  uint32_t n_nonempty_chunks; /* chunks with at least one match (the reference drops the others) */
+} hj_scan_info;
+
+/* Scans one integer key column (VALUE / DICT / GATHERED / FOR / RLE chunks, host or device resident; REFERENCE
+ * chunks of a DEVICE-resident relation) with `column <predicate> value`.
+ * Result `slot` (0..HJ_SCAN_SLOTS-1) then holds, in device memory, one PosList per input chunk, back to back:
+ * chunk c's matches are pos[chunk_begin[c] .. chunk_begin[c+1]) in ascending chunk offset, as
+ * BaseTableScanImpl::_unary_scan appends them (for a reference-table input the reference groups the matches by
+ * referenced chunk instead; its tests compare unordered). A match is RowID{segs[c].chunk_id, offset} — the row of the
+ * INPUT table, which is what the operator needs to filter every distinct PosList of a reference-table input
+ * (table_scan.cpp:112-131). With HJ_SCAN_DEREFERENCE a REFERENCE chunk emits its own PosList entry at that offset
+ * instead, i.e. the output PosList itself when all columns share the scanned column's PosList (the usual case:
+ * no multi-level referencing, table_scan.cpp:98-110).
+ * NULL keys match nothing but IS NULL; `value_is_null` != 0 (comparison with a NULL literal) matches nothing at all
+ * (single_column_table_scan_impl.cpp:25-34). A dictionary chunk is scanned on its value ids against the literal's
+ * lower/upper bound in the chunk's dictionary (:83-133) — no per-row dictionary access.
+ * HJ_ERR_INVALID: refused predicate, float/double column, literal outside an int32 column's range. */
+int hj_scan(hj_ctx* ctx, const hj_relation* column, int predicate, int64_t value, int value_is_null, int slot,
+            uint32_t scan_flags, void* cuda_stream, hj_scan_info* out_info);
+
+/* Device pointers to the result in `slot` (valid until the next hj_scan into that slot, hj_scan_release or
+ * hj_destroy): pos = hj_row_id[n_rows], chunk_begin = uint32[n_chunks + 1]. */
+int hj_scan_result_device(hj_ctx* ctx, int slot, const hj_row_id** pos, const uint32_t** chunk_begin, uint64_t* n_rows,
+                          uint32_t* n_chunks);
+
+/* Copies the result in `slot` to host memory: pos[capacity_rows] and (optionally) chunk_begin[n_chunks + 1]. */
+int hj_scan_fetch(hj_ctx* ctx, int slot, hj_row_id* pos, uint64_t capacity_rows, uint32_t* chunk_begin);
+
+/* Frees the result in `slot` (all slots if slot < 0). TableScan's output is owned by the operator, so it is NOT
+ * touched by hj_release_scratch. */
+int hj_scan_release(hj_ctx* ctx, int slot);
+
 /* ---- multi-GPU (one process per GPU) ---------------------------------------- */
 /* The exchange has no reference counterpart: both relations are split by the high bits of the
  * key hash so that every key's rows meet on one rank, exchanged with an NCCL all-to-all over
