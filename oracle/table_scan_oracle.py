@@ -19,6 +19,9 @@ A chunk's result is the ascending list of matching chunk offsets; the operator t
 Chunk descriptions (plain dicts of numpy arrays):
   {"kind": "value", "values": int array, "nulls": uint8 array or None}
   {"kind": "dict", "dictionary": sorted unique int array, "attr": uint array, "null_value_id": int}
+  {"kind": "for", "minima": int array (one per 2048 rows), "offsets": uint array, "nulls": uint8 array or None}
+  {"kind": "rle", "run_values": int array, "end_positions": uint32 array (inclusive), "run_nulls": uint8 array or None}
+      (both scanned as decoded values: handle_column(BaseEncodedColumn), single_column_table_scan_impl.cpp:58-81)
   {"kind": "reference", "pos_list": (n, 2) uint32 array [chunk_id, chunk_offset] (0xFFFFFFFF pairs = NULL_ROW_ID),
    "referenced": [chunk descriptions of the referenced data table's column]}
 """
@@ -38,6 +41,15 @@ def decode(chunk, offsets=None):
     if chunk["kind"] == "value":
         v = chunk["values"]
         n = np.zeros(len(v), bool) if chunk.get("nulls") is None else chunk["nulls"].astype(bool)
+    elif chunk["kind"] == "for":   # FrameOfReferenceColumn: block minimum + offset, 2048-row blocks (frame_of_reference_column.hpp:33-80)
+        off = chunk["offsets"].astype(np.int64)
+        v = (np.repeat(chunk["minima"].astype(np.int64), 2048)[:len(off)] + off).astype(chunk["minima"].dtype)
+        n = np.zeros(len(v), bool) if chunk.get("nulls") is None else chunk["nulls"].astype(bool)
+    elif chunk["kind"] == "rle":   # RunLengthColumn: run values + inclusive end positions (run_length_column.hpp:29-66)
+        ends = chunk["end_positions"].astype(np.int64)
+        lens = np.diff(np.concatenate([[-1], ends]))
+        v = np.repeat(chunk["run_values"], lens)
+        n = np.repeat(chunk["run_nulls"].astype(bool), lens) if chunk.get("run_nulls") is not None else np.zeros(len(v), bool)
     else:
         attr = chunk["attr"].astype(np.int64)
         n = attr == chunk["null_value_id"]

@@ -39,10 +39,37 @@ def dict_encode(values, nulls):
     return {"kind": "dict", "dictionary": dictionary, "attr": attr.astype(width), "null_value_id": len(dictionary)}
 
 
-class DataTable:
-    """load_table(name, chunk_size) + ChunkEncoder::encode_chunks on the listed chunks."""
+def for_encode(values, nulls):
+    """frame_of_reference_encoder.hpp:30-90: 2048-row blocks, NULL stored as 0, offset = value - block minimum."""
+    v = values.copy()
+    v[nulls != 0] = 0
+    n = len(v)
+    minima = np.array([v[b:b + 2048].min() for b in range(0, n, 2048)], dtype=values.dtype)
+    off = v.astype(np.int64) - np.repeat(minima.astype(np.int64), 2048)[:n]
+    top = int(off.max(initial=0))
+    width = np.uint8 if top < 256 else np.uint16 if top < 65536 else np.uint32
+    return {"kind": "for", "minima": minima, "offsets": off.astype(width), "nulls": nulls.copy() if nulls.any() else None}
 
-    def __init__(self, columns, chunk_size, encode, dtype=np.int32):
+
+def rle_encode(values, nulls):
+    """run_length_encoder.hpp:20-60: a run ends where the value or the NULL-ness changes; inclusive end positions."""
+    n = len(values)
+    change = np.ones(n, dtype=bool)
+    change[1:] = (nulls[1:] != nulls[:-1]) | ((nulls[1:] == 0) & (values[1:] != values[:-1]))
+    starts = np.nonzero(change)[0]
+    ends = np.append(starts[1:] - 1, n - 1).astype(np.uint32) if n else np.zeros(0, np.uint32)
+    return {"kind": "rle", "n_rows": n, "run_values": np.ascontiguousarray(values[starts]), "end_positions": ends,
+            "run_nulls": np.ascontiguousarray(nulls[starts])}
+
+
+ENCODERS = {"dict": dict_encode, "for": for_encode, "rle": rle_encode}
+
+
+class DataTable:
+    """load_table(name, chunk_size) + ChunkEncoder::encode_chunks on the listed chunks with EncodingType `style`."""
+
+    def __init__(self, columns, chunk_size, encode, dtype=np.int32, style="dict"):
+        self.style = style
         self.names = list(columns)
         n = len(next(iter(columns.values())))
         self.bounds = [(s, min(s + chunk_size, n)) for s in range(0, n, chunk_size)] or [(0, 0)]
@@ -57,7 +84,7 @@ class DataTable:
         lo, hi = self.bounds[c]
         v, nl = np.ascontiguousarray(self.values[name][lo:hi]), np.ascontiguousarray(self.nulls[name][lo:hi])
         if c in self.encoded:
-            return dict_encode(v, nl)
+            return ENCODERS[self.style](v, nl)
         return {"kind": "value", "values": v, "nulls": nl if nl.any() else None}
 
     def column_chunks(self, name):
@@ -72,14 +99,16 @@ def pos_array(rows):
     return np.array([[INVALID, INVALID] if r is None else r for r in rows], dtype=np.uint32).reshape(-1, 2)
 
 
-def run_case(case, tables, scan_fn, encode_override=None):
+def run_case(case, tables, scan_fn, encode_override=None, style="dict"):
     """Runs one fixture case through scan_fn; returns ("rows", n) / ("values", sorted list) to compare with the expectation."""
     if "generated" in case:  # get_table_op_with_n_dict_entries: values 0..n in one chunk
         n = case["generated"]["n"]
-        table = DataTable({"a": list(range(n + 1))}, n + 1, case["encode"] if encode_override is None else encode_override)
+        table = DataTable({"a": list(range(n + 1))}, n + 1, case["encode"] if encode_override is None else encode_override,
+                          style=style)
     else:
         t = tables[case["table"]]
-        table = DataTable(t["data"], case["chunk_size"], case["encode"] if encode_override is None else encode_override)
+        table = DataTable(t["data"], case["chunk_size"], case["encode"] if encode_override is None else encode_override,
+                          style=style)
     n_chunks = len(table.bounds)
     excluded = set(case.get("excluded_chunks", []))
     # current relation: list of chunks; a chunk is None (data chunk c of `table`) or {column: pos_list} (reference chunk)

@@ -37,7 +37,7 @@ def ctx():
 
 
 def key_type_of(chunk):
-    a = chunk["values"] if chunk["kind"] == "value" else chunk["dictionary"]
+    a = chunk[{"value": "values", "dict": "dictionary", "for": "minima", "rle": "run_values"}[chunk["kind"]]]
     return abi.KEY_INT64 if a.dtype == np.int64 else abi.KEY_INT32
 
 
@@ -48,6 +48,10 @@ def relation_of(chunks, ids, location=abi.LOC_HOST):
             rb.add_value(cid, chunk["values"], chunk.get("nulls"))
         elif chunk["kind"] == "dict":
             rb.add_dict(cid, chunk["dictionary"], chunk["attr"], chunk["null_value_id"])
+        elif chunk["kind"] == "for":
+            rb.add_for(cid, chunk["minima"], chunk["offsets"], chunk.get("nulls"))
+        elif chunk["kind"] == "rle":
+            rb.add_rle(cid, chunk["n_rows"], chunk["run_values"], chunk["end_positions"], chunk["run_nulls"])
         else:
             referenced = relation_of(chunk["referenced"], list(range(len(chunk["referenced"]))), location)
             kt = max(key_type_of(c) for c in chunk["referenced"])
@@ -78,6 +82,15 @@ def test_reference_scan_case_on_gpu(ctx, case, encode):
         assert e.value.status == abi.ERR_INVALID
         return
     assert sm.run_case(case, FIX["tables"], make_gpu_scan(ctx), encode) == sm.expected_of(case), case["cite"]
+
+
+@unvalidated
+@pytest.mark.parametrize("style", ["for", "rle"])
+@pytest.mark.parametrize("case,encode", [ce for ce in CASES if ce[1] != "none" and not ce[0].get("expect_error")],
+                         ids=[i for i, ce in zip(IDS, CASES) if ce[1] != "none" and not ce[0].get("expect_error")])
+def test_reference_scan_case_on_gpu_for_and_rle(ctx, case, encode, style):
+    """The reference's FrameOfReference / RunLength parametrisations: decoded on the device by k_gather_refs, then scanned."""
+    assert sm.run_case(case, FIX["tables"], make_gpu_scan(ctx), encode, style) == sm.expected_of(case), case["cite"]
 
 
 def random_chunks(rng, n_rows, chunk, dtype, encoding, nullable, domain):

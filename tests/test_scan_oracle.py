@@ -25,6 +25,15 @@ def test_oracle_reproduces_reference_expectation(case, encode):
     assert sm.run_case(case, FIX["tables"], oracle_scan, encode) == sm.expected_of(case), case["cite"]
 
 
+@pytest.mark.parametrize("style", ["for", "rle"])
+@pytest.mark.parametrize("case,encode", CASES, ids=IDS)
+def test_oracle_reproduces_reference_expectation_for_and_rle(case, encode, style):
+    """EncodingType::FrameOfReference / RunLength of the reference's INSTANTIATE_TEST_CASE_P (table_scan_test.cpp:211-214)."""
+    if case.get("expect_error") or encode == "none":
+        pytest.skip("same as the dictionary run")
+    assert sm.run_case(case, FIX["tables"], oracle_scan, encode, style) == sm.expected_of(case), case["cite"]
+
+
 def test_dictionary_value_id_scan_equals_value_scan_on_random_chunks():
     """The value-id formulation (single_column_table_scan_impl.cpp:83-199) and the plain comparison agree, NULLs included."""
     rng = np.random.default_rng(7)
