@@ -365,4 +365,15 @@ std::shared_ptr<const Table> JoinHash::_on_execute() {
   return output_table;
 }
 
+// ---- shared with the other device operators of the shim (table_scan.cpp) ---------------------------------------------
+namespace hjhost {
+hj_ctx* context() { return acquire_ctx(); }
+std::shared_ptr<void> flatten_column(const Table& table, ColumnID column_id, const hj_relation** relation) {
+  auto flat = std::make_shared<FlatColumn>();
+  flatten(table, column_id, *flat);
+  *relation = &flat->rel;
+  return flat;  // keeps the descriptors `relation` points into alive
+}
+}  // namespace hjhost
+
 }  // namespace opossum

@@ -8,12 +8,14 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <fstream>
 #include <iostream>
 #include <map>
 #include <sstream>
 
 #include "join_hash.hpp"
+#include "table_scan.hpp"
 
 using namespace opossum;
 
@@ -295,7 +297,9 @@ int main(int argc, char** argv) {
       cases.push_back(std::move(c));
     }
   }
-  int failed = 0, ran = 0, skipped = 0;
+  int failed = 0, ran = 0, skipped = 0, n_device_scans = 0;
+  const char* ds = std::getenv("HJ_SHIM_DEVICE_SCAN");
+  const bool device_scan = ds && ds[0] == '1';
   for (const auto& c : cases) {
     if (!filter.empty() && c.name.find(filter) == std::string::npos) continue;
     bool in_scope = true;
@@ -310,7 +314,29 @@ int main(int argc, char** argv) {
           if (op.size() > 5 && op[4] == "dict") encode_chunks(*t, op[5]);
           env[op[1]] = t;
         } else if (op[0] == "scan") {
-          env[op[1]] = table_scan(env.at(op[2]), static_cast<ColumnID>(std::stoul(op[3])), op[4], std::stod(op[5]));
+          const auto in_table = env.at(op[2]);
+          const auto column_id = static_cast<ColumnID>(std::stoul(op[3]));
+          const double literal = std::stod(op[5]);
+          const std::map<std::string, PredicateCondition> conds = {
+              {">=", PredicateCondition::GreaterThanEquals}, {">", PredicateCondition::GreaterThan}, {"=", PredicateCondition::Equals},
+              {"<=", PredicateCondition::LessThanEquals}, {"<", PredicateCondition::LessThan}};
+          const bool integral = literal == static_cast<double>(static_cast<int64_t>(literal));
+          // HJ_SHIM_DEVICE_SCAN=1: the scans the device operator covers (integer column, integer literal) run through
+          // opossum::TableScan -> hj_scan, so the case is scan -> join on the GPU; the others keep the semantic helper
+          if (device_scan && conds.count(op[4]) && integral &&
+              TableScan::supported(*in_table, column_id, conds.at(op[4]), AllParameterVariant{static_cast<int64_t>(literal)})) {
+            auto wrapper = std::make_shared<TableWrapper>(in_table);
+            wrapper->execute();
+            const AllParameterVariant value = in_table->column_data_type(column_id) == DataType::Int
+                                                  ? AllParameterVariant{static_cast<int>(literal)}
+                                                  : AllParameterVariant{static_cast<int64_t>(literal)};
+            auto scan = std::make_shared<TableScan>(wrapper, column_id, conds.at(op[4]), value);
+            scan->execute();
+            env[op[1]] = scan->get_output();
+            ++n_device_scans;
+          } else {
+            env[op[1]] = table_scan(in_table, column_id, op[4], literal);
+          }
         } else if (op[0] == "join") {
           auto l = std::make_shared<TableWrapper>(env.at(op[2])), r = std::make_shared<TableWrapper>(env.at(op[3]));
           l->execute();
@@ -337,5 +363,6 @@ int main(int argc, char** argv) {
     failed += ok ? 0 : 1;
   }
   std::printf("shim_test: %d cases run, %d failed, %d out of scope\n", ran, failed, skipped);
+  if (device_scan) std::printf("shim_test: %d scans ran on the device (opossum::TableScan -> hj_scan)\n", n_device_scans);
   return failed;
 }

@@ -24,3 +24,17 @@ def test_shim_replays_reference_cases(built):
     r = subprocess.run([EXE, FIXTURES], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-4000:] + r.stderr[-2000:]
     assert "53 cases run, 0 failed, 0 out of scope" in r.stdout, r.stdout[-1000:]
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(os.environ.get("HJ_RUN_UNVALIDATED") != "1",
+                    reason="opossum::TableScan (host/table_scan.cpp) has not run on a GPU yet (set HJ_RUN_UNVALIDATED=1)")
+def test_shim_replays_reference_cases_with_device_scans(built):
+    """Same 53 cases, but every `scan` the device operator covers (integer column vs integer literal) runs through the C++
+    opossum::TableScan -> hj_scan, so the filtered join inputs are produced on the GPU (SURVEY 8f N4)."""
+    env = dict(os.environ, HJ_SHIM_DEVICE_SCAN="1")
+    r = subprocess.run([EXE, FIXTURES], capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stdout[-4000:] + r.stderr[-2000:]
+    assert "53 cases run, 0 failed, 0 out of scope" in r.stdout, r.stdout[-1000:]
+    n = int(r.stdout.rsplit("shim_test: ", 1)[1].split(" scans ran on the device")[0])
+    assert n >= 20, r.stdout[-500:]
