@@ -259,13 +259,20 @@ class HashJoin:
 
     # ---- TableScan on the device -------------------------------------------------------------------
     def scan(self, column, predicate, value=None, slot=0, dereference=False, stream=None):
-        """hj_scan: `column <predicate> value` (value None = NULL literal). Returns hj_scan_info; the PosLists stay on the
-        device in `slot`."""
+        """hj_scan: `column <predicate> value` (value None = NULL literal; a Python / numpy float is passed as a double
+        literal, HJ_SCAN_VALUE_IS_DOUBLE). Returns hj_scan_info; the PosLists stay on the device in `slot`."""
         if isinstance(predicate, str):
             predicate = abi.PREDICATES[predicate]
         info = abi.ScanInfo()
-        self._check(self._l.hj_scan(self._ctx, C.byref(column), predicate, 0 if value is None else int(value),
-                                    1 if value is None else 0, slot, abi.SCAN_DEREFERENCE if dereference else 0, stream,
+        flags = abi.SCAN_DEREFERENCE if dereference else 0
+        if value is None:
+            bits = 0
+        elif isinstance(value, (float, np.floating)):
+            bits = int(np.array([value], dtype=np.float64).view(np.int64)[0])
+            flags |= abi.SCAN_VALUE_IS_DOUBLE
+        else:
+            bits = int(value)
+        self._check(self._l.hj_scan(self._ctx, C.byref(column), predicate, bits, 1 if value is None else 0, slot, flags, stream,
                                     C.byref(info)))
         return info
 

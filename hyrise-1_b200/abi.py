@@ -69,6 +69,7 @@ PREDICATES = {"Equals": PRED_EQUALS, "NotEquals": PRED_NOT_EQUALS, "LessThan": P
               "NotLike": PRED_NOT_LIKE, "IsNull": PRED_IS_NULL, "IsNotNull": PRED_IS_NOT_NULL}
 SCAN_SLOTS = 4
 SCAN_DEREFERENCE = 0x1
+SCAN_VALUE_IS_DOUBLE = 0x2
 
 
 class Timings(C.Structure):

@@ -1,6 +1,7 @@
 // hj_api.cu — host side of libhj: the C ABI of include/hj.h, device-memory management and kernel orchestration.
 // No CPU fallback anywhere: every compute entry point launches the sm_100a kernels of hj_kernels.cuh.
 #include <algorithm>
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -1242,9 +1243,11 @@ int check_ctx(hj_ctx* ctx) {
 
 constexpr size_t kPinnedScanTotals = 3616;  // two words inside the pinned readback area (behind kPinnedRefFlags)
 
-template <typename K>
-int run_scan(hj_ctx* ctx, const hj_relation* column, const hj_relation* original, int predicate, int64_t value, int slot,
-             uint32_t scan_flags, cudaStream_t st, hj_scan_info* info) {
+// K: integer type of the stored keys; V: type the comparison runs in (= K, or float / double over their bit patterns);
+// `value` the literal as V, `id_value` the literal the dictionary bounds are searched with (integer columns).
+template <typename K, typename V>
+int run_scan(hj_ctx* ctx, const hj_relation* column, const hj_relation* original, int predicate, V value, int64_t id_value,
+             int slot, uint32_t scan_flags, cudaStream_t st, hj_scan_info* info) {
   PreparedRel pr;
   HJ_TRY(prepare_relation(ctx, column, 1, kScanTile, st, &pr));
   const uint32_t n_segs = pr.meta.n_segs, n_tiles = pr.meta.n_tiles;
@@ -1281,11 +1284,11 @@ int run_scan(hj_ctx* ctx, const hj_relation* column, const hj_relation* original
 
   const uint32_t grid = std::max<uint32_t>(1, std::min<uint32_t>(n_tiles, uint32_t(ctx->n_sms) * 8));
   if (n_segs) {
-    k_scan_bounds<<<(n_segs + 127) / 128, 128, 0, st>>>(pr.meta.segs, n_segs, static_cast<long long>(value), bounds);
+    k_scan_bounds<<<(n_segs + 127) / 128, 128, 0, st>>>(pr.meta.segs, n_segs, static_cast<long long>(id_value), bounds);
     HJ_LAUNCH_CHECK(ctx, "k_scan_bounds");
   }
   if (n_tiles) {
-    k_scan_mask<K><<<grid, kScanThreads, 0, st>>>(pr.meta, predicate, static_cast<K>(value), bounds, mask, tile_count);
+    k_scan_mask<K, V><<<grid, kScanThreads, 0, st>>>(pr.meta, predicate, value, bounds, mask, tile_count);
     HJ_LAUNCH_CHECK(ctx, "k_scan_mask");
   }
   k_scan_prefix<1024><<<1, 1024, 0, st>>>(tile_count, n_tiles, pr.meta.segs, n_segs, tile_base, chunk_begin, totals);
@@ -1417,17 +1420,37 @@ int hj_scan(hj_ctx* ctx, const hj_relation* column, int predicate, int64_t value
     return fail(ctx, HJ_ERR_INVALID, "PredicateCondition %d is not a single-column comparison (Between/In/Like are refused, as "
                 "SingleColumnTableScanImpl fails on them)", predicate);
   HJ_TRY(validate_relation(ctx, column, "scan"));
-  bool wide = false;
+  bool wide = false, any_float = false, any_double = false;
   for (uint32_t i = 0; i < column->n_segs; ++i) {
     const hj_segment& sg = column->segs[i];
-    if (sg.key_type == HJ_KEY_FLOAT || sg.key_type == HJ_KEY_DOUBLE)
-      return fail(ctx, HJ_ERR_INVALID, "scan chunk %u: float/double columns are not scanned on the device yet", i);
+    any_float = any_float || sg.key_type == HJ_KEY_FLOAT;
+    any_double = any_double || sg.key_type == HJ_KEY_DOUBLE;
     wide = wide || sg.key_type == HJ_KEY_INT64;
     if (sg.kind == HJ_SEG_REFERENCE && (scan_flags & HJ_SCAN_DEREFERENCE) && column->location != HJ_LOC_DEVICE)
       return fail(ctx, HJ_ERR_INVALID, "scan chunk %u: HJ_SCAN_DEREFERENCE needs a device-resident relation (the kernel reads the "
                   "chunk's PosList where it lies)", i);
   }
-  if (!null_test && !value_is_null && !wide && (value < INT32_MIN || value > INT32_MAX))
+  // the literal in the column's type, as the reference's type_cast<ColumnDataType>(AllTypeVariant) converts it
+  // (single_column_table_scan_impl.cpp:36, type_cast.hpp:39-58)
+  const bool floating = any_float || any_double;
+  double literal_d = 0.0;
+  if (!null_test && !value_is_null) {
+    if (scan_flags & HJ_SCAN_VALUE_IS_DOUBLE) {
+      std::memcpy(&literal_d, &value, sizeof(double));
+      if (!floating) {
+        // integral column, floating literal: boost::numeric_cast<T>(double) truncates toward zero and throws outside T's range
+        const double t = std::trunc(literal_d);
+        const double lo = wide ? -9223372036854775808.0 : -2147483648.0, hi = wide ? 9223372036854775808.0 : 2147483648.0;
+        if (!(t >= lo && t < hi))
+          return fail(ctx, HJ_ERR_INVALID, "literal %g does not fit the %s column (boost::numeric_cast throws, type_cast.hpp:56)",
+                      literal_d, wide ? "int64" : "int32");
+        value = static_cast<int64_t>(t);
+      }
+    } else {
+      literal_d = static_cast<double>(value);
+    }
+  }
+  if (!floating && !null_test && !value_is_null && !wide && (value < INT32_MIN || value > INT32_MAX))
     return fail(ctx, HJ_ERR_INVALID, "literal %lld does not fit the int32 column (the reference's type_cast fails on it too)",
                 (long long)value);
   HJ_TRY(check_ctx(ctx));
@@ -1448,10 +1471,20 @@ int hj_scan(hj_ctx* ctx, const hj_relation* column, int predicate, int64_t value
   ctx->ref_h2d_bytes = 0;
   std::memset(static_cast<char*>(ctx->pinned) + kPinnedRefFlags, 0, 8);
   RefRewrite rw;
-  HJ_TRY(gather_references(ctx, column, 1, st, &rw, wide ? HJ_KEY_INT64 : HJ_KEY_INT32));
+  // float / double columns: EVERY chunk is rewritten into the bit patterns of the column type (to_hashed_type; a column
+  // with double chunks is compared in double), so the mask kernel sees value-like chunks only
+  const uint32_t scan_type = any_double ? HJ_KEY_DOUBLE : any_float ? HJ_KEY_FLOAT : wide ? HJ_KEY_INT64 : HJ_KEY_INT32;
+  HJ_TRY(gather_references(ctx, column, 1, st, &rw, scan_type));
   const hj_relation* rel = rw.any ? &rw.rel : column;
-  HJ_TRY(wide ? run_scan<int64_t>(ctx, rel, column, predicate, value, slot, scan_flags, st, out_info)
-              : run_scan<int32_t>(ctx, rel, column, predicate, value, slot, scan_flags, st, out_info));
+  switch (scan_type) {
+    case HJ_KEY_DOUBLE: HJ_TRY((run_scan<int64_t, double>(ctx, rel, column, predicate, literal_d, 0, slot, scan_flags, st, out_info))); break;
+    case HJ_KEY_FLOAT:
+      HJ_TRY((run_scan<int32_t, float>(ctx, rel, column, predicate, static_cast<float>(literal_d), 0, slot, scan_flags, st, out_info)));
+      break;
+    case HJ_KEY_INT64: HJ_TRY((run_scan<int64_t, int64_t>(ctx, rel, column, predicate, value, value, slot, scan_flags, st, out_info))); break;
+    default:
+      HJ_TRY((run_scan<int32_t, int32_t>(ctx, rel, column, predicate, static_cast<int32_t>(value), value, slot, scan_flags, st, out_info)));
+  }
   if (rw.any) {
     const auto* flag = reinterpret_cast<const uint32_t*>(static_cast<const char*>(ctx->pinned) + kPinnedRefFlags);
     if (flag[0] || flag[1]) {

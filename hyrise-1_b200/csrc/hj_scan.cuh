@@ -1,5 +1,6 @@
-// hj_scan.cuh — TableScan on the device: `integer column <predicate> literal` over the same chunk
-// descriptors the join reads, producing per-chunk PosLists that stay in HBM and feed hj_join as REFERENCE segments.
+// hj_scan.cuh — TableScan on the device: `column <predicate> literal` (int32 / int64 / float / double
+// columns) over the same chunk descriptors the join reads, producing per-chunk PosLists that stay in HBM and feed hj_join
+// as REFERENCE segments.
 //
 // Replaces TableScan::_on_execute (src/lib/operators/table_scan.cpp:84-171) with SingleColumnTableScanImpl
 // (operators/table_scan/single_column_table_scan_impl.cpp:23-133) and IsNullTableScanImpl (is_null_table_scan_impl.cpp):
@@ -13,6 +14,8 @@
 //                     its own PosList entry instead (table_scan.cpp:124-131).
 // All four are HBM-streaming kernels; algorithmic bytes per row: w_in + 8 B per match.
 #pragma once
+#include <type_traits>
+
 #include "hj_kernels.cuh"
 
 namespace hj {
@@ -62,9 +65,21 @@ __device__ __forceinline__ bool scan_compare(int pred, V left, V right) {
   }
 }
 
+// The stored key of a value-like chunk as the type the comparison runs in: V = K for integer columns; for float / double
+// columns the chunks were rewritten by k_gather_refs into the IEEE bit patterns of the column type (K = int32 / int64
+// carrying V = float / double), which are compared as the floating values they encode (NaN matches only !=, -0 == +0,
+// as the reference's C++ operators on the column type do).
+template <typename K, typename V>
+__device__ __forceinline__ V scan_key(const DevSegment& s, uint32_t i) {
+  const K raw = load_plain_key<K>(s, i);
+  if constexpr (std::is_same<V, float>::value) return __int_as_float(static_cast<int>(raw));
+  else if constexpr (std::is_same<V, double>::value) return __longlong_as_double(static_cast<long long>(raw));
+  else return raw;
+}
+
 // Does row i of segment s match? NULL rows match IS NULL only (base_table_scan_impl.hpp:41, is_null_table_scan_impl.cpp).
-template <typename K>
-__device__ __forceinline__ bool scan_row(const DevSegment& s, uint32_t i, int pred, K value, uint32_t lb, uint32_t ub) {
+template <typename K, typename V>
+__device__ __forceinline__ bool scan_row(const DevSegment& s, uint32_t i, int pred, V value, uint32_t lb, uint32_t ub) {
   if (s.kind == 1) {
     const uint32_t vid = load_attr(s, i);
     const bool is_null = vid == s.null_value_id;
@@ -84,12 +99,12 @@ __device__ __forceinline__ bool scan_row(const DevSegment& s, uint32_t i, int pr
   if (pred == kPredIsNull) return is_null;
   if (is_null) return false;
   if (pred == kPredIsNotNull) return true;
-  return scan_compare<K>(pred, load_plain_key<K>(s, i), value);
+  return scan_compare<V>(pred, scan_key<K, V>(s, i), value);
 }
 
 // S1. A warp owns 32 consecutive rows at a time, so a ballot IS the mask word. mask: kScanWordsPerTile words per tile.
-template <typename K>
-__global__ void __launch_bounds__(kScanThreads) k_scan_mask(RelMeta rel, int pred, K value, const uint32_t* __restrict__ bounds,
+template <typename K, typename V>
+__global__ void __launch_bounds__(kScanThreads) k_scan_mask(RelMeta rel, int pred, V value, const uint32_t* __restrict__ bounds,
                                                             uint32_t* __restrict__ mask, uint32_t* __restrict__ tile_count) {
   __shared__ uint32_t s_cnt[kScanThreads / 32];
   constexpr uint32_t NW = kScanThreads / 32;
@@ -104,7 +119,7 @@ __global__ void __launch_bounds__(kScanThreads) k_scan_mask(RelMeta rel, int pre
 #pragma unroll 4
     for (uint32_t w = warp; w < kScanWordsPerTile; w += NW) {
       const uint32_t i = w * 32 + lane;
-      const bool m = i < cnt && scan_row<K>(s, r0 + i, pred, value, lb, ub);
+      const bool m = i < cnt && scan_row<K, V>(s, r0 + i, pred, value, lb, ub);
       const uint32_t word = __ballot_sync(0xffffffffu, m);
       if (lane == 0) mask[static_cast<size_t>(tile) * kScanWordsPerTile + w] = word;
       matches += __popc(word);  // the same value in every lane

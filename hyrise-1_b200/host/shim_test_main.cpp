@@ -321,15 +321,18 @@ int main(int argc, char** argv) {
               {">=", PredicateCondition::GreaterThanEquals}, {">", PredicateCondition::GreaterThan}, {"=", PredicateCondition::Equals},
               {"<=", PredicateCondition::LessThanEquals}, {"<", PredicateCondition::LessThan}};
           const bool integral = literal == static_cast<double>(static_cast<int64_t>(literal));
-          // HJ_SHIM_DEVICE_SCAN=1: the scans the device operator covers (integer column, integer literal) run through
-          // opossum::TableScan -> hj_scan, so the case is scan -> join on the GPU; the others keep the semantic helper
-          if (device_scan && conds.count(op[4]) && integral &&
-              TableScan::supported(*in_table, column_id, conds.at(op[4]), AllParameterVariant{static_cast<int64_t>(literal)})) {
+          // HJ_SHIM_DEVICE_SCAN=1: the scans the device operator covers run through opossum::TableScan -> hj_scan, so the
+          // case is scan -> join on the GPU; the others keep the semantic helper. (A fractional literal on an INTEGER column
+          // stays with the helper: the reference truncates it, type_cast.hpp:56, the helper compares as double.)
+          const DataType column_type = in_table->column_data_type(column_id);
+          const bool floating_column = column_type == DataType::Float || column_type == DataType::Double;
+          if (device_scan && conds.count(op[4]) && (integral || floating_column) &&
+              TableScan::supported(*in_table, column_id, conds.at(op[4]), AllParameterVariant{literal})) {
             auto wrapper = std::make_shared<TableWrapper>(in_table);
             wrapper->execute();
-            const AllParameterVariant value = in_table->column_data_type(column_id) == DataType::Int
-                                                  ? AllParameterVariant{static_cast<int>(literal)}
-                                                  : AllParameterVariant{static_cast<int64_t>(literal)};
+            const AllParameterVariant value = floating_column ? AllParameterVariant{literal}
+                                              : column_type == DataType::Int ? AllParameterVariant{static_cast<int>(literal)}
+                                                                             : AllParameterVariant{static_cast<int64_t>(literal)};
             auto scan = std::make_shared<TableScan>(wrapper, column_id, conds.at(op[4]), value);
             scan->execute();
             env[op[1]] = scan->get_output();

@@ -4,6 +4,8 @@
 // hj_scan() call on the GPU.
 #include "table_scan.hpp"
 
+#include <cstring>
+
 #include <algorithm>
 #include <map>
 #include <unordered_set>
@@ -30,13 +32,19 @@ constexpr int kScanSlot = 0;
 
 bool is_null_predicate(PredicateCondition p) { return p == PredicateCondition::IsNull || p == PredicateCondition::IsNotNull; }
 
-// The literal as the column's integer type (type_cast<ColumnDataType>(_right_value), single_column_table_scan_impl.cpp:52):
-// integer literals only — a floating literal on an integer column goes through boost::lexical_cast in the reference and
-// fails unless it prints as an integer, which is not reproduced here.
-bool integer_literal(const AllTypeVariant& v, int64_t* out) {
+// The literal for hj_scan: an integer, or (is_double) the bits of a double. The library converts it to the column's type
+// the way type_cast<ColumnDataType>(_right_value) does (single_column_table_scan_impl.cpp:36, type_cast.hpp:39-58).
+bool numeric_literal(const AllTypeVariant& v, int64_t* out, bool* is_double) {
+  *is_double = false;
   if (const auto* p = std::get_if<int32_t>(&v)) { *out = *p; return true; }
   if (const auto* p = std::get_if<int64_t>(&v)) { *out = *p; return true; }
-  return false;
+  double d;
+  if (const auto* p = std::get_if<float>(&v)) d = static_cast<double>(*p);
+  else if (const auto* p = std::get_if<double>(&v)) d = *p;
+  else return false;
+  std::memcpy(out, &d, sizeof(d));
+  *is_double = true;
+  return true;
 }
 
 }  // namespace
@@ -67,23 +75,25 @@ const std::string TableScan::description(DescriptionMode description_mode) const
 bool TableScan::supported(const Table& table, ColumnID column_id, PredicateCondition predicate_condition,
                           const AllParameterVariant& right_parameter) {
   const DataType type = table.column_data_type(column_id);
-  if (type != DataType::Int && type != DataType::Long) return false;
+  if (type != DataType::Int && type != DataType::Long && type != DataType::Float && type != DataType::Double) return false;
   if (is_null_predicate(predicate_condition)) return true;
   if (static_cast<int>(predicate_condition) > static_cast<int>(PredicateCondition::GreaterThanEquals)) return false;
   if (right_parameter.is_column) return false;
   int64_t literal;
-  return variant_is_null(right_parameter.value) || integer_literal(right_parameter.value, &literal);
+  bool is_double;
+  return variant_is_null(right_parameter.value) || numeric_literal(right_parameter.value, &literal, &is_double);
 }
 
 std::shared_ptr<const Table> TableScan::_on_execute() {
   const auto in_table = input_table_left();
   Assert(in_table != nullptr, "TableScan: input has not been executed");
   if (!supported(*in_table, _left_column_id, _predicate_condition, _right_parameter))
-    Fail("TableScan on the device covers integer columns compared with an integer literal and IS [NOT] NULL; this scan is "
+    Fail("TableScan on the device covers numeric columns compared with a numeric literal and IS [NOT] NULL; this scan is "
          "not supported and there is no CPU fallback");
   int64_t literal = 0;
+  bool literal_is_double = false;
   const bool null_literal = !is_null_predicate(_predicate_condition) && variant_is_null(_right_parameter.value);
-  if (!is_null_predicate(_predicate_condition) && !null_literal) integer_literal(_right_parameter.value, &literal);
+  if (!is_null_predicate(_predicate_condition) && !null_literal) numeric_literal(_right_parameter.value, &literal, &literal_is_double);
 
   auto output = std::make_shared<Table>(in_table->column_definitions(), TableType::References);
   if (in_table->chunk_count() == 0) return output;
@@ -107,7 +117,8 @@ std::shared_ptr<const Table> TableScan::_on_execute() {
 
   hj_ctx* ctx = hjhost::context();
   hj_scan_info info;
-  if (hj_scan(ctx, &rel, static_cast<int>(_predicate_condition), literal, null_literal ? 1 : 0, kScanSlot, 0, nullptr, &info) != HJ_OK)
+  if (hj_scan(ctx, &rel, static_cast<int>(_predicate_condition), literal, null_literal ? 1 : 0, kScanSlot,
+              literal_is_double ? HJ_SCAN_VALUE_IS_DOUBLE : 0u, nullptr, &info) != HJ_OK)
     Fail(std::string("TableScan: ") + hj_last_error(ctx));
   std::vector<RowID> matches(std::max<uint64_t>(1, info.n_rows));
   std::vector<uint32_t> begin(segs.size() + 1, 0);

@@ -300,6 +300,7 @@ enum hj_predicate {
 
 #define HJ_SCAN_SLOTS 4 /* results a context keeps at a time (e.g. the two filtered inputs of a join) */
 #define HJ_SCAN_DEREFERENCE 0x1u /* hj_scan scan_flags: REFERENCE chunks emit pos_list[offset], not (chunk_id, offset) */
+#define HJ_SCAN_VALUE_IS_DOUBLE 0x2u /* hj_scan scan_flags: `value` holds the bit pattern of a double literal (memcpy) */
 
 typedef struct hj_scan_info {
   uint64_t n_rows;            /* matching rows over all chunks                                  */
@@ -307,8 +308,8 @@ typedef struct hj_scan_info {
   uint32_t n_nonempty_chunks; /* chunks with at least one match (the reference drops the others) */
 } hj_scan_info;
 
-/* Scans one integer key column (VALUE / DICT / GATHERED / FOR / RLE chunks, host or device resident; REFERENCE
- * chunks of a DEVICE-resident relation) with `column <predicate> value`.
+/* Scans one int32 / int64 / float / double column (VALUE / DICT / GATHERED / FOR / RLE chunks, host or device
+ * resident; REFERENCE chunks) with `column <predicate> value`.
  * Result `slot` (0..HJ_SCAN_SLOTS-1) then holds, in device memory, one PosList per input chunk, back to back:
  * chunk c's matches are pos[chunk_begin[c] .. chunk_begin[c+1]) in ascending chunk offset, as
  * BaseTableScanImpl::_unary_scan appends them (for a reference-table input the reference groups the matches by
@@ -320,7 +321,11 @@ typedef struct hj_scan_info {
  * NULL keys match nothing but IS NULL; `value_is_null` != 0 (comparison with a NULL literal) matches nothing at all
  * (single_column_table_scan_impl.cpp:25-34). A dictionary chunk is scanned on its value ids against the literal's
  * lower/upper bound in the chunk's dictionary (:83-133) — no per-row dictionary access.
- * HJ_ERR_INVALID: refused predicate, float/double column, literal outside an int32 column's range. */
+ * The literal is an integer in `value`, or with HJ_SCAN_VALUE_IS_DOUBLE a double whose bits are in `value`; it is
+ * converted to the column's type the way type_cast<ColumnDataType>() does (type_cast.hpp:39-58): to float / double
+ * for a floating column (the chunks of such a column are compared as values, dictionary chunks included), and a
+ * double literal on an integer column is truncated toward zero (boost::numeric_cast; `a < 457.9` scans `a < 457`).
+ * HJ_ERR_INVALID: refused predicate, literal outside the integer column's range. */
 int hj_scan(hj_ctx* ctx, const hj_relation* column, int predicate, int64_t value, int value_is_null, int slot,
             uint32_t scan_flags, void* cuda_stream, hj_scan_info* out_info);
 

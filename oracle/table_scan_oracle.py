@@ -1,4 +1,4 @@
-"""CPU restatement of the reference's single-column TableScan for integer columns (numpy). TEST INFRASTRUCTURE: imported
+"""CPU restatement of the reference's single-column TableScan for int / long / float / double columns (numpy). TEST INFRASTRUCTURE: imported
 only by tests/ — never by the product package (hyrise-1_b200 has no CPU path).
 
 Follows, per chunk, what TableScan::_on_execute dispatches to (src/lib/operators/table_scan.cpp:84-171, _init_scan :173-201):
@@ -60,15 +60,37 @@ def decode(chunk, offsets=None):
     return v, n
 
 
+def cast_literal(value, dtype):
+    """type_cast<ColumnDataType>(AllTypeVariant) (type_cast.hpp:39-58, called at single_column_table_scan_impl.cpp:36):
+    floating column -> the literal as that floating type; integral column with a floating literal ->
+    boost::numeric_cast<T>(double): truncation toward zero, bad_numeric_cast outside T's range."""
+    dtype = np.dtype(dtype)
+    if dtype.kind == "f":
+        return dtype.type(value)
+    if isinstance(value, float):
+        t = np.trunc(value)
+        info = np.iinfo(dtype)
+        if not (info.min <= t <= info.max):
+            raise OverflowError("bad numeric conversion")
+        return int(t)
+    return int(value)
+
+
+def _wide(values):
+    """Integers are compared as int64 (no wrap-around on the literal), floats in the column's own type."""
+    return values if values.dtype.kind == "f" else values.astype(np.int64)
+
+
 def _scan_value_like(values, is_null, predicate, value):
     """_unary_scan_with_value: NULL rows are skipped, the comparator decides the rest."""
-    return np.flatnonzero(~is_null & _COMPARE[predicate](values.astype(np.int64), np.int64(value)))
+    return np.flatnonzero(~is_null & _COMPARE[predicate](_wide(values), cast_literal(value, values.dtype)))
 
 
 def _scan_dictionary(chunk, predicate, value):
     """single_column_table_scan_impl.cpp:83-199 on value ids."""
-    d = chunk["dictionary"].astype(np.int64)
+    d = _wide(chunk["dictionary"])
     attr = chunk["attr"].astype(np.int64)
+    value = cast_literal(value, chunk["dictionary"].dtype)
     lower = int(np.searchsorted(d, value, side="left"))   # BaseDictionaryColumn::lower_bound
     upper = int(np.searchsorted(d, value, side="right"))  # upper_bound
     lower_id = INVALID if lower == len(d) else lower      # INVALID_VALUE_ID when no such entry
@@ -118,7 +140,9 @@ def _dereference(chunk):
     referenced row's value / null flag."""
     pl = chunk["pos_list"]
     n_rows = len(pl)
-    values = np.zeros(n_rows, np.int64)
+    kinds = {c[{"value": "values", "dict": "dictionary", "for": "minima", "rle": "run_values"}[c["kind"]]].dtype
+             for c in chunk["referenced"]}
+    values = np.zeros(n_rows, kinds.pop() if len(kinds) == 1 else np.int64)
     is_null = np.zeros(n_rows, bool)
     for i in range(n_rows):
         c, o = int(pl[i, 0]), int(pl[i, 1])
@@ -126,7 +150,7 @@ def _dereference(chunk):
             is_null[i] = True
             continue
         v, n = decode(chunk["referenced"][c], np.array([o]))
-        values[i], is_null[i] = int(v[0]), bool(n[0])
+        values[i], is_null[i] = v[0], bool(n[0])
     return values, is_null
 
 

@@ -134,7 +134,21 @@ for t in tables.values():  # only the integer columns are scanned; keep the othe
     t["columns"] = [n for n in t["columns"] if n in t["data"]]
     del t["types"]
 
+# Scans on a float column (kept apart from `cases`: their tables carry per-column types)
+typed_tables = {"int_float": load_tbl("int_float")}
+float_cases = [
+    # DoubleScan :211-221: a >= 1234, then b < 457.9 on the reference table -> int_float_filtered.tbl
+    {"name": "DoubleScan", "cite": f"{T}:211-221", "table": "int_float", "chunk_size": 2, "encode": "none",
+     "steps": [{"column": "a", "predicate": "GreaterThanEquals", "value": 1234},
+               {"column": "b", "predicate": "LessThan", "value": 457.9}],
+     "expect_column": "a", "expect": load_tbl("int_float_filtered")["data"]["a"]},
+    # ScanWithEmptyInput :466-478: the second scan runs on an empty reference table
+    {"name": "ScanWithEmptyInput", "cite": f"{T}:466-478", "table": "int_float", "chunk_size": 2, "encode": "none",
+     "steps": [{"column": "a", "predicate": "GreaterThan", "value": 12345},
+               {"column": "b", "predicate": "Equals", "value": 456.7}], "expect_rows": 0},
+]
+
 with open(os.path.join(HERE, "scan_fixtures.json"), "w") as f:
     json.dump({"source": "generated by tests/golden/make_scan_golden.py from /root/reference/" + T, "tables": tables,
-               "cases": cases}, f, indent=0)
-print(len(cases), "cases,", len(tables), "tables")
+               "cases": cases, "typed_tables": typed_tables, "float_cases": float_cases}, f, indent=0)
+print(len(cases), "cases,", len(tables), "tables,", len(float_cases), "float cases")

@@ -23,6 +23,9 @@ PREDICATES = {"Equals": 0, "NotEquals": 1, "LessThan": 2, "LessThanEquals": 3, "
               "Between": 6, "In": 7, "Like": 8, "NotLike": 9, "IsNull": 10, "IsNotNull": 11}
 
 
+TYPE_NAMES = {"int": np.int32, "long": np.int64, "float": np.float32, "double": np.float64}  # load_table.cpp column types
+
+
 def load_fixtures():
     with open(os.path.join(ROOT, "tests", "golden", "scan_fixtures.json")) as f:
         return json.load(f)
@@ -68,14 +71,15 @@ ENCODERS = {"dict": dict_encode, "for": for_encode, "rle": rle_encode}
 class DataTable:
     """load_table(name, chunk_size) + ChunkEncoder::encode_chunks on the listed chunks with EncodingType `style`."""
 
-    def __init__(self, columns, chunk_size, encode, dtype=np.int32, style="dict"):
+    def __init__(self, columns, chunk_size, encode, dtype=np.int32, style="dict", dtypes=None):
         self.style = style
+        dtypes = dtypes or {}
         self.names = list(columns)
         n = len(next(iter(columns.values())))
         self.bounds = [(s, min(s + chunk_size, n)) for s in range(0, n, chunk_size)] or [(0, 0)]
         self.values, self.nulls = {}, {}
         for name, col in columns.items():
-            self.values[name] = np.array([0 if v is None else v for v in col], dtype=dtype)
+            self.values[name] = np.array([0 if v is None else v for v in col], dtype=dtypes.get(name, dtype))
             self.nulls[name] = np.array([1 if v is None else 0 for v in col], dtype=np.uint8)
         all_chunks = list(range(len(self.bounds)))
         self.encoded = set(all_chunks if encode == "all" else [] if encode == "none" else encode)
@@ -92,7 +96,7 @@ class DataTable:
 
     def value_at(self, name, chunk_id, offset):
         i = self.bounds[chunk_id][0] + offset
-        return None if self.nulls[name][i] else int(self.values[name][i])
+        return None if self.nulls[name][i] else self.values[name][i].item()
 
 
 def pos_array(rows):
@@ -107,8 +111,9 @@ def run_case(case, tables, scan_fn, encode_override=None, style="dict"):
                           style=style)
     else:
         t = tables[case["table"]]
+        dtypes = {n: TYPE_NAMES[ty.replace("_null", "")] for n, ty in zip(t["columns"], t["types"])} if "types" in t else None
         table = DataTable(t["data"], case["chunk_size"], case["encode"] if encode_override is None else encode_override,
-                          style=style)
+                          style=style, dtypes=dtypes)
     n_chunks = len(table.bounds)
     excluded = set(case.get("excluded_chunks", []))
     # current relation: list of chunks; a chunk is None (data chunk c of `table`) or {column: pos_list} (reference chunk)

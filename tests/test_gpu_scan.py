@@ -38,7 +38,7 @@ def ctx():
 
 def key_type_of(chunk):
     a = chunk[{"value": "values", "dict": "dictionary", "for": "minima", "rle": "run_values"}[chunk["kind"]]]
-    return abi.KEY_INT64 if a.dtype == np.int64 else abi.KEY_INT32
+    return {"int32": abi.KEY_INT32, "int64": abi.KEY_INT64, "float32": abi.KEY_FLOAT, "float64": abi.KEY_DOUBLE}[a.dtype.name]
 
 
 def relation_of(chunks, ids, location=abi.LOC_HOST):
@@ -207,3 +207,41 @@ def test_scan_then_join_without_leaving_the_device(ctx):
     ob_b, ob_p, oinfo = ob.oracle_join(host_rel(bk, b_pos), host_rel(pk, p_pos), abi.MODE_INNER)
     assert info.n_rows == oinfo["n_rows"] == int(((pk >= 100_000) & (pk < 300_000)).sum())
     assert np.array_equal(ob.canonical(gb, gp), ob.canonical(ob_b, ob_p))
+
+
+# ---- float / double columns (hj_scan compares the column type's values; HJ_SCAN_VALUE_IS_DOUBLE literals) ---------------
+@unvalidated
+@pytest.mark.parametrize("case", FIX["float_cases"], ids=[c["name"] for c in FIX["float_cases"]])
+@pytest.mark.parametrize("encode,style", [("none", "dict"), ("all", "dict"), ("all", "rle")])
+def test_reference_float_scan_case_on_gpu(ctx, case, encode, style):
+    assert sm.run_case(case, FIX["typed_tables"], make_gpu_scan(ctx), encode, style) == sm.expected_of(case), case["cite"]
+
+
+@unvalidated
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("encoding", ["value", "dict", "mixed"])
+@pytest.mark.parametrize("nullable", [False, True])
+def test_random_float_scans_match_oracle(ctx, dtype, encoding, nullable):
+    from test_scan_oracle import FLOAT_LITERALS, float_chunks
+    rng = np.random.default_rng(0xF10A7)
+    scan = make_gpu_scan(ctx)
+    for n_rows, chunk in [(0, 8), (1, 8), (33, 32), (4097, 4096), (20000, 7000), (300000, 131072)]:
+        chunks = float_chunks(rng, n_rows, chunk, dtype, encoding, nullable)
+        ids = list(range(len(chunks)))
+        for pred in list(range(6)) + [10, 11]:
+            for lit in FLOAT_LITERALS:
+                scan(chunks, ids, pred, lit)
+        scan(chunks, ids, 0, None)
+
+
+@unvalidated
+def test_floating_literal_on_an_integer_column(ctx):
+    chunks = [{"kind": "value", "values": np.array([455, 456, 457, 458, -1, 0], np.int32), "nulls": None},
+              sm.dict_encode(np.array([455, 456, 457, 458, -1, 0], np.int32), np.zeros(6, np.uint8))]
+    scan = make_gpu_scan(ctx)
+    for pred in range(6):
+        for lit in (457.9, -0.5, 0.0, -1.5, 2147483647.5):
+            scan(chunks, [0, 1], pred, lit)
+    with pytest.raises(hj.HjError) as e:  # boost::numeric_cast<int32_t>(3e9) throws
+        ctx.scan(relation_of(chunks, [0, 1]), abi.PRED_EQUALS, 3.0e9)
+    assert e.value.status == abi.ERR_INVALID

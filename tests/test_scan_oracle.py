@@ -57,3 +57,62 @@ def test_dereference_emits_the_input_pos_list_entries():
     assert np.array_equal(pos, pl[[0, 1, 3]]) and list(begin) == [0, 3]
     pos, _ = tso.table_scan([chunk], [0], tso.IS_NULL, None, dereference=True)
     assert np.array_equal(pos, pl[[2]])
+
+
+# ---- float / double columns ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("case", FIX["float_cases"], ids=[c["name"] for c in FIX["float_cases"]])
+@pytest.mark.parametrize("encode,style", [("none", "dict"), ("all", "dict"), ("all", "rle")])
+def test_oracle_reproduces_reference_expectation_on_float_columns(case, encode, style):
+    assert sm.run_case(case, FIX["typed_tables"], oracle_scan, encode, style) == sm.expected_of(case), case["cite"]
+
+
+def float_chunks(rng, n_rows, chunk, dtype, encoding, nullable):
+    """Float keys from a small domain incl. -0.0, NaN and +-inf, so that every predicate has matches and ties."""
+    domain = np.array([-np.inf, -7.25, -0.0, 0.0, 0.1, 1.0, 457.7, 457.9, 3.0e9, np.inf, np.nan], dtype=dtype)
+    values = domain[rng.integers(0, len(domain), n_rows)]
+    nulls = (rng.random(n_rows) < 0.1).astype(np.uint8) if nullable else np.zeros(n_rows, np.uint8)
+    out = []
+    for c, lo in enumerate(range(0, max(n_rows, 1), chunk)):
+        v, nl = np.ascontiguousarray(values[lo:lo + chunk]), np.ascontiguousarray(nulls[lo:lo + chunk])
+        enc = encoding if encoding != "mixed" else ("dict" if c % 2 else "value")
+        if enc == "dict":   # a dictionary holds no NaN in these tests: std::sort on NaN keys is undefined in the reference
+            v = np.where(np.isnan(v), dtype(2.5), v).astype(dtype)
+            out.append(sm.dict_encode(v, nl))
+        else:
+            out.append({"kind": "value", "values": v, "nulls": nl if nullable else None})
+    return out
+
+
+FLOAT_LITERALS = (-np.inf, -8, -7.25, 0, 0.1, 457.8, 457.9, 3000000000, 1e30)
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("encoding", ["value", "dict", "mixed"])
+def test_float_scan_equals_a_row_by_row_comparison_in_the_column_type(dtype, encoding):
+    """single_column_table_scan_impl.cpp:36-81: the literal becomes the column type, rows compare with the C++ operator
+    of that type — NaN matches only !=, -0.0 == 0.0, 0.1f != 0.1."""
+    rng = np.random.default_rng(11)
+    ops = {0: lambda a, b: a == b, 1: lambda a, b: a != b, 2: lambda a, b: a < b, 3: lambda a, b: a <= b,
+           4: lambda a, b: a > b, 5: lambda a, b: a >= b}
+    chunks = float_chunks(rng, 700, 256, dtype, encoding, True)
+    for pred, op in ops.items():
+        for lit in FLOAT_LITERALS:
+            pos, begin = tso.table_scan(chunks, list(range(len(chunks))), pred, lit)
+            want = []
+            for cid, ch in enumerate(chunks):
+                v, n = tso.decode(ch)
+                with np.errstate(over="ignore"):
+                    right = dtype(lit)
+                want += [(cid, i) for i in range(len(v)) if not n[i] and op(v[i], right)]
+            assert [tuple(r) for r in pos.tolist()] == want, (pred, lit)
+
+
+def test_floating_literal_on_an_integer_column_is_truncated_like_numeric_cast():
+    """type_cast.hpp:48-57: `a < 457.9` on an int column scans `a < 457`; -0.5 becomes 0; outside the range it throws."""
+    chunks = [{"kind": "value", "values": np.array([455, 456, 457, 458, -1, 0], np.int32), "nulls": None}]
+    pos, _ = tso.table_scan(chunks, [0], tso.LESS_THAN, 457.9)
+    assert pos[:, 1].tolist() == [0, 1, 4, 5]
+    pos, _ = tso.table_scan(chunks, [0], tso.EQUALS, -0.5)
+    assert pos[:, 1].tolist() == [5]
+    with pytest.raises(OverflowError):
+        tso.table_scan(chunks, [0], tso.EQUALS, 3.0e9)
