@@ -97,6 +97,18 @@ class RelationBuilder:
         s.attr, k2 = _ptr_and_keep(attr)
         return self._add(s, k1, k2)
 
+    def add_value_ids(self, chunk_id, attr, null_value_id):
+        """A dictionary chunk of any value type for hj_scan_value_ids: the attribute vector and the NULL value id only —
+        the dictionary stays with the caller."""
+        s = abi.Segment()
+        s.chunk_id, s.n_rows, s.kind = chunk_id, len(attr), abi.SEG_DICT
+        s.key_type = abi.KEY_INT32
+        s.attr_width = {"uint8": 1, "uint16": 2, "int16": 2, "uint32": 4, "int32": 4}[_dtype_name(attr)]
+        s.dict_n = 0
+        s.null_value_id = null_value_id
+        s.attr, k = _ptr_and_keep(attr)
+        return self._add(s, k)
+
     def add_dict_bp128(self, chunk_id, dictionary, stream, n_rows, null_value_id=None):
         """DictionaryColumn<T> whose attribute vector is SimdBp128-compressed: `stream` = the uint128 words as uint32[4*words]."""
         s = abi.Segment()
@@ -274,6 +286,19 @@ class HashJoin:
             bits = int(value)
         self._check(self._l.hj_scan(self._ctx, C.byref(column), predicate, bits, 1 if value is None else 0, slot, flags, stream,
                                     C.byref(info)))
+        return info
+
+    def scan_value_ids(self, column, predicate, bounds=None, slot=0, stream=None):
+        """hj_scan_value_ids: dictionary chunks of any value type scanned on their value ids; bounds = (n_chunks, 2) uint32
+        [lower bound, upper bound] of the literal in every chunk's dictionary, found by the caller."""
+        if isinstance(predicate, str):
+            predicate = abi.PREDICATES[predicate]
+        info = abi.ScanInfo()
+        if bounds is not None:
+            bounds = np.ascontiguousarray(bounds, dtype=np.uint32)
+            assert bounds.size == 2 * column.n_segs
+        self._check(self._l.hj_scan_value_ids(self._ctx, C.byref(column), predicate, None if bounds is None else bounds.ctypes.data,
+                                              slot, 0, stream, C.byref(info)))
         return info
 
     def scan_fetch(self, slot=0):

@@ -96,6 +96,8 @@ SYMBOLS = {
     "hj_release_scratch": (C.c_int, [C.c_void_p]),
     "hj_scan": (C.c_int, [C.c_void_p, C.POINTER(Relation), C.c_int, C.c_int64, C.c_int, C.c_int, C.c_uint32, C.c_void_p,
                           C.POINTER(ScanInfo)]),
+    "hj_scan_value_ids": (C.c_int, [C.c_void_p, C.POINTER(Relation), C.c_int, C.c_void_p, C.c_int, C.c_uint32, C.c_void_p,
+                                    C.POINTER(ScanInfo)]),
     "hj_scan_result_device": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
                                         C.POINTER(C.c_uint64), C.POINTER(C.c_uint32)]),
     "hj_scan_fetch": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_uint64, C.c_void_p]),

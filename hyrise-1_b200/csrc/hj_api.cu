@@ -1247,7 +1247,7 @@ constexpr size_t kPinnedScanTotals = 3616;  // two words inside the pinned readb
 // `value` the literal as V, `id_value` the literal the dictionary bounds are searched with (integer columns).
 template <typename K, typename V>
 int run_scan(hj_ctx* ctx, const hj_relation* column, const hj_relation* original, int predicate, V value, int64_t id_value,
-             int slot, uint32_t scan_flags, cudaStream_t st, hj_scan_info* info) {
+             int slot, uint32_t scan_flags, cudaStream_t st, hj_scan_info* info, const uint32_t* given_bounds = nullptr) {
   PreparedRel pr;
   HJ_TRY(prepare_relation(ctx, column, 1, kScanTile, st, &pr));
   const uint32_t n_segs = pr.meta.n_segs, n_tiles = pr.meta.n_tiles;
@@ -1283,7 +1283,10 @@ int run_scan(hj_ctx* ctx, const hj_relation* column, const hj_relation* original
   }
 
   const uint32_t grid = std::max<uint32_t>(1, std::min<uint32_t>(n_tiles, uint32_t(ctx->n_sms) * 8));
-  if (n_segs) {
+  if (n_segs && given_bounds) {
+    // hj_scan_value_ids: the caller searched the dictionaries (pageable memory: the copy is staged before the call returns)
+    HJ_CUDA(ctx, cudaMemcpyAsync(bounds, given_bounds, size_t(n_segs) * 8, cudaMemcpyHostToDevice, st));
+  } else if (n_segs) {
     k_scan_bounds<<<(n_segs + 127) / 128, 128, 0, st>>>(pr.meta.segs, n_segs, static_cast<long long>(id_value), bounds);
     HJ_LAUNCH_CHECK(ctx, "k_scan_bounds");
   }
@@ -1493,6 +1496,42 @@ int hj_scan(hj_ctx* ctx, const hj_relation* column, int predicate, int64_t value
     }
   }
   return HJ_OK;
+}
+
+int hj_scan_value_ids(hj_ctx* ctx, const hj_relation* column, int predicate, const uint32_t* bounds, int slot,
+                      uint32_t scan_flags, void* cuda_stream, hj_scan_info* out_info) {
+  if (!ctx) return HJ_ERR_INVALID;
+  if (!out_info) return fail(ctx, HJ_ERR_INVALID, "out_info is NULL");
+  std::memset(out_info, 0, sizeof(*out_info));
+  if (slot < 0 || slot >= HJ_SCAN_SLOTS) return fail(ctx, HJ_ERR_INVALID, "scan slot %d outside 0..%d", slot, HJ_SCAN_SLOTS - 1);
+  ctx->scan_valid[slot] = false;
+  const bool null_test = predicate == HJ_PRED_IS_NULL || predicate == HJ_PRED_IS_NOT_NULL;
+  if (!null_test && (predicate < HJ_PRED_EQUALS || predicate > HJ_PRED_GREATER_THAN_EQUALS))
+    return fail(ctx, HJ_ERR_INVALID, "PredicateCondition %d is not a single-column comparison", predicate);
+  if (scan_flags) return fail(ctx, HJ_ERR_INVALID, "hj_scan_value_ids takes no scan flags (data chunks only, no literal)");
+  HJ_TRY(validate_relation(ctx, column, "scan"));
+  if (column->n_segs && !bounds && !null_test) return fail(ctx, HJ_ERR_INVALID, "bounds is NULL");
+  // only the attribute vectors travel: the dictionaries (strings, or anything else sorted) stay with the caller
+  std::vector<hj_segment> segs(column->segs, column->segs + column->n_segs);
+  for (uint32_t i = 0; i < column->n_segs; ++i) {
+    hj_segment& sg = segs[i];
+    if (sg.kind != HJ_SEG_DICT || (sg.attr_width != 1 && sg.attr_width != 2 && sg.attr_width != 4))
+      return fail(ctx, HJ_ERR_INVALID, "scan chunk %u: hj_scan_value_ids takes dictionary chunks with a FixedSizeByteAligned "
+                  "attribute vector (kind %u, width %u)", i, sg.kind, sg.attr_width);
+    sg.values = nullptr;
+    sg.dict_n = 0;
+    sg.key_type = HJ_KEY_INT32;
+  }
+  hj_relation rel = *column;
+  rel.segs = segs.data();
+  HJ_TRY(check_ctx(ctx));
+  cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
+  std::vector<uint32_t> zeros;
+  if (!bounds) {
+    zeros.assign(size_t(column->n_segs) * 2, 0u);
+    bounds = zeros.data();
+  }
+  return run_scan<int32_t, int32_t>(ctx, &rel, &rel, predicate, 0, 0, slot, 0u, st, out_info, bounds);
 }
 
 int hj_scan_result_device(hj_ctx* ctx, int slot, const hj_row_id** pos, const uint32_t** chunk_begin, uint64_t* n_rows,

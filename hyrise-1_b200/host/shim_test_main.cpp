@@ -316,10 +316,21 @@ int main(int argc, char** argv) {
         } else if (op[0] == "scan") {
           const auto in_table = env.at(op[2]);
           const auto column_id = static_cast<ColumnID>(std::stoul(op[3]));
-          const double literal = std::stod(op[5]);
           const std::map<std::string, PredicateCondition> conds = {
               {">=", PredicateCondition::GreaterThanEquals}, {">", PredicateCondition::GreaterThan}, {"=", PredicateCondition::Equals},
-              {"<=", PredicateCondition::LessThanEquals}, {"<", PredicateCondition::LessThan}};
+              {"<=", PredicateCondition::LessThanEquals}, {"<", PredicateCondition::LessThan}, {"!=", PredicateCondition::NotEquals}};
+          if (in_table->column_data_type(column_id) == DataType::String) {
+            // string columns exist on the device path only (dictionary chunks scanned on value ids, hj_scan_value_ids)
+            if (!device_scan) Fail("a scan on a string column needs HJ_SHIM_DEVICE_SCAN=1");
+            auto wrapper = std::make_shared<TableWrapper>(in_table);
+            wrapper->execute();
+            auto scan = std::make_shared<TableScan>(wrapper, column_id, conds.at(op[4]), AllParameterVariant{AllTypeVariant{op[5]}});
+            scan->execute();
+            env[op[1]] = scan->get_output();
+            ++n_device_scans;
+            continue;
+          }
+          const double literal = std::stod(op[5]);
           const bool integral = literal == static_cast<double>(static_cast<int64_t>(literal));
           // HJ_SHIM_DEVICE_SCAN=1: the scans the device operator covers run through opossum::TableScan -> hj_scan, so the
           // case is scan -> join on the GPU; the others keep the semantic helper. (A fractional literal on an INTEGER column

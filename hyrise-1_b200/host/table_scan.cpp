@@ -47,6 +47,27 @@ bool numeric_literal(const AllTypeVariant& v, int64_t* out, bool* is_double) {
   return true;
 }
 
+// String columns: the literal as std::string (type_cast<std::string>: integers as decimal text; floating literals are not
+// reproduced — lexical_cast's digits), and every chunk a DictionaryColumn<std::string> of a data table, so that the scan
+// can run on value ids (hj_scan_value_ids) with the dictionary searched here.
+bool string_literal(const AllTypeVariant& v, std::string* out) {
+  if (const auto* p = std::get_if<std::string>(&v)) { *out = *p; return true; }
+  if (const auto* p = std::get_if<int32_t>(&v)) { *out = std::to_string(*p); return true; }
+  if (const auto* p = std::get_if<int64_t>(&v)) { *out = std::to_string(*p); return true; }
+  return false;
+}
+
+bool all_string_dictionary_chunks(const Table& table, ColumnID column_id) {
+  if (table.type() != TableType::Data) return false;
+  for (ChunkID c = 0; c < table.chunk_count(); ++c) {
+    const auto column = std::dynamic_pointer_cast<const DictionaryColumn<std::string>>(table.get_chunk(c)->get_column(column_id));
+    if (!column) return false;
+    const uint8_t width = column->attribute_vector_raw()->width_bytes();
+    if (width != 1 && width != 2 && width != 4) return false;
+  }
+  return true;
+}
+
 }  // namespace
 
 TableScan::TableScan(const std::shared_ptr<const AbstractOperator>& in, ColumnID left_column_id,
@@ -75,6 +96,13 @@ const std::string TableScan::description(DescriptionMode description_mode) const
 bool TableScan::supported(const Table& table, ColumnID column_id, PredicateCondition predicate_condition,
                           const AllParameterVariant& right_parameter) {
   const DataType type = table.column_data_type(column_id);
+  if (type == DataType::String) {
+    if (!all_string_dictionary_chunks(table, column_id)) return false;
+    if (is_null_predicate(predicate_condition)) return true;
+    if (static_cast<int>(predicate_condition) > static_cast<int>(PredicateCondition::GreaterThanEquals)) return false;
+    std::string text;
+    return !right_parameter.is_column && (variant_is_null(right_parameter.value) || string_literal(right_parameter.value, &text));
+  }
   if (type != DataType::Int && type != DataType::Long && type != DataType::Float && type != DataType::Double) return false;
   if (is_null_predicate(predicate_condition)) return true;
   if (static_cast<int>(predicate_condition) > static_cast<int>(PredicateCondition::GreaterThanEquals)) return false;
@@ -88,8 +116,8 @@ std::shared_ptr<const Table> TableScan::_on_execute() {
   const auto in_table = input_table_left();
   Assert(in_table != nullptr, "TableScan: input has not been executed");
   if (!supported(*in_table, _left_column_id, _predicate_condition, _right_parameter))
-    Fail("TableScan on the device covers numeric columns compared with a numeric literal and IS [NOT] NULL; this scan is "
-         "not supported and there is no CPU fallback");
+    Fail("TableScan on the device covers numeric columns (and dictionary-encoded string columns of data tables) compared with "
+         "a literal and IS [NOT] NULL; this scan is not supported and there is no CPU fallback");
   int64_t literal = 0;
   bool literal_is_double = false;
   const bool null_literal = !is_null_predicate(_predicate_condition) && variant_is_null(_right_parameter.value);
@@ -98,28 +126,66 @@ std::shared_ptr<const Table> TableScan::_on_execute() {
   auto output = std::make_shared<Table>(in_table->column_definitions(), TableType::References);
   if (in_table->chunk_count() == 0) return output;
 
-  // the scanned column, one descriptor per chunk; excluded chunks (table_scan.cpp:93-96) are simply not handed over
-  const hj_relation* all = nullptr;
-  const auto keep_alive = hjhost::flatten_column(*in_table, _left_column_id, &all);
+  const bool string_column = in_table->column_data_type(_left_column_id) == DataType::String;
   const auto excluded = std::unordered_set<ChunkID>{_excluded_chunk_ids.cbegin(), _excluded_chunk_ids.cend()};
   std::vector<hj_segment> segs;
   std::vector<ChunkID> chunk_of_seg;
-  for (uint32_t i = 0; i < all->n_segs; ++i) {
-    if (excluded.count(static_cast<ChunkID>(i))) continue;
-    segs.push_back(all->segs[i]);
-    chunk_of_seg.push_back(static_cast<ChunkID>(i));
-  }
-  hj_relation rel = *all;
-  rel.segs = segs.data();
-  rel.n_segs = static_cast<uint32_t>(segs.size());
-  rel.n_rows = 0;
-  for (const auto& s : segs) rel.n_rows += s.n_rows;
-
   hj_ctx* ctx = hjhost::context();
   hj_scan_info info;
-  if (hj_scan(ctx, &rel, static_cast<int>(_predicate_condition), literal, null_literal ? 1 : 0, kScanSlot,
-              literal_is_double ? HJ_SCAN_VALUE_IS_DOUBLE : 0u, nullptr, &info) != HJ_OK)
-    Fail(std::string("TableScan: ") + hj_last_error(ctx));
+  if (string_column) {
+    // dictionary chunks of strings: the two binary searches per chunk run here (single_column_table_scan_impl.cpp:135-150),
+    // the attribute vectors are scanned on the device
+    std::string text;
+    if (!is_null_predicate(_predicate_condition) && !null_literal) string_literal(_right_parameter.value, &text);
+    std::vector<uint32_t> bounds;
+    uint64_t n_rows = 0;
+    for (ChunkID c = 0; c < in_table->chunk_count(); ++c) {
+      if (excluded.count(c)) continue;
+      const auto column = std::static_pointer_cast<const DictionaryColumn<std::string>>(in_table->get_chunk(c)->get_column(_left_column_id));
+      const auto& dictionary = *column->dictionary();
+      hj_segment sg{};
+      sg.chunk_id = c;
+      sg.n_rows = static_cast<uint32_t>(column->size());
+      sg.kind = HJ_SEG_DICT;
+      sg.key_type = HJ_KEY_INT32;
+      sg.attr = column->attribute_vector_raw()->raw_data();
+      sg.attr_width = column->attribute_vector_raw()->width_bytes();
+      sg.null_value_id = column->null_value_id();
+      segs.push_back(sg);
+      chunk_of_seg.push_back(c);
+      bounds.push_back(static_cast<uint32_t>(std::lower_bound(dictionary.cbegin(), dictionary.cend(), text) - dictionary.cbegin()));
+      bounds.push_back(static_cast<uint32_t>(std::upper_bound(dictionary.cbegin(), dictionary.cend(), text) - dictionary.cbegin()));
+      n_rows += sg.n_rows;
+    }
+    hj_relation rel{};
+    rel.segs = segs.data();
+    rel.n_segs = static_cast<uint32_t>(segs.size());
+    rel.n_rows = n_rows;
+    rel.location = HJ_LOC_HOST;
+    if (null_literal) {
+      // comparing with NULL matches nothing (single_column_table_scan_impl.cpp:25-34)
+      return output;
+    }
+    if (hj_scan_value_ids(ctx, &rel, static_cast<int>(_predicate_condition), bounds.data(), kScanSlot, 0u, nullptr, &info) != HJ_OK)
+      Fail(std::string("TableScan: ") + hj_last_error(ctx));
+  } else {
+    // the scanned column, one descriptor per chunk; excluded chunks (table_scan.cpp:93-96) are simply not handed over
+    const hj_relation* all = nullptr;
+    const auto keep_alive = hjhost::flatten_column(*in_table, _left_column_id, &all);
+    for (uint32_t i = 0; i < all->n_segs; ++i) {
+      if (excluded.count(static_cast<ChunkID>(i))) continue;
+      segs.push_back(all->segs[i]);
+      chunk_of_seg.push_back(static_cast<ChunkID>(i));
+    }
+    hj_relation rel = *all;
+    rel.segs = segs.data();
+    rel.n_segs = static_cast<uint32_t>(segs.size());
+    rel.n_rows = 0;
+    for (const auto& s : segs) rel.n_rows += s.n_rows;
+    if (hj_scan(ctx, &rel, static_cast<int>(_predicate_condition), literal, null_literal ? 1 : 0, kScanSlot,
+                literal_is_double ? HJ_SCAN_VALUE_IS_DOUBLE : 0u, nullptr, &info) != HJ_OK)
+      Fail(std::string("TableScan: ") + hj_last_error(ctx));
+  }
   std::vector<RowID> matches(std::max<uint64_t>(1, info.n_rows));
   std::vector<uint32_t> begin(segs.size() + 1, 0);
   static_assert(sizeof(RowID) == sizeof(hj_row_id), "PosList::data() is handed to hj_scan_fetch");

@@ -329,6 +329,17 @@ typedef struct hj_scan_info {
 int hj_scan(hj_ctx* ctx, const hj_relation* column, int predicate, int64_t value, int value_is_null, int slot,
             uint32_t scan_flags, void* cuda_stream, hj_scan_info* out_info);
 
+/* The same scan for dictionary chunks of ANY value type (strings included), on their value ids alone: the caller
+ * does what SingleColumnTableScanImpl does once per dictionary chunk (:135-150, BaseDictionaryColumn::lower_bound /
+ * upper_bound — two binary searches in the chunk's sorted dictionary, on the host where the strings are) and passes
+ * bounds[2c] = lower bound and bounds[2c+1] = upper bound value id of the literal in chunk c (the dictionary size or
+ * INVALID_VALUE_ID 0xFFFFFFFF when there is no such entry); the device then compares the attribute vectors against
+ * them exactly as hj_scan does (:83-133). Every chunk must be HJ_SEG_DICT with a FixedSizeByteAligned attribute
+ * vector (attr_width 1/2/4) and its null_value_id; `values` / `dict_n` / `key_type` are ignored, the dictionaries
+ * are never copied. bounds may be NULL for IS [NOT] NULL. Results are read like hj_scan's. scan_flags must be 0. */
+int hj_scan_value_ids(hj_ctx* ctx, const hj_relation* column, int predicate, const uint32_t* bounds, int slot,
+                      uint32_t scan_flags, void* cuda_stream, hj_scan_info* out_info);
+
 /* Device pointers to the result in `slot` (valid until the next hj_scan into that slot, hj_scan_release or
  * hj_destroy): pos = hj_row_id[n_rows], chunk_begin = uint32[n_chunks + 1]. */
 int hj_scan_result_device(hj_ctx* ctx, int slot, const hj_row_id** pos, const uint32_t** chunk_begin, uint64_t* n_rows,

@@ -1,4 +1,5 @@
-"""CPU restatement of the reference's single-column TableScan for int / long / float / double columns (numpy). TEST INFRASTRUCTURE: imported
+"""CPU restatement of the reference's single-column TableScan for int / long / float / double columns, and for string
+columns compared with <, <=, =, !=, >=, > (numpy). TEST INFRASTRUCTURE: imported
 only by tests/ — never by the product package (hyrise-1_b200 has no CPU path).
 
 Follows, per chunk, what TableScan::_on_execute dispatches to (src/lib/operators/table_scan.cpp:84-171, _init_scan :173-201):
@@ -54,7 +55,11 @@ def decode(chunk, offsets=None):
         attr = chunk["attr"].astype(np.int64)
         n = attr == chunk["null_value_id"]
         d = chunk["dictionary"]
-        v = np.where(n, 0, d[np.minimum(attr, max(len(d) - 1, 0))] if len(d) else 0).astype(d.dtype if len(d) else np.int64)
+        if len(d):   # NULL decodes to T{} (dictionary_column_iterable.hpp:80): 0, or the empty string
+            v = d[np.minimum(attr, len(d) - 1)].copy()
+            v[n] = d.dtype.type()
+        else:
+            v = np.zeros(len(attr), np.int64)
     if offsets is not None:
         return v[offsets], n[offsets]
     return v, n
@@ -65,6 +70,8 @@ def cast_literal(value, dtype):
     floating column -> the literal as that floating type; integral column with a floating literal ->
     boost::numeric_cast<T>(double): truncation toward zero, bad_numeric_cast outside T's range."""
     dtype = np.dtype(dtype)
+    if dtype.kind == "U":
+        return str(value)   # lexical_cast<std::string>: an integer literal becomes its decimal text
     if dtype.kind == "f":
         return dtype.type(value)
     if isinstance(value, float):
@@ -77,8 +84,9 @@ def cast_literal(value, dtype):
 
 
 def _wide(values):
-    """Integers are compared as int64 (no wrap-around on the literal), floats in the column's own type."""
-    return values if values.dtype.kind == "f" else values.astype(np.int64)
+    """Integers are compared as int64 (no wrap-around on the literal), floats and strings in the column's own type
+    (numpy orders str by code point = std::string's byte order on UTF-8)."""
+    return values.astype(np.int64) if values.dtype.kind in "iu" else values
 
 
 def _scan_value_like(values, is_null, predicate, value):

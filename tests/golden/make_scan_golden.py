@@ -32,6 +32,8 @@ def load_tbl(name):
                 cols[n].append(None)
             elif t.startswith("int") or t.startswith("long"):
                 cols[n].append(int(v))
+            elif t.startswith("string"):
+                cols[n].append(v)
             else:
                 cols[n].append(float(v))
     return {"columns": names, "types": types, "data": cols}
@@ -148,7 +150,47 @@ float_cases = [
                {"column": "b", "predicate": "Equals", "value": 456.7}], "expect_rows": 0},
 ]
 
+# String column scans, src/test/operators/table_scan_string_test.cpp (the comparison predicates; LIKE is out of scope):
+# int_string_like.tbl in chunks of 5, every chunk encoded (:48-53), column b <op> literal, column a of the result
+TS = "src/test/operators/table_scan_string_test.cpp"
+typed_tables["int_string_like"] = load_tbl("int_string_like")
+string_cases = [
+    {"name": "ScanEquals", "cite": f"{TS}:74-80", "predicate": "Equals", "value": "Reeperbahn", "expected": "int_string_like_equals"},
+    {"name": "ScanNotEquals", "cite": f"{TS}:82-89", "predicate": "NotEquals", "value": "Reeperbahn",
+     "expected": "int_string_like_not_equals"},
+    {"name": "ScanLessThan", "cite": f"{TS}:91-97", "predicate": "LessThan", "value": "Schiff", "expected": "int_string_like_less_than"},
+]
+string_cases = [{"name": c["name"], "cite": c["cite"], "table": "int_string_like", "chunk_size": 5, "encode": "all",
+                 "steps": [{"column": "b", "predicate": c["predicate"], "value": c["value"]}], "expect_column": "a",
+                 "expect": load_tbl(c["expected"])["data"]["a"]} for c in string_cases]
+
 with open(os.path.join(HERE, "scan_fixtures.json"), "w") as f:
     json.dump({"source": "generated by tests/golden/make_scan_golden.py from /root/reference/" + T, "tables": tables,
-               "cases": cases, "typed_tables": typed_tables, "float_cases": float_cases}, f, indent=0)
-print(len(cases), "cases,", len(tables), "tables,", len(float_cases), "float cases")
+               "cases": cases, "typed_tables": typed_tables, "float_cases": float_cases, "string_cases": string_cases}, f, indent=0,
+              ensure_ascii=False)
+print(len(cases), "cases,", len(tables), "tables,", len(float_cases), "float cases,", len(string_cases), "string cases")
+
+
+# The same float / string cases for the C++ operator (hyrise-1_b200/host/shim_test, grammar of join_fixtures.txt):
+# opossum::TableScan -> hj_scan / hj_scan_value_ids with HJ_SHIM_DEVICE_SCAN=1
+def tbl_text(name):
+    with open(os.path.join(TABLES, name + ".tbl"), encoding="utf-8") as f:
+        return "@table " + name + "\n" + "".join(l for l in f if l.strip()).rstrip("\n") + "\n@end\n"
+
+
+OPS = {"Equals": "=", "NotEquals": "!=", "LessThan": "<", "LessThanEquals": "<=", "GreaterThan": ">", "GreaterThanEquals": ">="}
+shim_tables = ["int_float", "int_float_filtered", "int_string_like", "int_string_like_equals", "int_string_like_not_equals",
+               "int_string_like_less_than"]
+with open(os.path.join(HERE, "scan_shim_fixtures.txt"), "w", encoding="utf-8") as f:
+    f.write("# GENERATED by tests/golden/make_scan_golden.py from the reference's TableScan tests. Do not edit by hand.\n")
+    for t in shim_tables:
+        f.write(tbl_text(t))
+    f.write(f"@case TableScanTest.DoubleScan {T}:211-221\nbase t int_float 2\nscan s1 t 0 >= 1234\nscan s2 s1 1 < 457.9\n"
+            "expect s2 int_float_filtered\n@end\n")
+    f.write(f"@case TableScanTest.DoubleScanDict {T}:211-221\nbase t int_float 2 dict all\nscan s1 t 0 >= 1234\n"
+            "scan s2 s1 1 < 457.9\nexpect s2 int_float_filtered\n@end\n")
+    for name, pred, lit, expected in (("ScanEquals", "Equals", "Reeperbahn", "int_string_like_equals"),
+                                      ("ScanNotEquals", "NotEquals", "Reeperbahn", "int_string_like_not_equals"),
+                                      ("ScanLessThan", "LessThan", "Schiff", "int_string_like_less_than")):
+        f.write(f"@case TableScanStringTest.{name} {TS}\nbase t int_string_like 5 dict all\nscan s t 1 {OPS[pred]} {lit}\n"
+                f"expect s {expected}\n@end\n")

@@ -23,11 +23,11 @@ PREDICATES = {"Equals": 0, "NotEquals": 1, "LessThan": 2, "LessThanEquals": 3, "
               "Between": 6, "In": 7, "Like": 8, "NotLike": 9, "IsNull": 10, "IsNotNull": 11}
 
 
-TYPE_NAMES = {"int": np.int32, "long": np.int64, "float": np.float32, "double": np.float64}  # load_table.cpp column types
+TYPE_NAMES = {"int": np.int32, "long": np.int64, "float": np.float32, "double": np.float64, "string": str}  # load_table.cpp column types
 
 
 def load_fixtures():
-    with open(os.path.join(ROOT, "tests", "golden", "scan_fixtures.json")) as f:
+    with open(os.path.join(ROOT, "tests", "golden", "scan_fixtures.json"), encoding="utf-8") as f:
         return json.load(f)
 
 

@@ -245,3 +245,51 @@ def test_floating_literal_on_an_integer_column(ctx):
     with pytest.raises(hj.HjError) as e:  # boost::numeric_cast<int32_t>(3e9) throws
         ctx.scan(relation_of(chunks, [0, 1]), abi.PRED_EQUALS, 3.0e9)
     assert e.value.status == abi.ERR_INVALID
+
+
+# ---- string (or any) dictionary columns scanned on value ids: hj_scan_value_ids ---------------------------------------
+def make_gpu_value_id_scan(j):
+    """scan_fn for scan_model.run_case: all chunks must be dictionary chunks; the dictionary search happens here on the
+    host (test_scan_oracle.value_id_bounds), the attribute vectors are scanned on the device."""
+    from test_scan_oracle import value_id_bounds
+
+    def scan(chunks, ids, pred, value):
+        assert all(c["kind"] == "dict" for c in chunks)
+        rb = hj.RelationBuilder(abi.LOC_HOST)
+        for c, cid in zip(chunks, ids):
+            rb.add_value_ids(cid, c["attr"], c["null_value_id"])
+        literal = tso.cast_literal(value, chunks[0]["dictionary"].dtype) if value is not None and chunks else value
+        bounds = value_id_bounds(chunks, literal) if pred < 6 else None
+        info = j.scan_value_ids(rb.build(), pred, bounds)
+        pos, begin = j.scan_fetch()
+        want_pos, want_begin = tso.table_scan(chunks, ids, pred, value)
+        assert info.n_rows == len(pos) and np.array_equal(begin, want_begin) and np.array_equal(pos, want_pos)
+        return pos, begin
+    return scan
+
+
+@unvalidated
+@pytest.mark.parametrize("case", FIX["string_cases"], ids=[c["name"] for c in FIX["string_cases"]])
+def test_reference_string_scan_case_on_gpu(ctx, case):
+    assert sm.run_case(case, FIX["typed_tables"], make_gpu_value_id_scan(ctx), "all") == sm.expected_of(case), case["cite"]
+
+
+@unvalidated
+def test_random_string_dictionary_scans_match_oracle(ctx):
+    from test_scan_oracle import string_chunks
+    rng = np.random.default_rng(77)
+    scan = make_gpu_value_id_scan(ctx)
+    for n_rows, chunk, n_words in [(1, 8, 3), (33, 32, 5), (5000, 4096, 40), (70000, 30000, 300)]:
+        chunks, words = string_chunks(rng, n_rows, chunk, n_words)
+        ids = list(range(len(chunks)))
+        for pred in list(range(6)) + [10, 11]:
+            for lit in ("", str(words[len(words) // 2]), "zzzz", "Xé"):
+                scan(chunks, ids, pred, lit)
+
+
+@unvalidated
+def test_value_id_scan_refuses_other_chunk_kinds(ctx):
+    small = [{"kind": "value", "values": np.arange(10, dtype=np.int32), "nulls": None}]
+    with pytest.raises(hj.HjError) as e:
+        ctx.scan_value_ids(relation_of(small, [0]), abi.PRED_EQUALS, np.zeros((1, 2), np.uint32))
+    assert e.value.status == abi.ERR_INVALID

@@ -116,3 +116,46 @@ def test_floating_literal_on_an_integer_column_is_truncated_like_numeric_cast():
     assert pos[:, 1].tolist() == [5]
     with pytest.raises(OverflowError):
         tso.table_scan(chunks, [0], tso.EQUALS, 3.0e9)
+
+
+# ---- string columns (dictionary chunks are scanned on value ids; the oracle compares the strings) -----------------------
+@pytest.mark.parametrize("case", FIX["string_cases"], ids=[c["name"] for c in FIX["string_cases"]])
+@pytest.mark.parametrize("encode,style", [("none", "dict"), ("all", "dict"), ("all", "rle")])
+def test_oracle_reproduces_reference_expectation_on_string_columns(case, encode, style):
+    assert sm.run_case(case, FIX["typed_tables"], oracle_scan, encode, style) == sm.expected_of(case), case["cite"]
+
+
+def value_id_bounds(chunks, literal):
+    """What the caller of hj_scan_value_ids does per dictionary chunk: BaseDictionaryColumn::lower_bound / upper_bound."""
+    return np.array([[np.searchsorted(c["dictionary"], literal, side="left"), np.searchsorted(c["dictionary"], literal, side="right")]
+                     for c in chunks], dtype=np.uint32).reshape(-1, 2)
+
+
+def string_chunks(rng, n_rows, chunk, n_words, nullable=True):
+    words = np.array(sorted({"".join(rng.choice(list("abcXYZ09 é"), rng.integers(0, 6))) for _ in range(n_words * 3)})[:n_words])
+    values = words[rng.integers(0, len(words), n_rows)]
+    nulls = (rng.random(n_rows) < 0.1).astype(np.uint8) if nullable else np.zeros(n_rows, np.uint8)
+    return [sm.dict_encode(np.ascontiguousarray(values[lo:lo + chunk]), np.ascontiguousarray(nulls[lo:lo + chunk]))
+            for lo in range(0, max(n_rows, 1), chunk)], words
+
+
+def test_value_id_comparison_with_host_side_bounds_equals_comparing_the_strings():
+    """single_column_table_scan_impl.cpp:83-133 needs only (lower bound, upper bound, attribute vector): the rows whose
+    value id passes the id comparison are the rows whose STRING passes the string comparison."""
+    rng = np.random.default_rng(3)
+    chunks, words = string_chunks(rng, 3000, 700, 40)
+    ops = {0: lambda a, b: a == b, 1: lambda a, b: a != b, 2: lambda a, b: a < b, 3: lambda a, b: a <= b,
+           4: lambda a, b: a > b, 5: lambda a, b: a >= b}
+    for lit in ["", "a", str(words[7]), str(words[-1]), "zzzz", "Xé"]:
+        bounds = value_id_bounds(chunks, lit)
+        for pred, op in ops.items():
+            pos, _ = tso.table_scan(chunks, list(range(len(chunks))), pred, lit)
+            want = []
+            for cid, (c, (lb, ub)) in enumerate(zip(chunks, bounds.tolist())):
+                attr = c["attr"].astype(np.int64)
+                ok = {0: (attr == lb) & (lb != ub), 1: (attr != lb) | (lb == ub), 2: attr < lb, 3: attr < ub, 4: attr >= ub,
+                      5: attr >= lb}[pred] & (attr != c["null_value_id"])
+                want += [(cid, int(i)) for i in np.flatnonzero(ok)]
+                v, n = tso.decode(c)
+                assert [int(i) for i in np.flatnonzero(ok)] == [i for i in range(len(v)) if not n[i] and op(str(v[i]), lit)]
+            assert [tuple(r) for r in pos.tolist()] == want, (pred, lit)

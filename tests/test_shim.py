@@ -38,3 +38,19 @@ def test_shim_replays_reference_cases_with_device_scans(built):
     assert "53 cases run, 0 failed, 0 out of scope" in r.stdout, r.stdout[-1000:]
     n = int(r.stdout.rsplit("shim_test: ", 1)[1].split(" scans ran on the device")[0])
     assert n >= 1, r.stdout[-500:]
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(os.environ.get("HJ_RUN_UNVALIDATED") != "1",
+                    reason="float / string scans of opossum::TableScan have not run on a GPU yet (set HJ_RUN_UNVALIDATED=1)")
+def test_shim_replays_reference_float_and_string_scan_cases(built):
+    """table_scan_test.cpp DoubleScan (float column behind a reference table) and table_scan_string_test.cpp ScanEquals /
+    ScanNotEquals / ScanLessThan (dictionary-encoded string column: dictionary searched on the host, attribute vectors
+    scanned on the device by hj_scan_value_ids) through the C++ operator."""
+    env = dict(os.environ, HJ_SHIM_DEVICE_SCAN="1")
+    fixtures = os.path.join(ROOT, "tests", "golden", "scan_shim_fixtures.txt")
+    r = subprocess.run([EXE, fixtures], capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stdout[-4000:] + r.stderr[-2000:]
+    assert "5 cases run, 0 failed" in r.stdout, r.stdout[-1000:]
+    n = int(r.stdout.rsplit("shim_test: ", 1)[1].split(" scans ran on the device")[0])
+    assert n == 7, r.stdout[-500:]
