@@ -301,6 +301,13 @@ class HashJoin:
                                               slot, 0, stream, C.byref(info)))
         return info
 
+    def gather_column(self, device_pos, n_rows, column, stream=None):
+        """hj_gather_column: (values device ptr, nulls device ptr, key type) of `column` at the rows of a device PosList."""
+        v, n, t = C.c_void_p(), C.c_void_p(), C.c_int()
+        self._check(self._l.hj_gather_column(self._ctx, device_pos, n_rows, C.byref(column), stream, C.byref(v), C.byref(n),
+                                             C.byref(t)))
+        return v.value, n.value, t.value
+
     def scan_fetch(self, slot=0):
         """(pos (n, 2) uint32 [chunk_id, chunk_offset], chunk_begin (n_chunks + 1,) uint32) of the scan result in `slot`."""
         _, _, n, n_chunks = self.scan_result_device(slot)

@@ -98,6 +98,8 @@ SYMBOLS = {
                           C.POINTER(ScanInfo)]),
     "hj_scan_value_ids": (C.c_int, [C.c_void_p, C.POINTER(Relation), C.c_int, C.c_void_p, C.c_int, C.c_uint32, C.c_void_p,
                                     C.POINTER(ScanInfo)]),
+    "hj_gather_column": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(Relation), C.c_void_p, C.POINTER(C.c_void_p),
+                                   C.POINTER(C.c_void_p), C.POINTER(C.c_int)]),
     "hj_scan_result_device": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
                                         C.POINTER(C.c_uint64), C.POINTER(C.c_uint32)]),
     "hj_scan_fetch": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_uint64, C.c_void_p]),

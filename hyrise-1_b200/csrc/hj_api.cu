@@ -145,7 +145,8 @@ struct hj_ctx {
   // receive sets: 0 = build, 1 = probe (or probe slices 0, 2, ..), 2 = probe slices 1, 3, ..
   DevBuf xchg_counts[2], xchg_cnt_dev, xchg_send_keys[2], xchg_send_rids[2], xchg_send_nulls[2], xchg_recv_keys[3],
       xchg_recv_rids[3], xchg_recv_nulls[3];
-  DevBuf ref_arena[2], ref_out[2];  // REFERENCE segments: staged referenced columns + PosLists / gathered keys + flags
+  DevBuf ref_arena[3], ref_out[3];  // REFERENCE segments: staged referenced columns + PosLists / gathered keys + flags
+                                    // ([0] build, [1] probe / scan, [2] hj_gather_column)
   uint64_t ref_h2d_bytes = 0;
   DevBuf acc_build, acc_probe;      // sliced sharded join: the slices' PosLists, appended
   cudaEvent_t ev_x[2] = {};         // sliced sharded join: slice set exchanged (recorded on copy_in, the exchange stream)
@@ -171,7 +172,7 @@ struct hj_ctx {
                       &out_build[0], &out_build[1], &out_probe[0], &out_probe[1], &misc, &xchg_counts[0], &xchg_counts[1], &xchg_cnt_dev, &xchg_send_keys[0],
                       &xchg_send_keys[1], &xchg_send_rids[0], &xchg_send_rids[1], &xchg_send_nulls[0], &xchg_send_nulls[1],
                       &xchg_recv_keys[0], &xchg_recv_keys[1], &xchg_recv_rids[0], &xchg_recv_rids[1], &xchg_recv_nulls[0],
-                      &xchg_recv_nulls[1], &xchg_recv_keys[2], &xchg_recv_rids[2], &xchg_recv_nulls[2], &acc_build, &acc_probe, &ref_arena[0], &ref_arena[1], &ref_out[0], &ref_out[1],
+                      &xchg_recv_nulls[1], &xchg_recv_keys[2], &xchg_recv_rids[2], &xchg_recv_nulls[2], &acc_build, &acc_probe, &ref_arena[0], &ref_arena[1], &ref_arena[2], &ref_out[0], &ref_out[1], &ref_out[2],
                       &xchg_hdl_dev, &scan_bounds, &scan_mask, &scan_tile_count, &scan_tile_base, &scan_ref_ptrs, &scan_totals})
       all_bufs.push_back(b);
   }
@@ -1532,6 +1533,57 @@ int hj_scan_value_ids(hj_ctx* ctx, const hj_relation* column, int predicate, con
     bounds = zeros.data();
   }
   return run_scan<int32_t, int32_t>(ctx, &rel, &rel, predicate, 0, 0, slot, 0u, st, out_info, bounds);
+}
+
+// ------------------------------------------------------------------------------------------------ column values at a PosList
+int hj_gather_column(hj_ctx* ctx, const hj_row_id* device_pos, uint64_t n_rows, const hj_relation* column, void* cuda_stream,
+                     const void** out_values, const uint8_t** out_nulls, int* out_key_type) {
+  if (!ctx) return HJ_ERR_INVALID;
+  if (!out_values || !out_nulls) return fail(ctx, HJ_ERR_INVALID, "out_values / out_nulls is NULL");
+  *out_values = nullptr;
+  *out_nulls = nullptr;
+  if (!column) return fail(ctx, HJ_ERR_INVALID, "column is NULL");
+  if (column->location != HJ_LOC_DEVICE)
+    return fail(ctx, HJ_ERR_INVALID, "hj_gather_column reads a device-resident column through a device-resident PosList");
+  if (n_rows && !device_pos) return fail(ctx, HJ_ERR_INVALID, "device_pos is NULL");
+  if (n_rows >= 0xFFFFFFFFull) return fail(ctx, HJ_ERR_TOO_LARGE, "PosList of %llu rows (limit 2^32-2)", (unsigned long long)n_rows);
+  // the column's type: the widest of its chunks, like a join key column (JoinHashTraits order: double > float > long > int)
+  uint32_t type = HJ_KEY_INT32;
+  for (uint32_t i = 0; i < column->n_segs; ++i) {
+    const uint8_t k = column->segs[i].key_type;
+    if (k == HJ_KEY_DOUBLE) type = HJ_KEY_DOUBLE;
+    else if (k == HJ_KEY_FLOAT && type != HJ_KEY_DOUBLE) type = HJ_KEY_FLOAT;
+    else if (k == HJ_KEY_INT64 && type == HJ_KEY_INT32) type = HJ_KEY_INT64;
+  }
+  for (uint32_t i = 0; i < column->n_segs; ++i)
+    if (column->segs[i].key_type != type)
+      return fail(ctx, HJ_ERR_INVALID, "column chunk %u has key type %u, others %u: one column has one type", i, column->segs[i].key_type, type);
+  // a one-chunk reference table over `column` whose PosList is device_pos: exactly what a join input looks like (N1)
+  hj_segment ref{};
+  ref.chunk_id = 0;
+  ref.n_rows = static_cast<uint32_t>(n_rows);
+  ref.kind = HJ_SEG_REFERENCE;
+  ref.key_type = static_cast<uint8_t>(type);
+  ref.values = column;
+  ref.attr = device_pos;
+  hj_relation rel{};
+  rel.segs = &ref;
+  rel.n_segs = 1;
+  rel.location = HJ_LOC_DEVICE;
+  rel.n_rows = n_rows;
+  HJ_TRY(validate_relation(ctx, &rel, "gather"));
+  HJ_TRY(check_ctx(ctx));
+  cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
+  auto* flag = reinterpret_cast<uint32_t*>(static_cast<char*>(ctx->pinned) + kPinnedRefFlags) + 2;
+  *flag = 0;
+  RefRewrite rw;
+  HJ_TRY(gather_references(ctx, &rel, 2, st, &rw, type));
+  HJ_CUDA(ctx, cudaStreamSynchronize(st));
+  if (*flag) return fail(ctx, HJ_ERR_INVALID, "gather: a PosList entry points outside the column");
+  *out_values = rw.segs[0].values;
+  *out_nulls = rw.segs[0].nulls;
+  if (out_key_type) *out_key_type = static_cast<int>(type);
+  return HJ_OK;
 }
 
 int hj_scan_result_device(hj_ctx* ctx, int slot, const hj_row_id** pos, const uint32_t** chunk_begin, uint64_t* n_rows,

@@ -352,6 +352,19 @@ int hj_scan_fetch(hj_ctx* ctx, int slot, hj_row_id* pos, uint64_t capacity_rows,
  * touched by hj_release_scratch. */
 int hj_scan_release(hj_ctx* ctx, int slot);
 
+/* ---- reading a column through a PosList on the device (consumers of the join) ---------------- */
+/* The values of `column` (a DEVICE-resident data-table column: VALUE / DICT / FOR / RLE chunks, segs[i] = chunk i) at
+ * the rows of a device-resident PosList — what every operator after the join (Aggregate, Projection, the next
+ * join) does first when it reads a ReferenceColumn (reference_column_iterable.hpp:30-75: per RowID the referenced
+ * chunk's value or NULL; NULL_ROW_ID = NULL). `device_pos` is typically a side of hj_result_device or a result of
+ * hj_scan_result_device. Output, in device memory owned by ctx and valid until the next hj_gather_column /
+ * hj_release_scratch / hj_destroy: out_values = n_rows values of the column's type (*out_key_type: int32 / int64 as
+ * such, float / double as their IEEE bit patterns in 4 / 8 bytes, NaNs canonicalised; 0 where NULL) and out_nulls =
+ * one byte per row. Runs the same kernel the join uses for REFERENCE key columns (k_gather_refs).
+ * HJ_ERR_INVALID if a RowID points outside the column. */
+int hj_gather_column(hj_ctx* ctx, const hj_row_id* device_pos, uint64_t n_rows, const hj_relation* column,
+                     void* cuda_stream, const void** out_values, const uint8_t** out_nulls, int* out_key_type);
+
 /* ---- multi-GPU (one process per GPU) ---------------------------------------- */
 /* The exchange has no reference counterpart: both relations are split by the high bits of the
  * key hash so that every key's rows meet on one rank, exchanged with an NCCL all-to-all over

@@ -293,3 +293,81 @@ def test_value_id_scan_refuses_other_chunk_kinds(ctx):
     with pytest.raises(hj.HjError) as e:
         ctx.scan_value_ids(relation_of(small, [0]), abi.PRED_EQUALS, np.zeros((1, 2), np.uint32))
     assert e.value.status == abi.ERR_INVALID
+
+
+# ---- hj_gather_column: a column read through a device PosList (what the join's consumers do first) ----------------------
+@unvalidated
+@pytest.mark.parametrize("encoding", ["value", "dict"])
+@pytest.mark.parametrize("dtype", [np.int32, np.int64, np.float32])
+def test_gather_column_at_the_join_result(ctx, dtype, encoding):
+    """After an Inner join the key column of either side, read through that side's PosList, holds the SAME keys row by
+    row (the join's defining property, at any size), and each equals the host-side gather of the fetched RowIDs. A second
+    (payload) column of the probe table, dictionary-encoded with NULLs, is read the same way."""
+    import torch
+    rng = np.random.default_rng(23)
+    chunk = 1 << 15
+    dev = torch.device("cuda", 0)
+    bk = (rng.permutation(200_000) + 1).astype(dtype)
+    pk = rng.integers(1, 260_001, 700_000).astype(dtype)
+    payload = rng.integers(-50, 50, len(pk)).astype(np.int32)
+    payload_null = (rng.random(len(pk)) < 0.2).astype(np.uint8)
+    keep = []
+
+    def device_column(values, nulls, enc):
+        rb = hj.RelationBuilder(abi.LOC_DEVICE)
+        for c, lo in enumerate(range(0, len(values), chunk)):
+            v, nl = values[lo:lo + chunk].copy(), nulls[lo:lo + chunk].copy()
+            if enc == "dict":
+                d = sm.dict_encode(v, nl)
+                t = [torch.from_numpy(d["dictionary"]).to(dev), torch.from_numpy(d["attr"].astype(np.int32)).to(dev)]
+                rb.add_dict(c, t[0], t[1], d["null_value_id"])
+            else:
+                t = [torch.from_numpy(v).to(dev), torch.from_numpy(nl).to(dev)]
+                rb.add_value(c, t[0], t[1])
+            keep.extend(t)
+        return rb.build()
+
+    def device_array(ptr, n, typestr):
+        class W:
+            __cuda_array_interface__ = {"shape": (max(n, 1),), "typestr": typestr, "data": (ptr, False), "version": 2}
+        return torch.as_tensor(W(), device=dev)[:n].cpu().numpy()
+
+    b_col = device_column(bk, np.zeros(len(bk), np.uint8), encoding)
+    p_col = device_column(pk, np.zeros(len(pk), np.uint8), encoding)
+    pay_col = device_column(payload, payload_null, "dict")
+    info = ctx.join(b_col, p_col, abi.MODE_INNER)
+    assert info.n_rows == int((pk <= 200_000).sum())
+    b_ptr, p_ptr, n = ctx.result_device()
+    gb, gp = ctx.fetch()
+    typestr = {np.int32: "<i4", np.int64: "<i8", np.float32: "<f4"}[dtype]
+    got = {}
+    for name, ptr, col in (("build", b_ptr, b_col), ("probe", p_ptr, p_col)):
+        v, nl, kt = ctx.gather_column(ptr, n, col)
+        assert kt == key_type_of({"kind": "value", "values": bk})
+        got[name] = device_array(v, n, typestr)       # copied before the next gather reuses the buffer
+        assert not device_array(nl, n, "|u1").any()
+    assert np.array_equal(got["build"], got["probe"])
+    assert np.array_equal(got["probe"], pk[gp[:, 0].astype(np.int64) * chunk + gp[:, 1]])
+    assert np.array_equal(got["build"], bk[gb[:, 0].astype(np.int64) * chunk + gb[:, 1]])
+    v, nl, kt = ctx.gather_column(p_ptr, n, pay_col)
+    rows = gp[:, 0].astype(np.int64) * chunk + gp[:, 1]
+    want_null = payload_null[rows]
+    assert kt == abi.KEY_INT32 and np.array_equal(device_array(nl, n, "|u1"), want_null)
+    assert np.array_equal(device_array(v, n, "<i4"), np.where(want_null, 0, payload[rows]))
+
+
+@unvalidated
+def test_gather_column_reports_row_ids_outside_the_column(ctx):
+    import torch
+    dev = torch.device("cuda", 0)
+    t = torch.arange(100, dtype=torch.int32, device=dev)
+    col = hj.RelationBuilder(abi.LOC_DEVICE).add_value(0, t).build()
+    pos = torch.tensor([[0, 5], [0, 100]], dtype=torch.int32, device=dev)   # offset 100 is one past the end
+    with pytest.raises(hj.HjError) as e:
+        ctx.gather_column(pos.data_ptr(), 2, col)
+    assert e.value.status == abi.ERR_INVALID
+    null_row = torch.tensor([[0, 7], [-1, -1]], dtype=torch.int32, device=dev)  # NULL_ROW_ID reads as NULL
+    v, nl, _ = ctx.gather_column(null_row.data_ptr(), 2, col)
+    class W:
+        __cuda_array_interface__ = {"shape": (2,), "typestr": "|u1", "data": (nl, False), "version": 2}
+    assert torch.as_tensor(W(), device=dev).cpu().tolist() == [0, 1]
