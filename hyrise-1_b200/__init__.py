@@ -308,6 +308,19 @@ class HashJoin:
                                              C.byref(t)))
         return v.value, n.value, t.value
 
+    def aggregate_column(self, device_values, device_nulls, n_rows, key_type, stream=None):
+        """hj_aggregate_column: COUNT / SUM / MIN / MAX (and AVG = sum / count) of a device column, as a dict with the
+        reference's result types; SUM / MIN / MAX / AVG are None when every row is NULL (aggregate.cpp:635-642)."""
+        a = abi.Aggregate()
+        self._check(self._l.hj_aggregate_column(self._ctx, device_values, device_nulls, n_rows, key_type, stream, C.byref(a)))
+        some = a.n_values > 0
+        floating = bool(a.is_floating)
+        return {"count_rows": a.n_rows, "count": a.n_values,
+                "sum": None if not some else (a.sum_double if floating else a.sum_int),
+                "min": None if not some else (a.min_double if floating else a.min_int),
+                "max": None if not some else (a.max_double if floating else a.max_int),
+                "avg": None if not some else a.sum_double / a.n_values}
+
     def scan_fetch(self, slot=0):
         """(pos (n, 2) uint32 [chunk_id, chunk_offset], chunk_begin (n_chunks + 1,) uint32) of the scan result in `slot`."""
         _, _, n, n_chunks = self.scan_result_device(slot)

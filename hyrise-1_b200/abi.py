@@ -56,6 +56,12 @@ class ResultInfo(C.Structure):
                 ("n_probe_passes", C.c_uint32), ("n_probe_slices", C.c_uint32)]
 
 
+class Aggregate(C.Structure):
+    _fields_ = [("n_rows", C.c_uint64), ("n_values", C.c_uint64), ("is_floating", C.c_int32), ("reserved", C.c_int32),
+                ("sum_int", C.c_int64), ("sum_double", C.c_double), ("min_int", C.c_int64), ("max_int", C.c_int64),
+                ("min_double", C.c_double), ("max_double", C.c_double)]
+
+
 class ScanInfo(C.Structure):
     _fields_ = [("n_rows", C.c_uint64), ("n_chunks", C.c_uint32), ("n_nonempty_chunks", C.c_uint32)]
 
@@ -100,6 +106,7 @@ SYMBOLS = {
                                     C.POINTER(ScanInfo)]),
     "hj_gather_column": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(Relation), C.c_void_p, C.POINTER(C.c_void_p),
                                    C.POINTER(C.c_void_p), C.POINTER(C.c_int)]),
+    "hj_aggregate_column": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p, C.POINTER(Aggregate)]),
     "hj_scan_result_device": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
                                         C.POINTER(C.c_uint64), C.POINTER(C.c_uint32)]),
     "hj_scan_fetch": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_uint64, C.c_void_p]),

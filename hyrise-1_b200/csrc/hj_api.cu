@@ -13,6 +13,7 @@
 #include "hj_kernels.cuh"
 #include "hj_fused.cuh"
 #include "hj_scan.cuh"
+#include "hj_aggregate.cuh"
 
 using namespace hj;
 
@@ -157,6 +158,7 @@ struct hj_ctx {
   bool p2p_ok = false;
   // TableScan (N4): scratch (freed by hj_release_scratch) and the result slots (owned by the scan's caller)
   DevBuf scan_bounds, scan_mask, scan_tile_count, scan_tile_base, scan_ref_ptrs, scan_totals;
+  DevBuf agg_partials;  // hj_aggregate_column: one AggPartial per CTA + the folded result
   DevBuf scan_pos[HJ_SCAN_SLOTS], scan_chunk_begin[HJ_SCAN_SLOTS];
   uint64_t scan_rows[HJ_SCAN_SLOTS] = {};
   uint32_t scan_chunks[HJ_SCAN_SLOTS] = {};
@@ -173,7 +175,7 @@ struct hj_ctx {
                       &xchg_send_keys[1], &xchg_send_rids[0], &xchg_send_rids[1], &xchg_send_nulls[0], &xchg_send_nulls[1],
                       &xchg_recv_keys[0], &xchg_recv_keys[1], &xchg_recv_rids[0], &xchg_recv_rids[1], &xchg_recv_nulls[0],
                       &xchg_recv_nulls[1], &xchg_recv_keys[2], &xchg_recv_rids[2], &xchg_recv_nulls[2], &acc_build, &acc_probe, &ref_arena[0], &ref_arena[1], &ref_arena[2], &ref_out[0], &ref_out[1], &ref_out[2],
-                      &xchg_hdl_dev, &scan_bounds, &scan_mask, &scan_tile_count, &scan_tile_base, &scan_ref_ptrs, &scan_totals})
+                      &xchg_hdl_dev, &scan_bounds, &scan_mask, &scan_tile_count, &scan_tile_base, &scan_ref_ptrs, &scan_totals, &agg_partials})
       all_bufs.push_back(b);
   }
 };
@@ -1242,7 +1244,7 @@ int check_ctx(hj_ctx* ctx) {
 
 // ------------------------------------------------------------------------------------------------ TableScan (N4)
 
-constexpr size_t kPinnedScanTotals = 3616;  // two words inside the pinned readback area (behind kPinnedRefFlags)
+constexpr size_t kPinnedScanTotals = 3616, kPinnedAggregate = 3648;  // + one AggPartial (56 B), below kPinnedCounts  // two words inside the pinned readback area (behind kPinnedRefFlags)
 
 // K: integer type of the stored keys; V: type the comparison runs in (= K, or float / double over their bit patterns);
 // `value` the literal as V, `id_value` the literal the dictionary bounds are searched with (integer columns).
@@ -1583,6 +1585,56 @@ int hj_gather_column(hj_ctx* ctx, const hj_row_id* device_pos, uint64_t n_rows, 
   *out_values = rw.segs[0].values;
   *out_nulls = rw.segs[0].nulls;
   if (out_key_type) *out_key_type = static_cast<int>(type);
+  return HJ_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ ungrouped aggregates
+int hj_aggregate_column(hj_ctx* ctx, const void* device_values, const uint8_t* device_nulls, uint64_t n_rows, int key_type,
+                        void* cuda_stream, hj_aggregate* out) {
+  if (!ctx) return HJ_ERR_INVALID;
+  if (!out) return fail(ctx, HJ_ERR_INVALID, "out is NULL");
+  std::memset(out, 0, sizeof(*out));
+  if (key_type < HJ_KEY_INT32 || key_type > HJ_KEY_DOUBLE) return fail(ctx, HJ_ERR_INVALID, "key type %d", key_type);
+  if (n_rows && !device_values) return fail(ctx, HJ_ERR_INVALID, "device_values is NULL");
+  HJ_TRY(check_ctx(ctx));
+  cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
+  const uint32_t grid = static_cast<uint32_t>(std::max<uint64_t>(1, std::min<uint64_t>((n_rows + kAggThreads - 1) / kAggThreads,
+                                                                                      uint64_t(ctx->n_sms) * 8)));
+  HJ_TRY(ensure(ctx, ctx->agg_partials, (size_t(grid) + 1) * sizeof(AggPartial)));
+  auto* partials = static_cast<AggPartial*>(ctx->agg_partials.p);
+  switch (key_type) {
+    case HJ_KEY_INT32:
+      k_aggregate_partial<int32_t><<<grid, kAggThreads, 0, st>>>(static_cast<const int32_t*>(device_values), device_nulls, n_rows, partials + 1);
+      break;
+    case HJ_KEY_INT64:
+      k_aggregate_partial<int64_t><<<grid, kAggThreads, 0, st>>>(static_cast<const int64_t*>(device_values), device_nulls, n_rows, partials + 1);
+      break;
+    case HJ_KEY_FLOAT:
+      k_aggregate_partial<float><<<grid, kAggThreads, 0, st>>>(static_cast<const float*>(device_values), device_nulls, n_rows, partials + 1);
+      break;
+    default:
+      k_aggregate_partial<double><<<grid, kAggThreads, 0, st>>>(static_cast<const double*>(device_values), device_nulls, n_rows, partials + 1);
+  }
+  HJ_LAUNCH_CHECK(ctx, "k_aggregate_partial");
+  k_aggregate_final<<<1, 32, 0, st>>>(partials + 1, grid, partials);
+  HJ_LAUNCH_CHECK(ctx, "k_aggregate_final");
+  auto* host = reinterpret_cast<AggPartial*>(static_cast<char*>(ctx->pinned) + kPinnedAggregate);
+  HJ_CUDA(ctx, cudaMemcpyAsync(host, partials, sizeof(AggPartial), cudaMemcpyDeviceToHost, st));
+  HJ_CUDA(ctx, cudaStreamSynchronize(st));
+  const bool floating = key_type >= HJ_KEY_FLOAT;
+  out->n_rows = n_rows;
+  out->n_values = host->n_values;
+  out->is_floating = floating ? 1 : 0;
+  out->sum_int = floating ? 0 : host->sum_i;
+  // AVG accumulates in double for every column type (aggregate_traits.hpp:40-46); for an integer column the int64 sum is
+  // that double sum exactly as long as it stays below 2^53
+  out->sum_double = floating ? host->sum_d : static_cast<double>(host->sum_i);
+  if (host->n_values) {
+    out->min_int = floating ? 0 : host->min_i;
+    out->max_int = floating ? 0 : host->max_i;
+    out->min_double = floating ? host->min_d : static_cast<double>(host->min_i);
+    out->max_double = floating ? host->max_d : static_cast<double>(host->max_i);
+  }
   return HJ_OK;
 }
 

@@ -365,6 +365,28 @@ int hj_scan_release(hj_ctx* ctx, int slot);
 int hj_gather_column(hj_ctx* ctx, const hj_row_id* device_pos, uint64_t n_rows, const hj_relation* column,
                      void* cuda_stream, const void** out_values, const uint8_t** out_nulls, int* out_key_type);
 
+/* Ungrouped aggregates of a column in device memory (typically hj_gather_column's output: the column of the joined
+ * rows), all from one pass: what Aggregate computes per aggregate column when there are no GROUP BY columns
+ * (operators/aggregate.cpp:203-252 with the functors :141-201 and result types aggregate_traits.hpp:16-66). */
+typedef struct hj_aggregate {
+  uint64_t n_rows;     /* COUNT(*)                                                                          */
+  uint64_t n_values;   /* COUNT(column): rows that are not NULL                                             */
+  int32_t is_floating; /* the column is float / double: read the *_double fields; else the *_int fields     */
+  int32_t reserved;
+  int64_t sum_int;     /* SUM of an int32 / int64 column, int64 arithmetic (wraps like the reference)       */
+  double sum_double;   /* SUM of a float / double column in double; for integer columns (double)sum_int.    */
+                       /* AVG = sum_double / n_values (aggregate.cpp:688-712)                               */
+  int64_t min_int, max_int;       /* MIN / MAX of an integer column                                         */
+  double min_double, max_double;  /* MIN / MAX of a float / double column (float values widened exactly)    */
+} hj_aggregate;
+/* device_values: n_rows values of type key_type (float / double as IEEE values or their bit patterns — the same
+ * bytes); device_nulls: one byte per row or NULL. With n_values == 0 SUM / MIN / MAX / AVG are NULL in the
+ * reference (:635-642) and the sum/min/max fields are 0. Double sums are folded in a fixed order (reproducible run
+ * to run) that is not the reference's row order: they agree up to rounding. NaN values: unspecified, as in the
+ * reference (it keeps a NaN only when it comes first). */
+int hj_aggregate_column(hj_ctx* ctx, const void* device_values, const uint8_t* device_nulls, uint64_t n_rows,
+                        int key_type, void* cuda_stream, hj_aggregate* out);
+
 /* ---- multi-GPU (one process per GPU) ---------------------------------------- */
 /* The exchange has no reference counterpart: both relations are split by the high bits of the
  * key hash so that every key's rows meet on one rank, exchanged with an NCCL all-to-all over

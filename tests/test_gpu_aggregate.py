@@ -1,0 +1,140 @@
+"""Ungrouped aggregates on the device (hj_aggregate_column) through the C ABI: the reference's own cases —
+on the data table and, like its test_output, behind a TableScan (device scan -> hj_gather_column -> hj_aggregate_column,
+nothing but the one result row leaves the GPU) — and randomized columns against the oracle. Integer results, counts,
+MIN and MAX are exact; double sums are folded in another order than the reference's row order and must agree to 1e-12
+relative (tolerance of this test; the reference's own table comparison allows 1e-4, testing_assert.cpp:21).
+
+Written after the round's GPU minutes were spent: skipped unless HJ_RUN_UNVALIDATED=1."""
+import importlib
+import os
+import sys
+
+import numpy as np
+import pytest
+
+import aggregate_model as am
+from oracle import aggregate_oracle as ao
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+hj = importlib.import_module("hyrise-1_b200")
+abi = hj.abi
+pytestmark = [pytest.mark.gpu,
+              pytest.mark.skipif(os.environ.get("HJ_RUN_UNVALIDATED") != "1",
+                                 reason="hj_aggregate_column has not run on a GPU yet (set HJ_RUN_UNVALIDATED=1)")]
+FIX = am.load_fixtures()
+KEY_TYPES = {"int32": abi.KEY_INT32, "int64": abi.KEY_INT64, "float32": abi.KEY_FLOAT, "float64": abi.KEY_DOUBLE}
+SUM_RTOL = 1e-12
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    j = hj.HashJoin(device=0)
+    yield j
+    j.close()
+
+
+def device_column(values, is_null, chunk):
+    """A device-resident value column in chunks of `chunk` rows: (relation, tensors to keep alive)."""
+    import torch
+    dev = torch.device("cuda", 0)
+    rb, keep = hj.RelationBuilder(abi.LOC_DEVICE), []
+    for c, lo in enumerate(range(0, max(len(values), 1), chunk)):
+        v = torch.from_numpy(values[lo:lo + chunk].copy()).to(dev)
+        z = torch.from_numpy(is_null[lo:lo + chunk].copy()).to(dev)
+        keep += [v, z]
+        rb.add_value(c, v, z)
+    return rb.build(), keep
+
+
+def close_enough(got, want):
+    for k in ("count_rows", "count", "min", "max"):
+        assert got[k] == want[k], (k, got[k], want[k])
+    for k in ("sum", "avg"):
+        if want[k] is None or isinstance(want[k], int):
+            assert got[k] == want[k], (k, got[k], want[k])
+        else:
+            assert got[k] == pytest.approx(want[k], rel=SUM_RTOL, abs=0.0), (k, got[k], want[k])
+
+
+@pytest.mark.parametrize("case", FIX["cases"], ids=[c["name"] for c in FIX["cases"]])
+@pytest.mark.parametrize("variant", [0, 1], ids=["data", "reference"])
+def test_reference_aggregate_case_on_gpu(ctx, case, variant):
+    table = FIX["tables"][case["table"]]
+    scans = am.scans_of(case)[variant]
+    v, z = am.column_of(table, case["column"])
+    col, keep = device_column(v, z, case["chunk_size"])
+    n_rows = len(v)
+    if not scans:
+        # the data table itself: all rows in chunk order = the identity PosList
+        import torch
+        pos = torch.tensor([[c, o] for c, lo in enumerate(range(0, n_rows, case["chunk_size"]))
+                            for o in range(min(case["chunk_size"], n_rows - lo))], dtype=torch.int32, device="cuda:0").reshape(-1, 2)
+        pos_ptr, n = pos.data_ptr(), n_rows
+    else:
+        # TableScan chain on the device; every scan after the first reads its column through the previous PosList
+        rel = None
+        for i, s in enumerate(scans):
+            sv, sz = am.column_of(table, s["column"])
+            scol, k = device_column(sv, sz, case["chunk_size"])
+            keep += k
+            if i == 0:
+                ctx.scan(scol, s["predicate"], s["value"], slot=i)
+            else:
+                ptr, _, n_prev, _ = ctx.scan_result_device(i - 1)
+                import torch
+
+                class W:
+                    __cuda_array_interface__ = {"shape": (max(n_prev, 1), 2), "typestr": "<i4", "data": (ptr, False), "version": 2}
+                view = torch.as_tensor(W(), device="cuda:0")[:n_prev]
+                keep.append(view)
+                rel = hj.RelationBuilder(abi.LOC_DEVICE).add_reference(0, view, scol, KEY_TYPES[sv.dtype.name]).build()
+                ctx.scan(rel, s["predicate"], s["value"], slot=i, dereference=True)
+        pos_ptr, _, n, _ = ctx.scan_result_device(len(scans) - 1)
+    values_ptr, nulls_ptr, kt = ctx.gather_column(pos_ptr, n, col)
+    assert kt == KEY_TYPES[v.dtype.name]
+    got = ctx.aggregate_column(values_ptr, nulls_ptr, n, kt)
+    assert am.matches_reference(got[case["function"]], case["expect"]), (got, case["expect"], case["cite"])
+
+
+@pytest.mark.parametrize("dtype", [np.int32, np.int64, np.float32, np.float64])
+@pytest.mark.parametrize("null_share", [0.0, 0.3, 1.0])
+def test_random_columns_match_oracle(ctx, dtype, null_share):
+    """Sizes around a warp, a CTA, the grid-stride unrolling and one past them; NULL-free (nulls = NULL pointer), partly and
+    all NULL."""
+    import torch
+    rng = np.random.default_rng(0xA66)
+    for n in (0, 1, 31, 33, 255, 257, 1023, 4 * 256 * 148 * 8 + 5, 3_000_001):
+        if np.dtype(dtype).kind == "f":
+            v = (rng.standard_normal(n) * 1e3).astype(dtype)
+        else:
+            v = rng.integers(-10**6, 10**6, n).astype(dtype)
+        z = (rng.random(n) < null_share).astype(np.uint8)
+        tv, tz = torch.from_numpy(v).cuda(), torch.from_numpy(z).cuda()
+        got = ctx.aggregate_column(tv.data_ptr() if n else None, tz.data_ptr() if (n and null_share > 0) else None, n,
+                                   KEY_TYPES[np.dtype(dtype).name])
+        close_enough(got, ao.aggregate_column(v, z if null_share > 0 else None))
+
+
+def test_aggregate_of_the_join_result_without_downloading_it(ctx):
+    """scan-free pipeline at a size where the download would matter: join, read a payload column of the probe table through
+    the probe-side PosList, SUM / COUNT / MIN / MAX it; compared with numpy over the fetched PosLists."""
+    import torch
+    rng = np.random.default_rng(9)
+    chunk = 1 << 16
+    bk = (rng.permutation(300_000) + 1).astype(np.int32)
+    pk = rng.integers(1, 400_001, 2_000_000).astype(np.int32)
+    pay = rng.integers(-1000, 1000, len(pk)).astype(np.int64)
+    pay_null = (rng.random(len(pk)) < 0.05).astype(np.uint8)
+    b_col, k1 = device_column(bk, np.zeros(len(bk), np.uint8), chunk)
+    p_col, k2 = device_column(pk, np.zeros(len(pk), np.uint8), chunk)
+    pay_col, k3 = device_column(pay, pay_null, chunk)
+    info = ctx.join(b_col, p_col, abi.MODE_INNER)
+    _, p_ptr, n = ctx.result_device()
+    assert n == info.n_rows == int((pk <= 300_000).sum())
+    values_ptr, nulls_ptr, kt = ctx.gather_column(p_ptr, n, pay_col)
+    got = ctx.aggregate_column(values_ptr, nulls_ptr, n, kt)
+    _, gp = ctx.fetch()
+    rows = gp[:, 0].astype(np.int64) * chunk + gp[:, 1]
+    close_enough(got, ao.aggregate_column(pay[rows], pay_null[rows]))
