@@ -22,6 +22,12 @@
 #ifndef HJ_TUNE_P1_DICT_PREFETCH
 #define HJ_TUNE_P1_DICT_PREFETCH 0
 #endif
+#ifndef HJ_TUNE_P1_GATHER
+// how P1 reads a dictionary entry: 0 = ld.global.nc (allocates an L1 line per gather; the default, measured), 1 = ld.global.cg
+// (L2 only), 2 = ld.global.nc.L1::no_allocate. The gather never hits L1 (a 2048-row tile touches 2048 of ~1 M entries), and
+// P1 is bound by the misses it can keep in flight — untried on a GPU: variants for tests/sweep_variants.py.
+#define HJ_TUNE_P1_GATHER 0
+#endif
 #ifndef HJ_TUNE_P2_STEPS
 #define HJ_TUNE_P2_STEPS 1
 #endif
@@ -30,6 +36,25 @@
 #endif
 
 namespace hj {
+
+template <typename K>
+__device__ __forceinline__ K dict_gather(const DevSegment& s, uint32_t vid) {
+#if HJ_TUNE_P1_GATHER == 0
+  return load_plain_key<K>(s, vid);
+#elif HJ_TUNE_P1_GATHER == 1
+  if (s.key_type == 0) return static_cast<K>(__ldcg(static_cast<const int32_t*>(s.values) + vid));
+  return static_cast<K>(__ldcg(static_cast<const long long*>(s.values) + vid));
+#else
+  if (s.key_type == 0) {
+    int32_t v;
+    asm volatile("ld.global.nc.L1::no_allocate.b32 %0, [%1];" : "=r"(v) : "l"(static_cast<const int32_t*>(s.values) + vid));
+    return static_cast<K>(v);
+  }
+  long long v;
+  asm volatile("ld.global.nc.L1::no_allocate.b64 %0, [%1];" : "=l"(v) : "l"(static_cast<const long long*>(s.values) + vid));
+  return static_cast<K>(v);
+#endif
+}
 
 // =====================================================================================================================
 // P1. One physical CTA of NT threads hosts VC virtual CTAs of VT = NT/VC threads (as K1 does) that share the
@@ -99,7 +124,7 @@ __global__ void __launch_bounds__(NT) k_part1(RelMeta rel, Tuple<K, false>* __re
 #pragma unroll
       for (int u = 0; u < ITEMS; ++u) {
         const bool valid = vid[u] != s.null_value_id;  // rows past the end carry null_value_id
-        key[u] = valid ? load_plain_key<K>(s, vid[u]) : K(0);  // NULL decodes to T{} (dictionary_column_iterable.hpp:80)
+        key[u] = valid ? dict_gather<K>(s, vid[u]) : K(0);  // NULL decodes to T{} (dictionary_column_iterable.hpp:80)
         vbits |= (valid ? 1u : 0u) << u;
       }
     } else {
