@@ -313,6 +313,17 @@ class HashJoin:
         reference's result types; SUM / MIN / MAX / AVG are None when every row is NULL (aggregate.cpp:635-642)."""
         a = abi.Aggregate()
         self._check(self._l.hj_aggregate_column(self._ctx, device_values, device_nulls, n_rows, key_type, stream, C.byref(a)))
+        return self._aggregate_dict(a)
+
+    def aggregate_relation(self, column, stream=None):
+        """hj_aggregate_relation: the same aggregates over a column given as chunk descriptors (host or device resident,
+        data or reference table)."""
+        a = abi.Aggregate()
+        self._check(self._l.hj_aggregate_relation(self._ctx, C.byref(column), stream, C.byref(a)))
+        return self._aggregate_dict(a)
+
+    @staticmethod
+    def _aggregate_dict(a):
         some = a.n_values > 0
         floating = bool(a.is_floating)
         return {"count_rows": a.n_rows, "count": a.n_values,

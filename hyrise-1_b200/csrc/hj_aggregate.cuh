@@ -11,6 +11,9 @@
 // reproducible run to run; they differ from the reference's row-order sum by rounding only — DESIGN.md §8).
 #pragma once
 #include <cstdint>
+#include <type_traits>
+
+#include "hj_kernels.cuh"
 
 namespace hj {
 
@@ -75,6 +78,23 @@ __device__ __forceinline__ void agg_add(AggPartial& a, T v) {
   }
 }
 
+// The CTA's partial: warp shuffles, then warp 0's lane 0 folds the warps in order.
+__device__ __forceinline__ void agg_block_store(AggPartial a, AggPartial* s_part, AggPartial* __restrict__ dst) {
+#pragma unroll
+  for (int delta = 16; delta > 0; delta >>= 1) {
+    const AggPartial b = agg_shfl_down(a, delta);
+    agg_merge(a, b);
+  }
+  if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = a;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    AggPartial t = s_part[0];
+#pragma unroll
+    for (int w = 1; w < kAggThreads / 32; ++w) agg_merge(t, s_part[w]);
+    *dst = t;
+  }
+}
+
 // A1. Grid-stride over the rows, four independent loads in flight per thread; one partial per CTA.
 template <typename T>
 __global__ void __launch_bounds__(kAggThreads) k_aggregate_partial(const T* __restrict__ values, const uint8_t* __restrict__ nulls,
@@ -98,19 +118,42 @@ __global__ void __launch_bounds__(kAggThreads) k_aggregate_partial(const T* __re
   }
   for (; i < n; i += stride)
     if (!(nulls && __ldg(nulls + i))) agg_add<T>(a, __ldg(values + i));
-#pragma unroll
-  for (int delta = 16; delta > 0; delta >>= 1) {
-    const AggPartial b = agg_shfl_down(a, delta);
-    agg_merge(a, b);
+  agg_block_store(a, s_part, partials + blockIdx.x);
+}
+
+// A1'. The same over a column given as chunk descriptors (the join's and the scan's input format), without materialising
+// it: VALUE / GATHERED chunks stream values + NULL bytes, DICT chunks stream the attribute vector and gather the
+// dictionary (NULL = null_value_id). K = integer type the keys are stored in, T = the column's type (K itself, or float /
+// double carried as bit patterns after k_gather_refs, as in hj_scan). TILE rows per tile as prepared by prepare_relation.
+template <typename K, typename T, int TILE>
+__global__ void __launch_bounds__(kAggThreads) k_aggregate_relation(RelMeta rel, AggPartial* __restrict__ partials) {
+  __shared__ AggPartial s_part[kAggThreads / 32];
+  AggPartial a;
+  agg_init(a);
+  for (uint32_t tile = blockIdx.x; tile < rel.n_tiles; tile += gridDim.x) {
+    const DevSegment s = rel.segs[__ldg(rel.tile_seg + tile)];
+    const uint32_t r0 = (tile - s.tile_begin) * TILE;
+    const uint32_t cnt = min(static_cast<uint32_t>(TILE), s.n_rows - r0);
+#pragma unroll 4
+    for (uint32_t i = threadIdx.x; i < cnt; i += kAggThreads) {
+      K raw;
+      bool is_null;
+      if (s.kind == 1) {
+        const uint32_t vid = load_attr(s, r0 + i);
+        is_null = vid == s.null_value_id;
+        raw = is_null ? K(0) : load_plain_key<K>(s, vid);
+      } else {
+        is_null = s.nulls && __ldg(s.nulls + r0 + i);
+        raw = load_plain_key<K>(s, r0 + i);
+      }
+      if (!is_null) {
+        if constexpr (std::is_same<T, float>::value) agg_add<float>(a, __int_as_float(static_cast<int>(raw)));
+        else if constexpr (std::is_same<T, double>::value) agg_add<double>(a, __longlong_as_double(static_cast<long long>(raw)));
+        else agg_add<K>(a, raw);
+      }
+    }
   }
-  if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = a;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    AggPartial t = s_part[0];
-#pragma unroll
-    for (int w = 1; w < kAggThreads / 32; ++w) agg_merge(t, s_part[w]);
-    partials[blockIdx.x] = t;
-  }
+  agg_block_store(a, s_part, partials + blockIdx.x);
 }
 
 // A2 (one warp): partials folded in CTA order into out[0].

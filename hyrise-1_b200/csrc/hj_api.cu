@@ -1319,6 +1319,30 @@ int run_scan(hj_ctx* ctx, const hj_relation* column, const hj_relation* original
 }
 
 
+// A2 + read-back shared by hj_aggregate_column and hj_aggregate_relation: partials[1 .. grid] -> partials[0] -> *out
+int finish_aggregate(hj_ctx* ctx, AggPartial* partials, uint32_t grid, uint64_t n_rows, int key_type, cudaStream_t st, hj_aggregate* out) {
+  k_aggregate_final<<<1, 32, 0, st>>>(partials + 1, grid, partials);
+  HJ_LAUNCH_CHECK(ctx, "k_aggregate_final");
+  auto* host = reinterpret_cast<AggPartial*>(static_cast<char*>(ctx->pinned) + kPinnedAggregate);
+  HJ_CUDA(ctx, cudaMemcpyAsync(host, partials, sizeof(AggPartial), cudaMemcpyDeviceToHost, st));
+  HJ_CUDA(ctx, cudaStreamSynchronize(st));
+  const bool floating = key_type >= HJ_KEY_FLOAT;
+  out->n_rows = n_rows;
+  out->n_values = host->n_values;
+  out->is_floating = floating ? 1 : 0;
+  out->sum_int = floating ? 0 : host->sum_i;
+  // AVG accumulates in double for every column type (aggregate_traits.hpp:40-46); for an integer column the int64 sum is
+  // that double sum exactly as long as it stays below 2^53
+  out->sum_double = floating ? host->sum_d : static_cast<double>(host->sum_i);
+  if (host->n_values) {
+    out->min_int = floating ? 0 : host->min_i;
+    out->max_int = floating ? 0 : host->max_i;
+    out->min_double = floating ? host->min_d : static_cast<double>(host->min_i);
+    out->max_double = floating ? host->max_d : static_cast<double>(host->max_i);
+  }
+  return HJ_OK;
+}
+
 }  // namespace
 
 // ============================================================================================================= C ABI
@@ -1616,24 +1640,50 @@ int hj_aggregate_column(hj_ctx* ctx, const void* device_values, const uint8_t* d
       k_aggregate_partial<double><<<grid, kAggThreads, 0, st>>>(static_cast<const double*>(device_values), device_nulls, n_rows, partials + 1);
   }
   HJ_LAUNCH_CHECK(ctx, "k_aggregate_partial");
-  k_aggregate_final<<<1, 32, 0, st>>>(partials + 1, grid, partials);
-  HJ_LAUNCH_CHECK(ctx, "k_aggregate_final");
-  auto* host = reinterpret_cast<AggPartial*>(static_cast<char*>(ctx->pinned) + kPinnedAggregate);
-  HJ_CUDA(ctx, cudaMemcpyAsync(host, partials, sizeof(AggPartial), cudaMemcpyDeviceToHost, st));
-  HJ_CUDA(ctx, cudaStreamSynchronize(st));
-  const bool floating = key_type >= HJ_KEY_FLOAT;
-  out->n_rows = n_rows;
-  out->n_values = host->n_values;
-  out->is_floating = floating ? 1 : 0;
-  out->sum_int = floating ? 0 : host->sum_i;
-  // AVG accumulates in double for every column type (aggregate_traits.hpp:40-46); for an integer column the int64 sum is
-  // that double sum exactly as long as it stays below 2^53
-  out->sum_double = floating ? host->sum_d : static_cast<double>(host->sum_i);
-  if (host->n_values) {
-    out->min_int = floating ? 0 : host->min_i;
-    out->max_int = floating ? 0 : host->max_i;
-    out->min_double = floating ? host->min_d : static_cast<double>(host->min_i);
-    out->max_double = floating ? host->max_d : static_cast<double>(host->max_i);
+  return finish_aggregate(ctx, partials, grid, n_rows, key_type, st, out);
+}
+
+int hj_aggregate_relation(hj_ctx* ctx, const hj_relation* column, void* cuda_stream, hj_aggregate* out) {
+  if (!ctx) return HJ_ERR_INVALID;
+  if (!out) return fail(ctx, HJ_ERR_INVALID, "out is NULL");
+  std::memset(out, 0, sizeof(*out));
+  HJ_TRY(validate_relation(ctx, column, "aggregate"));
+  bool wide = false, any_float = false, any_double = false;
+  for (uint32_t i = 0; i < column->n_segs; ++i) {
+    const uint8_t k = column->segs[i].key_type;
+    wide = wide || k == HJ_KEY_INT64;
+    any_float = any_float || k == HJ_KEY_FLOAT;
+    any_double = any_double || k == HJ_KEY_DOUBLE;
+  }
+  const uint32_t type = any_double ? HJ_KEY_DOUBLE : any_float ? HJ_KEY_FLOAT : wide ? HJ_KEY_INT64 : HJ_KEY_INT32;
+  HJ_TRY(check_ctx(ctx));
+  cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
+  // REFERENCE / FOR / RLE / SimdBp128 chunks (and every chunk of a float / double column) become value-like chunks on the
+  // device first, exactly as for hj_scan; VALUE and DICT chunks of integer columns are read where they are
+  ctx->ref_h2d_bytes = 0;
+  std::memset(static_cast<char*>(ctx->pinned) + kPinnedRefFlags, 0, 8);
+  RefRewrite rw;
+  HJ_TRY(gather_references(ctx, column, 1, st, &rw, type));
+  const hj_relation* rel = rw.any ? &rw.rel : column;
+  PreparedRel pr;
+  HJ_TRY(prepare_relation(ctx, rel, 1, kScanTile, st, &pr));
+  const uint32_t grid = std::max<uint32_t>(1, std::min<uint32_t>(pr.meta.n_tiles, uint32_t(ctx->n_sms) * 8));
+  HJ_TRY(ensure(ctx, ctx->agg_partials, (size_t(grid) + 1) * sizeof(AggPartial)));
+  auto* partials = static_cast<AggPartial*>(ctx->agg_partials.p);
+  switch (type) {
+    case HJ_KEY_DOUBLE: k_aggregate_relation<int64_t, double, kScanTile><<<grid, kAggThreads, 0, st>>>(pr.meta, partials + 1); break;
+    case HJ_KEY_FLOAT: k_aggregate_relation<int32_t, float, kScanTile><<<grid, kAggThreads, 0, st>>>(pr.meta, partials + 1); break;
+    case HJ_KEY_INT64: k_aggregate_relation<int64_t, int64_t, kScanTile><<<grid, kAggThreads, 0, st>>>(pr.meta, partials + 1); break;
+    default: k_aggregate_relation<int32_t, int32_t, kScanTile><<<grid, kAggThreads, 0, st>>>(pr.meta, partials + 1);
+  }
+  HJ_LAUNCH_CHECK(ctx, "k_aggregate_relation");
+  HJ_TRY(finish_aggregate(ctx, partials, grid, column->n_rows, static_cast<int>(type), st, out));
+  if (rw.any) {
+    const auto* flag = reinterpret_cast<const uint32_t*>(static_cast<const char*>(ctx->pinned) + kPinnedRefFlags);
+    if (flag[0] || flag[1]) {
+      std::memset(out, 0, sizeof(*out));
+      return fail(ctx, HJ_ERR_INVALID, "aggregate: a PosList entry points outside the referenced table");
+    }
   }
   return HJ_OK;
 }

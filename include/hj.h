@@ -387,6 +387,13 @@ typedef struct hj_aggregate {
 int hj_aggregate_column(hj_ctx* ctx, const void* device_values, const uint8_t* device_nulls, uint64_t n_rows,
                         int key_type, void* cuda_stream, hj_aggregate* out);
 
+/* The same aggregates over a column given as chunk descriptors — the input format of hj_join and hj_scan: VALUE /
+ * DICT / FOR / RLE chunks of a data table or REFERENCE chunks of a reference table (e.g. a join's or scan's output
+ * table), host or device resident — without materialising the column: what Aggregate::_aggregate_column does over
+ * all chunks of one aggregate column (aggregate.cpp:203-252). This is the call the host-side Aggregate operator
+ * makes for a plan `Aggregate(JoinHash(...))` or `Aggregate(TableScan(...))` without GROUP BY. */
+int hj_aggregate_relation(hj_ctx* ctx, const hj_relation* column, void* cuda_stream, hj_aggregate* out);
+
 /* ---- multi-GPU (one process per GPU) ---------------------------------------- */
 /* The exchange has no reference counterpart: both relations are split by the high bits of the
  * key hash so that every key's rows meet on one rank, exchanged with an NCCL all-to-all over

@@ -138,3 +138,58 @@ def test_aggregate_of_the_join_result_without_downloading_it(ctx):
     _, gp = ctx.fetch()
     rows = gp[:, 0].astype(np.int64) * chunk + gp[:, 1]
     close_enough(got, ao.aggregate_column(pay[rows], pay_null[rows]))
+
+
+# ---- hj_aggregate_relation: the column as chunk descriptors (what the host-side Aggregate operator passes) ---------------
+def host_relation(values, is_null, chunk, encoding):
+    import scan_model as sm
+    rb = hj.RelationBuilder(abi.LOC_HOST)
+    for c, lo in enumerate(range(0, max(len(values), 1), chunk)):
+        v, z = np.ascontiguousarray(values[lo:lo + chunk]), np.ascontiguousarray(is_null[lo:lo + chunk])
+        if encoding == "dict":
+            d = sm.dict_encode(v, z)
+            rb.add_dict(c, d["dictionary"], d["attr"], d["null_value_id"])
+        else:
+            rb.add_value(c, v, z if z.any() else None)
+    return rb.build()
+
+
+@pytest.mark.parametrize("case", FIX["cases"], ids=[c["name"] for c in FIX["cases"]])
+@pytest.mark.parametrize("encoding", ["value", "dict"])
+@pytest.mark.parametrize("variant", [0, 1], ids=["data", "reference"])
+def test_reference_aggregate_case_through_chunk_descriptors(ctx, case, encoding, variant):
+    """Host-resident tables like the C++ operator sees them; behind scans the column is a REFERENCE chunk whose PosList is
+    the (oracle) scan result — the reference's `Aggregate(TableScan(...))`."""
+    from oracle import table_scan_oracle as tso
+    from test_aggregate_oracle import PRED
+    table = FIX["tables"][case["table"]]
+    v, z = am.column_of(table, case["column"])
+    chunk = case["chunk_size"]
+    data = host_relation(v, z, chunk, encoding)
+    scans = am.scans_of(case)[variant]
+    if not scans:
+        rel = data
+    else:
+        rows = np.arange(len(v))
+        for s in scans:
+            sv, sz = am.column_of(table, s["column"])
+            pos, _ = tso.table_scan([{"kind": "value", "values": sv[rows], "nulls": sz[rows] if sz.any() else None}], [0],
+                                    PRED[s["predicate"]], s["value"])
+            rows = rows[pos[:, 1]]
+        pos_list = np.ascontiguousarray(np.stack([rows // chunk, rows % chunk], axis=1).astype(np.uint32)).reshape(-1, 2)
+        rel = hj.RelationBuilder(abi.LOC_HOST).add_reference(0, pos_list, data, KEY_TYPES[v.dtype.name]).build()
+    got = ctx.aggregate_relation(rel)
+    assert am.matches_reference(got[case["function"]], case["expect"]), (got, case["expect"], case["cite"])
+
+
+@pytest.mark.parametrize("dtype", [np.int32, np.int64, np.float32, np.float64])
+@pytest.mark.parametrize("encoding", ["value", "dict"])
+def test_random_relations_match_oracle(ctx, dtype, encoding):
+    rng = np.random.default_rng(0xA67)
+    for n, chunk in ((0, 8), (1, 8), (4097, 4096), (100_000, 30_000), (2_000_000, 1 << 18)):
+        if np.dtype(dtype).kind == "f":
+            v = (rng.integers(-5000, 5000, n) / 8).astype(dtype)   # few distinct values: small dictionaries
+        else:
+            v = rng.integers(-5000, 5000, n).astype(dtype)
+        z = (rng.random(n) < 0.2).astype(np.uint8)
+        close_enough(ctx.aggregate_relation(host_relation(v, z, chunk, encoding)), ao.aggregate_column(v, z))
