@@ -65,7 +65,7 @@ enum class PredicateCondition { Equals, NotEquals, LessThan, LessThanEquals, Gre
 enum class JoinMode { Inner, Left, Right, Outer, Cross, Semi, Anti };  // integer values are part of the C ABI (hj.h)
 enum class TableType { References, Data };
 enum class DescriptionMode { SingleLine, MultiLine };
-enum class OperatorType { JoinHash, TableWrapper, TableScan, Mock };
+enum class OperatorType { JoinHash, TableWrapper, TableScan, Aggregate, Mock };
 
 // ---- all_type_variant.hpp ------------------------------------------------------------------------------------------------
 enum class DataType : uint8_t { Null, Int, Long, Float, Double, String };

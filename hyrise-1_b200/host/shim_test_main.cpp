@@ -15,6 +15,7 @@
 #include <sstream>
 
 #include "join_hash.hpp"
+#include "aggregate.hpp"
 #include "table_scan.hpp"
 
 using namespace opossum;
@@ -360,6 +361,23 @@ int main(int argc, char** argv) {
                                                  PredicateCondition::Equals);
           join->execute();
           env[op[1]] = join->get_output();
+        } else if (op[0] == "aggregate") {
+          // aggregate <out> <in> <FUNCTION>:<column id | *> ...   (no GROUP BY; opossum::Aggregate -> hj_aggregate_relation)
+          const std::map<std::string, AggregateFunction> functions = {
+              {"MIN", AggregateFunction::Min}, {"MAX", AggregateFunction::Max}, {"SUM", AggregateFunction::Sum},
+              {"AVG", AggregateFunction::Avg}, {"COUNT", AggregateFunction::Count}};
+          std::vector<AggregateColumnDefinition> aggregates;
+          for (size_t k = 3; k < op.size(); ++k) {
+            const auto parts = split(op[k], ':');
+            std::optional<ColumnID> column;
+            if (parts.at(1) != "*") column = static_cast<ColumnID>(std::stoul(parts[1]));
+            aggregates.emplace_back(column, functions.at(parts[0]));
+          }
+          auto wrapper = std::make_shared<TableWrapper>(env.at(op[2]));
+          wrapper->execute();
+          auto aggregate = std::make_shared<Aggregate>(wrapper, aggregates, std::vector<ColumnID>{});
+          aggregate->execute();
+          env[op[1]] = aggregate->get_output();
         } else if (op[0] == "nlj") {
           env[op[1]] = nested_loop_join(env.at(op[2]), env.at(op[3]), parse_mode(op[4]), static_cast<ColumnID>(std::stoul(op[5])),
                                         static_cast<ColumnID>(std::stoul(op[6])));
