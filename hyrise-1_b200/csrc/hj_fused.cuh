@@ -28,6 +28,9 @@
 // P1 is bound by the misses it can keep in flight — untried on a GPU: variants for tests/sweep_variants.py.
 #define HJ_TUNE_P1_GATHER 0
 #endif
+#ifndef HJ_TUNE_P2_SMEM
+#define HJ_TUNE_P2_SMEM 0  // 1: pass 2's small shared arrays as members of one struct (instruction diet, unmeasured)
+#endif
 #ifndef HJ_TUNE_P2_STEPS
 #define HJ_TUNE_P2_STEPS 1
 #endif
@@ -232,11 +235,28 @@ __global__ void __launch_bounds__(NT, MINB) k_scatter2f(const Tuple<K, false>* _
   constexpr uint32_t TILE = NT * ITEMS;
   extern __shared__ __align__(16) unsigned char s_raw[];
   T* stage = reinterpret_cast<T*>(s_raw);
+  constexpr int OS = HJ_TUNE_P2_OWN_SHIFT;
+#if HJ_TUNE_P2_SMEM == 0
   __shared__ uint32_t s_cnt[kMaxDigits], s_loff[kMaxDigits], s_delta[kMaxDigits];
   __shared__ uint32_t s_pre[NT + 1], s_dsrc[NT];
-  constexpr int OS = HJ_TUNE_P2_OWN_SHIFT;
   __shared__ uint8_t s_own[TILE >> OS];
   __shared__ uint32_t scratch[33];
+#else
+  // one shared-memory object: every array is the same base + a constant. With separate arrays the compiler rebuilds three
+  // shared-window addresses (S2R SR_CgaCtaId + LEAs) inside each of the 16 unrolled items: 1992 -> 1776 SASS instructions for
+  // <int, 256, 16, 4>, at 8 bytes of spill. (An explicit 32-bit base through inline ld.shared changed nothing: ptxas
+  // rematerialises the base per item either way.)
+  struct Sm {
+    uint32_t cnt[kMaxDigits], loff[kMaxDigits], delta[kMaxDigits];
+    uint32_t pre[NT + 1], dsrc[NT];
+    uint32_t scratch[33];
+    uint8_t own[TILE >> OS];
+  };
+  __shared__ Sm sm;
+  uint32_t* const s_cnt = sm.cnt; uint32_t* const s_loff = sm.loff; uint32_t* const s_delta = sm.delta;
+  uint32_t* const s_pre = sm.pre; uint32_t* const s_dsrc = sm.dsrc; uint32_t* const scratch = sm.scratch;
+  uint8_t* const s_own = sm.own;
+#endif
 
   const uint32_t P = 1u << radix_bits, F1 = P >> bits2, FS = F1 + 2u;
   const uint32_t group = blockIdx.x / n_digits, d1 = blockIdx.x % n_digits;

@@ -1,6 +1,6 @@
 #!/bin/bash
 # Round-2 candidates (never run on a GPU yet): how P1 reads dictionary entries (L1 bypass).
-#   bash tests/build_variants5.sh && python tests/sweep_variants.py --scale 1.0 --runs default gather_cg gather_noalloc default
+#   bash tests/build_variants5.sh && python tests/sweep_variants.py --scale 1.0 --runs default gather_cg gather_noalloc p2_mb3 p2_mb2 p2_smem p2_smem_mb3 default
 cd "$(dirname "$0")/.."
 OUT=hyrise-1_b200/csrc/variants; mkdir -p $OUT; rm -f $OUT/*.so $OUT/*.ptxas
 FLAGS="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC --expt-relaxed-constexpr -shared -I include"
@@ -9,4 +9,12 @@ build() { name=$1; shift
     && echo "built $name" || echo "FAILED $name (see $OUT/$name.ptxas)"; }
 build gather_cg -DHJ_TUNE_P1_GATHER=1 &
 build gather_noalloc -DHJ_TUNE_P1_GATHER=2 &
+# pass 2 with more registers per thread (3 / 2 CTAs of 256 x 16 per SM instead of 4): at 64 registers the compiler
+# rematerialises the shared-memory base addresses inside every one of the 16 unrolled items (S2R SR_CgaCtaId + LEAs)
+build p2_mb3 -DHJ_TUNE_P2_MINBLOCKS=3 &
+build p2_mb2 -DHJ_TUNE_P2_MINBLOCKS=2 &
+wait
+# pass 2's small shared arrays in one struct: 11 % fewer SASS instructions in an issue-bound kernel (8 bytes of spill)
+build p2_smem -DHJ_TUNE_P2_SMEM=1 &
+build p2_smem_mb3 -DHJ_TUNE_P2_SMEM=1 -DHJ_TUNE_P2_MINBLOCKS=3 &
 wait
