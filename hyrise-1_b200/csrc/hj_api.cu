@@ -1536,7 +1536,7 @@ int hj_scan_value_ids(hj_ctx* ctx, const hj_relation* column, int predicate, con
   if (!null_test && (predicate < HJ_PRED_EQUALS || predicate > HJ_PRED_GREATER_THAN_EQUALS))
     return fail(ctx, HJ_ERR_INVALID, "PredicateCondition %d is not a single-column comparison", predicate);
   if (scan_flags) return fail(ctx, HJ_ERR_INVALID, "hj_scan_value_ids takes no scan flags (data chunks only, no literal)");
-  HJ_TRY(validate_relation(ctx, column, "scan"));
+  if (!column || (column->n_segs && !column->segs)) return fail(ctx, HJ_ERR_INVALID, "scan relation is NULL or has no segment array");
   if (column->n_segs && !bounds && !null_test) return fail(ctx, HJ_ERR_INVALID, "bounds is NULL");
   // only the attribute vectors travel: the dictionaries (strings, or anything else sorted) stay with the caller
   std::vector<hj_segment> segs(column->segs, column->segs + column->n_segs);
@@ -1551,6 +1551,7 @@ int hj_scan_value_ids(hj_ctx* ctx, const hj_relation* column, int predicate, con
   }
   hj_relation rel = *column;
   rel.segs = segs.data();
+  HJ_TRY(validate_relation(ctx, &rel, "scan"));  // after the rewrite: values / dict_n of the caller's segments are ignored
   HJ_TRY(check_ctx(ctx));
   cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
   std::vector<uint32_t> zeros;
