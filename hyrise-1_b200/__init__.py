@@ -301,6 +301,10 @@ class HashJoin:
                                               slot, 0, stream, C.byref(info)))
         return info
 
+    def translate_device(self, device_inout, n_rows, input_relation, stream=None):
+        """hj_translate_device: RowIDs of a device-resident reference-table input -> rows of the referenced data table, in place."""
+        self._check(self._l.hj_translate_device(self._ctx, device_inout, n_rows, C.byref(input_relation), stream))
+
     def gather_column(self, device_pos, n_rows, column, stream=None):
         """hj_gather_column: (values device ptr, nulls device ptr, key type) of `column` at the rows of a device PosList."""
         v, n, t = C.c_void_p(), C.c_void_p(), C.c_int()

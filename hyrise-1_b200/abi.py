@@ -104,6 +104,7 @@ SYMBOLS = {
                           C.POINTER(ScanInfo)]),
     "hj_scan_value_ids": (C.c_int, [C.c_void_p, C.POINTER(Relation), C.c_int, C.c_void_p, C.c_int, C.c_uint32, C.c_void_p,
                                     C.POINTER(ScanInfo)]),
+    "hj_translate_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(Relation), C.c_void_p]),
     "hj_gather_column": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(Relation), C.c_void_p, C.POINTER(C.c_void_p),
                                    C.POINTER(C.c_void_p), C.POINTER(C.c_int)]),
     "hj_aggregate_column": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p, C.POINTER(Aggregate)]),

@@ -1864,6 +1864,47 @@ int hj_translate(hj_ctx* ctx, hj_row_id* inout, uint64_t n, const hj_row_id* con
   return HJ_OK;
 }
 
+int hj_translate_device(hj_ctx* ctx, hj_row_id* device_inout, uint64_t n, const hj_relation* input, void* cuda_stream) {
+  if (!ctx) return HJ_ERR_INVALID;
+  if (!input) return fail(ctx, HJ_ERR_INVALID, "input relation is NULL");
+  if (input->location != HJ_LOC_DEVICE)
+    return fail(ctx, HJ_ERR_INVALID, "hj_translate_device reads the PosLists of a device-resident relation where they lie");
+  HJ_TRY(validate_relation(ctx, input, "translate"));
+  if (n == 0) return HJ_OK;
+  if (!device_inout) return fail(ctx, HJ_ERR_INVALID, "device_inout is NULL");
+  uint32_t n_ids = 0;
+  for (uint32_t i = 0; i < input->n_segs; ++i) {
+    if (input->segs[i].chunk_id >= (1u << 24))
+      return fail(ctx, HJ_ERR_INVALID, "translate: chunk id %u (the table of PosLists is indexed by chunk id, limit 2^24)", input->segs[i].chunk_id);
+    n_ids = std::max(n_ids, input->segs[i].chunk_id + 1);
+  }
+  std::vector<const uint64_t*> seg_pos(std::max<uint32_t>(1, n_ids), nullptr);
+  std::vector<uint32_t> seg_rows(std::max<uint32_t>(1, n_ids), 0xFFFFFFFFu);
+  for (uint32_t i = 0; i < input->n_segs; ++i) {
+    const hj_segment& sg = input->segs[i];
+    seg_rows[sg.chunk_id] = sg.n_rows;
+    seg_pos[sg.chunk_id] = sg.kind == HJ_SEG_REFERENCE ? static_cast<const uint64_t*>(sg.attr) : nullptr;
+  }
+  HJ_TRY(check_ctx(ctx));
+  cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
+  // misc layout: [PosList pointers n_ids*8][segment lengths n_ids*4, padded][error 4]
+  const size_t o_rows = size_t(seg_pos.size()) * 8, o_err = (o_rows + size_t(seg_rows.size()) * 4 + 7) & ~size_t(7);
+  HJ_TRY(ensure(ctx, ctx->misc, o_err + 8));
+  char* d = static_cast<char*>(ctx->misc.p);
+  HJ_CUDA(ctx, cudaMemcpyAsync(d, seg_pos.data(), seg_pos.size() * 8, cudaMemcpyHostToDevice, st));
+  HJ_CUDA(ctx, cudaMemcpyAsync(d + o_rows, seg_rows.data(), seg_rows.size() * 4, cudaMemcpyHostToDevice, st));
+  HJ_CUDA(ctx, cudaMemsetAsync(d + o_err, 0, 4, st));
+  const uint32_t grid = (uint32_t)std::min<uint64_t>((n + 255) / 256, uint64_t(ctx->n_sms) * 8);
+  k_translate_segments<<<grid, 256, 0, st>>>(reinterpret_cast<uint64_t*>(device_inout), n, reinterpret_cast<const uint64_t* const*>(d),
+                                             reinterpret_cast<const uint32_t*>(d + o_rows), n_ids, reinterpret_cast<uint32_t*>(d + o_err));
+  HJ_LAUNCH_CHECK(ctx, "k_translate_segments");
+  uint32_t err = 0;
+  HJ_CUDA(ctx, cudaMemcpyAsync(&err, d + o_err, 4, cudaMemcpyDeviceToHost, st));
+  HJ_CUDA(ctx, cudaStreamSynchronize(st));  // also: the pageable vectors above have been consumed
+  if (err) return fail(ctx, HJ_ERR_INVALID, "hj_translate_device: a RowID points outside its input chunk");
+  return HJ_OK;
+}
+
 int hj_get_timings(const hj_ctx* ctx, hj_timings* out) {
   if (!ctx || !out) return HJ_ERR_INVALID;
   *out = ctx->timings;

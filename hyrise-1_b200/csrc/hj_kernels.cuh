@@ -1420,6 +1420,26 @@ __global__ void __launch_bounds__(256) k_gather_refs(const RefJob* __restrict__ 
   }
 }
 
+// K9': the same for a result that stays on the device, through the PosLists where they lie: seg_pos[id] = PosList of the
+// REFERENCE segment with chunk id `id` (nullptr: a data chunk, its RowIDs are final), seg_rows[id] = its length
+// (0xFFFFFFFF: no segment has this chunk id -> error).
+__global__ void k_translate_segments(uint64_t* __restrict__ inout, uint64_t n, const uint64_t* const* __restrict__ seg_pos,
+                                     const uint32_t* __restrict__ seg_rows, uint32_t n_ids, uint32_t* __restrict__ error) {
+  for (uint64_t i = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<uint64_t>(gridDim.x) * blockDim.x) {
+    const uint64_t r = inout[i];
+    const uint32_t chunk = static_cast<uint32_t>(r), off = static_cast<uint32_t>(r >> 32);
+    if (off == kInvalid) continue;  // NULL_ROW_ID stays (join_hash.cpp:586-588)
+    const uint32_t rows = chunk < n_ids ? seg_rows[chunk] : 0xFFFFFFFFu;
+    if (rows == 0xFFFFFFFFu || off >= rows) {
+      *error = 1;
+      continue;
+    }
+    const uint64_t* pl = seg_pos[chunk];
+    if (pl) inout[i] = pl[off];
+  }
+}
+
 // K9: inout[i] = pos_lists[chunk_base[inout[i].chunk_id] + inout[i].chunk_offset]; NULL_ROW_ID stays (join_hash.cpp:584-592).
 // Out-of-range references are reported through *error instead of faulting.
 __global__ void k_translate(uint64_t* __restrict__ inout, uint64_t n, const uint64_t* __restrict__ pos_lists,

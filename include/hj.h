@@ -352,6 +352,14 @@ int hj_scan_fetch(hj_ctx* ctx, int slot, hj_row_id* pos, uint64_t capacity_rows,
  * touched by hj_release_scratch. */
 int hj_scan_release(hj_ctx* ctx, int slot);
 
+/* A7 for a result that stays in HBM (the device-side hj_translate): `device_inout` — n RowIDs in device memory,
+ * e.g. a side of hj_result_device, MODIFIED IN PLACE — holds rows of `input`, the DEVICE-resident relation that
+ * side was joined from. Every RowID whose chunk is an HJ_SEG_REFERENCE segment of `input` is replaced by that
+ * segment's PosList entry, i.e. by the row of the referenced data table (join_hash.cpp:584-592); NULL_ROW_ID stays
+ * NULL_ROW_ID, RowIDs of data chunks stay as they are. Afterwards the PosList addresses the data table and can be
+ * handed to hj_gather_column for any of its columns. HJ_ERR_INVALID if a RowID points outside its chunk. */
+int hj_translate_device(hj_ctx* ctx, hj_row_id* device_inout, uint64_t n, const hj_relation* input, void* cuda_stream);
+
 /* ---- reading a column through a PosList on the device (consumers of the join) ---------------- */
 /* The values of `column` (a DEVICE-resident data-table column: VALUE / DICT / FOR / RLE chunks, segs[i] = chunk i) at
  * the rows of a device-resident PosList — what every operator after the join (Aggregate, Projection, the next

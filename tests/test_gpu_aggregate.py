@@ -193,3 +193,50 @@ def test_random_relations_match_oracle(ctx, dtype, encoding):
             v = rng.integers(-5000, 5000, n).astype(dtype)
         z = (rng.random(n) < 0.2).astype(np.uint8)
         close_enough(ctx.aggregate_relation(host_relation(v, z, chunk, encoding)), ao.aggregate_column(v, z))
+
+
+def test_scan_join_translate_gather_aggregate_stays_on_the_device(ctx):
+    """SELECT COUNT(*), SUM(p.pay), MIN(p.pay), MAX(p.pay) FROM build b JOIN probe p ON b.key = p.key WHERE p.key >= :lit —
+    the probe key column filtered by hj_scan, its PosLists joined as REFERENCE chunks, the join's probe side translated to
+    rows of the probe table (hj_translate_device, A7), the payload column read through it and aggregated: only the
+    aggregate comes back. Compared with numpy."""
+    import torch
+    rng = np.random.default_rng(41)
+    chunk = 1 << 16
+    dev = torch.device("cuda", 0)
+    bk = (rng.permutation(300_000) + 1).astype(np.int32)
+    pk = rng.integers(1, 400_001, 1_500_000).astype(np.int32)
+    pay = rng.integers(-1000, 1000, len(pk)).astype(np.int32)
+    pay_null = (rng.random(len(pk)) < 0.1).astype(np.uint8)
+    lit = 120_000
+    b_col, k1 = device_column(bk, np.zeros(len(bk), np.uint8), chunk)
+    p_col, k2 = device_column(pk, np.zeros(len(pk), np.uint8), chunk)
+    pay_col, k3 = device_column(pay, pay_null, chunk)
+    n_chunks = (len(pk) + chunk - 1) // chunk
+
+    ctx.scan(p_col, abi.PRED_GREATER_THAN_EQUALS, lit, slot=1)
+    ptr, _, n_scan, nc = ctx.scan_result_device(1)
+    assert nc == n_chunks
+    _, begin = ctx.scan_fetch(1)   # chunk boundaries (host metadata of the reference table's chunks)
+
+    class W:
+        __cuda_array_interface__ = {"shape": (max(n_scan, 1), 2), "typestr": "<i4", "data": (ptr, False), "version": 2}
+    view = torch.as_tensor(W(), device=dev)[:n_scan]
+    rb = hj.RelationBuilder(abi.LOC_DEVICE)
+    for c in range(n_chunks):
+        if begin[c + 1] > begin[c]:
+            rb.add_reference(c, view[int(begin[c]):int(begin[c + 1])], p_col, abi.KEY_INT32)
+    filtered = rb.build()
+
+    info = ctx.join(b_col, filtered, abi.MODE_INNER)
+    _, p_ptr, n = ctx.result_device()
+    hit = (pk >= lit) & (pk <= 300_000)
+    assert n == info.n_rows == int(hit.sum())
+    ctx.translate_device(p_ptr, n, filtered)           # rows of `filtered` -> rows of the probe table, in place
+    values_ptr, nulls_ptr, kt = ctx.gather_column(p_ptr, n, pay_col)
+    got = ctx.aggregate_column(values_ptr, nulls_ptr, n, kt)
+    close_enough(got, ao.aggregate_column(pay[hit], pay_null[hit]))
+    # and the translated PosList itself: exactly the probe-table rows that qualify
+    _, gp = ctx.fetch()
+    rows = np.sort(gp[:, 0].astype(np.int64) * chunk + gp[:, 1])
+    assert np.array_equal(rows, np.flatnonzero(hit))
