@@ -24,6 +24,7 @@ step c1_dbgen 120 python -m pytest tests/test_gpu_configs.py -m gpu -q -k c1_tpc
 unset HJ_RUN_UNVALIDATED
 # 4. hj_scan against its algorithmic bytes on the C2 probe column (1 B rows, 4-byte attribute vectors)
 step scan_timing 90 python tests/profile_scan.py --workload c2 --scale 1.0
+step pipeline_timing 90 python tests/profile_pipeline.py --workload c2 --scale 0.25 --selectivity 0.5
 # 5. bench legs that have not run: C1 with dbgen keys; and the headline once more as a reference point for the session
 step bench_c1 90 python bench.py --workload c1 --steps 5 --warmup 3 --no-cpu
 step bench_c2 60 python bench.py --steps 5 --warmup 3 --no-e2e --no-cpu
