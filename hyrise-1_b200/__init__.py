@@ -344,6 +344,13 @@ class HashJoin:
         self._check(self._l.hj_scan_fetch(self._ctx, slot, pos.ctypes.data, n, begin.ctypes.data))
         return pos[:n], begin
 
+    def scan_chunk_begin(self, slot=0):
+        """chunk_begin (n_chunks + 1,) uint32 of the scan result in `slot` without downloading the PosLists."""
+        _, _, _, n_chunks = self.scan_result_device(slot)
+        begin = np.empty(n_chunks + 1, dtype=np.uint32)
+        self._check(self._l.hj_scan_fetch(self._ctx, slot, None, 0, begin.ctypes.data))
+        return begin
+
     def scan_result_device(self, slot=0):
         """(pos device ptr, chunk_begin device ptr, n_rows, n_chunks) of the scan result in `slot`."""
         p, b, n, c = C.c_void_p(), C.c_void_p(), C.c_uint64(), C.c_uint32()

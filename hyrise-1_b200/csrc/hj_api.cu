@@ -1704,12 +1704,13 @@ int hj_scan_fetch(hj_ctx* ctx, int slot, hj_row_id* pos, uint64_t capacity_rows,
   if (!ctx) return HJ_ERR_INVALID;
   if (slot < 0 || slot >= HJ_SCAN_SLOTS || !ctx->scan_valid[slot]) return fail(ctx, HJ_ERR_STATE, "no scan result in slot %d", slot);
   const uint64_t n = ctx->scan_rows[slot];
-  if (capacity_rows < n) return fail(ctx, HJ_ERR_CAPACITY, "capacity %llu < %llu scan result rows", (unsigned long long)capacity_rows,
-                                     (unsigned long long)n);
-  if (n && !pos) return fail(ctx, HJ_ERR_INVALID, "NULL output buffer");
+  // pos == NULL: only the chunk boundaries are wanted (the PosLists stay on the device for the next operator)
+  if (pos && capacity_rows < n) return fail(ctx, HJ_ERR_CAPACITY, "capacity %llu < %llu scan result rows", (unsigned long long)capacity_rows,
+                                            (unsigned long long)n);
+  if (!pos && !chunk_begin) return fail(ctx, HJ_ERR_INVALID, "NULL output buffers");
   HJ_TRY(check_ctx(ctx));
   cudaStream_t st = ctx->own_stream;
-  if (n) HJ_CUDA(ctx, cudaMemcpyAsync(pos, ctx->scan_pos[slot].p, n * 8, cudaMemcpyDeviceToHost, st));
+  if (n && pos) HJ_CUDA(ctx, cudaMemcpyAsync(pos, ctx->scan_pos[slot].p, n * 8, cudaMemcpyDeviceToHost, st));
   if (chunk_begin)
     HJ_CUDA(ctx, cudaMemcpyAsync(chunk_begin, ctx->scan_chunk_begin[slot].p, (size_t(ctx->scan_chunks[slot]) + 1) * 4,
                                  cudaMemcpyDeviceToHost, st));

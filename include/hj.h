@@ -345,7 +345,8 @@ int hj_scan_value_ids(hj_ctx* ctx, const hj_relation* column, int predicate, con
 int hj_scan_result_device(hj_ctx* ctx, int slot, const hj_row_id** pos, const uint32_t** chunk_begin, uint64_t* n_rows,
                           uint32_t* n_chunks);
 
-/* Copies the result in `slot` to host memory: pos[capacity_rows] and (optionally) chunk_begin[n_chunks + 1]. */
+/* Copies the result in `slot` to host memory: pos[capacity_rows] and (optionally) chunk_begin[n_chunks + 1].
+ * pos == NULL: only chunk_begin (the PosLists stay on the device for the operator that follows). */
 int hj_scan_fetch(hj_ctx* ctx, int slot, hj_row_id* pos, uint64_t capacity_rows, uint32_t* chunk_begin);
 
 /* Frees the result in `slot` (all slots if slot < 0). TableScan's output is owned by the operator, so it is NOT

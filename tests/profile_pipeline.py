@@ -85,7 +85,7 @@ for rep in range(args.repeats + 1):  # the first round allocates every buffer an
     j.scan(probe, abi.PRED_LESS_THAN, literal, slot=0)
     t.append(time.perf_counter())
     ptr, _, n_scan, n_chunks = j.scan_result_device(0)
-    _, begin = j.scan_fetch(0)  # also downloads the PosList: only the chunk boundaries are needed (host metadata)
+    begin = j.scan_chunk_begin(0)  # host metadata of the reference table's chunks; the PosLists stay in HBM
     view = device_view(ptr, n_scan)
     rb = hj.RelationBuilder(abi.LOC_DEVICE)
     for c in range(n_chunks):

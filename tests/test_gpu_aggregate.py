@@ -217,7 +217,7 @@ def test_scan_join_translate_gather_aggregate_stays_on_the_device(ctx):
     ctx.scan(p_col, abi.PRED_GREATER_THAN_EQUALS, lit, slot=1)
     ptr, _, n_scan, nc = ctx.scan_result_device(1)
     assert nc == n_chunks
-    _, begin = ctx.scan_fetch(1)   # chunk boundaries (host metadata of the reference table's chunks)
+    begin = ctx.scan_chunk_begin(1)   # chunk boundaries (host metadata of the reference table's chunks), no PosList download
 
     class W:
         __cuda_array_interface__ = {"shape": (max(n_scan, 1), 2), "typestr": "<i4", "data": (ptr, False), "version": 2}
