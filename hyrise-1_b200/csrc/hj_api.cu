@@ -763,6 +763,8 @@ int stage_hist(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int
   if (ps.fused) {
     if (pr.meta.n_tiles) {
       constexpr int VC = Cfg<K>::kP1Virtual;
+      if (F1 > uint32_t(kHistThreads / VC))  // cannot happen with the default geometry (VT >= kMaxDigits); HJ_TUNE_P1_SMALL_VT builds
+        return fail(ctx, HJ_ERR_INVALID, "this build of pass 1 scans at most %d level-1 digits, the join needs %u", kHistThreads / VC, F1);
       auto k = k_part1<K, kHistThreads, VC, p1_tile<K>()>;
       const size_t smem = part1_smem<K>(radix_bits);
       HJ_TRY(set_smem(ctx, k, smem));

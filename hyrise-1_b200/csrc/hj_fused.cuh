@@ -74,7 +74,10 @@ __global__ void __launch_bounds__(NT) k_part1(RelMeta rel, Tuple<K, false>* __re
   using T = Tuple<K, false>;
   constexpr int VT = NT / VC;
   constexpr int ITEMS = TILE / VT;
-  static_assert(VT >= kMaxDigits && TILE <= 65535, "one thread per digit in the scan; 16-bit fragment offsets");
+#ifndef HJ_TUNE_P1_SMALL_VT
+#define HJ_TUNE_P1_SMALL_VT 0  // 1: sweep builds with fewer threads per virtual CTA than kMaxDigits (the host refuses joins with F1 > VT)
+#endif
+  static_assert((VT >= kMaxDigits || HJ_TUNE_P1_SMALL_VT) && TILE <= 65535, "one thread per digit in the scan; 16-bit fragment offsets");
   extern __shared__ __align__(16) unsigned char s_raw[];
   uint32_t* s_hist = reinterpret_cast<uint32_t*>(s_raw);
   const uint32_t P = 1u << radix_bits;

@@ -1,6 +1,6 @@
 #!/bin/bash
 # Round-2 candidates (never run on a GPU yet): how P1 reads dictionary entries (L1 bypass).
-#   bash tests/build_variants5.sh && python tests/sweep_variants.py --scale 1.0 --runs default gather_cg gather_noalloc p2_mb3 p2_mb2 p2_smem p2_smem_mb3 default
+#   bash tests/build_variants5.sh && python tests/sweep_variants.py --scale 1.0 --runs default gather_cg gather_noalloc p2_mb3 p2_mb2 p2_smem p2_smem_mb3 p1_v8_t1024 default
 cd "$(dirname "$0")/.."
 OUT=hyrise-1_b200/csrc/variants; mkdir -p $OUT; rm -f $OUT/*.so $OUT/*.ptxas
 FLAGS="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC --expt-relaxed-constexpr -shared -I include"
@@ -15,6 +15,8 @@ build p2_mb3 -DHJ_TUNE_P2_MINBLOCKS=3 &
 build p2_mb2 -DHJ_TUNE_P2_MINBLOCKS=2 &
 wait
 # pass 2's small shared arrays in one struct: 11 % fewer SASS instructions in an issue-bound kernel (8 bytes of spill)
+# pass 1 with 8 tile streams of 1024 rows per SM (was 4 x 2048; pass 2's items are then only ~half full: read P1's time only)
+build p1_v8_t1024 -DHJ_TUNE_P1_VIRTUAL32=8 -DHJ_TUNE_P1_TILE32=1024 -DHJ_TUNE_P1_SMALL_VT=1 &
 build p2_smem -DHJ_TUNE_P2_SMEM=1 &
 build p2_smem_mb3 -DHJ_TUNE_P2_SMEM=1 -DHJ_TUNE_P2_MINBLOCKS=3 &
 wait
