@@ -705,6 +705,16 @@ int set_smem(hj_ctx* ctx, KernelT kernel, size_t bytes) {
 // The fused path (hj_fused.cuh) and the two-sweep path cut a relation into tiles of different sizes, so the choice is made
 // before prepare_relation builds the tile map. Rows received through the exchange carry RowIDs that only the two-sweep
 // kernels load (k_scatter1).
+#ifndef HJ_TUNE_BITS2_DELTA
+#define HJ_TUNE_BITS2_DELTA 0  // two-pass split: pass 2 takes radix_bits / 2 + delta bits (sweep builds; both passes stay <= 8 bits)
+#endif
+// low bits resolved by pass 2 (0: one pass)
+inline int pass2_bits(int radix_bits) {
+  if (radix_bits <= kSinglePassMaxBits) return 0;
+  const int b2 = radix_bits / 2 + HJ_TUNE_BITS2_DELTA;
+  return std::max(radix_bits - 8, std::min(8, b2));
+}
+
 template <bool PAY>
 bool use_fused(const hj_ctx* ctx, int bits2, int side) {
   return !PAY && bits2 > 0 && !(ctx->opts.flags & HJ_FLAG_TWO_SWEEP_PARTITION) && !ctx->xchg_rowids[side];
@@ -1055,7 +1065,7 @@ int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, in
 
   const int radix_bits = ctx->opts.radix_bits >= 0 ? std::min(ctx->opts.radix_bits, kMaxRadixBits)
                                                    : radix_bits_for(build->n_rows, sizeof(K) == 8 ? HJ_KEY_INT64 : HJ_KEY_INT32);
-  const int bits2 = radix_bits > kSinglePassMaxBits ? radix_bits / 2 : 0;
+  const int bits2 = pass2_bits(radix_bits);
 
   PreparedRel pb, pp;
   HJ_TRY(prepare_relation(ctx, build, 0, tile_rows<K, PAY>(ctx, bits2, 0), st, &pb));
@@ -1123,7 +1133,7 @@ int run_join_streamed(hj_ctx* ctx, const hj_relation* build, const hj_relation* 
   HJ_CUDA(ctx, cudaEventRecord(ctx->ev[0], st));
   const int radix_bits = ctx->opts.radix_bits >= 0 ? std::min(ctx->opts.radix_bits, kMaxRadixBits)
                                                    : radix_bits_for(build->n_rows, sizeof(K) == 8 ? HJ_KEY_INT64 : HJ_KEY_INT32);
-  const int bits2 = radix_bits > kSinglePassMaxBits ? radix_bits / 2 : 0;
+  const int bits2 = pass2_bits(radix_bits);
   const int probe_null_policy = !outer ? kNullDrop : ((ctx->opts.flags & HJ_FLAG_SQL_NULL_PROBE) ? kNullRoute : kNullAsValue);
 
   // slices: runs of whole chunks with about the same number of rows

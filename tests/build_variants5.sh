@@ -1,6 +1,6 @@
 #!/bin/bash
 # Round-2 candidates (never run on a GPU yet): how P1 reads dictionary entries (L1 bypass).
-#   bash tests/build_variants5.sh && python tests/sweep_variants.py --scale 1.0 --runs default gather_cg gather_noalloc p2_mb3 p2_mb2 p2_smem p2_smem_mb3 p1_v8_t1024 default
+#   bash tests/build_variants5.sh && python tests/sweep_variants.py --scale 1.0 --runs default gather_cg gather_noalloc p2_mb3 p2_mb2 p2_smem p2_smem_mb3 p1_v8_t1024 bits_6_8 bits_8_6 default
 cd "$(dirname "$0")/.."
 OUT=hyrise-1_b200/csrc/variants; mkdir -p $OUT; rm -f $OUT/*.so $OUT/*.ptxas
 FLAGS="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC --expt-relaxed-constexpr -shared -I include"
@@ -17,6 +17,10 @@ wait
 # pass 2's small shared arrays in one struct: 11 % fewer SASS instructions in an issue-bound kernel (8 bytes of spill)
 # pass 1 with 8 tile streams of 1024 rows per SM (was 4 x 2048; pass 2's items are then only ~half full: read P1's time only)
 build p1_v8_t1024 -DHJ_TUNE_P1_VIRTUAL32=8 -DHJ_TUNE_P1_TILE32=1024 -DHJ_TUNE_P1_SMALL_VT=1 &
+# the 14 radix bits split 6 + 8 / 8 + 6 instead of 7 + 7 (fragment length in pass 1 vs run length in pass 2)
+build bits_6_8 -DHJ_TUNE_BITS2_DELTA=1 &
+build bits_8_6 -DHJ_TUNE_BITS2_DELTA=-1 &
+wait
 build p2_smem -DHJ_TUNE_P2_SMEM=1 &
 build p2_smem_mb3 -DHJ_TUNE_P2_SMEM=1 -DHJ_TUNE_P2_MINBLOCKS=3 &
 wait
