@@ -14,13 +14,13 @@ build gather_noalloc -DHJ_TUNE_P1_GATHER=2 &
 build p2_mb3 -DHJ_TUNE_P2_MINBLOCKS=3 &
 build p2_mb2 -DHJ_TUNE_P2_MINBLOCKS=2 &
 wait
-# pass 2's small shared arrays in one struct: 11 % fewer SASS instructions in an issue-bound kernel (8 bytes of spill)
 # pass 1 with 8 tile streams of 1024 rows per SM (was 4 x 2048; pass 2's items are then only ~half full: read P1's time only)
 build p1_v8_t1024 -DHJ_TUNE_P1_VIRTUAL32=8 -DHJ_TUNE_P1_TILE32=1024 -DHJ_TUNE_P1_SMALL_VT=1 &
 # the 14 radix bits split 6 + 8 / 8 + 6 instead of 7 + 7 (fragment length in pass 1 vs run length in pass 2)
 build bits_6_8 -DHJ_TUNE_BITS2_DELTA=1 &
 build bits_8_6 -DHJ_TUNE_BITS2_DELTA=-1 &
 wait
+# pass 2's small shared arrays in one struct: 11 % fewer SASS instructions in an issue-bound kernel (8 bytes of spill)
 build p2_smem -DHJ_TUNE_P2_SMEM=1 &
 build p2_smem_mb3 -DHJ_TUNE_P2_SMEM=1 -DHJ_TUNE_P2_MINBLOCKS=3 &
 wait
