@@ -23,12 +23,15 @@ def aggregate_column(values, is_null=None):
         acc = np.add.accumulate(v.astype(np.float64))[-1]   # sequential double accumulation in row order (:173-175)
         out["sum"] = float(acc)
         out["avg"] = float(acc) / len(v)
-        lo = hi = v[0]
-        for x in v[1:]:   # plain < and > on the column type: a NaN replaces nothing and is replaced by nothing
-            if x < lo:
-                lo = x
-            if x > hi:
-                hi = x
+        if np.isnan(v).any():
+            lo = hi = v[0]
+            for x in v[1:]:   # plain < and > on the column type: a NaN replaces nothing and is replaced by nothing
+                if x < lo:
+                    lo = x
+                if x > hi:
+                    hi = x
+        else:                 # without NaNs the row-by-row replacement is the minimum / maximum
+            lo, hi = v.min(), v.max()
         out["min"], out["max"] = float(lo), float(hi)
     else:
         total = int(v.astype(np.int64).sum(dtype=np.int64))   # int64_t accumulator, wraps on overflow
