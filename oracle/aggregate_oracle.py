@@ -39,3 +39,32 @@ def aggregate_column(values, is_null=None):
         out["avg"] = float(np.add.accumulate(v.astype(np.float64))[-1]) / len(v)   # AVG accumulates in double
         out["min"], out["max"] = int(v.min()), int(v.max())
     return out
+
+
+def aggregate_grouped(columns, group_by, aggregates):
+    """Aggregate WITH group-by columns (aggregate.cpp:254-420: the group key of a row is the tuple of its group-by values,
+    NULL being a value of its own; groups appear in first-occurrence order, which the reference does not guarantee either).
+    columns: {name: (values, is_null)}; group_by: [name]; aggregates: [(function, name or None for COUNT(*))] with function in
+    "min" / "max" / "sum" / "avg" / "count". Returns a list of rows: group-by values (None = NULL) followed by the aggregates,
+    with the types and NULL rules of aggregate_column()."""
+    n_rows = len(next(iter(columns.values()))[0]) if columns else 0
+    groups, order = {}, []
+    for i in range(n_rows):
+        key = tuple(None if columns[g][1][i] else columns[g][0][i].item() for g in group_by)
+        if key not in groups:
+            groups[key] = []
+            order.append(key)
+        groups[key].append(i)
+    rows = []
+    for key in order:
+        idx = np.array(groups[key], dtype=np.int64)
+        row = list(key)
+        for function, name in aggregates:
+            if name is None:                       # COUNT(*): rows of the group (aggregate.cpp:424-431)
+                row.append(len(idx))
+                continue
+            values, is_null = columns[name]
+            result = aggregate_column(values[idx], np.asarray(is_null)[idx])
+            row.append(result[function])
+        rows.append(row)
+    return rows

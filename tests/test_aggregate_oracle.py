@@ -75,3 +75,21 @@ def test_integer_sum_wraps_like_an_int64_accumulator_and_avg_runs_in_double():
     assert got["sum"] == (3 * 2**62 + 2**63) % 2**64 - 2**63
     assert got["avg"] == float(2**62)
     assert functor_restated(v, np.zeros(3, np.uint8)) == got
+
+
+# ---- with group-by columns: oracle groundwork for the device GROUP BY (no device path yet) --------------------
+def rows_match(got, want):
+    """check_table_equal, unordered (testing_assert.cpp:118-254): same multiset of rows, floats within EPSILON."""
+    if len(got) != len(want):
+        return False
+    key = lambda row: tuple((v is None, 0 if v is None else round(float(v), 3)) for v in row)
+    got, want = sorted(got, key=key), sorted(want, key=key)
+    return all(len(g) == len(w) and all(am.matches_reference(a, b) for a, b in zip(g, w)) for g, w in zip(got, want))
+
+
+@pytest.mark.parametrize("case", FIX["grouped_cases"], ids=[c["name"] for c in FIX["grouped_cases"]])
+def test_grouped_oracle_reproduces_reference_expectation(case):
+    table = FIX["grouped_tables"][case["table"]]
+    columns = {name: am.column_of(table, name) for name in table["columns"]}
+    got = ao.aggregate_grouped(columns, case["group_by"], [tuple(a) for a in case["aggregates"]])
+    assert rows_match(got, case["expected_rows"]), (got, case["expected_rows"], case["cite"])
