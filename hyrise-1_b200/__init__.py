@@ -305,10 +305,11 @@ class HashJoin:
         """hj_translate_device: RowIDs of a device-resident reference-table input -> rows of the referenced data table, in place."""
         self._check(self._l.hj_translate_device(self._ctx, device_inout, n_rows, C.byref(input_relation), stream))
 
-    def gather_column(self, device_pos, n_rows, column, stream=None):
-        """hj_gather_column: (values device ptr, nulls device ptr, key type) of `column` at the rows of a device PosList."""
+    def gather_column(self, device_pos, n_rows, column, slot=0, stream=None):
+        """hj_gather_column: (values device ptr, nulls device ptr, key type) of `column` at the rows of a device PosList;
+        the output stays valid until the next gather into the same slot."""
         v, n, t = C.c_void_p(), C.c_void_p(), C.c_int()
-        self._check(self._l.hj_gather_column(self._ctx, device_pos, n_rows, C.byref(column), stream, C.byref(v), C.byref(n),
+        self._check(self._l.hj_gather_column(self._ctx, device_pos, n_rows, C.byref(column), slot, stream, C.byref(v), C.byref(n),
                                              C.byref(t)))
         return v.value, n.value, t.value
 
@@ -318,6 +319,22 @@ class HashJoin:
         a = abi.Aggregate()
         self._check(self._l.hj_aggregate_column(self._ctx, device_values, device_nulls, n_rows, key_type, stream, C.byref(a)))
         return self._aggregate_dict(a)
+
+    def aggregate_grouped(self, group_keys, group_nulls, group_key_type, values, value_nulls, value_type, n_rows, max_groups=0,
+                          stream=None):
+        """hj_aggregate_grouped + fetch: {group key or None: aggregate dict} for device columns (pointers as ints)."""
+        info = abi.GroupInfo()
+        self._check(self._l.hj_aggregate_grouped(self._ctx, group_keys, group_nulls, group_key_type, values, value_nulls, value_type,
+                                                 n_rows, max_groups, stream, C.byref(info)))
+        groups = (abi.Group * max(info.n_groups, 1))()
+        self._check(self._l.hj_aggregate_grouped_fetch(self._ctx, groups, info.n_groups))
+        out = {}
+        for i in range(info.n_groups):
+            g = groups[i]
+            key = None if g.key_is_null else g.key
+            assert key not in out, "a group was emitted twice"
+            out[key] = self._aggregate_dict(g.agg)
+        return out
 
     def aggregate_relation(self, column, stream=None):
         """hj_aggregate_relation: the same aggregates over a column given as chunk descriptors (host or device resident,

@@ -62,6 +62,14 @@ class Aggregate(C.Structure):
                 ("min_double", C.c_double), ("max_double", C.c_double)]
 
 
+class Group(C.Structure):
+    _fields_ = [("key", C.c_int64), ("key_is_null", C.c_int32), ("reserved", C.c_int32), ("agg", Aggregate)]
+
+
+class GroupInfo(C.Structure):
+    _fields_ = [("n_groups", C.c_uint64), ("n_rows", C.c_uint64)]
+
+
 class ScanInfo(C.Structure):
     _fields_ = [("n_rows", C.c_uint64), ("n_chunks", C.c_uint32), ("n_nonempty_chunks", C.c_uint32)]
 
@@ -105,9 +113,12 @@ SYMBOLS = {
     "hj_scan_value_ids": (C.c_int, [C.c_void_p, C.POINTER(Relation), C.c_int, C.c_void_p, C.c_int, C.c_uint32, C.c_void_p,
                                     C.POINTER(ScanInfo)]),
     "hj_translate_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(Relation), C.c_void_p]),
-    "hj_gather_column": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(Relation), C.c_void_p, C.POINTER(C.c_void_p),
+    "hj_gather_column": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(Relation), C.c_int, C.c_void_p, C.POINTER(C.c_void_p),
                                    C.POINTER(C.c_void_p), C.POINTER(C.c_int)]),
     "hj_aggregate_column": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p, C.POINTER(Aggregate)]),
+    "hj_aggregate_grouped": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_uint64,
+                                       C.c_uint64, C.c_void_p, C.POINTER(GroupInfo)]),
+    "hj_aggregate_grouped_fetch": (C.c_int, [C.c_void_p, C.POINTER(Group), C.c_uint64]),
     "hj_aggregate_relation": (C.c_int, [C.c_void_p, C.POINTER(Relation), C.c_void_p, C.POINTER(Aggregate)]),
     "hj_scan_result_device": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
                                         C.POINTER(C.c_uint64), C.POINTER(C.c_uint32)]),

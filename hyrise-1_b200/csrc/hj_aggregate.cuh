@@ -11,6 +11,7 @@
 // reproducible run to run; they differ from the reference's row-order sum by rounding only — DESIGN.md §8).
 #pragma once
 #include <cstdint>
+#include <cstring>
 #include <type_traits>
 
 #include "hj_kernels.cuh"
@@ -169,6 +170,209 @@ __global__ void __launch_bounds__(32) k_aggregate_final(const AggPartial* __rest
     agg_merge(a, b);
   }
   if (threadIdx.x == 0) out[0] = a;
+}
+
+
+// =====================================================================================================================
+// GROUP BY one integer column (Aggregate with one group-by column, aggregate.cpp:254-420): a hash table of the distinct
+// group keys with the same accumulators as above per group.
+//   G1 k_group_accumulate  every CTA pre-aggregates into a small shared-memory table (few groups: no global atomic per
+//                          row — same-address global atomics serialise at ~21 ns), rows whose group finds no place there
+//                          go to the global table directly; at the end the CTA's groups are merged into the global table
+//   G2 k_group_count / k_group_emit  number of groups, then one output record per group (order unspecified, as in the
+//                          reference: "we do not guarantee a stable operation with regards to positions")
+// NULL is a group key of its own (slot `cap`), and so is the one key value that serves as the EMPTY marker (slot cap + 1).
+// Every probe loop is bounded by the table size; a full global table raises *overflow instead of spinning.
+// MIN / MAX of float / double columns are kept as order-preserving int64 images of the doubles (sortable()).
+// =====================================================================================================================
+constexpr long long kGroupEmpty = static_cast<long long>(0x8000000000000000ull);
+constexpr int kGroupSmemSlots = 256;  // power of two; + 2 special slots
+constexpr int kGroupSmemProbes = 8;
+
+struct GroupTable {  // structure of arrays, `cap` + 2 entries each (cap = power of two)
+  long long* key;
+  unsigned long long* rows;    // COUNT(*)
+  unsigned long long* values;  // COUNT(column)
+  long long* sum_i;
+  double* sum_d;
+  long long* mn;
+  long long* mx;
+  unsigned long long cap;
+};
+
+__host__ __device__ __forceinline__ long long sortable(double d) {
+#ifdef __CUDA_ARCH__
+  const long long b = __double_as_longlong(d);
+#else
+  long long b;
+  memcpy(&b, &d, 8);
+#endif
+  return b >= 0 ? b : b ^ 0x7FFFFFFFFFFFFFFFll;
+}
+__host__ __device__ __forceinline__ double unsortable(long long s) {
+  const long long b = s >= 0 ? s : s ^ 0x7FFFFFFFFFFFFFFFll;
+#ifdef __CUDA_ARCH__
+  return __longlong_as_double(b);
+#else
+  double d;
+  memcpy(&d, &b, 8);
+  return d;
+#endif
+}
+
+__device__ __forceinline__ uint32_t group_hash(long long k) {
+  return hash_key(static_cast<int64_t>(k));
+}
+
+// slot of `key` in an open-addressing table of `mask + 1` slots, inserting it if absent; at most `max_probes` slots are
+// tried; returns mask + 1 ... never: returns 0xFFFFFFFFFFFFFFFF when no slot was found
+__device__ __forceinline__ unsigned long long group_slot(long long* keys, unsigned long long mask, long long key, unsigned long long max_probes) {
+  unsigned long long s = group_hash(key) & mask;
+  for (unsigned long long p = 0; p < max_probes; ++p) {
+    const long long prev = atomicCAS(reinterpret_cast<unsigned long long*>(keys + s), static_cast<unsigned long long>(kGroupEmpty),
+                                     static_cast<unsigned long long>(key));
+    if (prev == kGroupEmpty || prev == key) return s;
+    s = (s + 1) & mask;
+  }
+  return ~0ull;
+}
+
+// one row's contribution (T = type of the aggregate column; has_value false: NULL value or COUNT(*) only)
+template <typename T>
+__device__ __forceinline__ void group_update(unsigned long long* rows, unsigned long long* values, long long* sum_i, double* sum_d,
+                                             long long* mn, long long* mx, unsigned long long s, bool has_value, T v) {
+  atomicAdd(rows + s, 1ull);
+  if (!has_value) return;
+  atomicAdd(values + s, 1ull);
+  long long x;
+  if constexpr (std::is_floating_point<T>::value) {
+    atomicAdd(sum_d + s, static_cast<double>(v));
+    x = sortable(static_cast<double>(v));
+  } else {
+    x = static_cast<long long>(v);
+    atomicAdd(reinterpret_cast<unsigned long long*>(sum_i + s), static_cast<unsigned long long>(x));
+  }
+  atomicMin(mn + s, x);
+  atomicMax(mx + s, x);
+}
+
+__global__ void k_group_init(GroupTable t) {
+  const unsigned long long n = t.cap + 2;
+  for (unsigned long long i = blockIdx.x * static_cast<unsigned long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<unsigned long long>(gridDim.x) * blockDim.x) {
+    t.key[i] = kGroupEmpty;
+    t.rows[i] = 0;
+    t.values[i] = 0;
+    t.sum_i[i] = 0;
+    t.sum_d[i] = 0.0;
+    t.mn[i] = INT64_MAX;
+    t.mx[i] = INT64_MIN;
+  }
+}
+
+// G1. GK = type of the group column (int32_t / int64_t), T = type of the aggregate column (values may be nullptr: COUNT(*)).
+template <typename GK, typename T>
+__global__ void __launch_bounds__(kAggThreads) k_group_accumulate(const GK* __restrict__ group_keys, const uint8_t* __restrict__ group_nulls,
+                                                                  const T* __restrict__ values, const uint8_t* __restrict__ value_nulls,
+                                                                  unsigned long long n, GroupTable t, uint32_t* __restrict__ overflow) {
+  constexpr int S = kGroupSmemSlots;
+  __shared__ long long s_key[S + 2];
+  __shared__ unsigned long long s_rows[S + 2], s_values[S + 2];
+  __shared__ long long s_sum_i[S + 2], s_mn[S + 2], s_mx[S + 2];
+  __shared__ double s_sum_d[S + 2];
+  for (int i = threadIdx.x; i < S + 2; i += kAggThreads) {
+    s_key[i] = kGroupEmpty;
+    s_rows[i] = 0;
+    s_values[i] = 0;
+    s_sum_i[i] = 0;
+    s_sum_d[i] = 0.0;
+    s_mn[i] = INT64_MAX;
+    s_mx[i] = INT64_MIN;
+  }
+  __syncthreads();
+  const unsigned long long stride = static_cast<unsigned long long>(gridDim.x) * kAggThreads;
+  for (unsigned long long i = static_cast<unsigned long long>(blockIdx.x) * kAggThreads + threadIdx.x; i < n; i += stride) {
+    const bool key_null = group_nulls && __ldg(group_nulls + i);
+    const long long key = key_null ? 0 : static_cast<long long>(__ldg(group_keys + i));
+    const bool has_value = values && !(value_nulls && __ldg(value_nulls + i));
+    const T v = has_value ? __ldg(values + i) : T(0);
+    if (key_null || key == kGroupEmpty) {  // the two special groups always have their shared-memory slot
+      group_update<T>(s_rows, s_values, s_sum_i, s_sum_d, s_mn, s_mx, key_null ? S : S + 1, has_value, v);
+      continue;
+    }
+    const unsigned long long s = group_slot(s_key, S - 1, key, kGroupSmemProbes);
+    if (s != ~0ull) {
+      group_update<T>(s_rows, s_values, s_sum_i, s_sum_d, s_mn, s_mx, s, has_value, v);
+    } else {  // the CTA's table has no room for this group: straight to the global table
+      const unsigned long long g = group_slot(t.key, t.cap - 1, key, t.cap);
+      if (g == ~0ull) {
+        *overflow = 1;
+        continue;
+      }
+      group_update<T>(t.rows, t.values, t.sum_i, t.sum_d, t.mn, t.mx, g, has_value, v);
+    }
+  }
+  __syncthreads();
+  // merge this CTA's groups into the global table
+  for (int i = threadIdx.x; i < S + 2; i += kAggThreads) {
+    if (s_rows[i] == 0) continue;
+    unsigned long long g;
+    if (i >= S) {
+      g = t.cap + (i - S);
+    } else {
+      g = group_slot(t.key, t.cap - 1, s_key[i], t.cap);
+      if (g == ~0ull) {
+        *overflow = 1;
+        continue;
+      }
+    }
+    atomicAdd(t.rows + g, s_rows[i]);
+    if (s_values[i]) {
+      atomicAdd(t.values + g, s_values[i]);
+      atomicAdd(reinterpret_cast<unsigned long long*>(t.sum_i + g), static_cast<unsigned long long>(s_sum_i[i]));
+      atomicAdd(t.sum_d + g, s_sum_d[i]);
+      atomicMin(t.mn + g, s_mn[i]);
+      atomicMax(t.mx + g, s_mx[i]);
+    }
+  }
+}
+
+struct GroupRecord {  // one per group, in the layout hj_group of include/hj.h
+  long long key;
+  unsigned long long rows, values;
+  long long sum_i;
+  double sum_d;
+  long long mn, mx;
+  unsigned long long key_is_null;
+};
+
+// G2. *n_groups must be zero before k_group_emit; out == nullptr: only count.
+__global__ void k_group_emit(GroupTable t, GroupRecord* __restrict__ out, unsigned long long* __restrict__ n_groups) {
+  const unsigned long long n = t.cap + 2;
+  const unsigned long long stride = static_cast<unsigned long long>(gridDim.x) * blockDim.x;
+  const uint32_t lane = threadIdx.x & 31u;
+  // whole warps run the loop together (blockDim is a multiple of 32): one atomic per warp and trip, not per group
+  for (unsigned long long base = blockIdx.x * static_cast<unsigned long long>(blockDim.x) + (threadIdx.x & ~31u); base < n; base += stride) {
+    const unsigned long long i = base + lane;
+    const bool live = i < n && t.rows[i] != 0;
+    const uint32_t mask = __ballot_sync(0xffffffffu, live);
+    if (mask == 0) continue;
+    unsigned long long first = 0;
+    if (lane == 0) first = atomicAdd(n_groups, static_cast<unsigned long long>(__popc(mask)));
+    first = __shfl_sync(0xffffffffu, first, 0);
+    if (!live || !out) continue;
+    const unsigned long long dst = first + __popc(mask & ((1u << lane) - 1u));
+    GroupRecord r;
+    r.key = i == t.cap ? 0 : i == t.cap + 1 ? kGroupEmpty : t.key[i];
+    r.rows = t.rows[i];
+    r.values = t.values[i];
+    r.sum_i = t.sum_i[i];
+    r.sum_d = t.sum_d[i];
+    r.mn = t.mn[i];
+    r.mx = t.mx[i];
+    r.key_is_null = i == t.cap ? 1 : 0;
+    out[dst] = r;
+  }
 }
 
 }  // namespace hj

@@ -146,8 +146,8 @@ struct hj_ctx {
   // receive sets: 0 = build, 1 = probe (or probe slices 0, 2, ..), 2 = probe slices 1, 3, ..
   DevBuf xchg_counts[2], xchg_cnt_dev, xchg_send_keys[2], xchg_send_rids[2], xchg_send_nulls[2], xchg_recv_keys[3],
       xchg_recv_rids[3], xchg_recv_nulls[3];
-  DevBuf ref_arena[3], ref_out[3];  // REFERENCE segments: staged referenced columns + PosLists / gathered keys + flags
-                                    // ([0] build, [1] probe / scan, [2] hj_gather_column)
+  DevBuf ref_arena[2 + HJ_GATHER_SLOTS], ref_out[2 + HJ_GATHER_SLOTS];  // REFERENCE segments: staged referenced columns +
+                                    // PosLists / gathered keys + flags ([0] build, [1] probe / scan, [2 + slot] hj_gather_column)
   uint64_t ref_h2d_bytes = 0;
   DevBuf acc_build, acc_probe;      // sliced sharded join: the slices' PosLists, appended
   cudaEvent_t ev_x[2] = {};         // sliced sharded join: slice set exchanged (recorded on copy_in, the exchange stream)
@@ -159,6 +159,9 @@ struct hj_ctx {
   // TableScan (N4): scratch (freed by hj_release_scratch) and the result slots (owned by the scan's caller)
   DevBuf scan_bounds, scan_mask, scan_tile_count, scan_tile_base, scan_ref_ptrs, scan_totals;
   DevBuf agg_partials;  // hj_aggregate_column: one AggPartial per CTA + the folded result
+  DevBuf group_table, group_out, group_misc;  // hj_aggregate_grouped: hash table (SoA), one GroupRecord per group, count + overflow
+  uint64_t group_n = 0, group_rows = 0;
+  bool group_valid = false, group_floating = false;
   DevBuf scan_pos[HJ_SCAN_SLOTS], scan_chunk_begin[HJ_SCAN_SLOTS];
   uint64_t scan_rows[HJ_SCAN_SLOTS] = {};
   uint32_t scan_chunks[HJ_SCAN_SLOTS] = {};
@@ -174,9 +177,13 @@ struct hj_ctx {
                       &out_build[0], &out_build[1], &out_probe[0], &out_probe[1], &misc, &xchg_counts[0], &xchg_counts[1], &xchg_cnt_dev, &xchg_send_keys[0],
                       &xchg_send_keys[1], &xchg_send_rids[0], &xchg_send_rids[1], &xchg_send_nulls[0], &xchg_send_nulls[1],
                       &xchg_recv_keys[0], &xchg_recv_keys[1], &xchg_recv_rids[0], &xchg_recv_rids[1], &xchg_recv_nulls[0],
-                      &xchg_recv_nulls[1], &xchg_recv_keys[2], &xchg_recv_rids[2], &xchg_recv_nulls[2], &acc_build, &acc_probe, &ref_arena[0], &ref_arena[1], &ref_arena[2], &ref_out[0], &ref_out[1], &ref_out[2],
-                      &xchg_hdl_dev, &scan_bounds, &scan_mask, &scan_tile_count, &scan_tile_base, &scan_ref_ptrs, &scan_totals, &agg_partials})
+                      &xchg_recv_nulls[1], &xchg_recv_keys[2], &xchg_recv_rids[2], &xchg_recv_nulls[2], &acc_build, &acc_probe, &ref_arena[0], &ref_arena[1], &ref_out[0], &ref_out[1],
+                      &xchg_hdl_dev, &scan_bounds, &scan_mask, &scan_tile_count, &scan_tile_base, &scan_ref_ptrs, &scan_totals, &agg_partials, &group_table, &group_out, &group_misc})
       all_bufs.push_back(b);
+    for (int i = 2; i < 2 + HJ_GATHER_SLOTS; ++i) {
+      all_bufs.push_back(&ref_arena[i]);
+      all_bufs.push_back(&ref_out[i]);
+    }
   }
 };
 
@@ -1575,12 +1582,13 @@ int hj_scan_value_ids(hj_ctx* ctx, const hj_relation* column, int predicate, con
 }
 
 // ------------------------------------------------------------------------------------------------ column values at a PosList
-int hj_gather_column(hj_ctx* ctx, const hj_row_id* device_pos, uint64_t n_rows, const hj_relation* column, void* cuda_stream,
-                     const void** out_values, const uint8_t** out_nulls, int* out_key_type) {
+int hj_gather_column(hj_ctx* ctx, const hj_row_id* device_pos, uint64_t n_rows, const hj_relation* column, int slot,
+                     void* cuda_stream, const void** out_values, const uint8_t** out_nulls, int* out_key_type) {
   if (!ctx) return HJ_ERR_INVALID;
   if (!out_values || !out_nulls) return fail(ctx, HJ_ERR_INVALID, "out_values / out_nulls is NULL");
   *out_values = nullptr;
   *out_nulls = nullptr;
+  if (slot < 0 || slot >= HJ_GATHER_SLOTS) return fail(ctx, HJ_ERR_INVALID, "gather slot %d outside 0..%d", slot, HJ_GATHER_SLOTS - 1);
   if (!column) return fail(ctx, HJ_ERR_INVALID, "column is NULL");
   if (column->location != HJ_LOC_DEVICE)
     return fail(ctx, HJ_ERR_INVALID, "hj_gather_column reads a device-resident column through a device-resident PosList");
@@ -1613,10 +1621,10 @@ int hj_gather_column(hj_ctx* ctx, const hj_row_id* device_pos, uint64_t n_rows, 
   HJ_TRY(validate_relation(ctx, &rel, "gather"));
   HJ_TRY(check_ctx(ctx));
   cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
-  auto* flag = reinterpret_cast<uint32_t*>(static_cast<char*>(ctx->pinned) + kPinnedRefFlags) + 2;
+  auto* flag = reinterpret_cast<uint32_t*>(static_cast<char*>(ctx->pinned) + kPinnedRefFlags) + 2 + slot;  // words 2..5 of 8
   *flag = 0;
   RefRewrite rw;
-  HJ_TRY(gather_references(ctx, &rel, 2, st, &rw, type));
+  HJ_TRY(gather_references(ctx, &rel, 2 + slot, st, &rw, type));
   HJ_CUDA(ctx, cudaStreamSynchronize(st));
   if (*flag) return fail(ctx, HJ_ERR_INVALID, "gather: a PosList entry points outside the column");
   *out_values = rw.segs[0].values;
@@ -1654,6 +1662,116 @@ int hj_aggregate_column(hj_ctx* ctx, const void* device_values, const uint8_t* d
   }
   HJ_LAUNCH_CHECK(ctx, "k_aggregate_partial");
   return finish_aggregate(ctx, partials, grid, n_rows, key_type, st, out);
+}
+
+int hj_aggregate_grouped(hj_ctx* ctx, const void* device_group_keys, const uint8_t* device_group_nulls, int group_key_type,
+                         const void* device_values, const uint8_t* device_value_nulls, int value_type, uint64_t n_rows,
+                         uint64_t max_groups, void* cuda_stream, hj_group_info* out_info) {
+  if (!ctx) return HJ_ERR_INVALID;
+  if (!out_info) return fail(ctx, HJ_ERR_INVALID, "out_info is NULL");
+  std::memset(out_info, 0, sizeof(*out_info));
+  ctx->group_valid = false;
+  if (group_key_type != HJ_KEY_INT32 && group_key_type != HJ_KEY_INT64)
+    return fail(ctx, HJ_ERR_INVALID, "group-by column of key type %d: int32 / int64 only", group_key_type);
+  if (device_values && (value_type < HJ_KEY_INT32 || value_type > HJ_KEY_DOUBLE)) return fail(ctx, HJ_ERR_INVALID, "value type %d", value_type);
+  if (n_rows && !device_group_keys) return fail(ctx, HJ_ERR_INVALID, "device_group_keys is NULL");
+  if (!device_values) value_type = HJ_KEY_INT32;  // COUNT(*) only
+  // table size: a power of two >= 2 x the number of groups the caller expects (0: every row its own group)
+  const uint64_t want = std::max<uint64_t>(1024, 2 * (max_groups ? std::min(max_groups, n_rows) : n_rows));
+  uint64_t cap = 1024;
+  while (cap < want) cap <<= 1;
+  if (cap > (uint64_t(1) << 31)) return fail(ctx, HJ_ERR_TOO_LARGE, "group table of %llu slots: pass max_groups", (unsigned long long)cap);
+  HJ_TRY(check_ctx(ctx));
+  cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
+  const size_t entries = size_t(cap) + 2;
+  HJ_TRY(ensure(ctx, ctx->group_table, entries * 8 * 7));
+  HJ_TRY(ensure(ctx, ctx->group_misc, 16));
+  char* base = static_cast<char*>(ctx->group_table.p);
+  GroupTable t;
+  t.key = reinterpret_cast<long long*>(base);
+  t.rows = reinterpret_cast<unsigned long long*>(base + entries * 8);
+  t.values = reinterpret_cast<unsigned long long*>(base + entries * 16);
+  t.sum_i = reinterpret_cast<long long*>(base + entries * 24);
+  t.sum_d = reinterpret_cast<double*>(base + entries * 32);
+  t.mn = reinterpret_cast<long long*>(base + entries * 40);
+  t.mx = reinterpret_cast<long long*>(base + entries * 48);
+  t.cap = cap;
+  auto* n_groups = static_cast<unsigned long long*>(ctx->group_misc.p);
+  auto* overflow = reinterpret_cast<uint32_t*>(static_cast<char*>(ctx->group_misc.p) + 8);
+  HJ_CUDA(ctx, cudaMemsetAsync(ctx->group_misc.p, 0, 16, st));
+  const uint32_t init_grid = static_cast<uint32_t>(std::min<uint64_t>((entries + 255) / 256, uint64_t(ctx->n_sms) * 8));
+  k_group_init<<<init_grid, 256, 0, st>>>(t);
+  HJ_LAUNCH_CHECK(ctx, "k_group_init");
+  const uint32_t grid = static_cast<uint32_t>(std::max<uint64_t>(1, std::min<uint64_t>((n_rows + kAggThreads - 1) / kAggThreads,
+                                                                                      uint64_t(ctx->n_sms) * 4)));
+#define HJ_GROUP_LAUNCH(GK, T)                                                                                                   \
+  k_group_accumulate<GK, T><<<grid, kAggThreads, 0, st>>>(static_cast<const GK*>(device_group_keys), device_group_nulls,          \
+                                                          static_cast<const T*>(device_values), device_value_nulls, n_rows, t, overflow)
+  const bool g64 = group_key_type == HJ_KEY_INT64;
+  switch (value_type) {
+    case HJ_KEY_INT32: if (g64) HJ_GROUP_LAUNCH(int64_t, int32_t); else HJ_GROUP_LAUNCH(int32_t, int32_t); break;
+    case HJ_KEY_INT64: if (g64) HJ_GROUP_LAUNCH(int64_t, int64_t); else HJ_GROUP_LAUNCH(int32_t, int64_t); break;
+    case HJ_KEY_FLOAT: if (g64) HJ_GROUP_LAUNCH(int64_t, float); else HJ_GROUP_LAUNCH(int32_t, float); break;
+    default: if (g64) HJ_GROUP_LAUNCH(int64_t, double); else HJ_GROUP_LAUNCH(int32_t, double);
+  }
+#undef HJ_GROUP_LAUNCH
+  HJ_LAUNCH_CHECK(ctx, "k_group_accumulate");
+  k_group_emit<<<init_grid, 256, 0, st>>>(t, nullptr, n_groups);  // count
+  HJ_LAUNCH_CHECK(ctx, "k_group_emit");
+  auto* host = reinterpret_cast<unsigned long long*>(static_cast<char*>(ctx->pinned) + kPinnedAggregate);
+  HJ_CUDA(ctx, cudaMemcpyAsync(host, ctx->group_misc.p, 16, cudaMemcpyDeviceToHost, st));
+  HJ_CUDA(ctx, cudaStreamSynchronize(st));
+  if (reinterpret_cast<const uint32_t*>(host)[2])
+    return fail(ctx, HJ_ERR_CAPACITY, "more than %llu groups: the group table is full (max_groups was %llu)", (unsigned long long)cap,
+                (unsigned long long)max_groups);
+  const uint64_t n = host[0];
+  HJ_TRY(ensure(ctx, ctx->group_out, std::max<uint64_t>(1, n) * sizeof(GroupRecord)));
+  HJ_CUDA(ctx, cudaMemsetAsync(n_groups, 0, 8, st));
+  if (n) {
+    k_group_emit<<<init_grid, 256, 0, st>>>(t, static_cast<GroupRecord*>(ctx->group_out.p), n_groups);
+    HJ_LAUNCH_CHECK(ctx, "k_group_emit");
+  }
+  HJ_CUDA(ctx, cudaStreamSynchronize(st));
+  ctx->group_n = n;
+  ctx->group_rows = n_rows;
+  ctx->group_floating = device_values && value_type >= HJ_KEY_FLOAT;
+  ctx->group_valid = true;
+  out_info->n_groups = n;
+  out_info->n_rows = n_rows;
+  return HJ_OK;
+}
+
+int hj_aggregate_grouped_fetch(hj_ctx* ctx, hj_group* groups, uint64_t capacity) {
+  if (!ctx) return HJ_ERR_INVALID;
+  if (!ctx->group_valid) return fail(ctx, HJ_ERR_STATE, "no grouped aggregate result");
+  const uint64_t n = ctx->group_n;
+  if (capacity < n) return fail(ctx, HJ_ERR_CAPACITY, "capacity %llu < %llu groups", (unsigned long long)capacity, (unsigned long long)n);
+  if (n && !groups) return fail(ctx, HJ_ERR_INVALID, "NULL output buffer");
+  if (!n) return HJ_OK;
+  HJ_TRY(check_ctx(ctx));
+  std::vector<GroupRecord> rec(n);
+  HJ_CUDA(ctx, cudaMemcpyAsync(rec.data(), ctx->group_out.p, n * sizeof(GroupRecord), cudaMemcpyDeviceToHost, ctx->own_stream));
+  HJ_CUDA(ctx, cudaStreamSynchronize(ctx->own_stream));
+  const bool floating = ctx->group_floating;
+  for (uint64_t i = 0; i < n; ++i) {  // the device record in the ABI's layout (MIN / MAX of doubles back from their sortable images)
+    const GroupRecord& r = rec[i];
+    hj_group& g = groups[i];
+    std::memset(&g, 0, sizeof(g));
+    g.key = r.key;
+    g.key_is_null = static_cast<int32_t>(r.key_is_null);
+    g.agg.n_rows = r.rows;
+    g.agg.n_values = r.values;
+    g.agg.is_floating = floating ? 1 : 0;
+    g.agg.sum_int = floating ? 0 : r.sum_i;
+    g.agg.sum_double = floating ? r.sum_d : static_cast<double>(r.sum_i);
+    if (r.values) {
+      g.agg.min_int = floating ? 0 : r.mn;
+      g.agg.max_int = floating ? 0 : r.mx;
+      g.agg.min_double = floating ? unsortable(r.mn) : static_cast<double>(r.mn);
+      g.agg.max_double = floating ? unsortable(r.mx) : static_cast<double>(r.mx);
+    }
+  }
+  return HJ_OK;
 }
 
 int hj_aggregate_relation(hj_ctx* ctx, const hj_relation* column, void* cuda_stream, hj_aggregate* out) {

@@ -366,12 +366,14 @@ int hj_translate_device(hj_ctx* ctx, hj_row_id* device_inout, uint64_t n, const 
  * the rows of a device-resident PosList — what every operator after the join (Aggregate, Projection, the next
  * join) does first when it reads a ReferenceColumn (reference_column_iterable.hpp:30-75: per RowID the referenced
  * chunk's value or NULL; NULL_ROW_ID = NULL). `device_pos` is typically a side of hj_result_device or a result of
- * hj_scan_result_device. Output, in device memory owned by ctx and valid until the next hj_gather_column /
+ * hj_scan_result_device. Output, in device memory owned by ctx and valid until the next hj_gather_column into the
+ * same `slot` (0..HJ_GATHER_SLOTS-1: e.g. a group-by column and an aggregate column side by side) /
  * hj_release_scratch / hj_destroy: out_values = n_rows values of the column's type (*out_key_type: int32 / int64 as
  * such, float / double as their IEEE bit patterns in 4 / 8 bytes, NaNs canonicalised; 0 where NULL) and out_nulls =
  * one byte per row. Runs the same kernel the join uses for REFERENCE key columns (k_gather_refs).
  * HJ_ERR_INVALID if a RowID points outside the column. */
-int hj_gather_column(hj_ctx* ctx, const hj_row_id* device_pos, uint64_t n_rows, const hj_relation* column,
+#define HJ_GATHER_SLOTS 4
+int hj_gather_column(hj_ctx* ctx, const hj_row_id* device_pos, uint64_t n_rows, const hj_relation* column, int slot,
                      void* cuda_stream, const void** out_values, const uint8_t** out_nulls, int* out_key_type);
 
 /* Ungrouped aggregates of a column in device memory (typically hj_gather_column's output: the column of the joined
@@ -395,6 +397,31 @@ typedef struct hj_aggregate {
  * reference (it keeps a NaN only when it comes first). */
 int hj_aggregate_column(hj_ctx* ctx, const void* device_values, const uint8_t* device_nulls, uint64_t n_rows,
                         int key_type, void* cuda_stream, hj_aggregate* out);
+
+/* GROUP BY one integer column (Aggregate with one group-by column, aggregate.cpp:254-420): per distinct value of the
+ * group column — NULL being a group of its own — the aggregates of hj_aggregate over the rows of that group.
+ * device_group_keys / device_group_nulls: the group column of the n_rows input rows in device memory (int32 / int64;
+ * typically hj_gather_column output in one slot), device_values / device_value_nulls / value_type: the aggregate
+ * column in the same row order (another slot), or device_values == NULL for COUNT(*) alone. max_groups: an upper
+ * bound of the number of groups if the caller has one (dictionary size, statistics), 0 = n_rows; the hash table takes
+ * 56 bytes x 2 x that. HJ_ERR_CAPACITY if there are more groups than promised. The groups stay on the device until
+ * hj_aggregate_grouped_fetch copies them out (any order: the reference guarantees none, aggregate.hpp:45-47).
+ * Double sums are accumulated with atomics: they agree with the reference up to rounding and are not bit-reproducible
+ * from run to run. Several group-by columns: not built. */
+typedef struct hj_group {
+  int64_t key;         /* value of the group column (0 for the NULL group) */
+  int32_t key_is_null;
+  int32_t reserved;
+  hj_aggregate agg;    /* agg.n_rows = COUNT(*) of the group */
+} hj_group;
+typedef struct hj_group_info {
+  uint64_t n_groups;
+  uint64_t n_rows;
+} hj_group_info;
+int hj_aggregate_grouped(hj_ctx* ctx, const void* device_group_keys, const uint8_t* device_group_nulls, int group_key_type,
+                         const void* device_values, const uint8_t* device_value_nulls, int value_type, uint64_t n_rows,
+                         uint64_t max_groups, void* cuda_stream, hj_group_info* out_info);
+int hj_aggregate_grouped_fetch(hj_ctx* ctx, hj_group* groups, uint64_t capacity);
 
 /* The same aggregates over a column given as chunk descriptors — the input format of hj_join and hj_scan: VALUE /
  * DICT / FOR / RLE chunks of a data table or REFERENCE chunks of a reference table (e.g. a join's or scan's output

@@ -16,7 +16,7 @@ export HJ_RUN_UNVALIDATED=1
 # 1. the gated device paths: scan -> join on the device, FOR/RLE scans, float / double scans, value-id (string) scans,
 #    hj_gather_column
 step scan_gated 150 python -m pytest tests/test_gpu_scan.py -m gpu -q -x -k "without_leaving or for_and_rle or float or string or value_id or gather or integer_column"
-step aggregate_gated 90 python -m pytest tests/test_gpu_aggregate.py -m gpu -q -x
+step aggregate_gated 150 python -m pytest tests/test_gpu_aggregate.py -m gpu -q
 # 2. the C++ operators: TableScan -> hj_scan in front of JoinHash, float + string scans
 step shim_gated 90 python -m pytest tests/test_shim.py -m gpu -q
 # 3. C1 on the reference's own dbgen keys (SF1), through the C ABI against the oracle

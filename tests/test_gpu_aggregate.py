@@ -240,3 +240,101 @@ def test_scan_join_translate_gather_aggregate_stays_on_the_device(ctx):
     _, gp = ctx.fetch()
     rows = np.sort(gp[:, 0].astype(np.int64) * chunk + gp[:, 1])
     assert np.array_equal(rows, np.flatnonzero(hit))
+
+
+# ---- GROUP BY one integer column: hj_aggregate_grouped --------------------------------------------------------------------
+def grouped_on_gpu(ctx, gk, gz, v, vz, max_groups=0):
+    import torch
+    n = len(gk)
+    tg, tgz = torch.from_numpy(gk).cuda(), torch.from_numpy(gz).cuda()
+    tv = None if v is None else torch.from_numpy(v).cuda()
+    tvz = None if v is None else torch.from_numpy(vz).cuda()
+    return ctx.aggregate_grouped(tg.data_ptr() if n else None, tgz.data_ptr() if n and gz.any() else None, KEY_TYPES[gk.dtype.name],
+                                 None if (v is None or n == 0) else tv.data_ptr(), None if (v is None or n == 0 or not vz.any()) else tvz.data_ptr(),
+                                 abi.KEY_INT32 if v is None else KEY_TYPES[v.dtype.name], n, max_groups)
+
+
+def grouped_want(gk, gz, v, vz):
+    """{group key or None: aggregates} with ONE oracle call per group (aggregate_grouped, which the CPU tests pin on the
+    reference's tables, makes one call per aggregate: too slow for 100 000 groups)."""
+    members = {}
+    for i, (k, z) in enumerate(zip(gk.tolist(), gz.tolist())):
+        members.setdefault(None if z else k, []).append(i)
+    want = {}
+    for key, idx in members.items():
+        idx = np.array(idx, dtype=np.int64)
+        want[key] = {"count_rows": len(idx)} if v is None else ao.aggregate_column(v[idx], vz[idx])
+    return want
+
+
+def groups_close(got, want):
+    assert set(got) == set(want), (sorted(map(str, got))[:10], sorted(map(str, want))[:10])
+    for key, w in want.items():
+        g = got[key]
+        for k, x in w.items():
+            if x is None or isinstance(x, int):
+                assert g[k] == x, (key, k, g[k], x)
+            else:
+                assert g[k] == pytest.approx(x, rel=1e-9, abs=1e-9), (key, k, g[k], x)
+
+
+ONE_COLUMN_CASES = [c for c in FIX["grouped_cases"] if len(c["group_by"]) == 1 and len({a[1] for a in c["aggregates"] if a[1]}) <= 2]
+
+
+@pytest.mark.parametrize("case", ONE_COLUMN_CASES, ids=[c["name"] for c in ONE_COLUMN_CASES])
+def test_reference_group_by_case_on_gpu(ctx, case):
+    """The reference's one-group-column cases: every aggregate column of the case is one hj_aggregate_grouped call; the
+    expected table's rows are found by group key."""
+    table = FIX["grouped_tables"][case["table"]]
+    gk, gz = am.column_of(table, case["group_by"][0])
+    expected = {row[0]: row[1:] for row in case["expected_rows"]}
+    if not case["aggregates"]:
+        got = grouped_on_gpu(ctx, gk, gz, None, None)
+        assert set(got) == set(expected)
+        return
+    for j, (fn, name) in enumerate(case["aggregates"]):
+        if name is None:
+            got = grouped_on_gpu(ctx, gk, gz, None, None)
+            for key, row in expected.items():
+                assert got[key]["count_rows"] == row[j], (key, got[key], row)
+            continue
+        v, vz = am.column_of(table, name)
+        got = grouped_on_gpu(ctx, gk, gz, v, vz)
+        assert set(got) == set(expected)
+        for key, row in expected.items():
+            assert am.matches_reference(got[key][fn], row[j]), (key, fn, got[key], row, case["cite"])
+
+
+@pytest.mark.parametrize("gdtype", [np.int32, np.int64])
+@pytest.mark.parametrize("vdtype", [None, np.int32, np.int64, np.float32, np.float64])
+@pytest.mark.parametrize("n_groups", [1, 7, 200, 5000, 100_000])
+def test_random_group_by_matches_oracle(ctx, gdtype, vdtype, n_groups):
+    """From one group (every row updates the same shared-memory slot) over more groups than the CTA tables hold (the global
+    table is hit directly) to nearly one group per row; NULL group keys, NULL values, the key that is the table's EMPTY
+    marker, max_groups hints that are exact, generous and absent."""
+    rng = np.random.default_rng(n_groups)
+    n = 150_000
+    gk = rng.integers(-n_groups // 2, n_groups - n_groups // 2, n).astype(gdtype)
+    if gdtype == np.int64:
+        gk[rng.integers(0, n, 5)] = np.iinfo(np.int64).min   # = the EMPTY marker of the table
+        gk[rng.integers(0, n, 5)] = np.iinfo(np.int64).max
+    gz = (rng.random(n) < 0.05).astype(np.uint8)
+    if vdtype is None:
+        v = vz = None
+    else:
+        v = (rng.integers(-1000, 1000, n) / (4 if np.dtype(vdtype).kind == "f" else 1)).astype(vdtype)
+        vz = (rng.random(n) < 0.1).astype(np.uint8)
+    want = grouped_want(gk, gz, v, vz)
+    for hint in (0, len(want), 4 * len(want)):
+        got = grouped_on_gpu(ctx, gk, gz, v, vz, hint)
+        if v is None:
+            assert {k: g["count_rows"] for k, g in got.items()} == {k: w["count_rows"] for k, w in want.items()}
+        else:
+            groups_close(got, want)
+
+
+def test_group_table_overflow_is_an_error_not_a_hang(ctx):
+    gk = np.arange(100_000, dtype=np.int32)
+    with pytest.raises(hj.HjError) as e:
+        grouped_on_gpu(ctx, gk, np.zeros(len(gk), np.uint8), None, None, max_groups=100)   # 100 000 groups into 1024 slots
+    assert e.value.status == abi.ERR_CAPACITY
