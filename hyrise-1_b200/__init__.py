@@ -326,6 +326,17 @@ class HashJoin:
         info = abi.GroupInfo()
         self._check(self._l.hj_aggregate_grouped(self._ctx, group_keys, group_nulls, group_key_type, values, value_nulls, value_type,
                                                  n_rows, max_groups, stream, C.byref(info)))
+        return self._fetch_groups(info)
+
+    def aggregate_grouped_relation(self, group_column, value_column=None, max_groups=0, stream=None):
+        """hj_aggregate_grouped_relation + fetch: both columns as chunk descriptors of one table (value_column None: COUNT(*))."""
+        info = abi.GroupInfo()
+        self._check(self._l.hj_aggregate_grouped_relation(self._ctx, C.byref(group_column),
+                                                          None if value_column is None else C.byref(value_column), max_groups, stream,
+                                                          C.byref(info)))
+        return self._fetch_groups(info)
+
+    def _fetch_groups(self, info):
         groups = (abi.Group * max(info.n_groups, 1))()
         self._check(self._l.hj_aggregate_grouped_fetch(self._ctx, groups, info.n_groups))
         out = {}

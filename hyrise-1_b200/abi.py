@@ -118,6 +118,8 @@ SYMBOLS = {
     "hj_aggregate_column": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p, C.POINTER(Aggregate)]),
     "hj_aggregate_grouped": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_uint64,
                                        C.c_uint64, C.c_void_p, C.POINTER(GroupInfo)]),
+    "hj_aggregate_grouped_relation": (C.c_int, [C.c_void_p, C.POINTER(Relation), C.POINTER(Relation), C.c_uint64, C.c_void_p,
+                                                C.POINTER(GroupInfo)]),
     "hj_aggregate_grouped_fetch": (C.c_int, [C.c_void_p, C.POINTER(Group), C.c_uint64]),
     "hj_aggregate_relation": (C.c_int, [C.c_void_p, C.POINTER(Relation), C.c_void_p, C.POINTER(Aggregate)]),
     "hj_scan_result_device": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),

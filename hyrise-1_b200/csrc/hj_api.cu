@@ -458,7 +458,8 @@ struct RefRewrite {
 
 // hash_type (hj_key_type): the type the join hashes in. For float/double joins (N3) EVERY chunk goes through the kernel,
 // which converts the keys to the hashed type and hands the pipeline their bit patterns as int32 / int64 keys.
-int gather_references(hj_ctx* ctx, const hj_relation* in, int side, cudaStream_t st, RefRewrite* out, uint32_t hash_type) {
+int gather_references(hj_ctx* ctx, const hj_relation* in, int side, cudaStream_t st, RefRewrite* out, uint32_t hash_type,
+                      bool every_chunk = false) {
   out->rel = *in;
   out->any = false;
   const bool floating = hash_type >= HJ_KEY_FLOAT;
@@ -466,7 +467,7 @@ int gather_references(hj_ctx* ctx, const hj_relation* in, int side, cudaStream_t
   for (uint32_t i = 0; i < in->n_segs; ++i) {
     const uint8_t kind = in->segs[i].kind;
     const bool bp128 = (kind == HJ_SEG_DICT || kind == HJ_SEG_FOR) && in->segs[i].attr_width == 0;  // decoded here, too
-    if (floating || bp128 || kind == HJ_SEG_REFERENCE || kind == HJ_SEG_FOR || kind == HJ_SEG_RLE) job_segs.push_back(i);
+    if (every_chunk || floating || bp128 || kind == HJ_SEG_REFERENCE || kind == HJ_SEG_FOR || kind == HJ_SEG_RLE) job_segs.push_back(i);
   }
   if (job_segs.empty()) return HJ_OK;
   out->any = true;
@@ -1338,6 +1339,82 @@ int run_scan(hj_ctx* ctx, const hj_relation* column, const hj_relation* original
 }
 
 
+// hj_aggregate_grouped*: the hash table (power of two >= 2 x the expected number of groups), one accumulate launch per
+// pair of device arrays, then count + emit
+int group_begin(hj_ctx* ctx, uint64_t n_rows, uint64_t max_groups, cudaStream_t st, GroupTable* out) {
+  const uint64_t want = std::max<uint64_t>(1024, 2 * (max_groups ? std::min(max_groups, n_rows) : n_rows));
+  uint64_t cap = 1024;
+  while (cap < want) cap <<= 1;
+  if (cap > (uint64_t(1) << 31)) return fail(ctx, HJ_ERR_TOO_LARGE, "group table of %llu slots: pass max_groups", (unsigned long long)cap);
+  const size_t entries = size_t(cap) + 2;
+  HJ_TRY(ensure(ctx, ctx->group_table, entries * 8 * 7));
+  HJ_TRY(ensure(ctx, ctx->group_misc, 16));
+  char* base = static_cast<char*>(ctx->group_table.p);
+  GroupTable& t = *out;
+  t.key = reinterpret_cast<long long*>(base);
+  t.rows = reinterpret_cast<unsigned long long*>(base + entries * 8);
+  t.values = reinterpret_cast<unsigned long long*>(base + entries * 16);
+  t.sum_i = reinterpret_cast<long long*>(base + entries * 24);
+  t.sum_d = reinterpret_cast<double*>(base + entries * 32);
+  t.mn = reinterpret_cast<long long*>(base + entries * 40);
+  t.mx = reinterpret_cast<long long*>(base + entries * 48);
+  t.cap = cap;
+  HJ_CUDA(ctx, cudaMemsetAsync(ctx->group_misc.p, 0, 16, st));
+  const uint32_t grid = static_cast<uint32_t>(std::min<uint64_t>((entries + 255) / 256, uint64_t(ctx->n_sms) * 8));
+  k_group_init<<<grid, 256, 0, st>>>(t);
+  HJ_LAUNCH_CHECK(ctx, "k_group_init");
+  return HJ_OK;
+}
+
+int group_accumulate(hj_ctx* ctx, const GroupTable& t, const void* group_keys, const uint8_t* group_nulls, int group_key_type,
+                     const void* values, const uint8_t* value_nulls, int value_type, uint64_t n_rows, cudaStream_t st) {
+  auto* overflow = reinterpret_cast<uint32_t*>(static_cast<char*>(ctx->group_misc.p) + 8);
+  const uint32_t grid = static_cast<uint32_t>(std::max<uint64_t>(1, std::min<uint64_t>((n_rows + kAggThreads - 1) / kAggThreads,
+                                                                                      uint64_t(ctx->n_sms) * 4)));
+#define HJ_GROUP_LAUNCH(GK, T)                                                                                                    \
+  k_group_accumulate<GK, T><<<grid, kAggThreads, 0, st>>>(static_cast<const GK*>(group_keys), group_nulls, static_cast<const T*>(values), \
+                                                          value_nulls, n_rows, t, overflow)
+  const bool g64 = group_key_type == HJ_KEY_INT64;
+  switch (value_type) {
+    case HJ_KEY_INT32: if (g64) HJ_GROUP_LAUNCH(int64_t, int32_t); else HJ_GROUP_LAUNCH(int32_t, int32_t); break;
+    case HJ_KEY_INT64: if (g64) HJ_GROUP_LAUNCH(int64_t, int64_t); else HJ_GROUP_LAUNCH(int32_t, int64_t); break;
+    case HJ_KEY_FLOAT: if (g64) HJ_GROUP_LAUNCH(int64_t, float); else HJ_GROUP_LAUNCH(int32_t, float); break;
+    default: if (g64) HJ_GROUP_LAUNCH(int64_t, double); else HJ_GROUP_LAUNCH(int32_t, double);
+  }
+#undef HJ_GROUP_LAUNCH
+  HJ_LAUNCH_CHECK(ctx, "k_group_accumulate");
+  return HJ_OK;
+}
+
+int group_finish(hj_ctx* ctx, const GroupTable& t, uint64_t n_rows, uint64_t max_groups, bool floating, cudaStream_t st,
+                 hj_group_info* out_info) {
+  auto* n_groups = static_cast<unsigned long long*>(ctx->group_misc.p);
+  const uint32_t grid = static_cast<uint32_t>(std::min<uint64_t>((t.cap + 2 + 255) / 256, uint64_t(ctx->n_sms) * 8));
+  k_group_emit<<<grid, 256, 0, st>>>(t, nullptr, n_groups);  // count
+  HJ_LAUNCH_CHECK(ctx, "k_group_emit");
+  auto* host = reinterpret_cast<unsigned long long*>(static_cast<char*>(ctx->pinned) + kPinnedAggregate);
+  HJ_CUDA(ctx, cudaMemcpyAsync(host, ctx->group_misc.p, 16, cudaMemcpyDeviceToHost, st));
+  HJ_CUDA(ctx, cudaStreamSynchronize(st));
+  if (reinterpret_cast<const uint32_t*>(host)[2])
+    return fail(ctx, HJ_ERR_CAPACITY, "more than %llu groups: the group table is full (max_groups was %llu)", (unsigned long long)t.cap,
+                (unsigned long long)max_groups);
+  const uint64_t n = host[0];
+  HJ_TRY(ensure(ctx, ctx->group_out, std::max<uint64_t>(1, n) * sizeof(GroupRecord)));
+  HJ_CUDA(ctx, cudaMemsetAsync(n_groups, 0, 8, st));
+  if (n) {
+    k_group_emit<<<grid, 256, 0, st>>>(t, static_cast<GroupRecord*>(ctx->group_out.p), n_groups);
+    HJ_LAUNCH_CHECK(ctx, "k_group_emit");
+  }
+  HJ_CUDA(ctx, cudaStreamSynchronize(st));
+  ctx->group_n = n;
+  ctx->group_rows = n_rows;
+  ctx->group_floating = floating;
+  ctx->group_valid = true;
+  out_info->n_groups = n;
+  out_info->n_rows = n_rows;
+  return HJ_OK;
+}
+
 // A2 + read-back shared by hj_aggregate_column and hj_aggregate_relation: partials[1 .. grid] -> partials[0] -> *out
 int finish_aggregate(hj_ctx* ctx, AggPartial* partials, uint32_t grid, uint64_t n_rows, int key_type, cudaStream_t st, hj_aggregate* out) {
   k_aggregate_final<<<1, 32, 0, st>>>(partials + 1, grid, partials);
@@ -1676,68 +1753,61 @@ int hj_aggregate_grouped(hj_ctx* ctx, const void* device_group_keys, const uint8
   if (device_values && (value_type < HJ_KEY_INT32 || value_type > HJ_KEY_DOUBLE)) return fail(ctx, HJ_ERR_INVALID, "value type %d", value_type);
   if (n_rows && !device_group_keys) return fail(ctx, HJ_ERR_INVALID, "device_group_keys is NULL");
   if (!device_values) value_type = HJ_KEY_INT32;  // COUNT(*) only
-  // table size: a power of two >= 2 x the number of groups the caller expects (0: every row its own group)
-  const uint64_t want = std::max<uint64_t>(1024, 2 * (max_groups ? std::min(max_groups, n_rows) : n_rows));
-  uint64_t cap = 1024;
-  while (cap < want) cap <<= 1;
-  if (cap > (uint64_t(1) << 31)) return fail(ctx, HJ_ERR_TOO_LARGE, "group table of %llu slots: pass max_groups", (unsigned long long)cap);
   HJ_TRY(check_ctx(ctx));
   cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
-  const size_t entries = size_t(cap) + 2;
-  HJ_TRY(ensure(ctx, ctx->group_table, entries * 8 * 7));
-  HJ_TRY(ensure(ctx, ctx->group_misc, 16));
-  char* base = static_cast<char*>(ctx->group_table.p);
   GroupTable t;
-  t.key = reinterpret_cast<long long*>(base);
-  t.rows = reinterpret_cast<unsigned long long*>(base + entries * 8);
-  t.values = reinterpret_cast<unsigned long long*>(base + entries * 16);
-  t.sum_i = reinterpret_cast<long long*>(base + entries * 24);
-  t.sum_d = reinterpret_cast<double*>(base + entries * 32);
-  t.mn = reinterpret_cast<long long*>(base + entries * 40);
-  t.mx = reinterpret_cast<long long*>(base + entries * 48);
-  t.cap = cap;
-  auto* n_groups = static_cast<unsigned long long*>(ctx->group_misc.p);
-  auto* overflow = reinterpret_cast<uint32_t*>(static_cast<char*>(ctx->group_misc.p) + 8);
-  HJ_CUDA(ctx, cudaMemsetAsync(ctx->group_misc.p, 0, 16, st));
-  const uint32_t init_grid = static_cast<uint32_t>(std::min<uint64_t>((entries + 255) / 256, uint64_t(ctx->n_sms) * 8));
-  k_group_init<<<init_grid, 256, 0, st>>>(t);
-  HJ_LAUNCH_CHECK(ctx, "k_group_init");
-  const uint32_t grid = static_cast<uint32_t>(std::max<uint64_t>(1, std::min<uint64_t>((n_rows + kAggThreads - 1) / kAggThreads,
-                                                                                      uint64_t(ctx->n_sms) * 4)));
-#define HJ_GROUP_LAUNCH(GK, T)                                                                                                   \
-  k_group_accumulate<GK, T><<<grid, kAggThreads, 0, st>>>(static_cast<const GK*>(device_group_keys), device_group_nulls,          \
-                                                          static_cast<const T*>(device_values), device_value_nulls, n_rows, t, overflow)
-  const bool g64 = group_key_type == HJ_KEY_INT64;
-  switch (value_type) {
-    case HJ_KEY_INT32: if (g64) HJ_GROUP_LAUNCH(int64_t, int32_t); else HJ_GROUP_LAUNCH(int32_t, int32_t); break;
-    case HJ_KEY_INT64: if (g64) HJ_GROUP_LAUNCH(int64_t, int64_t); else HJ_GROUP_LAUNCH(int32_t, int64_t); break;
-    case HJ_KEY_FLOAT: if (g64) HJ_GROUP_LAUNCH(int64_t, float); else HJ_GROUP_LAUNCH(int32_t, float); break;
-    default: if (g64) HJ_GROUP_LAUNCH(int64_t, double); else HJ_GROUP_LAUNCH(int32_t, double);
+  HJ_TRY(group_begin(ctx, n_rows, max_groups, st, &t));
+  HJ_TRY(group_accumulate(ctx, t, device_group_keys, device_group_nulls, group_key_type, device_values, device_value_nulls, value_type,
+                          n_rows, st));
+  return group_finish(ctx, t, n_rows, max_groups, device_values && value_type >= HJ_KEY_FLOAT, st, out_info);
+}
+
+int hj_aggregate_grouped_relation(hj_ctx* ctx, const hj_relation* group_column, const hj_relation* value_column, uint64_t max_groups,
+                                  void* cuda_stream, hj_group_info* out_info) {
+  if (!ctx) return HJ_ERR_INVALID;
+  if (!out_info) return fail(ctx, HJ_ERR_INVALID, "out_info is NULL");
+  std::memset(out_info, 0, sizeof(*out_info));
+  ctx->group_valid = false;
+  HJ_TRY(validate_relation(ctx, group_column, "group-by"));
+  if (value_column) {
+    HJ_TRY(validate_relation(ctx, value_column, "aggregate"));
+    if (value_column->n_segs != group_column->n_segs) return fail(ctx, HJ_ERR_INVALID, "group-by and aggregate column: different chunk counts");
+    for (uint32_t i = 0; i < group_column->n_segs; ++i)
+      if (value_column->segs[i].n_rows != group_column->segs[i].n_rows)
+        return fail(ctx, HJ_ERR_INVALID, "group-by and aggregate column: chunk %u has %u vs %u rows", i, group_column->segs[i].n_rows,
+                    value_column->segs[i].n_rows);
   }
-#undef HJ_GROUP_LAUNCH
-  HJ_LAUNCH_CHECK(ctx, "k_group_accumulate");
-  k_group_emit<<<init_grid, 256, 0, st>>>(t, nullptr, n_groups);  // count
-  HJ_LAUNCH_CHECK(ctx, "k_group_emit");
-  auto* host = reinterpret_cast<unsigned long long*>(static_cast<char*>(ctx->pinned) + kPinnedAggregate);
-  HJ_CUDA(ctx, cudaMemcpyAsync(host, ctx->group_misc.p, 16, cudaMemcpyDeviceToHost, st));
-  HJ_CUDA(ctx, cudaStreamSynchronize(st));
-  if (reinterpret_cast<const uint32_t*>(host)[2])
-    return fail(ctx, HJ_ERR_CAPACITY, "more than %llu groups: the group table is full (max_groups was %llu)", (unsigned long long)cap,
-                (unsigned long long)max_groups);
-  const uint64_t n = host[0];
-  HJ_TRY(ensure(ctx, ctx->group_out, std::max<uint64_t>(1, n) * sizeof(GroupRecord)));
-  HJ_CUDA(ctx, cudaMemsetAsync(n_groups, 0, 8, st));
-  if (n) {
-    k_group_emit<<<init_grid, 256, 0, st>>>(t, static_cast<GroupRecord*>(ctx->group_out.p), n_groups);
-    HJ_LAUNCH_CHECK(ctx, "k_group_emit");
+  auto type_of = [](const hj_relation* r) {
+    uint32_t t = HJ_KEY_INT32;
+    for (uint32_t i = 0; i < r->n_segs; ++i) t = std::max<uint32_t>(t, r->segs[i].key_type);  // INT32 < INT64 < FLOAT < DOUBLE
+    return t;
+  };
+  const uint32_t gtype = type_of(group_column), vtype = value_column ? type_of(value_column) : uint32_t(HJ_KEY_INT32);
+  if (gtype != HJ_KEY_INT32 && gtype != HJ_KEY_INT64) return fail(ctx, HJ_ERR_INVALID, "group-by column of key type %u: int32 / int64 only", gtype);
+  for (const hj_relation* r : {group_column, value_column})
+    for (uint32_t i = 0; r && i < r->n_segs; ++i)
+      if (r->segs[i].key_type != (r == group_column ? gtype : vtype)) return fail(ctx, HJ_ERR_INVALID, "chunk %u: a column has one type", i);
+  HJ_TRY(check_ctx(ctx));
+  cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
+  // both columns as plain device arrays, chunk by chunk (K10 over every chunk; uses the buffers of gather slots 0 and 1)
+  auto* flags = reinterpret_cast<uint32_t*>(static_cast<char*>(ctx->pinned) + kPinnedRefFlags);
+  flags[2] = flags[3] = 0;
+  RefRewrite rg, rv;
+  HJ_TRY(gather_references(ctx, group_column, 2, st, &rg, gtype, true));
+  if (value_column) HJ_TRY(gather_references(ctx, value_column, 3, st, &rv, vtype, true));
+  GroupTable t;
+  HJ_TRY(group_begin(ctx, group_column->n_rows, max_groups, st, &t));
+  for (uint32_t i = 0; i < group_column->n_segs; ++i) {
+    const hj_segment& g = rg.segs[i];
+    if (!g.n_rows) continue;
+    HJ_TRY(group_accumulate(ctx, t, g.values, g.nulls, static_cast<int>(gtype), value_column ? rv.segs[i].values : nullptr,
+                            value_column ? rv.segs[i].nulls : nullptr, static_cast<int>(vtype), g.n_rows, st));
   }
-  HJ_CUDA(ctx, cudaStreamSynchronize(st));
-  ctx->group_n = n;
-  ctx->group_rows = n_rows;
-  ctx->group_floating = device_values && value_type >= HJ_KEY_FLOAT;
-  ctx->group_valid = true;
-  out_info->n_groups = n;
-  out_info->n_rows = n_rows;
+  HJ_TRY(group_finish(ctx, t, group_column->n_rows, max_groups, value_column && vtype >= HJ_KEY_FLOAT, st, out_info));
+  if (flags[2] || flags[3]) {
+    ctx->group_valid = false;
+    return fail(ctx, HJ_ERR_INVALID, "grouped aggregate: a PosList entry points outside the referenced table");
+  }
   return HJ_OK;
 }
 

@@ -422,6 +422,11 @@ int hj_aggregate_grouped(hj_ctx* ctx, const void* device_group_keys, const uint8
                          const void* device_values, const uint8_t* device_value_nulls, int value_type, uint64_t n_rows,
                          uint64_t max_groups, void* cuda_stream, hj_group_info* out_info);
 int hj_aggregate_grouped_fetch(hj_ctx* ctx, hj_group* groups, uint64_t capacity);
+/* The same with both columns given as chunk descriptors of ONE table (same chunks, same rows per chunk; data or
+ * reference table, host or device resident) — the call the host-side Aggregate operator makes per aggregate column.
+ * value_column == NULL: COUNT(*) per group. Uses the buffers of gather slots 0 and 1. */
+int hj_aggregate_grouped_relation(hj_ctx* ctx, const hj_relation* group_column, const hj_relation* value_column,
+                                  uint64_t max_groups, void* cuda_stream, hj_group_info* out_info);
 
 /* The same aggregates over a column given as chunk descriptors — the input format of hj_join and hj_scan: VALUE /
  * DICT / FOR / RLE chunks of a data table or REFERENCE chunks of a reference table (e.g. a join's or scan's output

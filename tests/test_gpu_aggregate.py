@@ -338,3 +338,40 @@ def test_group_table_overflow_is_an_error_not_a_hang(ctx):
     with pytest.raises(hj.HjError) as e:
         grouped_on_gpu(ctx, gk, np.zeros(len(gk), np.uint8), None, None, max_groups=100)   # 100 000 groups into 1024 slots
     assert e.value.status == abi.ERR_CAPACITY
+
+
+@pytest.mark.parametrize("case", ONE_COLUMN_CASES, ids=[c["name"] for c in ONE_COLUMN_CASES])
+@pytest.mark.parametrize("encoding", ["value", "dict"])
+def test_reference_group_by_case_through_chunk_descriptors(ctx, case, encoding):
+    """The same cases with host-resident chunked tables (chunk size 2 like the reference's fixtures), value and dictionary
+    chunks: hj_aggregate_grouped_relation, the call the C++ Aggregate makes."""
+    table = FIX["grouped_tables"][case["table"]]
+    gk, gz = am.column_of(table, case["group_by"][0])
+    group_rel = host_relation(gk, gz, case["chunk_size"], encoding)
+    expected = {row[0]: row[1:] for row in case["expected_rows"]}
+    if not case["aggregates"]:
+        assert set(ctx.aggregate_grouped_relation(group_rel)) == set(expected)
+        return
+    for j, (fn, name) in enumerate(case["aggregates"]):
+        if name is None:
+            got = ctx.aggregate_grouped_relation(group_rel)
+            assert {k: g["count_rows"] for k, g in got.items()} == {k: row[j] for k, row in expected.items()}
+            continue
+        v, vz = am.column_of(table, name)
+        got = ctx.aggregate_grouped_relation(group_rel, host_relation(v, vz, case["chunk_size"], encoding))
+        assert set(got) == set(expected)
+        for key, row in expected.items():
+            assert am.matches_reference(got[key][fn], row[j]), (key, fn, got[key], row, case["cite"])
+
+
+def test_random_grouped_relations_match_oracle(ctx):
+    rng = np.random.default_rng(77)
+    n, chunk = 300_000, 1 << 16
+    gk = rng.integers(0, 3000, n).astype(np.int32)
+    gz = (rng.random(n) < 0.03).astype(np.uint8)
+    v = (rng.integers(-500, 500, n) / 2).astype(np.float64)
+    vz = (rng.random(n) < 0.1).astype(np.uint8)
+    want = grouped_want(gk, gz, v, vz)
+    for encoding in ("value", "dict"):
+        got = ctx.aggregate_grouped_relation(host_relation(gk, gz, chunk, encoding), host_relation(v, vz, chunk, encoding), max_groups=4000)
+        groups_close(got, want)
