@@ -42,6 +42,24 @@ DataType aggregate_data_type(AggregateFunction f, DataType column_type) {
   }
 }
 
+// the value of one aggregate from the library's per-column result, typed like write_aggregate_values (aggregate.cpp:622-712)
+AllTypeVariant aggregate_value(AggregateFunction f, DataType column_type, const hj_aggregate& r) {
+  if (f == AggregateFunction::Count) return static_cast<int64_t>(r.n_values);
+  if (r.n_values == 0) return NULL_VALUE;  // no row contributed: NULL (aggregate.cpp:635-642, 805-811)
+  if (f == AggregateFunction::Avg) return r.sum_double / static_cast<double>(r.n_values);
+  if (f == AggregateFunction::Sum) {
+    if (r.is_floating) return r.sum_double;
+    return static_cast<int64_t>(r.sum_int);
+  }
+  const bool is_min = f == AggregateFunction::Min;
+  switch (column_type) {
+    case DataType::Int: return static_cast<int32_t>(is_min ? r.min_int : r.max_int);
+    case DataType::Long: return static_cast<int64_t>(is_min ? r.min_int : r.max_int);
+    case DataType::Float: return static_cast<float>(is_min ? r.min_double : r.max_double);
+    default: return is_min ? r.min_double : r.max_double;
+  }
+}
+
 }  // namespace
 
 Aggregate::Aggregate(const std::shared_ptr<AbstractOperator>& in, const std::vector<AggregateColumnDefinition>& aggregates,
@@ -69,7 +87,12 @@ const std::string Aggregate::description(DescriptionMode) const {  // aggregate.
 
 bool Aggregate::supported(const Table& table, const std::vector<AggregateColumnDefinition>& aggregates,
                           const std::vector<ColumnID>& groupby_column_ids) {
-  if (!groupby_column_ids.empty() || aggregates.empty()) return false;
+  if (groupby_column_ids.size() > 1) return false;
+  if (groupby_column_ids.empty() && aggregates.empty()) return false;
+  if (groupby_column_ids.size() == 1) {
+    const DataType t = table.column_data_type(groupby_column_ids[0]);
+    if (t != DataType::Int && t != DataType::Long) return false;
+  }
   for (const auto& a : aggregates) {
     if (a.function == AggregateFunction::CountDistinct) return false;
     if (!a.column) {
@@ -85,8 +108,9 @@ std::shared_ptr<const Table> Aggregate::_on_execute() {
   const auto in_table = input_table_left();
   Assert(in_table != nullptr, "Aggregate: input has not been executed");
   if (!supported(*in_table, _aggregates, _groupby_column_ids))
-    Fail("Aggregate on the device covers MIN / MAX / SUM / AVG / COUNT of numeric columns and COUNT(*) without GROUP BY; this "
-         "aggregate is not supported and there is no CPU fallback");
+    Fail("Aggregate on the device covers MIN / MAX / SUM / AVG / COUNT of numeric columns and COUNT(*), without GROUP BY or "
+         "grouped by one int / long column; this aggregate is not supported and there is no CPU fallback");
+  if (!_groupby_column_ids.empty()) return _execute_grouped(*in_table);
 
   hj_ctx* ctx = hjhost::context();
   std::map<ColumnID, hj_aggregate> per_column;  // one pass per distinct aggregate column
@@ -114,30 +138,75 @@ std::shared_ptr<const Table> Aggregate::_on_execute() {
       continue;
     }
     const DataType column_type = in_table->column_data_type(*a.column);
-    const DataType out_type = aggregate_data_type(a.function, column_type);
-    const hj_aggregate& r = per_column.at(*a.column);
-    const bool needs_null = a.function != AggregateFunction::Count;
-    definitions.emplace_back(column_name.str(), out_type, needs_null);
-    if (a.function == AggregateFunction::Count) {
-      row.emplace_back(static_cast<int64_t>(r.n_values));
-    } else if (r.n_values == 0) {
-      row.emplace_back(NULL_VALUE);  // no row contributed: NULL (aggregate.cpp:635-642, 805-811)
-    } else if (a.function == AggregateFunction::Avg) {
-      row.emplace_back(r.sum_double / static_cast<double>(r.n_values));
-    } else if (a.function == AggregateFunction::Sum) {
-      if (r.is_floating) row.emplace_back(r.sum_double); else row.emplace_back(static_cast<int64_t>(r.sum_int));
-    } else {
-      const bool is_min = a.function == AggregateFunction::Min;
-      switch (column_type) {
-        case DataType::Int: row.emplace_back(static_cast<int32_t>(is_min ? r.min_int : r.max_int)); break;
-        case DataType::Long: row.emplace_back(static_cast<int64_t>(is_min ? r.min_int : r.max_int)); break;
-        case DataType::Float: row.emplace_back(static_cast<float>(is_min ? r.min_double : r.max_double)); break;
-        default: row.emplace_back(is_min ? r.min_double : r.max_double);
-      }
-    }
+    definitions.emplace_back(column_name.str(), aggregate_data_type(a.function, column_type), a.function != AggregateFunction::Count);
+    row.emplace_back(aggregate_value(a.function, column_type, per_column.at(*a.column)));
   }
   auto output = std::make_shared<Table>(definitions, TableType::Data);
   output->append(row);
+  return output;
+}
+
+// GROUP BY one int / long column: one hj_aggregate_grouped_relation call per distinct aggregate column (or one for the
+// groups alone); group-by column first, then the aggregates (aggregate.cpp:540-560), one row per group.
+std::shared_ptr<const Table> Aggregate::_execute_grouped(const Table& in_table) {
+  const ColumnID group_id = _groupby_column_ids[0];
+  const DataType group_type = in_table.column_data_type(group_id);
+  TableColumnDefinitions definitions;
+  definitions.emplace_back(in_table.column_name(group_id), group_type, in_table.column_is_nullable(group_id));
+  for (const auto& a : _aggregates) {
+    std::stringstream column_name;
+    column_name << function_name(a.function) << "(" << (a.column ? in_table.column_name(*a.column) : std::string("*")) << ")";
+    if (!a.column) definitions.emplace_back(column_name.str(), DataType::Long, false);
+    else definitions.emplace_back(column_name.str(), aggregate_data_type(a.function, in_table.column_data_type(*a.column)),
+                                  a.function != AggregateFunction::Count);
+  }
+  auto output = std::make_shared<Table>(definitions, TableType::Data);
+  if (in_table.chunk_count() == 0) return output;  // no rows, no groups
+
+  using GroupKey = std::pair<bool, int64_t>;  // (is NULL, value)
+  hj_ctx* ctx = hjhost::context();
+  const hj_relation* group_rel = nullptr;
+  const auto keep_group = hjhost::flatten_column(in_table, group_id, &group_rel);
+  auto run = [&](const hj_relation* value_rel) {
+    hj_group_info info;
+    if (hj_aggregate_grouped_relation(ctx, group_rel, value_rel, 0, nullptr, &info) != HJ_OK) Fail(std::string("Aggregate: ") + hj_last_error(ctx));
+    std::vector<hj_group> groups(std::max<uint64_t>(1, info.n_groups));
+    if (hj_aggregate_grouped_fetch(ctx, groups.data(), groups.size()) != HJ_OK) Fail(std::string("Aggregate: ") + hj_last_error(ctx));
+    groups.resize(info.n_groups);
+    return groups;
+  };
+  std::vector<GroupKey> order;                                   // the groups, in the order of the first call
+  std::map<GroupKey, uint64_t> rows_per_group;                   // COUNT(*)
+  std::map<ColumnID, std::map<GroupKey, hj_aggregate>> per_column;
+  auto remember = [&](const std::vector<hj_group>& groups) {
+    if (!order.empty() || groups.empty()) return;
+    for (const auto& g : groups) {
+      order.emplace_back(g.key_is_null != 0, g.key);
+      rows_per_group[order.back()] = g.agg.n_rows;
+    }
+  };
+  for (const auto& a : _aggregates) {
+    if (!a.column || per_column.count(*a.column)) continue;
+    const hj_relation* value_rel = nullptr;
+    const auto keep_value = hjhost::flatten_column(in_table, *a.column, &value_rel);
+    const auto groups = run(value_rel);
+    remember(groups);
+    auto& m = per_column[*a.column];
+    for (const auto& g : groups) m[GroupKey(g.key_is_null != 0, g.key)] = g.agg;
+  }
+  if (order.empty()) remember(run(nullptr));  // no aggregate column: the groups (and COUNT(*)) alone
+
+  for (const auto& key : order) {
+    std::vector<AllTypeVariant> row;
+    if (key.first) row.emplace_back(NULL_VALUE);
+    else if (group_type == DataType::Int) row.emplace_back(static_cast<int32_t>(key.second));
+    else row.emplace_back(static_cast<int64_t>(key.second));
+    for (const auto& a : _aggregates) {
+      if (!a.column) row.emplace_back(static_cast<int64_t>(rows_per_group.at(key)));
+      else row.emplace_back(aggregate_value(a.function, in_table.column_data_type(*a.column), per_column.at(*a.column).at(key)));
+    }
+    output->append(row);
+  }
   return output;
 }
 

@@ -1,7 +1,8 @@
 // aggregate.hpp — Hyrise's Aggregate operator with the reference's class surface (src/lib/operators/aggregate.hpp:85-99),
-// whose _on_execute() runs aggregates WITHOUT group-by columns over numeric columns on a B200 through
-// hj_aggregate_relation() of include/hj.h (the consumer after the join). GROUP BY, COUNT(DISTINCT) and
-// string columns are refused with a message — there is no CPU fallback in this operator.
+// whose _on_execute() runs aggregates over numeric columns — without group-by columns (hj_aggregate_relation) or grouped
+// by one int / long column (hj_aggregate_grouped_relation) — on a B200 through include/hj.h (the
+// consumer after the join). Several group-by columns, COUNT(DISTINCT) and string columns are refused with a message —
+// there is no CPU fallback in this operator.
 #pragma once
 #include <memory>
 #include <optional>
@@ -39,6 +40,7 @@ class Aggregate : public AbstractReadOnlyOperator {
 
  protected:
   std::shared_ptr<const Table> _on_execute() override;
+  std::shared_ptr<const Table> _execute_grouped(const Table& in_table);
   std::shared_ptr<AbstractOperator> _on_deep_copy(const std::shared_ptr<AbstractOperator>& copied_input_left,
                                                   const std::shared_ptr<AbstractOperator>& copied_input_right) const override;
 

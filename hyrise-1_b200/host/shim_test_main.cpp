@@ -362,20 +362,25 @@ int main(int argc, char** argv) {
           join->execute();
           env[op[1]] = join->get_output();
         } else if (op[0] == "aggregate") {
-          // aggregate <out> <in> <FUNCTION>:<column id | *> ...   (no GROUP BY; opossum::Aggregate -> hj_aggregate_relation)
+          // aggregate <out> <in> [groupby:<column id>] <FUNCTION>:<column id | *> ...   (opossum::Aggregate -> hj_aggregate_*relation)
           const std::map<std::string, AggregateFunction> functions = {
               {"MIN", AggregateFunction::Min}, {"MAX", AggregateFunction::Max}, {"SUM", AggregateFunction::Sum},
               {"AVG", AggregateFunction::Avg}, {"COUNT", AggregateFunction::Count}};
           std::vector<AggregateColumnDefinition> aggregates;
+          std::vector<ColumnID> groupby;
           for (size_t k = 3; k < op.size(); ++k) {
             const auto parts = split(op[k], ':');
+            if (parts.at(0) == "groupby") {  // groupby:<column id>
+              groupby.push_back(static_cast<ColumnID>(std::stoul(parts.at(1))));
+              continue;
+            }
             std::optional<ColumnID> column;
             if (parts.at(1) != "*") column = static_cast<ColumnID>(std::stoul(parts[1]));
             aggregates.emplace_back(column, functions.at(parts[0]));
           }
           auto wrapper = std::make_shared<TableWrapper>(env.at(op[2]));
           wrapper->execute();
-          auto aggregate = std::make_shared<Aggregate>(wrapper, aggregates, std::vector<ColumnID>{});
+          auto aggregate = std::make_shared<Aggregate>(wrapper, aggregates, groupby);
           aggregate->execute();
           env[op[1]] = aggregate->get_output();
         } else if (op[0] == "nlj") {
