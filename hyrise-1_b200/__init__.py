@@ -328,6 +328,17 @@ class HashJoin:
                                                  n_rows, max_groups, stream, C.byref(info)))
         return self._fetch_groups(info)
 
+    def aggregate_grouped_rows(self, group_columns, values, value_nulls, value_type, n_rows, max_groups=0, stream=None):
+        """hj_aggregate_grouped_rows + fetch: group_columns = [(values ptr, nulls ptr or None, key type)]; returns
+        {representative row index: aggregate dict}."""
+        cols = (abi.GroupColumn * len(group_columns))()
+        for c, (v, z, kt) in zip(cols, group_columns):
+            c.values, c.nulls, c.key_type = v, z, kt
+        info = abi.GroupInfo()
+        self._check(self._l.hj_aggregate_grouped_rows(self._ctx, cols, len(group_columns), values, value_nulls, value_type, n_rows,
+                                                      max_groups, stream, C.byref(info)))
+        return self._fetch_groups(info)
+
     def aggregate_grouped_relation(self, group_column, value_column=None, max_groups=0, stream=None):
         """hj_aggregate_grouped_relation + fetch: both columns as chunk descriptors of one table (value_column None: COUNT(*))."""
         info = abi.GroupInfo()

@@ -66,6 +66,10 @@ class Group(C.Structure):
     _fields_ = [("key", C.c_int64), ("key_is_null", C.c_int32), ("reserved", C.c_int32), ("agg", Aggregate)]
 
 
+class GroupColumn(C.Structure):
+    _fields_ = [("values", C.c_void_p), ("nulls", C.c_void_p), ("key_type", C.c_int32), ("reserved", C.c_int32)]
+
+
 class GroupInfo(C.Structure):
     _fields_ = [("n_groups", C.c_uint64), ("n_rows", C.c_uint64)]
 
@@ -118,6 +122,8 @@ SYMBOLS = {
     "hj_aggregate_column": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p, C.POINTER(Aggregate)]),
     "hj_aggregate_grouped": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_uint64,
                                        C.c_uint64, C.c_void_p, C.POINTER(GroupInfo)]),
+    "hj_aggregate_grouped_rows": (C.c_int, [C.c_void_p, C.POINTER(GroupColumn), C.c_uint32, C.c_void_p, C.c_void_p, C.c_int, C.c_uint64,
+                                            C.c_uint64, C.c_void_p, C.POINTER(GroupInfo)]),
     "hj_aggregate_grouped_relation": (C.c_int, [C.c_void_p, C.POINTER(Relation), C.POINTER(Relation), C.c_uint64, C.c_void_p,
                                                 C.POINTER(GroupInfo)]),
     "hj_aggregate_grouped_fetch": (C.c_int, [C.c_void_p, C.POINTER(Group), C.c_uint64]),

@@ -375,4 +375,132 @@ __global__ void k_group_emit(GroupTable t, GroupRecord* __restrict__ out, unsign
   }
 }
 
+// =====================================================================================================================
+// GROUP BY several columns: the tables are keyed by a REPRESENTATIVE ROW (the reference's hash_entry.row_id,
+// aggregate.cpp:222): a slot holds the index of the row that claimed it; another row belongs to the group iff its group-by
+// columns (raw value bits + NULL flags, NULL = NULL) equal that row's. Same accumulators, same two-level scheme, same bounded
+// probing as above; GroupTable::key holds row indices (EMPTY = all ones), the two special slots are unused.
+// =====================================================================================================================
+constexpr int kMaxGroupColumns = 4;
+constexpr unsigned long long kRowEmpty = ~0ull;
+
+struct GroupColumns {
+  const void* values[kMaxGroupColumns];
+  const uint8_t* nulls[kMaxGroupColumns];
+  uint32_t width[kMaxGroupColumns];  // 4 or 8 bytes per value
+  uint32_t n;
+};
+
+// raw value bits of column c at row r (0 for NULL: a NULL's stored value does not take part in the comparison)
+__device__ __forceinline__ unsigned long long group_cell(const GroupColumns& g, uint32_t c, unsigned long long r, bool* is_null) {
+  *is_null = g.nulls[c] && __ldg(g.nulls[c] + r);
+  if (*is_null) return 0;
+  return g.width[c] == 4 ? static_cast<unsigned long long>(__ldg(static_cast<const uint32_t*>(g.values[c]) + r))
+                         : __ldg(static_cast<const unsigned long long*>(g.values[c]) + r);
+}
+
+__device__ __forceinline__ bool group_rows_equal(const GroupColumns& g, unsigned long long a, unsigned long long b) {
+  if (a == b) return true;
+  for (uint32_t c = 0; c < g.n; ++c) {
+    bool na, nb;
+    const unsigned long long va = group_cell(g, c, a, &na), vb = group_cell(g, c, b, &nb);
+    if (na != nb || va != vb) return false;
+  }
+  return true;
+}
+
+__device__ __forceinline__ uint32_t group_row_hash(const GroupColumns& g, unsigned long long r) {
+  uint32_t h = 0x9e3779b9u;
+  for (uint32_t c = 0; c < g.n; ++c) {
+    bool is_null;
+    const unsigned long long v = group_cell(g, c, r, &is_null);
+    h = fmix32(h ^ hash_key(static_cast<int64_t>(v)) ^ (is_null ? 0x85ebca6bu : 0u));
+  }
+  return h;
+}
+
+// slot of row r's group in a table of representative rows (`mask` + 1 slots), claiming a slot if the group is new; at most
+// max_probes slots are tried, ~0 if none was found
+__device__ __forceinline__ unsigned long long group_row_slot(unsigned long long* reps, unsigned long long mask, const GroupColumns& g,
+                                                             unsigned long long r, uint32_t h, unsigned long long max_probes) {
+  unsigned long long s = h & mask;
+  for (unsigned long long p = 0; p < max_probes; ++p) {
+    const unsigned long long prev = atomicCAS(reps + s, kRowEmpty, r);
+    if (prev == kRowEmpty || group_rows_equal(g, prev, r)) return s;
+    s = (s + 1) & mask;
+  }
+  return ~0ull;
+}
+
+__global__ void k_group_init_rows(GroupTable t) {  // like k_group_init with the row-index EMPTY marker
+  const unsigned long long n = t.cap + 2;
+  for (unsigned long long i = blockIdx.x * static_cast<unsigned long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<unsigned long long>(gridDim.x) * blockDim.x) {
+    t.key[i] = static_cast<long long>(kRowEmpty);
+    t.rows[i] = 0;
+    t.values[i] = 0;
+    t.sum_i[i] = 0;
+    t.sum_d[i] = 0.0;
+    t.mn[i] = INT64_MAX;
+    t.mx[i] = INT64_MIN;
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kAggThreads) k_group_accumulate_rows(GroupColumns g, const T* __restrict__ values,
+                                                                       const uint8_t* __restrict__ value_nulls, unsigned long long n,
+                                                                       GroupTable t, uint32_t* __restrict__ overflow) {
+  constexpr int S = kGroupSmemSlots;
+  __shared__ unsigned long long s_rep[S];
+  __shared__ unsigned long long s_rows[S], s_values[S];
+  __shared__ long long s_sum_i[S], s_mn[S], s_mx[S];
+  __shared__ double s_sum_d[S];
+  for (int i = threadIdx.x; i < S; i += kAggThreads) {
+    s_rep[i] = kRowEmpty;
+    s_rows[i] = 0;
+    s_values[i] = 0;
+    s_sum_i[i] = 0;
+    s_sum_d[i] = 0.0;
+    s_mn[i] = INT64_MAX;
+    s_mx[i] = INT64_MIN;
+  }
+  __syncthreads();
+  auto* reps = reinterpret_cast<unsigned long long*>(t.key);
+  const unsigned long long stride = static_cast<unsigned long long>(gridDim.x) * kAggThreads;
+  for (unsigned long long i = static_cast<unsigned long long>(blockIdx.x) * kAggThreads + threadIdx.x; i < n; i += stride) {
+    const bool has_value = values && !(value_nulls && __ldg(value_nulls + i));
+    const T v = has_value ? __ldg(values + i) : T(0);
+    const uint32_t h = group_row_hash(g, i);
+    const unsigned long long s = group_row_slot(s_rep, S - 1, g, i, h, kGroupSmemProbes);
+    if (s != ~0ull) {
+      group_update<T>(s_rows, s_values, s_sum_i, s_sum_d, s_mn, s_mx, s, has_value, v);
+    } else {
+      const unsigned long long gs = group_row_slot(reps, t.cap - 1, g, i, h, t.cap);
+      if (gs == ~0ull) {
+        *overflow = 1;
+        continue;
+      }
+      group_update<T>(t.rows, t.values, t.sum_i, t.sum_d, t.mn, t.mx, gs, has_value, v);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < S; i += kAggThreads) {
+    if (s_rows[i] == 0) continue;
+    const unsigned long long r = s_rep[i];
+    const unsigned long long gs = group_row_slot(reps, t.cap - 1, g, r, group_row_hash(g, r), t.cap);
+    if (gs == ~0ull) {
+      *overflow = 1;
+      continue;
+    }
+    atomicAdd(t.rows + gs, s_rows[i]);
+    if (s_values[i]) {
+      atomicAdd(t.values + gs, s_values[i]);
+      atomicAdd(reinterpret_cast<unsigned long long*>(t.sum_i + gs), static_cast<unsigned long long>(s_sum_i[i]));
+      atomicAdd(t.sum_d + gs, s_sum_d[i]);
+      atomicMin(t.mn + gs, s_mn[i]);
+      atomicMax(t.mx + gs, s_mx[i]);
+    }
+  }
+}
+
 }  // namespace hj

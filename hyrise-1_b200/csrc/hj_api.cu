@@ -1341,7 +1341,7 @@ int run_scan(hj_ctx* ctx, const hj_relation* column, const hj_relation* original
 
 // hj_aggregate_grouped*: the hash table (power of two >= 2 x the expected number of groups), one accumulate launch per
 // pair of device arrays, then count + emit
-int group_begin(hj_ctx* ctx, uint64_t n_rows, uint64_t max_groups, cudaStream_t st, GroupTable* out) {
+int group_begin(hj_ctx* ctx, uint64_t n_rows, uint64_t max_groups, cudaStream_t st, GroupTable* out, bool row_keys = false) {
   const uint64_t want = std::max<uint64_t>(1024, 2 * (max_groups ? std::min(max_groups, n_rows) : n_rows));
   uint64_t cap = 1024;
   while (cap < want) cap <<= 1;
@@ -1361,7 +1361,7 @@ int group_begin(hj_ctx* ctx, uint64_t n_rows, uint64_t max_groups, cudaStream_t 
   t.cap = cap;
   HJ_CUDA(ctx, cudaMemsetAsync(ctx->group_misc.p, 0, 16, st));
   const uint32_t grid = static_cast<uint32_t>(std::min<uint64_t>((entries + 255) / 256, uint64_t(ctx->n_sms) * 8));
-  k_group_init<<<grid, 256, 0, st>>>(t);
+  if (row_keys) k_group_init_rows<<<grid, 256, 0, st>>>(t); else k_group_init<<<grid, 256, 0, st>>>(t);
   HJ_LAUNCH_CHECK(ctx, "k_group_init");
   return HJ_OK;
 }
@@ -1759,6 +1759,51 @@ int hj_aggregate_grouped(hj_ctx* ctx, const void* device_group_keys, const uint8
   HJ_TRY(group_begin(ctx, n_rows, max_groups, st, &t));
   HJ_TRY(group_accumulate(ctx, t, device_group_keys, device_group_nulls, group_key_type, device_values, device_value_nulls, value_type,
                           n_rows, st));
+  return group_finish(ctx, t, n_rows, max_groups, device_values && value_type >= HJ_KEY_FLOAT, st, out_info);
+}
+
+int hj_aggregate_grouped_rows(hj_ctx* ctx, const hj_group_column* group_columns, uint32_t n_group_columns, const void* device_values,
+                              const uint8_t* device_value_nulls, int value_type, uint64_t n_rows, uint64_t max_groups, void* cuda_stream,
+                              hj_group_info* out_info) {
+  if (!ctx) return HJ_ERR_INVALID;
+  if (!out_info) return fail(ctx, HJ_ERR_INVALID, "out_info is NULL");
+  std::memset(out_info, 0, sizeof(*out_info));
+  ctx->group_valid = false;
+  if (!group_columns || n_group_columns == 0 || n_group_columns > uint32_t(kMaxGroupColumns))
+    return fail(ctx, HJ_ERR_INVALID, "%u group-by columns: 1..%d", n_group_columns, kMaxGroupColumns);
+  GroupColumns g{};
+  g.n = n_group_columns;
+  for (uint32_t c = 0; c < n_group_columns; ++c) {
+    const hj_group_column& col = group_columns[c];
+    if (col.key_type < HJ_KEY_INT32 || col.key_type > HJ_KEY_DOUBLE) return fail(ctx, HJ_ERR_INVALID, "group-by column %u: key type %d", c, col.key_type);
+    if (n_rows && !col.values) return fail(ctx, HJ_ERR_INVALID, "group-by column %u: values is NULL", c);
+    g.values[c] = col.values;
+    g.nulls[c] = col.nulls;
+    g.width[c] = (col.key_type == HJ_KEY_INT64 || col.key_type == HJ_KEY_DOUBLE) ? 8u : 4u;
+  }
+  if (device_values && (value_type < HJ_KEY_INT32 || value_type > HJ_KEY_DOUBLE)) return fail(ctx, HJ_ERR_INVALID, "value type %d", value_type);
+  if (!device_values) value_type = HJ_KEY_INT32;
+  HJ_TRY(check_ctx(ctx));
+  cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
+  GroupTable t;
+  HJ_TRY(group_begin(ctx, n_rows, max_groups, st, &t, /*row_keys=*/true));
+  auto* overflow = reinterpret_cast<uint32_t*>(static_cast<char*>(ctx->group_misc.p) + 8);
+  const uint32_t grid = static_cast<uint32_t>(std::max<uint64_t>(1, std::min<uint64_t>((n_rows + kAggThreads - 1) / kAggThreads,
+                                                                                      uint64_t(ctx->n_sms) * 4)));
+  switch (value_type) {
+    case HJ_KEY_INT32:
+      k_group_accumulate_rows<int32_t><<<grid, kAggThreads, 0, st>>>(g, static_cast<const int32_t*>(device_values), device_value_nulls, n_rows, t, overflow);
+      break;
+    case HJ_KEY_INT64:
+      k_group_accumulate_rows<int64_t><<<grid, kAggThreads, 0, st>>>(g, static_cast<const int64_t*>(device_values), device_value_nulls, n_rows, t, overflow);
+      break;
+    case HJ_KEY_FLOAT:
+      k_group_accumulate_rows<float><<<grid, kAggThreads, 0, st>>>(g, static_cast<const float*>(device_values), device_value_nulls, n_rows, t, overflow);
+      break;
+    default:
+      k_group_accumulate_rows<double><<<grid, kAggThreads, 0, st>>>(g, static_cast<const double*>(device_values), device_value_nulls, n_rows, t, overflow);
+  }
+  HJ_LAUNCH_CHECK(ctx, "k_group_accumulate_rows");
   return group_finish(ctx, t, n_rows, max_groups, device_values && value_type >= HJ_KEY_FLOAT, st, out_info);
 }
 

@@ -422,6 +422,20 @@ int hj_aggregate_grouped(hj_ctx* ctx, const void* device_group_keys, const uint8
                          const void* device_values, const uint8_t* device_value_nulls, int value_type, uint64_t n_rows,
                          uint64_t max_groups, void* cuda_stream, hj_group_info* out_info);
 int hj_aggregate_grouped_fetch(hj_ctx* ctx, hj_group* groups, uint64_t capacity);
+/* GROUP BY up to 4 columns of any numeric type: the groups are identified by a REPRESENTATIVE ROW, like the
+ * reference's hash_entry.row_id (aggregate.cpp:222) — two rows are in one group iff all their group-by columns are
+ * equal (raw value bits; NULL equals NULL). hj_group.key of the fetched groups is the index of one row of the group
+ * (key_is_null = 0): the caller reads the group-by values of the output from its own columns at that row, which is
+ * what _write_groupby_output does (:722-735). Everything else as hj_aggregate_grouped. */
+typedef struct hj_group_column {
+  const void* values;   /* device memory, n_rows values of key_type (float / double compared by their bits) */
+  const uint8_t* nulls; /* device memory, one byte per row, or NULL                                         */
+  int32_t key_type;
+  int32_t reserved;
+} hj_group_column;
+int hj_aggregate_grouped_rows(hj_ctx* ctx, const hj_group_column* group_columns, uint32_t n_group_columns,
+                              const void* device_values, const uint8_t* device_value_nulls, int value_type, uint64_t n_rows,
+                              uint64_t max_groups, void* cuda_stream, hj_group_info* out_info);
 /* The same with both columns given as chunk descriptors of ONE table (same chunks, same rows per chunk; data or
  * reference table, host or device resident) — the call the host-side Aggregate operator makes per aggregate column.
  * value_column == NULL: COUNT(*) per group. Uses the buffers of gather slots 0 and 1. */
