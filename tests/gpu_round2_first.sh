@@ -2,7 +2,7 @@
 # First GPU call of the next round (one B200, ~15 min of box time): everything that was written after round 1's GPU minutes
 # ran out, in order of how much depends on it. Each step has its own timeout and log under gpurun_out/; a failing step does
 # not stop the later ones.
-#   gpurun --timeout 1200 -- 'bash tests/gpu_round2_first.sh'
+#   gpurun --timeout 1500 -- 'bash tests/gpu_round2_first.sh'
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
 L=gpurun_out/round2_first.log; : > $L
@@ -16,7 +16,7 @@ export HJ_RUN_UNVALIDATED=1
 # 1. the gated device paths: scan -> join on the device, FOR/RLE scans, float / double scans, value-id (string) scans,
 #    hj_gather_column
 step scan_gated 150 python -m pytest tests/test_gpu_scan.py -m gpu -q -x -k "without_leaving or for_and_rle or float or string or value_id or gather or integer_column"
-step aggregate_gated 420 python -m pytest tests/test_gpu_aggregate.py -m gpu -q
+step aggregate_gated 600 python -m pytest tests/test_gpu_aggregate.py -m gpu -q
 # 2. the C++ operators: TableScan -> hj_scan in front of JoinHash, float + string scans
 step shim_gated 150 python -m pytest tests/test_shim.py -m gpu -q
 # 3. C1 on the reference's own dbgen keys (SF1), through the C ABI against the oracle
