@@ -339,6 +339,15 @@ class HashJoin:
                                                       max_groups, stream, C.byref(info)))
         return self._fetch_groups(info)
 
+    def aggregate_grouped_rows_relation(self, group_columns, value_column=None, max_groups=0, stream=None):
+        """hj_aggregate_grouped_rows_relation + fetch: {representative row number in the table: aggregate dict}."""
+        ptrs = (C.POINTER(abi.Relation) * len(group_columns))(*[C.pointer(r) for r in group_columns])
+        info = abi.GroupInfo()
+        self._check(self._l.hj_aggregate_grouped_rows_relation(self._ctx, ptrs, len(group_columns),
+                                                               None if value_column is None else C.byref(value_column), max_groups,
+                                                               stream, C.byref(info)))
+        return self._fetch_groups(info)
+
     def aggregate_grouped_relation(self, group_column, value_column=None, max_groups=0, stream=None):
         """hj_aggregate_grouped_relation + fetch: both columns as chunk descriptors of one table (value_column None: COUNT(*))."""
         info = abi.GroupInfo()

@@ -124,6 +124,8 @@ SYMBOLS = {
                                        C.c_uint64, C.c_void_p, C.POINTER(GroupInfo)]),
     "hj_aggregate_grouped_rows": (C.c_int, [C.c_void_p, C.POINTER(GroupColumn), C.c_uint32, C.c_void_p, C.c_void_p, C.c_int, C.c_uint64,
                                             C.c_uint64, C.c_void_p, C.POINTER(GroupInfo)]),
+    "hj_aggregate_grouped_rows_relation": (C.c_int, [C.c_void_p, C.POINTER(C.POINTER(Relation)), C.c_uint32, C.POINTER(Relation),
+                                                     C.c_uint64, C.c_void_p, C.POINTER(GroupInfo)]),
     "hj_aggregate_grouped_relation": (C.c_int, [C.c_void_p, C.POINTER(Relation), C.POINTER(Relation), C.c_uint64, C.c_void_p,
                                                 C.POINTER(GroupInfo)]),
     "hj_aggregate_grouped_fetch": (C.c_int, [C.c_void_p, C.POINTER(Group), C.c_uint64]),

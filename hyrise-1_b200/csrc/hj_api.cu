@@ -159,6 +159,7 @@ struct hj_ctx {
   // TableScan (N4): scratch (freed by hj_release_scratch) and the result slots (owned by the scan's caller)
   DevBuf scan_bounds, scan_mask, scan_tile_count, scan_tile_base, scan_ref_ptrs, scan_totals;
   DevBuf agg_partials;  // hj_aggregate_column: one AggPartial per CTA + the folded result
+  DevBuf group_cols[kMaxGroupColumns + 1];  // hj_aggregate_grouped_rows_relation: the columns as contiguous device arrays
   DevBuf group_table, group_out, group_misc;  // hj_aggregate_grouped: hash table (SoA), one GroupRecord per group, count + overflow
   uint64_t group_n = 0, group_rows = 0;
   bool group_valid = false, group_floating = false;
@@ -184,6 +185,7 @@ struct hj_ctx {
       all_bufs.push_back(&ref_arena[i]);
       all_bufs.push_back(&ref_out[i]);
     }
+    for (auto& b : group_cols) all_bufs.push_back(&b);
   }
 };
 
@@ -1805,6 +1807,64 @@ int hj_aggregate_grouped_rows(hj_ctx* ctx, const hj_group_column* group_columns,
   }
   HJ_LAUNCH_CHECK(ctx, "k_group_accumulate_rows");
   return group_finish(ctx, t, n_rows, max_groups, device_values && value_type >= HJ_KEY_FLOAT, st, out_info);
+}
+
+int hj_aggregate_grouped_rows_relation(hj_ctx* ctx, const hj_relation* const* group_columns, uint32_t n_group_columns,
+                                       const hj_relation* value_column, uint64_t max_groups, void* cuda_stream, hj_group_info* out_info) {
+  if (!ctx) return HJ_ERR_INVALID;
+  if (!out_info) return fail(ctx, HJ_ERR_INVALID, "out_info is NULL");
+  std::memset(out_info, 0, sizeof(*out_info));
+  ctx->group_valid = false;
+  if (!group_columns || n_group_columns == 0 || n_group_columns > uint32_t(kMaxGroupColumns))
+    return fail(ctx, HJ_ERR_INVALID, "%u group-by columns: 1..%d", n_group_columns, kMaxGroupColumns);
+  std::vector<const hj_relation*> rels(group_columns, group_columns + n_group_columns);
+  if (value_column) rels.push_back(value_column);
+  for (size_t c = 0; c < rels.size(); ++c) {
+    HJ_TRY(validate_relation(ctx, rels[c], c < n_group_columns ? "group-by" : "aggregate"));
+    if (rels[c]->n_segs != rels[0]->n_segs || rels[c]->n_rows != rels[0]->n_rows)
+      return fail(ctx, HJ_ERR_INVALID, "column %zu: the columns of one table have the same chunks", c);
+    for (uint32_t i = 0; i < rels[0]->n_segs; ++i)
+      if (rels[c]->segs[i].n_rows != rels[0]->segs[i].n_rows) return fail(ctx, HJ_ERR_INVALID, "column %zu: chunk %u has another row count", c, i);
+  }
+  const uint64_t n_rows = rels[0]->n_rows;
+  HJ_TRY(check_ctx(ctx));
+  cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
+  // every column as ONE contiguous device array (values, then NULL bytes): K10 over every chunk into the buffers of gather
+  // slot 0, then chunk by chunk device-to-device into the column's own buffer (representative rows index whole columns)
+  auto* flags = reinterpret_cast<uint32_t*>(static_cast<char*>(ctx->pinned) + kPinnedRefFlags);
+  std::vector<hj_group_column> cols(rels.size());
+  uint32_t bad = 0;
+  for (size_t c = 0; c < rels.size(); ++c) {
+    uint32_t type = HJ_KEY_INT32;
+    for (uint32_t i = 0; i < rels[c]->n_segs; ++i) type = std::max<uint32_t>(type, rels[c]->segs[i].key_type);
+    for (uint32_t i = 0; i < rels[c]->n_segs; ++i)
+      if (rels[c]->segs[i].key_type != type) return fail(ctx, HJ_ERR_INVALID, "column %zu chunk %u: a column has one type", c, i);
+    const size_t width = (type == HJ_KEY_INT64 || type == HJ_KEY_DOUBLE) ? 8 : 4;
+    const size_t nulls_off = (size_t(n_rows) * width + 255) & ~size_t(255);
+    HJ_TRY(ensure(ctx, ctx->group_cols[c], nulls_off + std::max<uint64_t>(1, n_rows)));
+    char* dst = static_cast<char*>(ctx->group_cols[c].p);
+    flags[2] = 0;
+    RefRewrite rw;
+    HJ_TRY(gather_references(ctx, rels[c], 2, st, &rw, type, true));
+    uint64_t row = 0;
+    for (uint32_t i = 0; i < rels[c]->n_segs; ++i) {
+      const hj_segment& sg = rw.segs[i];
+      if (!sg.n_rows) continue;
+      HJ_CUDA(ctx, cudaMemcpyAsync(dst + row * width, sg.values, size_t(sg.n_rows) * width, cudaMemcpyDeviceToDevice, st));
+      HJ_CUDA(ctx, cudaMemcpyAsync(dst + nulls_off + row, sg.nulls, sg.n_rows, cudaMemcpyDeviceToDevice, st));
+      row += sg.n_rows;
+    }
+    HJ_CUDA(ctx, cudaStreamSynchronize(st));  // the gather buffers are reused by the next column; the error flag has arrived
+    bad |= flags[2];
+    cols[c].values = dst;
+    cols[c].nulls = reinterpret_cast<const uint8_t*>(dst + nulls_off);
+    cols[c].key_type = static_cast<int32_t>(type);
+    cols[c].reserved = 0;
+  }
+  if (bad) return fail(ctx, HJ_ERR_INVALID, "grouped aggregate: a PosList entry points outside the referenced table");
+  const hj_group_column* value = value_column ? &cols[n_group_columns] : nullptr;
+  return hj_aggregate_grouped_rows(ctx, cols.data(), n_group_columns, value ? value->values : nullptr, value ? value->nulls : nullptr,
+                                   value ? value->key_type : HJ_KEY_INT32, n_rows, max_groups, cuda_stream, out_info);
 }
 
 int hj_aggregate_grouped_relation(hj_ctx* ctx, const hj_relation* group_column, const hj_relation* value_column, uint64_t max_groups,

@@ -4,6 +4,10 @@
 // so several aggregates on the same column cost one call).
 #include "aggregate.hpp"
 
+#include <algorithm>
+#include <cstdio>
+#include <type_traits>
+#include <variant>
 #include <map>
 #include <sstream>
 
@@ -87,12 +91,10 @@ const std::string Aggregate::description(DescriptionMode) const {  // aggregate.
 
 bool Aggregate::supported(const Table& table, const std::vector<AggregateColumnDefinition>& aggregates,
                           const std::vector<ColumnID>& groupby_column_ids) {
-  if (groupby_column_ids.size() > 1) return false;
+  if (groupby_column_ids.size() > 4) return false;
   if (groupby_column_ids.empty() && aggregates.empty()) return false;
-  if (groupby_column_ids.size() == 1) {
-    const DataType t = table.column_data_type(groupby_column_ids[0]);
-    if (t != DataType::Int && t != DataType::Long) return false;
-  }
+  for (const ColumnID g : groupby_column_ids)
+    if (!numeric(table.column_data_type(g))) return false;
   for (const auto& a : aggregates) {
     if (a.function == AggregateFunction::CountDistinct) return false;
     if (!a.column) {
@@ -109,7 +111,7 @@ std::shared_ptr<const Table> Aggregate::_on_execute() {
   Assert(in_table != nullptr, "Aggregate: input has not been executed");
   if (!supported(*in_table, _aggregates, _groupby_column_ids))
     Fail("Aggregate on the device covers MIN / MAX / SUM / AVG / COUNT of numeric columns and COUNT(*), without GROUP BY or "
-         "grouped by one int / long column; this aggregate is not supported and there is no CPU fallback");
+         "grouped by up to four numeric columns; this aggregate is not supported and there is no CPU fallback");
   if (!_groupby_column_ids.empty()) return _execute_grouped(*in_table);
 
   hj_ctx* ctx = hjhost::context();
@@ -146,13 +148,13 @@ std::shared_ptr<const Table> Aggregate::_on_execute() {
   return output;
 }
 
-// GROUP BY one int / long column: one hj_aggregate_grouped_relation call per distinct aggregate column (or one for the
-// groups alone); group-by column first, then the aggregates (aggregate.cpp:540-560), one row per group.
+// GROUP BY: one hj_aggregate_grouped_rows_relation call per distinct aggregate column (or one for the groups alone). A group
+// comes back as a representative row of the input table; the group-by columns of the output are that row's values
+// (_write_groupby_output, aggregate.cpp:722-735); group-by columns first, then the aggregates (:540-560).
 std::shared_ptr<const Table> Aggregate::_execute_grouped(const Table& in_table) {
-  const ColumnID group_id = _groupby_column_ids[0];
-  const DataType group_type = in_table.column_data_type(group_id);
   TableColumnDefinitions definitions;
-  definitions.emplace_back(in_table.column_name(group_id), group_type, in_table.column_is_nullable(group_id));
+  for (const ColumnID g : _groupby_column_ids)
+    definitions.emplace_back(in_table.column_name(g), in_table.column_data_type(g), in_table.column_is_nullable(g));
   for (const auto& a : _aggregates) {
     std::stringstream column_name;
     column_name << function_name(a.function) << "(" << (a.column ? in_table.column_name(*a.column) : std::string("*")) << ")";
@@ -163,44 +165,75 @@ std::shared_ptr<const Table> Aggregate::_execute_grouped(const Table& in_table) 
   auto output = std::make_shared<Table>(definitions, TableType::Data);
   if (in_table.chunk_count() == 0) return output;  // no rows, no groups
 
-  using GroupKey = std::pair<bool, int64_t>;  // (is NULL, value)
   hj_ctx* ctx = hjhost::context();
-  const hj_relation* group_rel = nullptr;
-  const auto keep_group = hjhost::flatten_column(in_table, group_id, &group_rel);
+  std::vector<std::shared_ptr<void>> keep_alive;
+  std::vector<const hj_relation*> group_rels;
+  for (const ColumnID g : _groupby_column_ids) {
+    const hj_relation* rel = nullptr;
+    keep_alive.push_back(hjhost::flatten_column(in_table, g, &rel));
+    group_rels.push_back(rel);
+  }
   auto run = [&](const hj_relation* value_rel) {
     hj_group_info info;
-    if (hj_aggregate_grouped_relation(ctx, group_rel, value_rel, 0, nullptr, &info) != HJ_OK) Fail(std::string("Aggregate: ") + hj_last_error(ctx));
+    if (hj_aggregate_grouped_rows_relation(ctx, group_rels.data(), static_cast<uint32_t>(group_rels.size()), value_rel, 0, nullptr, &info) != HJ_OK)
+      Fail(std::string("Aggregate: ") + hj_last_error(ctx));
     std::vector<hj_group> groups(std::max<uint64_t>(1, info.n_groups));
     if (hj_aggregate_grouped_fetch(ctx, groups.data(), groups.size()) != HJ_OK) Fail(std::string("Aggregate: ") + hj_last_error(ctx));
     groups.resize(info.n_groups);
     return groups;
   };
-  std::vector<GroupKey> order;                                   // the groups, in the order of the first call
-  std::map<GroupKey, uint64_t> rows_per_group;                   // COUNT(*)
-  std::map<ColumnID, std::map<GroupKey, hj_aggregate>> per_column;
-  auto remember = [&](const std::vector<hj_group>& groups) {
-    if (!order.empty() || groups.empty()) return;
+  // row number in the table -> (chunk, offset)
+  std::vector<uint64_t> chunk_begin(in_table.chunk_count() + 1, 0);
+  for (ChunkID c = 0; c < in_table.chunk_count(); ++c) chunk_begin[c + 1] = chunk_begin[c] + in_table.get_chunk(c)->size();
+  auto group_values = [&](uint64_t row) {
+    const auto it = std::upper_bound(chunk_begin.begin(), chunk_begin.end(), row);
+    const ChunkID c = static_cast<ChunkID>(it - chunk_begin.begin() - 1);
+    const ChunkOffset offset = static_cast<ChunkOffset>(row - chunk_begin[c]);
+    std::vector<AllTypeVariant> values;
+    for (const ColumnID g : _groupby_column_ids) values.push_back((*in_table.get_chunk(c)->get_column(g))[offset]);
+    return values;
+  };
+  // the representative row differs from call to call: groups are matched across calls by their group-by values (as text)
+  auto key_of = [](const std::vector<AllTypeVariant>& values) {
+    std::string k;
+    for (const auto& v : values) {
+      if (variant_is_null(v)) k += "~|";
+      else std::visit([&](const auto& x) {
+        using X = std::decay_t<decltype(x)>;
+        if constexpr (std::is_same_v<X, std::string>) k += x + "|";
+        else if constexpr (std::is_same_v<X, NullValue>) k += "~|";
+        else if constexpr (std::is_floating_point_v<X>) { char buf[40]; std::snprintf(buf, sizeof buf, "%a|", static_cast<double>(x)); k += buf; }
+        else k += std::to_string(x) + "|";
+      }, v);
+    }
+    return k;
+  };
+  std::vector<std::string> order;
+  std::map<std::string, std::vector<AllTypeVariant>> values_of_group;
+  std::map<std::string, uint64_t> rows_per_group;  // COUNT(*)
+  std::map<ColumnID, std::map<std::string, hj_aggregate>> per_column;
+  auto absorb = [&](const std::vector<hj_group>& groups, std::map<std::string, hj_aggregate>* into) {
     for (const auto& g : groups) {
-      order.emplace_back(g.key_is_null != 0, g.key);
-      rows_per_group[order.back()] = g.agg.n_rows;
+      auto values = group_values(static_cast<uint64_t>(g.key));
+      const std::string key = key_of(values);
+      if (!values_of_group.count(key)) {
+        order.push_back(key);
+        values_of_group.emplace(key, std::move(values));
+        rows_per_group[key] = g.agg.n_rows;
+      }
+      if (into) (*into)[key] = g.agg;
     }
   };
   for (const auto& a : _aggregates) {
     if (!a.column || per_column.count(*a.column)) continue;
     const hj_relation* value_rel = nullptr;
     const auto keep_value = hjhost::flatten_column(in_table, *a.column, &value_rel);
-    const auto groups = run(value_rel);
-    remember(groups);
-    auto& m = per_column[*a.column];
-    for (const auto& g : groups) m[GroupKey(g.key_is_null != 0, g.key)] = g.agg;
+    absorb(run(value_rel), &per_column[*a.column]);
   }
-  if (order.empty()) remember(run(nullptr));  // no aggregate column: the groups (and COUNT(*)) alone
+  if (per_column.empty()) absorb(run(nullptr), nullptr);  // no aggregate column: the groups (and COUNT(*)) alone
 
   for (const auto& key : order) {
-    std::vector<AllTypeVariant> row;
-    if (key.first) row.emplace_back(NULL_VALUE);
-    else if (group_type == DataType::Int) row.emplace_back(static_cast<int32_t>(key.second));
-    else row.emplace_back(static_cast<int64_t>(key.second));
+    std::vector<AllTypeVariant> row = values_of_group.at(key);
     for (const auto& a : _aggregates) {
       if (!a.column) row.emplace_back(static_cast<int64_t>(rows_per_group.at(key)));
       else row.emplace_back(aggregate_value(a.function, in_table.column_data_type(*a.column), per_column.at(*a.column).at(key)));

@@ -1,7 +1,7 @@
 // aggregate.hpp — Hyrise's Aggregate operator with the reference's class surface (src/lib/operators/aggregate.hpp:85-99),
 // whose _on_execute() runs aggregates over numeric columns — without group-by columns (hj_aggregate_relation) or grouped
-// by one int / long column (hj_aggregate_grouped_relation) — on a B200 through include/hj.h (the
-// consumer after the join). Several group-by columns, COUNT(DISTINCT) and string columns are refused with a message —
+// by up to four numeric columns (hj_aggregate_grouped_rows_relation) — on a B200 through include/hj.h (SURVEY.md §8f N4:
+// the consumer after the join). COUNT(DISTINCT) and string columns are refused with a message —
 // there is no CPU fallback in this operator.
 #pragma once
 #include <memory>

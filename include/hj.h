@@ -436,6 +436,12 @@ typedef struct hj_group_column {
 int hj_aggregate_grouped_rows(hj_ctx* ctx, const hj_group_column* group_columns, uint32_t n_group_columns,
                               const void* device_values, const uint8_t* device_value_nulls, int value_type, uint64_t n_rows,
                               uint64_t max_groups, void* cuda_stream, hj_group_info* out_info);
+/* ... and with the columns given as chunk descriptors of ONE table (same chunks, same rows per chunk; data or reference
+ * table, host or device resident): the representative row of a group is a row number of the whole table (chunks in
+ * order). value_column == NULL: COUNT(*) per group. Uses the buffers of gather slot 0. */
+int hj_aggregate_grouped_rows_relation(hj_ctx* ctx, const hj_relation* const* group_columns, uint32_t n_group_columns,
+                                       const hj_relation* value_column, uint64_t max_groups, void* cuda_stream,
+                                       hj_group_info* out_info);
 /* The same with both columns given as chunk descriptors of ONE table (same chunks, same rows per chunk; data or
  * reference table, host or device resident) — the call the host-side Aggregate operator makes per aggregate column.
  * value_column == NULL: COUNT(*) per group. Uses the buffers of gather slots 0 and 1. */

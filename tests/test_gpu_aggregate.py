@@ -443,3 +443,32 @@ def test_random_multi_column_group_by_matches_oracle(ctx, n_cols, cardinality):
     want = {key: ao.aggregate_column(v[np.array(idx)], vz[np.array(idx)]) for key, idx in members.items()}
     got = grouped_rows_on_gpu(ctx, group_cols, v, vz)
     groups_close(got, want)
+
+
+@pytest.mark.parametrize("case", FIX["grouped_cases"], ids=[c["name"] for c in FIX["grouped_cases"]])
+@pytest.mark.parametrize("encoding", ["value", "dict"])
+def test_reference_group_by_case_by_representative_rows_through_chunk_descriptors(ctx, case, encoding):
+    """All 39 cases with host-resident chunked tables (chunk size 2): hj_aggregate_grouped_rows_relation, the call the C++
+    Aggregate makes; a group's values are read from the host columns at its representative row number."""
+    table = FIX["grouped_tables"][case["table"]]
+    group_cols = [am.column_of(table, name) for name in case["group_by"]]
+    rels = [host_relation(gv, gz, case["chunk_size"], encoding) for gv, gz in group_cols]
+    k = len(group_cols)
+    expected = {tuple(row[:k]): row[k:] for row in case["expected_rows"]}
+
+    def keyed(got):
+        return {tuple(None if gz[row] else gv[row].item() for gv, gz in group_cols): agg for row, agg in got.items()}
+
+    if not case["aggregates"]:
+        assert set(keyed(ctx.aggregate_grouped_rows_relation(rels))) == set(expected)
+        return
+    for j, (fn, name) in enumerate(case["aggregates"]):
+        if name is None:
+            got = keyed(ctx.aggregate_grouped_rows_relation(rels))
+            assert {key: g["count_rows"] for key, g in got.items()} == {key: row[j] for key, row in expected.items()}
+            continue
+        v, vz = am.column_of(table, name)
+        got = keyed(ctx.aggregate_grouped_rows_relation(rels, host_relation(v, vz, case["chunk_size"], encoding)))
+        assert set(got) == set(expected)
+        for key, row in expected.items():
+            assert am.matches_reference(got[key][fn], row[j]), (key, fn, got[key], row, case["cite"])

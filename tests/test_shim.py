@@ -61,13 +61,13 @@ def test_shim_replays_reference_float_and_string_scan_cases(built):
                     reason="opossum::Aggregate (host/aggregate.cpp) has not run on a GPU yet (set HJ_RUN_UNVALIDATED=1)")
 def test_shim_replays_reference_ungrouped_aggregate_cases(built):
     """aggregate_test.cpp NoGroupbySingleAggregate{Max,Min,Sum,Avg,Count} — on the data table (value and dictionary chunks)
-    and, like the reference's test_output, behind a TableScan — TwoAggregateEmptyTable, and the 20 cases with ONE group-by
-    column (value and dictionary chunks, with and without NULLs, COUNT(*)), through the C++ operators opossum::TableScan ->
-    opossum::Aggregate (hj_scan, hj_aggregate_relation, hj_aggregate_grouped_relation)."""
+    and, like the reference's test_output, behind a TableScan — TwoAggregateEmptyTable, and all 39 numeric group-by cases (1, 2
+    and 3 group-by columns, value and dictionary chunks, with and without NULLs, COUNT(*)), through the C++ operators
+    opossum::TableScan -> opossum::Aggregate (hj_scan, hj_aggregate_relation, hj_aggregate_grouped_rows_relation)."""
     env = dict(os.environ, HJ_SHIM_DEVICE_SCAN="1")
     fixtures = os.path.join(ROOT, "tests", "golden", "aggregate_shim_fixtures.txt")
     r = subprocess.run([EXE, fixtures], capture_output=True, text=True, timeout=600, env=env)
     assert r.returncode == 0, r.stdout[-4000:] + r.stderr[-2000:]
-    assert "56 cases run, 0 failed" in r.stdout, r.stdout[-1000:]
+    assert "94 cases run, 0 failed" in r.stdout, r.stdout[-1000:]
     n = int(r.stdout.rsplit("shim_test: ", 1)[1].split(" scans ran on the device")[0])
     assert n == 6, r.stdout[-500:]
