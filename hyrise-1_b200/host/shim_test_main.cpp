@@ -369,6 +369,7 @@ int main(int argc, char** argv) {
           std::vector<AggregateColumnDefinition> aggregates;
           std::vector<ColumnID> groupby;
           for (size_t k = 3; k < op.size(); ++k) {
+            if (op[k].empty()) continue;  // trailing blank of a line without aggregates
             const auto parts = split(op[k], ':');
             if (parts.at(0) == "groupby") {  // groupby:<column id>
               groupby.push_back(static_cast<ColumnID>(std::stoul(parts.at(1))));

@@ -4,7 +4,7 @@ nothing but the one result row leaves the GPU) — and randomized columns agains
 MIN and MAX are exact; double sums are folded in another order than the reference's row order and must agree to 1e-12
 relative (tolerance of this test; the reference's own table comparison allows 1e-4, testing_assert.cpp:21).
 
-Written after the round's GPU minutes were spent: skipped unless HJ_RUN_UNVALIDATED=1."""
+First run on a B200 in round 2 (profiles/r02_gpu_call1_gated_suites.txt)."""
 import importlib
 import os
 import sys
@@ -20,9 +20,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 hj = importlib.import_module("hyrise-1_b200")
 abi = hj.abi
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("HJ_RUN_UNVALIDATED") != "1",
-                                 reason="hj_aggregate_column has not run on a GPU yet (set HJ_RUN_UNVALIDATED=1)")]
+pytestmark = pytest.mark.gpu
 FIX = am.load_fixtures()
 KEY_TYPES = {"int32": abi.KEY_INT32, "int64": abi.KEY_INT64, "float32": abi.KEY_FLOAT, "float64": abi.KEY_DOUBLE}
 SUM_RTOL = 1e-12
@@ -378,6 +376,12 @@ def test_random_grouped_relations_match_oracle(ctx):
 
 
 # ---- GROUP BY several columns: hj_aggregate_grouped_rows (tables keyed by a representative row) ---------------------------
+def _as_stored(key, group_cols):
+    """A fixture's group key as the column stores it: the .tbl text 350.7 of a float column is the float32 350.70001220703125
+    the device (and the reference's ValueColumn<float>) groups by."""
+    return tuple(None if x is None else gv.dtype.type(x).item() for x, (gv, _) in zip(key, group_cols))
+
+
 def grouped_rows_on_gpu(ctx, group_cols, v, vz, max_groups=0):
     """group_cols: [(values, is_null)]; returns {tuple of group values (None = NULL): aggregate dict}, the group values read
     from the host columns at the representative row the library reports."""
@@ -407,7 +411,7 @@ def test_reference_group_by_case_on_gpu_by_representative_rows(ctx, case):
     table = FIX["grouped_tables"][case["table"]]
     group_cols = [am.column_of(table, name) for name in case["group_by"]]
     k = len(group_cols)
-    expected = {tuple(row[:k]): row[k:] for row in case["expected_rows"]}
+    expected = {_as_stored(row[:k], group_cols): row[k:] for row in case["expected_rows"]}
     if not case["aggregates"]:
         assert set(grouped_rows_on_gpu(ctx, group_cols, None, None)) == set(expected)
         return
@@ -454,7 +458,7 @@ def test_reference_group_by_case_by_representative_rows_through_chunk_descriptor
     group_cols = [am.column_of(table, name) for name in case["group_by"]]
     rels = [host_relation(gv, gz, case["chunk_size"], encoding) for gv, gz in group_cols]
     k = len(group_cols)
-    expected = {tuple(row[:k]): row[k:] for row in case["expected_rows"]}
+    expected = {_as_stored(row[:k], group_cols): row[k:] for row in case["expected_rows"]}
 
     def keyed(got):
         return {tuple(None if gz[row] else gv[row].item() for gv, gz in group_cols): agg for row, agg in got.items()}

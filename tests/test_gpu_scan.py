@@ -1,8 +1,8 @@
 """Device TableScan (hj_scan) against the oracle and the reference's own expectations, through the C ABI.
 
 First GPU run: profiles/r01_gpu_scan_first_run.txt (312 passed: the reference's cases x encodings, the randomized
-differential scans, int64, slots). The last test — scan -> join with the PosLists staying in HBM — had no GPU seconds left
-this round and is skipped unless HJ_RUN_UNVALIDATED=1; it is the first thing to run next round.
+differential scans, int64, slots); the float / string / FOR / RLE scans, hj_gather_column and scan -> join with the PosLists
+staying in HBM first ran in round 2 (profiles/r02_gpu_call1_gated_suites.txt).
 Everything compared against (oracle/table_scan_oracle.py, tests/golden/scan_fixtures.json) is pinned on CPU by
 tests/test_scan_oracle.py."""
 import importlib
@@ -21,8 +21,6 @@ if ROOT not in sys.path:
 hj = importlib.import_module("hyrise-1_b200")
 abi = hj.abi
 pytestmark = pytest.mark.gpu
-unvalidated = pytest.mark.skipif(os.environ.get("HJ_RUN_UNVALIDATED") != "1",
-                                 reason="this path has not run on a GPU yet (set HJ_RUN_UNVALIDATED=1)")
 
 FIX = sm.load_fixtures()
 CASES = [(c, e) for c in FIX["cases"] for e in sm.encodings_for(c)]
@@ -84,7 +82,6 @@ def test_reference_scan_case_on_gpu(ctx, case, encode):
     assert sm.run_case(case, FIX["tables"], make_gpu_scan(ctx), encode) == sm.expected_of(case), case["cite"]
 
 
-@unvalidated
 @pytest.mark.parametrize("style", ["for", "rle"])
 @pytest.mark.parametrize("case,encode", [ce for ce in CASES if ce[1] != "none" and not ce[0].get("expect_error")],
                          ids=[i for i, ce in zip(IDS, CASES) if ce[1] != "none" and not ce[0].get("expect_error")])
@@ -152,7 +149,6 @@ def test_irregular_chunk_ids_and_slots(ctx):
     assert np.array_equal(ctx.scan_fetch(2)[0], want_b)
 
 
-@unvalidated
 def test_scan_then_join_without_leaving_the_device(ctx):
     """The point of N4: both join inputs are filtered by device scans; their PosLists never leave HBM and feed hj_join as
     REFERENCE segments of device-resident relations. Checked against the oracle join of the host-filtered inputs."""
@@ -210,14 +206,12 @@ def test_scan_then_join_without_leaving_the_device(ctx):
 
 
 # ---- float / double columns (hj_scan compares the column type's values; HJ_SCAN_VALUE_IS_DOUBLE literals) ---------------
-@unvalidated
 @pytest.mark.parametrize("case", FIX["float_cases"], ids=[c["name"] for c in FIX["float_cases"]])
 @pytest.mark.parametrize("encode,style", [("none", "dict"), ("all", "dict"), ("all", "rle")])
 def test_reference_float_scan_case_on_gpu(ctx, case, encode, style):
     assert sm.run_case(case, FIX["typed_tables"], make_gpu_scan(ctx), encode, style) == sm.expected_of(case), case["cite"]
 
 
-@unvalidated
 @pytest.mark.parametrize("dtype", [np.float32, np.float64])
 @pytest.mark.parametrize("encoding", ["value", "dict", "mixed"])
 @pytest.mark.parametrize("nullable", [False, True])
@@ -234,7 +228,6 @@ def test_random_float_scans_match_oracle(ctx, dtype, encoding, nullable):
         scan(chunks, ids, 0, None)
 
 
-@unvalidated
 def test_floating_literal_on_an_integer_column(ctx):
     chunks = [{"kind": "value", "values": np.array([455, 456, 457, 458, -1, 0], np.int32), "nulls": None},
               sm.dict_encode(np.array([455, 456, 457, 458, -1, 0], np.int32), np.zeros(6, np.uint8))]
@@ -268,13 +261,11 @@ def make_gpu_value_id_scan(j):
     return scan
 
 
-@unvalidated
 @pytest.mark.parametrize("case", FIX["string_cases"], ids=[c["name"] for c in FIX["string_cases"]])
 def test_reference_string_scan_case_on_gpu(ctx, case):
     assert sm.run_case(case, FIX["typed_tables"], make_gpu_value_id_scan(ctx), "all") == sm.expected_of(case), case["cite"]
 
 
-@unvalidated
 def test_random_string_dictionary_scans_match_oracle(ctx):
     from test_scan_oracle import string_chunks
     rng = np.random.default_rng(77)
@@ -287,7 +278,6 @@ def test_random_string_dictionary_scans_match_oracle(ctx):
                 scan(chunks, ids, pred, lit)
 
 
-@unvalidated
 def test_value_id_scan_refuses_other_chunk_kinds(ctx):
     small = [{"kind": "value", "values": np.arange(10, dtype=np.int32), "nulls": None}]
     with pytest.raises(hj.HjError) as e:
@@ -296,7 +286,6 @@ def test_value_id_scan_refuses_other_chunk_kinds(ctx):
 
 
 # ---- hj_gather_column: a column read through a device PosList (what the join's consumers do first) ----------------------
-@unvalidated
 @pytest.mark.parametrize("encoding", ["value", "dict"])
 @pytest.mark.parametrize("dtype", [np.int32, np.int64, np.float32])
 def test_gather_column_at_the_join_result(ctx, dtype, encoding):
@@ -356,7 +345,6 @@ def test_gather_column_at_the_join_result(ctx, dtype, encoding):
     assert np.array_equal(device_array(v, n, "<i4"), np.where(want_null, 0, payload[rows]))
 
 
-@unvalidated
 def test_gather_column_reports_row_ids_outside_the_column(ctx):
     import torch
     dev = torch.device("cuda", 0)

@@ -27,8 +27,6 @@ def test_shim_replays_reference_cases(built):
 
 
 @pytest.mark.gpu
-@pytest.mark.skipif(os.environ.get("HJ_RUN_UNVALIDATED") != "1",
-                    reason="opossum::TableScan (host/table_scan.cpp) has not run on a GPU yet (set HJ_RUN_UNVALIDATED=1)")
 def test_shim_replays_reference_cases_with_device_scans(built):
     """Same 53 cases, but every `scan` the device operator covers (integer column vs integer literal) runs through the C++
     opossum::TableScan -> hj_scan, so the filtered join inputs are produced on the GPU (SURVEY 8f N4)."""
@@ -41,8 +39,6 @@ def test_shim_replays_reference_cases_with_device_scans(built):
 
 
 @pytest.mark.gpu
-@pytest.mark.skipif(os.environ.get("HJ_RUN_UNVALIDATED") != "1",
-                    reason="float / string scans of opossum::TableScan have not run on a GPU yet (set HJ_RUN_UNVALIDATED=1)")
 def test_shim_replays_reference_float_and_string_scan_cases(built):
     """table_scan_test.cpp DoubleScan (float column behind a reference table) and table_scan_string_test.cpp ScanEquals /
     ScanNotEquals / ScanLessThan (dictionary-encoded string column: dictionary searched on the host, attribute vectors
@@ -57,8 +53,6 @@ def test_shim_replays_reference_float_and_string_scan_cases(built):
 
 
 @pytest.mark.gpu
-@pytest.mark.skipif(os.environ.get("HJ_RUN_UNVALIDATED") != "1",
-                    reason="opossum::Aggregate (host/aggregate.cpp) has not run on a GPU yet (set HJ_RUN_UNVALIDATED=1)")
 def test_shim_replays_reference_ungrouped_aggregate_cases(built):
     """aggregate_test.cpp NoGroupbySingleAggregate{Max,Min,Sum,Avg,Count} — on the data table (value and dictionary chunks)
     and, like the reference's test_output, behind a TableScan — TwoAggregateEmptyTable, and all 39 numeric group-by cases (1, 2
