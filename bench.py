@@ -34,10 +34,25 @@ WORKLOADS = {
            "C2 synthetic 1:N int32 inner equi-join, 100M build x 1B probe, uniform keys, dictionary-encoded"),
     "c3": (200_000_000, 2_000_000_000, "int64", "value",
            "C3 synthetic int64 join, Zipf(1.0) build keys, 200M x 2B, ValueColumns"),
+    "c5": (4_000_000_000, 4_000_000_000, "int64", "value",
+           "C5 radix-partitioned 4B x 4B int64 join over 2/4/8 GPUs, permutation build x uniform probe, ValueColumns "
+           "(STRONG scaling: the published row counts are the global relations, every rank holds 1/N)"),
     "c1": (1_500_000, 6_001_215, "int32", "dict",
            "C1 TPC-H SF1 lineitem x orders on l_orderkey = o_orderkey (dbgen keys when oracle/_ref/libref_dbgen.so is present, "
            "else 1.5M unique x 6M uniform), dictionary-encoded"),
 }
+
+
+def csrc_hash():
+    """sha256 over the CUDA sources of libhj (what profiles/traffic_c2_full.json was captured from)."""
+    import hashlib
+    h = hashlib.sha256()
+    d = os.path.join(ROOT, "hyrise-1_b200", "csrc")
+    for name in sorted(os.listdir(d)):
+        if name.endswith((".cu", ".cuh")):
+            with open(os.path.join(d, name), "rb") as f:
+                h.update(name.encode() + b"\0" + f.read())
+    return h.hexdigest()
 
 
 def log(*a):
@@ -45,13 +60,28 @@ def log(*a):
 
 
 # ------------------------------------------------------------------------------------------------------------ data
+STRONG = {"c5"}  # workloads whose published row counts are the GLOBAL relations (each rank holds 1/world of them)
+
+
+def perm_multiplier(domain):
+    """Odd multiplier A coprime to `domain` with x * A < 2^63 for every x < domain: x -> (x * A) mod domain + 1 is the
+    global permutation the build keys of a multi-rank run are cut from (every rank can generate its slice on its own)."""
+    import math
+    a = (2654435761 if domain < (1 << 31) else 1_000_000_007) % domain or 1
+    while math.gcd(a, domain) != 1:
+        a += 1
+    return a
+
+
 def gen_device_workload(name, scale, device, seed, rank=0, world=1):
     """Builds this rank's shard of the workload's key columns on `device` with torch: `scale` x the published row counts
-    PER RANK (weak scaling), keys drawn from the GLOBAL domain of world x n_build, chunk ids global. Returns dict with
-    per-relation lists of (chunk_id, dictionary|values tensor, attr tensor|None) and row counts."""
-    import math
+    PER RANK (weak scaling; STRONG workloads: 1/world of them), keys drawn from the GLOBAL domain of all ranks' build rows,
+    chunk ids global. Returns dict with per-relation lists of (chunk_id, dictionary|values tensor, attr tensor|None) and
+    row counts."""
     import torch
     n_build, n_probe, dtype, encoding, _ = WORKLOADS[name]
+    if name in STRONG:
+        n_build, n_probe = n_build // world, n_probe // world
     n_build, n_probe = max(1, int(n_build * scale)), max(1, int(n_probe * scale))
     tdt = torch.int32 if dtype == "int32" else torch.int64
     g = torch.Generator(device=device)
@@ -63,13 +93,11 @@ def gen_device_workload(name, scale, device, seed, rank=0, world=1):
         ranks = torch.exp(u * np.log(domain + 1.0)).floor().clamp_(1, domain).to(torch.int64)
         build_keys = ((ranks * 0x9E3779B1) % domain + 1).to(tdt)
         del u, ranks
-    elif world == 1:
+    elif world == 1 and name not in STRONG:
         build_keys = (torch.randperm(domain, device=device, generator=g) + 1).to(tdt)  # unique: 1:N join
     else:
         # this rank's slice of ONE global permutation of 1..domain: x -> (x * A) mod domain with gcd(A, domain) = 1
-        a = 2654435761 % domain or 1
-        while math.gcd(a, domain) != 1:
-            a += 1
+        a = perm_multiplier(domain)
         x = torch.arange(rank * n_build, (rank + 1) * n_build, device=device, dtype=torch.int64)
         build_keys = ((x * a) % domain + 1).to(tdt)
         del x
@@ -132,6 +160,95 @@ def to_pinned_host(chunks):
 
 def input_bytes(chunks):
     return sum(a.numel() * a.element_size() + (0 if b is None else b.numel() * b.element_size()) for _, a, b in chunks)
+
+
+# ------------------------------------------------------------------------------------------------------------ verify
+class _DevArray:
+    """A raw device pointer as something torch.as_tensor understands (no copy)."""
+    def __init__(self, ptr, n, typestr="<i8"):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
+
+
+def _flat_keys(chunks):
+    import torch
+    mask = {torch.int32: 0xFFFFFFFF, torch.int16: 0xFFFF, torch.uint8: 0xFF}
+    return torch.cat([a if at is None else a[at.long() & mask[at.dtype]] for _, a, at in chunks])
+
+
+def _mulmod(k, m, d):
+    """(k * m) mod d for int64 tensors k < d <= 2^32 and a Python int m < d, without leaving 63 bits."""
+    hi, lo = m >> 16, m & 0xFFFF
+    return (((k * hi) % d) * 65536 + k * lo) % d
+
+
+def verify_result(j, data, info, name, rank, world, dev, sample=1_000_000):
+    """Checks the PosLists the last step left in HBM (hj_result_device; nothing is fetched) against values computed
+    independently with torch, reduced over the ranks: exact global row count, probe-side and build-side RowID checksums
+    (sum of chunk_id * 2^20 + offset over all result rows, mod 2^64) and key equality of sampled result rows (across
+    ranks: the sampled RowIDs are sent to the rank that holds the probe row). Inner joins only."""
+    import torch
+    import torch.distributed as dist
+    nb, npr = data["n_build"], data["n_probe"]
+    nc_b, nc_p = (nb + CHUNK - 1) // CHUNK, (npr + CHUNK - 1) // CHUNK
+    bptr, pptr, n = j.result_device()
+    rb = torch.as_tensor(_DevArray(bptr, n), device=dev) if n else torch.zeros(0, dtype=torch.int64, device=dev)
+    rp = torch.as_tensor(_DevArray(pptr, n), device=dev) if n else torch.zeros(0, dtype=torch.int64, device=dev)
+    pos = lambda r: (r & 0xFFFFFFFF) * CHUNK + (r >> 32)  # chunk ids are global: rank * chunks_per_rank + c
+    got = torch.stack([torch.tensor(n, device=dev), pos(rb).sum(), pos(rp).sum()])
+    bk, pk = _flat_keys(data["build"]), _flat_keys(data["probe"])
+    my_pos_p = torch.arange(npr, device=dev, dtype=torch.int64)
+    my_pos_p = (rank * nc_p + my_pos_p // CHUNK) * CHUNK + my_pos_p % CHUNK
+    permutation = name != "c3"
+    if permutation and (world > 1 or name in STRONG):
+        # build key of global row x is (x * A) mod D + 1: the build row a probe key joins with is x = (key - 1) * A^-1 mod D
+        domain = nb * world
+        ainv = pow(perm_multiplier(domain), -1, domain)
+        x = _mulmod(pk.to(torch.int64) - 1, ainv, domain)
+        want = torch.stack([torch.tensor(npr, device=dev), ((x // nb * nc_b + x % nb // CHUNK) * CHUNK + x % nb % CHUNK).sum(),
+                            my_pos_p.sum()])
+        del x
+    elif world == 1:
+        domain = int(max(bk.max(), pk.max())) + 1
+        cb = torch.zeros(domain, dtype=torch.int64, device=dev).index_add_(0, bk.long(), torch.ones(nb, dtype=torch.int64, device=dev))
+        cp = torch.zeros(domain, dtype=torch.int64, device=dev).index_add_(0, pk.long(), torch.ones(npr, dtype=torch.int64, device=dev))
+        m = cb[pk.long()]  # matches per probe row
+        my_pos_b = torch.arange(nb, device=dev, dtype=torch.int64)
+        want = torch.stack([m.sum(), (my_pos_b * cp[bk.long()]).sum(), (my_pos_p * m).sum()])
+        del cb, cp, m
+    else:
+        return None
+    # sampled rows: the keys behind both RowIDs must be equal
+    k = min(sample, n)
+    bad = torch.zeros(1, dtype=torch.int64, device=dev)
+    if world == 1:
+        if k:
+            idx = torch.randint(0, n, (k,), device=dev)
+            bad += (bk[pos(rb[idx])].to(torch.int64) != pk[pos(rp[idx])].to(torch.int64)).sum()
+    else:
+        idx = torch.randint(0, max(n, 1), (sample,), device=dev)
+        smp = torch.full((sample, 2), -1, dtype=torch.int64, device=dev)  # (probe RowID, key the build RowID stands for)
+        if n:
+            xb = rb[idx]
+            xg = ((xb & 0xFFFFFFFF) // nc_b) * nb + ((xb & 0xFFFFFFFF) % nc_b) * CHUNK + (xb >> 32)  # global build row
+            smp = torch.stack([rp[idx], _mulmod(xg, perm_multiplier(nb * world), nb * world) + 1], dim=1) if permutation else smp
+        allsmp = [torch.empty_like(smp) for _ in range(world)]
+        dist.all_gather(allsmp, smp)
+        q = torch.cat(allsmp)
+        chunk = q[:, 0] & 0xFFFFFFFF
+        mine = (q[:, 0] != -1) & (chunk >= rank * nc_p) & (chunk < (rank + 1) * nc_p)
+        q = q[mine]
+        local = ((q[:, 0] & 0xFFFFFFFF) - rank * nc_p) * CHUNK + (q[:, 0] >> 32)
+        bad += (pk[local].to(torch.int64) != q[:, 1]).sum()
+        k = sample
+    if world > 1:
+        dist.all_reduce(got)
+        dist.all_reduce(want)
+        dist.all_reduce(bad)
+    ok_rows, ok_b, ok_p = (bool(got[i] == want[i]) for i in range(3))
+    return {"rows": int(got[0]), "rows_expected": int(want[0]), "rows_ok": ok_rows, "checksums": ok_b and ok_p,
+            "build_checksum_ok": ok_b, "probe_checksum_ok": ok_p, "sampled_rows_per_rank": int(k),
+            "sampled_key_mismatches": int(bad.item()), "ok": ok_rows and ok_b and ok_p and int(bad.item()) == 0,
+            "how": "device-side check of the last timed step's PosLists (hj_result_device), reduced over ranks"}
 
 
 # ------------------------------------------------------------------------------------------------------------ clocks
@@ -214,10 +331,12 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--scale", type=float, default=1.0, help="fraction of the workload's row counts (1.0 = as published)")
-    ap.add_argument("--cpu-scale", type=float, default=0.05, help="fraction of the workload the CPU baseline runs")
+    ap.add_argument("--cpu-scale", type=float, default=None,
+                    help="fraction of the workload the CPU baseline runs (default: BASELINE.md 4.3 — 0.1 of C2/C3, 0.01 of C5, all of C1)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--slice-rows", type=int, default=0, help="hj_options.stream_slice_rows (0 = library default)")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-verify", action="store_true", help="skip the device-side result check after the timed region")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -227,18 +346,28 @@ def main():
     metric = "JoinHash input tuples/s"
     unit = "tuples/s"
     n_threads = os.cpu_count() or 1
+    if args.cpu_scale is None:
+        args.cpu_scale = {"c2": 0.1, "c3": 0.1, "c5": 0.01, "c1": 1.0}[args.workload]
+    scaling = "strong" if args.workload in STRONG else "weak"
+
+    def cpu_baseline(steps, warmup):
+        """All host threads on the bounded sample + the single-threaded figure (what the reference's own
+        join_benchmark.cpp:62-79 measures: no scheduler, jobs run inline) on a tenth of that sample."""
+        val, sample, sec = cpu_reference_sample(args.workload, args.cpu_scale, n_threads, steps, warmup)
+        val1, sample1, _ = cpu_reference_sample(args.workload, args.cpu_scale / 10, 1, 1, 1)
+        return {"value": val, "unit": unit, "cores": n_threads, "kind": "port", "sample": sample,
+                "value_1thread": val1, "sample_1thread": sample1}, sec
 
     if args.impl == "reference":
         if rank != 0:
             return 0
-        W = max(1, min(args.warmup, 1))
-        val, sample, sec = cpu_reference_sample(args.workload, args.cpu_scale, n_threads, args.steps, W)
-        line = {"impl": "reference", "metric": metric, "value": val, "unit": unit, "n_gpus": args.gpus, "steps": args.steps,
-                "warmup": W, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        cpu, sec = cpu_baseline(args.steps, args.warmup)
+        line = {"impl": "reference", "metric": metric, "value": cpu["value"], "unit": unit, "n_gpus": args.gpus, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
                 "dtype": dtype, "data": "synthetic",
-                "config": {"workload": desc, "sample": sample},
-                "cpu_baseline": {"value": val, "unit": unit, "cores": n_threads, "kind": "port", "sample": sample},
-                "e2e": {"value": val, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+                "config": {"workload": desc, "sample": cpu["sample"]},
+                "cpu_baseline": cpu,
+                "e2e": {"value": cpu["value"], "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
         print(json.dumps(line), flush=True)
         return 0
 
@@ -336,10 +465,16 @@ def main():
         phase_kernel.update({"materialize": "k_part1", "scatter2": "k_scatter2f"})
     dom = max(phase_bytes, key=lambda p_: mean_ms[p_])
     traffic = None
-    tpath = os.path.join(ROOT, "profiles", "traffic_c2_full.json")  # dram bytes per launch from the committed ncu capture
+    # dram bytes per launch from the committed `ncu --set full` capture — only while the kernels are the ones that were
+    # profiled: the file records a hash of hyrise-1_b200/csrc/*, a stale one is refused (traffic stays null)
+    tpath = os.path.join(ROOT, "profiles", "traffic_c2_full.json")
     if os.path.exists(tpath) and args.workload == "c2" and args.scale == 1.0 and world == 1:
         with open(tpath) as f:
-            traffic = json.load(f).get(phase_kernel[dom])
+            tj = json.load(f)
+        if tj.get("csrc_sha256") == csrc_hash():
+            traffic = tj.get(phase_kernel[dom])
+        else:
+            log("profiles/traffic_c2_full.json was captured from other kernel sources: roofline.traffic = null")
     whole_bytes = (nb + npr) * (2 * w_in + 2 * t_bytes) + info.n_rows * 16
     ach = phase_bytes[dom] / (mean_ms[dom] * 1e-3) / 1e9 if mean_ms[dom] else None
     roofline = {"bound": "hbm", "kernel": phase_kernel[dom], "achieved": ach, "peak": peak, "unit": "GB/s",
@@ -358,6 +493,14 @@ def main():
         roofline["nvlink"] = {"bytes_sent_per_rank": sent, "transfer_ms": xms, "achieved": sent / (xms * 1e-3) / 1e9 if xms else None,
                               "peak": 900.0, "unit": "GB/s per direction",
                               "note": "transfer_ms also contains the probe side's destination scatter kernel"}
+
+    # ---- the last timed step's PosLists are still in HBM: check them (outside the timed region, every N)
+    verified = None
+    if not args.no_verify:
+        verified = verify_result(j, data, info, args.workload, rank, world, dev)
+        torch.cuda.empty_cache()
+        if rank == 0:
+            log(f"verified: {verified}")
 
     # ---- e2e: same join through the C ABI from pinned host buffers, PosLists fetched to pinned host memory
     e2e = None
@@ -406,19 +549,19 @@ def main():
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        val, sample, _ = cpu_reference_sample(args.workload, args.cpu_scale, n_threads, 2, 1)
-        cpu = {"value": val, "unit": unit, "cores": n_threads, "kind": "port", "sample": sample}
+        cpu, _ = cpu_baseline(2, 1)
 
     if rank == 0:
         line = {"metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps,
-                "warmup": W, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+                "warmup": W, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": scaling,
                 "vs_baseline": None, "dtype": dtype, "data": data.get("source", "synthetic"),
-                "config": {"workload": desc + (f"; {world} ranks each hold that many rows of one global join (hash exchange over NCCL)"
-                                               if world > 1 else ""),
+                "config": {"workload": desc + (f"; {world} ranks each hold that many rows of one global join (hash exchange over NVLink)"
+                                               if world > 1 and scaling == "weak" else ""),
                            "scale": args.scale, "n_build": nb * world, "n_probe": npr * world,
                            "chunk_rows": CHUNK, "mode": "Inner", "result_rows": total_results,
                            "radix_bits": info.radix_bits, "l2": "inputs larger than L2, no flush"},
-                "clocks": clocks, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e}
+                "clocks": clocks, "gpu_launches": launches, "verified": verified, "roofline": roofline, "cpu_baseline": cpu,
+                "e2e": e2e}
         print(json.dumps(line), flush=True)
     j.close()
     if world > 1:

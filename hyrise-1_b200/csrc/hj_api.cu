@@ -740,10 +740,15 @@ struct PartState {
   uint32_t gs = 0;     // fused: slabs per pass-2 work item
 };
 
-// P1's dynamic shared memory: the full-resolution histogram + one staging tile per virtual CTA
+// P1's dynamic shared memory: the full-resolution histogram + per virtual CTA one staging tile (k_part1) or two key
+// buffers and a 16-bit permutation (k_part1p)
+#ifndef HJ_TUNE_P1_PIPE
+#define HJ_TUNE_P1_PIPE 1  // 1: software-pipelined pass 1 (k_part1p, cp.async gathers); 0: k_part1 of round 1
+#endif
 template <typename K>
 size_t part1_smem(int radix_bits) {
-  return ((((size_t(1) << radix_bits) + 1) * 4 + 15) & ~size_t(15)) + size_t(Cfg<K>::kP1Virtual) * p1_tile<K>() * (sizeof(K) + 2);
+  const size_t per_row = HJ_TUNE_P1_PIPE ? 2 * sizeof(K) + 2 : sizeof(K) + 2;
+  return ((((size_t(1) << radix_bits) + 1) * 4 + 15) & ~size_t(15)) + size_t(Cfg<K>::kP1Virtual) * p1_tile<K>() * per_row;
 }
 
 template <typename K, bool PAY>
@@ -785,7 +790,11 @@ int stage_hist(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int
       constexpr int VC = Cfg<K>::kP1Virtual;
       if (F1 > uint32_t(kHistThreads / VC))  // cannot happen with the default geometry (VT >= kMaxDigits); HJ_TUNE_P1_SMALL_VT builds
         return fail(ctx, HJ_ERR_INVALID, "this build of pass 1 scans at most %d level-1 digits, the join needs %u", kHistThreads / VC, F1);
+#if HJ_TUNE_P1_PIPE
+      auto k = k_part1p<K, kHistThreads, VC, p1_tile<K>(), false>;
+#else
       auto k = k_part1<K, kHistThreads, VC, p1_tile<K>()>;
+#endif
       const size_t smem = part1_smem<K>(radix_bits);
       HJ_TRY(set_smem(ctx, k, smem));
       const uint32_t grid = std::min<uint32_t>((pr.meta.n_tiles + VC - 1) / VC, ctx->n_sms);

@@ -29,7 +29,7 @@
 #define HJ_TUNE_P1_GATHER 0
 #endif
 #ifndef HJ_TUNE_P2_SMEM
-#define HJ_TUNE_P2_SMEM 0  // 1: pass 2's small shared arrays as members of one struct (instruction diet, unmeasured)
+#define HJ_TUNE_P2_SMEM 1  // 1: pass 2's small shared arrays as members of one struct: 5.285 -> 5.175 ms on C2 (profiles/r02_sweep_variants5_c2_full.json)
 #endif
 #ifndef HJ_TUNE_P2_STEPS
 #define HJ_TUNE_P2_STEPS 1
@@ -216,6 +216,209 @@ __global__ void __launch_bounds__(NT) k_part1(RelMeta rel, Tuple<K, false>* __re
   for (uint32_t b = threadIdx.x; b < n_bins; b += NT) {
     const uint32_t cb = s_hist[b];
     if (cb) atomicAdd(hist + b, cb);
+  }
+}
+
+// =====================================================================================================================
+// P1, software-pipelined (the default since round 2). Same result as k_part1 — slab-local level-1 grouping + fragment
+// table + full-resolution histogram — but a virtual CTA keeps THREE tiles in flight instead of one:
+//   tile t+2: its attribute-vector entries (or NULL flags) are on their way into registers (`pre`);
+//   tile t+1: its dictionary gathers are on their way into shared memory — cp.async (LDGSTS), 4/8 bytes per row, no
+//             register and no scoreboard slot held while they fly;
+//   tile t  : ranked, grouped and written back.
+// k_part1 serialised "gather (wait) -> rank -> scan -> stage -> copy out" per virtual CTA, so the gather pipe idled
+// while a tile was being ranked and copied and the other way round: 2.09 cycles per row and SM where the gather alone
+// needs 1.03 (profiles/r02_microbench_gather.txt: LDG = LDGSTS = 1.03-1.09 cycles per row and SM for 4-byte entries of
+// a 4 MB L2-resident table, whatever the occupancy; 16-byte bulk copies through the TMA engine 3.6-4.1).
+// The gathered keys stay where cp.async put them (kbuf[row]); grouping a tile only writes a 16-bit permutation
+// (perm[position in the grouped slab] = row) and the copy-out reads kbuf through it — one shared-memory store and one
+// load per row fewer than staging (key, row) pairs.
+// XCH: the relation consists of kSegExch8 segments (rows received from the multi-GPU exchange as finished tuples:
+// int32 joins (hash, source position), int64 joins (key, source position, source rank)); an element is the whole tuple.
+// dynamic smem: (2^radix_bits + 1) * 4 (rounded up to 16) + VC * TILE * (2 * sizeof(E) + 2).
+// =====================================================================================================================
+__device__ __forceinline__ uint32_t smem_addr_of(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+template <int BYTES>
+__device__ __forceinline__ void cp_async_small(void* dst_smem, const void* src) {
+  static_assert(BYTES == 4 || BYTES == 8 || BYTES == 16, "cp.async copies 4, 8 or 16 bytes");
+  if constexpr (BYTES == 16)
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr_of(dst_smem)), "l"(src) : "memory");
+  else
+    asm volatile("cp.async.ca.shared.global [%0], [%1], %2;" ::"r"(smem_addr_of(dst_smem)), "l"(src), "n"(BYTES) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+constexpr uint8_t kSegExch8 = 14;  // internal: finished tuples received from the exchange (hj_comm.cuh); chunk_id = source rank,
+                                   // null_value_id != 0: every row of the segment is a routed NULL probe row
+
+template <typename K, bool XCH> struct P1Elem { using type = K; };
+template <typename K> struct P1Elem<K, true> { using type = Tuple<K, false>; };
+
+template <typename K, int NT, int VC, int TILE, bool XCH>
+__global__ void __launch_bounds__(NT) k_part1p(RelMeta rel, Tuple<K, false>* __restrict__ out1, uint16_t* __restrict__ frag,
+                                               uint32_t* __restrict__ hist, int radix_bits, int bits2, int null_policy) {
+  using T = Tuple<K, false>;
+  using E = typename P1Elem<K, XCH>::type;
+  constexpr int VT = NT / VC;
+  constexpr int ITEMS = TILE / VT;
+  static_assert(VT >= kMaxDigits && TILE <= 65535 && ITEMS >= 1 && ITEMS <= 32 && TILE % VT == 0,
+                "one thread per digit in the scan; 16-bit rows; validity bits in one word");
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  uint32_t* s_hist = reinterpret_cast<uint32_t*>(s_raw);
+  const uint32_t P = 1u << radix_bits;
+  const uint32_t n_bins = P + 1u;
+  unsigned char* buf_raw = s_raw + ((n_bins * 4u + 15u) & ~15u);
+  __shared__ uint32_t s_cnt[VC][kMaxDigits + 1], s_loff[VC][kMaxDigits + 2], s_scratch[VC][33];
+  const uint32_t pmask = P - 1u;
+  const uint32_t F1 = P >> bits2, FS = F1 + 2u;
+  const uint32_t v = threadIdx.x / VT, vt = threadIdx.x % VT;
+  const uint32_t G = gridDim.x * VC, c = blockIdx.x * VC + v;
+  E* kbuf = reinterpret_cast<E*>(buf_raw) + static_cast<size_t>(v) * 2 * TILE;  // [2][TILE]
+  uint16_t* perm = reinterpret_cast<uint16_t*>(buf_raw + static_cast<size_t>(VC) * 2 * TILE * sizeof(E)) + v * TILE;
+  for (uint32_t b = threadIdx.x; b < n_bins; b += NT) s_hist[b] = 0;
+  __syncthreads();
+
+  uint32_t pre[ITEMS];  // tile t+2: value ids (DICT) or NULL flags (other kinds)
+  // registers <- the tile's attribute-vector entries / NULL flags (plain loads; consumed one iteration later)
+  auto preload = [&](uint32_t tile) {
+    if (XCH || tile >= rel.n_tiles) return;
+    const DevSegment s = rel.segs[__ldg(rel.tile_seg + tile)];
+    const uint32_t r0 = (tile - s.tile_begin) * TILE;
+    const uint32_t cnt = min(static_cast<uint32_t>(TILE), s.n_rows - r0);
+#pragma unroll
+    for (int u = 0; u < ITEMS; ++u) {
+      const uint32_t i = u * VT + vt;
+      if (s.kind == 1) pre[u] = i < cnt ? load_attr(s, r0 + i) : s.null_value_id;
+      else pre[u] = (i < cnt && s.nulls && __ldg(s.nulls + r0 + i)) ? 1u : 0u;
+    }
+  };
+  // shared memory <- the tile's keys, asynchronously; returns the validity bits of this thread's rows
+  auto issue = [&](uint32_t tile, E* kb) -> uint32_t {
+    uint32_t vbits = 0;
+    if (tile < rel.n_tiles) {
+      const DevSegment s = rel.segs[__ldg(rel.tile_seg + tile)];
+      const uint32_t r0 = (tile - s.tile_begin) * TILE;
+      const uint32_t cnt = min(static_cast<uint32_t>(TILE), s.n_rows - r0);
+      if constexpr (XCH) {
+        const E* src = static_cast<const E*>(s.values) + r0;
+#pragma unroll
+        for (int u = 0; u < ITEMS; ++u) {
+          const uint32_t i = u * VT + vt;
+          if (i < cnt) cp_async_small<sizeof(E)>(kb + i, src + i);
+        }
+        vbits = s.null_value_id ? 0u : 0xFFFFFFFFu;
+      } else {
+        const bool narrow = sizeof(K) == 8 && s.key_type == 0;  // int32 chunk of an int64 join: widened by hand
+#pragma unroll
+        for (int u = 0; u < ITEMS; ++u) {
+          const uint32_t i = u * VT + vt;
+          if (i >= cnt) continue;
+          const bool valid = s.kind == 1 ? pre[u] != s.null_value_id : pre[u] == 0u;
+          vbits |= (valid ? 1u : 0u) << u;
+          if (s.kind == 1 && !valid) continue;             // no dictionary entry to fetch (the dictionary may be empty)
+          const uint32_t at = s.kind == 1 ? pre[u] : r0 + i;
+          if (narrow) kb[i] = static_cast<K>(__ldg(static_cast<const int32_t*>(s.values) + at));
+          else cp_async_small<sizeof(K)>(kb + i, static_cast<const K*>(s.values) + at);
+        }
+      }
+    }
+    cp_async_commit();  // one group per tile and thread, also when it is empty: wait_group counts groups
+    return vbits;
+  };
+
+  uint32_t tile = c;
+  preload(tile);
+  uint32_t vb_cur = issue(tile, kbuf);
+  preload(tile + G);
+  uint32_t b = 0;
+  for (; tile < rel.n_tiles; tile += G, b ^= 1u) {
+    for (uint32_t d = vt; d <= F1; d += VT) s_cnt[v][d] = 0;
+    vbar(v, VT);  // the previous tile's copy-out has read kbuf[b ^ 1] and perm
+    const uint32_t vb_nxt = issue(tile + G, kbuf + (b ^ 1u) * TILE);
+    preload(tile + 2 * G);
+    cp_async_wait<1>();  // everything but the group just committed has landed: this tile's keys (own rows)
+
+    const DevSegment s = rel.segs[__ldg(rel.tile_seg + tile)];
+    const uint32_t r0 = (tile - s.tile_begin) * TILE;
+    const uint32_t cnt = min(static_cast<uint32_t>(TILE), s.n_rows - r0);
+    E* kb = kbuf + b * TILE;
+    uint32_t packed[ITEMS];  // digit << 16 | rank inside the digit, or kNoDigit
+#pragma unroll
+    for (int u = 0; u < ITEMS; ++u) {
+      packed[u] = kNoDigit;
+      const uint32_t i = u * VT + vt;
+      if (i < cnt) {
+        const bool valid = (vb_cur >> u) & 1u;
+        uint32_t d = kNoDigit;
+        if (valid || null_policy == kNullAsValue) {
+          uint32_t h;
+          if constexpr (XCH) {
+            const E e = kb[i];
+            if constexpr (sizeof(K) == 4) h = static_cast<uint32_t>(e.key); else h = hash_key(e.key);
+          } else {
+            K key = kb[i];
+            // NULL decodes to T{} for dictionary / gathered chunks (dictionary_column_iterable.hpp:80,
+            // reference_column_iterable.hpp:60); a ValueColumn keeps its stored value (quirk Q4)
+            if (!valid && s.kind != 0) { key = K(0); kb[i] = key; }
+            h = hash_key(key);
+          }
+          const uint32_t p = h & pmask;
+          atomicAdd(&s_hist[p], 1u);
+          d = p >> bits2;
+        } else if (null_policy == kNullRoute) {
+          if constexpr (!XCH) kb[i] = K(0);
+          atomicAdd(&s_hist[P], 1u);
+          d = F1;
+        }
+        if (d != kNoDigit) packed[u] = (d << 16) | atomicAdd(&s_cnt[v][d], 1u);
+      }
+    }
+    vbar(v, VT);
+    {
+      const uint32_t cd = vt < F1 ? s_cnt[v][vt] : 0u;
+      uint32_t total;
+      const uint32_t ex = vblock_excl_scan<VT>(cd, v, vt, s_scratch[v], &total);
+      if (vt < F1) s_loff[v][vt] = ex;
+      if (vt == 0) {
+        s_loff[v][F1] = total;
+        s_loff[v][F1 + 1] = total + s_cnt[v][F1];
+      }
+    }
+    vbar(v, VT);
+#pragma unroll
+    for (int u = 0; u < ITEMS; ++u)
+      if (packed[u] != kNoDigit) perm[s_loff[v][packed[u] >> 16] + (packed[u] & 0xFFFFu)] = static_cast<uint16_t>(u * VT + vt);
+    for (uint32_t d = vt; d < FS; d += VT) frag[static_cast<size_t>(tile) * FS + d] = static_cast<uint16_t>(s_loff[v][d]);
+    vbar(v, VT);  // perm complete; every thread's cp.async data and NULL fix-ups are visible to the others
+    const uint32_t n_out = s_loff[v][F1 + 1];
+    T* dst = out1 + s.row_begin + r0;  // the slab: this tile's own rows' place
+    const uint32_t idx0 = s.row_begin + r0;
+#pragma unroll
+    for (int u = 0; u < ITEMS; ++u) {
+      const uint32_t i = u * VT + vt;
+      if (i < n_out) {
+        const uint32_t r = perm[i];
+        T t;
+        if constexpr (XCH) {
+          t = kb[r];
+          if constexpr (sizeof(K) == 8) t.pad = s.chunk_id;  // source rank (the exchange kernel leaves it to the segment)
+        } else {
+          t.key = kb[r];
+          t.idx = idx0 + r;
+          if constexpr (sizeof(K) == 8) t.pad = 0;
+        }
+        dst[i] = t;
+      }
+    }
+    vb_cur = vb_nxt;
+  }
+  cp_async_wait<0>();
+  __syncthreads();
+  for (uint32_t bb = threadIdx.x; bb < n_bins; bb += NT) {
+    const uint32_t cb = s_hist[bb];
+    if (cb) atomicAdd(hist + bb, cb);
   }
 }
 

@@ -1,0 +1,60 @@
+#!/bin/bash
+# One parameterised driver for everything that runs on the GPU box (replaces the per-session gpu_run*.sh scripts):
+#   gpurun --timeout 1800 -- 'bash tests/gpu.sh TAG step[:arg] step[:arg] ...'
+# Every step has its own timeout, writes gpurun_out/TAG_<step>.out and appends its exit code + tail to gpurun_out/TAG.log;
+# a failing step does not stop the later ones. Steps:
+#   box                      GPU / host facts
+#   smoke                    __graft_entry__.smoke()
+#   pytest[:-k expr]         python -m pytest tests -m gpu -q [-k expr]
+#   pytestx[:-k expr]        the same with -x
+#   sweep:"runs"             tests/sweep_variants.py --scale 1.0 --runs <runs> (variant libraries from tests/build_variants.sh)
+#   sweepw:"workload scale runs"
+#   bench[:args]             bench.py --steps 5 --warmup 3 <args>   (default args: --no-e2e --no-cpu)
+#   benchfull                bench.py with its defaults (the driver's line)
+#   benchref                 bench.py --impl reference --steps 3 --warmup 1
+#   launches[:bench args]    ncu launch list (gpu__time_duration) of bench.py --steps 2 --warmup 3 --no-e2e --no-cpu --no-verify
+#   ncufull:"regex skip count [workload scale]"   ncu --set full of tests/profile_join.py, report -> gpurun_out/TAG_ncu_<n>.ncu-rep
+#   micro:name               tests/micro/<name> (prebuilt binary)
+#   sharded[:args]           torchrun -n $NGPU tests/sharded_check.py --backend nccl <args>
+#   benchn[:args]            torchrun -n $NGPU bench.py --gpus $NGPU --steps 5 --warmup 3 <args>
+#   py:"script args"         python <script args>
+cd "$(dirname "$0")/.."
+TAG=$1; shift
+mkdir -p gpurun_out
+L=gpurun_out/$TAG.log; : > $L
+NGPU=${NGPU:-$(nvidia-smi -L | wc -l)}
+n=0
+run() {  # run <name> <timeout s> <command...>
+  local name=$1 t=$2; shift 2
+  local out="gpurun_out/${TAG}_${name}.out"
+  ( time timeout "$t" "$@" > "$out" 2>&1 ) 2>> $L
+  local rc=$?
+  echo "== $name rc=$rc" | tee -a $L
+  tail -${TAIL:-6} "$out" | cut -c1-${CUT:-600} | tee -a $L
+}
+TORCHRUN="python -m torch.distributed.run --nnodes=1 --nproc-per-node $NGPU --master-addr 127.0.0.1 --master-port"
+for spec in "$@"; do
+  step=${spec%%:*}; arg=""; [ "$spec" != "$step" ] && arg=${spec#*:}
+  n=$((n + 1))
+  case $step in
+    box) run box 30 bash -c 'nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,memory.total --format=csv; nvidia-smi topo -m 2>/dev/null | head -12; nproc; free -g | head -2' ;;
+    smoke) run smoke 300 python __graft_entry__.py smoke ;;
+    pytest) run pytest$n 1500 python -m pytest tests -m gpu -q $arg ;;
+    pytestx) run pytest$n 1500 python -m pytest tests -m gpu -q -x $arg ;;
+    sweep) run sweep$n 600 python tests/sweep_variants.py --scale 1.0 --runs $arg --out gpurun_out/${TAG}_sweep$n.json ;;
+    sweepw) set -- $arg; w=$1; sc=$2; shift 2; run sweep$n 600 python tests/sweep_variants.py --workload $w --scale $sc --joins 3 --runs "$@" --out gpurun_out/${TAG}_sweep$n.json ;;
+    bench) run bench$n 600 python bench.py --steps 5 --warmup 3 ${arg:---no-e2e --no-cpu} ;;
+    benchfull) run benchfull 900 python bench.py ;;
+    benchref) run benchref 600 python bench.py --impl reference --steps 3 --warmup 1 ;;
+    launches) run launches$n 300 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:k_ -c 400 --csv --log-file gpurun_out/${TAG}_launches$n.csv \
+                python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu --no-verify $arg ;;
+    ncufull) set -- $arg; rx=$1; skip=${2:-0}; cnt=${3:-4}; w=${4:-c2}; sc=${5:-1.0}
+             run ncu$n 1200 ncu --set full --clock-control none --import-source on -k "regex:$rx" -s $skip -c $cnt -o gpurun_out/${TAG}_ncu$n -f \
+                python tests/profile_join.py --workload $w --scale $sc --joins 2 ;;
+    micro) run micro_$arg 120 tests/micro/$arg ;;
+    sharded) run sharded$n 900 $TORCHRUN $((29500 + RANDOM % 400)) tests/sharded_check.py --backend nccl $arg ;;
+    benchn) run benchn$n 900 $TORCHRUN $((29500 + RANDOM % 400)) bench.py --gpus $NGPU --steps 5 --warmup 3 ${arg:---no-e2e --no-cpu} ;;
+    py) run py$n 900 python $arg ;;
+    *) echo "unknown step $step" | tee -a $L ;;
+  esac
+done
