@@ -743,7 +743,11 @@ struct PartState {
 // P1's dynamic shared memory: the full-resolution histogram + per virtual CTA one staging tile (k_part1) or two key
 // buffers and a 16-bit permutation (k_part1p)
 #ifndef HJ_TUNE_P1_PIPE
-#define HJ_TUNE_P1_PIPE 1  // 1: software-pipelined pass 1 (k_part1p, cp.async gathers); 0: k_part1 of round 1
+// 1: software-pipelined pass 1 (k_part1p, cp.async gathers); 0: k_part1 of round 1. Measured on C2 (profiles/
+// r02_sweep_p1_pipelined.md): k_part1p 8.54 ms, k_part1 + ld.global.cg 7.75 ms — the pipelined kernel loses (more shared
+// memory = less L1 for the gather's line allocations, 8-cycle LDGSTS issue), so k_part1 stays the default for column
+// inputs; k_part1p<XCH> partitions the tuples received from the multi-GPU exchange (hj_comm.cuh).
+#define HJ_TUNE_P1_PIPE 0
 #endif
 template <typename K>
 size_t part1_smem(int radix_bits) {

@@ -25,8 +25,9 @@
 #ifndef HJ_TUNE_P1_GATHER
 // how P1 reads a dictionary entry: 0 = ld.global.nc (allocates an L1 line per gather; the default, measured), 1 = ld.global.cg
 // (L2 only), 2 = ld.global.nc.L1::no_allocate. The gather never hits L1 (a 2048-row tile touches 2048 of ~1 M entries), and
-// P1 is bound by the misses it can keep in flight — untried on a GPU: variants for tests/sweep_variants.py.
-#define HJ_TUNE_P1_GATHER 0
+// P1 is bound by the misses it can keep in flight. Measured on C2 (profiles/r02_sweep_variants5_c2_full.json): 0 = 7.88 ms,
+// 1 = 7.75 ms, 2 = 19.96 ms.
+#define HJ_TUNE_P1_GATHER 1
 #endif
 #ifndef HJ_TUNE_P2_SMEM
 #define HJ_TUNE_P2_SMEM 1  // 1: pass 2's small shared arrays as members of one struct: 5.285 -> 5.175 ms on C2 (profiles/r02_sweep_variants5_c2_full.json)
@@ -220,7 +221,7 @@ __global__ void __launch_bounds__(NT) k_part1(RelMeta rel, Tuple<K, false>* __re
 }
 
 // =====================================================================================================================
-// P1, software-pipelined (the default since round 2). Same result as k_part1 — slab-local level-1 grouping + fragment
+// P1, software-pipelined (HJ_TUNE_P1_PIPE=1; measured SLOWER than k_part1 for column inputs, see hj_api.cu). Same result as k_part1 — slab-local level-1 grouping + fragment
 // table + full-resolution histogram — but a virtual CTA keeps THREE tiles in flight instead of one:
 //   tile t+2: its attribute-vector entries (or NULL flags) are on their way into registers (`pre`);
 //   tile t+1: its dictionary gathers are on their way into shared memory — cp.async (LDGSTS), 4/8 bytes per row, no
