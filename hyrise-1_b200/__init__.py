@@ -320,6 +320,16 @@ class HashJoin:
         self._check(self._l.hj_aggregate_column(self._ctx, device_values, device_nulls, n_rows, key_type, stream, C.byref(a)))
         return self._aggregate_dict(a)
 
+    def aggregate_column_static(self, device_values, device_nulls, n_rows, key_type, device_out, stream=None):
+        """hj_aggregate_column_static: the same aggregates without any allocation, synchronisation or host copy; the result
+        is one hj_aggregate record (abi.Aggregate, 80 bytes) written to the DEVICE address `device_out` in stream order.
+        `aggregate_record(bytes)` turns a copy of that record into the dict aggregate_column returns."""
+        self._check(self._l.hj_aggregate_column_static(self._ctx, device_values, device_nulls, n_rows, key_type, stream, device_out))
+
+    @classmethod
+    def aggregate_record(cls, raw):
+        return cls._aggregate_dict(abi.Aggregate.from_buffer_copy(bytes(raw)))
+
     def aggregate_grouped(self, group_keys, group_nulls, group_key_type, values, value_nulls, value_type, n_rows, max_groups=0,
                           stream=None):
         """hj_aggregate_grouped + fetch: {group key or None: aggregate dict} for device columns (pointers as ints)."""

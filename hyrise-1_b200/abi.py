@@ -120,6 +120,7 @@ SYMBOLS = {
     "hj_gather_column": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(Relation), C.c_int, C.c_void_p, C.POINTER(C.c_void_p),
                                    C.POINTER(C.c_void_p), C.POINTER(C.c_int)]),
     "hj_aggregate_column": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p, C.POINTER(Aggregate)]),
+    "hj_aggregate_column_static": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p, C.c_void_p]),
     "hj_aggregate_grouped": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_uint64,
                                        C.c_uint64, C.c_void_p, C.POINTER(GroupInfo)]),
     "hj_aggregate_grouped_rows": (C.c_int, [C.c_void_p, C.POINTER(GroupColumn), C.c_uint32, C.c_void_p, C.c_void_p, C.c_int, C.c_uint64,

@@ -1,5 +1,7 @@
 // hj_api.cu — host side of libhj: the C ABI of include/hj.h, device-memory management and kernel orchestration.
 // No CPU fallback anywhere: every compute entry point launches the sm_100a kernels of hj_kernels.cuh.
+#include <pthread.h>
+
 #include <algorithm>
 #include <cmath>
 #include <cstdarg>
@@ -1754,6 +1756,108 @@ int hj_aggregate_column(hj_ctx* ctx, const void* device_values, const uint8_t* d
   }
   HJ_LAUNCH_CHECK(ctx, "k_aggregate_partial");
   return finish_aggregate(ctx, partials, grid, n_rows, key_type, st, out);
+}
+
+// ---- hj_aggregate_column without allocations (no reference counterpart) ----
+}  // extern "C"
+
+namespace {
+
+// Scratch of hj_aggregate_column_static: [0] the folded result, [1..] one partial per CTA. File scope, so every GPU that
+// loads libhj holds these 112 KiB until the process exits. In HOST code `g_static_agg_partials` is only a stand-in for the
+// symbol, not a device address: the address comes from cudaGetSymbolAddress, once per device (static_agg_scratch).
+static __device__ __align__(256) AggPartial g_static_agg_partials[HJ_STATIC_AGG_MAX_PARTIALS + 1];
+
+constexpr int kStaticMaxDevices = 64;
+AggPartial* g_static_agg_ptr[kStaticMaxDevices] = {};
+pthread_mutex_t g_static_agg_lock = PTHREAD_MUTEX_INITIALIZER;
+
+// device address of the scratch array on ctx->device (which is current: check_ctx ran)
+int static_agg_scratch(hj_ctx* ctx, AggPartial** out) {
+  if (ctx->device < 0 || ctx->device >= kStaticMaxDevices) return fail(ctx, HJ_ERR_INVALID, "device %d: static scratch serves devices 0..%d", ctx->device, kStaticMaxDevices - 1);
+  pthread_mutex_lock(&g_static_agg_lock);
+  AggPartial* p = g_static_agg_ptr[ctx->device];
+  cudaError_t e = cudaSuccess;
+  if (!p) {
+    void* addr = nullptr;
+    e = cudaGetSymbolAddress(&addr, g_static_agg_partials);
+    if (e == cudaSuccess) g_static_agg_ptr[ctx->device] = p = static_cast<AggPartial*>(addr);
+  }
+  pthread_mutex_unlock(&g_static_agg_lock);
+  if (e != cudaSuccess) return fail(ctx, HJ_ERR_CUDA, "cudaGetSymbolAddress(g_static_agg_partials) failed: %s", cudaGetErrorString(e));
+  *out = p;
+  return HJ_OK;
+}
+
+// A2 of the static variant: the fold of k_aggregate_final (same order, same arithmetic) + finish_aggregate's conversion to
+// the ABI record, written to the caller's device memory.
+__global__ void __launch_bounds__(32) k_aggregate_final_out(const AggPartial* __restrict__ partials, uint32_t n_partials,
+                                                            unsigned long long n_rows, int floating, hj_aggregate* __restrict__ out) {
+  AggPartial a;
+  agg_init(a);
+  for (uint32_t p = threadIdx.x; p < n_partials; p += 32) agg_merge(a, partials[p]);
+#pragma unroll
+  for (int delta = 16; delta > 0; delta >>= 1) {
+    const AggPartial b = agg_shfl_down(a, delta);
+    agg_merge(a, b);
+  }
+  if (threadIdx.x == 0) {
+    hj_aggregate r;
+    r.n_rows = n_rows;
+    r.n_values = a.n_values;
+    r.is_floating = floating ? 1 : 0;
+    r.reserved = 0;
+    r.sum_int = floating ? 0 : a.sum_i;
+    r.sum_double = floating ? a.sum_d : static_cast<double>(a.sum_i);
+    r.min_int = r.max_int = 0;
+    r.min_double = r.max_double = 0.0;
+    if (a.n_values) {
+      r.min_int = floating ? 0 : a.min_i;
+      r.max_int = floating ? 0 : a.max_i;
+      r.min_double = floating ? a.min_d : static_cast<double>(a.min_i);
+      r.max_double = floating ? a.max_d : static_cast<double>(a.max_i);
+    }
+    *out = r;
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+int hj_aggregate_column_static(hj_ctx* ctx, const void* device_values, const uint8_t* device_nulls, uint64_t n_rows, int key_type,
+                               void* cuda_stream, hj_aggregate* device_out) {
+  if (!ctx) return HJ_ERR_INVALID;
+  if (!device_out) return fail(ctx, HJ_ERR_INVALID, "device_out is NULL");
+  if (key_type < HJ_KEY_INT32 || key_type > HJ_KEY_DOUBLE) return fail(ctx, HJ_ERR_INVALID, "key type %d", key_type);
+  if (n_rows && !device_values) return fail(ctx, HJ_ERR_INVALID, "device_values is NULL");
+  if (n_rows > HJ_STATIC_AGG_MAX_ROWS)
+    return fail(ctx, HJ_ERR_TOO_LARGE, "hj_aggregate_column_static: %llu rows exceed HJ_STATIC_AGG_MAX_ROWS = %llu (use hj_aggregate_column)",
+                (unsigned long long)n_rows, (unsigned long long)HJ_STATIC_AGG_MAX_ROWS);
+  HJ_TRY(check_ctx(ctx));
+  AggPartial* partials = nullptr;
+  HJ_TRY(static_agg_scratch(ctx, &partials));
+  cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
+  // the grid of hj_aggregate_column (so that double sums fold identically), capped by the scratch array
+  const uint32_t grid = static_cast<uint32_t>(std::min<uint64_t>(
+      HJ_STATIC_AGG_MAX_PARTIALS, std::max<uint64_t>(1, std::min<uint64_t>((n_rows + kAggThreads - 1) / kAggThreads, uint64_t(ctx->n_sms) * 8))));
+  switch (key_type) {
+    case HJ_KEY_INT32:
+      k_aggregate_partial<int32_t><<<grid, kAggThreads, 0, st>>>(static_cast<const int32_t*>(device_values), device_nulls, n_rows, partials + 1);
+      break;
+    case HJ_KEY_INT64:
+      k_aggregate_partial<int64_t><<<grid, kAggThreads, 0, st>>>(static_cast<const int64_t*>(device_values), device_nulls, n_rows, partials + 1);
+      break;
+    case HJ_KEY_FLOAT:
+      k_aggregate_partial<float><<<grid, kAggThreads, 0, st>>>(static_cast<const float*>(device_values), device_nulls, n_rows, partials + 1);
+      break;
+    default:
+      k_aggregate_partial<double><<<grid, kAggThreads, 0, st>>>(static_cast<const double*>(device_values), device_nulls, n_rows, partials + 1);
+  }
+  HJ_LAUNCH_CHECK(ctx, "k_aggregate_partial");
+  k_aggregate_final_out<<<1, 32, 0, st>>>(partials + 1, grid, n_rows, key_type >= HJ_KEY_FLOAT ? 1 : 0, device_out);
+  HJ_LAUNCH_CHECK(ctx, "k_aggregate_final_out");
+  return HJ_OK;
 }
 
 int hj_aggregate_grouped(hj_ctx* ctx, const void* device_group_keys, const uint8_t* device_group_nulls, int group_key_type,

@@ -398,6 +398,23 @@ typedef struct hj_aggregate {
 int hj_aggregate_column(hj_ctx* ctx, const void* device_values, const uint8_t* device_nulls, uint64_t n_rows,
                         int key_type, void* cuda_stream, hj_aggregate* out);
 
+/* hj_aggregate_column for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc). No counterpart in the reference.
+ * Same computation and same kernels' arithmetic as hj_aggregate_column (A1 one partial per CTA, A2 fold in CTA order: the
+ * results are identical, double sums included), but it calls no cudaMalloc / cudaFree / allocating routine, does not
+ * synchronise and copies nothing to the host: the per-CTA partials live in a file-scope `static __device__` array of
+ * libhj (HJ_STATIC_AGG_MAX_PARTIALS + 1 records of 56 bytes = 112 KiB, held by every GPU that loads the library until
+ * the process exits), and the result is written to `device_out`, one hj_aggregate in DEVICE memory provided by the caller,
+ * in stream order on `cuda_stream` (NULL = the context's own stream).
+ * Limits: n_rows <= HJ_STATIC_AGG_MAX_ROWS, else HJ_ERR_TOO_LARGE with a message naming the limit; nothing is launched.
+ * The scratch array is shared by every call on the device and keeps the last call's contents; nothing in it has to start
+ * at zero (every partial that is read was written by the same call). Calls that overlap on the GPU (different streams,
+ * different contexts or threads of one process) RACE on it: serialise them on one stream or with events. */
+#define HJ_STATIC_AGG_MAX_PARTIALS 2048u
+#define HJ_STATIC_AGG_MAX_ROWS (1ull << 31)
+int hj_aggregate_column_static(hj_ctx* ctx, const void* device_values, const uint8_t* device_nulls, uint64_t n_rows,
+                               int key_type, void* cuda_stream, hj_aggregate* device_out);
+
 /* GROUP BY one integer column (Aggregate with one group-by column, aggregate.cpp:254-420): per distinct value of the
  * group column — NULL being a group of its own — the aggregates of hj_aggregate over the rows of that group.
  * device_group_keys / device_group_nulls: the group column of the n_rows input rows in device memory (int32 / int64;
