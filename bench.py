@@ -169,23 +169,44 @@ class _DevArray:
         self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
 
 
-def _flat_keys(chunks):
-    import torch
-    mask = {torch.int32: 0xFFFFFFFF, torch.int16: 0xFFFF, torch.uint8: 0xFF}
-    return torch.cat([a if at is None else a[at.long() & mask[at.dtype]] for _, a, at in chunks])
-
-
 def _mulmod(k, m, d):
     """(k * m) mod d for int64 tensors k < d <= 2^32 and a Python int m < d, without leaving 63 bits."""
     hi, lo = m >> 16, m & 0xFFFF
     return (((k * hi) % d) * 65536 + k * lo) % d
 
 
+def _chunk_keys(chunk):
+    """Decoded keys of one (chunk_id, values | dictionary, attr | None) chunk as int64."""
+    import torch
+    _, a, at = chunk
+    if at is None:
+        return a.to(torch.int64)
+    mask = {torch.int32: 0xFFFFFFFF, torch.int16: 0xFFFF, torch.uint8: 0xFF}[at.dtype]
+    return a[at.long() & mask].to(torch.int64)
+
+
+def _keys_at(chunks, local_pos):
+    """Keys at local row positions (chunk index * CHUNK + offset) of a chunk list, without concatenating the column."""
+    import torch
+    out = torch.empty_like(local_pos)
+    c = local_pos // CHUNK
+    order = torch.argsort(c)
+    counts = torch.bincount(c, minlength=len(chunks)).tolist()
+    start = 0
+    for ci, n in enumerate(counts):
+        if n:
+            sel = order[start:start + n]
+            out[sel] = _chunk_keys(chunks[ci])[local_pos[sel] % CHUNK]
+            start += n
+    return out
+
+
 def verify_result(j, data, info, name, rank, world, dev, sample=1_000_000):
     """Checks the PosLists the last step left in HBM (hj_result_device; nothing is fetched) against values computed
     independently with torch, reduced over the ranks: exact global row count, probe-side and build-side RowID checksums
     (sum of chunk_id * 2^20 + offset over all result rows, mod 2^64) and key equality of sampled result rows (across
-    ranks: the sampled RowIDs are sent to the rank that holds the probe row). Inner joins only."""
+    ranks: the sampled RowIDs are sent to the rank that holds the probe row). Inner joins only. Works chunk by chunk so
+    that it fits next to the join's buffers at the full size of C3 / C5."""
     import torch
     import torch.distributed as dist
     nb, npr = data["n_build"], data["n_probe"]
@@ -193,52 +214,82 @@ def verify_result(j, data, info, name, rank, world, dev, sample=1_000_000):
     bptr, pptr, n = j.result_device()
     rb = torch.as_tensor(_DevArray(bptr, n), device=dev) if n else torch.zeros(0, dtype=torch.int64, device=dev)
     rp = torch.as_tensor(_DevArray(pptr, n), device=dev) if n else torch.zeros(0, dtype=torch.int64, device=dev)
-    pos = lambda r: (r & 0xFFFFFFFF) * CHUNK + (r >> 32)  # chunk ids are global: rank * chunks_per_rank + c
-    got = torch.stack([torch.tensor(n, device=dev), pos(rb).sum(), pos(rp).sum()])
-    bk, pk = _flat_keys(data["build"]), _flat_keys(data["probe"])
-    my_pos_p = torch.arange(npr, device=dev, dtype=torch.int64)
-    my_pos_p = (rank * nc_p + my_pos_p // CHUNK) * CHUNK + my_pos_p % CHUNK
+    return verify_poslists(rb, rp, data, name, rank, world, dev, sample)
+
+
+def verify_poslists(rb, rp, data, name, rank, world, dev, sample=1_000_000):
+    """verify_result over the two PosLists as int64 tensors (packed RowIDs: chunk_id | offset << 32)."""
+    import torch
+    import torch.distributed as dist
+    n = len(rp)
+    nb, npr = data["n_build"], data["n_probe"]
+    nc_b, nc_p = (nb + CHUNK - 1) // CHUNK, (npr + CHUNK - 1) // CHUNK
+
+    def pos_sum(r):  # sum of chunk_id * CHUNK + offset, in slices (chunk ids are global: rank * chunks_per_rank + c)
+        tot = torch.zeros((), dtype=torch.int64, device=dev)
+        for lo in range(0, len(r), 1 << 28):
+            x = r[lo:lo + (1 << 28)]
+            tot += ((x & 0xFFFFFFFF) * CHUNK + (x >> 32)).sum()
+        return tot
+    got = torch.stack([torch.tensor(n, device=dev), pos_sum(rb), pos_sum(rp)])
     permutation = name != "c3"
+    zero = lambda: torch.zeros((), dtype=torch.int64, device=dev)
     if permutation and (world > 1 or name in STRONG):
         # build key of global row x is (x * A) mod D + 1: the build row a probe key joins with is x = (key - 1) * A^-1 mod D
         domain = nb * world
         ainv = pow(perm_multiplier(domain), -1, domain)
-        x = _mulmod(pk.to(torch.int64) - 1, ainv, domain)
-        want = torch.stack([torch.tensor(npr, device=dev), ((x // nb * nc_b + x % nb // CHUNK) * CHUNK + x % nb % CHUNK).sum(),
-                            my_pos_p.sum()])
-        del x
+        want_b, want_p = zero(), zero()
+        for ci, ch in enumerate(data["probe"]):
+            pk = _chunk_keys(ch)
+            x = _mulmod(pk - 1, ainv, domain)
+            want_b += ((x // nb * nc_b + x % nb // CHUNK) * CHUNK + x % nb % CHUNK).sum()
+            want_p += (rank * nc_p + ci) * CHUNK * len(pk) + len(pk) * (len(pk) - 1) // 2
+        want = torch.stack([torch.tensor(npr, device=dev), want_b, want_p])
     elif world == 1:
-        domain = int(max(bk.max(), pk.max())) + 1
-        cb = torch.zeros(domain, dtype=torch.int64, device=dev).index_add_(0, bk.long(), torch.ones(nb, dtype=torch.int64, device=dev))
-        cp = torch.zeros(domain, dtype=torch.int64, device=dev).index_add_(0, pk.long(), torch.ones(npr, dtype=torch.int64, device=dev))
-        m = cb[pk.long()]  # matches per probe row
-        my_pos_b = torch.arange(nb, device=dev, dtype=torch.int64)
-        want = torch.stack([m.sum(), (my_pos_b * cp[bk.long()]).sum(), (my_pos_p * m).sum()])
-        del cb, cp, m
+        domain = int(max(max(int(_chunk_keys(ch).max()) for ch in data["build"]), max(int(_chunk_keys(ch).max()) for ch in data["probe"]))) + 1
+        cb = torch.zeros(domain, dtype=torch.int64, device=dev)
+        cp = torch.zeros(domain, dtype=torch.int64, device=dev)
+        for ch in data["build"]:
+            k = _chunk_keys(ch)
+            cb.index_add_(0, k, torch.ones_like(k))
+        for ch in data["probe"]:
+            k = _chunk_keys(ch)
+            cp.index_add_(0, k, torch.ones_like(k))
+        want_n, want_b, want_p = zero(), zero(), zero()
+        for ci, ch in enumerate(data["probe"]):
+            k = _chunk_keys(ch)
+            m = cb[k]  # matches per probe row
+            want_n += m.sum()
+            want_p += ((ci * CHUNK + torch.arange(len(k), device=dev)) * m).sum()
+        for ci, ch in enumerate(data["build"]):
+            k = _chunk_keys(ch)
+            want_b += ((ci * CHUNK + torch.arange(len(k), device=dev)) * cp[k]).sum()
+        want = torch.stack([want_n, want_b, want_p])
+        del cb, cp
     else:
         return None
     # sampled rows: the keys behind both RowIDs must be equal
     k = min(sample, n)
     bad = torch.zeros(1, dtype=torch.int64, device=dev)
+    lpos = lambda r, nc: ((r & 0xFFFFFFFF) - rank * nc) * CHUNK + (r >> 32)
     if world == 1:
         if k:
             idx = torch.randint(0, n, (k,), device=dev)
-            bad += (bk[pos(rb[idx])].to(torch.int64) != pk[pos(rp[idx])].to(torch.int64)).sum()
+            bad += (_keys_at(data["build"], lpos(rb[idx], nc_b)) != _keys_at(data["probe"], lpos(rp[idx], nc_p))).sum()
     else:
         idx = torch.randint(0, max(n, 1), (sample,), device=dev)
         smp = torch.full((sample, 2), -1, dtype=torch.int64, device=dev)  # (probe RowID, key the build RowID stands for)
-        if n:
+        if n and permutation:
             xb = rb[idx]
             xg = ((xb & 0xFFFFFFFF) // nc_b) * nb + ((xb & 0xFFFFFFFF) % nc_b) * CHUNK + (xb >> 32)  # global build row
-            smp = torch.stack([rp[idx], _mulmod(xg, perm_multiplier(nb * world), nb * world) + 1], dim=1) if permutation else smp
+            smp = torch.stack([rp[idx], _mulmod(xg, perm_multiplier(nb * world), nb * world) + 1], dim=1)
         allsmp = [torch.empty_like(smp) for _ in range(world)]
         dist.all_gather(allsmp, smp)
         q = torch.cat(allsmp)
         chunk = q[:, 0] & 0xFFFFFFFF
         mine = (q[:, 0] != -1) & (chunk >= rank * nc_p) & (chunk < (rank + 1) * nc_p)
         q = q[mine]
-        local = ((q[:, 0] & 0xFFFFFFFF) - rank * nc_p) * CHUNK + (q[:, 0] >> 32)
-        bad += (pk[local].to(torch.int64) != q[:, 1]).sum()
+        bad += (_keys_at(data["probe"], lpos(q[:, 0], nc_p)) != q[:, 1]).sum()
         k = sample
     if world > 1:
         dist.all_reduce(got)
@@ -457,6 +508,9 @@ def main():
                    "build_probe": n_local * t_real + info.n_rows * 16}
     phase_kernel = {"materialize": "k_materialize_hist", "scatter1": "k_scatter1", "scatter2": "k_scatter2",
                     "build_probe": "k_build_probe"}
+    xpath = int(phase_ms[-1].get("xchg_path", 0))  # 0 single GPU, 1 general exchange, 2 push exchange
+    if xpath == 2:
+        w_in = t_real  # the local join's pass 1 reads the finished tuples the exchange delivered, not the columns
     if mean_ms["scatter1"] < 0.05 * mean_ms["scatter2"]:
         # default two-pass path (hj_fused.cuh): pass 1 runs inside the histogram kernel — the "materialize" phase reads the
         # input and writes the slab-local tuples, there is no separate scatter1 kernel, pass 2 gathers fragments
@@ -489,10 +543,13 @@ def main():
                 "phase_ms": mean_ms}
     if world > 1:
         sent = float(np.mean([t["bytes_nvlink_sent"] for t in phase_ms]))
-        xms = mean_ms["xchg_transfer"]
+        xms = mean_ms["xchg_transfer"] + (mean_ms["xchg_partition"] if xpath == 2 else 0.0)
         roofline["nvlink"] = {"bytes_sent_per_rank": sent, "transfer_ms": xms, "achieved": sent / (xms * 1e-3) / 1e9 if xms else None,
-                              "peak": 900.0, "unit": "GB/s per direction",
-                              "note": "transfer_ms also contains the probe side's destination scatter kernel"}
+                              "peak": 900.0, "unit": "GB/s per direction", "frac": sent / (xms * 1e-3) / 1e9 / 900.0 if xms else None,
+                              "exchange": {1: "general (count sweep + RowID-carrying tuples, hj_comm.cuh)",
+                                           2: "push (one sweep, finished tuples stored into peer regions, hj_xpush.cuh)"}.get(xpath),
+                              "note": "transfer_ms is the exchange kernels' time: decode + hash + staging + NVLink stores, "
+                                      "both relations (push), or the probe side's scatter (general)"}
 
     # ---- the last timed step's PosLists are still in HBM: check them (outside the timed region, every N)
     verified = None

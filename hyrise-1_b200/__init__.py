@@ -423,7 +423,7 @@ class HashJoin:
         self._check(self._l.hj_get_timings(self._ctx, C.byref(t)))
         d = {name: t.ms[i] for i, name in enumerate(abi.PHASES)}
         d.update(bytes_h2d=t.bytes_h2d, bytes_d2h=t.bytes_d2h, n_kernel_launches=t.n_kernel_launches,
-                 bytes_nvlink_sent=t.bytes_nvlink_sent)
+                 bytes_nvlink_sent=t.bytes_nvlink_sent, xchg_path=t.xchg_path)
         return d
 
     def release_scratch(self):

@@ -15,6 +15,7 @@ FLAG_SQL_NULL_PROBE = 0x1
 FLAG_TIMINGS = 0x2
 FLAG_XCHG_STAGED = 0x4
 FLAG_TWO_SWEEP_PARTITION = 0x8
+FLAG_XCHG_GENERAL = 0x10
 INVALID_CHUNK_ID = 0xFFFFFFFF
 INVALID_CHUNK_OFFSET = 0xFFFFFFFF
 N_PHASES = 10
@@ -92,7 +93,7 @@ SCAN_VALUE_IS_DOUBLE = 0x2
 
 class Timings(C.Structure):
     _fields_ = [("ms", C.c_float * N_PHASES), ("bytes_h2d", C.c_uint64), ("bytes_d2h", C.c_uint64),
-                ("n_kernel_launches", C.c_uint32), ("reserved", C.c_uint32), ("bytes_nvlink_sent", C.c_uint64)]
+                ("n_kernel_launches", C.c_uint32), ("xchg_path", C.c_uint32), ("bytes_nvlink_sent", C.c_uint64)]
 
 
 # every symbol include/hj.h declares: name -> (restype, argtypes)

@@ -170,6 +170,12 @@ struct hj_ctx {
   uint32_t scan_chunks[HJ_SCAN_SLOTS] = {};
   bool scan_valid[HJ_SCAN_SLOTS] = {};
   const uint64_t* xchg_rowids[kSides] = {};  // set while hj_join_sharded runs its local join
+  // push exchange (hj_xpush.cuh): while set for a side, prepare_relation describes that relation's segments as receive
+  // regions (segment i = the rows sent by rank i)
+  struct XpRegion { const uint32_t* fill = nullptr; const uint32_t* nchunks = nullptr; uint32_t cap_chunks = 0; };
+  XpRegion xp_region[kSides];
+  XchMap xp_map[2] = {};
+  DevBuf xp_cursor;
   uint64_t xchg_bytes_sent[2] = {0, 0};
 
   hj_ctx() {
@@ -181,7 +187,7 @@ struct hj_ctx {
                       &xchg_send_keys[1], &xchg_send_rids[0], &xchg_send_rids[1], &xchg_send_nulls[0], &xchg_send_nulls[1],
                       &xchg_recv_keys[0], &xchg_recv_keys[1], &xchg_recv_rids[0], &xchg_recv_rids[1], &xchg_recv_nulls[0],
                       &xchg_recv_nulls[1], &xchg_recv_keys[2], &xchg_recv_rids[2], &xchg_recv_nulls[2], &acc_build, &acc_probe, &ref_arena[0], &ref_arena[1], &ref_out[0], &ref_out[1],
-                      &xchg_hdl_dev, &scan_bounds, &scan_mask, &scan_tile_count, &scan_tile_base, &scan_ref_ptrs, &scan_totals, &agg_partials, &group_table, &group_out, &group_misc})
+                      &xchg_hdl_dev, &xp_cursor, &scan_bounds, &scan_mask, &scan_tile_count, &scan_tile_base, &scan_ref_ptrs, &scan_totals, &agg_partials, &group_table, &group_out, &group_misc})
       all_bufs.push_back(b);
     for (int i = 2; i < 2 + HJ_GATHER_SLOTS; ++i) {
       all_bufs.push_back(&ref_arena[i]);
@@ -361,6 +367,12 @@ int prepare_relation(hj_ctx* ctx, const hj_relation* r, int side, uint32_t tile,
     if (ctx->xchg_rowids[side]) {  // local join of hj_join_sharded: the rows carry their RowIDs
       d.kind = kSegExchanged;
       d.attr = ctx->xchg_rowids[side];
+    }
+    if (ctx->xp_region[side].fill) {  // push exchange: segment i = the receive region of source rank i
+      d.kind = kSegExch8;
+      d.chunk_id = i;
+      d.attr = ctx->xp_region[side].fill + size_t(i) * ctx->xp_region[side].cap_chunks;
+      d.row_offsets = ctx->xp_region[side].nchunks + i;
     }
     d.key_type = s.key_type;
     d.attr_width = s.attr_width;
@@ -740,6 +752,7 @@ struct PartState {
   uint32_t G = 0;      // virtual CTAs of K1 / pass 1
   bool fused = false;  // hj_fused.cuh: slab-local pass 1 inside the histogram kernel, fragment-gathering pass 2
   uint32_t gs = 0;     // fused: slabs per pass-2 work item
+  bool xch = false;    // fused over push-exchanged tuples: k_part1p<XCH>, prehashed int32 tuples in pass 2
 };
 
 // P1's dynamic shared memory: the full-resolution histogram + per virtual CTA one staging tile (k_part1) or two key
@@ -764,6 +777,7 @@ int stage_alloc(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, in
   ps->G = std::max<uint32_t>(1, std::min<uint32_t>(pr.meta.n_tiles, uint32_t(kVirtualCtasPerSm) * ctx->n_sms));
   ps->G = (ps->G + kHistVirtual - 1) / kHistVirtual * kHistVirtual;  // K1 hosts kHistVirtual virtual CTAs per physical CTA
   ps->fused = use_fused<PAY>(ctx, bits2, side);
+  ps->xch = ps->fused && ctx->xp_region[side].fill != nullptr;
   if (ps->fused) {
     // an item gathers gs fragments of p1_tile/F1 tuples on average: HJ_TUNE_P2_FILL16/16 = 7/8 of a pass-2 batch (k_scatter2f needs gs < its CTA size and keeps fragment owners in 8 bits)
     ps->gs = std::min<uint32_t>(std::min(kP2Threads - 1, 255), std::max<uint64_t>(1, uint64_t(p2_tile<K>()) * HJ_TUNE_P2_FILL16 / 16 * F1 / p1_tile<K>()));
@@ -791,6 +805,25 @@ int stage_hist(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int
   auto* hist = static_cast<uint32_t*>(ctx->hist[side].p);
   auto* hist1 = static_cast<uint32_t*>(ctx->hist1[side].p);
   HJ_CUDA(ctx, cudaMemsetAsync(hist, 0, (size_t(P) + 1) * 4, st));
+  if (ps.fused && ps.xch) {
+    if (pr.meta.n_tiles) {
+      constexpr int VC = sizeof(K) == 4 ? 2 : 1;  // two key buffers per virtual CTA + a histogram of up to 2^15 bins in 227 KB
+      auto k = k_part1p<K, kHistThreads, VC, p1_tile<K>(), true>;
+      const size_t smem = ((((size_t(1) << radix_bits) + 1) * 4 + 15) & ~size_t(15)) + size_t(VC) * p1_tile<K>() * (2 * sizeof(Tuple<K, false>) + 2);
+      HJ_TRY(set_smem(ctx, k, smem));
+      const uint32_t grid = std::min<uint32_t>((pr.meta.n_tiles + VC - 1) / VC, ctx->n_sms);
+      k<<<grid, kHistThreads, smem, st>>>(pr.meta, static_cast<Tuple<K, false>*>(ctx->tup_a[side].p),
+                                          static_cast<uint16_t*>(ctx->frag[side].p), hist, radix_bits, bits2, null_policy);
+      HJ_LAUNCH_CHECK(ctx, "k_part1p<XCH>");
+      nl->n++;
+    }
+    k_offsets<1024><<<1, 1024, 0, st>>>(hist, static_cast<uint32_t*>(ctx->part_off[side].p),
+                                        static_cast<uint32_t*>(ctx->cur2[side].p),
+                                        static_cast<uint32_t*>(ctx->l1_tiles[side].p), radix_bits, bits2, tile2<K>());
+    HJ_LAUNCH_CHECK(ctx, "k_offsets");
+    nl->n++;
+    return HJ_OK;
+  }
   if (ps.fused) {
     if (pr.meta.n_tiles) {
       constexpr int VC = Cfg<K>::kP1Virtual;
@@ -878,9 +911,11 @@ int stage_pass2(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, in
   if constexpr (!PAY) {
     if (ps.fused) {
       constexpr int NT = kP2Threads;
-      auto k = k_scatter2f<K, NT, Cfg<K>::kP2Items, kP2MinBlocks>;
+      auto k = ps.xch ? k_scatter2f<K, NT, Cfg<K>::kP2Items, kP2MinBlocks, sizeof(K) == 4>
+                      : k_scatter2f<K, NT, Cfg<K>::kP2Items, kP2MinBlocks, false>;
       const size_t smem = size_t(p2_tile<K>()) * sizeof(Tuple<K, false>);
-      HJ_TRY(set_smem(ctx, k, smem));
+      HJ_TRY(set_smem(ctx, k_scatter2f<K, NT, Cfg<K>::kP2Items, kP2MinBlocks, false>, smem));
+      if (ps.xch) HJ_TRY(set_smem(ctx, k_scatter2f<K, NT, Cfg<K>::kP2Items, kP2MinBlocks, sizeof(K) == 4>, smem));
       const uint32_t F1 = (1u << radix_bits) >> bits2;
       const uint32_t n_digits = F1 + (null_policy == kNullRoute ? 1u : 0u);
       const uint64_t grid = uint64_t((pr.meta.n_tiles + ps.gs - 1) / ps.gs) * n_digits;
@@ -951,7 +986,7 @@ int launch_build_probe(hj_ctx* ctx, const JoinArgs<K, PAY>& a, cudaStream_t st) 
 // pinned Readback area.
 template <typename K, bool PAY>
 int probe_phase(hj_ctx* ctx, const PreparedRel& pb, const PreparedRel& pp, const PartState& pst, int sb, int sp, int oset,
-                int radix_bits, int bits2, int mode, int probe_null_policy, bool payload, uint64_t n_build_rows,
+                int radix_bits, int bits2, int mode, int probe_null_policy, int payload, uint64_t n_build_rows,
                 uint64_t n_probe_rows, cudaStream_t st, Launches* nl, int* passes_out, cudaEvent_t ev_probe,
                 cudaEvent_t ev_end) {
   const bool one_side = mode == HJ_MODE_SEMI || mode == HJ_MODE_ANTI;
@@ -1009,7 +1044,10 @@ int probe_phase(hj_ctx* ctx, const PreparedRel& pb, const PreparedRel& pp, const
   a.matched = static_cast<uint32_t*>(ctx->matched.p);
   a.radix_bits = radix_bits;
   a.mode = mode;
-  a.payload = payload ? 1 : 0;
+  a.payload = payload;  // 0: positions, 1: tuples carry RowIDs (general exchange), 2: (rank, position) (push exchange)
+  a.bits2 = bits2;
+  a.xmap[0] = ctx->xp_map[0];
+  a.xmap[1] = ctx->xp_map[1];
   const bool fast_rowid = pb.meta.uniform_shift >= 0 && pb.meta.identity && pp.meta.uniform_shift >= 0 && pp.meta.identity;
 
   auto* rb = static_cast<Readback*>(ctx->pinned);
@@ -1029,7 +1067,10 @@ int probe_phase(hj_ctx* ctx, const PreparedRel& pb, const PreparedRel& pp, const
     HJ_CUDA(ctx, cudaMemsetAsync(ctx->queue.p, 0, 4, st));
     HJ_CUDA(ctx, cudaMemsetAsync(ctx->out_state.p, 0, sizeof(OutState), st));
     if (mode != HJ_MODE_INNER) HJ_CUDA(ctx, cudaMemsetAsync(ctx->matched.p, 0, matched_bytes, st));
-    if (payload) {
+    if (payload == 2) {
+      if constexpr (!PAY) HJ_TRY((launch_build_probe<K, PAY, kRidXch>(ctx, a, st)));
+      else return fail(ctx, HJ_ERR_INVALID, "push-exchanged tuples are position tuples");
+    } else if (payload) {
       if constexpr (sizeof(Tuple<K, PAY>) > 8) HJ_TRY((launch_build_probe<K, PAY, kRidPayload>(ctx, a, st)));
       else return fail(ctx, HJ_ERR_INVALID, "RowID-carrying tuples need a tuple type with a payload");
     } else if constexpr (PAY) {
@@ -1113,7 +1154,7 @@ int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, in
   HJ_TRY(stage_pass2<K, PAY>(ctx, pp, 1, radix_bits, bits2, probe_null_policy, sp, st, &nl));
   HJ_CUDA(ctx, cudaEventRecord(ev[4], st));
   int passes = 0;
-  HJ_TRY((probe_phase<K, PAY>(ctx, pb, pp, sp, 0, 1, 0, radix_bits, bits2, mode, probe_null_policy, payload, build->n_rows,
+  HJ_TRY((probe_phase<K, PAY>(ctx, pb, pp, sp, 0, 1, 0, radix_bits, bits2, mode, probe_null_policy, payload ? 1 : 0, build->n_rows,
                               probe->n_rows, st, &nl, &passes, ev[5], ev[6])));
   auto* rb = static_cast<Readback*>(ctx->pinned);
   ctx->has_result = true;
@@ -2337,4 +2378,4 @@ int hj_get_timings(const hj_ctx* ctx, hj_timings* out) {
 }  // extern "C"
 
 // ============================================================================================================= multi-GPU
-#include "hj_comm.cuh"
+#include "hj_comm.cuh"  // includes hj_xpush.cuh

@@ -401,24 +401,35 @@ void close_peer_maps(hj_ctx* ctx) {
 }
 
 // All ranks publish the IPC handles of their receive buffers; every rank maps what changed. Collective.
-int exchange_handles(hj_ctx* ctx, cudaStream_t st) {
+// local_status: what this rank's preparations (allocations) returned; every rank learns every rank's status in the same
+// all-gather, so that all of them leave the join together instead of one returning early and the others hanging in the next
+// collective. Returns HJ_ERR_COMM when a PEER failed (this rank's own error is already in hj_last_error).
+int exchange_handles(hj_ctx* ctx, cudaStream_t st, int local_status = HJ_OK) {
   NcclApi* nc = nccl_api();
   const uint32_t R = ctx->n_ranks, me = ctx->rank;
   HJ_TRY(ensure(ctx, ctx->xchg_hdl_dev, sizeof(HandleRec) * (1 + kMaxRanks)));
   auto* dev = static_cast<HandleRec*>(ctx->xchg_hdl_dev.p);
   auto* host = reinterpret_cast<HandleRec*>(static_cast<char*>(ctx->pinned) + kPinnedHandles);  // [0] mine, [1..R] everybody's
   std::memset(&host[0], 0, sizeof(HandleRec));
-  for (int side = 0; side < 3; ++side)
+  host[0].pad[0] = static_cast<uint8_t>(local_status);
+  for (int side = 0; side < 3 && local_status == HJ_OK; ++side)
     for (int kind = 0; kind < 3; ++kind) {
       DevBuf* b = xchg_recv_buf(ctx, side, kind);
       if (!b->p) continue;
-      HJ_CUDA(ctx, cudaIpcGetMemHandle(&host[0].h[side * 3 + kind], b->p));
+      if (cudaIpcGetMemHandle(&host[0].h[side * 3 + kind], b->p) != cudaSuccess) {
+        (void)cudaGetLastError();
+        host[0].pad[0] = static_cast<uint8_t>(local_status = fail(ctx, HJ_ERR_CUDA, "cudaIpcGetMemHandle failed for receive buffer %d/%d", side, kind));
+        break;
+      }
       host[0].valid[side * 3 + kind] = 1;
     }
   HJ_CUDA(ctx, cudaMemcpyAsync(dev, &host[0], sizeof(HandleRec), cudaMemcpyHostToDevice, st));
   HJ_NCCL(ctx, nc->AllGather(dev, dev + 1, sizeof(HandleRec), ncclUint8, static_cast<ncclComm_t>(ctx->nccl_comm), st));
   HJ_CUDA(ctx, cudaMemcpyAsync(&host[1], dev + 1, sizeof(HandleRec) * R, cudaMemcpyDeviceToHost, st));
   HJ_CUDA(ctx, cudaStreamSynchronize(st));
+  if (local_status != HJ_OK) return local_status;
+  for (uint32_t p = 0; p < R; ++p)
+    if (host[1 + p].pad[0] != HJ_OK) return fail(ctx, HJ_ERR_COMM, "rank %u could not prepare its receive buffers (status %u)", p, host[1 + p].pad[0]);
   for (uint32_t p = 0; p < R; ++p) {
     if (p == me) continue;
     for (int k = 0; k < kXchgBufKinds; ++k) {
@@ -513,16 +524,24 @@ int run_join_sharded(hj_ctx* ctx, const hj_relation* build, const hj_relation* p
   if (direct) {
     // ---- X3 stores straight into the peers' receive buffers (CUDA IPC mappings over NVLink): no send buffers, no NCCL
     // copy; the only collectives are the count all-gather above, the handle all-gather and a 1-word barrier.
-    for (int side = 0; side < 2; ++side) {
-      for (uint32_t p = 0; p < R; ++p) n_recv[side] += cnt(p, side, me);
-      if (n_recv[side] >= 0xFFFFFFFFull)
-        return fail(ctx, HJ_ERR_TOO_LARGE, "rank %u would receive %llu %s rows (limit 2^32-2 per GPU)", me,
-                    (unsigned long long)n_recv[side], side ? "probe" : "build");
-      HJ_TRY(ensure_exported(ctx, ctx->xchg_recv_keys[side], std::max<uint64_t>(1, n_recv[side]) * sizeof(K)));
-      HJ_TRY(ensure_exported(ctx, ctx->xchg_recv_rids[side], std::max<uint64_t>(1, n_recv[side]) * 8));
-      if (xs[side].send_nulls) HJ_TRY(ensure_exported(ctx, ctx->xchg_recv_nulls[side], std::max<uint64_t>(1, n_recv[side])));
+    // every rank holds the whole count matrix: the "too large" verdict is computed for ALL ranks, so all fail identically
+    for (int side = 0; side < 2; ++side)
+      for (uint32_t r = 0; r < R; ++r) {
+        uint64_t n = 0;
+        for (uint32_t p = 0; p < R; ++p) n += cnt(p, side, r);
+        if (r == me) n_recv[side] = n;
+        if (n >= 0xFFFFFFFFull)
+          return fail(ctx, HJ_ERR_TOO_LARGE, "rank %u would receive %llu %s rows (limit 2^32-2 per GPU)", r,
+                      (unsigned long long)n, side ? "probe" : "build");
+      }
+    // allocations are rank-local: their status travels with the handle all-gather, so that no rank is left waiting
+    int local = HJ_OK;
+    for (int side = 0; side < 2 && local == HJ_OK; ++side) {
+      local = ensure_exported(ctx, ctx->xchg_recv_keys[side], std::max<uint64_t>(1, n_recv[side]) * sizeof(K));
+      if (local == HJ_OK) local = ensure_exported(ctx, ctx->xchg_recv_rids[side], std::max<uint64_t>(1, n_recv[side]) * 8);
+      if (local == HJ_OK && xs[side].send_nulls) local = ensure_exported(ctx, ctx->xchg_recv_nulls[side], std::max<uint64_t>(1, n_recv[side]));
     }
-    HJ_TRY(exchange_handles(ctx, st));
+    HJ_TRY(exchange_handles(ctx, st, local));
     for (int side = 0; side < 2; ++side) {
       uint64_t n_send = 0;
       if (xs[side].pr.meta.n_tiles) {
@@ -652,6 +671,7 @@ int run_join_sharded(hj_ctx* ctx, const hj_relation* build, const hj_relation* p
   t.ms[HJ_PH_XCHG_TRANSFER] = ev_ms(ev[10], ev[11]);   // build all-to-all, probe X3, probe all-to-all
   t.ms[HJ_PH_TOTAL] += ev_ms(ev[9], ev[11]);
   t.n_kernel_launches += n_launch;
+  t.xchg_path = 1;
   t.bytes_nvlink_sent = ctx->xchg_bytes_sent[0] + ctx->xchg_bytes_sent[1];
   return HJ_OK;
 }
@@ -941,11 +961,14 @@ int run_join_sharded_sliced(hj_ctx* ctx, const hj_relation* build, const hj_rela
   t.ms[HJ_PH_XCHG_TRANSFER] = ev_ms(ev[10], ev[11]);  // probe slices' X3 (overlaps the local joins of the earlier slices)
   t.ms[HJ_PH_TOTAL] = ev_ms(ev[9], ev[6]);
   t.n_kernel_launches = nl.n + n_launch;
+  t.xchg_path = 1;
   t.bytes_nvlink_sent = bytes_sent;
   return HJ_OK;
 }
 
 }  // namespace
+
+#include "hj_xpush.cuh"  // the push exchange: uses the IPC plumbing above, dispatched by hj_join_sharded below
 
 extern "C" {
 
@@ -1003,7 +1026,8 @@ int hj_join_sharded(hj_ctx* ctx, const hj_relation* build_shard, const hj_relati
     return fail(ctx, HJ_ERR_INVALID, "hj_join_sharded: float/double keys are joined by hj_join only");
   RefRewrite rw[2];  // REFERENCE / FOR / RLE segments -> gathered or decoded on the device (N1, N2)
   HJ_TRY(gather_both(ctx, build_shard, probe_shard, st, rw, hashed_type_of(build_shard, probe_shard)));
-  // the hashed key type must be the same on every rank (the destination of a key depends on it): all-gather "I hold int64"
+  // One all-gather tells every rank what the others hold: the hashed key type must be the same everywhere (the destination
+  // of a key depends on it), the probe rows decide about slicing, and the shard geometry about the push exchange.
   unsigned long long wide = 0;
   for (const hj_relation* r : {build_shard, probe_shard})
     for (uint32_t i = 0; i < r->n_segs; ++i) wide |= r->segs[i].key_type == HJ_KEY_INT64 ? 1ull : 0ull;
@@ -1011,21 +1035,48 @@ int hj_join_sharded(hj_ctx* ctx, const hj_relation* build_shard, const hj_relati
   auto* dev = static_cast<unsigned long long*>(ctx->xchg_cnt_dev.p);
   auto* host = reinterpret_cast<unsigned long long*>(static_cast<char*>(ctx->pinned) + kPinnedCounts);
   NcclApi* nc = nccl_api();
-  unsigned long long word = (static_cast<unsigned long long>(probe_shard->n_rows) << 1) | wide;  // + my probe rows (slicing)
-  HJ_CUDA(ctx, cudaMemcpyAsync(dev, &word, 8, cudaMemcpyHostToDevice, st));
-  HJ_NCCL(ctx, nc->AllGather(dev, dev + kMaxRanks, 1, ncclUint64, static_cast<ncclComm_t>(ctx->nccl_comm), st));
-  HJ_CUDA(ctx, cudaMemcpyAsync(host, dev + kMaxRanks, size_t(ctx->n_ranks) * 8, cudaMemcpyDeviceToHost, st));
+  const bool direct = ctx->p2p_ok && !(ctx->opts.flags & HJ_FLAG_XCHG_STAGED);
+  const bool outer_mode = mode == HJ_MODE_LEFT || mode == HJ_MODE_RIGHT;
+  const ShardGeometry gb = shard_geometry(build_shard), gp = shard_geometry(probe_shard);
+  const bool push_here = direct && gb.regular && gp.regular && !(ctx->opts.flags & (HJ_FLAG_XCHG_GENERAL | HJ_FLAG_TWO_SWEEP_PARTITION)) &&
+                         !(outer_mode && (ctx->opts.flags & HJ_FLAG_SQL_NULL_PROBE)) && !ctx->opts.stream_slice_rows;
+  unsigned long long word[kXpDescWords] = {build_shard->n_rows, probe_shard->n_rows,
+                                           gb.first_chunk | (static_cast<unsigned long long>(static_cast<uint32_t>(gb.shift)) << 32),
+                                           gp.first_chunk | (static_cast<unsigned long long>(static_cast<uint32_t>(gp.shift)) << 32),
+                                           wide | (push_here ? 2ull : 0ull), 0, 0, 0};
+  HJ_CUDA(ctx, cudaMemcpyAsync(dev, word, sizeof(word), cudaMemcpyHostToDevice, st));
+  HJ_NCCL(ctx, nc->AllGather(dev, dev + kXpDescWords, kXpDescWords, ncclUint64, static_cast<ncclComm_t>(ctx->nccl_comm), st));
+  std::vector<unsigned long long> desc(size_t(ctx->n_ranks) * kXpDescWords);
+  HJ_CUDA(ctx, cudaMemcpyAsync(host, dev + kXpDescWords, desc.size() * 8, cudaMemcpyDeviceToHost, st));
   HJ_CUDA(ctx, cudaStreamSynchronize(st));
-  for (int r = 0; r < ctx->n_ranks; ++r) wide |= host[r] & 1ull;
+  std::memcpy(desc.data(), host, desc.size() * 8);  // the pinned area is reused by the joins below
+  bool push = true;
+  uint64_t max_probe_rows = 0, total_build = 0;
+  for (int r = 0; r < ctx->n_ranks; ++r) {
+    wide |= desc[size_t(r) * kXpDescWords + 4] & 1ull;
+    push = push && (desc[size_t(r) * kXpDescWords + 4] & 2ull);
+    max_probe_rows = std::max<uint64_t>(max_probe_rows, desc[size_t(r) * kXpDescWords + 1]);
+    total_build += desc[size_t(r) * kXpDescWords + 0];
+  }
+  // Push exchange (hj_xpush.cuh): needs two partitioning passes in the local join — decided from the build rows a rank
+  // expects, the same number on every rank
+  const int xp_bits = ctx->opts.radix_bits >= 0 ? std::min(ctx->opts.radix_bits, kMaxRadixBits)
+                                                : radix_bits_for(total_build / ctx->n_ranks + 1, wide ? HJ_KEY_INT64 : HJ_KEY_INT32);
+  push = push && pass2_bits(xp_bits) > 0 && (1 << (xp_bits - pass2_bits(xp_bits))) >= ctx->n_ranks;
+  if (push) {
+    bool fell_back = false;
+    const int st_push = wide ? run_join_sharded_push<int64_t>(ctx, build_shard, probe_shard, mode, st, out_info, desc.data(), xp_bits, &fell_back)
+                             : run_join_sharded_push<int32_t>(ctx, build_shard, probe_shard, mode, st, out_info, desc.data(), xp_bits, &fell_back);
+    if (st_push != HJ_OK) return st_push;
+    if (!fell_back) return check_reference_flags(ctx, rw);
+    // a receive region overflowed on some rank (skew): every rank saw the flag and repeats the join on the general path
+  }
   // Probe slices (same S on every rank): opt-in through hj_options.stream_slice_rows. Slicing bounds the receive buffers
-  // to two slices (what a 4 B x 4 B join needs to fit), but it is NOT faster: measured on 2 x B200, C2 per rank,
-  // unsliced 54.8 ms, S=2 60.0 ms, S=4 66.4 ms — the persistent X3 CTAs hold their SMs, so the 1024-thread join kernels
-  // of the previous slice wait instead of overlapping, and every slice rebuilds the build-side hash tables.
-  uint64_t max_probe_rows = 0;
-  for (int r = 0; r < ctx->n_ranks; ++r) max_probe_rows = std::max<uint64_t>(max_probe_rows, host[r] >> 1);
+  // to two slices, but it is NOT faster: measured on 2 x B200, C2 per rank, unsliced 54.8 ms, S=2 60.0 ms, S=4 66.4 ms —
+  // the persistent X3 CTAs hold their SMs, so the 1024-thread join kernels of the previous slice wait instead of
+  // overlapping, and every slice rebuilds the build-side hash tables.
   const uint32_t S = ctx->opts.stream_slice_rows
                          ? uint32_t(std::min<uint64_t>(kMaxXchgSlices, max_probe_rows / ctx->opts.stream_slice_rows)) : 1u;
-  const bool direct = ctx->p2p_ok && !(ctx->opts.flags & HJ_FLAG_XCHG_STAGED);
   int status;
   if (direct && S >= 2)
     status = wide ? run_join_sharded_sliced<int64_t>(ctx, build_shard, probe_shard, mode, st, out_info, S)

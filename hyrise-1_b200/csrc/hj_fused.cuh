@@ -251,8 +251,14 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-constexpr uint8_t kSegExch8 = 14;  // internal: finished tuples received from the exchange (hj_comm.cuh); chunk_id = source rank,
-                                   // null_value_id != 0: every row of the segment is a routed NULL probe row
+constexpr uint8_t kSegExch8 = 14;  // internal: a receive region of the push exchange (hj_xpush.cuh): values = tuples, chunk_id =
+                                   // source rank, attr = per-chunk fill counts, row_offsets = &number of chunks in use
+
+// rows of tile t (0-based inside its segment): a receive region is a row of 2048-tuple chunks, of which the first *nchunks
+// (the word `row_offsets` points at) are in use, filled to fill[t] tuples (`attr`)
+__device__ __forceinline__ uint32_t exch_tile_rows(const DevSegment& s, uint32_t t) {
+  return t < __ldcg(s.row_offsets) ? __ldcg(static_cast<const uint32_t*>(s.attr) + t) : 0u;
+}
 
 template <typename K, bool XCH> struct P1Elem { using type = K; };
 template <typename K> struct P1Elem<K, true> { using type = Tuple<K, false>; };
@@ -301,7 +307,7 @@ __global__ void __launch_bounds__(NT) k_part1p(RelMeta rel, Tuple<K, false>* __r
     if (tile < rel.n_tiles) {
       const DevSegment s = rel.segs[__ldg(rel.tile_seg + tile)];
       const uint32_t r0 = (tile - s.tile_begin) * TILE;
-      const uint32_t cnt = min(static_cast<uint32_t>(TILE), s.n_rows - r0);
+      const uint32_t cnt = XCH ? exch_tile_rows(s, tile - s.tile_begin) : min(static_cast<uint32_t>(TILE), s.n_rows - r0);
       if constexpr (XCH) {
         const E* src = static_cast<const E*>(s.values) + r0;
 #pragma unroll
@@ -309,7 +315,7 @@ __global__ void __launch_bounds__(NT) k_part1p(RelMeta rel, Tuple<K, false>* __r
           const uint32_t i = u * VT + vt;
           if (i < cnt) cp_async_small<sizeof(E)>(kb + i, src + i);
         }
-        vbits = s.null_value_id ? 0u : 0xFFFFFFFFu;
+        vbits = 0xFFFFFFFFu;  // NULL rows never travel (kNullDrop) or travel as their value (kNullAsValue)
       } else {
         const bool narrow = sizeof(K) == 8 && s.key_type == 0;  // int32 chunk of an int64 join: widened by hand
 #pragma unroll
@@ -343,7 +349,7 @@ __global__ void __launch_bounds__(NT) k_part1p(RelMeta rel, Tuple<K, false>* __r
 
     const DevSegment s = rel.segs[__ldg(rel.tile_seg + tile)];
     const uint32_t r0 = (tile - s.tile_begin) * TILE;
-    const uint32_t cnt = min(static_cast<uint32_t>(TILE), s.n_rows - r0);
+    const uint32_t cnt = XCH ? exch_tile_rows(s, tile - s.tile_begin) : min(static_cast<uint32_t>(TILE), s.n_rows - r0);
     E* kb = kbuf + b * TILE;
     uint32_t packed[ITEMS];  // digit << 16 | rank inside the digit, or kNoDigit
 #pragma unroll
@@ -404,7 +410,10 @@ __global__ void __launch_bounds__(NT) k_part1p(RelMeta rel, Tuple<K, false>* __r
         T t;
         if constexpr (XCH) {
           t = kb[r];
-          if constexpr (sizeof(K) == 8) t.pad = s.chunk_id;  // source rank (the exchange kernel leaves it to the segment)
+          // the source rank (= the receive region, chunk_id): int64 tuples have a spare word; an int32 tuple's key field is
+          // the key's hash, whose level-1 digit bits are redundant from here on (this fragment IS that digit)
+          if constexpr (sizeof(K) == 8) t.pad = s.chunk_id;
+          else t.key = static_cast<K>((static_cast<uint32_t>(t.key) & ~(((1u << (radix_bits - bits2)) - 1u) << bits2)) | (s.chunk_id << bits2));
         } else {
           t.key = kb[r];
           t.idx = idx0 + r;
@@ -433,7 +442,7 @@ __global__ void __launch_bounds__(NT) k_part1p(RelMeta rel, Tuple<K, false>* __r
 // d1 == F1 (only with kNullRoute): the routed NULL probe rows, copied behind the last partition (part_off[P]).
 // dynamic smem: TILE * sizeof(Tuple<K>).
 // =====================================================================================================================
-template <typename K, int NT, int ITEMS, int MINB>
+template <typename K, int NT, int ITEMS, int MINB, bool PRE = false>
 __global__ void __launch_bounds__(NT, MINB) k_scatter2f(const Tuple<K, false>* __restrict__ in, const uint16_t* __restrict__ frag,
                                                             RelMeta rel, uint32_t tile1, Tuple<K, false>* __restrict__ out,
                                                             uint32_t* __restrict__ cur2, int radix_bits, int bits2, uint32_t gs,
@@ -518,7 +527,7 @@ __global__ void __launch_bounds__(NT, MINB) k_scatter2f(const Tuple<K, false>* _
       const uint32_t i = j * NT + threadIdx.x;
       packed[j] = kNoDigit;
       if (i < n_in) {
-        const uint32_t d = hash_key(tup[j].key) & (F2 - 1u);
+        const uint32_t d = tuple_hash<PRE>(tup[j].key) & (F2 - 1u);
         packed[j] = (d << 16) | atomicAdd(&s_cnt[d], 1u);
       }
     }
@@ -539,7 +548,7 @@ __global__ void __launch_bounds__(NT, MINB) k_scatter2f(const Tuple<K, false>* _
       if (packed[j] != kNoDigit) stage[s_loff[packed[j] >> 16] + (packed[j] & 0xFFFFu)] = tup[j];
     }
     __syncthreads();
-    copy_tile_out<K, false, NT, ITEMS>(stage, s_delta, out, n_in, F2 - 1u, 0, 0xFFFFFFFFu, 0u);
+    copy_tile_out<K, false, NT, ITEMS, PRE>(stage, s_delta, out, n_in, F2 - 1u, 0, 0xFFFFFFFFu, 0u);
   }
 }
 

@@ -262,7 +262,14 @@ constexpr uint32_t kNoDigit = 0xFFFFFFFFu;
 // digit's run is contiguous, so the stores coalesce per run), re-derive the digit from the key and add the digit's
 // (global - staged) delta, with no per-run control flow and no per-tuple destination array in shared memory. v1 copied run by run (a warp per digit) and spent ~120 thread-instructions per tuple on loop
 // overhead for the ~32-tuple runs (profiles/r01_ncu_v1_c2_full_summary.md).
-template <typename K, bool PAY, int NT, int ITEMS>
+// PRE: the key field of an int32 tuple already IS the hash (tuples that came through the multi-GPU push exchange)
+template <bool PRE, typename K>
+__device__ __forceinline__ uint32_t tuple_hash(K key) {
+  if constexpr (PRE && sizeof(K) == 4) return static_cast<uint32_t>(key);
+  else return hash_key(key);
+}
+
+template <typename K, bool PAY, int NT, int ITEMS, bool PRE = false>
 __device__ __forceinline__ void copy_tile_out(const Tuple<K, PAY>* stage, const uint32_t* s_delta, Tuple<K, PAY>* out, uint32_t n,
                                               uint32_t dmask, int shift, uint32_t null_start, uint32_t null_digit) {
 #pragma unroll
@@ -270,7 +277,7 @@ __device__ __forceinline__ void copy_tile_out(const Tuple<K, PAY>* stage, const 
     const uint32_t i = j * NT + threadIdx.x;
     if (i < n) {
       const Tuple<K, PAY> t = stage[i];
-      const uint32_t d = i >= null_start ? null_digit : (hash_key(t.key) & dmask) >> shift;
+      const uint32_t d = i >= null_start ? null_digit : (tuple_hash<PRE>(t.key) & dmask) >> shift;
       out[s_delta[d] + i] = t;  // s_delta[d] = global index of the digit's run - its offset in the staged tile (mod 2^32)
     }
   }
@@ -680,6 +687,18 @@ __device__ __forceinline__ void out_writer_finish(const OutWriter* w, OutState* 
 // expanded by its whole warp.
 // block: NT threads (1 CTA/SM), dynamic smem: (NS+1)*sizeof(K) + (NS+2)*4 + CAP*4.
 // =====================================================================================================================
+// Tuples that came through the multi-GPU push exchange (hj_xpush.cuh) name their row as (source rank, position in that
+// rank's shard). Shards that take this path are regular — chunks of 2^shift rows (the last one may be shorter) with
+// consecutive chunk ids — so the RowID is a shift, a mask and an add.
+struct XchMap {
+  uint32_t first_chunk[16];
+  int32_t shift[16];
+};
+__device__ __forceinline__ uint64_t xch_rowid(const XchMap& m, uint32_t rank, uint32_t pos) {
+  const int sh = m.shift[rank & 15u];
+  return pack_rowid(m.first_chunk[rank & 15u] + (pos >> sh), pos & ((1u << sh) - 1u));
+}
+
 template <typename K, bool PAY>
 struct JoinArgs {
   const Tuple<K, PAY>* build;
@@ -697,8 +716,18 @@ struct JoinArgs {
   int radix_bits;
   int mode;                            // hj_join_mode
   int chunk_shift;                     // result chunks are 2^chunk_shift rows
-  int payload;                         // 1: tuples carry their RowID (idx, pad) — local join of hj_join_sharded
+  int payload;                         // 1: tuples carry their RowID (idx, pad) — local join of hj_join_sharded; 2: (rank, position)
+  int bits2;                           // payload 2, int32 keys: the source rank sits in hash bits [bits2, radix_bits)
+  XchMap xmap[2];                      // payload 2: [0] build side, [1] probe side
 };
+
+// source rank of a push-exchanged tuple: int64 tuples carry it in `pad`, int32 tuples in the level-1 digit bits of their
+// hash (redundant once pass 1 has grouped by them)
+template <typename K, bool PAY>
+__device__ __forceinline__ uint32_t xch_rank(const Tuple<K, PAY>& t, int bits2, int radix_bits) {
+  if constexpr (sizeof(K) == 8) return t.pad;
+  else return (static_cast<uint32_t>(t.key) >> bits2) & ((1u << (radix_bits - bits2)) - 1u);
+}
 
 template <typename K> struct KeyTraits;
 template <> struct KeyTraits<int32_t> { static constexpr int32_t kEmpty = INT32_MIN; };
@@ -809,7 +838,8 @@ __device__ __forceinline__ uint32_t table_find_first(const K* keys, K key, uint3
 //   kRidGeneric  position -> RowID through the relation's chunk table (make_rowid)
 //   kRidFast     both relations have power-of-two chunks and identity chunk ids: shift/mask
 //   kRidPayload  the tuple carries the RowID itself (idx = ChunkID, pad = ChunkOffset); int64-key tuples only
-constexpr int kRidGeneric = 0, kRidFast = 1, kRidPayload = 2;
+//   kRidXch      the tuple names its row as (source rank, position in that rank's shard): push exchange (xch_rowid)
+constexpr int kRidGeneric = 0, kRidFast = 1, kRidPayload = 2, kRidXch = 3;
 template <int RM>
 __device__ __forceinline__ uint64_t rowid_of(const RelMeta& m, uint32_t idx) {
   if (RM == kRidFast) return pack_rowid(idx >> m.uniform_shift, idx & ((1u << m.uniform_shift) - 1u));
@@ -822,6 +852,12 @@ __device__ __forceinline__ uint32_t tuple_hi(const Tuple<K, PAY>& t) {
 template <typename K, bool PAY>
 __device__ __forceinline__ uint64_t tuple_rowid(const RelMeta& m, const Tuple<K, PAY>& t, int payload) {
   return payload ? pack_rowid(t.idx, tuple_hi(t)) : make_rowid(m, t.idx);
+}
+// probe-side RowID of a tuple in any of the three tuple flavours (K6, K7)
+template <typename K, bool PAY>
+__device__ __forceinline__ uint64_t probe_rowid(const JoinArgs<K, PAY>& a, const Tuple<K, PAY>& t) {
+  if (a.payload == 2) return xch_rowid(a.xmap[1], xch_rank<K, PAY>(t, a.bits2, a.radix_bits), t.idx);
+  return tuple_rowid<K, PAY>(a.probe_rel, t, a.payload);
 }
 
 // Mode classes the probe loop is specialised for (compile time: no per-row mode branches).
@@ -859,14 +895,21 @@ __device__ __forceinline__ void emit_tile(const JoinArgs<K, PAY>& a, const uint3
   // build-side RowID of grouped entry g: s_grp holds relation positions, or (payload mode) positions inside this build
   // chunk, whose tuples (<= CAP x 16 B, read by every probe row of the partition) stay cache-resident
   auto brid = [&](uint32_t g) -> uint64_t {
-    if (RM == kRidPayload) {
+    if constexpr (RM == kRidPayload) {
       const Tuple<K, PAY> t = bchunk[s_grp[g]];
       return pack_rowid(t.idx, tuple_hi(t));
+    } else if constexpr (RM == kRidXch) {
+      const Tuple<K, PAY> t = bchunk[s_grp[g]];
+      return xch_rowid(a.xmap[0], xch_rank<K, PAY>(t, a.bits2, a.radix_bits), t.idx);
+    } else {
+      return rowid_of<RM>(a.build_rel, s_grp[g]);
     }
-    return rowid_of<RM>(a.build_rel, s_grp[g]);
   };
+  // pad: the probe tuple's ChunkOffset (kRidPayload) / source rank (kRidXch)
   auto prid_of = [&](uint32_t idx, uint32_t pad) -> uint64_t {
-    return RM == kRidPayload ? pack_rowid(idx, pad) : rowid_of<RM>(a.probe_rel, idx);
+    if constexpr (RM == kRidPayload) return pack_rowid(idx, pad);
+    else if constexpr (RM == kRidXch) return xch_rowid(a.xmap[1], pad, idx);
+    else return rowid_of<RM>(a.probe_rel, idx);
   };
   const uint32_t lane = lane_id();
   uint32_t heavy = 0;
@@ -927,6 +970,13 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K, PAY> a)
   const uint32_t n_items = a.plan->n_items;
   const int radix_bits = a.radix_bits;
   const int chunk_shift = a.chunk_shift;
+  // push-exchanged int32 tuples: the key field is the key's hash (a bijection of the key) with the source rank written over
+  // the level-1 digit bits; equal keys = equal fields once those bits are forced to one (the partition fixes them anyway)
+  constexpr bool PRE = RM == kRidXch && sizeof(K) == 4;
+  const uint32_t rank_bits = PRE ? ((1u << (radix_bits - a.bits2)) - 1u) << a.bits2 : 0u;
+  auto canon = [&](K k) -> K {
+    if constexpr (PRE) return static_cast<K>(static_cast<uint32_t>(k) | rank_bits); else return k;
+  };
   OutWriter wr;  // every warp is its own result writer (state replicated in the lanes' registers, lane 0 allocates)
   out_writer_init(&wr);
   if (threadIdx.x == 0) s_w[NS + 1] = 0;
@@ -971,14 +1021,14 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K, PAY> a)
 #pragma unroll
       for (int u = 0; u < BU; ++u) {
         const uint32_t i = (r0 + u) * NT + threadIdx.x;
-        bk[u] = i < it.b_cnt ? build[i].key : K(0);
+        bk[u] = i < it.b_cnt ? canon(build[i].key) : K(0);
       }
 #pragma unroll
       for (int u = 0; u < BU; ++u) {
         const uint32_t i = (r0 + u) * NT + threadIdx.x;
         uint32_t slot = NS + 1;
         if (i < it.b_cnt) {
-          slot = table_insert<K, NS>(s_keys, ns_mask, bk[u], table_start<K>(hash_key(bk[u]) >> radix_bits, ns_mask));
+          slot = table_insert<K, NS>(s_keys, ns_mask, bk[u], table_start<K>(tuple_hash<PRE>(bk[u]) >> radix_bits, ns_mask));
           atomicAdd(&s_w[slot], 1u);
         }
         if ((u & 1) == 0) bslot[(r0 + u) / 2] = slot; else bslot[(r0 + u) / 2] |= slot << 16;
@@ -1022,7 +1072,7 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K, PAY> a)
 #pragma unroll
       for (int u = 0; u < BU; ++u) {
         const uint32_t i = (r0 + u) * NT + threadIdx.x;
-        bi[u] = RM == kRidPayload ? i : (i < it.b_cnt ? build[i].idx : 0u);
+        bi[u] = (RM == kRidPayload || RM == kRidXch) ? i : (i < it.b_cnt ? build[i].idx : 0u);
       }
 #pragma unroll
       for (int u = 0; u < BU; ++u) {
@@ -1047,8 +1097,8 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K, PAY> a)
       uint32_t fstart[V], fslot[V];
 #pragma unroll
       for (int j = 0; j < V; ++j) {
-        fstart[j] = table_start<K>(hash_key(nxt[j].key) >> radix_bits, ns_mask);
-        fslot[j] = table_find_first<K, NS>(s_keys, nxt[j].key, fstart[j]);
+        fstart[j] = table_start<K>(tuple_hash<PRE>(nxt[j].key) >> radix_bits, ns_mask);
+        fslot[j] = table_find_first<K, NS>(s_keys, canon(nxt[j].key), fstart[j]);
       }
 #endif
 #pragma unroll
@@ -1056,14 +1106,14 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K, PAY> a)
         const bool act = row0 + j * 32 < it.p_cnt;
         pw[j] = 0;
         pidx[j] = nxt[j].idx;
-        ppad[j] = RM == kRidPayload ? tuple_hi(nxt[j]) : 0u;
+        ppad[j] = RM == kRidPayload ? tuple_hi(nxt[j]) : RM == kRidXch ? xch_rank<K, PAY>(nxt[j], a.bits2, radix_bits) : 0u;
 #if HJ_TUNE_FIND_ILP
         if (act) pw[j] = s_w[fslot[j] != kFindPending ? fslot[j]
-                                 : table_find<K, NS>(s_keys, ns_mask, nxt[j].key, (fstart[j] + kBucketKeys<K>) & ns_mask)];
+                                 : table_find<K, NS>(s_keys, ns_mask, canon(nxt[j].key), (fstart[j] + kBucketKeys<K>) & ns_mask)];
 #else
         if (act) {
-          const K key = nxt[j].key;
-          const uint32_t slot = table_find<K, NS>(s_keys, ns_mask, key, table_start<K>(hash_key(key) >> radix_bits, ns_mask));
+          const K key = canon(nxt[j].key);
+          const uint32_t slot = table_find<K, NS>(s_keys, ns_mask, key, table_start<K>(tuple_hash<PRE>(nxt[j].key) >> radix_bits, ns_mask));
           pw[j] = s_w[slot];
         }
 #endif
@@ -1153,7 +1203,7 @@ __global__ void __launch_bounds__(NT) k_finalize_multi(const JoinArgs<K, PAY> a,
         const uint32_t pos = it.p_begin + i;
         const bool hit = (a.matched[pos >> 5] >> (pos & 31u)) & 1u;
         flag = (mode == 5) ? hit : !hit;  // Semi keeps matched rows; Left/Right/Anti the unmatched ones
-        if (flag) prid = tuple_rowid<K, PAY>(a.probe_rel, a.probe[pos], a.payload);
+        if (flag) prid = probe_rowid<K, PAY>(a, a.probe[pos]);
       }
       emit_flagged<NT>(flag, kNullRowId, prid, a.out_build, a.out_probe, a.capacity, &s_out, a.out_state, scratch, a.chunk_shift);
     }
@@ -1174,7 +1224,7 @@ __global__ void __launch_bounds__(NT) k_emit_null_probe(const JoinArgs<K, PAY> a
   for (uint32_t base = lo + blockIdx.x * NT; base < hi; base += gridDim.x * NT) {
     const uint32_t i = base + threadIdx.x;
     const bool flag = i < hi;
-    const uint64_t prid = flag ? tuple_rowid<K, PAY>(a.probe_rel, pass1[i], a.payload) : 0;
+    const uint64_t prid = flag ? probe_rowid<K, PAY>(a, pass1[i]) : 0;
     emit_flagged<NT>(flag, kNullRowId, prid, a.out_build, a.out_probe, a.capacity, &s_out, a.out_state, scratch, a.chunk_shift);
   }
   if (threadIdx.x == 0) out_writer_finish(&s_out, a.out_state, a.out_tails);

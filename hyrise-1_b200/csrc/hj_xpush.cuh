@@ -1,0 +1,423 @@
+// hj_xpush.cuh — the fast multi-GPU path of hj_join_sharded ("push exchange"; no reference counterpart: the
+// reference is single-process). Included by hj_api.cu behind hj_comm.cuh, whose IPC plumbing it uses.
+//
+// What round 1 did per rank (hj_comm.cuh): X1 count sweep (decode, decoded keys through HBM) -> host sync -> X3 scatter of
+// (key, 8-byte RowID) into the peers -> local join over 12/16-byte RowID-carrying tuples on the two-sweep kernels: 62 ms per
+// C2-sized shard on 8 GPUs against 19.6 ms on one. Here:
+//   XP1 k_xchg_push   ONE sweep over the shard: decode (dictionary gather once), hash, destination rank, and the tile's rows
+//                     grouped by destination are stored STRAIGHT into the destination GPUs' receive regions over NVLink as
+//                     finished 8-byte tuples (int32 keys: (hash, position in the shard) — fmix32 is a bijection, so equal
+//                     hashes = equal keys and keys are never output) or 16-byte tuples (int64 keys: (key, position, 0)).
+//                     No count pass: a receive region is a row of 2048-tuple chunks that the sender's virtual CTAs take one
+//                     at a time from a sender-local cursor (one global atomic per 16 KB sent); only a virtual CTA's last
+//                     chunk per destination stays partly filled. The sender writes each chunk's fill count next to it.
+//   XP2 k_xchg_publish  chunks used per destination -> the destinations' region headers; overflow flag.
+//   barrier             1-word NCCL all-gather ("all stores have landed" + everybody's overflow flag).
+//   local join          the unchanged single-GPU kernels on the fused path: k_part1p<XCH> reads the regions (a chunk = a
+//                       tile, cp.async double-buffered: no gather here, the tuples stream), writes the source rank into the
+//                       tuple (int64: the spare word; int32: over the level-1 digit bits of the hash, which the fragment it
+//                       lands in makes redundant), k_scatter2f<PRE>, k_build_probe<kRidXch> emits RowIDs from (rank, position)
+//                       through the all-gathered shard geometry (XchMap).
+// Preconditions (else hj_join_sharded takes the general path of hj_comm.cuh): every rank maps every peer (CUDA IPC), two-pass
+// radix partitioning (> 8 bits), no routed NULLs (HJ_FLAG_SQL_NULL_PROBE), every shard "regular" (chunks of 2^k rows with
+// consecutive chunk ids, no reported row offsets). A destination region that would overflow (heavy skew) raises a flag that
+// all ranks see at the barrier; they then repeat the join on the general path.
+#pragma once
+
+namespace hj {
+
+constexpr uint32_t kXpChunk = 2048;  // tuples per receive chunk = one pass-1 tile of the local join
+
+struct XpushArgs {
+  RelMeta rel;
+  void* dst_tuples[kMaxRanks];     // destination d's receive region for MY rows (peer-mapped; own rank: local)
+  uint32_t* dst_fill[kMaxRanks];   // fill count per chunk of that region
+  uint32_t* cursor;                // [kMaxRanks] chunks taken per destination (sender-local)
+  uint32_t* overflow;              // raised when a region is full
+  uint32_t cap_chunks;             // chunks per region
+  uint32_t n_ranks;
+  int null_policy;                 // kNullDrop or kNullAsValue
+};
+
+// One physical CTA = VC virtual CTAs of VT threads (named barriers), each streaming its own tiles: c, c + G, ...
+// dynamic smem: VC * TILE * sizeof(Tuple<K>).
+template <typename K, int NT, int VC, int TILE>
+__global__ void __launch_bounds__(NT) k_xchg_push(const XpushArgs a) {
+  using T = Tuple<K, false>;
+  constexpr int VT = NT / VC;
+  constexpr int ITEMS = TILE / VT;
+  static_assert(TILE == kXpChunk && ITEMS >= 1 && ITEMS <= 32 && VT >= kMaxRanks, "a tile's run to one destination fits one chunk");
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  T* stage = reinterpret_cast<T*>(s_raw) + static_cast<size_t>(threadIdx.x / VT) * TILE;
+  __shared__ uint32_t s_cnt[VC][kMaxRanks], s_loff[VC][kMaxRanks + 1];
+  __shared__ uint32_t s_pos0[VC][kMaxRanks], s_first[VC][kMaxRanks], s_pos1[VC][kMaxRanks];  // this tile's run: where it goes
+  __shared__ uint32_t s_open[VC][kMaxRanks], s_left[VC][kMaxRanks];                          // open chunk (index, free tuples)
+  const uint32_t v = threadIdx.x / VT, vt = threadIdx.x % VT;
+  const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+  const uint32_t G = gridDim.x * VC, c = blockIdx.x * VC + v;
+  const uint32_t R = a.n_ranks;
+  if (vt < kMaxRanks) {
+    s_open[v][vt] = kInvalid;
+    s_left[v][vt] = 0;
+  }
+  for (uint32_t tile = c; tile < a.rel.n_tiles; tile += G) {
+    const DevSegment s = a.rel.segs[__ldg(a.rel.tile_seg + tile)];
+    const uint32_t r0 = (tile - s.tile_begin) * TILE;
+    const uint32_t cnt = min(static_cast<uint32_t>(TILE), s.n_rows - r0);
+    if (vt < kMaxRanks) s_cnt[v][vt] = 0;
+    K key[ITEMS];
+    uint32_t vbits = 0;
+    if (s.kind == 1) {
+      uint32_t vid[ITEMS];
+#pragma unroll
+      for (int u = 0; u < ITEMS; ++u) {
+        const uint32_t i = u * VT + vt;
+        vid[u] = i < cnt ? load_attr(s, r0 + i) : s.null_value_id;
+      }
+#pragma unroll
+      for (int u = 0; u < ITEMS; ++u) {
+        const bool valid = vid[u] != s.null_value_id;
+        key[u] = valid ? dict_gather<K>(s, vid[u]) : K(0);
+        vbits |= (valid ? 1u : 0u) << u;
+      }
+    } else {
+#pragma unroll
+      for (int u = 0; u < ITEMS; ++u) {
+        const uint32_t i = u * VT + vt;
+        key[u] = K(0);
+        if (i < cnt) {
+          key[u] = load_plain_key<K>(s, r0 + i);
+          const bool valid = !(s.nulls && __ldg(s.nulls + r0 + i));
+          if (s.kind == 2 && !valid) key[u] = K(0);
+          vbits |= (valid ? 1u : 0u) << u;
+        }
+      }
+    }
+    // destination + rank inside (warp, destination) by ballots: R <= 16 destinations, no shared-memory atomics per row
+    uint32_t h[ITEMS], packed[ITEMS];  // packed: destination << 16 | rank inside the warp's rows for that destination
+    uint32_t run = 0;                  // lane q: this warp's rows for destination q so far
+#pragma unroll
+    for (int u = 0; u < ITEMS; ++u) {
+      const bool kept = u * VT + vt < cnt && (((vbits >> u) & 1u) || a.null_policy == kNullAsValue);
+      h[u] = hash_key(key[u]);
+      const uint32_t d = kept ? dest_rank_of_hash(h[u], R) : kNoDigit;
+      packed[u] = kNoDigit;
+      for (uint32_t q = 0; q < R; ++q) {
+        const uint32_t bal = __ballot_sync(0xffffffffu, d == q);
+        const uint32_t before = __shfl_sync(0xffffffffu, run, q);
+        if (d == q) packed[u] = (q << 16) | (before + __popc(bal & lt));
+        if (lane == q) run += __popc(bal);
+      }
+    }
+    vbar(v, VT);  // s_cnt zeroed; the previous tile's copy-out is done with `stage`
+    uint32_t wbase = 0;  // lane q: start of this warp's rows inside the tile's run for destination q
+    if (lane < R && run) wbase = atomicAdd(&s_cnt[v][lane], run);
+    vbar(v, VT);
+    if (vt == 0) {
+      // where the tile's R runs go: the rest of the open chunk, then a fresh one
+      uint32_t off = 0;
+      for (uint32_t q = 0; q < R; ++q) {
+        const uint32_t n = s_cnt[v][q];
+        s_loff[v][q] = off;
+        off += n;
+        uint32_t left = s_left[v][q], open = s_open[v][q];
+        s_pos0[v][q] = open * kXpChunk + (kXpChunk - left);  // unused when left == 0
+        s_first[v][q] = left;
+        if (n > left) {
+          if (open != kInvalid) a.dst_fill[q][open] = kXpChunk;  // the open chunk ends up full
+          uint32_t fresh = atomicAdd(a.cursor + q, 1u);
+          if (fresh >= a.cap_chunks) {  // the region is full (skew): flag it; the rows fall on the region's last chunk and are
+            *a.overflow = 1u;           // never read, because every rank repeats the join on the general path
+            fresh = a.cap_chunks - 1u;
+          }
+          s_pos1[v][q] = fresh * kXpChunk;
+          s_open[v][q] = fresh;
+          s_left[v][q] = kXpChunk - (n - left);
+        } else {
+          s_left[v][q] = left - n;
+        }
+      }
+      s_loff[v][R] = off;
+    }
+#pragma unroll
+    for (int u = 0; u < ITEMS; ++u) {
+      const uint32_t q = packed[u] >> 16;
+      const uint32_t wb = __shfl_sync(0xffffffffu, wbase, q & 31u);
+      if (packed[u] != kNoDigit) packed[u] += wb;
+    }
+    vbar(v, VT);
+    const uint32_t pos0 = s.row_begin + r0;
+#pragma unroll
+    for (int u = 0; u < ITEMS; ++u) {
+      if (packed[u] != kNoDigit) {
+        T t;
+        if constexpr (sizeof(K) == 4) {
+          t.key = static_cast<K>(h[u]);
+        } else {
+          t.key = key[u];
+          t.pad = 0;
+        }
+        t.idx = pos0 + u * VT + vt;
+        stage[s_loff[v][packed[u] >> 16] + (packed[u] & 0xFFFFu)] = t;
+      }
+    }
+    vbar(v, VT);
+    for (uint32_t q = 0; q < R; ++q) {
+      const uint32_t n = s_loff[v][q + 1] - s_loff[v][q];
+      if (n == 0) continue;  // uniform over the virtual CTA
+      T* dst = static_cast<T*>(a.dst_tuples[q]);
+      const T* src = stage + s_loff[v][q];
+      const uint32_t first = s_first[v][q], p0 = s_pos0[v][q], p1 = s_pos1[v][q];
+      for (uint32_t i = vt; i < n; i += VT) dst[i < first ? p0 + i : p1 + (i - first)] = src[i];
+    }
+  }
+  vbar(v, VT);
+  if (vt < R && s_open[v][vt] != kInvalid) a.dst_fill[vt][s_open[v][vt]] = kXpChunk - s_left[v][vt];
+  __threadfence_system();  // the stores went to peer memory; the ranks meet at a barrier after XP2
+}
+
+// XP2 (one CTA, after XP1 on the same stream): my chunk counts -> the header of my region on every destination.
+struct XpushPublish {
+  uint32_t* dst[kMaxRanks];
+};
+__global__ void k_xchg_publish(const uint32_t* __restrict__ cursor, uint32_t cap_chunks, uint32_t n_ranks, const XpushPublish p) {
+  if (threadIdx.x < n_ranks) *p.dst[threadIdx.x] = min(cursor[threadIdx.x], cap_chunks);
+  __threadfence_system();
+}
+
+}  // namespace hj
+
+// ============================================================================================================= host side
+namespace {
+
+constexpr int kXpThreads = 1024;
+template <typename K> constexpr int xp_virtual() { return sizeof(K) == 4 ? 4 : 2; }  // 64 KB of staging either way
+constexpr uint32_t kXpSlackChunks = 1024;  // >= virtual CTAs of any sender: each may strand one partly filled chunk per region
+
+// What every rank tells the others about its shards before the exchange (one all-gather of kXpDescWords words).
+constexpr int kXpDescWords = 8;
+struct ShardGeometry {
+  bool regular = false;
+  uint32_t first_chunk = 0;
+  int32_t shift = 0;
+};
+
+// "regular": VALUE / DICT chunks of 2^k rows (the last one may be shorter) with consecutive chunk ids — the shape of a Hyrise
+// data table (Chunk::MAX_SIZE-sized chunks appended in order, storage/table.cpp) and of a contiguous run of its chunks.
+ShardGeometry shard_geometry(const hj_relation* r) {
+  ShardGeometry g;
+  if (r->n_segs == 0) {
+    g.regular = true;
+    return g;
+  }
+  for (uint32_t i = 0; i < r->n_segs; ++i) {
+    const hj_segment& s = r->segs[i];
+    if ((s.kind != HJ_SEG_VALUE && s.kind != HJ_SEG_DICT) || s.chunk_id != r->segs[0].chunk_id + i) return g;
+  }
+  g.first_chunk = r->segs[0].chunk_id;
+  if (r->n_segs == 1) {
+    if (r->segs[0].n_rows > (1u << 31)) return g;
+    g.shift = 31;
+    g.regular = true;
+    return g;
+  }
+  const uint32_t first = r->segs[0].n_rows;
+  if (!first || (first & (first - 1))) return g;
+  while ((1u << g.shift) != first) ++g.shift;
+  for (uint32_t i = 1; i < r->n_segs; ++i) {
+    const uint32_t n = r->segs[i].n_rows;
+    if ((i + 1 < r->n_segs && n != first) || n > first) return g;
+  }
+  g.regular = true;
+  return g;
+}
+
+// The sharded join over the push exchange, for hashed key type K. `desc`: the all-gathered shard descriptors
+// ([rank][kXpDescWords]: build rows, probe rows, build first chunk | shift << 32, probe first chunk | shift << 32, flags).
+// *fell_back: a region overflowed somewhere — nothing was produced, the caller runs the general path (on every rank).
+template <typename K>
+int run_join_sharded_push(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, int mode, cudaStream_t st,
+                          hj_result_info* info, const unsigned long long* desc, int radix_bits, bool* fell_back) {
+  using T = Tuple<K, false>;
+  NcclApi* nc = nccl_api();
+  ncclComm_t comm = static_cast<ncclComm_t>(ctx->nccl_comm);
+  const uint32_t R = ctx->n_ranks, me = ctx->rank;
+  const bool one_side = mode == HJ_MODE_SEMI || mode == HJ_MODE_ANTI;
+  const bool outer = mode == HJ_MODE_LEFT || mode == HJ_MODE_RIGHT;
+  const int probe_null_policy = outer ? kNullAsValue : kNullDrop;  // kNullRoute never comes here
+  const int bits2 = pass2_bits(radix_bits);
+  *fell_back = false;
+  Launches nl;
+  cudaEvent_t* ev = ctx->ev;
+  HJ_CUDA(ctx, cudaEventRecord(ev[9], st));
+
+  // ---- geometry: regions of cap[side] chunks per (source, destination), the same number on every rank
+  uint32_t cap[2];
+  for (int side = 0; side < 2; ++side) {
+    uint64_t max_rows = 0;
+    for (uint32_t r = 0; r < R; ++r) {
+      max_rows = std::max<uint64_t>(max_rows, desc[size_t(r) * kXpDescWords + side]);
+      const unsigned long long g = desc[size_t(r) * kXpDescWords + 2 + side];
+      ctx->xp_map[side].first_chunk[r] = static_cast<uint32_t>(g);
+      ctx->xp_map[side].shift[r] = static_cast<int32_t>(g >> 32);
+    }
+    const uint64_t expect = (max_rows + R - 1) / R;  // rows one shard sends to one destination under a uniform hash
+    cap[side] = static_cast<uint32_t>((expect + expect / 16 + kXpChunk - 1) / kXpChunk) + kXpSlackChunks;
+  }
+
+  // buffers outgrown during earlier sharded joins: their peers dropped the mappings when they saw the new handles
+  for (void* p : ctx->xchg_graveyard) cudaFree(p);
+  ctx->xchg_graveyard.clear();
+
+  // ---- my shards as the kernels see them, receive regions, handles (collective; rank-local failures travel with it)
+  PreparedRel ps_[2];
+  int local = prepare_relation(ctx, build, 0, kXpChunk, st, &ps_[0]);
+  if (local == HJ_OK) local = prepare_relation(ctx, probe, 1, kXpChunk, st, &ps_[1]);
+  for (int side = 0; side < 2 && local == HJ_OK; ++side) {
+    if (uint64_t(R) * cap[side] * kXpChunk >= 0xFFFFFFFFull)
+      local = fail(ctx, HJ_ERR_TOO_LARGE, "rank %u: receive regions of %llu tuples (limit 2^32-2 per GPU)", me,
+                   (unsigned long long)(uint64_t(R) * cap[side] * kXpChunk));
+    if (local == HJ_OK) local = ensure_exported(ctx, ctx->xchg_recv_keys[side], size_t(R) * cap[side] * kXpChunk * sizeof(T));
+    if (local == HJ_OK) local = ensure_exported(ctx, ctx->xchg_recv_rids[side], (size_t(kMaxRanks) + size_t(R) * cap[side]) * 4);
+  }
+  if (local == HJ_OK) local = ensure(ctx, ctx->xp_cursor, 64 * 4);
+  HJ_TRY(exchange_handles(ctx, st, local));
+  auto* cursor = static_cast<uint32_t*>(ctx->xp_cursor.p);  // [0..15] build cursors, [16..31] probe cursors, [32], [33] overflow flags
+  HJ_CUDA(ctx, cudaMemsetAsync(cursor, 0, 64 * 4, st));
+  // a region header nobody writes (a rank with an empty shard launches nothing) must read "0 chunks"
+  for (int side = 0; side < 2; ++side) HJ_CUDA(ctx, cudaMemsetAsync(ctx->xchg_recv_rids[side].p, 0, kMaxRanks * 4, st));
+  // every rank's headers are zeroed before anybody publishes into them
+  auto* bar_dev = static_cast<unsigned long long*>(ctx->xchg_cnt_dev.p);
+  HJ_NCCL(ctx, nc->AllGather(bar_dev, bar_dev + kMaxRanks, 1, ncclUint64, comm, st));
+
+  // ---- XP1 + XP2 per side
+  for (int side = 0; side < 2; ++side) {
+    XpushArgs a{};
+    XpushPublish pub{};
+    a.rel = ps_[side].meta;
+    a.cursor = cursor + side * kMaxRanks;
+    a.overflow = cursor + 32 + side;
+    a.cap_chunks = cap[side];
+    a.n_ranks = R;
+    a.null_policy = side == 0 ? kNullDrop : probe_null_policy;
+    for (uint32_t d = 0; d < R; ++d) {
+      char* tuples = static_cast<char*>(d == me ? ctx->xchg_recv_keys[side].p : ctx->xchg_peer[d][side * 3 + 0].ptr);
+      auto* meta = static_cast<uint32_t*>(d == me ? ctx->xchg_recv_rids[side].p : ctx->xchg_peer[d][side * 3 + 1].ptr);
+      if (!tuples || !meta) return fail(ctx, HJ_ERR_COMM, "rank %u has no mapping of rank %u's receive regions", me, d);
+      a.dst_tuples[d] = tuples + size_t(me) * cap[side] * kXpChunk * sizeof(T);
+      a.dst_fill[d] = meta + kMaxRanks + size_t(me) * cap[side];
+      pub.dst[d] = meta + me;
+    }
+    if (ps_[side].meta.n_tiles) {
+      constexpr int VC = xp_virtual<K>();
+      auto k = k_xchg_push<K, kXpThreads, VC, int(kXpChunk)>;
+      const size_t smem = size_t(VC) * kXpChunk * sizeof(T);
+      HJ_TRY(set_smem(ctx, k, smem));
+      const uint32_t grid = std::min<uint32_t>((ps_[side].meta.n_tiles + VC - 1) / VC, ctx->n_sms);
+      k<<<grid, kXpThreads, smem, st>>>(a);
+      HJ_LAUNCH_CHECK(ctx, "k_xchg_push");
+      nl.n++;
+    }
+    k_xchg_publish<<<1, 32, 0, st>>>(a.cursor, cap[side], R, pub);
+    HJ_LAUNCH_CHECK(ctx, "k_xchg_publish");
+    nl.n++;
+    if (side == 0) HJ_CUDA(ctx, cudaEventRecord(ev[10], st));
+  }
+  // barrier "all stores have landed" + everybody's overflow flags (one 64-bit word per rank: [32] | [33] << 32)
+  auto* flag_dev = reinterpret_cast<unsigned long long*>(cursor + 32);
+  HJ_NCCL(ctx, nc->AllGather(flag_dev, bar_dev + kMaxRanks, 1, ncclUint64, comm, st));
+  auto* host_words = reinterpret_cast<unsigned long long*>(static_cast<char*>(ctx->pinned) + kPinnedCounts);
+  HJ_CUDA(ctx, cudaMemcpyAsync(host_words, bar_dev + kMaxRanks, size_t(R) * 8, cudaMemcpyDeviceToHost, st));
+  HJ_CUDA(ctx, cudaMemcpyAsync(host_words + kMaxRanks, cursor, 32 * 4, cudaMemcpyDeviceToHost, st));  // my chunk counts (bytes sent)
+  HJ_CUDA(ctx, cudaEventRecord(ev[11], st));
+
+  // ---- local join over the regions: fused partitioning (k_part1p<XCH>, k_scatter2f) + k_build_probe<kRidXch>
+  hj_segment seg[2][kMaxRanks];
+  hj_relation rel[2];
+  PreparedRel pr[2];
+  PartState pst[2];
+  struct RegionGuard {
+    hj_ctx* c;
+    ~RegionGuard() { c->xp_region[2] = hj_ctx::XpRegion{}; c->xp_region[3] = hj_ctx::XpRegion{}; }
+  } guard{ctx};
+  for (int side = 0; side < 2; ++side) {
+    const auto* meta = static_cast<const uint32_t*>(ctx->xchg_recv_rids[side].p);
+    std::memset(seg[side], 0, sizeof(seg[side]));
+    for (uint32_t r = 0; r < R; ++r) {
+      seg[side][r].chunk_id = r;
+      seg[side][r].n_rows = cap[side] * kXpChunk;
+      seg[side][r].kind = HJ_SEG_VALUE;
+      seg[side][r].key_type = sizeof(K) == 8 ? HJ_KEY_INT64 : HJ_KEY_INT32;
+      seg[side][r].values = static_cast<const char*>(ctx->xchg_recv_keys[side].p) + size_t(r) * cap[side] * kXpChunk * sizeof(T);
+    }
+    rel[side].segs = seg[side];
+    rel[side].n_segs = R;
+    rel[side].location = HJ_LOC_DEVICE;
+    rel[side].n_rows = uint64_t(R) * cap[side] * kXpChunk;
+    ctx->xp_region[2 + side].fill = meta + kMaxRanks;
+    ctx->xp_region[2 + side].nchunks = meta;
+    ctx->xp_region[2 + side].cap_chunks = cap[side];
+    HJ_TRY(prepare_relation(ctx, &rel[side], 2 + side, p1_tile<K>(), st, &pr[side]));
+    HJ_TRY((stage_alloc<K, false>(ctx, pr[side], 2 + side, radix_bits, bits2, &pst[side])));
+    if (!pst[side].xch) return fail(ctx, HJ_ERR_INVALID, "push exchange needs the fused partitioning path");
+  }
+  HJ_CUDA(ctx, cudaEventRecord(ev[1], st));
+  HJ_TRY(stage_hist<K>(ctx, pr[0], 2, radix_bits, bits2, kNullAsValue, pst[0], st, &nl));
+  HJ_TRY(stage_hist<K>(ctx, pr[1], 3, radix_bits, bits2, kNullAsValue, pst[1], st, &nl));
+  HJ_CUDA(ctx, cudaEventRecord(ev[2], st));
+  HJ_CUDA(ctx, cudaEventRecord(ev[3], st));
+  HJ_TRY((stage_pass2<K, false>(ctx, pr[0], 2, radix_bits, bits2, kNullAsValue, pst[0], st, &nl)));
+  HJ_TRY((stage_pass2<K, false>(ctx, pr[1], 3, radix_bits, bits2, kNullAsValue, pst[1], st, &nl)));
+  HJ_CUDA(ctx, cudaEventRecord(ev[4], st));
+  int passes = 0;
+  // sizes for the planner and the first output estimate: what the regions can hold at most
+  uint64_t est[2];
+  for (int side = 0; side < 2; ++side) {
+    uint64_t total = 0;
+    for (uint32_t r = 0; r < R; ++r) total += desc[size_t(r) * kXpDescWords + side];
+    est[side] = total / R + total / R / 16 + 1;
+  }
+  for (int side = 0; side < 2; ++side) est[side] = std::max<uint64_t>(est[side], rel[side].n_rows);  // the hard bound
+  HJ_TRY((probe_phase<K, false>(ctx, pr[0], pr[1], pst[1], 2, 3, 0, radix_bits, bits2, mode, probe_null_policy, 2, est[0], est[1],
+                                st, &nl, &passes, ev[5], ev[6])));
+  // probe_phase synchronised the stream: the flags are here
+  for (uint32_t r = 0; r < R; ++r)
+    if (host_words[r]) *fell_back = true;
+  if (*fell_back) return HJ_OK;
+
+  auto* rb = static_cast<Readback*>(ctx->pinned);
+  ctx->has_result = true;
+  ctx->res_build = ctx->out_build[0].p;
+  ctx->res_probe = ctx->out_probe[0].p;
+  ctx->n_result = rb->out.n_rows;
+  ctx->n_sides = one_side ? 1 : 2;
+  info->n_rows = rb->out.n_rows;
+  info->n_sides = ctx->n_sides;
+  info->radix_bits = radix_bits;
+  info->n_build_tuples = rb->n_build_tuples;
+  info->n_probe_tuples = rb->n_probe_tuples;
+  info->n_partitions = 1u << radix_bits;
+  info->n_overflow_partitions = rb->plan.n_overflow_parts;
+  info->n_probe_passes = passes;
+  info->n_probe_slices = 0;
+  hj_timings& t = ctx->timings;
+  std::memset(&t, 0, sizeof(t));
+  t.ms[HJ_PH_XCHG_PARTITION] = ev_ms(ev[9], ev[10]);  // shard prepare, handles, build-side push
+  t.ms[HJ_PH_XCHG_TRANSFER] = ev_ms(ev[10], ev[11]);  // probe-side push + barrier
+  t.ms[HJ_PH_MATERIALIZE] = ev_ms(ev[1], ev[2]);      // pass 1 over the received tuples (both sides)
+  t.ms[HJ_PH_SCATTER2] = ev_ms(ev[3], ev[4]);
+  t.ms[HJ_PH_BUILD_PROBE] = passes == 1 ? ev_ms(ev[4], ev[5]) : 0.f;
+  t.ms[HJ_PH_FINALIZE] = passes == 1 ? ev_ms(ev[5], ev[6]) : 0.f;
+  t.ms[HJ_PH_TOTAL] = ev_ms(ev[9], ev[6]);
+  t.n_kernel_launches = nl.n;
+  t.xchg_path = 2;
+  const auto* my_chunks = reinterpret_cast<const uint32_t*>(host_words + kMaxRanks);
+  uint64_t sent = 0;
+  for (int side = 0; side < 2; ++side)
+    for (uint32_t d = 0; d < R; ++d)
+      if (d != me) sent += uint64_t(my_chunks[side * kMaxRanks + d]) * kXpChunk * sizeof(T);
+  t.bytes_nvlink_sent = sent;  // whole chunks: at most one partly filled chunk per virtual CTA and region too many
+  return HJ_OK;
+}
+
+}  // namespace

@@ -147,6 +147,10 @@ typedef struct hj_relation {
                                        that stores decoded keys, then two scatter passes. Default: pass 1 is done
                                        slab-locally inside the histogram kernel (hj_fused.cuh). Same results.    */
 
+#define HJ_FLAG_XCHG_GENERAL 0x10u   /* hj_join_sharded: always the general exchange (count sweep, RowID-carrying tuples,
+                                       hj_comm.cuh). Default: the push exchange (hj_xpush.cuh) wherever its preconditions
+                                       hold, the general one otherwise. Same results.                            */
+
 typedef struct hj_options {
   uint32_t abi_version;       /* HJ_ABI_VERSION                                              */
   uint32_t flags;             /* HJ_FLAG_*                                                   */
@@ -194,7 +198,7 @@ typedef struct hj_timings {
   uint64_t bytes_h2d;
   uint64_t bytes_d2h;
   uint32_t n_kernel_launches; /* kernels of this library launched by the last hj_join       */
-  uint32_t reserved;
+  uint32_t xchg_path;         /* hj_join_sharded: 1 = general exchange (hj_comm.cuh), 2 = push exchange (hj_xpush.cuh); else 0 */
   uint64_t bytes_nvlink_sent; /* hj_join_sharded: bytes this rank sent to its peers         */
 } hj_timings;
 

@@ -589,6 +589,13 @@ int oracle_join(const hj_relation* build, const hj_relation* probe, int mode, in
         g_error = "all chunks of a column share one data type";
         return HJ_ERR_INVALID;
       }
+      // the oracle restates JoinHash over the values a column iterable yields: a ReferenceColumn / encoded column arrives
+      // GATHERED (the caller dereferences it). Anything else would be read as a dictionary chunk with garbage pointers.
+      const uint8_t kind = r->segs[i].kind;
+      if (kind != HJ_SEG_VALUE && kind != HJ_SEG_DICT && kind != HJ_SEG_GATHERED) {
+        g_error = "the oracle takes VALUE, DICT and GATHERED chunks only (gather REFERENCE / FOR / RLE chunks first)";
+        return HJ_ERR_INVALID;
+      }
     }
   }
   OracleResult r;

@@ -55,3 +55,29 @@ int ref_dbgen_keys(float scale, int32_t* c_custkey, int32_t* o_orderkey, int32_t
   *n_lineitem = n_line;
   return rc;
 }
+
+/* o_custkey alone, for the large scale factors the full generator is too slow for (C4 at SF100: 150 M orders with their
+ * comments and lineitems take minutes). mk_order draws the customer key with ONE value of random stream O_CKEY_SD per order
+ * (build.c:180-189) and row_stop(ORDER) moves every stream to its per-row boundary, which is 1 for that stream (the Seed[]
+ * table in rnd.h / driver.c): the column IS that stream. The draw and the CUST_MORTALITY loop below are build.c's own
+ * statements, run on the reference's RANDOM; tests/test_dbgen_keys.py checks the result against mk_order's at SF 0.1 and 1. */
+int ref_dbgen_o_custkey(float scale, int32_t* o_custkey) {
+  int64_t n_cust, n_ord;
+  ref_dbgen_counts(scale, &n_cust, &n_ord);
+  if (scale >= 30000) return -1; /* RANDOM64 territory: not needed here */
+  dbgen_reset_seeds();
+  for (int64_t i = 0; i < n_ord; ++i) {
+    DSS_HUGE custkey;
+    int delta = 1;
+    row_start(ORDER);
+    RANDOM(custkey, O_CKEY_MIN, O_CKEY_MAX, O_CKEY_SD);
+    while (custkey % CUST_MORTALITY == 0) {
+      custkey += delta;
+      custkey = MIN(custkey, O_CKEY_MAX);
+      delta *= -1;
+    }
+    /* row_stop(ORDER) for this stream alone: usage 1 == boundary 1, nothing to skip */
+    o_custkey[i] = (int32_t)custkey;
+  }
+  return 0;
+}

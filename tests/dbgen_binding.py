@@ -25,6 +25,8 @@ def lib():
         l.ref_dbgen_counts.restype = None
         l.ref_dbgen_keys.argtypes = [C.c_float] + [C.c_void_p] * 5 + [C.c_int64, C.POINTER(C.c_int64)]
         l.ref_dbgen_keys.restype = C.c_int
+        l.ref_dbgen_o_custkey.argtypes = [C.c_float, C.c_void_p]
+        l.ref_dbgen_o_custkey.restype = C.c_int
         _lib = l
     return _lib
 
@@ -44,3 +46,16 @@ def tpch_keys(scale):
     if rc != 0:
         raise RuntimeError(f"ref_dbgen_keys: {nl.value} lineitems do not fit {cap}")
     return dict(c_custkey=c, o_orderkey=ok, o_custkey=oc, o_lines=ol, l_orderkey=lk[:nl.value].copy())
+
+
+def tpch_custkeys(scale):
+    """(c_custkey, o_custkey) alone — the C4 join columns — at scale factors the full generator is too slow for: c_custkey
+    is 1..n (mk_cust(i + 1)), o_custkey the reference's own draw + CUST_MORTALITY loop on random stream O_CKEY_SD
+    (ref_dbgen_o_custkey; equal to mk_order's column, tests/test_dbgen_keys.py)."""
+    l = lib()
+    nc, no = C.c_int64(), C.c_int64()
+    l.ref_dbgen_counts(scale, C.byref(nc), C.byref(no))
+    oc = np.zeros(no.value, np.int32)
+    if l.ref_dbgen_o_custkey(scale, oc.ctypes.data) != 0:
+        raise RuntimeError("ref_dbgen_o_custkey: scale factor out of range")
+    return np.arange(1, nc.value + 1, dtype=np.int32), oc

@@ -5,8 +5,9 @@
 # a failing step does not stop the later ones. Steps:
 #   box                      GPU / host facts
 #   smoke                    __graft_entry__.smoke()
-#   pytest[:-k expr]         python -m pytest tests -m gpu -q [-k expr]
-#   pytestx[:-k expr]        the same with -x
+#   pytest[:files / -k expr] python -m pytest -m gpu -q <files ... | tests>   (give the directory yourself with -k: "tests -k expr")
+#   pytestx[:...]            the same with -x
+#   pytestmon                the whole suite with -x --durations=30 and a memory monitor (TAG_pytestmon<n>.mem / .dmesg)
 #   sweep:"runs"             tests/sweep_variants.py --scale 1.0 --runs <runs> (variant libraries from tests/build_variants.sh)
 #   sweepw:"workload scale runs"
 #   bench[:args]             bench.py --steps 5 --warmup 3 <args>   (default args: --no-e2e --no-cpu)
@@ -39,8 +40,12 @@ for spec in "$@"; do
   case $step in
     box) run box 30 bash -c 'nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,memory.total --format=csv; nvidia-smi topo -m 2>/dev/null | head -12; nproc; free -g | head -2' ;;
     smoke) run smoke 300 python __graft_entry__.py smoke ;;
-    pytest) run pytest$n 1500 python -m pytest tests -m gpu -q $arg ;;
-    pytestx) run pytest$n 1500 python -m pytest tests -m gpu -q -x $arg ;;
+    pytest) run pytest$n 1500 python -m pytest -m gpu -q ${arg:-tests} ;;
+    pytestx) run pytest$n 1500 python -m pytest -m gpu -q -x ${arg:-tests} ;;
+    pytestmon) # the whole suite as the driver runs it, with the process's memory sampled every 5 s and the slowest tests listed
+             ( while sleep 5; do p=$(pgrep -n -f "pytest tests -m gpu" ); [ -n "$p" ] && echo "$(date +%s) rss_kb=$(awk '/VmRSS/{print $2}' /proc/$p/status 2>/dev/null) $(free -m | awk '/Mem:/{print "used_mb="$3" free_mb="$4}') $(nvidia-smi --query-gpu=memory.used --format=csv,noheader)"; done > gpurun_out/${TAG}_pytestmon$n.mem 2>&1 ) & mon=$!
+             run pytestmon$n 1500 python -m pytest tests -m gpu -q -x --durations=30 $arg
+             kill $mon 2>/dev/null; (dmesg 2>/dev/null | tail -20) > gpurun_out/${TAG}_pytestmon$n.dmesg 2>&1 ;;
     sweep) run sweep$n 600 python tests/sweep_variants.py --scale 1.0 --runs $arg --out gpurun_out/${TAG}_sweep$n.json ;;
     sweepw) set -- $arg; w=$1; sc=$2; shift 2; run sweep$n 600 python tests/sweep_variants.py --workload $w --scale $sc --joins 3 --runs "$@" --out gpurun_out/${TAG}_sweep$n.json ;;
     bench) run bench$n 600 python bench.py --steps 5 --warmup 3 ${arg:---no-e2e --no-cpu} ;;

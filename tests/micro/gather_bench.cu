@@ -6,6 +6,8 @@
 //   mode 3  UBLKCP     cp.async.bulk 16 B     (TMA engine: the aligned 16-byte block holding the entry, mbarrier-tracked)
 //   mode 4  LDG pairs  two adjacent lanes read the same 128-byte line (what sorting the value ids would buy)
 //   mode 5  LDG.64     8-byte entries (is the cost per row or per byte?)
+//   mode 6  stream     control: only the value ids are read (what the coalesced sweep alone costs)
+// The GPU is warmed up first (a fresh process starts at idle clocks; 1-ms kernels do not ramp them).
 // Every mode reads its value ids coalesced from an index array (like the attribute vector) and reduces the entries to a
 // checksum so nothing is optimised away. Reported: rows/ns, cycles per row and SM at the clock nvidia-smi reports.
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o gather_bench gather_bench.cu
@@ -62,6 +64,9 @@ __global__ void __launch_bounds__(NT) k_gather(const uint32_t* __restrict__ idx,
       for (int u = 0; u < ITEMS; ++u) v[u] = __ldg(reinterpret_cast<const unsigned long long*>(table) + (vid[u] >> 1));
 #pragma unroll
       for (int u = 0; u < ITEMS; ++u) acc += v[u];
+    } else if (MODE == 6) {
+#pragma unroll
+      for (int u = 0; u < ITEMS; ++u) acc += vid[u];
     } else if (MODE == 2) {
 #pragma unroll
       for (int u = 0; u < ITEMS; ++u)
@@ -109,7 +114,7 @@ void run(const char* name, int ctas_per_sm, int carve, const uint32_t* idx, cons
   const int grid = sms * ctas_per_sm;
   float best = 1e9f;
   unsigned long long got = 0;
-  for (int rep = 0; rep < 3; ++rep) {
+  for (int rep = 0; rep < 6; ++rep) {
     CK(cudaMemset(out, 0, 8));
     CK(cudaEventRecord(a));
     kern<<<grid, NT, smem>>>(idx, table, n, out);
@@ -120,7 +125,7 @@ void run(const char* name, int ctas_per_sm, int carve, const uint32_t* idx, cons
     CK(cudaMemcpy(&got, out, 8, cudaMemcpyDeviceToHost));
   }
   const unsigned long long rows = n / TILE * TILE;
-  const char* ok = (MODE == 4 || MODE == 5) ? "n/a" : (got == want ? "ok" : "MISMATCH");
+  const char* ok = (MODE == 4 || MODE == 5 || MODE == 6) ? "n/a" : (got == want ? "ok" : "MISMATCH");
   printf("%-10s NT=%4d ITEMS=%2d ctas/sm=%d carve=%3d  %7.3f ms  %6.2f rows/ns  %5.2f cyc/row/SM  sum %s\n", name, NT, ITEMS,
          ctas_per_sm, carve, best, rows / best / 1e6, best * 1e-3 * g_mhz * 1e6 * sms / rows, ok);
   fflush(stdout);
@@ -149,6 +154,10 @@ int main(int argc, char** argv) {
     for (auto v : h_idx) want_block += h_table[v];
     unsigned long long want = want_block * (n / h_idx.size());
     // every mode's TILE divides 2^28 only if TILE is a power of two: all configurations below are
+    for (int w = 0; w < 300; ++w) k_gather<0, 256, 8><<<sms * 8, 256>>>(idx, table, n, out);  // ~0.3 s of warm-up
+    CK(cudaDeviceSynchronize());
+    run<6, 256, 8>("stream", 8, -1, idx, table, n, out, sms, want);
+    run<6, 1024, 8>("stream", 2, -1, idx, table, n, out, sms, want);
     run<0, 256, 8>("LDG", 4, -1, idx, table, n, out, sms, want);
     run<0, 256, 8>("LDG", 8, -1, idx, table, n, out, sms, want);
     run<0, 256, 16>("LDG", 4, -1, idx, table, n, out, sms, want);

@@ -106,6 +106,13 @@ def main():
     ap.add_argument("--slice-rows", type=int, default=0,
                     help="nccl only: hj_options.stream_slice_rows — small values force the sliced exchange (probe slices "
                          "exchanged while the previous slice is joined) on these small cases")
+    ap.add_argument("--radix-bits", type=int, default=-1,
+                    help="nccl only: hj_options.radix_bits; > 8 makes the local join two-pass, which lets shards with regular "
+                         "chunks (2^k rows) take the PUSH exchange (hj_xpush.cuh) on these small cases")
+    ap.add_argument("--general", action="store_true", help="nccl only: HJ_FLAG_XCHG_GENERAL (never the push exchange)")
+    ap.add_argument("--c5", type=float, default=0.0,
+                    help="nccl only: add config C5 at this scale (0.01 = 40 M x 40 M int64, permutation build x uniform probe, "
+                         "ValueColumns of 2^20-row chunks), Inner, compared bit-exactly with the oracle's join of the global relations")
     args = ap.parse_args()
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local_rank = int(os.environ.get("LOCAL_RANK", rank))
@@ -117,8 +124,8 @@ def main():
 
     j = None
     if args.backend == "nccl":
-        j = hj.HashJoin(device=local_rank, flags=abi.FLAG_XCHG_STAGED if args.staged else 0,
-                        stream_slice_rows=args.slice_rows)
+        j = hj.HashJoin(device=local_rank, flags=(abi.FLAG_XCHG_STAGED if args.staged else 0) | (abi.FLAG_XCHG_GENERAL if args.general else 0),
+                        stream_slice_rows=args.slice_rows, radix_bits=args.radix_bits)
         uid = [hj.comm_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(uid, src=0)
         j.comm_init(uid[0], world, rank)
@@ -129,16 +136,34 @@ def main():
         ("int64 gathered", 2500, 6000, 2000, np.int64, True, "gathered", 512),
         ("empty build", 0, 500, 100, np.int32, False, "value", 128),
     ]
+    if args.backend == "nccl":
+        cases += [  # regular shards (chunks of 2^k rows): the push exchange when the local join is two-pass (--radix-bits > 8)
+            ("int32 dict 2^k", 40_000, 130_000, 30_000, np.int32, True, "dict", 4096),
+            ("int32 value 2^k", 50_000, 90_000, 45_000, np.int32, True, "value", 8192),
+            ("int64 value 2^k", 30_000, 100_000, 20_000, np.int64, True, "value", 2048),
+            ("int64 mixed 2^k", 25_000, 60_000, 1_000, np.int64, False, "mixed", 1024),
+            ("empty probe 2^k", 3000, 0, 100, np.int32, False, "value", 1024),
+            ("one chunk each", 900, 1500, 500, np.int32, True, "dict", 1024),
+        ]
     if args.backend == "gloo":
         cases = [(n, b // 4, p // 4, max(1, d // 4), t, nu, e, max(16, c // 4)) for n, b, p, d, t, nu, e, c in cases]
     elif args.big:
         cases.append(("2M x 8M dict", 2_000_000, 8_000_000, 2_000_000, np.int32, False, "dict", 1 << 18))
 
+    if args.backend == "nccl" and args.c5 > 0:
+        n5 = int(4_000_000_000 * args.c5)
+        cases.append(("C5 x %g" % args.c5, n5, n5, n5, np.int64, False, "value", 1 << 20))
+
     failures = 0
+    paths = {0: "-", 1: "general", 2: "push"}
     for ci, (name, nb, npr, domain, dtype, nullable, encoding, chunk) in enumerate(cases):
-        bk, bn, pk, pn = global_case(1000 + ci, nb, npr, domain, dtype, nullable)
+        if name.startswith("C5"):
+            rng = np.random.default_rng(0xB205)
+            bk, bn, pk, pn = (rng.permutation(nb) + 1).astype(np.int64), None, rng.integers(1, nb + 1, npr, dtype=np.int64), None
+        else:
+            bk, bn, pk, pn = global_case(1000 + ci, nb, npr, domain, dtype, nullable)
         wide = dtype == np.int64
-        for mode in MODES:
+        for mode in (["Inner"] if name.startswith("C5") else MODES):
             if args.backend == "nccl":
                 b_rel = make_shard(bk, bn, chunk, encoding, rank, world)
                 p_rel = make_shard(pk, pn, chunk, encoding, rank, world)
@@ -157,8 +182,9 @@ def main():
                 got, want = ob.canonical(gb, gp), ob.canonical(ob_b, ob_p)
                 ok = got.shape == want.shape and np.array_equal(got, want)
                 slices = info.n_probe_slices if args.backend == "nccl" else 0
-                print(f"[{args.backend} x{world}] {name:14s} {mode:5s} rows={len(want):8d} per-rank={[len(x[1]) for x in parts]} "
-                      f"slices={slices} {'OK' if ok else 'MISMATCH'}", flush=True)
+                path = paths.get(j.timings()["xchg_path"], "?") if args.backend == "nccl" else "model"
+                print(f"[{args.backend} x{world}] {name:16s} {mode:5s} rows={len(want):8d} per-rank={[len(x[1]) for x in parts]} "
+                      f"slices={slices} exchange={path} {'OK' if ok else 'MISMATCH'}", flush=True)
                 failures += 0 if ok else 1
     res = [failures]
     dist.broadcast_object_list(res, src=0)

@@ -53,6 +53,14 @@ def test_closed_forms_used_by_the_gpu_config_tests(sf01):
     assert np.array_equal(sf01["l_orderkey"], np.repeat(sf01["o_orderkey"], sf01["o_lines"]))
 
 
+@pytest.mark.parametrize("sf", [0.1, 1.0])
+def test_custkey_columns_alone_equal_the_full_generator(sf):
+    """tpch_custkeys (what C4 at SF100 uses: only random stream O_CKEY_SD is run) == the columns mk_cust / mk_order produce."""
+    full = db.tpch_keys(sf)
+    c, oc = db.tpch_custkeys(sf)
+    assert np.array_equal(c, full["c_custkey"]) and np.array_equal(oc, full["o_custkey"])
+
+
 @pytest.mark.parametrize("encoding", ["value", "dict"])
 def test_oracle_joins_dbgen_lineitem_with_orders(sf01, encoding):
     """C1 at SF 0.1 through the oracle: Inner on l_orderkey = o_orderkey, chunk size 100 000 (hyriseBenchmarkTPCH default)."""

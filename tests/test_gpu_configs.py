@@ -121,6 +121,59 @@ def test_c4_customer_orders_nulls(join, mode, encoding):
         assert 0.63 * non_null_c < info.n_rows < 0.70 * non_null_c
 
 
+def _pair_digest(b, p):
+    """Order-independent digest of a result: (rows, wrapping sum, xor) of a 64-bit mix of every (build RowID, probe RowID) row.
+    Equal multisets give equal digests; used where sorting 150 M rows twice would take longer than the join by far."""
+    x = p.reshape(-1, 2).astype(np.uint64)
+    h = (x[:, 0] << np.uint64(32) | x[:, 1]) * np.uint64(0x9E3779B97F4A7C15)
+    if b is not None:
+        y = b.reshape(-1, 2).astype(np.uint64)
+        h ^= ((y[:, 0] << np.uint64(32) | y[:, 1]) + np.uint64(0x632BE59BD9B4E019)) * np.uint64(0xC2B2AE3D27D4EB4F)
+    h ^= h >> np.uint64(29)
+    h *= np.uint64(0xBF58476D1CE4E5B9)
+    h ^= h >> np.uint64(32)
+    return len(x), int(h.sum(dtype=np.uint64)), int(np.bitwise_xor.reduce(h)) if len(h) else 0
+
+
+@pytest.fixture(scope="module")
+def c4_sf100():
+    """C4 as published: TPC-H SF100 customer (15 M c_custkey) x orders (150 M o_custkey) on the keys the reference's own dbgen
+    draws (tests/dbgen_binding.py tpch_custkeys: random stream O_CKEY_SD + CUST_MORTALITY, equal to mk_order's column), 1 % of
+    the keys of both sides set NULL by a seeded generator."""
+    import dbgen_binding as db
+    if not db.available():
+        pytest.skip("oracle/_ref/libref_dbgen.so not built")
+    ckeys, okeys = db.tpch_custkeys(100.0)
+    assert len(ckeys) == 15_000_000 and len(okeys) == 150_000_000
+    rng = np.random.default_rng(0xB204)
+    cn = (rng.random(len(ckeys)) < 0.01).astype(np.uint8)
+    on = (rng.random(len(okeys)) < 0.01).astype(np.uint8)
+    return ckeys, okeys, cn, on
+
+
+@pytest.mark.parametrize("mode,encoding", [("Left", "value"), ("Semi", "value"), ("Anti", "dict")])
+def test_c4_sf100_customer_orders_dbgen_keys(join, c4_sf100, mode, encoding):
+    """C4 at its published size against the oracle: orders build, customer probes (join_hash.cpp:58-70). Semi / Anti: sorted
+    RowID lists bit-exact; Left (150 M pairs): row count + an order-independent 64-bit digest of all (build, probe) RowID rows."""
+    ckeys, okeys, cn, on = c4_sf100
+    build = wl.make_relation(okeys, 1 << 20, encoding, on)
+    probe = wl.make_relation(ckeys, 1 << 20, encoding, cn)
+    mode_id = abi.MODES[mode]
+    info = join.join(build, probe, mode_id)
+    b, p = join.fetch()
+    ob_b, ob_p, oinfo = ob.oracle_join(build, probe, mode_id, n_threads=os.cpu_count() or 1)
+    assert info.n_rows == oinfo["n_rows"], f"C4 SF100 {mode} {encoding}: {info.n_rows} rows, oracle {oinfo['n_rows']}"
+    assert info.n_build_tuples == oinfo["n_build_tuples"] and info.n_probe_tuples == oinfo["n_probe_tuples"]
+    if mode == "Left":
+        assert _pair_digest(b, p) == _pair_digest(ob_b, ob_p), f"C4 SF100 Left {encoding}: result digests differ"
+    else:
+        assert np.array_equal(ob.canonical(b, p), ob.canonical(ob_b, ob_p)), f"C4 SF100 {mode} {encoding}: sorted RowIDs differ"
+    non_null_c = int((cn == 0).sum())
+    if mode == "Anti":  # quirk Q5: NULL customers are not returned; a third of the customers never ordered (CUST_MORTALITY)
+        assert 0.32 * non_null_c < info.n_rows < 0.35 * non_null_c
+    join.release_scratch()
+
+
 # ------------------------------------------------------------------------------------------------------- full-size properties
 def _device_case(name, scale):
     import torch
@@ -129,52 +182,48 @@ def _device_case(name, scale):
     data = bench.gen_device_workload(name, scale, dev, seed=0xB200 + 7)
     b = bench.relation_from_chunks(hj, data["build"], abi.LOC_DEVICE)
     p = bench.relation_from_chunks(hj, data["probe"], abi.LOC_DEVICE)
-
-    def flat_keys(chunks):
-        return torch.cat([(a if at is None else a[at.long() & (0xFFFFFFFF if at.dtype == torch.int32 else 0xFFFF if at.dtype == torch.int16 else 0xFF)])
-                          for _, a, at in chunks]).to(torch.int64)
-    return data, b, p, flat_keys
+    return data, b, p
 
 
-def _check_properties(j, data, b, p, flat_keys, sample=2_000_000):
-    """Exact row count, RowID checksum and sampled key equality of an Inner join, computed independently with torch."""
+def _check_properties(j, data, b, p, name):
+    """Exact row count, RowID checksums of both sides and key equality of 1 M sampled result rows of an Inner join, computed
+    independently with torch on the PosLists where the join left them (bench.verify_result: nothing is copied to the host,
+    everything chunk by chunk, so it fits beside the join's buffers at the full size of C3)."""
     import torch
+    import bench
     info = j.join(b, p, abi.MODE_INNER)
-    bk, pk = flat_keys(data["build"]), flat_keys(data["probe"])
-    domain = int(max(bk.max(), pk.max())) + 1
-    cb = torch.bincount(bk, minlength=domain)
-    matches_per_probe = cb[pk]                      # how many build rows every probe row joins with
-    want_rows = int(matches_per_probe.sum())
-    assert info.n_rows == want_rows, f"row count {info.n_rows} != {want_rows}"
-    bs, ps = j.fetch()
-    chunk = 1 << 20                                  # bench.CHUNK: position = chunk_id * 2^20 + offset
-    ppos = torch.from_numpy(ps.astype(np.int64)).cuda()
-    ppos = ppos[:, 0] * chunk + ppos[:, 1]
-    # checksum: every probe row appears exactly matches_per_probe times
-    want_sum = int((torch.arange(len(pk), device=pk.device) * matches_per_probe).sum())
-    assert int(ppos.sum()) == want_sum, "probe-side RowID checksum differs"
-    bpos = torch.from_numpy(bs.astype(np.int64)).cuda()
-    bpos = bpos[:, 0] * chunk + bpos[:, 1]
-    cp = torch.bincount(pk, minlength=domain)
-    want_bsum = int((torch.arange(len(bk), device=bk.device) * cp[bk]).sum())
-    assert int(bpos.sum()) == want_bsum, "build-side RowID checksum differs"
-    idx = torch.randint(0, info.n_rows, (min(sample, info.n_rows),), device=bk.device)
-    assert bool((bk[bpos[idx]] == pk[ppos[idx]]).all()), "a sampled result row joins unequal keys"
+    v = bench.verify_result(j, data, info, name, 0, 1, torch.device("cuda", 0))
+    assert v["rows"] == v["rows_expected"] == info.n_rows, v
+    assert v["checksums"] and v["sampled_key_mismatches"] == 0 and v["ok"], v
     return info
 
 
 @pytest.mark.parametrize("scale", [1.0])
 def test_c2_full_size_properties(join, scale):
     """C2 as published: 100 M x 1 B int32, dictionary-encoded, 1 e9 result pairs."""
-    data, b, p, flat_keys = _device_case("c2", scale)
-    info = _check_properties(join, data, b, p, flat_keys)
+    data, b, p = _device_case("c2", scale)
+    info = _check_properties(join, data, b, p, "c2")
     assert info.n_rows == data["n_probe"] and info.n_probe_passes == 1
     join.release_scratch()
 
 
+def test_c3_full_size_properties(join):
+    """C3 as published: 200 M Zipf(1.0) int64 build x 2 B uniform int64 probe, ValueColumns (~120 GB of the 180 GB HBM with
+    the join's buffers): ~2e9 pairs, the hottest key ~1e7 build duplicates."""
+    import torch
+    join.release_scratch()
+    torch.cuda.empty_cache()
+    data, b, p = _device_case("c3", 1.0)
+    info = _check_properties(join, data, b, p, "c3")
+    assert info.n_overflow_partitions >= 1 and 1.9e9 < info.n_rows < 2.1e9
+    join.release_scratch()
+    del data, b, p
+    torch.cuda.empty_cache()
+
+
 def test_c3_tenth_size_properties(join):
     """C3 at 1/10 (20 M x 200 M int64, Zipf build): ~2e8 pairs, hottest key ~1e6 duplicates expanded by whole warps."""
-    data, b, p, flat_keys = _device_case("c3", 0.1)
-    info = _check_properties(join, data, b, p, flat_keys)
+    data, b, p = _device_case("c3", 0.1)
+    info = _check_properties(join, data, b, p, "c3")
     assert info.n_overflow_partitions >= 1
     join.release_scratch()

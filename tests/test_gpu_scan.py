@@ -194,11 +194,13 @@ def test_scan_then_join_without_leaving_the_device(ctx):
     info = ctx.join(b_rel, p_rel, abi.MODE_INNER)
     gb, gp = ctx.fetch()
     # oracle: the same reference tables on the host
+    # (the oracle restates JoinHash, not ReferenceColumn: it gets the rows a ReferenceColumnIterable would yield, gathered here)
     def host_rel(keys, pos):
-        data = wl.make_relation(keys, chunk, "value")
         rb = hj.RelationBuilder(abi.LOC_HOST)
         for c in np.unique(pos[:, 0]):
-            rb.add_reference(int(c), np.ascontiguousarray(pos[pos[:, 0] == c]), data, abi.KEY_INT32)
+            rows = pos[pos[:, 0] == c]
+            gathered = np.ascontiguousarray(keys[rows[:, 0].astype(np.int64) * chunk + rows[:, 1]])
+            rb.add_value(int(c), gathered, None, kind=abi.SEG_GATHERED)
         return rb.build()
     ob_b, ob_p, oinfo = ob.oracle_join(host_rel(bk, b_pos), host_rel(pk, p_pos), abi.MODE_INNER)
     assert info.n_rows == oinfo["n_rows"] == int(((pk >= 100_000) & (pk < 300_000)).sum())
