@@ -807,9 +807,16 @@ int stage_hist(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int
   HJ_CUDA(ctx, cudaMemsetAsync(hist, 0, (size_t(P) + 1) * 4, st));
   if (ps.fused && ps.xch) {
     if (pr.meta.n_tiles) {
-      constexpr int VC = sizeof(K) == 4 ? 2 : 1;  // two key buffers per virtual CTA + a histogram of up to 2^15 bins in 227 KB
-      auto k = k_part1p<K, kHistThreads, VC, p1_tile<K>(), true>;
-      const size_t smem = ((((size_t(1) << radix_bits) + 1) * 4 + 15) & ~size_t(15)) + size_t(VC) * p1_tile<K>() * (2 * sizeof(Tuple<K, false>) + 2);
+      // per virtual CTA two tuple buffers + a permutation, next to a histogram of up to 2^15 bins, in 227 KB: as many tile
+      // streams per SM as fit (2^14 bins: 4 streams of int32 tuples / 2 of int64 tuples; 2^15 bins: half as many)
+      constexpr int VCW = sizeof(K) == 4 ? 4 : 2;
+      auto smem_for = [&](int vc) {
+        return ((((size_t(1) << radix_bits) + 1) * 4 + 15) & ~size_t(15)) + size_t(vc) * p1_tile<K>() * (2 * sizeof(Tuple<K, false>) + 2);
+      };
+      const bool wide = smem_for(VCW) + 12 * 1024 <= 227 * 1024;
+      auto k = wide ? k_part1p<K, kHistThreads, VCW, p1_tile<K>(), true> : k_part1p<K, kHistThreads, VCW / 2, p1_tile<K>(), true>;
+      const int VC = wide ? VCW : VCW / 2;
+      const size_t smem = smem_for(VC);
       HJ_TRY(set_smem(ctx, k, smem));
       const uint32_t grid = std::min<uint32_t>((pr.meta.n_tiles + VC - 1) / VC, ctx->n_sms);
       k<<<grid, kHistThreads, smem, st>>>(pr.meta, static_cast<Tuple<K, false>*>(ctx->tup_a[side].p),
@@ -962,7 +969,8 @@ float ev_ms(cudaEvent_t a, cudaEvent_t b) {
 template <typename K, bool PAY, int RM, int CLS>
 int launch_build_probe_cls(hj_ctx* ctx, const JoinArgs<K, PAY>& a, cudaStream_t st) {
   auto k5 = k_build_probe<K, PAY, kJoinThreads, Cfg<K>::kNS, Cfg<K>::kCap, kProbeV, RM, CLS>;
-  const size_t smem5 = (size_t(Cfg<K>::kNS) + 1) * sizeof(K) + (size_t(Cfg<K>::kNS) + 2) * 4 + size_t(Cfg<K>::kCap) * 4;
+  const size_t smem5 = (size_t(Cfg<K>::kNS) + 1) * sizeof(K) + (size_t(Cfg<K>::kNS) + 2) * 4 + size_t(Cfg<K>::kCap) * 4 +
+                       (RM == kRidXch ? size_t(Cfg<K>::kCap) : 0);  // kRidXch: + one source-rank byte per grouped build row
   HJ_TRY(set_smem(ctx, k5, smem5));
   k5<<<ctx->n_sms, kJoinThreads, smem5, st>>>(a);
   HJ_LAUNCH_CHECK(ctx, "k_build_probe");

@@ -1005,7 +1005,9 @@ int hj_comm_init(hj_ctx* ctx, const uint8_t id[HJ_NCCL_UNIQUE_ID_BYTES], int n_r
   ctx->nccl_comm = comm;
   ctx->n_ranks = n_ranks;
   ctx->rank = rank;
-  ctx->p2p_ok = n_ranks > 1 && probe_p2p(ctx);
+  // one rank: the exchange degenerates to stores into the rank's own receive buffers — kept working because it is how the
+  // exchange kernels are profiled on a single GPU (ncu follows one process; tests/profile_join.py --sharded)
+  ctx->p2p_ok = n_ranks == 1 || probe_p2p(ctx);
   return HJ_OK;
 }
 

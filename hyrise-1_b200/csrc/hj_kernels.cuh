@@ -867,7 +867,8 @@ constexpr int kClsInner = 0, kClsOuter = 1, kClsSemi = 2, kClsAnti = 3;
 // output arrays (the common case), so a row's position is ob/op + a 32-bit index; otherwise every row goes through
 // out_pos() and the capacity check (chunk boundary inside the tile, or the overflow pass that only counts).
 template <typename K, bool PAY, int V, int CLS, int RM, bool CONTIG>
-__device__ __forceinline__ void emit_tile(const JoinArgs<K, PAY>& a, const uint32_t* s_grp, const Tuple<K, PAY>* bchunk,
+__device__ __forceinline__ void emit_tile(const JoinArgs<K, PAY>& a, const uint32_t* s_grp, const uint8_t* s_rk, const XchMap* s_xmap,
+                                          const Tuple<K, PAY>* bchunk,
                                           const uint32_t (&pw)[V], const uint32_t (&pidx)[V], const uint32_t (&ppad)[V],
                                           const uint32_t (&outc)[V], const uint32_t (&ex)[V], uint32_t wbase,
                                           unsigned long long base0, unsigned long long base1, uint32_t first) {
@@ -899,8 +900,7 @@ __device__ __forceinline__ void emit_tile(const JoinArgs<K, PAY>& a, const uint3
       const Tuple<K, PAY> t = bchunk[s_grp[g]];
       return pack_rowid(t.idx, tuple_hi(t));
     } else if constexpr (RM == kRidXch) {
-      const Tuple<K, PAY> t = bchunk[s_grp[g]];
-      return xch_rowid(a.xmap[0], xch_rank<K, PAY>(t, a.bits2, a.radix_bits), t.idx);
+      return xch_rowid(s_xmap[0], s_rk[g], s_grp[g]);  // (source rank, position in that rank's shard), both grouped in smem
     } else {
       return rowid_of<RM>(a.build_rel, s_grp[g]);
     }
@@ -908,7 +908,7 @@ __device__ __forceinline__ void emit_tile(const JoinArgs<K, PAY>& a, const uint3
   // pad: the probe tuple's ChunkOffset (kRidPayload) / source rank (kRidXch)
   auto prid_of = [&](uint32_t idx, uint32_t pad) -> uint64_t {
     if constexpr (RM == kRidPayload) return pack_rowid(idx, pad);
-    else if constexpr (RM == kRidXch) return xch_rowid(a.xmap[1], pad, idx);
+    else if constexpr (RM == kRidXch) return xch_rowid(s_xmap[1], pad, idx);
     else return rowid_of<RM>(a.probe_rel, idx);
   };
   const uint32_t lane = lane_id();
@@ -962,8 +962,18 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K, PAY> a)
   K* s_keys = reinterpret_cast<K*>(s_raw);                          // NS + 1
   uint32_t* s_w = reinterpret_cast<uint32_t*>(s_keys + (NS + 1));   // NS + 2 (slot NS: sentinel key, NS+1: always 0)
   uint32_t* s_grp = s_w + (NS + 2);                                 // CAP
+  uint8_t* s_rk = reinterpret_cast<uint8_t*>(s_grp + CAP);          // CAP, kRidXch only: source rank of every grouped build row
   __shared__ uint32_t s_wtot[NW + 1];
   __shared__ uint32_t s_item;
+  // kRidXch: the shard geometry by rank, indexed per lane (a divergent index into the parameter bank would be serialised)
+  __shared__ XchMap s_xmap[RM == kRidXch ? 2 : 1];
+  if constexpr (RM == kRidXch) {
+    if (threadIdx.x < 32) {
+      const int side = threadIdx.x >> 4, r = threadIdx.x & 15;
+      s_xmap[side].first_chunk[r] = a.xmap[side].first_chunk[r];
+      s_xmap[side].shift[r] = a.xmap[side].shift[r];
+    }
+  }
 
   const uint32_t lane = lane_id(), warp = warp_id();
   const uint32_t lt_mask = (1u << lane) - 1u;
@@ -1068,11 +1078,20 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K, PAY> a)
 #pragma unroll
     for (int r0 = 0; r0 < BR; r0 += BU) {
       if (r0 * NT >= it.b_cnt) break;  // CTA-uniform
-      uint32_t bi[BU];
+      uint32_t bi[BU], brk[BU];
 #pragma unroll
       for (int u = 0; u < BU; ++u) {
         const uint32_t i = (r0 + u) * NT + threadIdx.x;
-        bi[u] = (RM == kRidPayload || RM == kRidXch) ? i : (i < it.b_cnt ? build[i].idx : 0u);
+        brk[u] = 0;
+        if constexpr (RM == kRidXch) {
+          if (i < it.b_cnt) {
+            const Tuple<K, PAY> t = ld_stream(build + i);
+            bi[u] = t.idx;
+            brk[u] = xch_rank<K, PAY>(t, a.bits2, radix_bits);
+          }
+        } else {
+          bi[u] = RM == kRidPayload ? i : (i < it.b_cnt ? build[i].idx : 0u);
+        }
       }
 #pragma unroll
       for (int u = 0; u < BU; ++u) {
@@ -1081,6 +1100,7 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K, PAY> a)
           const uint32_t slot = (bslot[(r0 + u) / 2] >> ((u & 1) * 16)) & 0xFFFFu;
           const uint32_t old = atomicAdd(&s_w[slot], 0x10000u);
           s_grp[old >> 16] = bi[u];
+          if constexpr (RM == kRidXch) s_rk[old >> 16] = static_cast<uint8_t>(brk[u]);
         }
       }
     }
@@ -1155,9 +1175,9 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K, PAY> a)
       if (running == 0) continue;  // warp-uniform
       warp_writer_reserve(&wr, a.out_state, running, chunk_shift);
       if (wr.first == 0xFFFFFFFFu && wr.base0 + running <= a.capacity)
-        emit_tile<K, PAY, V, CLS, RM, true>(a, s_grp, build, pw, pidx, ppad, outc, ex, 0u, wr.base0, wr.base1, wr.first);
+        emit_tile<K, PAY, V, CLS, RM, true>(a, s_grp, s_rk, s_xmap, build, pw, pidx, ppad, outc, ex, 0u, wr.base0, wr.base1, wr.first);
       else
-        emit_tile<K, PAY, V, CLS, RM, false>(a, s_grp, build, pw, pidx, ppad, outc, ex, 0u, wr.base0, wr.base1, wr.first);
+        emit_tile<K, PAY, V, CLS, RM, false>(a, s_grp, s_rk, s_xmap, build, pw, pidx, ppad, outc, ex, 0u, wr.base0, wr.base1, wr.first);
     }
   }
   if (lane == 0) out_writer_finish(&wr, a.out_state, a.out_tails);

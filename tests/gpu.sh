@@ -15,6 +15,7 @@
 #   benchref                 bench.py --impl reference --steps 3 --warmup 1
 #   launches[:bench args]    ncu launch list (gpu__time_duration) of bench.py --steps 2 --warmup 3 --no-e2e --no-cpu --no-verify
 #   ncufull:"regex skip count [workload scale]"   ncu --set full of tests/profile_join.py, report -> gpurun_out/TAG_ncu_<n>.ncu-rep
+#   prof:"args"              tests/profile_join.py --joins 3 <args> (per-phase timings, e.g. "--scale 1.0 --sharded")
 #   micro:name               tests/micro/<name> (prebuilt binary)
 #   sharded[:args]           torchrun -n $NGPU tests/sharded_check.py --backend nccl <args>
 #   benchn[:args]            torchrun -n $NGPU bench.py --gpus $NGPU --steps 5 --warmup 3 <args>
@@ -55,7 +56,8 @@ for spec in "$@"; do
                 python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu --no-verify $arg ;;
     ncufull) set -- $arg; rx=$1; skip=${2:-0}; cnt=${3:-4}; w=${4:-c2}; sc=${5:-1.0}
              run ncu$n 1200 ncu --set full --clock-control none --import-source on -k "regex:$rx" -s $skip -c $cnt -o gpurun_out/${TAG}_ncu$n -f \
-                python tests/profile_join.py --workload $w --scale $sc --joins 2 ;;
+                python tests/profile_join.py --workload $w --scale $sc --joins 2 $6 ;;
+    prof) run prof$n 300 python tests/profile_join.py --joins 3 $arg ;;
     micro) run micro_$arg 120 tests/micro/$arg ;;
     sharded) run sharded$n 900 $TORCHRUN $((29500 + RANDOM % 400)) tests/sharded_check.py --backend nccl $arg ;;
     benchn) run benchn$n 900 $TORCHRUN $((29500 + RANDOM % 400)) bench.py --gpus $NGPU --steps 5 --warmup 3 ${arg:---no-e2e --no-cpu} ;;
