@@ -753,21 +753,26 @@ struct PartState {
   bool fused = false;  // hj_fused.cuh: slab-local pass 1 inside the histogram kernel, fragment-gathering pass 2
   uint32_t gs = 0;     // fused: slabs per pass-2 work item
   bool xch = false;    // fused over push-exchanged tuples: k_part1p<XCH>, prehashed int32 tuples in pass 2
+  uint32_t slab = 0;   // fused: tuples per pass-1 slab (tile rows + F1 + 2: room for the holes that align the fragments)
 };
 
-// P1's dynamic shared memory: the full-resolution histogram + per virtual CTA one staging tile (k_part1) or two key
-// buffers and a 16-bit permutation (k_part1p)
+// P1's dynamic shared memory: the full-resolution histogram + per virtual CTA one staging tile of full tuples (k_part1) or
+// two key buffers and a 16-bit permutation (k_part1p), each with room for the holes that align the fragments
+// 1: software-pipelined pass 1 (k_part1p, cp.async gathers); 0: k_part1. Measured on C2 (profiles/r02_sweep_p1_pipelined.md):
+// k_part1p 8.54 ms, k_part1 + ld.global.cg 7.75 ms — the pipelined kernel loses (more shared memory = less L1 for the gather's
+// line allocations, 8-cycle LDGSTS issue), so k_part1 stays the default for column inputs; k_part1p<XCH> partitions the
+// tuples received from the multi-GPU push exchange (hj_xpush.cuh).
 #ifndef HJ_TUNE_P1_PIPE
-// 1: software-pipelined pass 1 (k_part1p, cp.async gathers); 0: k_part1 of round 1. Measured on C2 (profiles/
-// r02_sweep_p1_pipelined.md): k_part1p 8.54 ms, k_part1 + ld.global.cg 7.75 ms — the pipelined kernel loses (more shared
-// memory = less L1 for the gather's line allocations, 8-cycle LDGSTS issue), so k_part1 stays the default for column
-// inputs; k_part1p<XCH> partitions the tuples received from the multi-GPU exchange (hj_comm.cuh).
 #define HJ_TUNE_P1_PIPE 0
+#endif
+#ifndef HJ_TUNE_P2_TMA
+#define HJ_TUNE_P2_TMA 1  // 1: pass 2 fetches its fragments with TMA bulk copies (k_scatter2t); 0: per-thread loads (k_scatter2f)
 #endif
 template <typename K>
 size_t part1_smem(int radix_bits) {
-  const size_t per_row = HJ_TUNE_P1_PIPE ? 2 * sizeof(K) + 2 : sizeof(K) + 2;
-  return ((((size_t(1) << radix_bits) + 1) * 4 + 15) & ~size_t(15)) + size_t(Cfg<K>::kP1Virtual) * p1_tile<K>() * per_row;
+  const size_t per_stream = HJ_TUNE_P1_PIPE ? size_t(p1_tile<K>()) * 2 * sizeof(K) + (p1_tile<K>() + kSlabPad) * 2
+                                            : (p1_tile<K>() + kSlabPad) * sizeof(Tuple<K, false>);
+  return ((((size_t(1) << radix_bits) + 1) * 4 + 15) & ~size_t(15)) + size_t(Cfg<K>::kP1Virtual) * per_stream;
 }
 
 template <typename K, bool PAY>
@@ -782,13 +787,16 @@ int stage_alloc(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, in
     // an item gathers gs fragments of p1_tile/F1 tuples on average: HJ_TUNE_P2_FILL16/16 = 7/8 of a pass-2 batch (k_scatter2f needs gs < its CTA size and keeps fragment owners in 8 bits)
     ps->gs = std::min<uint32_t>(std::min(kP2Threads - 1, 255), std::max<uint64_t>(1, uint64_t(p2_tile<K>()) * HJ_TUNE_P2_FILL16 / 16 * F1 / p1_tile<K>()));
     HJ_TRY(ensure(ctx, ctx->frag[side], std::max<size_t>(1, pr.meta.n_tiles) * (F1 + 2) * 2));
+    ps->slab = tile_rows<K, PAY>(ctx, bits2, side) + F1 + 2;
+    if (uint64_t(pr.meta.n_tiles) * ps->slab >= 0xFFFFFFFFull)
+      return fail(ctx, HJ_ERR_TOO_LARGE, "%u tiles of %u slab tuples exceed the 32-bit tuple index of pass 2", pr.meta.n_tiles, ps->slab);
   }
   HJ_TRY(ensure(ctx, ctx->hist[side], (size_t(P) + 1) * 4));
   if (!ps->fused) HJ_TRY(ensure(ctx, ctx->hist1[side], size_t(ps->G) * (F1 + 1) * 4));
   HJ_TRY(ensure(ctx, ctx->part_off[side], (size_t(P) + 2) * 4));
   HJ_TRY(ensure(ctx, ctx->cur2[side], (size_t(P) + 1) * 4));
   HJ_TRY(ensure(ctx, ctx->l1_tiles[side], (size_t(F1) + 1) * 4));
-  HJ_TRY(ensure(ctx, ctx->tup_a[side], std::max<size_t>(1, n) * sizeof(Tuple<K, PAY>)));
+  HJ_TRY(ensure(ctx, ctx->tup_a[side], std::max<size_t>(1, ps->fused ? size_t(pr.meta.n_tiles) * ps->slab : size_t(n)) * sizeof(Tuple<K, PAY>)));
   if (bits2) HJ_TRY(ensure(ctx, ctx->tup_b[side], std::max<size_t>(1, n) * sizeof(Tuple<K, PAY>)));
   if (pr.has_dict && !ps->fused) {
     HJ_TRY(ensure(ctx, ctx->keys_mat[side], std::max<size_t>(1, n) * sizeof(K)));
@@ -811,7 +819,8 @@ int stage_hist(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int
       // streams per SM as fit (2^14 bins: 4 streams of int32 tuples / 2 of int64 tuples; 2^15 bins: half as many)
       constexpr int VCW = sizeof(K) == 4 ? 4 : 2;
       auto smem_for = [&](int vc) {
-        return ((((size_t(1) << radix_bits) + 1) * 4 + 15) & ~size_t(15)) + size_t(vc) * p1_tile<K>() * (2 * sizeof(Tuple<K, false>) + 2);
+        return ((((size_t(1) << radix_bits) + 1) * 4 + 15) & ~size_t(15)) +
+               size_t(vc) * (size_t(p1_tile<K>()) * 2 * sizeof(Tuple<K, false>) + (p1_tile<K>() + kSlabPad) * 2);
       };
       const bool wide = smem_for(VCW) + 12 * 1024 <= 227 * 1024;
       auto k = wide ? k_part1p<K, kHistThreads, VCW, p1_tile<K>(), true> : k_part1p<K, kHistThreads, VCW / 2, p1_tile<K>(), true>;
@@ -820,7 +829,7 @@ int stage_hist(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int
       HJ_TRY(set_smem(ctx, k, smem));
       const uint32_t grid = std::min<uint32_t>((pr.meta.n_tiles + VC - 1) / VC, ctx->n_sms);
       k<<<grid, kHistThreads, smem, st>>>(pr.meta, static_cast<Tuple<K, false>*>(ctx->tup_a[side].p),
-                                          static_cast<uint16_t*>(ctx->frag[side].p), hist, radix_bits, bits2, null_policy);
+                                          static_cast<uint16_t*>(ctx->frag[side].p), hist, radix_bits, bits2, null_policy, ps.slab);
       HJ_LAUNCH_CHECK(ctx, "k_part1p<XCH>");
       nl->n++;
     }
@@ -845,7 +854,7 @@ int stage_hist(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int
       HJ_TRY(set_smem(ctx, k, smem));
       const uint32_t grid = std::min<uint32_t>((pr.meta.n_tiles + VC - 1) / VC, ctx->n_sms);
       k<<<grid, kHistThreads, smem, st>>>(pr.meta, static_cast<Tuple<K, false>*>(ctx->tup_a[side].p),
-                                          static_cast<uint16_t*>(ctx->frag[side].p), hist, radix_bits, bits2, null_policy);
+                                          static_cast<uint16_t*>(ctx->frag[side].p), hist, radix_bits, bits2, null_policy, ps.slab);
       HJ_LAUNCH_CHECK(ctx, "k_part1");
       nl->n++;
     }
@@ -918,17 +927,20 @@ int stage_pass2(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, in
   if constexpr (!PAY) {
     if (ps.fused) {
       constexpr int NT = kP2Threads;
-      auto k = ps.xch ? k_scatter2f<K, NT, Cfg<K>::kP2Items, kP2MinBlocks, sizeof(K) == 4>
-                      : k_scatter2f<K, NT, Cfg<K>::kP2Items, kP2MinBlocks, false>;
+      constexpr bool PREX = sizeof(K) == 4;  // push-exchanged int32 tuples carry the hash in the key field
+#if HJ_TUNE_P2_TMA
+      auto k = ps.xch ? k_scatter2t<K, NT, Cfg<K>::kP2Items, kP2MinBlocks, PREX> : k_scatter2t<K, NT, Cfg<K>::kP2Items, kP2MinBlocks, false>;
+#else
+      auto k = ps.xch ? k_scatter2f<K, NT, Cfg<K>::kP2Items, kP2MinBlocks, PREX> : k_scatter2f<K, NT, Cfg<K>::kP2Items, kP2MinBlocks, false>;
+#endif
       const size_t smem = size_t(p2_tile<K>()) * sizeof(Tuple<K, false>);
-      HJ_TRY(set_smem(ctx, k_scatter2f<K, NT, Cfg<K>::kP2Items, kP2MinBlocks, false>, smem));
-      if (ps.xch) HJ_TRY(set_smem(ctx, k_scatter2f<K, NT, Cfg<K>::kP2Items, kP2MinBlocks, sizeof(K) == 4>, smem));
+      HJ_TRY(set_smem(ctx, k, smem));
       const uint32_t F1 = (1u << radix_bits) >> bits2;
       const uint32_t n_digits = F1 + (null_policy == kNullRoute ? 1u : 0u);
       const uint64_t grid = uint64_t((pr.meta.n_tiles + ps.gs - 1) / ps.gs) * n_digits;
       if (grid > 0x7FFFFFFFull) return fail(ctx, HJ_ERR_TOO_LARGE, "pass 2: %llu work items", (unsigned long long)grid);
       k<<<uint32_t(grid), NT, smem, st>>>(static_cast<const Tuple<K, false>*>(ctx->tup_a[side].p),
-                                          static_cast<const uint16_t*>(ctx->frag[side].p), pr.meta, uint32_t(p1_tile<K>()),
+                                          static_cast<const uint16_t*>(ctx->frag[side].p), pr.meta.n_tiles, ps.slab,
                                           static_cast<Tuple<K, false>*>(ctx->tup_b[side].p),
                                           static_cast<uint32_t*>(ctx->cur2[side].p), radix_bits, bits2, ps.gs, n_digits);
       HJ_LAUNCH_CHECK(ctx, "k_scatter2f");

@@ -14,6 +14,8 @@
 //
 // v1/v2 of the library (K1 + k_scatter1 + k_scatter2) spent 6.3 + 5.0 + 4.0 ms here on C2; see DESIGN.md §4.
 #pragma once
+#include <type_traits>
+
 #include "hj_kernels.cuh"
 
 #ifndef HJ_TUNE_P1_PREFETCH
@@ -41,6 +43,24 @@
 
 namespace hj {
 
+__device__ __forceinline__ uint32_t smem_addr_of(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+
+// Slab layout (pass 1 -> pass 2): tile t's slab starts at t * slab tuples (slab = tile rows + F1 + 2, even) and holds the
+// tile's tuples grouped by level-1 digit; every fragment starts on a 16-byte boundary, so a digit with an odd number of
+// 8-byte tuples is followed by a hole: a tuple whose position is kHoleIdx (no row has it: relations hold < 2^32 - 1 rows).
+constexpr uint32_t kHoleIdx = 0xFFFFFFFFu;
+constexpr uint32_t kSlabPad = kMaxDigits + 2;  // shared-memory staging per tile: tile rows + this
+template <typename T>
+__device__ __forceinline__ uint32_t slab_pad(uint32_t n) { return sizeof(T) == 8 ? (n + 1u) & ~1u : n; }
+template <typename K>
+__device__ __forceinline__ Tuple<K, false> hole_tuple() {
+  Tuple<K, false> t;
+  t.key = K(0);
+  t.idx = kHoleIdx;
+  if constexpr (sizeof(K) == 8) t.pad = 0;
+  return t;
+}
+
 template <typename K>
 __device__ __forceinline__ K dict_gather(const DevSegment& s, uint32_t vid) {
 #if HJ_TUNE_P1_GATHER == 0
@@ -60,6 +80,80 @@ __device__ __forceinline__ K dict_gather(const DevSegment& s, uint32_t vid) {
 #endif
 }
 
+// One tile's keys into registers: row u * VT + vt of the tile for u = 0 .. ITEMS-1, bit u of vbits = the row is not NULL.
+// The chunk's encoding (attribute-vector width, element width of the values / dictionary, NULL flags) is resolved ONCE per
+// tile here and the unrolled loops below are instantiated per case; with the dispatch inside the loops (round 1) every row
+// paid three branches on segment fields, ~15 % of pass 1's instructions.
+template <typename K, typename A, typename D, int ITEMS, int VT>
+__device__ __forceinline__ void load_dict_rows(const DevSegment& s, uint32_t r0, uint32_t cnt, uint32_t vt, K (&key)[ITEMS], uint32_t& vbits) {
+  const A* attr = static_cast<const A*>(s.attr) + r0;
+  const D* dict = static_cast<const D*>(s.values);
+  const uint32_t nv = s.null_value_id;
+  uint32_t vid[ITEMS];
+#pragma unroll
+  for (int u = 0; u < ITEMS; ++u) {
+    const uint32_t i = u * VT + vt;
+    vid[u] = i < cnt ? static_cast<uint32_t>(__ldg(attr + i)) : nv;  // rows past the end carry null_value_id
+  }
+#pragma unroll
+  for (int u = 0; u < ITEMS; ++u) {
+    const bool valid = vid[u] != nv;
+    // NULL decodes to T{} (dictionary_column_iterable.hpp:80); ld.global.cg: the gather never hits L1 (HJ_TUNE_P1_GATHER)
+    key[u] = valid ? static_cast<K>(__ldcg(dict + vid[u])) : K(0);
+    vbits |= (valid ? 1u : 0u) << u;
+  }
+}
+template <typename K, typename D, bool NULLS, int ITEMS, int VT>
+__device__ __forceinline__ void load_value_rows(const DevSegment& s, uint32_t r0, uint32_t cnt, uint32_t vt, K (&key)[ITEMS], uint32_t& vbits) {
+  const D* values = static_cast<const D*>(s.values) + r0;
+  const uint8_t* nulls = s.nulls + r0;
+  const bool zero_nulls = s.kind == 2;  // GATHERED NULL yields T{} (reference_column_iterable.hpp:60); a ValueColumn keeps its value
+#pragma unroll
+  for (int u = 0; u < ITEMS; ++u) {
+    const uint32_t i = u * VT + vt;
+    key[u] = K(0);
+    if (i < cnt) {
+      key[u] = static_cast<K>(__ldg(values + i));
+      bool valid = true;
+      if constexpr (NULLS) {
+        valid = __ldg(nulls + i) == 0;
+        if (zero_nulls && !valid) key[u] = K(0);
+      }
+      vbits |= (valid ? 1u : 0u) << u;
+    }
+  }
+}
+template <typename K, int ITEMS, int VT>
+__device__ __forceinline__ void load_tile_keys(const DevSegment& s, uint32_t r0, uint32_t cnt, uint32_t vt, K (&key)[ITEMS], uint32_t& vbits) {
+  vbits = 0;
+  const bool narrow = sizeof(K) == 8 && s.key_type == 0;  // an int32 chunk of an int64 join
+  if (s.kind == 1) {
+    if constexpr (sizeof(K) == 8) {
+      if (narrow) {
+        if (s.attr_width == 4) load_dict_rows<K, uint32_t, int32_t, ITEMS, VT>(s, r0, cnt, vt, key, vbits);
+        else if (s.attr_width == 2) load_dict_rows<K, uint16_t, int32_t, ITEMS, VT>(s, r0, cnt, vt, key, vbits);
+        else load_dict_rows<K, uint8_t, int32_t, ITEMS, VT>(s, r0, cnt, vt, key, vbits);
+        return;
+      }
+    }
+    using D = typename std::conditional<sizeof(K) == 8, long long, int32_t>::type;
+    if (s.attr_width == 4) load_dict_rows<K, uint32_t, D, ITEMS, VT>(s, r0, cnt, vt, key, vbits);
+    else if (s.attr_width == 2) load_dict_rows<K, uint16_t, D, ITEMS, VT>(s, r0, cnt, vt, key, vbits);
+    else load_dict_rows<K, uint8_t, D, ITEMS, VT>(s, r0, cnt, vt, key, vbits);
+  } else {
+    if constexpr (sizeof(K) == 8) {
+      if (narrow) {
+        if (s.nulls) load_value_rows<K, int32_t, true, ITEMS, VT>(s, r0, cnt, vt, key, vbits);
+        else load_value_rows<K, int32_t, false, ITEMS, VT>(s, r0, cnt, vt, key, vbits);
+        return;
+      }
+    }
+    using D = typename std::conditional<sizeof(K) == 8, long long, int32_t>::type;
+    if (s.nulls) load_value_rows<K, D, true, ITEMS, VT>(s, r0, cnt, vt, key, vbits);
+    else load_value_rows<K, D, false, ITEMS, VT>(s, r0, cnt, vt, key, vbits);
+  }
+}
+
 // =====================================================================================================================
 // P1. One physical CTA of NT threads hosts VC virtual CTAs of VT = NT/VC threads (as K1 does) that share the
 // full-resolution histogram; every virtual CTA has its own staging tile. Virtual CTA c owns tiles c, c+G, ...
@@ -67,11 +161,11 @@ __device__ __forceinline__ K dict_gather(const DevSegment& s, uint32_t vid) {
 // A tile is staged as keys + 16-bit row numbers inside the tile (6 instead of 8 bytes per int32 row): shared memory is L1
 // taken away from the dictionary gather, whose rate is set by the L1 lines that can be in flight — measured on C2 (14
 // radix bits, 64 KB histogram): 4 virtual CTAs with 8-byte staging (228 KB carve-out) 28 ms, 2 virtual CTAs 8.9 ms.
-// dynamic smem: (2^radix_bits + 1) * 4 (rounded up to 16) + VC * TILE * (sizeof(K) + 2).
+// dynamic smem: (2^radix_bits + 1) * 4 (rounded up to 16) + VC * (TILE + kSlabPad) * sizeof(Tuple<K>).
 // =====================================================================================================================
 template <typename K, int NT, int VC, int TILE>
 __global__ void __launch_bounds__(NT) k_part1(RelMeta rel, Tuple<K, false>* __restrict__ out1, uint16_t* __restrict__ frag,
-                                              uint32_t* __restrict__ hist, int radix_bits, int bits2, int null_policy) {
+                                              uint32_t* __restrict__ hist, int radix_bits, int bits2, int null_policy, uint32_t slab) {
   using T = Tuple<K, false>;
   constexpr int VT = NT / VC;
   constexpr int ITEMS = TILE / VT;
@@ -89,8 +183,7 @@ __global__ void __launch_bounds__(NT) k_part1(RelMeta rel, Tuple<K, false>* __re
   const uint32_t F1 = P >> bits2, FS = F1 + 2u;
   const uint32_t v = threadIdx.x / VT, vt = threadIdx.x % VT;
   const uint32_t G = gridDim.x * VC, c = blockIdx.x * VC + v;
-  K* skey = reinterpret_cast<K*>(stage_raw) + v * TILE;
-  uint16_t* srow = reinterpret_cast<uint16_t*>(stage_raw + VC * TILE * sizeof(K)) + v * TILE;
+  T* stile = reinterpret_cast<T*>(stage_raw) + v * (TILE + kSlabPad);
   for (uint32_t b = threadIdx.x; b < n_bins; b += NT) s_hist[b] = 0;
   __syncthreads();
 
@@ -120,33 +213,8 @@ __global__ void __launch_bounds__(NT) k_part1(RelMeta rel, Tuple<K, false>* __re
     vbar(v, VT);  // also orders the previous tile's copy-out before this tile's staging
 
     K key[ITEMS];
-    uint32_t vbits = 0;  // bit u: row u*VT+vt is valid (non-NULL)
-    if (s.kind == 1) {
-      uint32_t vid[ITEMS];
-#pragma unroll
-      for (int u = 0; u < ITEMS; ++u) {
-        const uint32_t i = u * VT + vt;
-        vid[u] = i < cnt ? load_attr(s, r0 + i) : s.null_value_id;
-      }
-#pragma unroll
-      for (int u = 0; u < ITEMS; ++u) {
-        const bool valid = vid[u] != s.null_value_id;  // rows past the end carry null_value_id
-        key[u] = valid ? dict_gather<K>(s, vid[u]) : K(0);  // NULL decodes to T{} (dictionary_column_iterable.hpp:80)
-        vbits |= (valid ? 1u : 0u) << u;
-      }
-    } else {
-#pragma unroll
-      for (int u = 0; u < ITEMS; ++u) {
-        const uint32_t i = u * VT + vt;
-        key[u] = K(0);
-        if (i < cnt) {
-          key[u] = load_plain_key<K>(s, r0 + i);
-          const bool valid = !(s.nulls && __ldg(s.nulls + r0 + i));
-          if (s.kind == 2 && !valid) key[u] = K(0);  // GATHERED NULL yields T{} (reference_column_iterable.hpp:60)
-          vbits |= (valid ? 1u : 0u) << u;
-        }
-      }
-    }
+    uint32_t vbits;  // bit u: row u*VT+vt is valid (non-NULL)
+    load_tile_keys<K, ITEMS, VT>(s, r0, cnt, vt, key, vbits);
 #if HJ_TUNE_P1_PREFETCH
     // the virtual CTA's next tile: pull its attribute vector / value lines into L2 while this tile is ranked and staged
     // (no registers held across the tile, unlike a software-pipelined load)
@@ -178,38 +246,47 @@ __global__ void __launch_bounds__(NT) k_part1(RelMeta rel, Tuple<K, false>* __re
     }
     vbar(v, VT);
     {
+      // fragment starts are 16-byte aligned inside the slab (pass 2 fetches fragments with TMA bulk copies): a digit with an
+      // odd number of 8-byte tuples is followed by a hole, a tuple whose position is kHoleIdx
       const uint32_t cd = vt < F1 ? s_cnt[v][vt] : 0u;
       uint32_t total;
-      const uint32_t ex = vblock_excl_scan<VT>(cd, v, vt, s_scratch[v], &total);
-      if (vt < F1) s_loff[v][vt] = ex;
+      const uint32_t ex = vblock_excl_scan<VT>(slab_pad<T>(cd), v, vt, s_scratch[v], &total);
+      if (vt < F1) {
+        s_loff[v][vt] = ex;
+        if (slab_pad<T>(cd) != cd) stile[ex + cd] = hole_tuple<K>();
+      }
       if (vt == 0) {
+        const uint32_t cn = s_cnt[v][F1];
         s_loff[v][F1] = total;
-        s_loff[v][F1 + 1] = total + s_cnt[v][F1];
+        s_loff[v][F1 + 1] = total + slab_pad<T>(cn);
+        if (slab_pad<T>(cn) != cn) stile[total + cn] = hole_tuple<K>();
       }
     }
     vbar(v, VT);
+    {
+      const uint32_t idx0 = s.row_begin + r0;
 #pragma unroll
-    for (int u = 0; u < ITEMS; ++u) {
-      if (packed[u] != kNoDigit) {
-        const uint32_t pos = s_loff[v][packed[u] >> 16] + (packed[u] & 0xFFFFu);
-        skey[pos] = key[u];
-        srow[pos] = static_cast<uint16_t>(u * VT + vt);
+      for (int u = 0; u < ITEMS; ++u) {
+        if (packed[u] != kNoDigit) {
+          T t;
+          t.key = key[u];
+          t.idx = idx0 + u * VT + vt;
+          if constexpr (sizeof(K) == 8) t.pad = 0;
+          stile[s_loff[v][packed[u] >> 16] + (packed[u] & 0xFFFFu)] = t;
+        }
       }
-    }
-    for (uint32_t d = vt; d < FS; d += VT) frag[static_cast<size_t>(tile) * FS + d] = static_cast<uint16_t>(s_loff[v][d]);
-    vbar(v, VT);
-    const uint32_t n_out = s_loff[v][F1 + 1];
-    T* dst = out1 + s.row_begin + r0;  // the slab: this tile's own rows' place
-    const uint32_t idx0 = s.row_begin + r0;
-#pragma unroll
-    for (int u = 0; u < ITEMS; ++u) {
-      const uint32_t i = u * VT + vt;
-      if (i < n_out) {
-        T t;
-        t.key = skey[i];
-        t.idx = idx0 + srow[i];
-        if constexpr (sizeof(K) == 8) t.pad = 0;
-        dst[i] = t;
+      for (uint32_t d = vt; d < FS; d += VT) frag[static_cast<size_t>(tile) * FS + d] = static_cast<uint16_t>(s_loff[v][d]);
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // the staged tuples, for the TMA engine's reads
+      vbar(v, VT);
+      // the slab goes out with ONE bulk copy of the TMA engine (measured against per-thread stores: P1 7.77 -> 7.61 ms on C2,
+      // profiles/r02_sweep_tma_variants.md); its size is a multiple of 16 bytes by construction
+      const uint32_t n_out = s_loff[v][F1 + 1];
+      if (vt == 0 && n_out) {
+        T* dst = out1 + static_cast<size_t>(tile) * slab;
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_addr_of(stile)),
+                     "r"(n_out * static_cast<uint32_t>(sizeof(T))) : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // staging may be overwritten after this
       }
     }
   }
@@ -236,9 +313,8 @@ __global__ void __launch_bounds__(NT) k_part1(RelMeta rel, Tuple<K, false>* __re
 // load per row fewer than staging (key, row) pairs.
 // XCH: the relation consists of kSegExch8 segments (rows received from the multi-GPU exchange as finished tuples:
 // int32 joins (hash, source position), int64 joins (key, source position, source rank)); an element is the whole tuple.
-// dynamic smem: (2^radix_bits + 1) * 4 (rounded up to 16) + VC * TILE * (2 * sizeof(E) + 2).
+// dynamic smem: (2^radix_bits + 1) * 4 (rounded up to 16) + VC * (TILE * 2 * sizeof(E) + (TILE + kSlabPad) * 2).
 // =====================================================================================================================
-__device__ __forceinline__ uint32_t smem_addr_of(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
 template <int BYTES>
 __device__ __forceinline__ void cp_async_small(void* dst_smem, const void* src) {
   static_assert(BYTES == 4 || BYTES == 8 || BYTES == 16, "cp.async copies 4, 8 or 16 bytes");
@@ -265,7 +341,7 @@ template <typename K> struct P1Elem<K, true> { using type = Tuple<K, false>; };
 
 template <typename K, int NT, int VC, int TILE, bool XCH>
 __global__ void __launch_bounds__(NT) k_part1p(RelMeta rel, Tuple<K, false>* __restrict__ out1, uint16_t* __restrict__ frag,
-                                               uint32_t* __restrict__ hist, int radix_bits, int bits2, int null_policy) {
+                                               uint32_t* __restrict__ hist, int radix_bits, int bits2, int null_policy, uint32_t slab) {
   using T = Tuple<K, false>;
   using E = typename P1Elem<K, XCH>::type;
   constexpr int VT = NT / VC;
@@ -283,7 +359,7 @@ __global__ void __launch_bounds__(NT) k_part1p(RelMeta rel, Tuple<K, false>* __r
   const uint32_t v = threadIdx.x / VT, vt = threadIdx.x % VT;
   const uint32_t G = gridDim.x * VC, c = blockIdx.x * VC + v;
   E* kbuf = reinterpret_cast<E*>(buf_raw) + static_cast<size_t>(v) * 2 * TILE;  // [2][TILE]
-  uint16_t* perm = reinterpret_cast<uint16_t*>(buf_raw + static_cast<size_t>(VC) * 2 * TILE * sizeof(E)) + v * TILE;
+  uint16_t* perm = reinterpret_cast<uint16_t*>(buf_raw + static_cast<size_t>(VC) * 2 * TILE * sizeof(E)) + v * (TILE + kSlabPad);
   for (uint32_t b = threadIdx.x; b < n_bins; b += NT) s_hist[b] = 0;
   __syncthreads();
 
@@ -384,13 +460,18 @@ __global__ void __launch_bounds__(NT) k_part1p(RelMeta rel, Tuple<K, false>* __r
     }
     vbar(v, VT);
     {
-      const uint32_t cd = vt < F1 ? s_cnt[v][vt] : 0u;
+      const uint32_t cd = vt < F1 ? s_cnt[v][vt] : 0u;  // fragments start on 16-byte boundaries: holes (see slab_pad)
       uint32_t total;
-      const uint32_t ex = vblock_excl_scan<VT>(cd, v, vt, s_scratch[v], &total);
-      if (vt < F1) s_loff[v][vt] = ex;
+      const uint32_t ex = vblock_excl_scan<VT>(slab_pad<T>(cd), v, vt, s_scratch[v], &total);
+      if (vt < F1) {
+        s_loff[v][vt] = ex;
+        if (slab_pad<T>(cd) != cd) perm[ex + cd] = 0xFFFFu;
+      }
       if (vt == 0) {
+        const uint32_t cn = s_cnt[v][F1];
         s_loff[v][F1] = total;
-        s_loff[v][F1 + 1] = total + s_cnt[v][F1];
+        s_loff[v][F1 + 1] = total + slab_pad<T>(cn);
+        if (slab_pad<T>(cn) != cn) perm[total + cn] = 0xFFFFu;
       }
     }
     vbar(v, VT);
@@ -399,16 +480,18 @@ __global__ void __launch_bounds__(NT) k_part1p(RelMeta rel, Tuple<K, false>* __r
       if (packed[u] != kNoDigit) perm[s_loff[v][packed[u] >> 16] + (packed[u] & 0xFFFFu)] = static_cast<uint16_t>(u * VT + vt);
     for (uint32_t d = vt; d < FS; d += VT) frag[static_cast<size_t>(tile) * FS + d] = static_cast<uint16_t>(s_loff[v][d]);
     vbar(v, VT);  // perm complete; every thread's cp.async data and NULL fix-ups are visible to the others
-    const uint32_t n_out = s_loff[v][F1 + 1];
-    T* dst = out1 + s.row_begin + r0;  // the slab: this tile's own rows' place
+    const uint32_t n_out = s_loff[v][F1 + 1];  // <= TILE + F1 + 1
+    T* dst = out1 + static_cast<size_t>(tile) * slab;
     const uint32_t idx0 = s.row_begin + r0;
 #pragma unroll
-    for (int u = 0; u < ITEMS; ++u) {
+    for (int u = 0; u <= ITEMS; ++u) {
       const uint32_t i = u * VT + vt;
       if (i < n_out) {
         const uint32_t r = perm[i];
         T t;
-        if constexpr (XCH) {
+        if (r == 0xFFFFu) {
+          t = hole_tuple<K>();
+        } else if constexpr (XCH) {
           t = kb[r];
           // the source rank (= the receive region, chunk_id): int64 tuples have a spare word; an int32 tuple's key field is
           // the key's hash, whose level-1 digit bits are redundant from here on (this fragment IS that digit)
@@ -444,7 +527,7 @@ __global__ void __launch_bounds__(NT) k_part1p(RelMeta rel, Tuple<K, false>* __r
 // =====================================================================================================================
 template <typename K, int NT, int ITEMS, int MINB, bool PRE = false>
 __global__ void __launch_bounds__(NT, MINB) k_scatter2f(const Tuple<K, false>* __restrict__ in, const uint16_t* __restrict__ frag,
-                                                            RelMeta rel, uint32_t tile1, Tuple<K, false>* __restrict__ out,
+                                                            uint32_t n_tiles, uint32_t slab, Tuple<K, false>* __restrict__ out,
                                                             uint32_t* __restrict__ cur2, int radix_bits, int bits2, uint32_t gs,
                                                             uint32_t n_digits) {
   using T = Tuple<K, false>;
@@ -476,7 +559,7 @@ __global__ void __launch_bounds__(NT, MINB) k_scatter2f(const Tuple<K, false>* _
 
   const uint32_t P = 1u << radix_bits, F1 = P >> bits2, FS = F1 + 2u;
   const uint32_t group = blockIdx.x / n_digits, d1 = blockIdx.x % n_digits;
-  const uint32_t s0 = group * gs, ns = min(gs, rel.n_tiles - s0);  // gs < NT
+  const uint32_t s0 = group * gs, ns = min(gs, n_tiles - s0);  // gs < NT
   const bool null_item = d1 == F1;
   const uint32_t F2 = null_item ? 1u : 1u << bits2;
   uint32_t* cursors = cur2 + (null_item ? P : d1 << bits2);
@@ -486,9 +569,8 @@ __global__ void __launch_bounds__(NT, MINB) k_scatter2f(const Tuple<K, false>* _
     const uint32_t tile = s0 + threadIdx.x;
     const uint16_t* f = frag + static_cast<size_t>(tile) * FS + d1;
     const uint32_t f0 = __ldg(f), f1 = __ldg(f + 1);
-    const DevSegment* sg = rel.segs + __ldg(rel.tile_seg + tile);
-    src = sg->row_begin + (tile - sg->tile_begin) * tile1 + f0;
-    len = f1 - f0;
+    src = tile * slab + f0;
+    len = f1 - f0;  // holes included
   }
   uint32_t total;
   const uint32_t pre = block_excl_scan(len, scratch, &total);
@@ -526,16 +608,16 @@ __global__ void __launch_bounds__(NT, MINB) k_scatter2f(const Tuple<K, false>* _
     for (int j = 0; j < ITEMS; ++j) {
       const uint32_t i = j * NT + threadIdx.x;
       packed[j] = kNoDigit;
-      if (i < n_in) {
+      if (i < n_in && tup[j].idx != kHoleIdx) {
         const uint32_t d = tuple_hash<PRE>(tup[j].key) & (F2 - 1u);
         packed[j] = (d << 16) | atomicAdd(&s_cnt[d], 1u);
       }
     }
     __syncthreads();
+    uint32_t tot;
     {
       const uint32_t d = threadIdx.x;
       const uint32_t c = d < F2 ? s_cnt[d] : 0u;
-      uint32_t tot;
       const uint32_t ex = block_excl_scan(c, scratch, &tot);
       if (d < F2) {
         s_loff[d] = ex;
@@ -548,7 +630,121 @@ __global__ void __launch_bounds__(NT, MINB) k_scatter2f(const Tuple<K, false>* _
       if (packed[j] != kNoDigit) stage[s_loff[packed[j] >> 16] + (packed[j] & 0xFFFFu)] = tup[j];
     }
     __syncthreads();
-    copy_tile_out<K, false, NT, ITEMS, PRE>(stage, s_delta, out, n_in, F2 - 1u, 0, 0xFFFFFFFFu, 0u);
+    copy_tile_out<K, false, NT, ITEMS, PRE>(stage, s_delta, out, tot, F2 - 1u, 0, 0xFFFFFFFFu, 0u);
+  }
+}
+
+// =====================================================================================================================
+// P2t. Pass 2 with the fragments fetched by the TMA engine (the default since round 2; k_scatter2f above is the same pass
+// with per-thread loads, kept for the variant sweep). Same work items as k_scatter2f. The item's fragments — contiguous,
+// 16-byte aligned runs of the slabs (see slab_pad) — are copied into the shared-memory tile with one cp.async.bulk per
+// fragment, all tracked by ONE mbarrier (expect_tx = the batch's bytes); the threads then read their tuples from the tile
+// with coalesced shared-memory loads. That removes what made k_scatter2f issue-bound (66 % issue slots, ~125 instructions
+// per tuple): the fragment-owner table, the per-tuple owner search and flat-index arithmetic, and 16 scattered global loads
+// per thread. Holes (odd fragments of 8-byte tuples) arrive with the data and are skipped by their position field.
+// The tile is then reused as the staging area of the ranking/copy-out exactly as in k_scatter2f.
+// dynamic smem: TILE * sizeof(Tuple<K>).
+// =====================================================================================================================
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr_of(bar)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr_of(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t parity) {
+  uint32_t done = 0;
+  while (!done)
+    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                 : "=r"(done) : "r"(smem_addr_of(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32_t bytes, unsigned long long* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_addr_of(dst_smem)),
+               "l"(src), "r"(bytes), "r"(smem_addr_of(bar)) : "memory");
+}
+
+template <typename K, int NT, int ITEMS, int MINB, bool PRE = false>
+__global__ void __launch_bounds__(NT, MINB) k_scatter2t(const Tuple<K, false>* __restrict__ in, const uint16_t* __restrict__ frag,
+                                                            uint32_t n_tiles, uint32_t slab, Tuple<K, false>* __restrict__ out,
+                                                            uint32_t* __restrict__ cur2, int radix_bits, int bits2, uint32_t gs,
+                                                            uint32_t n_digits) {
+  using T = Tuple<K, false>;
+  constexpr uint32_t TILE = NT * ITEMS;
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  T* stage = reinterpret_cast<T*>(s_raw);
+  struct Sm {
+    uint32_t cnt[kMaxDigits], loff[kMaxDigits], delta[kMaxDigits];
+    uint32_t scratch[33];
+    uint32_t pad;
+    unsigned long long bar;
+  };
+  __shared__ __align__(8) Sm sm;
+  const uint32_t P = 1u << radix_bits, F1 = P >> bits2, FS = F1 + 2u;
+  const uint32_t group = blockIdx.x / n_digits, d1 = blockIdx.x % n_digits;
+  const uint32_t s0 = group * gs, ns = min(gs, n_tiles - s0);  // gs < NT
+  const bool null_item = d1 == F1;
+  const uint32_t F2 = null_item ? 1u : 1u << bits2;
+  uint32_t* cursors = cur2 + (null_item ? P : d1 << bits2);
+  if (threadIdx.x == 0) mbar_init(&sm.bar, 1);
+
+  uint32_t len = 0, src = 0;  // this thread's fragment: first tuple (index into `in`; the host checked that it fits 32 bits), tuples
+  if (threadIdx.x < ns) {
+    const uint32_t tile = s0 + threadIdx.x;
+    const uint16_t* f = frag + static_cast<size_t>(tile) * FS + d1;
+    const uint32_t f0 = __ldg(f), f1 = __ldg(f + 1);
+    src = tile * slab + f0;
+    len = f1 - f0;  // holes included: even for 8-byte tuples, like f0
+  }
+  uint32_t total;
+  const uint32_t pre = block_excl_scan(len, sm.scratch, &total);  // its barriers also publish the mbarrier's initialisation
+  uint32_t phase = 0;
+  for (uint32_t lo = 0; lo < total; lo += TILE, phase ^= 1u) {
+    const uint32_t n_in = min(TILE, total - lo);
+    for (uint32_t d = threadIdx.x; d < F2; d += NT) sm.cnt[d] = 0;
+    __syncthreads();  // the previous batch's copy-out has read the tile: the TMA engine may overwrite it
+    if (threadIdx.x == 0) mbar_expect_tx(&sm.bar, n_in * static_cast<uint32_t>(sizeof(T)));
+    if (len) {
+      const uint32_t a = max(pre, lo), b = min(pre + len, lo + TILE);  // this fragment's part of the batch (even bounds)
+      if (a < b) bulk_g2s(stage + (a - lo), in + (src + (a - pre)), (b - a) * static_cast<uint32_t>(sizeof(T)), &sm.bar);
+    }
+    mbar_wait(&sm.bar, phase);
+
+    // the tile's tuples go to registers; a tuple's rank inside its digit is kept as 16 bits (two per register) and the digit
+    // is re-derived from the key when the tuple is staged: 8 registers less than a (digit, rank) word per tuple, which is what
+    // the kernel needs to stay inside the 64 registers that four CTAs per SM allow without spilling
+    static_assert(ITEMS % 2 == 0, "ranks are packed in pairs");
+    T tup[ITEMS];
+    uint32_t rank2[ITEMS / 2];
+#pragma unroll
+    for (int j = 0; j < ITEMS; ++j) {
+      const uint32_t i = j * NT + threadIdx.x;
+      uint32_t r = 0;
+      tup[j].idx = kHoleIdx;
+      if (i < n_in) {
+        tup[j] = stage[i];
+        if (tup[j].idx != kHoleIdx) r = atomicAdd(&sm.cnt[tuple_hash<PRE>(tup[j].key) & (F2 - 1u)], 1u);
+      }
+      if (j & 1) rank2[j / 2] |= r << 16; else rank2[j / 2] = r;
+    }
+    __syncthreads();  // every tuple of the tile is in registers; the counts are complete
+    uint32_t tot;
+    {
+      const uint32_t d = threadIdx.x;
+      const uint32_t c = d < F2 ? sm.cnt[d] : 0u;
+      const uint32_t ex = block_excl_scan(c, sm.scratch, &tot);
+      if (d < F2) {
+        sm.loff[d] = ex;
+        if (c) sm.delta[d] = atomicAdd(cursors + d, c) - ex;
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < ITEMS; ++j) {
+      if (tup[j].idx != kHoleIdx)
+        stage[sm.loff[tuple_hash<PRE>(tup[j].key) & (F2 - 1u)] + ((rank2[j / 2] >> ((j & 1) * 16)) & 0xFFFFu)] = tup[j];
+    }
+    __syncthreads();
+    copy_tile_out<K, false, NT, ITEMS, PRE>(stage, sm.delta, out, tot, F2 - 1u, 0, 0xFFFFFFFFu, 0u);
   }
 }
 

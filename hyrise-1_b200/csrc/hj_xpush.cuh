@@ -53,7 +53,6 @@ __global__ void __launch_bounds__(NT) k_xchg_push(const XpushArgs a) {
   __shared__ uint32_t s_pos0[VC][kMaxRanks], s_first[VC][kMaxRanks], s_pos1[VC][kMaxRanks];  // this tile's run: where it goes
   __shared__ uint32_t s_open[VC][kMaxRanks], s_left[VC][kMaxRanks];                          // open chunk (index, free tuples)
   const uint32_t v = threadIdx.x / VT, vt = threadIdx.x % VT;
-  const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
   const uint32_t G = gridDim.x * VC, c = blockIdx.x * VC + v;
   const uint32_t R = a.n_ranks;
   if (vt < kMaxRanks) {
@@ -66,52 +65,23 @@ __global__ void __launch_bounds__(NT) k_xchg_push(const XpushArgs a) {
     const uint32_t cnt = min(static_cast<uint32_t>(TILE), s.n_rows - r0);
     if (vt < kMaxRanks) s_cnt[v][vt] = 0;
     K key[ITEMS];
-    uint32_t vbits = 0;
-    if (s.kind == 1) {
-      uint32_t vid[ITEMS];
-#pragma unroll
-      for (int u = 0; u < ITEMS; ++u) {
-        const uint32_t i = u * VT + vt;
-        vid[u] = i < cnt ? load_attr(s, r0 + i) : s.null_value_id;
-      }
-#pragma unroll
-      for (int u = 0; u < ITEMS; ++u) {
-        const bool valid = vid[u] != s.null_value_id;
-        key[u] = valid ? dict_gather<K>(s, vid[u]) : K(0);
-        vbits |= (valid ? 1u : 0u) << u;
-      }
-    } else {
-#pragma unroll
-      for (int u = 0; u < ITEMS; ++u) {
-        const uint32_t i = u * VT + vt;
-        key[u] = K(0);
-        if (i < cnt) {
-          key[u] = load_plain_key<K>(s, r0 + i);
-          const bool valid = !(s.nulls && __ldg(s.nulls + r0 + i));
-          if (s.kind == 2 && !valid) key[u] = K(0);
-          vbits |= (valid ? 1u : 0u) << u;
-        }
-      }
-    }
-    // destination + rank inside (warp, destination) by ballots: R <= 16 destinations, no shared-memory atomics per row
-    uint32_t h[ITEMS], packed[ITEMS];  // packed: destination << 16 | rank inside the warp's rows for that destination
-    uint32_t run = 0;                  // lane q: this warp's rows for destination q so far
+    uint32_t vbits;
+    load_tile_keys<K, ITEMS, VT>(s, r0, cnt, vt, key, vbits);
+    // destination + rank inside the tile's run for that destination: one shared-memory atomic per row. (A ballot loop over
+    // the <= 16 destinations was tried first: 3376 SASS instructions, ~128 executed per row, the kernel half issue-bound —
+    // profiles/r02_ncu_push_p1_summary.md.)
+    vbar(v, VT);  // s_cnt zeroed; the previous tile's copy-out is done with `stage`
+    uint32_t h[ITEMS], packed[ITEMS];  // packed: destination << 16 | rank
 #pragma unroll
     for (int u = 0; u < ITEMS; ++u) {
       const bool kept = u * VT + vt < cnt && (((vbits >> u) & 1u) || a.null_policy == kNullAsValue);
       h[u] = hash_key(key[u]);
-      const uint32_t d = kept ? dest_rank_of_hash(h[u], R) : kNoDigit;
       packed[u] = kNoDigit;
-      for (uint32_t q = 0; q < R; ++q) {
-        const uint32_t bal = __ballot_sync(0xffffffffu, d == q);
-        const uint32_t before = __shfl_sync(0xffffffffu, run, q);
-        if (d == q) packed[u] = (q << 16) | (before + __popc(bal & lt));
-        if (lane == q) run += __popc(bal);
+      if (kept) {
+        const uint32_t d = dest_rank_of_hash(h[u], R);
+        packed[u] = (d << 16) | atomicAdd(&s_cnt[v][d], 1u);
       }
     }
-    vbar(v, VT);  // s_cnt zeroed; the previous tile's copy-out is done with `stage`
-    uint32_t wbase = 0;  // lane q: start of this warp's rows inside the tile's run for destination q
-    if (lane < R && run) wbase = atomicAdd(&s_cnt[v][lane], run);
     vbar(v, VT);
     if (vt == 0) {
       // where the tile's R runs go: the rest of the open chunk, then a fresh one
@@ -138,12 +108,6 @@ __global__ void __launch_bounds__(NT) k_xchg_push(const XpushArgs a) {
         }
       }
       s_loff[v][R] = off;
-    }
-#pragma unroll
-    for (int u = 0; u < ITEMS; ++u) {
-      const uint32_t q = packed[u] >> 16;
-      const uint32_t wb = __shfl_sync(0xffffffffu, wbase, q & 31u);
-      if (packed[u] != kNoDigit) packed[u] += wb;
     }
     vbar(v, VT);
     const uint32_t pos0 = s.row_begin + r0;

@@ -56,7 +56,12 @@ for spec in "$@"; do
                 python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu --no-verify $arg ;;
     ncufull) set -- $arg; rx=$1; skip=${2:-0}; cnt=${3:-4}; w=${4:-c2}; sc=${5:-1.0}
              run ncu$n 1200 ncu --set full --clock-control none --import-source on -k "regex:$rx" -s $skip -c $cnt -o gpurun_out/${TAG}_ncu$n -f \
-                python tests/profile_join.py --workload $w --scale $sc --joins 2 $6 ;;
+                python tests/profile_join.py --workload $w --scale $sc --joins 2 $6
+             # what comes back is text (gpurun_out/ may hold 64 MiB): the raw metrics and the per-line source counters
+             ncu -i gpurun_out/${TAG}_ncu$n.ncu-rep --page raw --csv > gpurun_out/${TAG}_ncu$n.raw.csv 2>/dev/null
+             ncu -i gpurun_out/${TAG}_ncu$n.ncu-rep --page source --csv --print-source cuda 2>/dev/null | gzip -9 > gpurun_out/${TAG}_ncu$n.source.csv.gz
+             ncu -i gpurun_out/${TAG}_ncu$n.ncu-rep --page details --csv 2>/dev/null | gzip -9 > gpurun_out/${TAG}_ncu$n.details.csv.gz
+             [ $(stat -c %s gpurun_out/${TAG}_ncu$n.ncu-rep) -gt 12000000 ] && rm -f gpurun_out/${TAG}_ncu$n.ncu-rep ;;
     prof) run prof$n 300 python tests/profile_join.py --joins 3 $arg ;;
     micro) run micro_$arg 120 tests/micro/$arg ;;
     sharded) run sharded$n 900 $TORCHRUN $((29500 + RANDOM % 400)) tests/sharded_check.py --backend nccl $arg ;;
