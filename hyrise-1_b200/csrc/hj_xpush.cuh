@@ -46,15 +46,18 @@ __global__ void __launch_bounds__(NT) k_xchg_push(const XpushArgs a) {
   using T = Tuple<K, false>;
   constexpr int VT = NT / VC;
   constexpr int ITEMS = TILE / VT;
-  static_assert(TILE == kXpChunk && ITEMS >= 1 && ITEMS <= 32 && VT >= kMaxRanks, "a tile's run to one destination fits one chunk");
+  static_assert(TILE == kXpChunk && ITEMS >= 1 && ITEMS <= 32 && VT >= 32 && kMaxRanks * 2 <= 32, "a tile's run to one destination fits one chunk");
   extern __shared__ __align__(16) unsigned char s_raw[];
   T* stage = reinterpret_cast<T*>(s_raw) + static_cast<size_t>(threadIdx.x / VT) * TILE;
-  __shared__ uint32_t s_cnt[VC][kMaxRanks], s_loff[VC][kMaxRanks + 1];
-  __shared__ uint32_t s_pos0[VC][kMaxRanks], s_first[VC][kMaxRanks], s_pos1[VC][kMaxRanks];  // this tile's run: where it goes
+  __shared__ uint32_t s_cnt[VC][32], s_loff[VC][32];
+  __shared__ uint32_t s_run[VC][kMaxRanks], s_n[VC][kMaxRanks];                              // this tile's run per destination
+  __shared__ uint32_t s_pos0[VC][kMaxRanks], s_first[VC][kMaxRanks], s_pos1[VC][kMaxRanks];  // ... and where it goes
   __shared__ uint32_t s_open[VC][kMaxRanks], s_left[VC][kMaxRanks];                          // open chunk (index, free tuples)
   const uint32_t v = threadIdx.x / VT, vt = threadIdx.x % VT;
   const uint32_t G = gridDim.x * VC, c = blockIdx.x * VC + v;
   const uint32_t R = a.n_ranks;
+  const uint32_t nb = R > 1 ? 32u - __clz(R - 1u) : 0u;  // bits of a destination number
+  const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
   if (vt < kMaxRanks) {
     s_open[v][vt] = kInvalid;
     s_left[v][vt] = 0;
@@ -63,34 +66,51 @@ __global__ void __launch_bounds__(NT) k_xchg_push(const XpushArgs a) {
     const DevSegment s = a.rel.segs[__ldg(a.rel.tile_seg + tile)];
     const uint32_t r0 = (tile - s.tile_begin) * TILE;
     const uint32_t cnt = min(static_cast<uint32_t>(TILE), s.n_rows - r0);
-    if (vt < kMaxRanks) s_cnt[v][vt] = 0;
+    if (vt < 32) s_cnt[v][vt] = 0;
     K key[ITEMS];
     uint32_t vbits;
     load_tile_keys<K, ITEMS, VT>(s, r0, cnt, vt, key, vbits);
-    // destination + rank inside the tile's run for that destination: one shared-memory atomic per row. (A ballot loop over
-    // the <= 16 destinations was tried first: 3376 SASS instructions, ~128 executed per row, the kernel half issue-bound —
-    // profiles/r02_ncu_push_p1_summary.md.)
+    // Destination + rank inside the tile's run for that destination, WITHOUT a shared-memory atomic per row: the lanes of a
+    // warp that go to the same destination find each other with one ballot per destination bit (<= 4), the first of them
+    // reserves the group's ranks with one atomic, the others derive theirs from their place in the group. Consecutive lanes
+    // of a group get consecutive ranks, so the staging stores below stay bank-conflict free.
+    // Measured alternatives for 1 B rows through ONE rank (tests/profile_join.py --sharded): a ballot per DESTINATION (loop
+    // over R) 7.1 ms but 3 376 SASS instructions and ~80 more executed per row at R = 8; one atomic per row on R x 4
+    // sub-counters 8.4 ms, on 32 sub-counters 10.6 ms (the sub-runs make the staging stores 4- / 32-way bank conflicts).
     vbar(v, VT);  // s_cnt zeroed; the previous tile's copy-out is done with `stage`
     uint32_t h[ITEMS], packed[ITEMS];  // packed: destination << 16 | rank
 #pragma unroll
     for (int u = 0; u < ITEMS; ++u) {
       const bool kept = u * VT + vt < cnt && (((vbits >> u) & 1u) || a.null_policy == kNullAsValue);
       h[u] = hash_key(key[u]);
-      packed[u] = kNoDigit;
-      if (kept) {
-        const uint32_t d = dest_rank_of_hash(h[u], R);
-        packed[u] = (d << 16) | atomicAdd(&s_cnt[v][d], 1u);
+      const uint32_t d = kept ? dest_rank_of_hash(h[u], R) : 0u;
+      uint32_t peers = __ballot_sync(0xffffffffu, kept);
+#pragma unroll
+      for (uint32_t bit = 0; bit < 4; ++bit) {
+        if (bit < nb) {  // uniform
+          const uint32_t m = __ballot_sync(0xffffffffu, (d >> bit) & 1u);
+          peers &= ((d >> bit) & 1u) ? m : ~m;
+        }
       }
+      packed[u] = kNoDigit;
+      const int leader = __ffs(peers) - 1;  // peers is only meaningful in kept lanes; it contains the lane itself there
+      uint32_t base = 0;
+      if (kept && static_cast<int>(lane) == leader) base = atomicAdd(&s_cnt[v][d], __popc(peers));
+      base = __shfl_sync(0xffffffffu, base, kept ? leader : 0);
+      if (kept) packed[u] = (d << 16) | (base + __popc(peers & lt));
     }
     vbar(v, VT);
-    if (vt == 0) {
-      // where the tile's R runs go: the rest of the open chunk, then a fresh one
-      uint32_t off = 0;
-      for (uint32_t q = 0; q < R; ++q) {
-        const uint32_t n = s_cnt[v][q];
-        s_loff[v][q] = off;
-        off += n;
-        uint32_t left = s_left[v][q], open = s_open[v][q];
+    if (vt < 32) {
+      // the virtual CTA's first warp, lane q = destination q: prefix sum -> where the tile's run for q is staged; then q's
+      // run is placed: the rest of the open chunk, then a fresh one
+      const uint32_t q = vt;
+      const uint32_t n = q < R ? s_cnt[v][q] : 0u;
+      const uint32_t ex = warp_incl_scan(n) - n;
+      if (q < R) {
+        s_loff[v][q] = ex;
+        s_run[v][q] = ex;
+        s_n[v][q] = n;
+        const uint32_t left = s_left[v][q], open = s_open[v][q];
         s_pos0[v][q] = open * kXpChunk + (kXpChunk - left);  // unused when left == 0
         s_first[v][q] = left;
         if (n > left) {
@@ -107,7 +127,6 @@ __global__ void __launch_bounds__(NT) k_xchg_push(const XpushArgs a) {
           s_left[v][q] = left - n;
         }
       }
-      s_loff[v][R] = off;
     }
     vbar(v, VT);
     const uint32_t pos0 = s.row_begin + r0;
@@ -127,10 +146,10 @@ __global__ void __launch_bounds__(NT) k_xchg_push(const XpushArgs a) {
     }
     vbar(v, VT);
     for (uint32_t q = 0; q < R; ++q) {
-      const uint32_t n = s_loff[v][q + 1] - s_loff[v][q];
+      const uint32_t n = s_n[v][q];
       if (n == 0) continue;  // uniform over the virtual CTA
       T* dst = static_cast<T*>(a.dst_tuples[q]);
-      const T* src = stage + s_loff[v][q];
+      const T* src = stage + s_run[v][q];
       const uint32_t first = s_first[v][q], p0 = s_pos0[v][q], p1 = s_pos1[v][q];
       for (uint32_t i = vt; i < n; i += VT) dst[i < first ? p0 + i : p1 + (i - first)] = src[i];
     }
