@@ -580,12 +580,12 @@ def main():
             ok = int(okt.item())
         if ok:
             def e2e_step():
+                # the operator's call sequence for host tables: bind the PosLists, join (streamed: copy-in, [exchange +] join
+                # and copy-out of probe slices overlap), fetch (a no-op after a bound join)
+                j.bind_output(out_b, out_p)
                 if world > 1:
                     inf_ = j.join_sharded(build_host, probe_host, abi.MODE_INNER, stream=stream)
                 else:
-                    # the operator's call sequence for host tables: bind the PosLists, join (streamed: copy-in, join and
-                    # copy-out of probe slices overlap), fetch (a no-op after a bound join)
-                    j.bind_output(out_b, out_p)
                     inf_ = j.join(build_host, probe_host, abi.MODE_INNER, stream=stream)
                 j.fetch(out_b, out_p)
                 return inf_

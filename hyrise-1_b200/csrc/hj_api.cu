@@ -108,7 +108,7 @@ thread_local std::string g_create_error;
 
 }  // namespace
 
-constexpr int kSides = 5;
+constexpr int kSides = 6;
 // pinned readback area: Readback at 0, exchange count matrices at kPinnedCounts, IPC handle records at kPinnedHandles
 constexpr size_t kPinnedBytes = 96 * 1024, kPinnedRefFlags = 3584, kPinnedCounts = 4096, kPinnedHandles = 64 * 1024;
 
@@ -2225,6 +2225,11 @@ int hj_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, int
             hj_result_info* out_info) {
   if (!ctx) return HJ_ERR_INVALID;
   ctx->has_result = false;
+  // a binding (hj_bind_output) holds for exactly one join, whether that join succeeds or not: it is consumed before anything
+  // can fail, so that a later unbound join never streams into buffers the caller may have freed
+  const bool bound = ctx->bound;
+  ctx->bound = false;
+  ctx->result_in_bound = false;
   if (!out_info) return fail(ctx, HJ_ERR_INVALID, "out_info is NULL");
   std::memset(out_info, 0, sizeof(*out_info));
   if (!(mode == HJ_MODE_INNER || mode == HJ_MODE_LEFT || mode == HJ_MODE_RIGHT || mode == HJ_MODE_SEMI || mode == HJ_MODE_ANTI))
@@ -2236,9 +2241,6 @@ int hj_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, int
   // JoinHashTraits: int32 x int64 hashes as int64, anything with a float/double column as that floating type
   const uint32_t hash_type = hashed_type_of(build, probe);
   const bool wide = hash_type == HJ_KEY_INT64 || hash_type == HJ_KEY_DOUBLE;  // 8-byte keys in the pipeline
-  const bool bound = ctx->bound;
-  ctx->bound = false;  // a binding holds for one join
-  ctx->result_in_bound = false;
   RefRewrite rw[2];  // REFERENCE segments -> gathered on the device (N1)
   HJ_TRY(gather_both(ctx, build, probe, st, rw, hash_type));
   const int status = join_dispatch(ctx, build, probe, mode, st, out_info, wide, bound);

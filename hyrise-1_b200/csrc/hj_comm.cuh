@@ -1015,11 +1015,26 @@ int hj_join_sharded(hj_ctx* ctx, const hj_relation* build_shard, const hj_relati
                     void* cuda_stream, hj_result_info* out_info) {
   if (!ctx) return HJ_ERR_INVALID;
   ctx->has_result = false;
+  const bool bound = ctx->bound;  // hj_bind_output: consumed by this join whatever happens (see hj_join)
+  ctx->bound = false;
+  ctx->result_in_bound = false;
   if (!out_info) return fail(ctx, HJ_ERR_INVALID, "out_info is NULL");
   std::memset(out_info, 0, sizeof(*out_info));
   if (!(mode == HJ_MODE_INNER || mode == HJ_MODE_LEFT || mode == HJ_MODE_RIGHT || mode == HJ_MODE_SEMI || mode == HJ_MODE_ANTI))
     return fail(ctx, HJ_ERR_INVALID, "JoinMode %d is not supported by JoinHash (Inner/Left/Right/Semi/Anti only)", mode);
   if (!ctx->nccl_comm) return fail(ctx, HJ_ERR_COMM, "hj_join_sharded without hj_comm_init");
+  const bool one_side_mode = mode == HJ_MODE_SEMI || mode == HJ_MODE_ANTI;
+  if (bound && (!ctx->bound_probe || (!one_side_mode && !ctx->bound_build))) return fail(ctx, HJ_ERR_INVALID, "hj_bind_output: NULL output buffer");
+  // the join's result into the bound host buffers (joins that were not streamed)
+  auto deliver_bound = [&]() -> int {
+    if (!bound) return HJ_OK;
+    if (out_info->n_rows > ctx->bound_capacity)
+      return fail(ctx, HJ_ERR_CAPACITY, "bound output holds %llu rows, this rank's result has %llu (still on the device: hj_fetch it)",
+                  (unsigned long long)ctx->bound_capacity, (unsigned long long)out_info->n_rows);
+    HJ_TRY(hj_fetch(ctx, one_side_mode ? nullptr : ctx->bound_build, ctx->bound_probe, ctx->bound_capacity));
+    ctx->result_in_bound = true;
+    return HJ_OK;
+  };
   HJ_TRY(validate_relation(ctx, build_shard, "build"));
   HJ_TRY(validate_relation(ctx, probe_shard, "probe"));
   HJ_TRY(check_ctx(ctx));
@@ -1041,22 +1056,24 @@ int hj_join_sharded(hj_ctx* ctx, const hj_relation* build_shard, const hj_relati
   const bool outer_mode = mode == HJ_MODE_LEFT || mode == HJ_MODE_RIGHT;
   const ShardGeometry gb = shard_geometry(build_shard), gp = shard_geometry(probe_shard);
   const bool push_here = direct && gb.regular && gp.regular && !(ctx->opts.flags & (HJ_FLAG_XCHG_GENERAL | HJ_FLAG_TWO_SWEEP_PARTITION)) &&
-                         !(outer_mode && (ctx->opts.flags & HJ_FLAG_SQL_NULL_PROBE)) && !ctx->opts.stream_slice_rows;
+                         !(outer_mode && (ctx->opts.flags & HJ_FLAG_SQL_NULL_PROBE)) && (bound || !ctx->opts.stream_slice_rows);
   unsigned long long word[kXpDescWords] = {build_shard->n_rows, probe_shard->n_rows,
                                            gb.first_chunk | (static_cast<unsigned long long>(static_cast<uint32_t>(gb.shift)) << 32),
                                            gp.first_chunk | (static_cast<unsigned long long>(static_cast<uint32_t>(gp.shift)) << 32),
-                                           wide | (push_here ? 2ull : 0ull), 0, 0, 0};
+                                           wide | (push_here ? 2ull : 0ull) | ((bound && probe_shard->location == HJ_LOC_HOST) ? 4ull : 0ull),
+                                           probe_shard->n_segs ? probe_shard->segs[0].n_rows : 0ull, 0, 0};
   HJ_CUDA(ctx, cudaMemcpyAsync(dev, word, sizeof(word), cudaMemcpyHostToDevice, st));
   HJ_NCCL(ctx, nc->AllGather(dev, dev + kXpDescWords, kXpDescWords, ncclUint64, static_cast<ncclComm_t>(ctx->nccl_comm), st));
   std::vector<unsigned long long> desc(size_t(ctx->n_ranks) * kXpDescWords);
   HJ_CUDA(ctx, cudaMemcpyAsync(host, dev + kXpDescWords, desc.size() * 8, cudaMemcpyDeviceToHost, st));
   HJ_CUDA(ctx, cudaStreamSynchronize(st));
   std::memcpy(desc.data(), host, desc.size() * 8);  // the pinned area is reused by the joins below
-  bool push = true;
+  bool push = true, streamable = true;
   uint64_t max_probe_rows = 0, total_build = 0;
   for (int r = 0; r < ctx->n_ranks; ++r) {
     wide |= desc[size_t(r) * kXpDescWords + 4] & 1ull;
     push = push && (desc[size_t(r) * kXpDescWords + 4] & 2ull);
+    streamable = streamable && (desc[size_t(r) * kXpDescWords + 4] & 4ull);
     max_probe_rows = std::max<uint64_t>(max_probe_rows, desc[size_t(r) * kXpDescWords + 1]);
     total_build += desc[size_t(r) * kXpDescWords + 0];
   }
@@ -1067,10 +1084,22 @@ int hj_join_sharded(hj_ctx* ctx, const hj_relation* build_shard, const hj_relati
   push = push && pass2_bits(xp_bits) > 0 && (1 << (xp_bits - pass2_bits(xp_bits))) >= ctx->n_ranks;
   if (push) {
     bool fell_back = false;
-    const int st_push = wide ? run_join_sharded_push<int64_t>(ctx, build_shard, probe_shard, mode, st, out_info, desc.data(), xp_bits, &fell_back)
-                             : run_join_sharded_push<int32_t>(ctx, build_shard, probe_shard, mode, st, out_info, desc.data(), xp_bits, &fell_back);
+    // every rank bound host outputs for host-resident probe shards and the shards are long enough: streamed (copy-in, exchange
+    // + join, copy-out of probe slices overlap), with the same number of slices on every rank
+    const uint64_t min_slice = ctx->opts.stream_slice_rows ? ctx->opts.stream_slice_rows : kMinSliceRows;
+    const uint32_t n_slices = streamable ? uint32_t(std::min<uint64_t>(24, max_probe_rows / min_slice)) : 0u;
+    int st_push;
+    if (n_slices >= 2)
+      st_push = wide ? run_join_sharded_push_streamed<int64_t>(ctx, build_shard, probe_shard, mode, st, out_info, desc.data(), xp_bits, n_slices, &fell_back)
+                     : run_join_sharded_push_streamed<int32_t>(ctx, build_shard, probe_shard, mode, st, out_info, desc.data(), xp_bits, n_slices, &fell_back);
+    else
+      st_push = wide ? run_join_sharded_push<int64_t>(ctx, build_shard, probe_shard, mode, st, out_info, desc.data(), xp_bits, &fell_back)
+                     : run_join_sharded_push<int32_t>(ctx, build_shard, probe_shard, mode, st, out_info, desc.data(), xp_bits, &fell_back);
     if (st_push != HJ_OK) return st_push;
-    if (!fell_back) return check_reference_flags(ctx, rw);
+    if (!fell_back) {
+      if (n_slices < 2) HJ_TRY(deliver_bound());
+      return check_reference_flags(ctx, rw);
+    }
     // a receive region overflowed on some rank (skew): every rank saw the flag and repeats the join on the general path
   }
   // Probe slices (same S on every rank): opt-in through hj_options.stream_slice_rows. Slicing bounds the receive buffers
@@ -1087,6 +1116,7 @@ int hj_join_sharded(hj_ctx* ctx, const hj_relation* build_shard, const hj_relati
     status = wide ? run_join_sharded<int64_t>(ctx, build_shard, probe_shard, mode, st, out_info)
                   : run_join_sharded<int32_t>(ctx, build_shard, probe_shard, mode, st, out_info);
   if (status != HJ_OK) return status;
+  HJ_TRY(deliver_bound());
   return check_reference_flags(ctx, rw);
 }
 

@@ -35,6 +35,7 @@ struct XpushArgs {
   uint32_t* cursor;                // [kMaxRanks] chunks taken per destination (sender-local)
   uint32_t* overflow;              // raised when a region is full
   uint32_t cap_chunks;             // chunks per region
+  uint32_t pos_base;               // position of the relation's first row in the rank's shard (slices of a streamed join)
   uint32_t n_ranks;
   int null_policy;                 // kNullDrop or kNullAsValue
 };
@@ -129,7 +130,7 @@ __global__ void __launch_bounds__(NT) k_xchg_push(const XpushArgs a) {
       }
     }
     vbar(v, VT);
-    const uint32_t pos0 = s.row_begin + r0;
+    const uint32_t pos0 = a.pos_base + s.row_begin + r0;
 #pragma unroll
     for (int u = 0; u < ITEMS; ++u) {
       if (packed[u] != kNoDigit) {
@@ -321,7 +322,7 @@ int run_join_sharded_push(hj_ctx* ctx, const hj_relation* build, const hj_relati
   PartState pst[2];
   struct RegionGuard {
     hj_ctx* c;
-    ~RegionGuard() { c->xp_region[2] = hj_ctx::XpRegion{}; c->xp_region[3] = hj_ctx::XpRegion{}; }
+    ~RegionGuard() { for (int i = 0; i < kSides; ++i) c->xp_region[i] = hj_ctx::XpRegion{}; }
   } guard{ctx};
   for (int side = 0; side < 2; ++side) {
     const auto* meta = static_cast<const uint32_t*>(ctx->xchg_recv_rids[side].p);
@@ -400,6 +401,250 @@ int run_join_sharded_push(hj_ctx* ctx, const hj_relation* build, const hj_relati
     for (uint32_t d = 0; d < R; ++d)
       if (d != me) sent += uint64_t(my_chunks[side * kMaxRanks + d]) * kXpChunk * sizeof(T);
   t.bytes_nvlink_sent = sent;  // whole chunks: at most one partly filled chunk per virtual CTA and region too many
+  return HJ_OK;
+}
+
+
+// ---- push exchange, streamed: host-resident shards, bound host outputs (hj_bind_output + hj_join_sharded) ---------------
+// The sharded counterpart of run_join_streamed: every rank cuts its probe shard into the SAME number S of slices (runs of
+// whole chunks). Per slice i: copy-in (stream copy_in) -> push into receive set i & 1 of every rank -> 1-word barrier -> local
+// join of what arrived against the build side's partitions (exchanged and partitioned once, before the first slice) ->
+// copy-out of the slice's PosLists into the bound host buffers (stream copy_out). Copy-in of slice i + 1 and copy-out of slice
+// i - 1 overlap with the exchange + join of slice i, so both PCIe directions and the SMs work concurrently.
+// Why two receive sets are enough: exchange and join of all slices run on ONE stream, so a rank enters barrier(i + 1) only
+// after its join of slice i; a peer that has passed barrier(i + 1) may therefore overwrite set i & 1 (slice i + 2).
+template <typename K>
+int run_join_sharded_push_streamed(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, int mode, cudaStream_t st,
+                                   hj_result_info* info, const unsigned long long* desc, int radix_bits, uint32_t S, bool* fell_back) {
+  using T = Tuple<K, false>;
+  NcclApi* nc = nccl_api();
+  ncclComm_t comm = static_cast<ncclComm_t>(ctx->nccl_comm);
+  const uint32_t R = ctx->n_ranks, me = ctx->rank;
+  const bool one_side = mode == HJ_MODE_SEMI || mode == HJ_MODE_ANTI;
+  const bool outer = mode == HJ_MODE_LEFT || mode == HJ_MODE_RIGHT;
+  const int probe_null_policy = outer ? kNullAsValue : kNullDrop;
+  const int bits2 = pass2_bits(radix_bits);
+  *fell_back = false;
+  Launches nl;
+  HJ_CUDA(ctx, cudaEventRecord(ctx->ev[0], st));
+  for (void* p : ctx->xchg_graveyard) cudaFree(p);
+  ctx->xchg_graveyard.clear();
+
+  // ---- my probe slices: runs of whole chunks with about the same number of rows; every rank has exactly S (possibly empty)
+  std::vector<uint32_t> cut(S + 1, probe->n_segs);
+  cut[0] = 0;
+  {
+    const uint64_t per = (probe->n_rows + S - 1) / S;
+    uint64_t acc = 0;
+    uint32_t k = 1;
+    for (uint32_t i = 0; i < probe->n_segs && k < S; ++i) {
+      acc += probe->segs[i].n_rows;
+      if (acc >= per * k) cut[k++] = i + 1;
+    }
+  }
+  auto slice_rel = [&](uint32_t i) {
+    hj_relation r{};
+    r.segs = probe->segs + cut[i];
+    r.n_segs = cut[i + 1] - cut[i];
+    r.location = probe->location;
+    r.n_rows = 0;
+    for (uint32_t k = 0; k < r.n_segs; ++k) r.n_rows += r.segs[k].n_rows;
+    return r;
+  };
+  // position of a slice's first row in the shard (regular shards: every chunk before it has 2^shift rows)
+  auto slice_pos = [&](uint32_t i) { return probe->n_segs > 1 ? cut[i] << ctx->xp_map[1].shift[me] : 0u; };
+
+  // ---- geometry: region capacities (same on every rank). Build: as in the one-shot exchange; probe: per slice
+  uint32_t cap_b, cap_p;
+  uint64_t max_build = 0, max_probe = 0;
+  for (uint32_t r = 0; r < R; ++r) {
+    max_build = std::max<uint64_t>(max_build, desc[size_t(r) * kXpDescWords + 0]);
+    max_probe = std::max<uint64_t>(max_probe, desc[size_t(r) * kXpDescWords + 1]);
+    const unsigned long long gb = desc[size_t(r) * kXpDescWords + 2], gp = desc[size_t(r) * kXpDescWords + 3];
+    ctx->xp_map[0].first_chunk[r] = static_cast<uint32_t>(gb);
+    ctx->xp_map[0].shift[r] = static_cast<int32_t>(gb >> 32);
+    ctx->xp_map[1].first_chunk[r] = static_cast<uint32_t>(gp);
+    ctx->xp_map[1].shift[r] = static_cast<int32_t>(gp >> 32);
+  }
+  auto cap_for = [&](uint64_t rows) {
+    const uint64_t expect = (rows + R - 1) / R;
+    return static_cast<uint32_t>((expect + expect / 16 + kXpChunk - 1) / kXpChunk) + kXpSlackChunks;
+  };
+  cap_b = cap_for(max_build);
+  // a slice holds at most one S-th of the largest shard plus one chunk of rounding (chunks are <= 2^shift rows)
+  uint64_t max_chunk = 1;
+  for (uint32_t r = 0; r < R; ++r) max_chunk = std::max<uint64_t>(max_chunk, desc[size_t(r) * kXpDescWords + 5]);
+  cap_p = cap_for((max_probe + S - 1) / S + max_chunk);
+
+  // ---- build shard + slice 0 staged; receive sets; handles
+  PreparedRel psb, psp[2];
+  hj_relation rel_s[2];
+  int local = prepare_relation(ctx, build, 0, kXpChunk, st, &psb);
+  rel_s[0] = slice_rel(0);
+  if (local == HJ_OK) local = prepare_relation(ctx, &rel_s[0], 1, kXpChunk, ctx->copy_in, &psp[0]);
+  if (local == HJ_OK && cudaEventRecord(ctx->ev_in[0], ctx->copy_in) != cudaSuccess) local = fail(ctx, HJ_ERR_CUDA, "cudaEventRecord failed");
+  const uint32_t caps[3] = {cap_b, cap_p, cap_p};
+  for (int set = 0; set < 3 && local == HJ_OK; ++set) {
+    local = ensure_exported(ctx, ctx->xchg_recv_keys[set], size_t(R) * caps[set] * kXpChunk * sizeof(T));
+    if (local == HJ_OK) local = ensure_exported(ctx, ctx->xchg_recv_rids[set], (size_t(kMaxRanks) + size_t(R) * caps[set]) * 4);
+  }
+  if (local == HJ_OK) local = ensure(ctx, ctx->xp_cursor, 64 * 4);
+  HJ_TRY(exchange_handles(ctx, st, local));
+  auto* cursor = static_cast<uint32_t*>(ctx->xp_cursor.p);  // [0..15] cursors of the push in flight, [32] overflow (sticky)
+  auto* bar_dev = static_cast<unsigned long long*>(ctx->xchg_cnt_dev.p);
+  HJ_CUDA(ctx, cudaMemsetAsync(cursor, 0, 64 * 4, st));
+  // every rank has finished reading its receive sets of an earlier join before anybody stores into them again
+  HJ_NCCL(ctx, nc->AllGather(bar_dev, bar_dev + kMaxRanks, 1, ncclUint64, comm, st));
+
+  auto push = [&](const PreparedRel& pr, int set, int null_policy, uint32_t pos_base) -> int {
+    XpushArgs a{};
+    XpushPublish pub{};
+    a.rel = pr.meta;
+    a.pos_base = pos_base;
+    a.cursor = cursor;
+    a.overflow = cursor + 32;
+    a.cap_chunks = caps[set];
+    a.n_ranks = R;
+    a.null_policy = null_policy;
+    for (uint32_t d = 0; d < R; ++d) {
+      char* tuples = static_cast<char*>(d == me ? ctx->xchg_recv_keys[set].p : ctx->xchg_peer[d][set * 3 + 0].ptr);
+      auto* meta = static_cast<uint32_t*>(d == me ? ctx->xchg_recv_rids[set].p : ctx->xchg_peer[d][set * 3 + 1].ptr);
+      if (!tuples || !meta) return fail(ctx, HJ_ERR_COMM, "rank %u has no mapping of rank %u's receive set %d", me, d, set);
+      a.dst_tuples[d] = tuples + size_t(me) * caps[set] * kXpChunk * sizeof(T);
+      a.dst_fill[d] = meta + kMaxRanks + size_t(me) * caps[set];
+      pub.dst[d] = meta + me;
+    }
+    HJ_CUDA(ctx, cudaMemsetAsync(cursor, 0, kMaxRanks * 4, st));
+    if (pr.meta.n_tiles) {
+      constexpr int VC = xp_virtual<K>();
+      auto k = k_xchg_push<K, kXpThreads, VC, int(kXpChunk)>;
+      const size_t smem = size_t(VC) * kXpChunk * sizeof(T);
+      HJ_TRY(set_smem(ctx, k, smem));
+      const uint32_t grid = std::min<uint32_t>((pr.meta.n_tiles + VC - 1) / VC, ctx->n_sms);
+      k<<<grid, kXpThreads, smem, st>>>(a);
+      HJ_LAUNCH_CHECK(ctx, "k_xchg_push");
+      nl.n++;
+    }
+    k_xchg_publish<<<1, 32, 0, st>>>(a.cursor, caps[set], R, pub);
+    HJ_LAUNCH_CHECK(ctx, "k_xchg_publish");
+    nl.n++;
+    // barrier "all stores of this push have landed"
+    HJ_NCCL(ctx, nc->AllGather(reinterpret_cast<unsigned long long*>(cursor + 32), bar_dev + kMaxRanks, 1, ncclUint64, comm, st));
+    return HJ_OK;
+  };
+  hj_segment seg[3][kMaxRanks];
+  hj_relation rrel[3];
+  auto recv_relation = [&](int set, int side) {
+    const auto* meta = static_cast<const uint32_t*>(ctx->xchg_recv_rids[set].p);
+    std::memset(seg[set], 0, sizeof(seg[set]));
+    for (uint32_t r = 0; r < R; ++r) {
+      seg[set][r].chunk_id = r;
+      seg[set][r].n_rows = caps[set] * kXpChunk;
+      seg[set][r].kind = HJ_SEG_VALUE;
+      seg[set][r].key_type = sizeof(K) == 8 ? HJ_KEY_INT64 : HJ_KEY_INT32;
+      seg[set][r].values = static_cast<const char*>(ctx->xchg_recv_keys[set].p) + size_t(r) * caps[set] * kXpChunk * sizeof(T);
+    }
+    rrel[set].segs = seg[set];
+    rrel[set].n_segs = R;
+    rrel[set].location = HJ_LOC_DEVICE;
+    rrel[set].n_rows = uint64_t(R) * caps[set] * kXpChunk;
+    ctx->xp_region[side].fill = meta + kMaxRanks;
+    ctx->xp_region[side].nchunks = meta;
+    ctx->xp_region[side].cap_chunks = caps[set];
+  };
+  struct RegionGuard {
+    hj_ctx* c;
+    ~RegionGuard() { for (int i = 0; i < kSides; ++i) c->xp_region[i] = hj_ctx::XpRegion{}; }
+  } guard{ctx};
+
+  // ---- build side: exchange + partition once
+  HJ_TRY(push(psb, 0, kNullDrop, 0));
+  PreparedRel pb, pp[2];
+  PartState sb, sp[2];
+  recv_relation(0, 3);  // sides: 0 build shard, 1 / 2 probe slices being staged, 3 received build rows, 4 / 5 received probe slices
+  HJ_TRY(prepare_relation(ctx, &rrel[0], 3, p1_tile<K>(), st, &pb));
+  HJ_TRY((stage_alloc<K, false>(ctx, pb, 3, radix_bits, bits2, &sb)));
+  HJ_TRY(stage_hist<K>(ctx, pb, 3, radix_bits, bits2, kNullAsValue, sb, st, &nl));
+  HJ_TRY((stage_pass2<K, false>(ctx, pb, 3, radix_bits, bits2, kNullAsValue, sb, st, &nl)));
+
+  auto* rb = static_cast<Readback*>(ctx->pinned);
+  auto* host_words = reinterpret_cast<unsigned long long*>(static_cast<char*>(ctx->pinned) + kPinnedCounts);
+  uint64_t total = 0, probe_tuples = 0, h2d = psb.h2d_bytes;
+  uint32_t overflow_parts = 0;
+  int max_passes = 0, status = HJ_OK;
+  for (uint32_t i = 0; i < S; ++i) {
+    const int cur = i & 1, nxt = (i + 1) & 1;
+    if (i + 1 < S) {  // stage the next slice into the other staging set, once the push that read it has run
+      if (i >= 1) HJ_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_in, ctx->ev_x[nxt], 0));
+      rel_s[nxt] = slice_rel(i + 1);
+      psp[nxt] = PreparedRel{};
+      HJ_TRY(prepare_relation(ctx, &rel_s[nxt], 1 + nxt, kXpChunk, ctx->copy_in, &psp[nxt]));
+      HJ_CUDA(ctx, cudaEventRecord(ctx->ev_in[nxt], ctx->copy_in));
+    }
+    HJ_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_in[cur], 0));
+    HJ_TRY(push(psp[cur], 1 + cur, probe_null_policy, slice_pos(i)));
+    HJ_CUDA(ctx, cudaEventRecord(ctx->ev_x[cur], st));  // staging set `cur` may be overwritten
+    if (i >= 2) HJ_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_out[cur], 0));  // result buffers of this set are free again
+    const int side = 4 + cur;
+    recv_relation(1 + cur, side);
+    pp[cur] = PreparedRel{};
+    HJ_TRY(prepare_relation(ctx, &rrel[1 + cur], side, p1_tile<K>(), st, &pp[cur]));
+    HJ_TRY((stage_alloc<K, false>(ctx, pp[cur], side, radix_bits, bits2, &sp[cur])));
+    HJ_TRY(stage_hist<K>(ctx, pp[cur], side, radix_bits, bits2, kNullAsValue, sp[cur], st, &nl));
+    HJ_TRY((stage_pass2<K, false>(ctx, pp[cur], side, radix_bits, bits2, kNullAsValue, sp[cur], st, &nl)));
+    HJ_CUDA(ctx, cudaMemcpyAsync(host_words, bar_dev + kMaxRanks, size_t(R) * 8, cudaMemcpyDeviceToHost, st));
+    int passes = 0;
+    HJ_TRY((probe_phase<K, false>(ctx, pb, pp[cur], sp[cur], 3, side, cur, radix_bits, bits2, mode, probe_null_policy, 2,
+                                  rrel[0].n_rows, rrel[1 + cur].n_rows, st, &nl, &passes, nullptr, nullptr)));
+    HJ_CUDA(ctx, cudaEventRecord(ctx->ev_done[cur], st));
+    for (uint32_t r = 0; r < R; ++r)
+      if (host_words[r]) *fell_back = true;  // a region overflowed somewhere: every rank sees it in the same slice
+    if (*fell_back) break;
+    const uint64_t rows = rb->out.n_rows;  // probe_phase synchronised the stream
+    probe_tuples += rb->n_probe_tuples;
+    overflow_parts = std::max(overflow_parts, rb->plan.n_overflow_parts);
+    max_passes = std::max(max_passes, passes);
+    h2d += psp[cur].h2d_bytes;
+    if (total + rows > ctx->bound_capacity) {
+      status = fail(ctx, HJ_ERR_CAPACITY, "bound output holds %llu rows, this rank's result has more (>= %llu after %u of %u probe slices)",
+                    (unsigned long long)ctx->bound_capacity, (unsigned long long)(total + rows), i + 1, S);
+      // (this rank keeps taking part in the remaining exchanges and barriers: the other ranks cannot know)
+    } else if (rows) {
+      HJ_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_out, ctx->ev_done[cur], 0));
+      if (!one_side)
+        HJ_CUDA(ctx, cudaMemcpyAsync(ctx->bound_build + total, ctx->out_build[cur].p, rows * 8, cudaMemcpyDeviceToHost, ctx->copy_out));
+      HJ_CUDA(ctx, cudaMemcpyAsync(ctx->bound_probe + total, ctx->out_probe[cur].p, rows * 8, cudaMemcpyDeviceToHost, ctx->copy_out));
+    }
+    HJ_CUDA(ctx, cudaEventRecord(ctx->ev_out[cur], ctx->copy_out));
+    if (status == HJ_OK) total += rows;
+  }
+  HJ_CUDA(ctx, cudaEventRecord(ctx->ev[6], ctx->copy_out));
+  HJ_CUDA(ctx, cudaStreamSynchronize(ctx->copy_in));
+  HJ_CUDA(ctx, cudaStreamSynchronize(ctx->copy_out));
+  HJ_CUDA(ctx, cudaStreamSynchronize(st));
+  if (*fell_back) return HJ_OK;
+  if (status != HJ_OK) return status;
+
+  ctx->has_result = false;  // nothing left on the device: the PosLists are in the bound buffers
+  ctx->result_in_bound = true;
+  ctx->n_result = total;
+  ctx->n_sides = one_side ? 1 : 2;
+  info->n_rows = total;
+  info->n_sides = ctx->n_sides;
+  info->radix_bits = radix_bits;
+  info->n_build_tuples = rb->n_build_tuples;
+  info->n_probe_tuples = probe_tuples;
+  info->n_partitions = 1u << radix_bits;
+  info->n_overflow_partitions = overflow_parts;
+  info->n_probe_passes = max_passes;
+  info->n_probe_slices = S;
+  hj_timings& t = ctx->timings;
+  std::memset(&t, 0, sizeof(t));
+  t.ms[HJ_PH_TOTAL] = ev_ms(ctx->ev[0], ctx->ev[6]);
+  t.bytes_h2d = h2d;
+  t.bytes_d2h = total * 8 * ctx->n_sides;
+  t.n_kernel_launches = nl.n;
+  t.xchg_path = 2;
   return HJ_OK;
 }
 

@@ -109,6 +109,9 @@ def main():
     ap.add_argument("--radix-bits", type=int, default=-1,
                     help="nccl only: hj_options.radix_bits; > 8 makes the local join two-pass, which lets shards with regular "
                          "chunks (2^k rows) take the PUSH exchange (hj_xpush.cuh) on these small cases")
+    ap.add_argument("--bound", action="store_true",
+                    help="nccl only: hj_bind_output before every join (host outputs); with --radix-bits > 8 and a small --slice-rows "
+                         "the regular shards take the STREAMED push exchange (probe slices: copy-in, exchange + join, copy-out overlap)")
     ap.add_argument("--general", action="store_true", help="nccl only: HJ_FLAG_XCHG_GENERAL (never the push exchange)")
     ap.add_argument("--c5", type=float, default=0.0,
                     help="nccl only: add config C5 at this scale (0.01 = 40 M x 40 M int64, permutation build x uniform probe, "
@@ -167,8 +170,16 @@ def main():
             if args.backend == "nccl":
                 b_rel = make_shard(bk, bn, chunk, encoding, rank, world)
                 p_rel = make_shard(pk, pn, chunk, encoding, rank, world)
-                info = j.join_sharded(b_rel, p_rel, mode)
-                b, p = j.fetch()
+                if args.bound:
+                    cap = 10_000_000
+                    out_b = None if mode in ("Semi", "Anti") else np.empty((cap, 2), np.uint32)
+                    out_p = np.empty((cap, 2), np.uint32)
+                    j.bind_output(out_b, out_p)
+                    info = j.join_sharded(b_rel, p_rel, mode)
+                    b, p = j.fetch(out_b, out_p)
+                else:
+                    info = j.join_sharded(b_rel, p_rel, mode)
+                    b, p = j.fetch()
             else:
                 b, p = model_join(rank, world, bk, bn, pk, pn, chunk, encoding, mode, wide)
             parts = [None] * world

@@ -73,13 +73,17 @@ def test_sharded_join_nccl_2gpus():
     # joined) forced onto these small cases; then the PUSH exchange: --radix-bits 10 makes the local join two-pass, so the
     # shards with regular chunks take it (the irregular / gathered ones stay on the general path), and the same with
     # HJ_FLAG_XCHG_GENERAL as the control
-    for extra in ([], ["--staged"], ["--slice-rows", "700"], ["--radix-bits", "10"], ["--radix-bits", "10", "--general"]):
+    # ... and the STREAMED push exchange: bound host outputs, probe slices of >= 3000 rows (copy-in, exchange + join, copy-out overlap)
+    for extra in ([], ["--staged"], ["--slice-rows", "700"], ["--radix-bits", "10"], ["--radix-bits", "10", "--general"],
+                  ["--radix-bits", "10", "--bound", "--slice-rows", "3000"]):
         r = _torchrun(2, "--backend", "nccl", "--big", *extra)
         assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
         assert "MISMATCH" not in r.stdout and r.stdout.count(" OK") == 55
         if extra and extra[0] == "--slice-rows":
             assert "slices=8" in r.stdout and "slices=0" in r.stdout  # big cases sliced, the empty-build case not
-        if extra == ["--radix-bits", "10"]:
+        if "--bound" in extra:
+            assert r.stdout.count("exchange=push") == 40 and "slices=21" in r.stdout and "slices=24" in r.stdout, r.stdout[-3000:]
+        elif extra == ["--radix-bits", "10"]:
             # regular shards: the six 2^k cases, "empty build" (128-row chunks) and the 2M x 8M case
             assert r.stdout.count("exchange=push") == 40 and r.stdout.count("exchange=general") == 15, r.stdout[-3000:]
         else:
