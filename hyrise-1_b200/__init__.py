@@ -16,7 +16,9 @@ import numpy as np
 abi = importlib.import_module(__name__ + ".abi")
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libhj.so")
+# HJ_LIB_VARIANT=name loads csrc/variants/libhj_<name>.so instead (tuning builds of tests/build_variants.sh; development only)
+LIB_PATH = (os.path.join(_HERE, "csrc", "variants", f"libhj_{os.environ['HJ_LIB_VARIANT']}.so") if os.environ.get("HJ_LIB_VARIANT")
+            else os.path.join(_HERE, "csrc", "libhj.so"))
 _lib = None
 
 

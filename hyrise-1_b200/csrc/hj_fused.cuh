@@ -433,9 +433,10 @@ __global__ void __launch_bounds__(NT) k_part1p(RelMeta rel, Tuple<K, false>* __r
       packed[u] = kNoDigit;
       const uint32_t i = u * VT + vt;
       if (i < cnt) {
-        const bool valid = (vb_cur >> u) & 1u;
+        bool valid = (vb_cur >> u) & 1u;
+        if constexpr (XCH) valid = kb[i].idx != kHoleIdx;  // the exchange pads its runs to 16-byte units with holes
         uint32_t d = kNoDigit;
-        if (valid || null_policy == kNullAsValue) {
+        if (valid || (!XCH && null_policy == kNullAsValue)) {
           uint32_t h;
           if constexpr (XCH) {
             const E e = kb[i];

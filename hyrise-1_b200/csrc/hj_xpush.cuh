@@ -24,6 +24,10 @@
 // all ranks see at the barrier; they then repeat the join on the general path.
 #pragma once
 
+#ifndef HJ_TUNE_XP_BULK
+#define HJ_TUNE_XP_BULK 1  // 1: k_xchg_push sends its runs with TMA bulk copies; 0: per-thread 8/16-byte stores
+#endif
+
 namespace hj {
 
 constexpr uint32_t kXpChunk = 2048;  // tuples per receive chunk = one pass-1 tile of the local join
@@ -41,7 +45,7 @@ struct XpushArgs {
 };
 
 // One physical CTA = VC virtual CTAs of VT threads (named barriers), each streaming its own tiles: c, c + G, ...
-// dynamic smem: VC * TILE * sizeof(Tuple<K>).
+// dynamic smem: VC * (TILE + kMaxRanks) * sizeof(Tuple<K>).
 template <typename K, int NT, int VC, int TILE>
 __global__ void __launch_bounds__(NT) k_xchg_push(const XpushArgs a) {
   using T = Tuple<K, false>;
@@ -49,7 +53,7 @@ __global__ void __launch_bounds__(NT) k_xchg_push(const XpushArgs a) {
   constexpr int ITEMS = TILE / VT;
   static_assert(TILE == kXpChunk && ITEMS >= 1 && ITEMS <= 32 && VT >= 32 && kMaxRanks * 2 <= 32, "a tile's run to one destination fits one chunk");
   extern __shared__ __align__(16) unsigned char s_raw[];
-  T* stage = reinterpret_cast<T*>(s_raw) + static_cast<size_t>(threadIdx.x / VT) * TILE;
+  T* stage = reinterpret_cast<T*>(s_raw) + static_cast<size_t>(threadIdx.x / VT) * (TILE + kMaxRanks);  // + one hole per run
   __shared__ uint32_t s_cnt[VC][32], s_loff[VC][32];
   __shared__ uint32_t s_run[VC][kMaxRanks], s_n[VC][kMaxRanks];                              // this tile's run per destination
   __shared__ uint32_t s_pos0[VC][kMaxRanks], s_first[VC][kMaxRanks], s_pos1[VC][kMaxRanks];  // ... and where it goes
@@ -102,15 +106,22 @@ __global__ void __launch_bounds__(NT) k_xchg_push(const XpushArgs a) {
     }
     vbar(v, VT);
     if (vt < 32) {
+#if HJ_TUNE_XP_BULK
+      // the previous tile's bulk copies (issued by threads of this warp) must have read the staging area before it is written
+      // again; until here they had the next tile's loads, gathers and ranking to drain into NVLink
+      asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+#endif
       // the virtual CTA's first warp, lane q = destination q: prefix sum -> where the tile's run for q is staged; then q's
       // run is placed: the rest of the open chunk, then a fresh one
       const uint32_t q = vt;
-      const uint32_t n = q < R ? s_cnt[v][q] : 0u;
+      const uint32_t real = q < R ? s_cnt[v][q] : 0u;
+      const uint32_t n = slab_pad<T>(real);  // runs of 8-byte tuples are padded to whole 16-byte units: bulk copies below
       const uint32_t ex = warp_incl_scan(n) - n;
       if (q < R) {
         s_loff[v][q] = ex;
         s_run[v][q] = ex;
         s_n[v][q] = n;
+        if (n != real) stage[ex + real] = hole_tuple<K>();  // skipped by the receiver's pass 1 (position = kHoleIdx)
         const uint32_t left = s_left[v][q], open = s_open[v][q];
         s_pos0[v][q] = open * kXpChunk + (kXpChunk - left);  // unused when left == 0
         s_first[v][q] = left;
@@ -145,6 +156,28 @@ __global__ void __launch_bounds__(NT) k_xchg_push(const XpushArgs a) {
         stage[s_loff[v][packed[u] >> 16] + (packed[u] & 0xFFFFu)] = t;
       }
     }
+#if HJ_TUNE_XP_BULK
+    // every run leaves with at most two bulk copies of the TMA engine (the part that fills the open chunk, the part that opens
+    // a fresh one) straight into the destination GPU's memory: thread 2q + part issues it. Sources, destinations and sizes
+    // are multiples of 16 bytes by construction (padded runs, 2048-tuple chunks).
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // the staged tuples, for the TMA engine's reads
+    vbar(v, VT);
+    if (vt < 2 * R) {
+      const uint32_t q = vt >> 1, part = vt & 1u;
+      const uint32_t n = s_n[v][q], first = min(s_first[v][q], n);
+      const uint32_t len = part ? n - first : first;
+      if (len) {
+        T* dst = static_cast<T*>(a.dst_tuples[q]) + (part ? s_pos1[v][q] : s_pos0[v][q]);
+        const T* src = stage + s_run[v][q] + (part ? first : 0u);
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_addr_of(src)),
+                     "r"(len * static_cast<uint32_t>(sizeof(T))) : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");  // waited for where the next tile needs the staging area
+      }
+    }
+  }
+  asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  vbar(v, VT);
+#else
     vbar(v, VT);
     for (uint32_t q = 0; q < R; ++q) {
       const uint32_t n = s_n[v][q];
@@ -156,6 +189,7 @@ __global__ void __launch_bounds__(NT) k_xchg_push(const XpushArgs a) {
     }
   }
   vbar(v, VT);
+#endif
   if (vt < R && s_open[v][vt] != kInvalid) a.dst_fill[vt][s_open[v][vt]] = kXpChunk - s_left[v][vt];
   __threadfence_system();  // the stores went to peer memory; the ranks meet at a barrier after XP2
 }
@@ -295,7 +329,7 @@ int run_join_sharded_push(hj_ctx* ctx, const hj_relation* build, const hj_relati
     if (ps_[side].meta.n_tiles) {
       constexpr int VC = xp_virtual<K>();
       auto k = k_xchg_push<K, kXpThreads, VC, int(kXpChunk)>;
-      const size_t smem = size_t(VC) * kXpChunk * sizeof(T);
+      const size_t smem = size_t(VC) * (kXpChunk + kMaxRanks) * sizeof(T);
       HJ_TRY(set_smem(ctx, k, smem));
       const uint32_t grid = std::min<uint32_t>((ps_[side].meta.n_tiles + VC - 1) / VC, ctx->n_sms);
       k<<<grid, kXpThreads, smem, st>>>(a);
@@ -518,7 +552,7 @@ int run_join_sharded_push_streamed(hj_ctx* ctx, const hj_relation* build, const 
     if (pr.meta.n_tiles) {
       constexpr int VC = xp_virtual<K>();
       auto k = k_xchg_push<K, kXpThreads, VC, int(kXpChunk)>;
-      const size_t smem = size_t(VC) * kXpChunk * sizeof(T);
+      const size_t smem = size_t(VC) * (kXpChunk + kMaxRanks) * sizeof(T);
       HJ_TRY(set_smem(ctx, k, smem));
       const uint32_t grid = std::min<uint32_t>((pr.meta.n_tiles + VC - 1) / VC, ctx->n_sms);
       k<<<grid, kXpThreads, smem, st>>>(a);
