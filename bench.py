@@ -516,7 +516,7 @@ def main():
         # input and writes the slab-local tuples, there is no separate scatter1 kernel, pass 2 gathers fragments
         phase_bytes["materialize"] = n_local * (w_in + t_real)
         del phase_bytes["scatter1"]
-        phase_kernel.update({"materialize": "k_part1", "scatter2": "k_scatter2f"})
+        phase_kernel.update({"materialize": "k_part1p<XCH>" if xpath == 2 else "k_part1", "scatter2": "k_scatter2t"})
     dom = max(phase_bytes, key=lambda p_: mean_ms[p_])
     traffic = None
     # dram bytes per launch from the committed `ncu --set full` capture — only while the kernels are the ones that were
@@ -526,7 +526,7 @@ def main():
         with open(tpath) as f:
             tj = json.load(f)
         if tj.get("csrc_sha256") == csrc_hash():
-            traffic = tj.get(phase_kernel[dom])
+            traffic = tj.get(phase_kernel[dom])  # per launch set: the kernel's launches of one join (build + probe side)
         else:
             log("profiles/traffic_c2_full.json was captured from other kernel sources: roofline.traffic = null")
     whole_bytes = (nb + npr) * (2 * w_in + 2 * t_bytes) + info.n_rows * 16

@@ -59,7 +59,7 @@ for spec in "$@"; do
                 python tests/profile_join.py --workload $w --scale $sc --joins 2 $6
              # what comes back is text (gpurun_out/ may hold 64 MiB): the raw metrics and the per-line source counters
              ncu -i gpurun_out/${TAG}_ncu$n.ncu-rep --page raw --csv > gpurun_out/${TAG}_ncu$n.raw.csv 2>/dev/null
-             ncu -i gpurun_out/${TAG}_ncu$n.ncu-rep --page source --csv --print-source cuda 2>/dev/null | gzip -9 > gpurun_out/${TAG}_ncu$n.source.csv.gz
+             ncu -i gpurun_out/${TAG}_ncu$n.ncu-rep --page source --csv --print-source sass,cuda 2>/dev/null | gzip -9 > gpurun_out/${TAG}_ncu$n.source.csv.gz
              ncu -i gpurun_out/${TAG}_ncu$n.ncu-rep --page details --csv 2>/dev/null | gzip -9 > gpurun_out/${TAG}_ncu$n.details.csv.gz
              [ $(stat -c %s gpurun_out/${TAG}_ncu$n.ncu-rep) -gt 12000000 ] && rm -f gpurun_out/${TAG}_ncu$n.ncu-rep ;;
     prof) run prof$n 300 python tests/profile_join.py --joins 3 $arg ;;
