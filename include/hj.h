@@ -477,9 +477,10 @@ int hj_aggregate_grouped_relation(hj_ctx* ctx, const hj_relation* group_column, 
 int hj_aggregate_relation(hj_ctx* ctx, const hj_relation* column, void* cuda_stream, hj_aggregate* out);
 
 /* ---- multi-GPU (one process per GPU) ---------------------------------------- */
-/* The exchange has no reference counterpart: both relations are split by the high bits of the
- * key hash so that every key's rows meet on one rank, exchanged with an NCCL all-to-all over
- * NVLink, and joined locally. RowIDs stay global, so per-rank results simply concatenate. */
+/* The exchange has no reference counterpart: both relations are split by a hash of the key so that
+ * every key's rows meet on one rank, exchanged over NVLink by the library's own kernels (stores into
+ * peer-mapped memory; NCCL carries the control words, or — HJ_FLAG_XCHG_STAGED — the data), and
+ * joined locally. RowIDs stay global, so per-rank results simply concatenate. */
 
 /* The rank (0..n_ranks-1) on which all rows with this key meet. Pure host arithmetic; the same function runs on the
  * device. `key_type` is the HASHED key type of the join (HJ_KEY_INT64 if either column is int64). */
@@ -492,7 +493,14 @@ int hj_comm_unique_id(uint8_t id[HJ_NCCL_UNIQUE_ID_BYTES]);
 int hj_comm_init(hj_ctx* ctx, const uint8_t id[HJ_NCCL_UNIQUE_ID_BYTES], int n_ranks, int rank);
 /* Collective: like hj_join, but `build`/`probe` are this rank's shard of the relations (segments
  * carry GLOBAL chunk ids); afterwards hj_fetch/hj_result_device return this rank's share of the
- * result. out_info counts are per rank. */
+ * result. out_info counts are per rank. Two exchanges, same results (hj_timings.xchg_path): the PUSH
+ * exchange for large joins over regular shards (VALUE / DICT chunks of 2^k rows with consecutive chunk
+ * ids; one sweep, finished tuples stored into the peers' memory, no count pass) and the GENERAL one
+ * for everything else. hj_bind_output before the call works as for hj_join; when every rank binds host
+ * outputs for host-resident shards of a large join, the join is streamed in probe slices (copy-in,
+ * exchange + join and copy-out overlap; the same number of slices on every rank). A rank-local failure
+ * before the exchange (allocation, IPC mapping) is agreed on by all ranks: all of them return an error
+ * (the failing rank its own, the others HJ_ERR_COMM) instead of one leaving the others in a collective. */
 int hj_join_sharded(hj_ctx* ctx, const hj_relation* build_shard, const hj_relation* probe_shard,
                     int mode, void* cuda_stream, hj_result_info* out_info);
 
