@@ -23,8 +23,14 @@ struct AggPartial {
   long long sum_i;              // integer columns: wrap-around int64 sum like the reference's int64_t accumulator
   double sum_d;                 // floating columns: sum of the values widened to double
   long long min_i, max_i;
-  double min_d, max_d;
+  double min_d, max_d;          // over the values that are not NaN
+  unsigned long long first;     // floating columns: (row order of the first non-NULL value) << 1 | (that value is NaN)
 };
+// MIN / MAX and NaN (aggregate.cpp:141-165): the first non-NULL value seeds the aggregate and is then replaced on plain
+// `<` / `>`, so a NaN that comes FIRST stays (nothing compares smaller or greater than it) and a NaN anywhere else replaces
+// nothing. The streaming kernels therefore keep min / max over the non-NaN values plus `first`; agg_min_max() below applies
+// the rule when the result is read.
+constexpr unsigned long long kAggNoFirst = ~0ull;
 
 constexpr int kAggThreads = 256;
 
@@ -36,6 +42,25 @@ __device__ __forceinline__ void agg_init(AggPartial& a) {
   a.max_i = INT64_MIN;
   a.min_d = __longlong_as_double(0x7FF0000000000000ll);   // +inf
   a.max_d = __longlong_as_double(0xFFF0000000000000ull);  // -inf
+  a.first = kAggNoFirst;
+}
+
+__host__ __device__ __forceinline__ bool agg_first_is_nan(unsigned long long first) { return first != kAggNoFirst && (first & 1ull); }
+__host__ __device__ __forceinline__ double agg_quiet_nan() {
+#ifdef __CUDA_ARCH__
+  return __longlong_as_double(0x7FF8000000000000ll);
+#else
+  const long long b = 0x7FF8000000000000ll;
+  double d;
+  memcpy(&d, &b, 8);
+  return d;
+#endif
+}
+// MIN / MAX of a floating column as the reference reports them
+__host__ __device__ __forceinline__ void agg_min_max(const AggPartial& a, double* mn, double* mx) {
+  const bool nan_first = agg_first_is_nan(a.first);
+  *mn = nan_first ? agg_quiet_nan() : a.min_d;
+  *mx = nan_first ? agg_quiet_nan() : a.max_d;
 }
 
 // b folded into a; a's rows come first (the order matters for nothing but the rounding of sum_d)
@@ -47,6 +72,7 @@ __device__ __forceinline__ void agg_merge(AggPartial& a, const AggPartial& b) {
   a.max_i = b.max_i > a.max_i ? b.max_i : a.max_i;
   a.min_d = b.min_d < a.min_d ? b.min_d : a.min_d;
   a.max_d = b.max_d > a.max_d ? b.max_d : a.max_d;
+  a.first = b.first < a.first ? b.first : a.first;
 }
 
 __device__ __forceinline__ AggPartial agg_shfl_down(const AggPartial& a, int delta) {
@@ -58,19 +84,23 @@ __device__ __forceinline__ AggPartial agg_shfl_down(const AggPartial& a, int del
   b.max_i = __shfl_down_sync(0xffffffffu, a.max_i, delta);
   b.min_d = __shfl_down_sync(0xffffffffu, a.min_d, delta);
   b.max_d = __shfl_down_sync(0xffffffffu, a.max_d, delta);
+  b.first = __shfl_down_sync(0xffffffffu, a.first, delta);
   return b;
 }
 
 // T: int32_t / int64_t / float / double — the column's type; float / double columns arrive as their bit patterns in
 // 4 / 8-byte integers (hj_gather_column), which is the same memory.
+// `order`: position of the row in the column's row order (only its order matters; used for floating columns).
 template <typename T>
-__device__ __forceinline__ void agg_add(AggPartial& a, T v) {
+__device__ __forceinline__ void agg_add(AggPartial& a, T v, unsigned long long order) {
   ++a.n_values;
   if constexpr (std::is_floating_point<T>::value) {
     const double d = static_cast<double>(v);
     a.sum_d += d;
     a.min_d = d < a.min_d ? d : a.min_d;  // value_smaller / value_greater: plain < and > (a NaN never replaces anything)
     a.max_d = d > a.max_d ? d : a.max_d;
+    const unsigned long long f = order << 1 | (d != d ? 1ull : 0ull);
+    a.first = f < a.first ? f : a.first;
   } else {
     const long long x = static_cast<long long>(v);
     a.sum_i = static_cast<long long>(static_cast<unsigned long long>(a.sum_i) + static_cast<unsigned long long>(x));
@@ -115,10 +145,10 @@ __global__ void __launch_bounds__(kAggThreads) k_aggregate_partial(const T* __re
     }
 #pragma unroll
     for (int u = 0; u < 4; ++u)
-      if (!z[u]) agg_add<T>(a, v[u]);
+      if (!z[u]) agg_add<T>(a, v[u], i + u * stride);
   }
   for (; i < n; i += stride)
-    if (!(nulls && __ldg(nulls + i))) agg_add<T>(a, __ldg(values + i));
+    if (!(nulls && __ldg(nulls + i))) agg_add<T>(a, __ldg(values + i), i);
   agg_block_store(a, s_part, partials + blockIdx.x);
 }
 
@@ -148,9 +178,10 @@ __global__ void __launch_bounds__(kAggThreads) k_aggregate_relation(RelMeta rel,
         raw = load_plain_key<K>(s, r0 + i);
       }
       if (!is_null) {
-        if constexpr (std::is_same<T, float>::value) agg_add<float>(a, __int_as_float(static_cast<int>(raw)));
-        else if constexpr (std::is_same<T, double>::value) agg_add<double>(a, __longlong_as_double(static_cast<long long>(raw)));
-        else agg_add<K>(a, raw);
+        const unsigned long long order = static_cast<unsigned long long>(tile) * TILE + i;  // tiles follow the chunk order
+        if constexpr (std::is_same<T, float>::value) agg_add<float>(a, __int_as_float(static_cast<int>(raw)), order);
+        else if constexpr (std::is_same<T, double>::value) agg_add<double>(a, __longlong_as_double(static_cast<long long>(raw)), order);
+        else agg_add<K>(a, raw, order);
       }
     }
   }
@@ -183,7 +214,11 @@ __global__ void __launch_bounds__(32) k_aggregate_final(const AggPartial* __rest
 //                          reference: "we do not guarantee a stable operation with regards to positions")
 // NULL is a group key of its own (slot `cap`), and so is the one key value that serves as the EMPTY marker (slot cap + 1).
 // Every probe loop is bounded by the table size; a full global table raises *overflow instead of spinning.
-// MIN / MAX of float / double columns are kept as order-preserving int64 images of the doubles (sortable()).
+// MIN / MAX of float / double columns are kept as order-preserving int64 images of the doubles (sortable()), over the values
+// that are not NaN; `first` holds (row order of the group's first non-NULL value) << 1 | (it is NaN), and k_group_emit
+// reports NaN for the groups whose first value is one (the reference's rule, see AggPartial).
+// The global table is probed at most GroupTable::max_probes slots far; a row that finds no slot raises *overflow, stops its
+// thread, and the other threads stop at their next look at the flag: the host then repeats the aggregate with a larger table.
 // =====================================================================================================================
 constexpr long long kGroupEmpty = static_cast<long long>(0x8000000000000000ull);
 constexpr int kGroupSmemSlots = 256;  // power of two; + 2 special slots
@@ -197,8 +232,15 @@ struct GroupTable {  // structure of arrays, `cap` + 2 entries each (cap = power
   double* sum_d;
   long long* mn;
   long long* mx;
+  unsigned long long* first;
   unsigned long long cap;
+  unsigned long long max_probes;  // <= cap
 };
+constexpr int kGroupArrays = 8;  // 8-byte arrays of cap + 2 entries behind one allocation
+
+__device__ __forceinline__ bool group_overflowed(const uint32_t* overflow) {
+  return *reinterpret_cast<const volatile uint32_t*>(overflow) != 0;
+}
 
 __host__ __device__ __forceinline__ long long sortable(double d) {
 #ifdef __CUDA_ARCH__
@@ -240,14 +282,18 @@ __device__ __forceinline__ unsigned long long group_slot(long long* keys, unsign
 // one row's contribution (T = type of the aggregate column; has_value false: NULL value or COUNT(*) only)
 template <typename T>
 __device__ __forceinline__ void group_update(unsigned long long* rows, unsigned long long* values, long long* sum_i, double* sum_d,
-                                             long long* mn, long long* mx, unsigned long long s, bool has_value, T v) {
+                                             long long* mn, long long* mx, unsigned long long* first, unsigned long long s,
+                                             bool has_value, T v, unsigned long long order) {
   atomicAdd(rows + s, 1ull);
   if (!has_value) return;
   atomicAdd(values + s, 1ull);
   long long x;
   if constexpr (std::is_floating_point<T>::value) {
-    atomicAdd(sum_d + s, static_cast<double>(v));
-    x = sortable(static_cast<double>(v));
+    const double d = static_cast<double>(v);
+    atomicAdd(sum_d + s, d);
+    atomicMin(first + s, order << 1 | (d != d ? 1ull : 0ull));
+    if (d != d) return;  // a NaN replaces nothing
+    x = sortable(d);
   } else {
     x = static_cast<long long>(v);
     atomicAdd(reinterpret_cast<unsigned long long*>(sum_i + s), static_cast<unsigned long long>(x));
@@ -267,6 +313,7 @@ __global__ void k_group_init(GroupTable t) {
     t.sum_d[i] = 0.0;
     t.mn[i] = INT64_MAX;
     t.mx[i] = INT64_MIN;
+    t.first[i] = kAggNoFirst;
   }
 }
 
@@ -274,10 +321,11 @@ __global__ void k_group_init(GroupTable t) {
 template <typename GK, typename T>
 __global__ void __launch_bounds__(kAggThreads) k_group_accumulate(const GK* __restrict__ group_keys, const uint8_t* __restrict__ group_nulls,
                                                                   const T* __restrict__ values, const uint8_t* __restrict__ value_nulls,
-                                                                  unsigned long long n, GroupTable t, uint32_t* __restrict__ overflow) {
+                                                                  unsigned long long n, unsigned long long row_base, GroupTable t,
+                                                                  uint32_t* __restrict__ overflow) {
   constexpr int S = kGroupSmemSlots;
   __shared__ long long s_key[S + 2];
-  __shared__ unsigned long long s_rows[S + 2], s_values[S + 2];
+  __shared__ unsigned long long s_rows[S + 2], s_values[S + 2], s_first[S + 2];
   __shared__ long long s_sum_i[S + 2], s_mn[S + 2], s_mx[S + 2];
   __shared__ double s_sum_d[S + 2];
   for (int i = threadIdx.x; i < S + 2; i += kAggThreads) {
@@ -288,31 +336,35 @@ __global__ void __launch_bounds__(kAggThreads) k_group_accumulate(const GK* __re
     s_sum_d[i] = 0.0;
     s_mn[i] = INT64_MAX;
     s_mx[i] = INT64_MIN;
+    s_first[i] = kAggNoFirst;
   }
   __syncthreads();
   const unsigned long long stride = static_cast<unsigned long long>(gridDim.x) * kAggThreads;
+  uint32_t trip = 0;
   for (unsigned long long i = static_cast<unsigned long long>(blockIdx.x) * kAggThreads + threadIdx.x; i < n; i += stride) {
+    if ((trip++ & 15u) == 0 && group_overflowed(overflow)) break;
     const bool key_null = group_nulls && __ldg(group_nulls + i);
     const long long key = key_null ? 0 : static_cast<long long>(__ldg(group_keys + i));
     const bool has_value = values && !(value_nulls && __ldg(value_nulls + i));
     const T v = has_value ? __ldg(values + i) : T(0);
     if (key_null || key == kGroupEmpty) {  // the two special groups always have their shared-memory slot
-      group_update<T>(s_rows, s_values, s_sum_i, s_sum_d, s_mn, s_mx, key_null ? S : S + 1, has_value, v);
+      group_update<T>(s_rows, s_values, s_sum_i, s_sum_d, s_mn, s_mx, s_first, key_null ? S : S + 1, has_value, v, row_base + i);
       continue;
     }
     const unsigned long long s = group_slot(s_key, S - 1, key, kGroupSmemProbes);
     if (s != ~0ull) {
-      group_update<T>(s_rows, s_values, s_sum_i, s_sum_d, s_mn, s_mx, s, has_value, v);
+      group_update<T>(s_rows, s_values, s_sum_i, s_sum_d, s_mn, s_mx, s_first, s, has_value, v, row_base + i);
     } else {  // the CTA's table has no room for this group: straight to the global table
-      const unsigned long long g = group_slot(t.key, t.cap - 1, key, t.cap);
+      const unsigned long long g = group_slot(t.key, t.cap - 1, key, t.max_probes);
       if (g == ~0ull) {
         *overflow = 1;
-        continue;
+        break;
       }
-      group_update<T>(t.rows, t.values, t.sum_i, t.sum_d, t.mn, t.mx, g, has_value, v);
+      group_update<T>(t.rows, t.values, t.sum_i, t.sum_d, t.mn, t.mx, t.first, g, has_value, v, row_base + i);
     }
   }
   __syncthreads();
+  if (group_overflowed(overflow)) return;  // the table is discarded
   // merge this CTA's groups into the global table
   for (int i = threadIdx.x; i < S + 2; i += kAggThreads) {
     if (s_rows[i] == 0) continue;
@@ -320,10 +372,10 @@ __global__ void __launch_bounds__(kAggThreads) k_group_accumulate(const GK* __re
     if (i >= S) {
       g = t.cap + (i - S);
     } else {
-      g = group_slot(t.key, t.cap - 1, s_key[i], t.cap);
+      g = group_slot(t.key, t.cap - 1, s_key[i], t.max_probes);
       if (g == ~0ull) {
         *overflow = 1;
-        continue;
+        break;
       }
     }
     atomicAdd(t.rows + g, s_rows[i]);
@@ -333,6 +385,7 @@ __global__ void __launch_bounds__(kAggThreads) k_group_accumulate(const GK* __re
       atomicAdd(t.sum_d + g, s_sum_d[i]);
       atomicMin(t.mn + g, s_mn[i]);
       atomicMax(t.mx + g, s_mx[i]);
+      atomicMin(t.first + g, s_first[i]);
     }
   }
 }
@@ -368,8 +421,9 @@ __global__ void k_group_emit(GroupTable t, GroupRecord* __restrict__ out, unsign
     r.values = t.values[i];
     r.sum_i = t.sum_i[i];
     r.sum_d = t.sum_d[i];
-    r.mn = t.mn[i];
-    r.mx = t.mx[i];
+    const bool nan_first = agg_first_is_nan(t.first[i]);  // only floating aggregate columns set the bit
+    r.mn = nan_first ? sortable(agg_quiet_nan()) : t.mn[i];
+    r.mx = nan_first ? sortable(agg_quiet_nan()) : t.mx[i];
     r.key_is_null = i == t.cap ? 1 : 0;
     out[dst] = r;
   }
@@ -388,15 +442,19 @@ struct GroupColumns {
   const void* values[kMaxGroupColumns];
   const uint8_t* nulls[kMaxGroupColumns];
   uint32_t width[kMaxGroupColumns];  // 4 or 8 bytes per value
+  uint32_t floating[kMaxGroupColumns];  // float / double column: -0.0 groups with +0.0 (the reference compares values with ==)
   uint32_t n;
 };
 
-// raw value bits of column c at row r (0 for NULL: a NULL's stored value does not take part in the comparison)
+// raw value bits of column c at row r (0 for NULL: a NULL's stored value does not take part in the comparison; the bits of
+// +0.0 for a floating -0.0)
 __device__ __forceinline__ unsigned long long group_cell(const GroupColumns& g, uint32_t c, unsigned long long r, bool* is_null) {
   *is_null = g.nulls[c] && __ldg(g.nulls[c] + r);
   if (*is_null) return 0;
-  return g.width[c] == 4 ? static_cast<unsigned long long>(__ldg(static_cast<const uint32_t*>(g.values[c]) + r))
-                         : __ldg(static_cast<const unsigned long long*>(g.values[c]) + r);
+  const unsigned long long v = g.width[c] == 4 ? static_cast<unsigned long long>(__ldg(static_cast<const uint32_t*>(g.values[c]) + r))
+                                               : __ldg(static_cast<const unsigned long long*>(g.values[c]) + r);
+  const unsigned long long minus_zero = g.width[c] == 4 ? 0x80000000ull : 0x8000000000000000ull;
+  return g.floating[c] && v == minus_zero ? 0ull : v;
 }
 
 __device__ __forceinline__ bool group_rows_equal(const GroupColumns& g, unsigned long long a, unsigned long long b) {
@@ -443,6 +501,7 @@ __global__ void k_group_init_rows(GroupTable t) {  // like k_group_init with the
     t.sum_d[i] = 0.0;
     t.mn[i] = INT64_MAX;
     t.mx[i] = INT64_MIN;
+    t.first[i] = kAggNoFirst;
   }
 }
 
@@ -452,7 +511,7 @@ __global__ void __launch_bounds__(kAggThreads) k_group_accumulate_rows(GroupColu
                                                                        GroupTable t, uint32_t* __restrict__ overflow) {
   constexpr int S = kGroupSmemSlots;
   __shared__ unsigned long long s_rep[S];
-  __shared__ unsigned long long s_rows[S], s_values[S];
+  __shared__ unsigned long long s_rows[S], s_values[S], s_first[S];
   __shared__ long long s_sum_i[S], s_mn[S], s_mx[S];
   __shared__ double s_sum_d[S];
   for (int i = threadIdx.x; i < S; i += kAggThreads) {
@@ -463,34 +522,38 @@ __global__ void __launch_bounds__(kAggThreads) k_group_accumulate_rows(GroupColu
     s_sum_d[i] = 0.0;
     s_mn[i] = INT64_MAX;
     s_mx[i] = INT64_MIN;
+    s_first[i] = kAggNoFirst;
   }
   __syncthreads();
   auto* reps = reinterpret_cast<unsigned long long*>(t.key);
   const unsigned long long stride = static_cast<unsigned long long>(gridDim.x) * kAggThreads;
+  uint32_t trip = 0;
   for (unsigned long long i = static_cast<unsigned long long>(blockIdx.x) * kAggThreads + threadIdx.x; i < n; i += stride) {
+    if ((trip++ & 15u) == 0 && group_overflowed(overflow)) break;
     const bool has_value = values && !(value_nulls && __ldg(value_nulls + i));
     const T v = has_value ? __ldg(values + i) : T(0);
     const uint32_t h = group_row_hash(g, i);
     const unsigned long long s = group_row_slot(s_rep, S - 1, g, i, h, kGroupSmemProbes);
     if (s != ~0ull) {
-      group_update<T>(s_rows, s_values, s_sum_i, s_sum_d, s_mn, s_mx, s, has_value, v);
+      group_update<T>(s_rows, s_values, s_sum_i, s_sum_d, s_mn, s_mx, s_first, s, has_value, v, i);
     } else {
-      const unsigned long long gs = group_row_slot(reps, t.cap - 1, g, i, h, t.cap);
+      const unsigned long long gs = group_row_slot(reps, t.cap - 1, g, i, h, t.max_probes);
       if (gs == ~0ull) {
         *overflow = 1;
-        continue;
+        break;
       }
-      group_update<T>(t.rows, t.values, t.sum_i, t.sum_d, t.mn, t.mx, gs, has_value, v);
+      group_update<T>(t.rows, t.values, t.sum_i, t.sum_d, t.mn, t.mx, t.first, gs, has_value, v, i);
     }
   }
   __syncthreads();
+  if (group_overflowed(overflow)) return;  // the table is discarded
   for (int i = threadIdx.x; i < S; i += kAggThreads) {
     if (s_rows[i] == 0) continue;
     const unsigned long long r = s_rep[i];
-    const unsigned long long gs = group_row_slot(reps, t.cap - 1, g, r, group_row_hash(g, r), t.cap);
+    const unsigned long long gs = group_row_slot(reps, t.cap - 1, g, r, group_row_hash(g, r), t.max_probes);
     if (gs == ~0ull) {
       *overflow = 1;
-      continue;
+      break;
     }
     atomicAdd(t.rows + gs, s_rows[i]);
     if (s_values[i]) {
@@ -499,6 +562,7 @@ __global__ void __launch_bounds__(kAggThreads) k_group_accumulate_rows(GroupColu
       atomicAdd(t.sum_d + gs, s_sum_d[i]);
       atomicMin(t.mn + gs, s_mn[i]);
       atomicMax(t.mx + gs, s_mx[i]);
+      atomicMin(t.first + gs, s_first[i]);
     }
   }
 }

@@ -1342,7 +1342,7 @@ int check_ctx(hj_ctx* ctx) {
 
 // ------------------------------------------------------------------------------------------------ TableScan (N4)
 
-constexpr size_t kPinnedScanTotals = 3616, kPinnedAggregate = 3648;  // + one AggPartial (56 B), below kPinnedCounts  // two words inside the pinned readback area (behind kPinnedRefFlags)
+constexpr size_t kPinnedScanTotals = 3616, kPinnedAggregate = 3648;  // + one AggPartial (64 B), below kPinnedCounts  // two words inside the pinned readback area (behind kPinnedRefFlags)
 
 // K: integer type of the stored keys; V: type the comparison runs in (= K, or float / double over their bit patterns);
 // `value` the literal as V, `id_value` the literal the dictionary bounds are searched with (integer columns).
@@ -1417,15 +1417,25 @@ int run_scan(hj_ctx* ctx, const hj_relation* column, const hj_relation* original
 }
 
 
-// hj_aggregate_grouped*: the hash table (power of two >= 2 x the expected number of groups), one accumulate launch per
-// pair of device arrays, then count + emit
-int group_begin(hj_ctx* ctx, uint64_t n_rows, uint64_t max_groups, cudaStream_t st, GroupTable* out, bool row_keys = false) {
-  const uint64_t want = std::max<uint64_t>(1024, 2 * (max_groups ? std::min(max_groups, n_rows) : n_rows));
+// hj_aggregate_grouped*: the hash table (power of two >= `want_slots`), the accumulate launches, then count + emit.
+// Sizing (group_run): a caller's max_groups is taken at its word — 2 x max_groups slots, one attempt. Without one the number
+// of groups is unknown until the pass is over, and 2 x n_rows slots of 64 bytes (round 1) cost 128 bytes of HBM per input row:
+// the table starts at kGroupFirstSlots (or 2 x n_rows if that is less) and, when an accumulate launch reports it full
+// (bounded probing, see GroupTable::max_probes), is rebuilt 8 x larger and the launches are repeated, up to 2 x n_rows slots,
+// which cannot overflow. A retry costs one more pass over the group-by and aggregate columns; GROUP BYs with up to
+// kGroupFirstSlots / 2 groups never retry.
+constexpr uint64_t kGroupFirstSlots = uint64_t(1) << 20;  // 64 MB
+constexpr uint64_t kGroupProbeLimit = 1024;                // probes per lookup before a non-final table counts as full
+constexpr uint64_t kGroupProbeLimitFinal = 1 << 16;        // ... and the final one (half empty unless max_groups was wrong)
+constexpr int kGroupTableFull = 1;                         // group_finish -> group_run: the overflow flag was set
+
+int group_begin(hj_ctx* ctx, uint64_t want_slots, bool final_attempt, cudaStream_t st, GroupTable* out, bool row_keys = false) {
+  const uint64_t want = std::max<uint64_t>(1024, want_slots);
   uint64_t cap = 1024;
   while (cap < want) cap <<= 1;
   if (cap > (uint64_t(1) << 31)) return fail(ctx, HJ_ERR_TOO_LARGE, "group table of %llu slots: pass max_groups", (unsigned long long)cap);
   const size_t entries = size_t(cap) + 2;
-  HJ_TRY(ensure(ctx, ctx->group_table, entries * 8 * 7));
+  HJ_TRY(ensure(ctx, ctx->group_table, entries * 8 * kGroupArrays));
   HJ_TRY(ensure(ctx, ctx->group_misc, 16));
   char* base = static_cast<char*>(ctx->group_table.p);
   GroupTable& t = *out;
@@ -1436,7 +1446,9 @@ int group_begin(hj_ctx* ctx, uint64_t n_rows, uint64_t max_groups, cudaStream_t 
   t.sum_d = reinterpret_cast<double*>(base + entries * 32);
   t.mn = reinterpret_cast<long long*>(base + entries * 40);
   t.mx = reinterpret_cast<long long*>(base + entries * 48);
+  t.first = reinterpret_cast<unsigned long long*>(base + entries * 56);
   t.cap = cap;
+  t.max_probes = std::min(cap, final_attempt ? kGroupProbeLimitFinal : kGroupProbeLimit);
   HJ_CUDA(ctx, cudaMemsetAsync(ctx->group_misc.p, 0, 16, st));
   const uint32_t grid = static_cast<uint32_t>(std::min<uint64_t>((entries + 255) / 256, uint64_t(ctx->n_sms) * 8));
   if (row_keys) k_group_init_rows<<<grid, 256, 0, st>>>(t); else k_group_init<<<grid, 256, 0, st>>>(t);
@@ -1445,13 +1457,13 @@ int group_begin(hj_ctx* ctx, uint64_t n_rows, uint64_t max_groups, cudaStream_t 
 }
 
 int group_accumulate(hj_ctx* ctx, const GroupTable& t, const void* group_keys, const uint8_t* group_nulls, int group_key_type,
-                     const void* values, const uint8_t* value_nulls, int value_type, uint64_t n_rows, cudaStream_t st) {
+                     const void* values, const uint8_t* value_nulls, int value_type, uint64_t n_rows, uint64_t row_base, cudaStream_t st) {
   auto* overflow = reinterpret_cast<uint32_t*>(static_cast<char*>(ctx->group_misc.p) + 8);
   const uint32_t grid = static_cast<uint32_t>(std::max<uint64_t>(1, std::min<uint64_t>((n_rows + kAggThreads - 1) / kAggThreads,
                                                                                       uint64_t(ctx->n_sms) * 4)));
 #define HJ_GROUP_LAUNCH(GK, T)                                                                                                    \
   k_group_accumulate<GK, T><<<grid, kAggThreads, 0, st>>>(static_cast<const GK*>(group_keys), group_nulls, static_cast<const T*>(values), \
-                                                          value_nulls, n_rows, t, overflow)
+                                                          value_nulls, n_rows, row_base, t, overflow)
   const bool g64 = group_key_type == HJ_KEY_INT64;
   switch (value_type) {
     case HJ_KEY_INT32: if (g64) HJ_GROUP_LAUNCH(int64_t, int32_t); else HJ_GROUP_LAUNCH(int32_t, int32_t); break;
@@ -1464,8 +1476,8 @@ int group_accumulate(hj_ctx* ctx, const GroupTable& t, const void* group_keys, c
   return HJ_OK;
 }
 
-int group_finish(hj_ctx* ctx, const GroupTable& t, uint64_t n_rows, uint64_t max_groups, bool floating, cudaStream_t st,
-                 hj_group_info* out_info) {
+// returns kGroupTableFull (no error recorded) when an accumulate launch found the table full
+int group_finish(hj_ctx* ctx, const GroupTable& t, uint64_t n_rows, bool floating, cudaStream_t st, hj_group_info* out_info) {
   auto* n_groups = static_cast<unsigned long long*>(ctx->group_misc.p);
   const uint32_t grid = static_cast<uint32_t>(std::min<uint64_t>((t.cap + 2 + 255) / 256, uint64_t(ctx->n_sms) * 8));
   k_group_emit<<<grid, 256, 0, st>>>(t, nullptr, n_groups);  // count
@@ -1473,9 +1485,7 @@ int group_finish(hj_ctx* ctx, const GroupTable& t, uint64_t n_rows, uint64_t max
   auto* host = reinterpret_cast<unsigned long long*>(static_cast<char*>(ctx->pinned) + kPinnedAggregate);
   HJ_CUDA(ctx, cudaMemcpyAsync(host, ctx->group_misc.p, 16, cudaMemcpyDeviceToHost, st));
   HJ_CUDA(ctx, cudaStreamSynchronize(st));
-  if (reinterpret_cast<const uint32_t*>(host)[2])
-    return fail(ctx, HJ_ERR_CAPACITY, "more than %llu groups: the group table is full (max_groups was %llu)", (unsigned long long)t.cap,
-                (unsigned long long)max_groups);
+  if (reinterpret_cast<const uint32_t*>(host)[2]) return kGroupTableFull;
   const uint64_t n = host[0];
   HJ_TRY(ensure(ctx, ctx->group_out, std::max<uint64_t>(1, n) * sizeof(GroupRecord)));
   HJ_CUDA(ctx, cudaMemsetAsync(n_groups, 0, 8, st));
@@ -1491,6 +1501,26 @@ int group_finish(hj_ctx* ctx, const GroupTable& t, uint64_t n_rows, uint64_t max
   out_info->n_groups = n;
   out_info->n_rows = n_rows;
   return HJ_OK;
+}
+
+// table sizing + retry around `accumulate(const GroupTable&)`, which issues the accumulate launches of one attempt
+template <typename Accumulate>
+int group_run(hj_ctx* ctx, uint64_t n_rows, uint64_t max_groups, bool row_keys, bool floating, cudaStream_t st, hj_group_info* out_info,
+              Accumulate&& accumulate) {
+  const uint64_t full = 2 * (max_groups ? std::min(max_groups, n_rows) : n_rows);
+  uint64_t want = max_groups ? full : std::min(full, kGroupFirstSlots);
+  for (;;) {
+    const bool final_attempt = want >= full;
+    GroupTable t;
+    HJ_TRY(group_begin(ctx, want, final_attempt, st, &t, row_keys));
+    HJ_TRY(accumulate(t));
+    const int rc = group_finish(ctx, t, n_rows, floating, st, out_info);
+    if (rc != kGroupTableFull) return rc;
+    if (final_attempt)
+      return fail(ctx, HJ_ERR_CAPACITY, "more than %llu groups: the group table is full (max_groups was %llu)", (unsigned long long)t.cap,
+                  (unsigned long long)max_groups);
+    want = t.cap * 8;
+  }
 }
 
 // A2 + read-back shared by hj_aggregate_column and hj_aggregate_relation: partials[1 .. grid] -> partials[0] -> *out
@@ -1511,8 +1541,9 @@ int finish_aggregate(hj_ctx* ctx, AggPartial* partials, uint32_t grid, uint64_t 
   if (host->n_values) {
     out->min_int = floating ? 0 : host->min_i;
     out->max_int = floating ? 0 : host->max_i;
-    out->min_double = floating ? host->min_d : static_cast<double>(host->min_i);
-    out->max_double = floating ? host->max_d : static_cast<double>(host->max_i);
+    out->min_double = static_cast<double>(host->min_i);
+    out->max_double = static_cast<double>(host->max_i);
+    if (floating) agg_min_max(*host, &out->min_double, &out->max_double);
   }
   return HJ_OK;
 }
@@ -1825,7 +1856,7 @@ int hj_aggregate_column(hj_ctx* ctx, const void* device_values, const uint8_t* d
 namespace {
 
 // Scratch of hj_aggregate_column_static: [0] the folded result, [1..] one partial per CTA. File scope, so every GPU that
-// loads libhj holds these 112 KiB until the process exits. In HOST code `g_static_agg_partials` is only a stand-in for the
+// loads libhj holds these 128 KiB until the process exits. In HOST code `g_static_agg_partials` is only a stand-in for the
 // symbol, not a device address: the address comes from cudaGetSymbolAddress, once per device (static_agg_scratch).
 static __device__ __align__(256) AggPartial g_static_agg_partials[HJ_STATIC_AGG_MAX_PARTIALS + 1];
 
@@ -1875,8 +1906,9 @@ __global__ void __launch_bounds__(32) k_aggregate_final_out(const AggPartial* __
     if (a.n_values) {
       r.min_int = floating ? 0 : a.min_i;
       r.max_int = floating ? 0 : a.max_i;
-      r.min_double = floating ? a.min_d : static_cast<double>(a.min_i);
-      r.max_double = floating ? a.max_d : static_cast<double>(a.max_i);
+      r.min_double = static_cast<double>(a.min_i);
+      r.max_double = static_cast<double>(a.max_i);
+      if (floating) agg_min_max(a, &r.min_double, &r.max_double);
     }
     *out = r;
   }
@@ -1935,11 +1967,11 @@ int hj_aggregate_grouped(hj_ctx* ctx, const void* device_group_keys, const uint8
   if (!device_values) value_type = HJ_KEY_INT32;  // COUNT(*) only
   HJ_TRY(check_ctx(ctx));
   cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
-  GroupTable t;
-  HJ_TRY(group_begin(ctx, n_rows, max_groups, st, &t));
-  HJ_TRY(group_accumulate(ctx, t, device_group_keys, device_group_nulls, group_key_type, device_values, device_value_nulls, value_type,
-                          n_rows, st));
-  return group_finish(ctx, t, n_rows, max_groups, device_values && value_type >= HJ_KEY_FLOAT, st, out_info);
+  return group_run(ctx, n_rows, max_groups, /*row_keys=*/false, device_values && value_type >= HJ_KEY_FLOAT, st, out_info,
+                   [&](const GroupTable& t) -> int {
+                     return group_accumulate(ctx, t, device_group_keys, device_group_nulls, group_key_type, device_values,
+                                             device_value_nulls, value_type, n_rows, 0, st);
+                   });
 }
 
 int hj_aggregate_grouped_rows(hj_ctx* ctx, const hj_group_column* group_columns, uint32_t n_group_columns, const void* device_values,
@@ -1960,31 +1992,33 @@ int hj_aggregate_grouped_rows(hj_ctx* ctx, const hj_group_column* group_columns,
     g.values[c] = col.values;
     g.nulls[c] = col.nulls;
     g.width[c] = (col.key_type == HJ_KEY_INT64 || col.key_type == HJ_KEY_DOUBLE) ? 8u : 4u;
+    g.floating[c] = col.key_type >= HJ_KEY_FLOAT ? 1u : 0u;
   }
   if (device_values && (value_type < HJ_KEY_INT32 || value_type > HJ_KEY_DOUBLE)) return fail(ctx, HJ_ERR_INVALID, "value type %d", value_type);
   if (!device_values) value_type = HJ_KEY_INT32;
   HJ_TRY(check_ctx(ctx));
   cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
-  GroupTable t;
-  HJ_TRY(group_begin(ctx, n_rows, max_groups, st, &t, /*row_keys=*/true));
-  auto* overflow = reinterpret_cast<uint32_t*>(static_cast<char*>(ctx->group_misc.p) + 8);
   const uint32_t grid = static_cast<uint32_t>(std::max<uint64_t>(1, std::min<uint64_t>((n_rows + kAggThreads - 1) / kAggThreads,
                                                                                       uint64_t(ctx->n_sms) * 4)));
-  switch (value_type) {
-    case HJ_KEY_INT32:
-      k_group_accumulate_rows<int32_t><<<grid, kAggThreads, 0, st>>>(g, static_cast<const int32_t*>(device_values), device_value_nulls, n_rows, t, overflow);
-      break;
-    case HJ_KEY_INT64:
-      k_group_accumulate_rows<int64_t><<<grid, kAggThreads, 0, st>>>(g, static_cast<const int64_t*>(device_values), device_value_nulls, n_rows, t, overflow);
-      break;
-    case HJ_KEY_FLOAT:
-      k_group_accumulate_rows<float><<<grid, kAggThreads, 0, st>>>(g, static_cast<const float*>(device_values), device_value_nulls, n_rows, t, overflow);
-      break;
-    default:
-      k_group_accumulate_rows<double><<<grid, kAggThreads, 0, st>>>(g, static_cast<const double*>(device_values), device_value_nulls, n_rows, t, overflow);
-  }
-  HJ_LAUNCH_CHECK(ctx, "k_group_accumulate_rows");
-  return group_finish(ctx, t, n_rows, max_groups, device_values && value_type >= HJ_KEY_FLOAT, st, out_info);
+  return group_run(ctx, n_rows, max_groups, /*row_keys=*/true, device_values && value_type >= HJ_KEY_FLOAT, st, out_info,
+                   [&](const GroupTable& t) -> int {
+    auto* overflow = reinterpret_cast<uint32_t*>(static_cast<char*>(ctx->group_misc.p) + 8);
+    switch (value_type) {
+      case HJ_KEY_INT32:
+        k_group_accumulate_rows<int32_t><<<grid, kAggThreads, 0, st>>>(g, static_cast<const int32_t*>(device_values), device_value_nulls, n_rows, t, overflow);
+        break;
+      case HJ_KEY_INT64:
+        k_group_accumulate_rows<int64_t><<<grid, kAggThreads, 0, st>>>(g, static_cast<const int64_t*>(device_values), device_value_nulls, n_rows, t, overflow);
+        break;
+      case HJ_KEY_FLOAT:
+        k_group_accumulate_rows<float><<<grid, kAggThreads, 0, st>>>(g, static_cast<const float*>(device_values), device_value_nulls, n_rows, t, overflow);
+        break;
+      default:
+        k_group_accumulate_rows<double><<<grid, kAggThreads, 0, st>>>(g, static_cast<const double*>(device_values), device_value_nulls, n_rows, t, overflow);
+    }
+    HJ_LAUNCH_CHECK(ctx, "k_group_accumulate_rows");
+    return int(HJ_OK);
+  });
 }
 
 int hj_aggregate_grouped_rows_relation(hj_ctx* ctx, const hj_relation* const* group_columns, uint32_t n_group_columns,
@@ -2078,15 +2112,18 @@ int hj_aggregate_grouped_relation(hj_ctx* ctx, const hj_relation* group_column, 
   RefRewrite rg, rv;
   HJ_TRY(gather_references(ctx, group_column, 2, st, &rg, gtype, true));
   if (value_column) HJ_TRY(gather_references(ctx, value_column, 3, st, &rv, vtype, true));
-  GroupTable t;
-  HJ_TRY(group_begin(ctx, group_column->n_rows, max_groups, st, &t));
-  for (uint32_t i = 0; i < group_column->n_segs; ++i) {
-    const hj_segment& g = rg.segs[i];
-    if (!g.n_rows) continue;
-    HJ_TRY(group_accumulate(ctx, t, g.values, g.nulls, static_cast<int>(gtype), value_column ? rv.segs[i].values : nullptr,
-                            value_column ? rv.segs[i].nulls : nullptr, static_cast<int>(vtype), g.n_rows, st));
-  }
-  HJ_TRY(group_finish(ctx, t, group_column->n_rows, max_groups, value_column && vtype >= HJ_KEY_FLOAT, st, out_info));
+  HJ_TRY(group_run(ctx, group_column->n_rows, max_groups, /*row_keys=*/false, value_column && vtype >= HJ_KEY_FLOAT, st, out_info,
+                   [&](const GroupTable& t) -> int {
+    uint64_t row_base = 0;  // the chunks in order: the row order MIN / MAX's NaN rule refers to
+    for (uint32_t i = 0; i < group_column->n_segs; ++i) {
+      const hj_segment& g = rg.segs[i];
+      if (!g.n_rows) continue;
+      HJ_TRY(group_accumulate(ctx, t, g.values, g.nulls, static_cast<int>(gtype), value_column ? rv.segs[i].values : nullptr,
+                              value_column ? rv.segs[i].nulls : nullptr, static_cast<int>(vtype), g.n_rows, row_base, st));
+      row_base += g.n_rows;
+    }
+    return int(HJ_OK);
+  }));
   if (flags[2] || flags[3]) {
     ctx->group_valid = false;
     return fail(ctx, HJ_ERR_INVALID, "grouped aggregate: a PosList entry points outside the referenced table");

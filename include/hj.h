@@ -397,8 +397,10 @@ typedef struct hj_aggregate {
 /* device_values: n_rows values of type key_type (float / double as IEEE values or their bit patterns — the same
  * bytes); device_nulls: one byte per row or NULL. With n_values == 0 SUM / MIN / MAX / AVG are NULL in the
  * reference (:635-642) and the sum/min/max fields are 0. Double sums are folded in a fixed order (reproducible run
- * to run) that is not the reference's row order: they agree up to rounding. NaN values: unspecified, as in the
- * reference (it keeps a NaN only when it comes first). */
+ * to run) that is not the reference's row order: they agree up to rounding. NaN values in MIN / MAX follow the
+ * reference (aggregate.cpp:141-165: the first non-NULL value seeds the aggregate, later values replace it on plain
+ * < / >): MIN and MAX are NaN exactly when the column's first non-NULL value is a NaN, otherwise NaNs are ignored;
+ * the grouped entry points apply the same rule per group. */
 int hj_aggregate_column(hj_ctx* ctx, const void* device_values, const uint8_t* device_nulls, uint64_t n_rows,
                         int key_type, void* cuda_stream, hj_aggregate* out);
 
@@ -407,7 +409,7 @@ int hj_aggregate_column(hj_ctx* ctx, const void* device_values, const uint8_t* d
  * Same computation and same kernels' arithmetic as hj_aggregate_column (A1 one partial per CTA, A2 fold in CTA order: the
  * results are identical, double sums included), but it calls no cudaMalloc / cudaFree / allocating routine, does not
  * synchronise and copies nothing to the host: the per-CTA partials live in a file-scope `static __device__` array of
- * libhj (HJ_STATIC_AGG_MAX_PARTIALS + 1 records of 56 bytes = 112 KiB, held by every GPU that loads the library until
+ * libhj (HJ_STATIC_AGG_MAX_PARTIALS + 1 records of 64 bytes = 128 KiB, held by every GPU that loads the library until
  * the process exits), and the result is written to `device_out`, one hj_aggregate in DEVICE memory provided by the caller,
  * in stream order on `cuda_stream` (NULL = the context's own stream).
  * Limits: n_rows <= HJ_STATIC_AGG_MAX_ROWS, else HJ_ERR_TOO_LARGE with a message naming the limit; nothing is launched.
@@ -424,8 +426,10 @@ int hj_aggregate_column_static(hj_ctx* ctx, const void* device_values, const uin
  * device_group_keys / device_group_nulls: the group column of the n_rows input rows in device memory (int32 / int64;
  * typically hj_gather_column output in one slot), device_values / device_value_nulls / value_type: the aggregate
  * column in the same row order (another slot), or device_values == NULL for COUNT(*) alone. max_groups: an upper
- * bound of the number of groups if the caller has one (dictionary size, statistics), 0 = n_rows; the hash table takes
- * 56 bytes x 2 x that. HJ_ERR_CAPACITY if there are more groups than promised. The groups stay on the device until
+ * bound of the number of groups if the caller has one (dictionary size, statistics): the hash table takes 64 bytes x 2 x
+ * that, and HJ_ERR_CAPACITY is returned if there are more groups than promised. 0 = unknown: the table starts at 2^20
+ * slots (64 MB; less for small inputs) and, whenever the pass finds it full, is rebuilt 8 x larger and the pass repeated
+ * (at most 2 x n_rows slots, which always suffices). The groups stay on the device until
  * hj_aggregate_grouped_fetch copies them out (any order: the reference guarantees none, aggregate.hpp:45-47).
  * Double sums are accumulated with atomics: they agree with the reference up to rounding and are not bit-reproducible
  * from run to run. Several group-by columns: not built. */

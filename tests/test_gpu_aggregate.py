@@ -476,3 +476,139 @@ def test_reference_group_by_case_by_representative_rows_through_chunk_descriptor
         assert set(got) == set(expected)
         for key, row in expected.items():
             assert am.matches_reference(got[key][fn], row[j]), (key, fn, got[key], row, case["cite"])
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# MIN / MAX and NaN, -0.0 / +0.0 group keys, the growing group table
+# ------------------------------------------------------------------------------------------------------------------
+def same_or_both_nan(a, b):
+    return a == b or (isinstance(a, float) and isinstance(b, float) and np.isnan(a) and np.isnan(b))
+
+
+NAN_COLUMNS = {
+    # the reference seeds MIN / MAX with the first non-NULL value and replaces on plain < / > (aggregate.cpp:141-165): a NaN
+    # that comes first stays, a NaN anywhere else replaces nothing; the oracle walks the rows like the reference
+    "nan_first": ([np.nan, 3.0, -2.0, 8.5], [0, 0, 0, 0]),
+    "nan_first_after_nulls": ([7.0, np.nan, 3.0, -2.0], [1, 0, 0, 0]),
+    "nan_in_the_middle": ([3.0, np.nan, -2.0, 8.5], [0, 0, 0, 0]),
+    "nan_last": ([3.0, -2.0, 8.5, np.nan], [0, 0, 0, 0]),
+    "null_nan_first_is_skipped": ([np.nan, 3.0, -2.0, np.nan], [1, 0, 0, 0]),
+    "only_nans": ([np.nan, np.nan], [0, 0]),
+    "negative_nan_first": ([-np.nan, 1.0, 2.0], [0, 0, 0]),
+}
+
+
+@pytest.mark.parametrize("name", list(NAN_COLUMNS))
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("tail", [0, 70_001])
+def test_min_max_keep_a_nan_only_when_it_comes_first(ctx, name, dtype, tail):
+    """Ungrouped, all three entry points (device arrays, chunk descriptors, the no-allocation one); `tail` appends ordinary
+    rows so that the first value and the rest are seen by different CTAs."""
+    import ctypes as C
+    import torch
+    values, nulls = NAN_COLUMNS[name]
+    rng = np.random.default_rng(len(name) + tail)
+    v = np.concatenate([np.array(values, dtype=dtype), (rng.standard_normal(tail) * 100).astype(dtype)])
+    z = np.concatenate([np.array(nulls, dtype=np.uint8), (rng.random(tail) < 0.2).astype(np.uint8)])
+    want = ao.aggregate_column(v, z)
+    assert np.isnan(want["min"]) == name.replace("negative_", "").startswith(("nan_first", "only_nans")), "the oracle follows the reference"
+    tv, tz = torch.from_numpy(v).cuda(), torch.from_numpy(z).cuda()
+    kt = KEY_TYPES[np.dtype(dtype).name]
+    out = torch.empty(C.sizeof(abi.Aggregate), dtype=torch.uint8, device="cuda")
+    ctx.aggregate_column_static(tv.data_ptr(), tz.data_ptr(), len(v), kt, out.data_ptr())
+    torch.cuda.synchronize()
+    rel, keep = device_column(v, z, 4096)
+    for how, got in (("arrays", ctx.aggregate_column(tv.data_ptr(), tz.data_ptr(), len(v), kt)),
+                     ("static", hj.HashJoin.aggregate_record(out.cpu().numpy().tobytes())),
+                     ("chunks", ctx.aggregate_relation(rel))):
+        for k in ("min", "max"):
+            assert same_or_both_nan(got[k], want[k]), (how, k, got[k], want[k])
+        assert got["count"] == want["count"], how
+    del keep
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_grouped_min_max_keep_a_nan_only_when_it_comes_first_in_the_group(ctx, dtype):
+    """One group per NAN_COLUMNS entry (+ ordinary groups around them), rows of the groups interleaved; through the
+    one-integer-column table, the representative-row table and the chunk-descriptor entry point."""
+    rng = np.random.default_rng(77)
+    names = list(NAN_COLUMNS)
+    longest = max(len(NAN_COLUMNS[n][0]) for n in names)
+    gk, v, z = [], [], []
+    for i in range(longest):               # row i of every group, group after group: a group's rows keep their order
+        for g, n in enumerate(names):
+            values, nulls = NAN_COLUMNS[n]
+            if i < len(values):
+                gk.append(g), v.append(values[i]), z.append(nulls[i])
+    filler = 50_000
+    gk = np.concatenate([np.array(gk, np.int32), rng.integers(100, 400, filler).astype(np.int32)])
+    v = np.concatenate([np.array(v, dtype), (rng.standard_normal(filler) * 10).astype(dtype)])
+    z = np.concatenate([np.array(z, np.uint8), (rng.random(filler) < 0.1).astype(np.uint8)])
+    gz = np.zeros(len(gk), np.uint8)
+    want = grouped_want(gk, gz, v, z)
+    assert any(w["min"] is not None and np.isnan(w["min"]) for w in want.values())
+    rel_g, keep_g = device_column(gk, gz, 8192)
+    rel_v, keep_v = device_column(v, z, 8192)
+    by_rows = grouped_rows_on_gpu(ctx, [(gk, gz)], v, z)
+    for how, got in (("one column", grouped_on_gpu(ctx, gk, gz, v, z)),
+                     ("representative rows", {k[0]: a for k, a in by_rows.items()}),
+                     ("chunks", ctx.aggregate_grouped_relation(rel_g, rel_v))):
+        assert set(got) == set(want), how
+        for key, w in want.items():
+            for k in ("min", "max"):
+                assert same_or_both_nan(got[key][k], w[k]), (how, key, k, got[key][k], w[k])
+            assert got[key]["count"] == w["count"], (how, key)
+    del keep_g, keep_v
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_minus_zero_and_plus_zero_are_one_group(ctx, dtype):
+    """The reference maps group-by values to ids through a map that compares with == (aggregate.cpp:254-300): -0.0 and +0.0
+    are one group. The device compares bit patterns and therefore canonicalises the zero first."""
+    rng = np.random.default_rng(3)
+    n = 40_000
+    gv = rng.integers(-3, 4, n).astype(dtype)
+    gv[gv == 0] = np.where(rng.random((gv == 0).sum()) < 0.5, dtype(-0.0), dtype(0.0))
+    assert np.signbit(gv[gv == 0]).any() and not np.signbit(gv[gv == 0]).all()
+    other = rng.integers(0, 3, n).astype(np.int32)
+    gz = np.zeros(n, np.uint8)
+    v = rng.integers(-50, 50, n).astype(np.int64)
+    for cols in ([(gv, gz)], [(other, gz), (gv, gz)]):
+        got = grouped_rows_on_gpu(ctx, cols, v, gz)   # keys are read from the representative rows: -0.0 == 0.0 == 0 in a dict
+        members = {}
+        for i in range(n):
+            members.setdefault(tuple(c[0][i].item() + 0.0 for c in cols), []).append(i)   # x + 0.0: -0.0 -> 0.0
+        assert len(got) == len(members) == (7 if len(cols) == 1 else 21)
+        for key, idx in members.items():
+            hit = [a for k, a in got.items() if all(float(x) == y for x, y in zip(k, key))]
+            assert len(hit) == 1 and hit[0]["count_rows"] == len(idx) and hit[0]["sum"] == int(v[idx].sum()), key
+
+
+def test_group_table_grows_when_no_bound_is_given(ctx):
+    """Without max_groups the table starts at 2^20 slots (64 MB) instead of 2 x n_rows; 1.2 M distinct keys do not fit,
+    the library notices (bounded probing), rebuilds the table 8 x larger and repeats the pass (group_run, hj_api.cu).
+    Checked vectorised on the fetched records: every key once, COUNT(*) = 1, SUM = the row's value."""
+    import ctypes as C
+    import torch
+    n = 1_200_000
+    rng = np.random.default_rng(5)
+    gk = (rng.permutation(n).astype(np.int64) - n // 2) * 7
+    v = rng.integers(-10**6, 10**6, n).astype(np.int64)
+    tg, tv = torch.from_numpy(gk).cuda(), torch.from_numpy(v).cuda()
+    for repeat in range(2):   # the second call starts small again and must grow again
+        info = abi.GroupInfo()
+        ctx._check(ctx._l.hj_aggregate_grouped(ctx._ctx, tg.data_ptr(), None, abi.KEY_INT64, tv.data_ptr(), None, abi.KEY_INT64, n, 0,
+                                               None, C.byref(info)))
+        assert info.n_groups == n and info.n_rows == n
+        groups = (abi.Group * n)()
+        ctx._check(ctx._l.hj_aggregate_grouped_fetch(ctx._ctx, groups, n))
+        rec = np.ctypeslib.as_array(groups)
+        order = np.argsort(rec["key"], kind="stable")
+        by_key = np.argsort(gk, kind="stable")
+        assert (rec["key"][order] == gk[by_key]).all()
+        assert (rec["agg"]["n_rows"] == 1).all() and (rec["agg"]["n_values"] == 1).all()
+        assert (rec["agg"]["sum_int"][order] == v[by_key]).all()
+        assert (rec["agg"]["min_int"][order] == v[by_key]).all() and (rec["agg"]["max_int"][order] == v[by_key]).all()
+    # a small GROUP BY right after it on the same context
+    small = grouped_on_gpu(ctx, np.array([1, 2, 1], np.int32), np.zeros(3, np.uint8), np.array([5, 6, 7], np.int32), np.zeros(3, np.uint8))
+    assert small[1]["sum"] == 12 and small[2]["sum"] == 6
