@@ -83,6 +83,15 @@ static_assert(sizeof(Tuple<int32_t, false>) == 8 && sizeof(Tuple<int32_t, true>)
 
 // vector loads of a partitioned tuple through the read-only path (evict-first .cs hints measured slower on B200: K1 +12 ms
 // with st.cs, passes +0.1..0.4 ms with ld.cs)
+// [p, p + bytes) requested into L2 by the TMA engine (one instruction; the range is widened to 16-byte bounds, which stay
+// inside the allocation: device buffers are 256-byte aligned and padded)
+__device__ __forceinline__ void bulk_prefetch_l2(const void* p, uint32_t bytes) {
+  if (bytes == 0) return;
+  const unsigned long long a0 = reinterpret_cast<unsigned long long>(p) & ~15ull;
+  const unsigned long long a1 = (reinterpret_cast<unsigned long long>(p) + bytes + 15ull) & ~15ull;
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a0), "r"(static_cast<uint32_t>(a1 - a0)) : "memory");
+}
+
 __device__ __forceinline__ Tuple<int32_t, false> ld_stream(const Tuple<int32_t, false>* p) {
   const uint2 v = __ldg(reinterpret_cast<const uint2*>(p));
   Tuple<int32_t, false> t;

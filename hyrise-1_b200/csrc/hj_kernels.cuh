@@ -765,6 +765,12 @@ __device__ __forceinline__ uint32_t table_insert(K* keys, uint32_t ns_mask, K ke
 #ifndef HJ_TUNE_OUT_CS
 #define HJ_TUNE_OUT_CS 0  // 1: result rows stored with st.global.cs (evict-first)
 #endif
+#ifndef HJ_TUNE_BP_NEXT
+// 1: k_build_probe takes its NEXT work item while the current one is joined (queue pop during the build, descriptor into
+// shared memory, the item's build tuples and first probe stripe requested into L2 by two bulk prefetches when the probe
+// phase starts), so that an item starts with a shared-memory read instead of an atomic + a dependent load + DRAM latency
+#define HJ_TUNE_BP_NEXT 0
+#endif
 #ifndef HJ_TUNE_FIND_ILP
 #define HJ_TUNE_FIND_ILP 1  // 1: first-bucket lookups of a warp's V rows in straight-line code (needs HJ_TUNE_BUCKET_FIND)
 #endif
@@ -965,6 +971,14 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K, PAY> a)
   uint8_t* s_rk = reinterpret_cast<uint8_t*>(s_grp + CAP);          // CAP, kRidXch only: source rank of every grouped build row
   __shared__ uint32_t s_wtot[NW + 1];
   __shared__ uint32_t s_item;
+#if HJ_TUNE_BP_NEXT
+  __shared__ WorkItem s_next_item;
+  uint32_t next_idx = 0;  // thread 0: the popped index on its way back from the atomic
+  if (threadIdx.x == 0) {
+    s_item = atomicAdd(a.queue_head, 1u);
+    if (s_item < a.plan->n_items) s_next_item = a.items[s_item];
+  }
+#endif
   // kRidXch: the shard geometry by rank, indexed per lane (a divergent index into the parameter bank would be serialised)
   __shared__ XchMap s_xmap[RM == kRidXch ? 2 : 1];
   if constexpr (RM == kRidXch) {
@@ -992,11 +1006,18 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K, PAY> a)
   if (threadIdx.x == 0) s_w[NS + 1] = 0;
 
   for (;;) {
+#if HJ_TUNE_BP_NEXT
+    __syncthreads();
+    const uint32_t item_idx = s_item;
+    if (item_idx >= n_items) break;
+    const WorkItem it = s_next_item;
+#else
     if (threadIdx.x == 0) s_item = atomicAdd(a.queue_head, 1u);
     __syncthreads();
     const uint32_t item_idx = s_item;
     if (item_idx >= n_items) break;
     const WorkItem it = a.items[item_idx];
+#endif
     const bool multi = it.flags & kItemMulti;
 
     // table size for this chunk: >= 2x the tuples (load factor <= 0.5) up to NS (then <= CAP/NS)
@@ -1045,6 +1066,9 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K, PAY> a)
       }
     }
     __syncthreads();
+#if HJ_TUNE_BP_NEXT
+    if (threadIdx.x == 0) next_idx = atomicAdd(a.queue_head, 1u);  // comes back while the counts are scanned
+#endif
 
     // ---- exclusive scan of the counts in slot order (warp-contiguous ranges), then the sentinel slot
     {
@@ -1105,6 +1129,18 @@ __global__ void __launch_bounds__(NT, 1) k_build_probe(const JoinArgs<K, PAY> a)
       }
     }
     __syncthreads();  // s_w[slot] is now (end of run << 16) | count
+#if HJ_TUNE_BP_NEXT
+    // every thread has read s_item / s_next_item (barriers above); the loop's top barrier publishes the new values
+    if (threadIdx.x == 0) {
+      s_item = next_idx;
+      if (next_idx < n_items) {
+        const WorkItem ni = a.items[next_idx];
+        s_next_item = ni;
+        bulk_prefetch_l2(a.build + ni.b_begin, ni.b_cnt * static_cast<uint32_t>(sizeof(Tuple<K, PAY>)));
+        bulk_prefetch_l2(a.probe + ni.p_begin, min(ni.p_cnt, static_cast<uint32_t>(NT * V)) * static_cast<uint32_t>(sizeof(Tuple<K, PAY>)));
+      }
+    }
+#endif
 
     // ---- probe: every warp walks its own rows (warp w: rows w*32V .. +32V of every NT*V-row stripe) without CTA barriers
     for (uint32_t base = warp * (32 * V); base < it.p_cnt; base += NT * V) {
