@@ -36,8 +36,20 @@ namespace {
 #ifndef HJ_TUNE_P1_VIRTUAL64
 #define HJ_TUNE_P1_VIRTUAL64 2
 #endif
-#ifndef HJ_TUNE_P2_THREADS
-#define HJ_TUNE_P2_THREADS 256
+// Pass-2 geometry and the split of the radix bits between the passes, per key width (profiles/r02_sweep_p1_p2_geometry*_c{2,3}.json,
+// r02_sweep_p2_occupancy_bpnext_c2.json; C2 = int32, C3 = int64, ms for P1 + pass 2):
+//   int32, 14 bits: 7 + 7 bits, 256 threads x 16, fill 14/16 (round 1)   7.47 + 5.08
+//                   6 + 8 bits                                            7.43 + 5.11   (P1: fewer digits to rank and scan)
+//                   6 + 8 bits, 512 threads x 16 (2 CTAs per SM)           7.37 + 5.02   (32-row fragments fill an 8192-tuple batch)
+//                   ... and fill 15/16                                     7.37 + 4.86   <- shipped
+//                   ... fill 16/16 / 13/16: pass 2 6.2 / 5.2; 1024 threads: 8.4; 512 x 8 or x 12 tuples, 3-4 CTAs per SM: 5.15-6.3
+//                   ... with 8 pass-1 streams of 1024 rows per SM: P1 7.16 but pass 2 5.06-5.30 (16-row fragments): no gain
+//   int64, 15 bits: 8 + 7, 256 x 8 (round 1) 15.2 + 18.7; 7 + 8: 15.3 + 18.9; 512 threads: 15.3 + 23.4  -> unchanged
+#ifndef HJ_TUNE_P2_THREADS32
+#define HJ_TUNE_P2_THREADS32 512
+#endif
+#ifndef HJ_TUNE_P2_THREADS64
+#define HJ_TUNE_P2_THREADS64 256
 #endif
 #ifndef HJ_TUNE_P2_ITEMS32
 #define HJ_TUNE_P2_ITEMS32 16
@@ -45,11 +57,17 @@ namespace {
 #ifndef HJ_TUNE_P2_ITEMS64
 #define HJ_TUNE_P2_ITEMS64 8
 #endif
-#ifndef HJ_TUNE_P2_MINBLOCKS
-#define HJ_TUNE_P2_MINBLOCKS (1024 / HJ_TUNE_P2_THREADS)
+#ifndef HJ_TUNE_P2_FILL16_32
+#define HJ_TUNE_P2_FILL16_32 15  // a pass-2 work item holds FILL16/16 of a batch on average
 #endif
-#ifndef HJ_TUNE_P2_FILL16
-#define HJ_TUNE_P2_FILL16 14  // a pass-2 work item holds FILL16/16 of a batch on average
+#ifndef HJ_TUNE_P2_FILL16_64
+#define HJ_TUNE_P2_FILL16_64 14
+#endif
+#ifndef HJ_TUNE_BITS2_DELTA32
+#define HJ_TUNE_BITS2_DELTA32 1  // two-pass split: pass 2 takes radix_bits / 2 + delta bits (both passes stay <= 8 bits)
+#endif
+#ifndef HJ_TUNE_BITS2_DELTA64
+#define HJ_TUNE_BITS2_DELTA64 0
 #endif
 #ifndef HJ_TUNE_PROBE_V
 #define HJ_TUNE_PROBE_V 4
@@ -58,7 +76,8 @@ template <typename K> struct Cfg;
 template <> struct Cfg<int32_t> {
   static constexpr int kItems1 = HJ_TUNE_ITEMS1_32;  // pass 1: 256 threads x 16 = 4096 rows per tile (32 KB staged)
   static constexpr int kItems2 = 16;      // pass 2: 4096 tuples per tile
-  static constexpr int kP2Items = HJ_TUNE_P2_ITEMS32;  // fused pass 2 (k_scatter2f): tuples per thread and batch
+  static constexpr int kP2Items = HJ_TUNE_P2_ITEMS32;  // fused pass 2 (k_scatter2t/f): tuples per thread and batch
+  static constexpr int kP2Threads = HJ_TUNE_P2_THREADS32, kP2Fill16 = HJ_TUNE_P2_FILL16_32, kBits2Delta = HJ_TUNE_BITS2_DELTA32;
   // fused pass 1 (k_part1): 4 virtual CTAs of 256 threads with 2048-row tiles. Same shared memory as 2 x 4096 (L1 left to
   // the dictionary gather), but four independent tile streams per SM keep the gather pipeline busier: C2 P1 8.54 -> 7.88 ms,
   // pass 2 +0.12 ms for the shorter fragments (profiles/r01_sweep_variants_c2_full.json)
@@ -70,6 +89,7 @@ template <> struct Cfg<int64_t> {
   static constexpr int kItems1 = 8;       // 2048 rows per tile (32 KB staged)
   static constexpr int kItems2 = 8;
   static constexpr int kP2Items = HJ_TUNE_P2_ITEMS64;
+  static constexpr int kP2Threads = HJ_TUNE_P2_THREADS64, kP2Fill16 = HJ_TUNE_P2_FILL16_64, kBits2Delta = HJ_TUNE_BITS2_DELTA64;
   static constexpr int kP1Tile = 2048, kP1Virtual = HJ_TUNE_P1_VIRTUAL64;
   static constexpr int kNS = 8192;
   static constexpr int kCap = 6144;
@@ -92,9 +112,17 @@ constexpr int kMinChunkShift = 8, kMaxChunkShift = HJ_TUNE_MAX_CHUNK_SHIFT;  // 
 constexpr int kVirtualCtasPerSm = 4;       // K1 / pass 1 tile ownership: G = min(n_tiles, 4 * SMs) virtual CTAs
 template <typename K> constexpr int tile1() { return kScatterThreads * Cfg<K>::kItems1; }
 template <typename K> constexpr int tile2() { return kScatterThreads * Cfg<K>::kItems2; }
-constexpr int kP2Threads = HJ_TUNE_P2_THREADS, kP2MinBlocks = HJ_TUNE_P2_MINBLOCKS;  // fused pass 2: CTA size and CTAs per SM
-template <typename K> constexpr int p2_tile() { return kP2Threads * Cfg<K>::kP2Items; }
+// fused pass 2: CTA size (per key width) and CTAs per SM (1024 threads per SM at 64 registers)
+#ifndef HJ_TUNE_P2_MINBLOCKS32
+#define HJ_TUNE_P2_MINBLOCKS32 (1024 / HJ_TUNE_P2_THREADS32)
+#endif
+template <typename K> constexpr int p2_min_blocks() { return sizeof(K) == 4 ? HJ_TUNE_P2_MINBLOCKS32 : 1024 / Cfg<K>::kP2Threads; }
+template <typename K> constexpr int p2_tile() { return Cfg<K>::kP2Threads * Cfg<K>::kP2Items; }
 template <typename K> constexpr int p1_tile() { return Cfg<K>::kP1Tile; }
+// rows per tile of the fused pass 1: column inputs p1_tile(); tuples received through the push exchange come in chunks of
+// kXpChunk (hj_xpush.cuh), and a chunk is a tile
+constexpr int kXpTile = 2048;
+template <typename K> constexpr uint32_t fused_tile(bool xch) { return xch ? uint32_t(kXpTile) : uint32_t(p1_tile<K>()); }
 // 12-byte RowID-carrying tuples of int32 keys: same tile sizes with twice the threads and half the rows per thread, so that
 // a thread's keys + RowIDs (pass 1) / three-word tuples (pass 2) fit the register file without spilling
 template <typename K, bool PAY> constexpr int scatter_threads() { return (PAY && sizeof(K) == 4) ? 2 * kScatterThreads : kScatterThreads; }
@@ -729,15 +757,13 @@ int set_smem(hj_ctx* ctx, KernelT kernel, size_t bytes) {
 // The fused path (hj_fused.cuh) and the two-sweep path cut a relation into tiles of different sizes, so the choice is made
 // before prepare_relation builds the tile map. Rows received through the exchange carry RowIDs that only the two-sweep
 // kernels load (k_scatter1).
-#ifndef HJ_TUNE_BITS2_DELTA
-#define HJ_TUNE_BITS2_DELTA 0  // two-pass split: pass 2 takes radix_bits / 2 + delta bits (sweep builds; both passes stay <= 8 bits)
-#endif
 // low bits resolved by pass 2 (0: one pass)
-inline int pass2_bits(int radix_bits) {
+inline int pass2_bits(int radix_bits, bool wide) {
   if (radix_bits <= kSinglePassMaxBits) return 0;
-  const int b2 = radix_bits / 2 + HJ_TUNE_BITS2_DELTA;
+  const int b2 = radix_bits / 2 + (wide ? Cfg<int64_t>::kBits2Delta : Cfg<int32_t>::kBits2Delta);
   return std::max(radix_bits - 8, std::min(8, b2));
 }
+template <typename K> int pass2_bits(int radix_bits) { return pass2_bits(radix_bits, sizeof(K) == 8); }
 
 template <bool PAY>
 bool use_fused(const hj_ctx* ctx, int bits2, int side) {
@@ -745,7 +771,7 @@ bool use_fused(const hj_ctx* ctx, int bits2, int side) {
 }
 template <typename K, bool PAY>
 uint32_t tile_rows(const hj_ctx* ctx, int bits2, int side) {
-  return use_fused<PAY>(ctx, bits2, side) ? uint32_t(p1_tile<K>()) : uint32_t(tile1<K>());
+  return use_fused<PAY>(ctx, bits2, side) ? fused_tile<K>(ctx->xp_region[side].fill != nullptr) : uint32_t(tile1<K>());
 }
 
 struct PartState {
@@ -784,8 +810,10 @@ int stage_alloc(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, in
   ps->fused = use_fused<PAY>(ctx, bits2, side);
   ps->xch = ps->fused && ctx->xp_region[side].fill != nullptr;
   if (ps->fused) {
-    // an item gathers gs fragments of p1_tile/F1 tuples on average: HJ_TUNE_P2_FILL16/16 = 7/8 of a pass-2 batch (k_scatter2f needs gs < its CTA size and keeps fragment owners in 8 bits)
-    ps->gs = std::min<uint32_t>(std::min(kP2Threads - 1, 255), std::max<uint64_t>(1, uint64_t(p2_tile<K>()) * HJ_TUNE_P2_FILL16 / 16 * F1 / p1_tile<K>()));
+    // an item gathers gs fragments of tile/F1 tuples on average: kP2Fill16/16 of a pass-2 batch. One fragment per thread of the
+    // CTA at most (k_scatter2t issues one bulk copy per thread; k_scatter2f also keeps fragment owners in 8 bits)
+    const uint32_t gs_max = HJ_TUNE_P2_TMA ? uint32_t(Cfg<K>::kP2Threads) : uint32_t(std::min(Cfg<K>::kP2Threads - 1, 255));
+    ps->gs = std::min<uint32_t>(gs_max, std::max<uint64_t>(1, uint64_t(p2_tile<K>()) * Cfg<K>::kP2Fill16 / 16 * F1 / fused_tile<K>(ps->xch)));
     HJ_TRY(ensure(ctx, ctx->frag[side], std::max<size_t>(1, pr.meta.n_tiles) * (F1 + 2) * 2));
     ps->slab = tile_rows<K, PAY>(ctx, bits2, side) + F1 + 2;
     if (uint64_t(pr.meta.n_tiles) * ps->slab >= 0xFFFFFFFFull)
@@ -820,10 +848,10 @@ int stage_hist(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int
       constexpr int VCW = sizeof(K) == 4 ? 4 : 2;
       auto smem_for = [&](int vc) {
         return ((((size_t(1) << radix_bits) + 1) * 4 + 15) & ~size_t(15)) +
-               size_t(vc) * (size_t(p1_tile<K>()) * 2 * sizeof(Tuple<K, false>) + (p1_tile<K>() + kSlabPad) * 2);
+               size_t(vc) * (size_t(kXpTile) * 2 * sizeof(Tuple<K, false>) + (kXpTile + kSlabPad) * 2);
       };
       const bool wide = smem_for(VCW) + 12 * 1024 <= 227 * 1024;
-      auto k = wide ? k_part1p<K, kHistThreads, VCW, p1_tile<K>(), true> : k_part1p<K, kHistThreads, VCW / 2, p1_tile<K>(), true>;
+      auto k = wide ? k_part1p<K, kHistThreads, VCW, kXpTile, true> : k_part1p<K, kHistThreads, VCW / 2, kXpTile, true>;
       const int VC = wide ? VCW : VCW / 2;
       const size_t smem = smem_for(VC);
       HJ_TRY(set_smem(ctx, k, smem));
@@ -843,8 +871,6 @@ int stage_hist(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, int
   if (ps.fused) {
     if (pr.meta.n_tiles) {
       constexpr int VC = Cfg<K>::kP1Virtual;
-      if (F1 > uint32_t(kHistThreads / VC))  // cannot happen with the default geometry (VT >= kMaxDigits); HJ_TUNE_P1_SMALL_VT builds
-        return fail(ctx, HJ_ERR_INVALID, "this build of pass 1 scans at most %d level-1 digits, the join needs %u", kHistThreads / VC, F1);
 #if HJ_TUNE_P1_PIPE
       auto k = k_part1p<K, kHistThreads, VC, p1_tile<K>(), false>;
 #else
@@ -926,7 +952,7 @@ int stage_pass2(hj_ctx* ctx, const PreparedRel& pr, int side, int radix_bits, in
   if (!pr.meta.n_tiles || !bits2) return HJ_OK;
   if constexpr (!PAY) {
     if (ps.fused) {
-      constexpr int NT = kP2Threads;
+      constexpr int NT = Cfg<K>::kP2Threads, kP2MinBlocks = p2_min_blocks<K>();
       constexpr bool PREX = sizeof(K) == 4;  // push-exchanged int32 tuples carry the hash in the key field
 #if HJ_TUNE_P2_TMA
       auto k = ps.xch ? k_scatter2t<K, NT, Cfg<K>::kP2Items, kP2MinBlocks, PREX> : k_scatter2t<K, NT, Cfg<K>::kP2Items, kP2MinBlocks, false>;
@@ -1151,7 +1177,7 @@ int run_join(hj_ctx* ctx, const hj_relation* build, const hj_relation* probe, in
 
   const int radix_bits = ctx->opts.radix_bits >= 0 ? std::min(ctx->opts.radix_bits, kMaxRadixBits)
                                                    : radix_bits_for(build->n_rows, sizeof(K) == 8 ? HJ_KEY_INT64 : HJ_KEY_INT32);
-  const int bits2 = pass2_bits(radix_bits);
+  const int bits2 = pass2_bits<K>(radix_bits);
 
   PreparedRel pb, pp;
   HJ_TRY(prepare_relation(ctx, build, 0, tile_rows<K, PAY>(ctx, bits2, 0), st, &pb));
@@ -1219,7 +1245,7 @@ int run_join_streamed(hj_ctx* ctx, const hj_relation* build, const hj_relation* 
   HJ_CUDA(ctx, cudaEventRecord(ctx->ev[0], st));
   const int radix_bits = ctx->opts.radix_bits >= 0 ? std::min(ctx->opts.radix_bits, kMaxRadixBits)
                                                    : radix_bits_for(build->n_rows, sizeof(K) == 8 ? HJ_KEY_INT64 : HJ_KEY_INT32);
-  const int bits2 = pass2_bits(radix_bits);
+  const int bits2 = pass2_bits<K>(radix_bits);
   const int probe_null_policy = !outer ? kNullDrop : ((ctx->opts.flags & HJ_FLAG_SQL_NULL_PROBE) ? kNullRoute : kNullAsValue);
 
   // slices: runs of whole chunks with about the same number of rows

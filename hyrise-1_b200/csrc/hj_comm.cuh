@@ -1081,7 +1081,7 @@ int hj_join_sharded(hj_ctx* ctx, const hj_relation* build_shard, const hj_relati
   // expects, the same number on every rank
   const int xp_bits = ctx->opts.radix_bits >= 0 ? std::min(ctx->opts.radix_bits, kMaxRadixBits)
                                                 : radix_bits_for(total_build / ctx->n_ranks + 1, wide ? HJ_KEY_INT64 : HJ_KEY_INT32);
-  push = push && pass2_bits(xp_bits) > 0 && (1 << (xp_bits - pass2_bits(xp_bits))) >= ctx->n_ranks;
+  push = push && pass2_bits(xp_bits, wide) > 0 && (1 << (xp_bits - pass2_bits(xp_bits, wide))) >= ctx->n_ranks;
   if (push) {
     bool fell_back = false;
     // every rank bound host outputs for host-resident probe shards and the shards are long enough: streamed (copy-in, exchange

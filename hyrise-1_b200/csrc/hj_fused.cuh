@@ -169,10 +169,8 @@ __global__ void __launch_bounds__(NT) k_part1(RelMeta rel, Tuple<K, false>* __re
   using T = Tuple<K, false>;
   constexpr int VT = NT / VC;
   constexpr int ITEMS = TILE / VT;
-#ifndef HJ_TUNE_P1_SMALL_VT
-#define HJ_TUNE_P1_SMALL_VT 0  // 1: sweep builds with fewer threads per virtual CTA than kMaxDigits (the host refuses joins with F1 > VT)
-#endif
-  static_assert((VT >= kMaxDigits || HJ_TUNE_P1_SMALL_VT) && TILE <= 65535, "one thread per digit in the scan; 16-bit fragment offsets");
+  constexpr int DPT = (kMaxDigits + VT - 1) / VT;  // level-1 digits per thread in the scan of the tile's counts
+  static_assert(VT % 32 == 0 && TILE % VT == 0 && TILE <= 65535, "whole warps per virtual CTA; 16-bit fragment offsets");
   extern __shared__ __align__(16) unsigned char s_raw[];
   uint32_t* s_hist = reinterpret_cast<uint32_t*>(s_raw);
   const uint32_t P = 1u << radix_bits;
@@ -248,12 +246,23 @@ __global__ void __launch_bounds__(NT) k_part1(RelMeta rel, Tuple<K, false>* __re
     {
       // fragment starts are 16-byte aligned inside the slab (pass 2 fetches fragments with TMA bulk copies): a digit with an
       // odd number of 8-byte tuples is followed by a hole, a tuple whose position is kHoleIdx
-      const uint32_t cd = vt < F1 ? s_cnt[v][vt] : 0u;
+      uint32_t cd[DPT], mine = 0;  // thread vt scans digits vt * DPT .. + DPT
+#pragma unroll
+      for (int k = 0; k < DPT; ++k) {
+        const uint32_t d = vt * DPT + k;
+        cd[k] = d < F1 ? s_cnt[v][d] : 0u;
+        mine += slab_pad<T>(cd[k]);
+      }
       uint32_t total;
-      const uint32_t ex = vblock_excl_scan<VT>(slab_pad<T>(cd), v, vt, s_scratch[v], &total);
-      if (vt < F1) {
-        s_loff[v][vt] = ex;
-        if (slab_pad<T>(cd) != cd) stile[ex + cd] = hole_tuple<K>();
+      uint32_t ex = vblock_excl_scan<VT>(mine, v, vt, s_scratch[v], &total);
+#pragma unroll
+      for (int k = 0; k < DPT; ++k) {
+        const uint32_t d = vt * DPT + k;
+        if (d < F1) {
+          s_loff[v][d] = ex;
+          if (slab_pad<T>(cd[k]) != cd[k]) stile[ex + cd[k]] = hole_tuple<K>();
+          ex += slab_pad<T>(cd[k]);
+        }
       }
       if (vt == 0) {
         const uint32_t cn = s_cnt[v][F1];

@@ -30,7 +30,7 @@
 
 namespace hj {
 
-constexpr uint32_t kXpChunk = 2048;  // tuples per receive chunk = one pass-1 tile of the local join
+constexpr uint32_t kXpChunk = kXpTile;  // tuples per receive chunk = one pass-1 tile of the local join (hj_api.cu)
 
 struct XpushArgs {
   RelMeta rel;
@@ -263,7 +263,7 @@ int run_join_sharded_push(hj_ctx* ctx, const hj_relation* build, const hj_relati
   const bool one_side = mode == HJ_MODE_SEMI || mode == HJ_MODE_ANTI;
   const bool outer = mode == HJ_MODE_LEFT || mode == HJ_MODE_RIGHT;
   const int probe_null_policy = outer ? kNullAsValue : kNullDrop;  // kNullRoute never comes here
-  const int bits2 = pass2_bits(radix_bits);
+  const int bits2 = pass2_bits<K>(radix_bits);
   *fell_back = false;
   Launches nl;
   cudaEvent_t* ev = ctx->ev;
@@ -375,7 +375,7 @@ int run_join_sharded_push(hj_ctx* ctx, const hj_relation* build, const hj_relati
     ctx->xp_region[2 + side].fill = meta + kMaxRanks;
     ctx->xp_region[2 + side].nchunks = meta;
     ctx->xp_region[2 + side].cap_chunks = cap[side];
-    HJ_TRY(prepare_relation(ctx, &rel[side], 2 + side, p1_tile<K>(), st, &pr[side]));
+    HJ_TRY(prepare_relation(ctx, &rel[side], 2 + side, kXpTile, st, &pr[side]));
     HJ_TRY((stage_alloc<K, false>(ctx, pr[side], 2 + side, radix_bits, bits2, &pst[side])));
     if (!pst[side].xch) return fail(ctx, HJ_ERR_INVALID, "push exchange needs the fused partitioning path");
   }
@@ -457,7 +457,7 @@ int run_join_sharded_push_streamed(hj_ctx* ctx, const hj_relation* build, const 
   const bool one_side = mode == HJ_MODE_SEMI || mode == HJ_MODE_ANTI;
   const bool outer = mode == HJ_MODE_LEFT || mode == HJ_MODE_RIGHT;
   const int probe_null_policy = outer ? kNullAsValue : kNullDrop;
-  const int bits2 = pass2_bits(radix_bits);
+  const int bits2 = pass2_bits<K>(radix_bits);
   *fell_back = false;
   Launches nl;
   HJ_CUDA(ctx, cudaEventRecord(ctx->ev[0], st));
@@ -596,7 +596,7 @@ int run_join_sharded_push_streamed(hj_ctx* ctx, const hj_relation* build, const 
   PreparedRel pb, pp[2];
   PartState sb, sp[2];
   recv_relation(0, 3);  // sides: 0 build shard, 1 / 2 probe slices being staged, 3 received build rows, 4 / 5 received probe slices
-  HJ_TRY(prepare_relation(ctx, &rrel[0], 3, p1_tile<K>(), st, &pb));
+  HJ_TRY(prepare_relation(ctx, &rrel[0], 3, kXpTile, st, &pb));
   HJ_TRY((stage_alloc<K, false>(ctx, pb, 3, radix_bits, bits2, &sb)));
   HJ_TRY(stage_hist<K>(ctx, pb, 3, radix_bits, bits2, kNullAsValue, sb, st, &nl));
   HJ_TRY((stage_pass2<K, false>(ctx, pb, 3, radix_bits, bits2, kNullAsValue, sb, st, &nl)));
@@ -622,7 +622,7 @@ int run_join_sharded_push_streamed(hj_ctx* ctx, const hj_relation* build, const 
     const int side = 4 + cur;
     recv_relation(1 + cur, side);
     pp[cur] = PreparedRel{};
-    HJ_TRY(prepare_relation(ctx, &rrel[1 + cur], side, p1_tile<K>(), st, &pp[cur]));
+    HJ_TRY(prepare_relation(ctx, &rrel[1 + cur], side, kXpTile, st, &pp[cur]));
     HJ_TRY((stage_alloc<K, false>(ctx, pp[cur], side, radix_bits, bits2, &sp[cur])));
     HJ_TRY(stage_hist<K>(ctx, pp[cur], side, radix_bits, bits2, kNullAsValue, sp[cur], st, &nl));
     HJ_TRY((stage_pass2<K, false>(ctx, pp[cur], side, radix_bits, bits2, kNullAsValue, sp[cur], st, &nl)));
