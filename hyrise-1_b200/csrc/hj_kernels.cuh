@@ -768,7 +768,9 @@ __device__ __forceinline__ uint32_t table_insert(K* keys, uint32_t ns_mask, K ke
 #ifndef HJ_TUNE_BP_NEXT
 // 1: k_build_probe takes its NEXT work item while the current one is joined (queue pop during the build, descriptor into
 // shared memory, the item's build tuples and first probe stripe requested into L2 by two bulk prefetches when the probe
-// phase starts), so that an item starts with a shared-memory read instead of an atomic + a dependent load + DRAM latency
+// phase starts), so that an item starts with a shared-memory read instead of an atomic + a dependent load + DRAM latency.
+// Measured on C2: build+probe 6.09 -> 6.07 ms (profiles/r02_sweep_bits_fill_bpnext_c2.json, r02_sweep_p2_occupancy_bpnext_c2.json),
+// C3 unchanged, and the exchange instantiations spill 24-28 bytes with it: off — the start of an item is not what the kernel waits for
 #define HJ_TUNE_BP_NEXT 0
 #endif
 #ifndef HJ_TUNE_FIND_ILP
