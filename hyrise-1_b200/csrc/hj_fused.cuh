@@ -530,8 +530,8 @@ __global__ void __launch_bounds__(NT) k_part1p(RelMeta rel, Tuple<K, false>* __r
 // fastest, so the CTAs resident at one moment read the same slabs (frag table and slab lines are shared through L2) and
 // add to different cursors. The item's tuples are addressed through a flat index over its fragments: s_pre[] is the prefix
 // sum of the fragment lengths, s_own[k] the fragment holding flat index 32k, so a thread finds its fragment with one
-// lookup and a step or two, and all ITEMS loads of a thread are independent. gs is chosen so that an item holds 7/8 of
-// TILE tuples on average; an item that holds more (skew) is worked off in batches of TILE.
+// lookup and a step or two, and all ITEMS loads of a thread are independent. gs is chosen so that an item holds 14/16 or
+// 15/16 of TILE tuples on average (Cfg<K>::kP2Fill16); an item that holds more (skew) is worked off in batches of TILE.
 // d1 == F1 (only with kNullRoute): the routed NULL probe rows, copied behind the last partition (part_off[P]).
 // dynamic smem: TILE * sizeof(Tuple<K>).
 // =====================================================================================================================
@@ -691,7 +691,7 @@ __global__ void __launch_bounds__(NT, MINB) k_scatter2t(const Tuple<K, false>* _
   __shared__ __align__(8) Sm sm;
   const uint32_t P = 1u << radix_bits, F1 = P >> bits2, FS = F1 + 2u;
   const uint32_t group = blockIdx.x / n_digits, d1 = blockIdx.x % n_digits;
-  const uint32_t s0 = group * gs, ns = min(gs, n_tiles - s0);  // gs < NT
+  const uint32_t s0 = group * gs, ns = min(gs, n_tiles - s0);  // gs <= NT: one fragment per thread
   const bool null_item = d1 == F1;
   const uint32_t F2 = null_item ? 1u : 1u << bits2;
   uint32_t* cursors = cur2 + (null_item ? P : d1 << bits2);
@@ -721,7 +721,7 @@ __global__ void __launch_bounds__(NT, MINB) k_scatter2t(const Tuple<K, false>* _
 
     // the tile's tuples go to registers; a tuple's rank inside its digit is kept as 16 bits (two per register) and the digit
     // is re-derived from the key when the tuple is staged: 8 registers less than a (digit, rank) word per tuple, which is what
-    // the kernel needs to stay inside the 64 registers that four CTAs per SM allow without spilling
+    // the kernel needs to stay close to the 64 registers that 1024 resident threads per SM (2 CTAs of 512 / 4 of 256) allow
     static_assert(ITEMS % 2 == 0, "ranks are packed in pairs");
     T tup[ITEMS];
     uint32_t rank2[ITEMS / 2];
